@@ -1,0 +1,277 @@
+// TEST INFRASTRUCTURE — C ABI over the CPU oracle (oracle/h2o_tree_oracle.hpp) so that tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg can drive it through
+// ctypes. Never linked into, or called from, the product library (h2o-3_b200/).
+#include "h2o_tree_oracle.hpp"
+
+using namespace h2o_oracle;
+
+extern "C" {
+
+// ---------------------------------------------------------------- DHistogram
+void* orc_hist_new(int nbins, int nbins_cats, int isInt, double min, double maxEx, int intOpt, int initNA,
+                   double minSplitImprovement, long long seed, int checkFloatSplits) {
+  try {
+    return new DHistogram(nbins, nbins_cats, (uint8_t)isInt, min, maxEx, intOpt != 0, initNA != 0, minSplitImprovement,
+                          seed, checkFloatSplits != 0);
+  } catch (...) {
+    return nullptr;
+  }
+}
+void orc_hist_free(void* h) { delete (DHistogram*)h; }
+void orc_hist_init(void* h) { ((DHistogram*)h)->init(); }
+int orc_hist_nbin(void* h) { return ((DHistogram*)h)->_nbin; }
+double orc_hist_step(void* h) { return ((DHistogram*)h)->_step; }
+double orc_hist_min2(void* h) { return ((DHistogram*)h)->_min2; }
+double orc_hist_maxIn(void* h) { return ((DHistogram*)h)->_maxIn; }
+int orc_hist_bin(void* h, double x) { return ((DHistogram*)h)->bin(x); }
+void orc_hist_bin_many(void* h, const double* x, long long n, int* out) {
+  DHistogram* d = (DHistogram*)h;
+  for (long long i = 0; i < n; i++) out[i] = d->bin(x[i]);
+}
+double orc_hist_binAt(void* h, int b) { return ((DHistogram*)h)->binAt(b); }
+int orc_hist_nonEmptyBins(void* h) { return ((DHistogram*)h)->nonEmptyBins(); }
+void orc_hist_update(void* h, const double* ws, const double* cs, const double* ys, const int* rows, int hi, int lo) {
+  ((DHistogram*)h)->updateHisto(ws, cs, ys, rows, hi, lo);
+}
+void orc_hist_update_int(void* h, const double* ws, const int* cs, const double* ys, const int* rows, int hi, int lo) {
+  ((DHistogram*)h)->updateHistoInt(ws, cs, ys, rows, hi, lo);
+}
+void orc_hist_reduce_precision(void* h) { ((DHistogram*)h)->reducePrecision(); }
+int orc_hist_vals(void* h, double* out) {
+  DHistogram* d = (DHistogram*)h;
+  if (out) std::copy(d->_vals.begin(), d->_vals.end(), out);
+  return (int)d->_vals.size();
+}
+void orc_hist_set_vals(void* h, const double* in, int n) {
+  DHistogram* d = (DHistogram*)h;
+  if (!d->_has_vals) d->init();
+  for (int i = 0; i < n && i < (int)d->_vals.size(); i++) d->_vals[i] = in[i];
+}
+double orc_find_maxEx(double maxIn, int isInt) { return DHistogram::find_maxEx(maxIn, isInt); }
+
+struct OrcSplit {
+  int col, bin, nasplit, equal;
+  double se, se0, se1, n0, n1, p0, p1, tree_p0, tree_p1;
+  int bs_nbits, bs_bitoff, bs_nbytes;
+  unsigned char bs[132];
+};
+static void fill_split(const Split& s, OrcSplit* out) {
+  out->col = s._col;
+  out->bin = s._bin;
+  out->nasplit = s._nasplit;
+  out->equal = s._equal;
+  out->se = s._se;
+  out->se0 = s._se0;
+  out->se1 = s._se1;
+  out->n0 = s._n0;
+  out->n1 = s._n1;
+  out->p0 = s._p0;
+  out->p1 = s._p1;
+  out->tree_p0 = s._tree_p0;
+  out->tree_p1 = s._tree_p1;
+  out->bs_nbits = out->bs_bitoff = out->bs_nbytes = 0;
+  memset(out->bs, 0, sizeof(out->bs));
+  if (s._bs) {
+    out->bs_nbits = s._bs->_nbits;
+    out->bs_bitoff = s._bs->_bitoff;
+    out->bs_nbytes = (int)s._bs->_val.size();
+    for (int i = 0; i < out->bs_nbytes && i < 132; i++) out->bs[i] = s._bs->_val[i];
+  }
+}
+int orc_find_split(void* h, int col, double min_rows, OrcSplit* out) {
+  auto s = findBestSplitPoint(*(DHistogram*)h, col, min_rows);
+  if (!s) return 0;
+  fill_split(*s, out);
+  return 1;
+}
+float orc_splat_numeric(void* h, int bin, int nasplit) {
+  Split s;
+  s._col = 0;
+  s._bin = bin;
+  s._nasplit = nasplit;
+  s._equal = 0;
+  return s.splatNumeric(*(DHistogram*)h);
+}
+
+// ---------------------------------------------------------------- RNG / sampler
+void orc_pcg_floats(long long seed, int n, float* out) {
+  PCGRNG r(seed);
+  for (int i = 0; i < n; i++) out[i] = r.nextFloat();
+}
+void orc_pcg_ints(long long seed, int bound, int n, int* out) {
+  PCGRNG r(seed);
+  for (int i = 0; i < n; i++) out[i] = r.nextInt(bound);
+}
+long long orc_pcg_next_long(long long seed, int nth) {
+  PCGRNG r(seed);
+  long long v = 0;
+  for (int i = 0; i <= nth; i++) v = r.nextLong();
+  return v;
+}
+// T/Sample.java:22-36 on rows [row0,row0+n): out[i]=1 if the row is sampled OUT.
+void orc_sample(long long tree_seed, double rate, long long row0, long long n, unsigned char* out) {
+  PCGRNG rand(tree_seed);
+  for (long long i = 0; i < n; i++) {
+    rand.setSeed((int64_t)((uint64_t)tree_seed + (uint64_t)(row0 + i)));
+    out[i] = rand.nextFloat() >= rate ? 1 : 0;
+  }
+}
+// TT/DHistogramTest.java:173-206 input generator (java.util.Random(42))
+void orc_java_random_intopt_inputs(long long seed, int n, double* ys, int* dataInt) {
+  JavaRandom r(seed);
+  for (int i = 0; i < n; i++) {
+    ys[i] = r.nextGaussian();
+    dataInt[i] = 13 + r.nextInt(900);
+  }
+}
+int orc_equals_within_one_small_ulp_f(float a, float b) { return equalsWithinOneSmallUlp(a, b) ? 1 : 0; }
+
+// ---------------------------------------------------------------- Frame / GBM
+void* orc_frame_new(long long nrows, int ncols) {
+  Frame* f = new Frame();
+  f->cols.resize(ncols);
+  f->y.assign(nrows, 0.0);
+  return f;
+}
+void orc_frame_free(void* f) { delete (Frame*)f; }
+void orc_frame_set_col(void* f, int c, const double* v, int isCat, int cardinality) {
+  Frame* fr = (Frame*)f;
+  Column& col = fr->cols[c];
+  col.v.assign(v, v + fr->y.size());
+  col.isCat = isCat != 0;
+  col.cardinality = cardinality;
+  col.rollup();
+}
+void orc_frame_set_y(void* f, const double* y) { Frame* fr = (Frame*)f; std::copy(y, y + fr->y.size(), fr->y.begin()); }
+void orc_frame_set_w(void* f, const double* w) { Frame* fr = (Frame*)f; fr->w.assign(w, w + fr->y.size()); }
+void orc_frame_set_off(void* f, const double* o) { Frame* fr = (Frame*)f; fr->off.assign(o, o + fr->y.size()); }
+
+struct OrcParams {
+  int ntrees, max_depth, nbins, nbins_cats, nbins_top_level, family, nclass, nthreads;
+  double min_rows, min_split_improvement, sample_rate, col_sample_rate, col_sample_rate_per_tree,
+      col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
+  long long seed;
+  long long chunk_rows;
+};
+static Params to_params(const OrcParams* p) {
+  Params q;
+  q.ntrees = p->ntrees;
+  q.max_depth = p->max_depth;
+  q.nbins = p->nbins;
+  q.nbins_cats = p->nbins_cats;
+  q.nbins_top_level = p->nbins_top_level;
+  q.family = p->family;
+  q.nclass = p->nclass;
+  q.nthreads = p->nthreads;
+  q.min_rows = p->min_rows;
+  q.min_split_improvement = p->min_split_improvement;
+  q.sample_rate = p->sample_rate;
+  q.col_sample_rate = p->col_sample_rate;
+  q.col_sample_rate_per_tree = p->col_sample_rate_per_tree;
+  q.col_sample_rate_change_per_level = p->col_sample_rate_change_per_level;
+  q.learn_rate = p->learn_rate;
+  q.learn_rate_annealing = p->learn_rate_annealing;
+  q.max_abs_leafnode_pred = p->max_abs_leafnode_pred;
+  q.seed = p->seed;
+  return q;
+}
+
+void* orc_gbm_train(void* f, const OrcParams* p, int capture) {
+  try {
+    Params q = to_params(p);
+    GBM g(*(Frame*)f, q);
+    g.capture = capture != 0;
+    if (p->chunk_rows > 0) g.chunk_rows_ = p->chunk_rows;
+    g.train();
+    return new GBMModel(std::move(g.model));
+  } catch (const std::exception& e) {
+    fprintf(stderr, "orc_gbm_train: %s\n", e.what());
+    return nullptr;
+  }
+}
+void orc_model_free(void* m) { delete (GBMModel*)m; }
+double orc_model_init_f(void* m) { return ((GBMModel*)m)->init_f; }
+int orc_model_ntrees(void* m) { return (int)((GBMModel*)m)->trees.size(); }
+int orc_model_K(void* m) { return (int)((GBMModel*)m)->F.size(); }
+void orc_model_F(void* m, int k, double* out) {
+  auto& F = ((GBMModel*)m)->F[k];
+  std::copy(F.begin(), F.end(), out);
+}
+void orc_model_timing(void* m, double* t_hist, double* t_total, double* rowcols) {
+  GBMModel* g = (GBMModel*)m;
+  *t_hist = g->t_hist_s;
+  *t_total = g->t_total_s;
+  *rowcols = g->hist_rowcols;
+}
+void orc_model_varimp(void* m, float* out) {
+  auto& v = ((GBMModel*)m)->varimp;
+  std::copy(v.begin(), v.end(), out);
+}
+
+struct OrcNode {
+  int kind, pid, nid, nid0, nid1;
+  float splat, pred;
+  int has_split;
+  OrcSplit split;
+};
+int orc_model_tree_len(void* m, int t, int k) { return (int)((GBMModel*)m)->trees[t][k].nodes.size(); }
+int orc_model_tree_leaves_start(void* m, int t, int k) { return ((GBMModel*)m)->trees[t][k].leaves_start; }
+void orc_model_tree_nodes(void* m, int t, int k, OrcNode* out) {
+  const TreeOut& tr = ((GBMModel*)m)->trees[t][k];
+  for (size_t i = 0; i < tr.nodes.size(); i++) {
+    const Node& n = tr.nodes[i];
+    OrcNode& o = out[i];
+    memset(&o, 0, sizeof(o));
+    o.kind = n.kind;
+    o.pid = n._pid;
+    o.nid = n._nid;
+    o.nid0 = n._nids[0];
+    o.nid1 = n._nids[1];
+    o.splat = n._splat;
+    o.pred = n._pred;
+    o.has_split = n._split ? 1 : 0;
+    if (n._split) fill_split(*n._split, &o.split);
+  }
+}
+float orc_model_score_tree(void* m, int t, int k, const double* x) {
+  const TreeOut& tr = ((GBMModel*)m)->trees[t][k];
+  return scoreTree(tr, [&](int c) { return x[c]; });
+}
+
+// ---- level captures (histogram-monitor analogue)
+int orc_model_ncaptures(void* m) { return (int)((GBMModel*)m)->captures.size(); }
+void orc_capture_info(void* m, int i, int* tree, int* k, int* leaf, int* nleaves) {
+  const LevelCapture& c = ((GBMModel*)m)->captures[i];
+  *tree = c.tree;
+  *k = c.k;
+  *leaf = c.leaf;
+  *nleaves = c.nleaves;
+}
+struct OrcHistDesc {
+  int present, has_vals, isInt, intOpt, nbin;
+  double min, maxEx, step, min2, maxIn;
+};
+void orc_capture_desc(void* m, int i, int n, int c, int ncols, OrcHistDesc* out) {
+  const LevelCapture::Entry& e = ((GBMModel*)m)->captures[i].entries[(size_t)n * ncols + c];
+  out->present = e.present;
+  out->has_vals = e.has_vals;
+  out->isInt = e.isInt;
+  out->intOpt = e.intOpt;
+  out->nbin = e.nbin;
+  out->min = e.min;
+  out->maxEx = e.maxEx;
+  out->step = e.step;
+  out->min2 = e.min2;
+  out->maxIn = e.maxIn;
+}
+int orc_capture_vals(void* m, int i, int n, int c, int ncols, double* out) {
+  const LevelCapture::Entry& e = ((GBMModel*)m)->captures[i].entries[(size_t)n * ncols + c];
+  if (out) std::copy(e.vals.begin(), e.vals.end(), out);
+  return (int)e.vals.size();
+}
+void orc_capture_nids(void* m, int i, int* out) {
+  const auto& v = ((GBMModel*)m)->captures[i].nids_after;
+  std::copy(v.begin(), v.end(), out);
+}
+
+}  // extern "C"
