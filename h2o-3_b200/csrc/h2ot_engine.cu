@@ -1,0 +1,1070 @@
+// libh2otree_b200.so — engine state + the C ABI declared in include/h2ot.h.
+// One engine == one model build on one B200 (one process per GPU). No CPU fallback anywhere.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "k_level.cuh"
+#include "k_rows.cuh"
+#include "k_split.cuh"
+
+namespace h2ot {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+template <class T>
+struct DBuf {  // grow-only device buffer
+  T* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t n) {
+    if (n <= cap) return H2OT_OK;
+    if (p) CUDA_TRY(cudaFree(p));
+    p = nullptr;
+    cap = 0;
+    size_t want = std::max<size_t>(n, 16);
+    CUDA_TRY(cudaMalloc(&p, want * sizeof(T)));
+    cap = want;
+    return H2OT_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct Timer {  // CUDA-event timing of one kernel family inside an API call
+  cudaEvent_t a = nullptr, b = nullptr;
+  double* acc = nullptr;
+};
+
+struct Column {
+  void* data = nullptr;
+  double* staging = nullptr;
+  int storage = H2OT_STORE_F32;
+  double base = 0;
+  h2ot_column_info info{};
+  bool finalized = false;
+};
+
+struct TreeState {  // per class-tree k
+  double* F = nullptr;
+  float* work = nullptr;
+  int32_t* nids = nullptr;
+  uint16_t* code = nullptr;
+  DBuf<h2ot_decided_node> nodes;       // device node table indexed by nid
+  std::vector<h2ot_decided_node> h_nodes;  // host mirror
+  DBuf<uint8_t> bitsets;
+  std::vector<uint8_t> h_bitsets;
+  int n_nodes = 0;
+  double work_bound = 1.0;
+  int ey = 0, eyy = 0;
+  // level state
+  int L = 0, leaf_offset = 0;
+  bool built = false, finished = false;
+  std::vector<DescDev> h_descs;
+  std::vector<GroupDev> h_groups;
+  int n_smem_groups = 0;
+  size_t smem_bytes = 0;
+  int64_t total_bins = 0, total_vals = 0;
+  int active_cols = 0;
+  DBuf<DescDev> d_descs;
+  DBuf<h2ot_hist_desc> d_hdescs;
+  DBuf<GroupDev> d_groups;
+  DBuf<long long> d_sums;  // [3*total_bins | L leaf_rows]
+  DBuf<unsigned long long> d_minmax;
+  DBuf<double> d_vals, d_min2, d_maxIn;
+  DBuf<uint8_t> d_has;
+  DBuf<h2ot_split> d_cand, d_best;
+  DBuf<long long> d_gamma;
+  DBuf<float> d_pred;
+  int max_split_nbin = 0;
+  bool any_cat = false;
+};
+
+// minimal NCCL surface, resolved with dlopen so that the library has no link-time NCCL dependency
+struct IdByValue { char internal[H2OT_COMM_ID_BYTES]; };
+struct Nccl {
+  void* lib = nullptr;
+  void* comm = nullptr;
+  int world = 1, rank = 0;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, IdByValue, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+
+}  // namespace h2ot
+
+using namespace h2ot;
+
+struct h2ot_engine {
+  h2ot_config cfg{};
+  int64_t n = 0, n_pad = 0;
+  int C = 0, K = 0;
+  int sm_count = 148;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  std::vector<Column> cols;
+  DBuf<ColRef> d_cols;
+  double* resp = nullptr;
+  double* w = nullptr;
+  double* off = nullptr;
+  double* resp_staging = nullptr;
+  double w_max = 1.0;
+  bool frame_final = false;
+  std::vector<TreeState> ts;
+  // device pointer tables
+  DBuf<double*> d_Fp;
+  DBuf<float*> d_workp;
+  DBuf<int32_t*> d_nidsp;
+  DBuf<unsigned int> d_absmax;
+  DBuf<unsigned long long> d_scalar;
+  DBuf<RollupDev> d_rollup;
+  h2ot_stats stats{};
+  std::vector<Timer> timers;
+  int hist_mode = 0;
+  int smem_budget_kb = 0;  // 0: automatic
+  Nccl nccl;
+};
+
+namespace {
+
+int check(h2ot_engine* h) {
+  if (!h) H2OT_FAIL(H2OT_ERR_INVALID, "null engine handle");
+  cudaError_t e = cudaSetDevice(h->cfg.device);
+  if (e != cudaSuccess) H2OT_FAIL(H2OT_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+  return H2OT_OK;
+}
+#define CHECK_ENGINE(h)         \
+  do {                          \
+    int _r = check(h);          \
+    if (_r != H2OT_OK) return _r; \
+  } while (0)
+#define CHECK_K(h, k) \
+  if ((k) < 0 || (k) >= (h)->K) H2OT_FAIL(H2OT_ERR_INVALID, "class-tree index out of range")
+#define TRY(expr)               \
+  do {                          \
+    int _r = (expr);            \
+    if (_r != H2OT_OK) return _r; \
+  } while (0)
+
+int t_begin(h2ot_engine* h, double* acc) {
+  Timer t;
+  CUDA_TRY(cudaEventCreate(&t.a));
+  CUDA_TRY(cudaEventCreate(&t.b));
+  t.acc = acc;
+  CUDA_TRY(cudaEventRecord(t.a, h->stream));
+  h->timers.push_back(t);
+  return H2OT_OK;
+}
+int t_end(h2ot_engine* h) {
+  CUDA_TRY(cudaEventRecord(h->timers.back().b, h->stream));
+  return H2OT_OK;
+}
+// synchronise the stream and fold the per-family event times into the stats
+int finish_call(h2ot_engine* h) {
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  for (Timer& t : h->timers) {
+    float ms = 0;
+    if (t.a && t.b && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) *t.acc += ms;
+    if (t.a) cudaEventDestroy(t.a);
+    if (t.b) cudaEventDestroy(t.b);
+  }
+  h->timers.clear();
+  CUDA_TRY(cudaGetLastError());
+  return H2OT_OK;
+}
+int h2d(h2ot_engine* h, void* dst, const void* src, size_t bytes) {
+  if (!bytes) return H2OT_OK;
+  CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->stream));
+  h->stats.h2d_bytes += (int64_t)bytes;
+  return H2OT_OK;
+}
+int d2h(h2ot_engine* h, void* dst, const void* src, size_t bytes) {
+  if (!bytes) return H2OT_OK;
+  CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream));
+  h->stats.d2h_bytes += (int64_t)bytes;
+  return H2OT_OK;
+}
+int grid_for(h2ot_engine* h, int64_t n, int block, int per_sm = 8) {
+  int64_t need = (n + block - 1) / block;
+  int64_t cap = (int64_t)h->sm_count * per_sm;
+  return (int)std::max<int64_t>(1, std::min(need, cap));
+}
+int exponent_for(double bound, int bitsN) {  // 2^e scale such that N * bound * 2^e <= 2^62
+  if (!(bound > 0) || std::isinf(bound)) bound = 1.0;
+  int e2;
+  std::frexp(bound, &e2);  // bound <= 2^e2
+  int e = 62 - bitsN - e2;
+  return std::max(-900, std::min(900, e));
+}
+
+}  // namespace
+
+extern "C" {
+
+int h2ot_version(void) { return 100; }
+const char* h2ot_last_error(void) { return g_last_error.c_str(); }
+
+int h2ot_device_count(int32_t* out) {
+  int n = 0;
+  CUDA_TRY(cudaGetDeviceCount(&n));
+  *out = n;
+  return H2OT_OK;
+}
+
+int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
+  if (!cfg || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  if (cfg->nrows <= 0 || cfg->ncols <= 0 || cfg->nclass_trees <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "nrows/ncols/nclass_trees must be positive");
+  if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    H2OT_FAIL(H2OT_ERR_CUDA, std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev) H2OT_FAIL(H2OT_ERR_INVALID, "device ordinal out of range");
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  h2ot_engine* h = new h2ot_engine();
+  h->cfg = *cfg;
+  if (h->cfg.nrows_global <= 0) h->cfg.nrows_global = cfg->nrows;
+  h->n = cfg->nrows;
+  h->n_pad = (cfg->nrows + kRowPad - 1) / kRowPad * kRowPad;
+  h->C = cfg->ncols;
+  h->K = cfg->nclass_trees;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+  h->sm_count = prop.multiProcessorCount;
+  h->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+  if (const char* s = getenv("H2OT_SMEM_BUDGET_KB")) h->smem_budget_kb = atoi(s);
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  h->cols.resize(h->C);
+  h->ts.resize(h->K);
+  const size_t np = (size_t)h->n_pad;
+  CUDA_TRY(cudaMalloc(&h->resp, np * sizeof(double)));
+  CUDA_TRY(cudaMemsetAsync(h->resp, 0xFF, np * sizeof(double), h->stream));  // all-ones == NaN == NA
+  if (cfg->has_weights) {
+    CUDA_TRY(cudaMalloc(&h->w, np * sizeof(double)));
+    CUDA_TRY(cudaMemsetAsync(h->w, 0, np * sizeof(double), h->stream));
+  }
+  if (cfg->has_offset) {
+    CUDA_TRY(cudaMalloc(&h->off, np * sizeof(double)));
+    CUDA_TRY(cudaMemsetAsync(h->off, 0, np * sizeof(double), h->stream));
+  }
+  std::vector<double*> Fp(h->K);
+  std::vector<float*> wp(h->K);
+  std::vector<int32_t*> np_(h->K);
+  for (int k = 0; k < h->K; k++) {
+    TreeState& t = h->ts[k];
+    CUDA_TRY(cudaMalloc(&t.F, np * sizeof(double)));
+    CUDA_TRY(cudaMalloc(&t.work, np * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&t.nids, np * sizeof(int32_t)));
+    CUDA_TRY(cudaMalloc(&t.code, np * sizeof(uint16_t)));
+    CUDA_TRY(cudaMemsetAsync(t.F, 0, np * sizeof(double), h->stream));
+    CUDA_TRY(cudaMemsetAsync(t.work, 0, np * sizeof(float), h->stream));
+    CUDA_TRY(cudaMemsetAsync(t.nids, 0, np * sizeof(int32_t), h->stream));
+    CUDA_TRY(cudaMemsetAsync(t.code, 0xFF, np * sizeof(uint16_t), h->stream));
+    Fp[k] = t.F;
+    wp[k] = t.work;
+    np_[k] = t.nids;
+  }
+  TRY(h->d_Fp.ensure(h->K));
+  TRY(h->d_workp.ensure(h->K));
+  TRY(h->d_nidsp.ensure(h->K));
+  TRY(h->d_absmax.ensure(h->K));
+  TRY(h->d_scalar.ensure(8));
+  TRY(h->d_rollup.ensure(1));
+  TRY(h->d_cols.ensure(h->C));
+  CUDA_TRY(cudaMemcpyAsync(h->d_Fp.p, Fp.data(), h->K * sizeof(double*), cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(h->d_workp.p, wp.data(), h->K * sizeof(float*), cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaMemcpyAsync(h->d_nidsp.p, np_.data(), h->K * sizeof(int32_t*), cudaMemcpyHostToDevice, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  // opt in to the large dynamic shared memory carve-out once
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  CUDA_TRY(cudaFuncSetAttribute(find_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  *out = h;
+  return H2OT_OK;
+}
+
+int h2ot_destroy(h2ot_engine* h) {
+  if (!h) return H2OT_OK;
+  cudaSetDevice(h->cfg.device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  if (h->nccl.comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->nccl.comm);
+  for (Column& c : h->cols) {
+    if (c.data) cudaFree(c.data);
+    if (c.staging) cudaFree(c.staging);
+  }
+  if (h->resp) cudaFree(h->resp);
+  if (h->w) cudaFree(h->w);
+  if (h->off) cudaFree(h->off);
+  for (TreeState& t : h->ts) {
+    if (t.F) cudaFree(t.F);
+    if (t.work) cudaFree(t.work);
+    if (t.nids) cudaFree(t.nids);
+    if (t.code) cudaFree(t.code);
+    t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release();
+    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_min2.release(); t.d_maxIn.release();
+    t.d_has.release(); t.d_cand.release(); t.d_best.release(); t.d_gamma.release(); t.d_pred.release();
+  }
+  h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
+  h->d_rollup.release(); h->d_cols.release();
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return H2OT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ ingest
+static int load_rows(h2ot_engine* h, double* dst, int64_t row0, int64_t n, const double* values) {
+  if (!values || row0 < 0 || n < 0 || row0 + n > h->n) H2OT_FAIL(H2OT_ERR_INVALID, "row range out of bounds");
+  TRY(h2d(h, dst + row0, values, (size_t)n * sizeof(double)));
+  return finish_call(h);
+}
+
+int h2ot_load_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, const double* values) {
+  CHECK_ENGINE(h);
+  if (col < 0 || col >= h->C) H2OT_FAIL(H2OT_ERR_INVALID, "column index out of range");
+  if (h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame already finalized");
+  Column& c = h->cols[col];
+  if (!c.staging) {
+    CUDA_TRY(cudaMalloc(&c.staging, (size_t)h->n * sizeof(double)));
+    CUDA_TRY(cudaMemsetAsync(c.staging, 0xFF, (size_t)h->n * sizeof(double), h->stream));  // unloaded rows are NA
+  }
+  return load_rows(h, c.staging, row0, n, values);
+}
+int h2ot_load_response(h2ot_engine* h, int64_t row0, int64_t n, const double* values) {
+  CHECK_ENGINE(h);
+  return load_rows(h, h->resp, row0, n, values);
+}
+int h2ot_load_weights(h2ot_engine* h, int64_t row0, int64_t n, const double* values) {
+  CHECK_ENGINE(h);
+  if (!h->w) H2OT_FAIL(H2OT_ERR_INVALID, "engine was created without a weights column");
+  return load_rows(h, h->w, row0, n, values);
+}
+int h2ot_load_offset(h2ot_engine* h, int64_t row0, int64_t n, const double* values) {
+  CHECK_ENGINE(h);
+  if (!h->off) H2OT_FAIL(H2OT_ERR_INVALID, "engine was created without an offset column");
+  return load_rows(h, h->off, row0, n, values);
+}
+
+static int rollup(h2ot_engine* h, const double* v, RollupDev* out) {
+  CUDA_TRY(cudaMemsetAsync(h->d_rollup.p, 0, sizeof(RollupDev), h->stream));
+  rollup_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(v, h->n, h->d_rollup.p);
+  h->stats.launches++;
+  CUDA_TRY(cudaMemcpyAsync(out, h->d_rollup.p, sizeof(RollupDev), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return H2OT_OK;
+}
+
+int h2ot_finalize_frame(h2ot_engine* h) {
+  CHECK_ENGINE(h);
+  if (h->frame_final) return H2OT_OK;
+  TRY(t_begin(h, &h->stats.ms_ingest));
+  std::vector<ColRef> refs(h->C);
+  for (int ci = 0; ci < h->C; ci++) {
+    Column& c = h->cols[ci];
+    if (!c.staging) H2OT_FAIL(H2OT_ERR_INVALID, "column " + std::to_string(ci) + " was never loaded");
+    RollupDev r;
+    TRY(rollup(h, c.staging, &r));
+    c.info.nacnt = (int64_t)r.nacnt;
+    const bool any = r.max_key != 0;
+    c.info.min = any ? dkey_inv(~r.min_key) : NAN;
+    c.info.max = any ? dkey_inv(r.max_key) : NAN;
+    c.info.is_int = r.not_int ? 0 : 1;
+    int storage = r.not_f32 ? H2OT_STORE_F64 : H2OT_STORE_F32;
+    double base = 0;
+    if (any && c.info.is_int) {
+      const double span = c.info.max - c.info.min;
+      if (span < 255) { storage = H2OT_STORE_U8; base = c.info.min; }
+      else if (span < 65535) { storage = H2OT_STORE_U16; base = c.info.min; }
+    }
+    c.storage = storage;
+    c.base = base;
+    c.info.storage = storage;
+    const size_t esz = storage == H2OT_STORE_F32 ? 4 : storage == H2OT_STORE_F64 ? 8 : storage == H2OT_STORE_U8 ? 1 : 2;
+    CUDA_TRY(cudaMalloc(&c.data, (size_t)h->n_pad * esz));
+    encode_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(c.staging, h->n, h->n_pad, storage, base, c.data);
+    h->stats.launches++;
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    CUDA_TRY(cudaFree(c.staging));
+    c.staging = nullptr;
+    c.finalized = true;
+    refs[ci].data = c.data;
+    refs[ci].base = base;
+    refs[ci].storage = storage;
+    refs[ci].pad = 0;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->d_cols.p, refs.data(), refs.size() * sizeof(ColRef), cudaMemcpyHostToDevice, h->stream));
+  if (h->w) {
+    RollupDev r;
+    TRY(rollup(h, h->w, &r));
+    h->w_max = r.max_key ? std::max(dkey_inv(r.max_key), -dkey_inv(~r.min_key)) : 1.0;
+    if (!(h->w_max > 0)) h->w_max = 1.0;
+  }
+  TRY(t_end(h));
+  h->frame_final = true;
+  return finish_call(h);
+}
+
+int h2ot_column_info_get(h2ot_engine* h, int32_t col, h2ot_column_info* out) {
+  CHECK_ENGINE(h);
+  if (col < 0 || col >= h->C || !out) H2OT_FAIL(H2OT_ERR_INVALID, "bad column / null out");
+  if (!h->cols[col].finalized) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  *out = h->cols[col].info;
+  return H2OT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ model state
+namespace {
+__global__ void fill_f64_kernel(double* p, int64_t n, double v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void f32_to_f64_kernel(const float* s, double* d, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) d[i] = (double)s[i];
+}
+__global__ void f64_to_f32_kernel(const double* s, float* d, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) d[i] = (float)s[i];
+}
+}  // namespace
+
+int h2ot_init_model(h2ot_engine* h, const double* init_f, int64_t* out_skipped) {
+  CHECK_ENGINE(h);
+  if (!init_f) H2OT_FAIL(H2OT_ERR_INVALID, "null init_f");
+  for (int k = 0; k < h->K; k++) {
+    fill_f64_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(h->ts[k].F, h->n_pad, init_f[k]);
+    h->stats.launches++;
+  }
+  CUDA_TRY(cudaMemsetAsync(h->d_scalar.p, 0, sizeof(unsigned long long), h->stream));
+  InitArgs a{h->n, h->n_pad, h->K, h->resp, h->w, h->d_nidsp.p, h->d_scalar.p};
+  init_rows_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  unsigned long long skipped = 0;
+  TRY(d2h(h, &skipped, h->d_scalar.p, sizeof(skipped)));
+  TRY(finish_call(h));
+  if (out_skipped) *out_skipped = (int64_t)skipped;
+  return H2OT_OK;
+}
+
+int h2ot_set_predictions(h2ot_engine* h, int32_t k, const double* f) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(h2d(h, h->ts[k].F, f, (size_t)h->n * sizeof(double)));
+  return finish_call(h);
+}
+int h2ot_get_predictions(h2ot_engine* h, int32_t k, double* f) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(d2h(h, f, h->ts[k].F, (size_t)h->n * sizeof(double)));
+  return finish_call(h);
+}
+int h2ot_get_work(h2ot_engine* h, int32_t k, double* work) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  DBuf<double> tmp;
+  TRY(tmp.ensure(h->n));
+  f32_to_f64_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->ts[k].work, tmp.p, h->n);
+  h->stats.launches++;
+  TRY(d2h(h, work, tmp.p, (size_t)h->n * sizeof(double)));
+  int r = finish_call(h);
+  tmp.release();
+  return r;
+}
+int h2ot_set_work(h2ot_engine* h, int32_t k, const double* work, double abs_bound) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  DBuf<double> tmp;
+  TRY(tmp.ensure(h->n));
+  TRY(h2d(h, tmp.p, work, (size_t)h->n * sizeof(double)));
+  f64_to_f32_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(tmp.p, h->ts[k].work, h->n);
+  h->stats.launches++;
+  h->ts[k].work_bound = abs_bound;
+  int r = finish_call(h);
+  tmp.release();
+  return r;
+}
+int h2ot_get_nids(h2ot_engine* h, int32_t k, int32_t* nids) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(d2h(h, nids, h->ts[k].nids, (size_t)h->n * sizeof(int32_t)));
+  return finish_call(h);
+}
+int h2ot_set_nids(h2ot_engine* h, int32_t k, const int32_t* nids) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(h2d(h, h->ts[k].nids, nids, (size_t)h->n * sizeof(int32_t)));
+  return finish_call(h);
+}
+
+// ------------------------------------------------------------------------------------------------ per tree
+int h2ot_compute_residuals(h2ot_engine* h, double* out_abs_max) {
+  CHECK_ENGINE(h);
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  CUDA_TRY(cudaMemsetAsync(h->d_absmax.p, 0, h->K * sizeof(unsigned int), h->stream));
+  ResidArgs a{h->n, h->K, h->cfg.nclass, h->cfg.family, h->resp, h->w, h->off, h->d_Fp.p, h->d_workp.p, h->d_absmax.p};
+  TRY(t_begin(h, &h->stats.ms_residuals));
+  residuals_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  std::vector<unsigned int> bits(h->K);
+  TRY(d2h(h, bits.data(), h->d_absmax.p, h->K * sizeof(unsigned int)));
+  TRY(finish_call(h));
+  for (int k = 0; k < h->K; k++) {
+    float f;
+    memcpy(&f, &bits[k], 4);
+    if (out_abs_max) out_abs_max[k] = (double)f;
+    h->ts[k].work_bound = (double)f;
+  }
+  return H2OT_OK;
+}
+
+int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate, double work_abs_bound) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  t.n_nodes = 0;
+  t.built = t.finished = false;
+  t.L = 0;
+  if (work_abs_bound > 0) t.work_bound = work_abs_bound;
+  const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
+  const double b = t.work_bound > 0 ? t.work_bound : 1.0;
+  t.ey = exponent_for(h->w_max * b, bitsN);
+  t.eyy = exponent_for(h->w_max * b * b, bitsN);
+  if (sample_rate < 1.0) {
+    TRY(t_begin(h, &h->stats.ms_sample));
+    sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed,
+                                                                 (float)sample_rate, sample_rate, h->resp, t.nids);
+    h->stats.launches++;
+    TRY(t_end(h));
+  }
+  return finish_call(h);
+}
+
+
+// ------------------------------------------------------------------------------------------------ per level
+}  // extern "C" (helpers below are internal)
+
+namespace {
+
+// Merge caller-supplied DecidedNodes (+ their bitset bytes) into the per-tree node table (host mirror + device).
+int upload_nodes(h2ot_engine* h, TreeState& t, int n_decided, const h2ot_decided_node* decided, const uint8_t* pool,
+                 int64_t pool_bytes, bool replace_all) {
+  if (replace_all) {
+    t.h_nodes.clear();
+    t.h_bitsets.clear();
+    t.n_nodes = 0;
+  }
+  if (n_decided <= 0) return H2OT_OK;
+  if (!decided) H2OT_FAIL(H2OT_ERR_INVALID, "null decided-node array");
+  const size_t bs_base = t.h_bitsets.size();
+  if (pool_bytes > 0) {
+    if (!pool) H2OT_FAIL(H2OT_ERR_INVALID, "null bitset pool");
+    t.h_bitsets.insert(t.h_bitsets.end(), pool, pool + pool_bytes);
+  }
+  int min_nid = INT32_MAX, max_nid = -1;
+  for (int i = 0; i < n_decided; i++) {
+    const h2ot_decided_node& d = decided[i];
+    if (d.nid < 0) H2OT_FAIL(H2OT_ERR_INVALID, "negative node id");
+    if (d.col >= h->C) H2OT_FAIL(H2OT_ERR_INVALID, "split column out of range");
+    if (d.col >= 0 && d.equal >= 2) {
+      const int nbytes = ((d.bs_nbits - 1) >> 3) + 1;
+      if (d.bs_off < 0 || (int64_t)d.bs_off + nbytes > pool_bytes) H2OT_FAIL(H2OT_ERR_INVALID, "bitset outside the pool");
+    }
+    min_nid = std::min(min_nid, d.nid);
+    max_nid = std::max(max_nid, d.nid);
+  }
+  if ((size_t)max_nid + 1 > t.h_nodes.size()) {
+    h2ot_decided_node blank;
+    memset(&blank, 0xFF, sizeof(blank));  // col = pid = -1
+    t.h_nodes.resize((size_t)max_nid + 1, blank);
+  }
+  for (int i = 0; i < n_decided; i++) {
+    h2ot_decided_node d = decided[i];
+    if (d.col >= 0 && d.equal >= 2) d.bs_off += (int32_t)bs_base;
+    t.h_nodes[d.nid] = d;
+  }
+  t.n_nodes = (int)t.h_nodes.size();
+  if (t.h_nodes.size() > t.nodes.cap) {
+    TRY(t.nodes.ensure(std::max<size_t>(t.h_nodes.size() * 2, 256)));
+    min_nid = 0;
+    max_nid = (int)t.h_nodes.size() - 1;
+  }
+  TRY(h2d(h, t.nodes.p + min_nid, t.h_nodes.data() + min_nid, (size_t)(max_nid - min_nid + 1) * sizeof(h2ot_decided_node)));
+  if (!t.h_bitsets.empty()) {
+    if (t.h_bitsets.size() > t.bitsets.cap) {
+      TRY(t.bitsets.ensure(std::max<size_t>(t.h_bitsets.size() * 2, 4096)));
+      TRY(h2d(h, t.bitsets.p, t.h_bitsets.data(), t.h_bitsets.size()));
+    } else if (pool_bytes > 0) {
+      TRY(h2d(h, t.bitsets.p + bs_base, t.h_bitsets.data() + bs_base, (size_t)pool_bytes));
+    }
+  } else {
+    TRY(t.bitsets.ensure(16));
+  }
+  return H2OT_OK;
+}
+
+// Places every active (leaf, col) histogram: global bin offsets, packed-vals offsets, shared-memory groups.
+int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs) {
+  const int C = h->C;
+  const int WPB = h->w ? 7 : 5;
+  t.h_descs.assign((size_t)L * C, DescDev{});
+  t.total_bins = 0;
+  t.total_vals = 0;
+  t.max_split_nbin = 0;
+  t.any_cat = false;
+  std::vector<int64_t> col_words(C, 0);
+  for (int l = 0; l < L; l++)
+    for (int c = 0; c < C; c++) {
+      const h2ot_hist_desc& s = descs[(size_t)l * C + c];
+      DescDev& d = t.h_descs[(size_t)l * C + c];
+      d.min = s.min;
+      d.step = s.step;
+      d.flags = s.flags;
+      d.smem_off = -1;
+      d.pad = 0;
+      if (!(s.flags & H2OT_DESC_ACTIVE)) {
+        d.nbin = -1;
+        d.gbin = 0;
+        d.voff = 0;
+        continue;
+      }
+      if (s.nbin < 1 || s.nbin > 65534) H2OT_FAIL(H2OT_ERR_INVALID, "nbin out of range (1..65534)");
+      if (!(s.step > 0) || std::isinf(s.step)) H2OT_FAIL(H2OT_ERR_INVALID, "histogram step must be positive and finite");
+      d.nbin = s.nbin;
+      d.gbin = t.total_bins;
+      d.voff = t.total_vals;
+      t.total_bins += s.nbin + 1;
+      t.total_vals += (int64_t)(s.nbin + 1) * 3;
+      col_words[c] += (int64_t)(s.nbin + 1) * WPB;
+      t.max_split_nbin = std::max(t.max_split_nbin, (int)s.nbin);
+      if ((s.flags & H2OT_DESC_ISCAT) && s.step == 1.0) t.any_cat = true;
+    }
+  // ---- shared-memory groups
+  auto fixed_bytes = [&](int ncg) { return (size_t)ncg * L * (sizeof(DescS) + sizeof(MinMaxS)) + (size_t)ncg * sizeof(ColRef); };
+  const size_t full_budget = (size_t)h->max_smem_optin;
+  const size_t half_budget = 112 * 1024;
+  size_t budget = 0;
+  if (h->smem_budget_kb > 0) budget = std::min<size_t>((size_t)h->smem_budget_kb * 1024, full_budget);
+  else {
+    size_t worst = 0;
+    for (int c = 0; c < C; c++)
+      if (col_words[c]) worst = std::max(worst, (size_t)col_words[c] * 4 + fixed_bytes(1));
+    budget = worst > half_budget ? full_budget : half_budget;
+  }
+  t.h_groups.clear();
+  t.active_cols = 0;
+  std::vector<int> smem_cols, glob_cols;
+  for (int c = 0; c < C; c++) {
+    if (!col_words[c]) continue;
+    t.active_cols++;
+    if (h->hist_mode == 1 || (size_t)col_words[c] * 4 + fixed_bytes(1) > full_budget) glob_cols.push_back(c);
+    else smem_cols.push_back(c);
+  }
+  // greedy count, then even re-split over the same number of groups (keeps CTAs of one launch balanced)
+  auto pack = [&](size_t target_words, std::vector<GroupDev>& out) {
+    out.clear();
+    size_t i = 0;
+    while (i < smem_cols.size()) {
+      GroupDev g{smem_cols[i], smem_cols[i] + 1, 0, 0};
+      size_t words = 0;
+      int ncg = 0;
+      while (i < smem_cols.size()) {
+        const int c = smem_cols[i];
+        const int span = c + 1 - g.c_begin;  // groups are contiguous column ranges (inactive columns inside cost only descriptors)
+        const size_t nw = words + (size_t)col_words[c];
+        if (ncg > 0 && (nw * 4 + fixed_bytes(span) > budget || words >= target_words)) break;
+        words = nw;
+        ncg++;
+        g.c_end = c + 1;
+        i++;
+      }
+      g.smem_words = (int32_t)words;
+      out.push_back(g);
+    }
+  };
+  std::vector<GroupDev> groups;
+  pack(SIZE_MAX, groups);
+  if (groups.size() > 1) {
+    size_t total = 0;
+    for (int c : smem_cols) total += (size_t)col_words[c];
+    std::vector<GroupDev> even;
+    pack((total + groups.size() - 1) / groups.size(), even);
+    if (even.size() <= groups.size()) groups = even;
+  }
+  t.n_smem_groups = (int)groups.size();
+  t.smem_bytes = 0;
+  for (GroupDev& g : groups) {
+    int off = 0;
+    for (int c = g.c_begin; c < g.c_end; c++)
+      for (int l = 0; l < L; l++) {
+        DescDev& d = t.h_descs[(size_t)l * C + c];
+        if (d.nbin < 0) continue;
+        d.smem_off = off;
+        off += (d.nbin + 1) * WPB;
+      }
+    t.smem_bytes = std::max(t.smem_bytes, fixed_bytes(g.c_end - g.c_begin) + (size_t)g.smem_words * 4);
+    t.h_groups.push_back(g);
+  }
+  for (int c : glob_cols) t.h_groups.push_back(GroupDev{c, c + 1, 0, 1});
+  return H2OT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                     const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
+                     const h2ot_hist_desc* descs) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  if (n_leaves <= 0 || n_leaves > 65534) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "n_leaves must be in 1..65534");
+  if (!descs) H2OT_FAIL(H2OT_ERR_INVALID, "null descs");
+  TreeState& t = h->ts[k];
+  t.built = t.finished = false;
+  TRY(upload_nodes(h, t, n_decided, decided, bitset_pool, bitset_bytes, false));
+  if (leaf_offset > 0 && t.n_nodes == 0) H2OT_FAIL(H2OT_ERR_INVALID, "no decided nodes uploaded for a non-root level");
+  TRY(t.nodes.ensure(1));
+  TRY(t.bitsets.ensure(16));
+  TRY(plan_level(h, t, n_leaves, descs));
+  t.L = n_leaves;
+  t.leaf_offset = leaf_offset;
+  const size_t LC = (size_t)n_leaves * h->C;
+  TRY(t.d_descs.ensure(LC));
+  TRY(t.d_hdescs.ensure(LC));
+  TRY(t.d_groups.ensure(std::max<size_t>(1, t.h_groups.size())));
+  TRY(t.d_sums.ensure((size_t)t.total_bins * 3 + n_leaves));
+  TRY(t.d_minmax.ensure(LC * 2));
+  TRY(h2d(h, t.d_descs.p, t.h_descs.data(), LC * sizeof(DescDev)));
+  TRY(h2d(h, t.d_hdescs.p, descs, LC * sizeof(h2ot_hist_desc)));
+  if (!t.h_groups.empty()) TRY(h2d(h, t.d_groups.p, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev)));
+  CUDA_TRY(cudaMemsetAsync(t.d_sums.p, 0, ((size_t)t.total_bins * 3 + n_leaves) * sizeof(long long), h->stream));
+  CUDA_TRY(cudaMemsetAsync(t.d_minmax.p, 0, LC * 2 * sizeof(unsigned long long), h->stream));
+
+  // K2a
+  ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
+               reinterpret_cast<unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3)};
+  TRY(t_begin(h, &h->stats.ms_score));
+  score_decide_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(sa);
+  h->stats.launches++;
+  TRY(t_end(h));
+
+  // K2b
+  HistArgs ha{};
+  ha.n_pad = h->n_pad;
+  ha.L = n_leaves;
+  ha.C = h->C;
+  ha.n_groups = t.n_smem_groups;
+  const int ctas_per_sm = t.smem_bytes <= 112 * 1024 ? 2 : 1;
+  ha.n_slices = std::max(1, (h->sm_count * ctas_per_sm) / std::max(1, t.n_smem_groups));
+  const int64_t n_tiles = h->n_pad / kTileRows;
+  ha.n_slices = (int)std::min<int64_t>(ha.n_slices, std::max<int64_t>(1, n_tiles));
+  ha.code = t.code;
+  ha.work = t.work;
+  ha.w = h->w;
+  ha.cols = h->d_cols.p;
+  ha.descs = t.d_descs.p;
+  ha.groups = t.d_groups.p;
+  ha.acc = t.d_sums.p;
+  ha.minmax = t.d_minmax.p;
+  ha.sy = std::ldexp(1.0, t.ey);
+  ha.syy = std::ldexp(1.0, t.eyy);
+  const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
+  const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
+  ha.sw = std::ldexp(1.0, ew);
+  TRY(t_begin(h, &h->stats.ms_hist));
+  if (t.n_smem_groups > 0) {
+    if (t.smem_bytes > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "shared-memory plan exceeds the device limit");
+    const int grid = t.n_smem_groups * ha.n_slices;
+    if (h->w) hist_smem_kernel<7, true><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
+    else hist_smem_kernel<5, false><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
+    h->stats.launches++;
+  }
+  for (size_t g = t.n_smem_groups; g < t.h_groups.size(); g++) {
+    const GroupDev& gd = t.h_groups[g];
+    const int grid = grid_for(h, h->n_pad / 4, 256, 8);
+    if (h->w) hist_global_kernel<true><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
+    else hist_global_kernel<false><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
+    h->stats.launches++;
+  }
+  TRY(t_end(h));
+  CUDA_TRY(cudaGetLastError());
+  // accounting: N*(sum B_c + nid r [+ nid w] + y [+ w]) + bins*24
+  int64_t bytes_per_row = 4 + 4 + (leaf_offset > 0 ? 4 : 0) + (h->w ? 4 : 0);
+  for (int c = 0; c < h->C; c++) {
+    bool act = false;
+    for (int l = 0; l < n_leaves && !act; l++) act = t.h_descs[(size_t)l * h->C + c].nbin >= 0;
+    if (!act) continue;
+    const int st = h->cols[c].storage;
+    bytes_per_row += st == H2OT_STORE_F32 ? 4 : st == H2OT_STORE_F64 ? 8 : st == H2OT_STORE_U8 ? 1 : 2;
+  }
+  h->stats.hist_rows_cols += h->n * (int64_t)t.active_cols;
+  h->stats.hist_algo_bytes += h->n * bytes_per_row + t.total_bins * 24;
+  t.built = true;
+  return finish_call(h);
+}
+
+int h2ot_level_buffers(h2ot_engine* h, int32_t k, void** d_sums, int64_t* n_sums, void** d_minmax, int64_t* n_minmax) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
+  if (d_sums) *d_sums = t.d_sums.p;
+  if (n_sums) *n_sums = t.total_bins * 3 + t.L;
+  if (d_minmax) *d_minmax = t.d_minmax.p;
+  if (n_minmax) *n_minmax = (int64_t)t.L * h->C * 2;
+  return H2OT_OK;
+}
+
+static int nccl_check(h2ot_engine* h, int rc, const char* what) {
+  if (rc == 0) return H2OT_OK;
+  std::string m = std::string(what) + " failed: ";
+  m += h->nccl.GetErrorString ? h->nccl.GetErrorString(rc) : "nccl error";
+  H2OT_FAIL(H2OT_ERR_COMM, m);
+}
+
+int h2ot_allreduce_level(h2ot_engine* h, int32_t k) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
+  if (h->nccl.world <= 1 || !h->nccl.comm) return H2OT_OK;
+  const size_t ns = (size_t)t.total_bins * 3 + t.L, nm = (size_t)t.L * h->C * 2;
+  TRY(nccl_check(h, h->nccl.AllReduce(t.d_sums.p, t.d_sums.p, ns, /*ncclInt64*/ 4, /*ncclSum*/ 0, h->nccl.comm, h->stream), "ncclAllReduce(sums)"));
+  TRY(nccl_check(h, h->nccl.AllReduce(t.d_minmax.p, t.d_minmax.p, nm, /*ncclUint64*/ 5, /*ncclMax*/ 2, h->nccl.comm, h->stream), "ncclAllReduce(minmax)"));
+  return finish_call(h);
+}
+
+int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_vals_capacity, int64_t* out_val_offsets,
+                      double* out_min2, double* out_maxIn, uint8_t* out_has_vals) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
+  const size_t LC = (size_t)t.L * h->C;
+  TRY(t.d_vals.ensure(std::max<int64_t>(1, t.total_vals)));
+  TRY(t.d_min2.ensure(LC));
+  TRY(t.d_maxIn.ensure(LC));
+  TRY(t.d_has.ensure(LC));
+  FinalizeArgs fa{};
+  fa.L = t.L;
+  fa.C = h->C;
+  fa.descs = t.d_descs.p;
+  fa.acc = t.d_sums.p;
+  fa.minmax = t.d_minmax.p;
+  fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3);
+  fa.vals = t.d_vals.p;
+  fa.min2 = t.d_min2.p;
+  fa.maxIn = t.d_maxIn.p;
+  fa.has_vals = t.d_has.p;
+  const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
+  const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
+  fa.inv_sy = std::ldexp(1.0, -t.ey);
+  fa.inv_syy = std::ldexp(1.0, -t.eyy);
+  fa.inv_sw = std::ldexp(1.0, -ew);
+  TRY(t_begin(h, &h->stats.ms_finalize));
+  finalize_kernel<<<(unsigned)LC, 128, 0, h->stream>>>(fa);
+  h->stats.launches++;
+  TRY(t_end(h));
+  if (out_vals) {
+    if (out_vals_capacity < t.total_vals) H2OT_FAIL(H2OT_ERR_INVALID, "out_vals too small: need " + std::to_string(t.total_vals) + " doubles");
+    TRY(d2h(h, out_vals, t.d_vals.p, (size_t)t.total_vals * sizeof(double)));
+  }
+  if (out_min2) TRY(d2h(h, out_min2, t.d_min2.p, LC * sizeof(double)));
+  if (out_maxIn) TRY(d2h(h, out_maxIn, t.d_maxIn.p, LC * sizeof(double)));
+  if (out_has_vals) TRY(d2h(h, out_has_vals, t.d_has.p, LC));
+  if (out_val_offsets)
+    for (size_t i = 0; i < LC; i++) out_val_offsets[i] = t.h_descs[i].nbin >= 0 ? t.h_descs[i].voff : -1;
+  t.finished = true;
+  return finish_call(h);
+}
+
+int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_split_improvement, h2ot_split* out_splits) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  if (!t.finished) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_finish_level must run before h2ot_find_splits");
+  const size_t LC = (size_t)t.L * h->C;
+  TRY(t.d_cand.ensure(LC));
+  TRY(t.d_best.ensure(t.L));
+  const size_t n1 = (size_t)t.max_split_nbin + 1;
+  size_t smem = 8 * 9 * n1;
+  if (t.any_cat) smem += 8 * (3 * n1 + n1) + 4 * n1;
+  if (smem > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
+  if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
+  SplitArgs sa{t.L, h->C, t.d_descs.p, t.d_vals.p, t.d_min2.p, t.d_maxIn.p, t.d_has.p, min_rows, min_split_improvement, t.d_cand.p};
+  TRY(t_begin(h, &h->stats.ms_split));
+  find_split_kernel<<<(unsigned)LC, kSplitThreads, smem, h->stream>>>(sa);
+  best_col_kernel<<<(t.L + 63) / 64, 64, 0, h->stream>>>(t.L, h->C, t.d_descs.p, t.d_hdescs.p, t.d_cand.p, t.d_best.p);
+  h->stats.launches += 2;
+  TRY(t_end(h));
+  if (out_splits) TRY(d2h(h, out_splits, t.d_best.p, (size_t)t.L * sizeof(h2ot_split)));
+  return finish_call(h);
+}
+
+// ------------------------------------------------------------------------------------------------ end of tree
+int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,
+                  int64_t bitset_bytes) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(upload_nodes(h, h->ts[k], n_nodes, nodes, bitset_pool, bitset_bytes, true));
+  return finish_call(h);
+}
+
+int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_leaf_nodes, double* out_num, double* out_denom) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (n_leaf_nodes <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "n_leaf_nodes must be positive");
+  TreeState& t = h->ts[k];
+  if (t.n_nodes == 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_set_tree must run before h2ot_gamma_pass");
+  TRY(t.d_gamma.ensure((size_t)n_leaf_nodes * 4));
+  CUDA_TRY(cudaMemsetAsync(t.d_gamma.p, 0, (size_t)n_leaf_nodes * 4 * sizeof(long long), h->stream));
+  GammaArgs ga{};
+  ga.n = h->n;
+  ga.family = h->cfg.family;
+  ga.leaf_start = leaf_start;
+  ga.n_leaf_nodes = n_leaf_nodes;
+  ga.rows_per_cta = 65536;
+  ga.resp = h->resp;
+  ga.w = h->w;
+  ga.work = t.work;
+  ga.nids = t.nids;
+  ga.nodes = t.nodes.p;
+  ga.bitsets = t.bitsets.p;
+  ga.cols = h->d_cols.p;
+  ga.acc = t.d_gamma.p;
+  const double b = t.work_bound > 0 ? t.work_bound : 1.0;
+  const int e_num = exponent_for(h->w_max * b, 17);  // <= 2^16 rows per CTA partial, one spare bit
+  const int e_den = exponent_for(h->w_max, 17);
+  ga.s_num = std::ldexp(1.0, e_num);
+  ga.s_den = std::ldexp(1.0, e_den);
+  const int grid = (int)((h->n + ga.rows_per_cta - 1) / ga.rows_per_cta);
+  TRY(t_begin(h, &h->stats.ms_gamma));
+  gamma_kernel<<<grid, 256, 0, h->stream>>>(ga);
+  h->stats.launches++;
+  TRY(t_end(h));
+  if (h->nccl.world > 1 && h->nccl.comm)
+    TRY(nccl_check(h, h->nccl.AllReduce(t.d_gamma.p, t.d_gamma.p, (size_t)n_leaf_nodes * 4, 4, 0, h->nccl.comm, h->stream), "ncclAllReduce(gamma)"));
+  std::vector<long long> acc((size_t)n_leaf_nodes * 4);
+  TRY(d2h(h, acc.data(), t.d_gamma.p, acc.size() * sizeof(long long)));
+  TRY(finish_call(h));
+  for (int i = 0; i < n_leaf_nodes; i++) {
+    if (out_num) out_num[i] = std::ldexp((double)acc[i * 4 + 0], kGammaSplitBits - e_num) + std::ldexp((double)acc[i * 4 + 1], -e_num);
+    if (out_denom) out_denom[i] = std::ldexp((double)acc[i * 4 + 2], kGammaSplitBits - e_den) + std::ldexp((double)acc[i * 4 + 3], -e_den);
+  }
+  return H2OT_OK;
+}
+
+int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (n_nodes <= 0 || !node_pred) H2OT_FAIL(H2OT_ERR_INVALID, "bad node_pred");
+  TreeState& t = h->ts[k];
+  TRY(t.d_pred.ensure(n_nodes));
+  TRY(h2d(h, t.d_pred.p, node_pred, (size_t)n_nodes * sizeof(float)));
+  AddTreeArgs a{h->n, n_nodes, h->resp, h->w, t.nids, t.F, t.d_pred.p};
+  TRY(t_begin(h, &h->stats.ms_addtree));
+  add_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  return finish_call(h);
+}
+
+// ------------------------------------------------------------------------------------------------ multi-GPU plumbing
+static int nccl_load(Nccl& n) {
+  if (n.lib) return H2OT_OK;
+  const char* names[] = {getenv("H2OT_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    if (!nm || !*nm) continue;
+    n.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+    if (n.lib) break;
+  }
+  if (!n.lib) H2OT_FAIL(H2OT_ERR_COMM, "cannot dlopen libnccl.so.2 (set H2OT_NCCL_LIB to its path)");
+  n.GetUniqueId = (int (*)(void*))dlsym(n.lib, "ncclGetUniqueId");
+  n.CommInitRank = (int (*)(void**, int, IdByValue, int))dlsym(n.lib, "ncclCommInitRank");
+  n.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(n.lib, "ncclAllReduce");
+  n.CommDestroy = (int (*)(void*))dlsym(n.lib, "ncclCommDestroy");
+  n.GetErrorString = (const char* (*)(int))dlsym(n.lib, "ncclGetErrorString");
+  if (!n.GetUniqueId || !n.CommInitRank || !n.AllReduce) H2OT_FAIL(H2OT_ERR_COMM, "libnccl is missing required symbols");
+  return H2OT_OK;
+}
+
+int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]) {
+  static Nccl loader;
+  TRY(nccl_load(loader));
+  IdByValue id;
+  int rc = loader.GetUniqueId(&id);
+  if (rc != 0) H2OT_FAIL(H2OT_ERR_COMM, "ncclGetUniqueId failed");
+  memcpy(out_id, id.internal, H2OT_COMM_ID_BYTES);
+  return H2OT_OK;
+}
+
+int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]) {
+  CHECK_ENGINE(h);
+  if (world_size < 1 || rank < 0 || rank >= world_size) H2OT_FAIL(H2OT_ERR_INVALID, "bad world size / rank");
+  h->nccl.world = world_size;
+  h->nccl.rank = rank;
+  if (world_size == 1) return H2OT_OK;
+  TRY(nccl_load(h->nccl));
+  IdByValue v;
+  memcpy(v.internal, id, H2OT_COMM_ID_BYTES);
+  return nccl_check(h, h->nccl.CommInitRank(&h->nccl.comm, world_size, v, rank), "ncclCommInitRank");
+}
+
+int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op) {
+  CHECK_ENGINE(h);
+  if (h->nccl.world <= 1 || !h->nccl.comm) return H2OT_OK;
+  DBuf<double> tmp;
+  TRY(tmp.ensure(n));
+  TRY(h2d(h, tmp.p, inout, (size_t)n * sizeof(double)));
+  TRY(nccl_check(h, h->nccl.AllReduce(tmp.p, tmp.p, (size_t)n, /*ncclFloat64*/ 8, op == 1 ? 2 : 0, h->nccl.comm, h->stream), "ncclAllReduce(f64)"));
+  TRY(d2h(h, inout, tmp.p, (size_t)n * sizeof(double)));
+  int r = finish_call(h);
+  tmp.release();
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------ diagnostics
+int h2ot_debug_bin_codes(h2ot_engine* h, int32_t col, const h2ot_hist_desc* desc, uint16_t* out_codes) {
+  CHECK_ENGINE(h);
+  if (col < 0 || col >= h->C || !desc || !out_codes) H2OT_FAIL(H2OT_ERR_INVALID, "bad arguments");
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  DBuf<uint16_t> tmp;
+  TRY(tmp.ensure(h->n));
+  ColRef cr{h->cols[col].data, h->cols[col].base, h->cols[col].storage, 0};
+  bin_codes_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, cr, desc->min, desc->step, desc->nbin,
+                                                                 (desc->flags & H2OT_DESC_CHECKFLOAT) ? 1 : 0, tmp.p);
+  h->stats.launches++;
+  TRY(d2h(h, out_codes, tmp.p, (size_t)h->n * sizeof(uint16_t)));
+  int r = finish_call(h);
+  tmp.release();
+  return r;
+}
+
+int h2ot_stats_get(h2ot_engine* h, h2ot_stats* out) {
+  if (!h || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  *out = h->stats;
+  return H2OT_OK;
+}
+int h2ot_stats_reset(h2ot_engine* h) {
+  if (!h) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  h->stats = h2ot_stats{};
+  return H2OT_OK;
+}
+int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode) {
+  if (!h || mode < 0 || mode > 1) H2OT_FAIL(H2OT_ERR_INVALID, "bad mode");
+  h->hist_mode = mode;
+  return H2OT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,279 @@
+// Per-tree row passes and frame ingest kernels.
+//  - rollup / encode : W/fvec/RollupStats.java:88-200 (min/max/isInt/naCnt) + lossless narrow storage
+//  - init            : GBM.initializeModelSpecifics / MarkDecidedRows, T/gbm/GBM.java:282-349
+//  - residuals       : GBM.ComputePredAndRes, T/gbm/GBM.java:1032-1081 (+ score1static :1486-1513, log_rescale G/GenModel.java:671-681)
+//  - sample          : T/Sample.java:22-36 on PCG (W/util/RandomUtils.java:50-119)
+//  - gamma           : GBM.GammaPass, T/gbm/GBM.java:1286-1407
+//  - add_tree        : GBM.AddTreeContributions, T/gbm/GBM.java:1410-1470
+#pragma once
+#include "common.cuh"
+#include "k_level.cuh"
+
+namespace h2ot {
+
+// ------------------------------------------------------------------------------------------ ingest
+struct RollupDev {
+  unsigned long long min_key;  // ~dkey(min) max-merged ; 0 == none
+  unsigned long long max_key;  // dkey(max)
+  unsigned long long nacnt;
+  unsigned int not_int;        // != 0 if some value is not integral
+  unsigned int not_f32;        // != 0 if some value is not fp32-exact
+};
+
+__global__ void __launch_bounds__(256) rollup_kernel(const double* v, int64_t n, RollupDev* out) {
+  unsigned long long mn = 0, mx = 0, na = 0;
+  unsigned int ni = 0, nf = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double d = v[i];
+    if (isnan(d)) { na++; continue; }
+    const unsigned long long k = dkey(d);
+    if (~k > mn) mn = ~k;
+    if (k > mx) mx = k;
+    // RollupStats._isInt: ((long)d) == d  (Java saturating cast)
+    const long long l = __double2ll_rz(d);
+    if ((double)l != d) ni = 1;
+    if ((double)(float)d != d) nf = 1;
+  }
+  // warp reduce then one atomic per warp
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long t;
+    t = __shfl_xor_sync(0xffffffffu, mn, o); if (t > mn) mn = t;
+    t = __shfl_xor_sync(0xffffffffu, mx, o); if (t > mx) mx = t;
+    na += __shfl_xor_sync(0xffffffffu, na, o);
+    ni |= __shfl_xor_sync(0xffffffffu, ni, o);
+    nf |= __shfl_xor_sync(0xffffffffu, nf, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (mn) atomicMax(&out->min_key, mn);
+    if (mx) atomicMax(&out->max_key, mx);
+    if (na) atomicAdd(&out->nacnt, na);
+    if (ni) atomicOr(&out->not_int, 1u);
+    if (nf) atomicOr(&out->not_f32, 1u);
+  }
+}
+
+// n_pad >= n : pad rows are written as NA
+__global__ void __launch_bounds__(256) encode_kernel(const double* v, int64_t n, int64_t n_pad, int storage, double base, void* out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pad; i += (int64_t)gridDim.x * blockDim.x) {
+    const double d = i < n ? v[i] : __longlong_as_double(0x7ff8000000000000LL);
+    switch (storage) {
+      case H2OT_STORE_F32: reinterpret_cast<float*>(out)[i] = (float)d; break;
+      case H2OT_STORE_F64: reinterpret_cast<double*>(out)[i] = d; break;
+      case H2OT_STORE_U8: reinterpret_cast<unsigned char*>(out)[i] = isnan(d) ? 255 : (unsigned char)(int)(d - base); break;
+      default: reinterpret_cast<unsigned short*>(out)[i] = isnan(d) ? 65535 : (unsigned short)(int)(d - base); break;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ init
+struct InitArgs {
+  int64_t n, n_pad;
+  int32_t K;
+  const double* resp;
+  const double* w;
+  int32_t* const* nids;  // [K]
+  unsigned long long* skipped;
+};
+__global__ void __launch_bounds__(256) init_rows_kernel(InitArgs a) {
+  unsigned long long cnt = 0;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n_pad; row += (int64_t)gridDim.x * blockDim.x) {
+    int v = H2OT_DECIDED_ROW;
+    if (row < a.n) {
+      const double wv = a.w ? a.w[row] : 1.0;
+      const bool skip = (wv == 0.0) || isnan(a.resp[row]);
+      v = skip ? H2OT_DECIDED_ROW : 0;
+      if (skip) cnt++;
+    }
+    for (int k = 0; k < a.K; k++) a.nids[k][row] = v;
+  }
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(a.skipped, cnt);
+}
+
+// ------------------------------------------------------------------------------------------ residuals
+struct ResidArgs {
+  int64_t n;
+  int32_t K, nclass, family;
+  const double* resp;
+  const double* w;
+  const double* off;
+  const double* const* F;  // [K] Tree_k (fp64: holds the double init_f until a row's first update, float valued after)
+  float* const* work;      // [K]
+  unsigned int* absmax;   // [K] float bits of max |work|
+};
+
+__device__ __forceinline__ double tree_val(const ResidArgs& a, int k, int64_t row) {
+  return a.F[k][row];
+}
+
+__global__ void __launch_bounds__(256) residuals_kernel(ResidArgs a) {
+  float amaxk = 0.f;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    const double wv = a.w ? a.w[row] : 1.0;
+    if (wv == 0.0) continue;
+    const double y = a.resp[row];
+    if (isnan(y)) continue;
+    const double f = tree_val(a, 0, row) + (a.off ? a.off[row] : 0.0);
+    if (a.family == H2OT_FAMILY_MULTINOMIAL) {
+      // score1static: fs[1] = f ; fs[k+1] = Tree_k ; log_rescale: max, exp(fs - max), sum in k order
+      double maxval = f;
+      for (int k = 1; k < a.nclass; k++) maxval = fmax(maxval, tree_val(a, k, row));
+      double dsum = 0;
+      for (int k = 0; k < a.nclass; k++) dsum += exp((k == 0 ? f : tree_val(a, k, row)) - maxval);
+      const int yi = (int)y;
+      for (int k = 0; k < a.nclass; k++) {
+        const double e = exp((k == 0 ? f : tree_val(a, k, row)) - maxval);
+        float r;
+        if (isinf(dsum)) r = (float)((double)(yi == k ? 1.0f : 0.0f) - (double)(isinf(e) ? 1.0f : 0.0f));
+        else r = (float)((double)(yi == k ? 1.0f : 0.0f) - (double)(float)(e / dsum));
+        a.work[k][row] = r;
+        amaxk = fmaxf(amaxk, fabsf(r));
+      }
+    } else {
+      double r;
+      if (a.family == H2OT_FAMILY_BERNOULLI) r = y - 1.0 / (1.0 + fmin(1e19, exp(-f)));  // LogitFunction.linkInv
+      else r = y - f;
+      const float rf = (float)r;
+      a.work[0][row] = rf;
+      amaxk = fmaxf(amaxk, fabsf(rf));
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) amaxk = fmaxf(amaxk, __shfl_xor_sync(0xffffffffu, amaxk, o));
+  // one bound shared by all K class-trees (max over k) keeps the kernel simple
+  if ((threadIdx.x & 31) == 0 && amaxk > 0.f)
+    for (int k = 0; k < a.K; k++) atomicMax(&a.absmax[k], __float_as_uint(amaxk));
+}
+
+// ------------------------------------------------------------------------------------------ sample
+__device__ __forceinline__ uint32_t pcg_next(unsigned long long& state, unsigned long long inc) {
+  const unsigned long long old = state;
+  state = old * 6364136223846793005ULL + inc;
+  const uint32_t xorshifted = (uint32_t)(((old >> 18) ^ old) >> 27);
+  const uint32_t rot = (uint32_t)(old >> 59);
+  return (xorshifted >> rot) | (xorshifted << ((-rot) & 31));
+}
+__global__ void __launch_bounds__(256) sample_kernel(int64_t n, int64_t row_offset, long long tree_seed, float rate,
+                                                     double rate_d, const double* resp, int32_t* nids) {
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (int64_t)gridDim.x * blockDim.x) {
+    bool skip = isnan(resp[row]);
+    if (!skip) {
+      // rand.setSeed(_tree._seed + row + nids.start()) ; nextFloat() = next(24) / (float)(1 << 24)
+      const unsigned long long inc = 3ULL;  // (seq << 1) | 1 with seq == 1
+      unsigned long long state = 0ULL;
+      pcg_next(state, inc);
+      state += (unsigned long long)tree_seed + (unsigned long long)(row + row_offset);
+      pcg_next(state, inc);
+      const uint32_t hi = pcg_next(state, inc);
+      const uint32_t lo = pcg_next(state, inc);
+      (void)hi;
+      const int bits24 = (int)(lo & 0xFFFFFFu);  // next(24) keeps the low 24 bits of nextLong()
+      const float u = (float)bits24 / (float)(1 << 24);
+      skip = (double)u >= rate_d;  // float compared with the double rate
+    }
+    if (skip) nids[row] = H2OT_OUT_OF_BAG;
+  }
+}
+
+// ------------------------------------------------------------------------------------------ gamma
+struct GammaArgs {
+  int64_t n;
+  int32_t family, leaf_start, n_leaf_nodes, rows_per_cta;
+  const double* resp;
+  const double* w;
+  const float* work;
+  int32_t* nids;
+  const h2ot_decided_node* nodes;
+  const uint8_t* bitsets;
+  const ColRef* cols;
+  long long* acc;  // [n_leaf_nodes][4] : num.hi, num.lo, den.hi, den.lo (fixed point, split at bit 24)
+  double s_num, s_den;
+};
+constexpr int kGammaSmemLeaves = 2048;
+constexpr int kGammaSplitBits = 24;
+
+__global__ void __launch_bounds__(256) gamma_kernel(GammaArgs a) {
+  __shared__ uint32_t s_acc[kGammaSmemLeaves * 4];
+  const bool use_s = a.n_leaf_nodes <= kGammaSmemLeaves;
+  if (use_s)
+    for (int i = threadIdx.x; i < a.n_leaf_nodes * 4; i += blockDim.x) s_acc[i] = 0;
+  __syncthreads();
+  const int64_t lo = (int64_t)blockIdx.x * a.rows_per_cta;
+  const int64_t hi = min(a.n, lo + (int64_t)a.rows_per_cta);
+  for (int64_t row = lo + threadIdx.x; row < hi; row += blockDim.x) {
+    const double wv = a.w ? a.w[row] : 1.0;
+    if (wv == 0.0) continue;
+    const double y = a.resp[row];
+    if (isnan(y)) continue;
+    int nid = a.nids[row];
+    const bool oob = nid <= H2OT_OUT_OF_BAG;
+    if (oob) nid = -nid + H2OT_OUT_OF_BAG;
+    if (nid < 0) continue;
+    h2ot_decided_node dn = a.nodes[nid];
+    if (dn.col < 0) dn = a.nodes[dn.pid];
+    const int leafnid = child_node_id(dn, a.cols, a.bitsets, row);
+    a.nids[row] = leafnid;
+    if (oob) continue;
+    const int idx = leafnid - a.leaf_start;
+    if (idx < 0 || idx >= a.n_leaf_nodes) continue;
+    const double z = (double)a.work[row];
+    const double num = __dmul_rn(wv, z);
+    double den;
+    if (a.family == H2OT_FAMILY_GAUSSIAN) den = wv;
+    else if (a.family == H2OT_FAMILY_BERNOULLI) {
+      const double ff = __dsub_rn(y, z);
+      den = __dmul_rn(__dmul_rn(wv, ff), __dsub_rn(1.0, ff));
+    } else {
+      const double az = fabs(z);
+      den = __dmul_rn(wv, __dmul_rn(az, __dsub_rn(1.0, az)));
+    }
+    const long long qn = __double2ll_rn(__dmul_rn(num, a.s_num));
+    const long long qd = __double2ll_rn(__dmul_rn(den, a.s_den));
+    if (use_s) {
+      smem_add64(&s_acc[idx * 4], qn);
+      smem_add64(&s_acc[idx * 4 + 2], qd);
+    } else {
+      unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc + (size_t)idx * 4);
+      atomicAdd(g, (unsigned long long)(qn >> kGammaSplitBits));
+      atomicAdd(g + 1, (unsigned long long)(qn & ((1LL << kGammaSplitBits) - 1)));
+      atomicAdd(g + 2, (unsigned long long)(qd >> kGammaSplitBits));
+      atomicAdd(g + 3, (unsigned long long)(qd & ((1LL << kGammaSplitBits) - 1)));
+    }
+  }
+  __syncthreads();
+  if (use_s)
+    for (int i = threadIdx.x; i < a.n_leaf_nodes * 2; i += blockDim.x) {
+      const long long v = (long long)(((unsigned long long)s_acc[i * 2 + 1] << 32) | s_acc[i * 2]);
+      if (v == 0) continue;
+      unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc + (size_t)(i >> 1) * 4 + (i & 1) * 2);
+      atomicAdd(g, (unsigned long long)(v >> kGammaSplitBits));
+      atomicAdd(g + 1, (unsigned long long)(v & ((1LL << kGammaSplitBits) - 1)));
+    }
+}
+
+// ------------------------------------------------------------------------------------------ add tree
+struct AddTreeArgs {
+  int64_t n;
+  int32_t n_nodes;
+  const double* resp;
+  const double* w;
+  int32_t* nids;
+  double* F;
+  const float* node_pred;
+};
+__global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    const int nid = a.nids[row];
+    int nv = 0;  // FRESH
+    if (nid < 0) {
+      const double wv = a.w ? a.w[row] : 1.0;
+      if (wv == 0.0 || isnan(a.resp[row])) nv = H2OT_DECIDED_ROW;
+      a.nids[row] = nv;
+      continue;
+    }
+    a.nids[row] = nv;
+    const float pred = nid < a.n_nodes ? a.node_pred[nid] : 0.f;
+    a.F[row] = (double)(float)__dadd_rn(a.F[row], (double)pred);  // float-rounded every tree (q3)
+  }
+}
+
+}  // namespace h2ot

@@ -1,0 +1,225 @@
+/*
+ * h2ot.h — C ABI of libh2otree_b200.so: the B200-native engine behind H2O-3's hex.tree
+ * ScoreBuildHistogram2 seam (per-level score-rows + build-histograms + find-splits, plus the GBM
+ * per-tree row passes).
+ *
+ * The reference has no FFI for this path: the seam is the Java class boundary where
+ * SharedTree.ScoreBuildOneTree.compute2 constructs ScoreBuildHistogram2 and calls dfork2
+ * (h2o-algos/src/main/java/hex/tree/SharedTree.java:671-683). A Java subclass
+ * (ScoreBuildHistogramGPU) binds these entry points over JNI / Panama FFM.
+ * Each entry point below cites the reference code it replaces (paths relative to the reference root;
+ * T/ = h2o-algos/src/main/java/hex/tree/, W/ = h2o-core/src/main/java/water/).
+ *
+ * Conventions: plain C types only; every function returns 0 (H2OT_OK) or a negative error code and
+ * never throws; h2ot_last_error() returns a thread-local UTF-8 message for the last failure on the
+ * calling thread. Handles are opaque; calls on one handle must be serialised by the caller;
+ * different handles are independent. All calls block until their device work is complete unless
+ * stated otherwise. There is NO CPU fallback: with no CUDA device h2ot_create fails.
+ */
+#ifndef H2OT_H
+#define H2OT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define H2OT_OK 0
+#define H2OT_ERR_INVALID -1   /* bad argument / call order */
+#define H2OT_ERR_CUDA -2      /* CUDA runtime error (message has the CUDA string) */
+#define H2OT_ERR_NOMEM -3
+#define H2OT_ERR_UNSUPPORTED -4
+#define H2OT_ERR_COMM -5      /* NCCL error */
+
+/* hex.genmodel.utils.DistributionFamily subset handled on device (H/DistributionFactory.java:73-134,243-272) */
+#define H2OT_FAMILY_GAUSSIAN 0
+#define H2OT_FAMILY_BERNOULLI 1
+#define H2OT_FAMILY_MULTINOMIAL 2
+
+/* T/DHistogram.java:152-168 NASplitDir */
+#define H2OT_NA_NONE 0
+#define H2OT_NA_VS_REST 1
+#define H2OT_NA_LEFT 2
+#define H2OT_NA_RIGHT 3
+#define H2OT_LEFT 4
+#define H2OT_RIGHT 5
+
+/* T/ScoreBuildHistogram.java:60-67 row markers kept in the NIDs_k column */
+#define H2OT_DECIDED_ROW (-1)
+#define H2OT_OUT_OF_BAG (-2)
+
+/* column storage chosen by the ingest kernel (lossless, order preserving) */
+#define H2OT_STORE_F32 0 /* every non-NA value is fp32-exact */
+#define H2OT_STORE_F64 1
+#define H2OT_STORE_U8 2  /* integer valued, max-min < 255 : code = x - min, 255 = NA */
+#define H2OT_STORE_U16 3 /* integer valued, max-min < 65535 : code = x - min, 65535 = NA */
+
+typedef struct h2ot_engine h2ot_engine;
+
+typedef struct h2ot_config {
+  int32_t device;        /* CUDA device ordinal */
+  int32_t ncols;         /* predictor columns */
+  int64_t nrows;         /* rows held by THIS engine (this rank's shard) */
+  int64_t row_offset;    /* global index of local row 0 (T/Sample.java:31 seeds by global row) */
+  int64_t nrows_global;  /* rows over all ranks (fixes the histogram fixed-point scale); 0 => nrows */
+  int32_t nclass_trees;  /* K: class-trees built per iteration (1 for regression/binomial) */
+  int32_t nclass;        /* 1 regression, 2 binomial, >2 multinomial */
+  int32_t family;        /* H2OT_FAMILY_* */
+  int32_t has_weights;
+  int32_t has_offset;
+  int32_t reserved;
+} h2ot_config;
+
+/* Per (leaf, column) histogram descriptor == the DHistogram fields the CPU kernel reads
+ * (T/DHistogram.java:56-62, ctor :190-269). Built by the host (Java keeps DHistogram/DTree). */
+typedef struct h2ot_hist_desc {
+  double min;      /* _min */
+  double maxEx;    /* _maxEx */
+  double step;     /* _step */
+  int32_t nbin;    /* _nbin (NA bucket excluded) */
+  int16_t order;   /* position of the column in the leaf's _scoreCols (column index if null): bestCol tie order, T/DTree.java:631-654 */
+  uint8_t flags;   /* H2OT_DESC_* */
+  uint8_t pad;
+} h2ot_hist_desc;
+#define H2OT_DESC_ACTIVE 1      /* DHistogram non-null AND column in the leaf's _scoreCols (T/ScoreBuildHistogram2.java:421-426) */
+#define H2OT_DESC_ISINT 2       /* _isInt > 0 */
+#define H2OT_DESC_ISCAT 4       /* _isInt == 2 */
+#define H2OT_DESC_INTOPT 8      /* _intOpt (only changes the untouched _min2/_maxIn sentinels, T/DHistogram.java:677-703) */
+#define H2OT_DESC_CHECKFLOAT 16 /* _checkFloatSplits (DRF, T/drf/DRF.java:201) */
+#define H2OT_DESC_INITNA 32     /* _initNA */
+
+/* One DecidedNode as score_decide / GammaPass read it (T/DTree.java:587-763). */
+typedef struct h2ot_decided_node {
+  int32_t nid;
+  int32_t pid;        /* -1 for the root */
+  int32_t col;        /* _split._col, -1 when _split == null */
+  int32_t equal;      /* _split._equal: 0 range split, 2/3 bitset split */
+  int32_t nasplit;    /* H2OT_NA_* */
+  float splat;        /* _splat (float; the row test is double >= float, T/DTree.java:738) */
+  int32_t child[2];   /* _nids */
+  int32_t bs_off;     /* byte offset of the IcedBitSet bytes in the bitset pool (equal >= 2) */
+  int32_t bs_nbits;   /* IcedBitSet._nbits */
+  int32_t bs_bitoff;  /* IcedBitSet._bitoff */
+  int32_t pad;
+} h2ot_decided_node;
+
+#define H2OT_MAX_BITSET_BYTES 512 /* nbins_cats <= 4096 */
+
+/* DTree.Split (T/DTree.java:182-209) + _splat, as produced by the device split search. */
+typedef struct h2ot_split {
+  int32_t col;      /* -1: no split found (DecidedNode._split == null) */
+  int32_t bin;
+  int32_t nasplit;
+  int32_t equal;
+  float splat;      /* Split.splat(hs) (T/DTree.java:240-291); NaN when abandoned */
+  int32_t bs_nbits, bs_bitoff, bs_nbytes;
+  double se, se0, se1, n0, n1, p0, p1, tree_p0, tree_p1;
+  uint8_t bs[H2OT_MAX_BITSET_BYTES];
+} h2ot_split;
+
+typedef struct h2ot_column_info { /* rollups: W/fvec/RollupStats.java:31-48 */
+  double min, max;   /* over non-NA values (NaN if all NA) */
+  int64_t nacnt;
+  int32_t is_int;    /* every non-NA value integral */
+  int32_t storage;   /* H2OT_STORE_* */
+} h2ot_column_info;
+
+typedef struct h2ot_stats { /* diagnostics: device time per kernel family (ms) and launch counts since create / last reset */
+  double ms_score, ms_hist, ms_finalize, ms_split, ms_residuals, ms_gamma, ms_addtree, ms_sample, ms_ingest;
+  int64_t launches;          /* kernels launched by this library */
+  int64_t h2d_bytes, d2h_bytes;
+  int64_t hist_rows_cols;    /* sum over level passes of local rows x active columns */
+  int64_t hist_algo_bytes;   /* algorithmic bytes of those passes (SURVEY.md section 8d formula) */
+} h2ot_stats;
+
+/* ---- lifetime: one engine per model build per GPU (created after T/SharedTree.java:385, destroyed in the finally at :407-425) */
+int h2ot_version(void);
+const char* h2ot_last_error(void);
+int h2ot_device_count(int32_t* out);
+int h2ot_create(const h2ot_config* cfg, h2ot_engine** out);
+int h2ot_destroy(h2ot_engine* h);
+
+/* ---- frame ingest: the host pushes what Chunk.getDoubles hands to DHistogram.extractData
+ * (T/DHistogram.java:715-728, W/fvec/Chunk.java:785-794); NaN == NA. Columns may arrive in pieces
+ * (one call per Chunk). is_categorical/cardinality mirror Vec.isCategorical()/domain().length. */
+int h2ot_load_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, const double* values);
+int h2ot_load_response(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
+int h2ot_load_weights(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
+int h2ot_load_offset(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
+/* rollups (min/max/isInt/naCnt) + lossless narrow encoding of every loaded column, resident in HBM */
+int h2ot_finalize_frame(h2ot_engine* h);
+int h2ot_column_info_get(h2ot_engine* h, int32_t col, h2ot_column_info* out);
+
+/* ---- model state sync with the Java work vecs (Tree_k / Work_k / NIDs_k; T/SharedTree.java:364-385,464-475) */
+/* GBM.initializeModelSpecifics (T/gbm/GBM.java:282-311): Tree_k <- init_f[k]; rows with w==0 or NA response <- DECIDED_ROW. */
+int h2ot_init_model(h2ot_engine* h, const double* init_f /*[K]*/, int64_t* out_skipped);
+int h2ot_set_predictions(h2ot_engine* h, int32_t k, const double* f);
+int h2ot_get_predictions(h2ot_engine* h, int32_t k, double* f);
+int h2ot_get_work(h2ot_engine* h, int32_t k, double* work);
+int h2ot_set_work(h2ot_engine* h, int32_t k, const double* work, double abs_bound);
+int h2ot_get_nids(h2ot_engine* h, int32_t k, int32_t* nids);
+int h2ot_set_nids(h2ot_engine* h, int32_t k, const int32_t* nids);
+
+/* ---- per tree */
+/* GBM.ComputePredAndRes (T/gbm/GBM.java:1032-1081): Work_k <- (float) negHalfGradient for all K.
+ * out_abs_max[k] receives max |Work_k| over local rows (fixes the fixed-point scale; nullable). */
+int h2ot_compute_residuals(h2ot_engine* h, double* out_abs_max /*[K]*/);
+/* Starts class-tree k: clears its node table, fixes the accumulator scale from work_abs_bound
+ * (>= max |Work_k| over ALL ranks), and runs Sample (T/Sample.java:22-36) when sample_rate < 1. */
+int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate, double work_abs_bound);
+
+/* ---- per level: the drop-in for new ScoreBuildHistogram2(...).dfork2(fr2) (T/SharedTree.java:681-682).
+ * decided[0..n_decided): the DecidedNodes created by the previous level's onCompletion (nid order);
+ * descs[n_leaves][ncols]: the UndecidedNodes' DHistograms for nids leaf_offset..leaf_offset+n_leaves-1.
+ * Runs score_decide (T/ScoreBuildHistogram2.java:139-168,201-211) then the histogram build
+ * (T/DHistogram.java:609-704) for every active (leaf, col). Results stay on the device. */
+int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                     const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
+                     const h2ot_hist_desc* descs);
+/* Device buffers of the level just built, for the cross-rank exchange that replaces MRTask.reduce /
+ * ScoreBuildHistogram.reduce / DHistogram.add (T/ScoreBuildHistogram.java:74-88, T/DHistogram.java:434-447):
+ * sums[n_sums] int64 (allreduce SUM) and minmax[n_minmax] uint64 order-preserving keys laid out so that
+ * an allreduce MAX merges both bounds (min is stored complemented). Single rank: skip. */
+int h2ot_level_buffers(h2ot_engine* h, int32_t k, void** d_sums, int64_t* n_sums, void** d_minmax, int64_t* n_minmax);
+/* Built-in exchange over NCCL (h2ot_comm_init must have been called); no-op for world size 1. */
+int h2ot_allreduce_level(h2ot_engine* h, int32_t k);
+/* postGlobal (T/ScoreBuildHistogram2.java:455-466): fixed-point -> fp64, reducePrecision (T/DHistogram.java:734-740).
+ * Optional host copies (all nullable): vals packed per active (leaf,col) in [leaf][col] order, (nbin+1)*3 doubles each;
+ * val_offsets[n_leaves*ncols] = start (in doubles) of each block or -1; min2/maxIn[n_leaves*ncols]; has_vals = _vals != null. */
+int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_vals_capacity, int64_t* out_val_offsets,
+                      double* out_min2, double* out_maxIn, uint8_t* out_has_vals);
+/* DecidedNode ctor's bestCol / FindSplits / findBestSplitPoint / splat (T/DTree.java:616-726, 984-1487, 240-291)
+ * on the histograms of the level just finished. out_splits[n_leaves]. */
+int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_split_improvement, h2ot_split* out_splits);
+
+/* ---- end of tree */
+/* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */
+int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,
+                  int64_t bitset_bytes);
+/* GBM.GammaPass (T/gbm/GBM.java:1286-1407): final descent (NIDs_k <- leaf nid) and per-leaf sums.
+ * out_num/out_denom[n_leaf_nodes] for leaf nids leaf_start..leaf_start+n_leaf_nodes-1 (local rows only;
+ * h2ot_gamma_buffers exposes the device int64 buffers for a cross-rank SUM before reading). */
+int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_leaf_nodes, double* out_num, double* out_denom);
+/* GBM.AddTreeContributions (T/gbm/GBM.java:1410-1470): Tree_k <- (float)(Tree_k + pred[nid]); NIDs_k <- 0 / DECIDED_ROW. */
+int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred /*[n_nodes], leaf nids used*/);
+
+/* ---- multi-GPU plumbing (one process per GPU; rows sharded; replaces the MRTask node tree, W/MRTask.java:695-756,871-930) */
+#define H2OT_COMM_ID_BYTES 128
+int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]);
+int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
+int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op /*0 sum, 1 max*/);
+
+/* ---- diagnostics / parity hooks */
+/* Per-row bin index of column col under desc (DHistogram.bin, T/DHistogram.java:272-306), uint16 codes to the host. */
+int h2ot_debug_bin_codes(h2ot_engine* h, int32_t col, const h2ot_hist_desc* desc, uint16_t* out_codes);
+int h2ot_stats_get(h2ot_engine* h, h2ot_stats* out);
+int h2ot_stats_reset(h2ot_engine* h);
+/* 0: shared-memory privatised histograms (default), 1: global (L2) atomics only — used by tests to cross-check. */
+int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* H2OT_H */

@@ -1,0 +1,84 @@
+/*
+ * h2ot_gbm.h — C ABI of the host-side GBM driver shipped in libh2otree_b200.so.
+ *
+ * In an H2O-3 deployment this layer IS the unchanged Java code (hex.tree.SharedTree / gbm.GBM / DTree /
+ * DHistogram): it keeps the trees, builds the per-level DHistogram descriptors and sequences the levels,
+ * calling the engine (include/h2ot.h) where ScoreBuildHistogram2 and the GBM row passes used to run.
+ * No JDK exists in this build image, so the same sequencing is written in C++ (h2o-3_b200/csrc/host_gbm.cpp)
+ * strictly on top of the public C ABI of h2ot.h — it is what the tests, the benchmark and non-JVM users call.
+ * Parameter names and meanings are those of GBMV3/SharedTreeV3
+ * (h2o-algos/src/main/java/hex/schemas/GBMV3.java:13-75, hex/tree/SharedTreeModel.java:51-98, hex/tree/gbm/GBMModel.java:24-41).
+ */
+#ifndef H2OT_GBM_H
+#define H2OT_GBM_H
+#include "h2ot.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct h2ot_gbm h2ot_gbm;
+
+typedef struct h2ot_gbm_params {
+  int32_t ntrees, max_depth, nbins, nbins_cats, nbins_top_level, family, nclass, reserved;
+  double min_rows, min_split_improvement, sample_rate, col_sample_rate, col_sample_rate_per_tree,
+      col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
+  int64_t seed;
+} h2ot_gbm_params;
+
+/* Flat view of one DTree node (DecidedNode / LeafNode, T/DTree.java:587-965) */
+typedef struct h2ot_tree_node {
+  int32_t kind; /* 0 undecided (never in a finished tree), 1 decided, 2 leaf */
+  int32_t pid, nid, nid0, nid1;
+  float splat, pred;
+  int32_t has_split;
+  int32_t col, bin, nasplit, equal;
+  double se, se0, se1, n0, n1, p0, p1, tree_p0, tree_p1;
+  int32_t bs_nbits, bs_bitoff, bs_nbytes;
+  uint8_t bs[H2OT_MAX_BITSET_BYTES];
+} h2ot_tree_node;
+
+typedef struct h2ot_gbm_timing {
+  double total_s;        /* wall seconds spent in h2ot_gbm_train */
+  double level_s;        /* wall seconds inside the per-level engine calls (score + histogram + finalize + split search) */
+  double hist_rows_cols; /* sum over level passes of global rows x active columns */
+  int64_t levels;        /* number of level passes */
+} h2ot_gbm_timing;
+
+int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int32_t ncols, int64_t row_offset,
+                    int64_t nrows_global, int32_t has_weights, int32_t has_offset, h2ot_gbm** out);
+int h2ot_gbm_destroy(h2ot_gbm* g);
+/* one call per column: full local column, NaN == NA; categorical columns carry integer level codes */
+int h2ot_gbm_set_column(h2ot_gbm* g, int32_t col, const double* values, int32_t is_categorical, int32_t cardinality);
+int h2ot_gbm_set_response(h2ot_gbm* g, const double* y);
+int h2ot_gbm_set_weights(h2ot_gbm* g, const double* w);
+int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o);
+int h2ot_gbm_comm_init(h2ot_gbm* g, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
+/* Frame finalisation, rollups, init_f, MarkDecidedRows (GBM.initializeModelSpecifics, T/gbm/GBM.java:254-312) */
+int h2ot_gbm_init(h2ot_gbm* g);
+/* Builds the next n iterations (GBM.buildNextKTrees, T/gbm/GBM.java:464-591) */
+int h2ot_gbm_train(h2ot_gbm* g, int32_t n_iterations);
+int h2ot_gbm_capture_levels(h2ot_gbm* g, int32_t on); /* histogram monitor analogue (T/SharedTree.java:1253-1289) */
+
+double h2ot_gbm_init_f(h2ot_gbm* g);
+int32_t h2ot_gbm_ntrees(h2ot_gbm* g);
+int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k);
+int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k);
+int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out);
+int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out);
+int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
+int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
+h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);
+
+/* captured levels */
+int32_t h2ot_gbm_ncaptures(h2ot_gbm* g);
+int h2ot_gbm_capture_info(h2ot_gbm* g, int32_t i, int32_t* tree, int32_t* k, int32_t* leaf, int32_t* nleaves);
+int h2ot_gbm_capture_desc(h2ot_gbm* g, int32_t i, int32_t n, int32_t c, h2ot_hist_desc* desc, double* min2, double* maxIn,
+                          int32_t* has_vals, int64_t* nvals);
+int h2ot_gbm_capture_vals(h2ot_gbm* g, int32_t i, int32_t n, int32_t c, double* out);
+int h2ot_gbm_capture_nids(h2ot_gbm* g, int32_t i, int32_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
