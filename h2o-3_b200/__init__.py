@@ -1,0 +1,521 @@
+"""h2o-3_b200 — Python (ctypes) binding of libh2otree_b200.so, the B200-native engine behind H2O-3's
+hex.tree ScoreBuildHistogram2 seam.
+
+Import with ``importlib.import_module("h2o-3_b200")`` (the directory name is not a Python identifier).
+
+Two layers, both thin wrappers over the C ABI declared in include/h2ot.h and include/h2ot_gbm.h:
+
+* ``Engine``  — the per-level drop-in (h2ot_* entry points): what a Java ``ScoreBuildHistogramGPU`` binds.
+* ``GBM``     — the host-side model builder (h2ot_gbm_* entry points); parameter names are those of
+  ``H2OGradientBoostingEstimator`` / GBMV3 (ntrees, max_depth, nbins, nbins_cats, min_rows, sample_rate,
+  col_sample_rate, learn_rate, distribution, seed ...).
+
+There is no CPU fallback: loading fails loudly when the shared library is missing, and engine creation
+fails when no CUDA device is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libh2otree_b200.so")
+
+OK = 0
+FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2}
+NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT, LEFT, RIGHT = 0, 1, 2, 3, 4, 5
+DECIDED_ROW, OUT_OF_BAG = -1, -2
+STORE_F32, STORE_F64, STORE_U8, STORE_U16 = 0, 1, 2, 3
+DESC_ACTIVE, DESC_ISINT, DESC_ISCAT, DESC_INTOPT, DESC_CHECKFLOAT, DESC_INITNA = 1, 2, 4, 8, 16, 32
+MAX_BITSET_BYTES = 512
+COMM_ID_BYTES = 128
+
+
+class H2OTError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("h2ot error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("ncols", C.c_int32), ("nrows", C.c_int64), ("row_offset", C.c_int64),
+                ("nrows_global", C.c_int64), ("nclass_trees", C.c_int32), ("nclass", C.c_int32), ("family", C.c_int32),
+                ("has_weights", C.c_int32), ("has_offset", C.c_int32), ("reserved", C.c_int32)]
+
+
+class HistDesc(C.Structure):
+    _fields_ = [("min", C.c_double), ("maxEx", C.c_double), ("step", C.c_double), ("nbin", C.c_int32),
+                ("order", C.c_int16), ("flags", C.c_uint8), ("pad", C.c_uint8)]
+
+
+class DecidedNode(C.Structure):
+    _fields_ = [("nid", C.c_int32), ("pid", C.c_int32), ("col", C.c_int32), ("equal", C.c_int32),
+                ("nasplit", C.c_int32), ("splat", C.c_float), ("child", C.c_int32 * 2), ("bs_off", C.c_int32),
+                ("bs_nbits", C.c_int32), ("bs_bitoff", C.c_int32), ("pad", C.c_int32)]
+
+
+class Split(C.Structure):
+    _fields_ = [("col", C.c_int32), ("bin", C.c_int32), ("nasplit", C.c_int32), ("equal", C.c_int32),
+                ("splat", C.c_float), ("bs_nbits", C.c_int32), ("bs_bitoff", C.c_int32), ("bs_nbytes", C.c_int32),
+                ("se", C.c_double), ("se0", C.c_double), ("se1", C.c_double), ("n0", C.c_double), ("n1", C.c_double),
+                ("p0", C.c_double), ("p1", C.c_double), ("tree_p0", C.c_double), ("tree_p1", C.c_double),
+                ("bs", C.c_uint8 * MAX_BITSET_BYTES)]
+
+
+class ColumnInfo(C.Structure):
+    _fields_ = [("min", C.c_double), ("max", C.c_double), ("nacnt", C.c_int64), ("is_int", C.c_int32),
+                ("storage", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("ms_score", C.c_double), ("ms_hist", C.c_double), ("ms_finalize", C.c_double),
+                ("ms_split", C.c_double), ("ms_residuals", C.c_double), ("ms_gamma", C.c_double),
+                ("ms_addtree", C.c_double), ("ms_sample", C.c_double), ("ms_ingest", C.c_double),
+                ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
+                ("hist_rows_cols", C.c_int64), ("hist_algo_bytes", C.c_int64), ("hist_launches", C.c_int64)]
+
+
+class GbmParams(C.Structure):
+    _fields_ = [("ntrees", C.c_int32), ("max_depth", C.c_int32), ("nbins", C.c_int32), ("nbins_cats", C.c_int32),
+                ("nbins_top_level", C.c_int32), ("family", C.c_int32), ("nclass", C.c_int32), ("reserved", C.c_int32),
+                ("min_rows", C.c_double), ("min_split_improvement", C.c_double), ("sample_rate", C.c_double),
+                ("col_sample_rate", C.c_double), ("col_sample_rate_per_tree", C.c_double),
+                ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
+                ("learn_rate_annealing", C.c_double), ("max_abs_leafnode_pred", C.c_double), ("seed", C.c_int64)]
+
+
+class TreeNode(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("pid", C.c_int32), ("nid", C.c_int32), ("nid0", C.c_int32), ("nid1", C.c_int32),
+                ("splat", C.c_float), ("pred", C.c_float), ("has_split", C.c_int32), ("col", C.c_int32),
+                ("bin", C.c_int32), ("nasplit", C.c_int32), ("equal", C.c_int32),
+                ("se", C.c_double), ("se0", C.c_double), ("se1", C.c_double), ("n0", C.c_double), ("n1", C.c_double),
+                ("p0", C.c_double), ("p1", C.c_double), ("tree_p0", C.c_double), ("tree_p1", C.c_double),
+                ("bs_nbits", C.c_int32), ("bs_bitoff", C.c_int32), ("bs_nbytes", C.c_int32),
+                ("bs", C.c_uint8 * MAX_BITSET_BYTES)]
+
+
+class GbmTiming(C.Structure):
+    _fields_ = [("total_s", C.c_double), ("level_s", C.c_double), ("hist_rows_cols", C.c_double), ("levels", C.c_int64)]
+
+
+# every symbol declared in include/h2ot.h and include/h2ot_gbm.h (tests check that the library exports all of them)
+ENGINE_SYMBOLS = [
+    "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
+    "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
+    "h2ot_init_model", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
+    "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
+    "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_set_tree",
+    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
+    "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
+    "h2ot_set_hist_mode",
+]
+GBM_SYMBOLS = [
+    "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
+    "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
+    "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
+    "h2ot_gbm_predictions", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
+    "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
+]
+
+_lib = None
+
+
+def load():
+    """Loads libh2otree_b200.so. Raises if it was not built (``python h2o-3_b200/build.py``): no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError("libh2otree_b200.so is missing (%s); build it with `python h2o-3_b200/build.py` — "
+                          "there is no CPU or PyTorch fallback" % SO_PATH)
+    L = C.CDLL(SO_PATH)
+    vp, i32, i64, dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+    L.h2ot_last_error.restype = C.c_char_p
+    L.h2ot_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.h2ot_destroy.argtypes = [vp]
+    L.h2ot_device_count.argtypes = [C.POINTER(i32)]
+    for n in ("h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset"):
+        getattr(L, n).argtypes = [vp, i64, i64, vp]
+    L.h2ot_load_column.argtypes = [vp, i32, i64, i64, vp]
+    L.h2ot_finalize_frame.argtypes = [vp]
+    L.h2ot_column_info_get.argtypes = [vp, i32, C.POINTER(ColumnInfo)]
+    L.h2ot_init_model.argtypes = [vp, vp, C.POINTER(i64)]
+    for n in ("h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_get_nids", "h2ot_set_nids"):
+        getattr(L, n).argtypes = [vp, i32, vp]
+    L.h2ot_set_work.argtypes = [vp, i32, vp, dbl]
+    L.h2ot_compute_residuals.argtypes = [vp, vp]
+    L.h2ot_begin_tree.argtypes = [vp, i32, i64, dbl, dbl]
+    L.h2ot_build_level.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp]
+    L.h2ot_level_buffers.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(vp), C.POINTER(i64)]
+    L.h2ot_allreduce_level.argtypes = [vp, i32]
+    L.h2ot_finish_level.argtypes = [vp, i32, vp, i64, vp, vp, vp, vp, vp]
+    L.h2ot_find_splits.argtypes = [vp, i32, dbl, dbl, vp]
+    L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
+    L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
+    L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]
+    L.h2ot_comm_unique_id.argtypes = [vp]
+    L.h2ot_comm_init.argtypes = [vp, i32, i32, vp]
+    L.h2ot_allreduce_host_f64.argtypes = [vp, vp, i64, i32]
+    L.h2ot_get_weight_bound.argtypes = [vp, C.POINTER(dbl)]
+    L.h2ot_set_weight_bound.argtypes = [vp, dbl]
+    L.h2ot_debug_bin_codes.argtypes = [vp, i32, C.POINTER(HistDesc), vp]
+    L.h2ot_stats_get.argtypes = [vp, C.POINTER(Stats)]
+    L.h2ot_stats_reset.argtypes = [vp]
+    L.h2ot_set_hist_mode.argtypes = [vp, i32]
+    L.h2ot_gbm_create.argtypes = [C.POINTER(GbmParams), i32, i64, i32, i64, i64, i32, i32, C.POINTER(vp)]
+    L.h2ot_gbm_destroy.argtypes = [vp]
+    L.h2ot_gbm_set_column.argtypes = [vp, i32, vp, i32, i32]
+    for n in ("h2ot_gbm_set_response", "h2ot_gbm_set_weights", "h2ot_gbm_set_offset"):
+        getattr(L, n).argtypes = [vp, vp]
+    L.h2ot_gbm_comm_init.argtypes = [vp, i32, i32, vp]
+    L.h2ot_gbm_init.argtypes = [vp]
+    L.h2ot_gbm_train.argtypes = [vp, i32]
+    L.h2ot_gbm_capture_levels.argtypes = [vp, i32]
+    L.h2ot_gbm_init_f.argtypes = [vp]
+    L.h2ot_gbm_init_f.restype = dbl
+    L.h2ot_gbm_ntrees.argtypes = [vp]
+    L.h2ot_gbm_tree_len.argtypes = [vp, i32, i32]
+    L.h2ot_gbm_tree_leaves_start.argtypes = [vp, i32, i32]
+    L.h2ot_gbm_tree_nodes.argtypes = [vp, i32, i32, vp]
+    L.h2ot_gbm_predictions.argtypes = [vp, i32, vp]
+    L.h2ot_gbm_varimp.argtypes = [vp, vp]
+    L.h2ot_gbm_timing_get.argtypes = [vp, C.POINTER(GbmTiming)]
+    L.h2ot_gbm_engine.argtypes = [vp]
+    L.h2ot_gbm_engine.restype = vp
+    L.h2ot_gbm_ncaptures.argtypes = [vp]
+    L.h2ot_gbm_capture_info.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.h2ot_gbm_capture_desc.argtypes = [vp, i32, i32, i32, C.POINTER(HistDesc), C.POINTER(dbl), C.POINTER(dbl),
+                                        C.POINTER(i32), C.POINTER(i64)]
+    L.h2ot_gbm_capture_vals.argtypes = [vp, i32, i32, i32, vp]
+    L.h2ot_gbm_capture_nids.argtypes = [vp, i32, vp]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != OK:
+        raise H2OTError(rc, load().h2ot_last_error().decode("utf-8", "replace"))
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def device_count():
+    n = C.c_int32(0)
+    _check(load().h2ot_device_count(C.byref(n)))
+    return n.value
+
+
+def comm_unique_id():
+    buf = np.zeros(COMM_ID_BYTES, dtype=np.uint8)
+    _check(load().h2ot_comm_unique_id(_p(buf)))
+    return buf
+
+
+class Engine:
+    """One model build on one GPU: resident frame + per-level / per-tree passes (include/h2ot.h)."""
+
+    def __init__(self, nrows, ncols, family="gaussian", nclass=1, nclass_trees=1, has_weights=False,
+                 has_offset=False, device=0, row_offset=0, nrows_global=0, _handle=None):
+        self.L = load()
+        self.nrows, self.ncols, self.K = int(nrows), int(ncols), int(nclass_trees)
+        self._owned = _handle is None
+        if _handle is not None:
+            self.h = C.c_void_p(_handle)
+            return
+        cfg = Config(device=device, ncols=ncols, nrows=nrows, row_offset=row_offset, nrows_global=nrows_global,
+                     nclass_trees=nclass_trees, nclass=nclass, family=FAMILY[family] if isinstance(family, str) else family,
+                     has_weights=int(has_weights), has_offset=int(has_offset), reserved=0)
+        self.h = C.c_void_p()
+        _check(self.L.h2ot_create(C.byref(cfg), C.byref(self.h)))
+
+    def close(self):
+        if self._owned and self.h:
+            self.L.h2ot_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- frame
+    def load_column(self, col, values, row0=0):
+        v = _f64(values)
+        _check(self.L.h2ot_load_column(self.h, col, row0, v.size, _p(v)))
+
+    def load_response(self, y, row0=0):
+        v = _f64(y)
+        _check(self.L.h2ot_load_response(self.h, row0, v.size, _p(v)))
+
+    def load_weights(self, w, row0=0):
+        v = _f64(w)
+        _check(self.L.h2ot_load_weights(self.h, row0, v.size, _p(v)))
+
+    def load_offset(self, o, row0=0):
+        v = _f64(o)
+        _check(self.L.h2ot_load_offset(self.h, row0, v.size, _p(v)))
+
+    def finalize_frame(self):
+        _check(self.L.h2ot_finalize_frame(self.h))
+
+    def column_info(self, col):
+        ci = ColumnInfo()
+        _check(self.L.h2ot_column_info_get(self.h, col, C.byref(ci)))
+        return ci
+
+    # ---- model state
+    def init_model(self, init_f):
+        f = _f64(np.atleast_1d(init_f))
+        skipped = C.c_int64(0)
+        _check(self.L.h2ot_init_model(self.h, _p(f), C.byref(skipped)))
+        return skipped.value
+
+    def get_predictions(self, k=0):
+        out = np.empty(self.nrows, dtype=np.float64)
+        _check(self.L.h2ot_get_predictions(self.h, k, _p(out)))
+        return out
+
+    def set_predictions(self, f, k=0):
+        v = _f64(f)
+        _check(self.L.h2ot_set_predictions(self.h, k, _p(v)))
+
+    def get_work(self, k=0):
+        out = np.empty(self.nrows, dtype=np.float64)
+        _check(self.L.h2ot_get_work(self.h, k, _p(out)))
+        return out
+
+    def set_work(self, work, abs_bound=None, k=0):
+        v = _f64(work)
+        if abs_bound is None:
+            abs_bound = float(np.nanmax(np.abs(v))) if v.size else 1.0
+        _check(self.L.h2ot_set_work(self.h, k, _p(v), abs_bound))
+
+    def get_nids(self, k=0):
+        out = np.empty(self.nrows, dtype=np.int32)
+        _check(self.L.h2ot_get_nids(self.h, k, _p(out)))
+        return out
+
+    def set_nids(self, nids, k=0):
+        v = np.ascontiguousarray(nids, dtype=np.int32)
+        _check(self.L.h2ot_set_nids(self.h, k, _p(v)))
+
+    # ---- per tree / per level
+    def compute_residuals(self):
+        out = np.zeros(self.K, dtype=np.float64)
+        _check(self.L.h2ot_compute_residuals(self.h, _p(out)))
+        return out
+
+    def begin_tree(self, k=0, tree_seed=0, sample_rate=1.0, work_abs_bound=0.0):
+        _check(self.L.h2ot_begin_tree(self.h, k, tree_seed, sample_rate, work_abs_bound))
+
+    def build_level(self, descs, leaf_offset=0, decided=None, bitset_pool=None, k=0):
+        """descs: ctypes array (HistDesc * (n_leaves*ncols)); decided: ctypes array of DecidedNode or None."""
+        n_leaves = len(descs) // self.ncols
+        nd = len(decided) if decided is not None else 0
+        pool = np.ascontiguousarray(bitset_pool, dtype=np.uint8) if bitset_pool is not None else None
+        _check(self.L.h2ot_build_level(self.h, k, leaf_offset, n_leaves, nd,
+                                       C.cast(decided, C.c_void_p) if nd else None, _p(pool),
+                                       pool.size if pool is not None else 0, C.cast(descs, C.c_void_p)))
+        self._last_descs = descs
+        return n_leaves
+
+    def allreduce_level(self, k=0):
+        _check(self.L.h2ot_allreduce_level(self.h, k))
+
+    def finish_level(self, k=0, want_vals=True):
+        descs = self._last_descs
+        LC = len(descs)
+        nvals = sum((d.nbin + 1) * 3 for d in descs if d.flags & DESC_ACTIVE)
+        vals = np.zeros(max(1, nvals), dtype=np.float64) if want_vals else None
+        offs = np.zeros(LC, dtype=np.int64)
+        min2 = np.zeros(LC, dtype=np.float64)
+        max_in = np.zeros(LC, dtype=np.float64)
+        wna = np.zeros(LC, dtype=np.float64)
+        has = np.zeros(LC, dtype=np.uint8)
+        _check(self.L.h2ot_finish_level(self.h, k, _p(vals), vals.size if want_vals else 0, _p(offs), _p(min2),
+                                        _p(max_in), _p(wna), _p(has)))
+        return dict(vals=vals, offsets=offs, min2=min2, maxIn=max_in, wNA=wna, has_vals=has)
+
+    def find_splits(self, min_rows, min_split_improvement, k=0):
+        n_leaves = len(self._last_descs) // self.ncols
+        out = (Split * n_leaves)()
+        _check(self.L.h2ot_find_splits(self.h, k, min_rows, min_split_improvement, C.cast(out, C.c_void_p)))
+        return out
+
+    def set_tree(self, nodes, bitset_pool=None, k=0):
+        pool = np.ascontiguousarray(bitset_pool, dtype=np.uint8) if bitset_pool is not None else None
+        _check(self.L.h2ot_set_tree(self.h, k, len(nodes), C.cast(nodes, C.c_void_p), _p(pool),
+                                    pool.size if pool is not None else 0))
+
+    def gamma_pass(self, leaf_start, n_leaf_nodes, k=0):
+        num = np.zeros(n_leaf_nodes, dtype=np.float64)
+        den = np.zeros(n_leaf_nodes, dtype=np.float64)
+        _check(self.L.h2ot_gamma_pass(self.h, k, leaf_start, n_leaf_nodes, _p(num), _p(den)))
+        return num, den
+
+    def add_tree(self, node_pred, k=0):
+        v = np.ascontiguousarray(node_pred, dtype=np.float32)
+        _check(self.L.h2ot_add_tree(self.h, k, v.size, _p(v)))
+
+    # ---- multi-GPU
+    def comm_init(self, world_size, rank, uid):
+        u = np.ascontiguousarray(uid, dtype=np.uint8)
+        _check(self.L.h2ot_comm_init(self.h, world_size, rank, _p(u)))
+
+    # ---- diagnostics
+    def bin_codes(self, col, desc):
+        out = np.empty(self.nrows, dtype=np.uint16)
+        _check(self.L.h2ot_debug_bin_codes(self.h, col, C.byref(desc), _p(out)))
+        return out
+
+    def stats(self):
+        s = Stats()
+        _check(self.L.h2ot_stats_get(self.h, C.byref(s)))
+        return s
+
+    def stats_reset(self):
+        _check(self.L.h2ot_stats_reset(self.h))
+
+    def set_hist_mode(self, mode):
+        _check(self.L.h2ot_set_hist_mode(self.h, mode))
+
+
+def make_desc(mn, max_ex, nbin, step=None, is_int=0, int_opt=False, check_float=False, init_na=False, order=0, active=True):
+    """HistDesc for the UniformAdaptive layout. step defaults to nbin/(maxEx-min) (T/DHistogram.java:253)."""
+    if step is None:
+        step = nbin / (max_ex - mn)
+    flags = (DESC_ACTIVE if active else 0) | (DESC_ISINT if is_int > 0 else 0) | (DESC_ISCAT if is_int == 2 else 0) | \
+        (DESC_INTOPT if int_opt else 0) | (DESC_CHECKFLOAT if check_float else 0) | (DESC_INITNA if init_na else 0)
+    return HistDesc(min=mn, maxEx=max_ex, step=step, nbin=nbin, order=order, flags=flags, pad=0)
+
+
+class GBM:
+    """Gradient boosting on the B200 engine. Parameter names follow H2OGradientBoostingEstimator
+    (h2o-py/h2o/estimators/gbm.py) / GBMV3; defaults follow T/SharedTreeModel.java:51-98 and T/gbm/GBMModel.java:24-41."""
+
+    def __init__(self, ntrees=50, max_depth=5, min_rows=10.0, nbins=20, nbins_cats=1024, nbins_top_level=1024,
+                 min_split_improvement=1e-5, sample_rate=1.0, col_sample_rate=1.0, col_sample_rate_per_tree=1.0,
+                 col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
+                 max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
+                 device=0):
+        self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
+                                nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, reserved=0,
+                                min_rows=min_rows, min_split_improvement=min_split_improvement, sample_rate=sample_rate,
+                                col_sample_rate=col_sample_rate, col_sample_rate_per_tree=col_sample_rate_per_tree,
+                                col_sample_rate_change_per_level=col_sample_rate_change_per_level, learn_rate=learn_rate,
+                                learn_rate_annealing=learn_rate_annealing, max_abs_leafnode_pred=max_abs_leafnode_pred,
+                                seed=seed)
+        self.device = device
+        self.L = load()
+        self.g = None
+        self.K = 1 if distribution != "multinomial" else nclass
+
+    def close(self):
+        if self.g:
+            self.L.h2ot_gbm_destroy(self.g)
+        self.g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def load(self, columns, y, weights=None, offset=None, categorical=None, row_offset=0, nrows_global=0, comm=None):
+        """columns: sequence of 1-D arrays (NaN == NA); categorical: {col: cardinality}.
+        comm: (world_size, rank, unique_id) for the row-sharded multi-GPU build."""
+        self.close()
+        nrows, ncols = len(y), len(columns)
+        self.nrows, self.ncols = nrows, ncols
+        self.g = C.c_void_p()
+        _check(self.L.h2ot_gbm_create(C.byref(self.params), self.device, nrows, ncols, row_offset, nrows_global,
+                                      int(weights is not None), int(offset is not None), C.byref(self.g)))
+        if comm is not None:
+            u = np.ascontiguousarray(comm[2], dtype=np.uint8)
+            _check(self.L.h2ot_gbm_comm_init(self.g, comm[0], comm[1], _p(u)))
+        categorical = categorical or {}
+        for c, col in enumerate(columns):
+            v = _f64(col)
+            _check(self.L.h2ot_gbm_set_column(self.g, c, _p(v), int(c in categorical), int(categorical.get(c, 0))))
+        v = _f64(y)
+        _check(self.L.h2ot_gbm_set_response(self.g, _p(v)))
+        if weights is not None:
+            v = _f64(weights)
+            _check(self.L.h2ot_gbm_set_weights(self.g, _p(v)))
+        if offset is not None:
+            v = _f64(offset)
+            _check(self.L.h2ot_gbm_set_offset(self.g, _p(v)))
+        _check(self.L.h2ot_gbm_init(self.g))
+        return self
+
+    def capture_levels(self, on=True):
+        _check(self.L.h2ot_gbm_capture_levels(self.g, int(on)))
+
+    def train(self, n_iterations=None):
+        n = self.params.ntrees if n_iterations is None else n_iterations
+        _check(self.L.h2ot_gbm_train(self.g, n))
+        return self
+
+    def engine(self):
+        return Engine(self.nrows, self.ncols, nclass_trees=self.K, _handle=self.L.h2ot_gbm_engine(self.g))
+
+    @property
+    def init_f(self):
+        return self.L.h2ot_gbm_init_f(self.g)
+
+    @property
+    def ntrees(self):
+        return self.L.h2ot_gbm_ntrees(self.g)
+
+    def tree(self, t, k=0):
+        n = self.L.h2ot_gbm_tree_len(self.g, t, k)
+        out = (TreeNode * n)()
+        _check(self.L.h2ot_gbm_tree_nodes(self.g, t, k, C.cast(out, C.c_void_p)))
+        return out, self.L.h2ot_gbm_tree_leaves_start(self.g, t, k)
+
+    def predictions(self, k=0):
+        out = np.empty(self.nrows, dtype=np.float64)
+        _check(self.L.h2ot_gbm_predictions(self.g, k, _p(out)))
+        return out
+
+    def varimp(self):
+        out = np.zeros(self.ncols, dtype=np.float32)
+        _check(self.L.h2ot_gbm_varimp(self.g, _p(out)))
+        return out
+
+    def timing(self):
+        t = GbmTiming()
+        _check(self.L.h2ot_gbm_timing_get(self.g, C.byref(t)))
+        return t
+
+    # captured levels (histogram monitor analogue)
+    def ncaptures(self):
+        return self.L.h2ot_gbm_ncaptures(self.g)
+
+    def capture_info(self, i):
+        a, b, c, d = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        _check(self.L.h2ot_gbm_capture_info(self.g, i, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return dict(tree=a.value, k=b.value, leaf=c.value, nleaves=d.value)
+
+    def capture_desc(self, i, n, c):
+        d = HistDesc()
+        mn, mx, has, nv = C.c_double(), C.c_double(), C.c_int32(), C.c_int64()
+        _check(self.L.h2ot_gbm_capture_desc(self.g, i, n, c, C.byref(d), C.byref(mn), C.byref(mx), C.byref(has), C.byref(nv)))
+        return d, mn.value, mx.value, has.value, nv.value
+
+    def capture_vals(self, i, n, c, nvals):
+        out = np.empty(nvals, dtype=np.float64)
+        _check(self.L.h2ot_gbm_capture_vals(self.g, i, n, c, _p(out)))
+        return out
+
+    def capture_nids(self, i):
+        out = np.empty(self.nrows, dtype=np.int32)
+        _check(self.L.h2ot_gbm_capture_nids(self.g, i, _p(out)))
+        return out

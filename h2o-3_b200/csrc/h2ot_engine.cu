@@ -82,7 +82,7 @@ struct TreeState {  // per class-tree k
   DBuf<GroupDev> d_groups;
   DBuf<long long> d_sums;  // [3*total_bins | L leaf_rows]
   DBuf<unsigned long long> d_minmax;
-  DBuf<double> d_vals, d_min2, d_maxIn;
+  DBuf<double> d_vals, d_min2, d_maxIn, d_wna;
   DBuf<uint8_t> d_has;
   DBuf<h2ot_split> d_cand, d_best;
   DBuf<long long> d_gamma;
@@ -314,7 +314,7 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.nids) cudaFree(t.nids);
     if (t.code) cudaFree(t.code);
     t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release();
-    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_min2.release(); t.d_maxIn.release();
+    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_min2.release(); t.d_maxIn.release(); t.d_wna.release();
     t.d_has.release(); t.d_cand.release(); t.d_best.release(); t.d_gamma.release(); t.d_pred.release();
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
@@ -789,6 +789,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     if (h->w) hist_smem_kernel<7, true><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
     else hist_smem_kernel<5, false><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
     h->stats.launches++;
+    h->stats.hist_launches++;
   }
   for (size_t g = t.n_smem_groups; g < t.h_groups.size(); g++) {
     const GroupDev& gd = t.h_groups[g];
@@ -796,6 +797,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     if (h->w) hist_global_kernel<true><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
     else hist_global_kernel<false><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
     h->stats.launches++;
+    h->stats.hist_launches++;
   }
   TRY(t_end(h));
   CUDA_TRY(cudaGetLastError());
@@ -846,7 +848,7 @@ int h2ot_allreduce_level(h2ot_engine* h, int32_t k) {
 }
 
 int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_vals_capacity, int64_t* out_val_offsets,
-                      double* out_min2, double* out_maxIn, uint8_t* out_has_vals) {
+                      double* out_min2, double* out_maxIn, double* out_wNA, uint8_t* out_has_vals) {
   CHECK_ENGINE(h);
   CHECK_K(h, k);
   TreeState& t = h->ts[k];
@@ -856,6 +858,7 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   TRY(t.d_min2.ensure(LC));
   TRY(t.d_maxIn.ensure(LC));
   TRY(t.d_has.ensure(LC));
+  TRY(t.d_wna.ensure(LC));
   FinalizeArgs fa{};
   fa.L = t.L;
   fa.C = h->C;
@@ -867,6 +870,7 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   fa.min2 = t.d_min2.p;
   fa.maxIn = t.d_maxIn.p;
   fa.has_vals = t.d_has.p;
+  fa.wna = t.d_wna.p;
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
   fa.inv_sy = std::ldexp(1.0, -t.ey);
@@ -882,6 +886,7 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   }
   if (out_min2) TRY(d2h(h, out_min2, t.d_min2.p, LC * sizeof(double)));
   if (out_maxIn) TRY(d2h(h, out_maxIn, t.d_maxIn.p, LC * sizeof(double)));
+  if (out_wNA) TRY(d2h(h, out_wNA, t.d_wna.p, LC * sizeof(double)));
   if (out_has_vals) TRY(d2h(h, out_has_vals, t.d_has.p, LC));
   if (out_val_offsets)
     for (size_t i = 0; i < LC; i++) out_val_offsets[i] = t.h_descs[i].nbin >= 0 ? t.h_descs[i].voff : -1;
@@ -1059,6 +1064,16 @@ int h2ot_stats_get(h2ot_engine* h, h2ot_stats* out) {
 int h2ot_stats_reset(h2ot_engine* h) {
   if (!h) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
   h->stats = h2ot_stats{};
+  return H2OT_OK;
+}
+int h2ot_get_weight_bound(h2ot_engine* h, double* out) {
+  if (!h || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  *out = h->w_max;
+  return H2OT_OK;
+}
+int h2ot_set_weight_bound(h2ot_engine* h, double bound) {
+  if (!h || !(bound > 0) || std::isinf(bound)) H2OT_FAIL(H2OT_ERR_INVALID, "weight bound must be positive and finite");
+  h->w_max = bound;
   return H2OT_OK;
 }
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode) {

@@ -1,0 +1,879 @@
+// Host-side GBM driver of libh2otree_b200.so (C ABI: include/h2ot_gbm.h).
+//
+// In an H2O-3 deployment this role is played by the unchanged Java classes hex.tree.SharedTree, gbm.GBM,
+// DTree and DHistogram; only the calls below the ScoreBuildHistogram2 seam go to the engine. No JDK exists
+// in this image, so the same sequencing is written here in C++ strictly on top of the engine's public C ABI
+// (include/h2ot.h): it keeps the tree (node table), builds the per-(leaf, column) DHistogram descriptors,
+// draws the per-node column samples, and sequences levels and per-tree row passes. It never touches rows:
+// every O(rows) step is a device kernel behind an h2ot_* call.
+//
+// Reference code mirrored here (paths relative to the reference root; T/ = h2o-algos/src/main/java/hex/tree/):
+//   DHistogram ctor / make / initialHist / useIntOpt / find_maxEx   T/DHistogram.java:190-269, 453-459, 474-554
+//   DTree ctor, UndecidedNode.scoreCols, doNotSplit, DecidedNode ctor   T/DTree.java:56-86, 443-511, 703-726
+//   Split.nextLevelHistos                                            T/DTree.java:312-417
+//   SharedTree.buildLayer / ScoreBuildOneTree.onCompletion          T/SharedTree.java:554-628, 684-710
+//   GBM.initializeModelSpecifics / buildNextKTrees / growTrees / fitBestConstants   T/gbm/GBM.java:254-312, 464-680, 813-847
+//   SharedTree.InitialValue                                         T/SharedTree.java:1138-1185
+//   PCGRNG                                                           h2o-core/src/main/java/water/util/RandomUtils.java:50-119
+#include <algorithm>
+#include <cfloat>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/h2ot_gbm.h"
+
+namespace h2ot {
+void set_error(const std::string& msg);
+}
+
+namespace {
+
+constexpr int kNoParent = -1;
+constexpr int kUndecidedChild = -1;  // T/ScoreBuildHistogram.java:65
+
+#define GFAIL(code, msg)      \
+  do {                        \
+    ::h2ot::set_error(msg);   \
+    return (code);            \
+  } while (0)
+#define GTRY(expr)                \
+  do {                            \
+    int _r = (expr);              \
+    if (_r != H2OT_OK) return _r; \
+  } while (0)
+
+// ---- Java numeric casts (JLS 5.1.3)
+inline int32_t d2i(double d) {
+  if (std::isnan(d)) return 0;
+  if (d >= 2147483647.0) return INT32_MAX;
+  if (d <= -2147483648.0) return INT32_MIN;
+  return (int32_t)d;
+}
+inline int64_t d2l(double d) {
+  if (std::isnan(d)) return 0;
+  if (d >= 9223372036854775807.0) return INT64_MAX;
+  if (d <= -9223372036854775808.0) return INT64_MIN;
+  return (int64_t)d;
+}
+inline double ulp_d(double d) {  // Math.ulp(double)
+  if (std::isnan(d)) return d;
+  d = std::fabs(d);
+  if (std::isinf(d)) return d;
+  if (d == DBL_MAX) return std::ldexp(1.0, 971);
+  return std::nextafter(d, INFINITY) - d;
+}
+inline bool within_one_small_ulp(double a, double b) {  // water/util/MathUtils.java:391-397
+  if (std::isnan(a) && std::isnan(b)) return true;
+  return std::fabs(a - b) <= std::fmin(ulp_d(a), ulp_d(b));
+}
+
+// ---- PCG-XSH-RR 64/32 as java.util.Random subclass (RandomUtils.java:50-119)
+struct Pcg {
+  uint64_t state = 0, inc = 3;
+  explicit Pcg(int64_t seed) { set_seed(seed); }
+  void set_seed(int64_t seed) {
+    state = 0;
+    next_int();
+    state += (uint64_t)seed;
+    next_int();
+  }
+  uint32_t next_int() {
+    const uint64_t old = state;
+    state = old * 6364136223846793005ULL + inc;
+    const uint32_t xs = (uint32_t)(((old >> 18) ^ old) >> 27);
+    const uint32_t rot = (uint32_t)(old >> 59);
+    return (xs >> rot) | (xs << ((-rot) & 31));
+  }
+  int64_t next_long() {
+    const uint64_t hi = next_int();
+    const uint64_t lo = next_int();
+    return (int64_t)((hi << 32) | lo);
+  }
+  int32_t next_bounded(int32_t bound) {  // :88-118
+    const uint64_t threshold = (uint64_t)((-(int64_t)bound) % (int64_t)bound) & 0xFFFFFFFFULL;
+    for (;;) {
+      const uint64_t r = next_int();
+      if (r >= threshold) return (int32_t)(r % (uint64_t)bound);
+    }
+  }
+};
+
+// ---- DHistogram metadata: everything of a DHistogram except the bins (those live on the device)
+struct Hist {
+  bool present = false;  // false == Java null
+  uint8_t is_int = 0;    // 0 real, 1 int, 2 categorical
+  bool int_opt = false, init_na = false, check_float = false;
+  int nbin = 0;
+  double min = 0, max_ex = 0, step = 0;
+  int64_t seed = 0;
+  // filled by the level pass
+  bool has_vals = false;
+  double min2 = DBL_MAX, max_in = -DBL_MAX, w_na = 0;
+
+  bool has_na_bin() const { return has_vals ? w_na > 0 : init_na; }  // T/DHistogram.java:335-340
+  double find_max_ex() const { return find_max_ex_of(max_in, is_int); }
+  static double find_max_ex_of(double max_in, int is_int) {  // :453-459
+    double ulp = ulp_d(max_in);
+    if (is_int > 0 && 1 > ulp) ulp = 1;
+    const double res = max_in + ulp;
+    return std::isinf(res) ? max_in : res;
+  }
+};
+
+// DHistogram ctor (T/DHistogram.java:190-269, UniformAdaptive). Returns false for StepOutOfRangeException.
+bool make_hist(Hist& h, int nbins, int nbins_cats, uint8_t is_int, double min, double max_ex, bool int_opt, bool init_na,
+               int64_t seed, bool check_float) {
+  h = Hist{};
+  h.is_int = is_int;
+  h.min = min;
+  h.max_ex = max_ex;
+  h.init_na = init_na;
+  h.int_opt = int_opt;
+  h.seed = seed;
+  h.check_float = check_float;
+  int xbins = is_int == 2 ? nbins_cats : nbins;
+  if (is_int > 0 && max_ex - min <= xbins) {
+    xbins = (uint16_t)(d2l(max_ex) - d2l(min));  // (char) cast
+    h.step = 1.0;
+  } else {
+    h.step = xbins / (max_ex - min);
+    if (h.step <= 0 || std::isinf(h.step) || std::isnan(h.step)) return false;
+  }
+  h.nbin = (uint16_t)xbins;
+  h.present = true;
+  return true;
+}
+
+struct ColMeta {  // Vec rollups + type (RollupStats.java:31-48)
+  double min = NAN, max = NAN;
+  int64_t nacnt = 0;
+  bool is_int = true, is_cat = false;
+  int cardinality = 0;
+  bool loaded = false;
+};
+
+struct Node {
+  int kind = 0;  // 0 undecided, 1 decided, 2 leaf
+  int pid = kNoParent, nid = 0;
+  std::vector<Hist> hs;  // undecided only ([ncols]); empty == no histograms
+  bool score_cols_null = true;
+  std::vector<int> score_cols;
+  bool has_split = false;
+  h2ot_split split{};
+  float splat = NAN;
+  int nids[2] = {-1, -1};
+  float pred = 0;
+};
+
+struct Tree {
+  int ncols = 0, depth = 0, leaves = 0;
+  int64_t seed = 0;
+  int mtrys = 0, mtrys_per_tree = 0;
+  double change_per_level = 1.0;
+  Pcg rand;
+  std::vector<int> cols;
+  std::vector<Node> ns;
+  std::vector<int> dirty;  // decided nodes whose device copy is stale
+
+  Tree(int ncols_, int mtrys_, int mtrys_per_tree_, int64_t seed_, double change)
+      : ncols(ncols_), seed(seed_), mtrys(mtrys_), mtrys_per_tree(mtrys_per_tree_), change_per_level(change), rand(seed_) {
+    // T/DTree.java:60-86
+    std::vector<int> active(ncols);
+    for (int i = 0; i < ncols; i++) active[i] = i;
+    int len = ncols;
+    if (mtrys_per_tree < ncols) {
+      Pcg col_rng((int64_t)((uint64_t)seed * 0xDA7AULL));
+      for (int i = 0; i < mtrys_per_tree; i++) {
+        if (len == 0) break;
+        const int idx2 = col_rng.next_bounded(len);
+        const int col = active[idx2];
+        active[idx2] = active[--len];
+        active[len] = col;
+      }
+      active.assign(active.begin() + len, active.end());
+    }
+    cols = active;
+  }
+  int len() const { return (int)ns.size(); }
+  int actual_mtries() const {  // :56-58
+    return std::min(std::max(1, d2i((double)mtrys * std::pow(change_per_level, depth))), ncols);
+  }
+  // UndecidedNode ctor + scoreCols (:443-499)
+  int new_undecided(int pid, std::vector<Hist> hs) {
+    Node n;
+    n.kind = 0;
+    n.pid = pid;
+    n.nid = len();
+    n.hs = std::move(hs);
+    const int hslen = (int)n.hs.size();
+    if (actual_mtries() == hslen && mtrys_per_tree == hslen) {
+      n.score_cols_null = true;
+    } else {
+      std::vector<int> c(cols.size());
+      int l = 0;
+      for (size_t i = 0; i < cols.size(); i++) {
+        if (!n.hs[cols[i]].present) continue;
+        c[l++] = cols[i];
+      }
+      const int choices = l;
+      const int mtries = actual_mtries();
+      if (choices > 0)
+        for (int i = 0; i < mtries; i++) {
+          if (l == 0) break;
+          const int idx2 = rand.next_bounded(l);
+          const int col = c[idx2];
+          c[idx2] = c[--l];
+          c[l] = col;
+        }
+      n.score_cols_null = false;
+      n.score_cols.assign(c.begin() + l, c.begin() + choices);
+    }
+    ns.push_back(std::move(n));
+    return ns.back().nid;
+  }
+  void do_not_split(int nid) {  // :504-511
+    const int pid = ns[nid].pid;
+    if (pid == kNoParent) return;
+    for (int i = 0; i < 2; i++)
+      if (ns[pid].nids[i] == nid) {
+        ns[pid].nids[i] = kUndecidedChild;
+        dirty.push_back(pid);
+        return;
+      }
+  }
+  int new_leaf(int pid) {
+    Node n;
+    n.kind = 2;
+    n.pid = pid;
+    n.nid = len();
+    ns.push_back(n);
+    leaves++;
+    return ns.back().nid;
+  }
+};
+
+struct Capture {
+  int tree, k, leaf, nleaves;
+  std::vector<h2ot_hist_desc> descs;
+  std::vector<double> vals, min2, max_in;
+  std::vector<int64_t> offs;
+  std::vector<uint8_t> has;
+  std::vector<int32_t> nids;
+};
+
+struct FinishedTree {
+  std::vector<Node> nodes;
+  int leaves_start = 0;
+};
+
+}  // namespace
+
+struct h2ot_gbm {
+  h2ot_gbm_params p{};
+  h2ot_engine* eng = nullptr;
+  int64_t nrows = 0, nrows_global = 0, row_offset = 0;
+  int ncols = 0, K = 1, nclass = 1;
+  bool has_w = false, has_off = false, inited = false;
+  int world = 1;
+  std::vector<ColMeta> cols;
+  std::vector<double> y, w, off;  // host copies of the O(rows) scalars needed once for init_f
+  double init_f = 0;
+  int mtry = 0, mtry_per_tree = 0;
+  Pcg rand{0};
+  int ntrees_built = 0;
+  std::vector<std::vector<FinishedTree>> trees;  // [tree][k]
+  std::vector<float> varimp;
+  bool capture = false;
+  std::vector<Capture> captures;
+  h2ot_gbm_timing timing{};
+  // scratch
+  std::vector<h2ot_hist_desc> descs;
+  std::vector<double> min2, max_in, w_na;
+  std::vector<uint8_t> has;
+  std::vector<h2ot_split> splits;
+};
+
+namespace {
+
+// T/DHistogram.java:526-554
+bool use_int_opt(const ColMeta& v, const h2ot_gbm_params& p) {
+  if (v.is_cat) return v.cardinality < p.nbins_cats;
+  if (v.is_int) {
+    const double len = v.max - v.min;
+    return len < p.nbins && d2i(v.max) - d2i(v.min) == d2i(len);
+  }
+  return false;
+}
+
+// T/DHistogram.java:474-502
+std::vector<Hist> initial_hist(const h2ot_gbm* g, int nbins, int64_t seed) {
+  std::vector<Hist> hs(g->ncols);
+  for (int c = 0; c < g->ncols; c++) {
+    const ColMeta& v = g->cols[c];
+    const double min_in = v.is_cat ? 0 : std::fmax(v.min, -DBL_MAX);
+    const double max_in = v.is_cat ? v.cardinality - 1 : std::fmin(v.max, DBL_MAX);
+    const double max_ex = v.is_cat ? v.cardinality : Hist::find_max_ex_of(max_in, v.is_int ? 1 : 0);
+    const bool all_na = v.nacnt == g->nrows_global;
+    const bool is_const = v.min == v.max && v.nacnt == 0;
+    if (all_na || is_const) continue;
+    const uint8_t type = (uint8_t)(v.is_cat ? 2 : (v.is_int ? 1 : 0));
+    Hist h;
+    if (make_hist(h, nbins, g->p.nbins_cats, type, min_in, max_ex, use_int_opt(v, g->p), v.nacnt > 0, seed, false)) hs[c] = h;
+  }
+  return hs;
+}
+
+// Split.nextLevelHistos (T/DTree.java:312-417; no constraints). Empty result == Java null.
+std::vector<Hist> next_level_histos(const h2ot_gbm* g, const h2ot_split& s, const std::vector<Hist>& cur, int way, double splat) {
+  const double n = way == 0 ? s.n0 : s.n1;
+  if (n < g->p.min_rows) return {};
+  const double se = way == 0 ? s.se0 : s.se1;
+  if (se <= 1e-30) return {};
+  int cnt = 0;
+  std::vector<Hist> nh(cur.size());
+  for (size_t j = 0; j < cur.size(); j++) {
+    const Hist& h = cur[j];
+    if (!h.present) continue;
+    const int adj_nbins = std::max(h.nbin >> 1, g->p.nbins);
+    double min, max_ex;
+    if (!h.has_vals || s.equal > 1) {
+      min = h.min;
+      max_ex = h.max_ex;
+    } else {
+      min = h.min2;
+      if (h.max_in == min) continue;
+      max_ex = h.find_max_ex();
+    }
+    if (s.nasplit == H2OT_NA_VS_REST && way == 1) continue;
+    if (s.col == (int)j) {
+      if (s.equal == 0) {
+        double split = splat;
+        if (h.is_int > 0) split = (float)std::ceil(split);
+        if (s.nasplit != H2OT_NA_VS_REST) {
+          if (way == 0) max_ex = split;
+          else min = split;
+        }
+      } else if (s.equal == 1) {
+        if (way == 1) continue;
+      }
+    }
+    if (min > max_ex) continue;
+    if (within_one_small_ulp(min, max_ex)) continue;
+    if (std::isinf(adj_nbins / (max_ex - min))) continue;
+    if (h.is_int > 0 && !(min + 1 < max_ex)) continue;
+    const bool has_nas = ((s.nasplit == H2OT_NA_LEFT && way == 0) || (s.nasplit == H2OT_NA_RIGHT && way == 1)) && h.has_na_bin();
+    Hist c;
+    // DHistogram.make (:504-512): seed = h._seed*0xDECAF+(way+1)
+    if (!make_hist(c, adj_nbins, g->p.nbins_cats, h.is_int, min, max_ex, h.int_opt, has_nas,
+                   (int64_t)((uint64_t)h.seed * 0xDECAFULL + (uint64_t)(way + 1)), h.check_float))
+      continue;
+    nh[j] = c;
+    cnt++;
+  }
+  if (cnt == 0) return {};
+  return nh;
+}
+
+void to_device_node(const Node& n, h2ot_decided_node& d, std::vector<uint8_t>& pool) {
+  memset(&d, 0, sizeof(d));
+  d.nid = n.nid;
+  d.pid = n.pid;
+  d.col = n.has_split ? n.split.col : -1;
+  d.equal = n.has_split ? n.split.equal : 0;
+  d.nasplit = n.has_split ? n.split.nasplit : H2OT_NA_NONE;
+  d.splat = n.splat;
+  d.child[0] = n.nids[0];
+  d.child[1] = n.nids[1];
+  if (n.has_split && n.split.equal >= 2) {
+    d.bs_off = (int32_t)pool.size();
+    d.bs_nbits = n.split.bs_nbits;
+    d.bs_bitoff = n.split.bs_bitoff;
+    pool.insert(pool.end(), n.split.bs, n.split.bs + n.split.bs_nbytes);
+  }
+}
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+// One ScoreBuildHistogram2 pass + ScoreBuildOneTree.onCompletion for class-tree k (T/SharedTree.java:661-710).
+int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_split) {
+  did_split = false;
+  const int C = g->ncols;
+  const int tmax = tree.len();
+  const int L = tmax - leaf_offset;
+  if (L <= 0) return H2OT_OK;
+  const double t0 = now_s();
+  // descriptors of the undecided leaves
+  g->descs.assign((size_t)L * C, h2ot_hist_desc{});
+  int64_t active_pairs = 0;
+  std::vector<char> col_active(C, 0);
+  for (int l = 0; l < L; l++) {
+    const Node& u = tree.ns[leaf_offset + l];
+    std::vector<int16_t> order(C, -1);
+    if (u.score_cols_null)
+      for (int c = 0; c < C; c++) order[c] = (int16_t)c;
+    else
+      for (size_t i = 0; i < u.score_cols.size(); i++) order[u.score_cols[i]] = (int16_t)i;
+    for (int c = 0; c < C; c++) {
+      h2ot_hist_desc& d = g->descs[(size_t)l * C + c];
+      if (u.hs.empty() || !u.hs[c].present || order[c] < 0) continue;
+      const Hist& h = u.hs[c];
+      d.min = h.min;
+      d.maxEx = h.max_ex;
+      d.step = h.step;
+      d.nbin = h.nbin;
+      d.order = order[c];
+      d.flags = H2OT_DESC_ACTIVE | (h.is_int > 0 ? H2OT_DESC_ISINT : 0) | (h.is_int == 2 ? H2OT_DESC_ISCAT : 0) |
+                (h.int_opt ? H2OT_DESC_INTOPT : 0) | (h.check_float ? H2OT_DESC_CHECKFLOAT : 0) | (h.init_na ? H2OT_DESC_INITNA : 0);
+      active_pairs++;
+      col_active[c] = 1;
+    }
+  }
+  // decided nodes the device does not have yet
+  std::vector<h2ot_decided_node> dn;
+  std::vector<uint8_t> pool;
+  std::sort(tree.dirty.begin(), tree.dirty.end());
+  tree.dirty.erase(std::unique(tree.dirty.begin(), tree.dirty.end()), tree.dirty.end());
+  for (int nid : tree.dirty) {
+    dn.emplace_back();
+    to_device_node(tree.ns[nid], dn.back(), pool);
+  }
+  tree.dirty.clear();
+  GTRY(h2ot_build_level(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data()));
+  if (g->world > 1) GTRY(h2ot_allreduce_level(g->eng, k));
+  const size_t LC = (size_t)L * C;
+  g->min2.resize(LC);
+  g->max_in.resize(LC);
+  g->w_na.resize(LC);
+  g->has.resize(LC);
+  g->splits.resize(L);
+  if (g->capture) {
+    Capture cap;
+    cap.tree = g->ntrees_built;
+    cap.k = k;
+    cap.leaf = leaf_offset;
+    cap.nleaves = L;
+    cap.descs = g->descs;
+    int64_t nvals = 0;
+    for (const h2ot_hist_desc& d : g->descs)
+      if (d.flags & H2OT_DESC_ACTIVE) nvals += (int64_t)(d.nbin + 1) * 3;
+    cap.vals.resize((size_t)std::max<int64_t>(1, nvals));
+    cap.offs.resize(LC);
+    GTRY(h2ot_finish_level(g->eng, k, cap.vals.data(), (int64_t)cap.vals.size(), cap.offs.data(), g->min2.data(), g->max_in.data(),
+                           g->w_na.data(), g->has.data()));
+    cap.min2 = g->min2;
+    cap.max_in = g->max_in;
+    cap.has = g->has;
+    cap.nids.resize((size_t)g->nrows);
+    GTRY(h2ot_get_nids(g->eng, k, cap.nids.data()));
+    g->captures.push_back(std::move(cap));
+  } else {
+    GTRY(h2ot_finish_level(g->eng, k, nullptr, 0, nullptr, g->min2.data(), g->max_in.data(), g->w_na.data(), g->has.data()));
+  }
+  GTRY(h2ot_find_splits(g->eng, k, g->p.min_rows, g->p.min_split_improvement, g->splits.data()));
+  g->timing.level_s += now_s() - t0;
+  g->timing.levels++;
+  int64_t ncol_active = 0;
+  for (int c = 0; c < C; c++) ncol_active += col_active[c];
+  g->timing.hist_rows_cols += (double)g->nrows_global * (double)ncol_active;
+
+  // onCompletion: DecidedNode ctor per leaf (T/DTree.java:703-726)
+  for (int l = 0; l < L; l++) {
+    const int nid = leaf_offset + l;
+    std::vector<Hist> hs = std::move(tree.ns[nid].hs);
+    for (int c = 0; c < C && !hs.empty(); c++) {
+      Hist& h = hs[c];
+      const size_t i = (size_t)l * C + c;
+      if (!h.present || !(g->descs[i].flags & H2OT_DESC_ACTIVE)) continue;
+      h.has_vals = g->has[i] != 0;
+      h.min2 = g->min2[i];
+      h.max_in = g->max_in[i];
+      h.w_na = g->w_na[i];
+    }
+    Node& dnode = tree.ns[nid];
+    dnode.kind = 1;
+    dnode.hs.clear();
+    dnode.score_cols.clear();
+    const h2ot_split& s = g->splits[l];
+    tree.dirty.push_back(nid);
+    if (s.col < 0 || hs.empty()) {
+      dnode.has_split = false;
+      dnode.splat = NAN;
+      dnode.nids[0] = dnode.nids[1] = kUndecidedChild;
+      tree.do_not_split(nid);
+      continue;
+    }
+    dnode.has_split = true;
+    dnode.split = s;
+    dnode.splat = s.splat;
+    did_split = true;
+    g->varimp[s.col] += (float)(s.se - (s.se0 + s.se1));  // T/SharedTree.java:697-700
+    for (int way = 0; way < 2; way++) {
+      std::vector<Hist> nh = next_level_histos(g, s, hs, way, (double)s.splat);
+      const int child = nh.empty() ? kUndecidedChild : tree.new_undecided(nid, std::move(nh));
+      tree.ns[nid].nids[way] = child;
+    }
+  }
+  leaf_offset = tmax;
+  if (did_split) tree.depth++;
+  return H2OT_OK;
+}
+
+int allreduce(h2ot_gbm* g, double* v, int64_t n, int op) {
+  if (g->world <= 1) return H2OT_OK;
+  return h2ot_allreduce_host_f64(g->eng, v, n, op);
+}
+
+// GBM.buildNextKTrees (T/gbm/GBM.java:464-591)
+int build_next_k_trees(h2ot_gbm* g) {
+  const int K = g->K;
+  std::vector<double> absmax(K, 0.0);
+  GTRY(h2ot_compute_residuals(g->eng, absmax.data()));
+  GTRY(allreduce(g, absmax.data(), K, 1));
+  std::vector<std::unique_ptr<Tree>> kt(K);
+  std::vector<int> leaves(K, 0);
+  const int adj_nbins = std::max(g->p.nbins_top_level, g->p.nbins);
+  const int64_t rseed = g->rand.next_long();
+  for (int k = 0; k < K; k++) {
+    kt[k] = std::make_unique<Tree>(g->ncols, g->mtry, g->mtry_per_tree, rseed, g->p.col_sample_rate_change_per_level);
+    kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed));
+    GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, absmax[k]));
+  }
+  for (int depth = 0; depth < g->p.max_depth; depth++) {
+    bool any = false;
+    for (int k = 0; k < K; k++) {
+      bool did = false;
+      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did));
+      any = any || did;
+    }
+    if (!any) break;
+  }
+  // leaf insertion (:655-679)
+  for (int k = 0; k < K; k++) {
+    Tree& t = *kt[k];
+    const int leaf = t.len();
+    leaves[k] = leaf;
+    for (int nid = 0; nid < leaf; nid++) {
+      if (t.ns[nid].kind != 1) continue;
+      if (!t.ns[nid].has_split) {
+        if (nid == 0) {  // the root never split: it becomes a LeafNode in place
+          Node n;
+          n.kind = 2;
+          n.pid = kNoParent;
+          n.nid = 0;
+          t.ns[0] = n;
+          t.leaves++;
+        }
+        continue;
+      }
+      for (int i = 0; i < 2; i++) {
+        const int cn = t.ns[nid].nids[i];
+        if (cn == kUndecidedChild || t.ns[cn].kind == 0 || (t.ns[cn].kind == 1 && !t.ns[cn].has_split))
+          t.ns[nid].nids[i] = t.new_leaf(nid);
+      }
+    }
+  }
+  // GammaPass + fitBestConstants (:1286-1407, 813-847)
+  const double m1class = (g->nclass > 1 && g->p.family == H2OT_FAMILY_MULTINOMIAL) ? (double)(g->nclass - 1) / g->nclass : 1.0;
+  const double eff_lr = g->p.learn_rate * std::pow(g->p.learn_rate_annealing, (double)(g->ntrees_built - 1));
+  for (int k = 0; k < K; k++) {
+    Tree& t = *kt[k];
+    const int nleaf = t.len() - leaves[k];
+    if (t.ns[0].kind == 2 || nleaf <= 0) continue;
+    std::vector<h2ot_decided_node> dn;
+    std::vector<uint8_t> pool;
+    for (int nid = 0; nid < leaves[k]; nid++)
+      if (t.ns[nid].kind == 1) {
+        dn.emplace_back();
+        to_device_node(t.ns[nid], dn.back(), pool);
+      }
+    GTRY(h2ot_set_tree(g->eng, k, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size()));
+    std::vector<double> num(nleaf), den(nleaf);
+    GTRY(h2ot_gamma_pass(g->eng, k, leaves[k], nleaf, num.data(), den.data()));
+    for (int i = 0; i < nleaf; i++) {
+      const double gamma = den[i] == 0 ? 0 : num[i] / den[i];
+      double gf = eff_lr * m1class * gamma;
+      if (g->p.family == H2OT_FAMILY_MULTINOMIAL) {
+        if (gf > 1e4) gf = 1e4f;
+        else if (gf < -1e4) gf = -1e4f;
+      }
+      if (std::isnan(gf)) gf = 0;
+      else if (std::isinf(gf)) gf = (gf > 0 ? 1.0 : -1.0) * 1e4f;
+      if (gf > g->p.max_abs_leafnode_pred) gf = g->p.max_abs_leafnode_pred;
+      if (gf < -g->p.max_abs_leafnode_pred) gf = -g->p.max_abs_leafnode_pred;
+      t.ns[leaves[k] + i].pred = (float)gf;
+    }
+  }
+  // AddTreeContributions (:1410-1470)
+  std::vector<FinishedTree> outs(K);
+  for (int k = 0; k < K; k++) {
+    Tree& t = *kt[k];
+    std::vector<float> pred(t.len());
+    for (int i = 0; i < t.len(); i++) pred[i] = t.ns[i].pred;
+    GTRY(h2ot_add_tree(g->eng, k, t.len(), pred.data()));
+    outs[k].nodes = std::move(t.ns);
+    for (Node& n : outs[k].nodes) n.hs.clear();
+    outs[k].leaves_start = leaves[k];
+  }
+  g->trees.push_back(std::move(outs));
+  g->ntrees_built++;
+  return H2OT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int32_t ncols, int64_t row_offset, int64_t nrows_global,
+                    int32_t has_weights, int32_t has_offset, h2ot_gbm** out) {
+  if (!p || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_MULTINOMIAL) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
+  if (p->max_depth < 1 || p->nbins < 2 || p->nbins_cats < 2 || p->ntrees < 0) GFAIL(H2OT_ERR_INVALID, "bad tree parameters");
+  if (p->nbins_cats > H2OT_MAX_BITSET_BYTES * 8) GFAIL(H2OT_ERR_UNSUPPORTED, "nbins_cats above 4096");
+  h2ot_gbm* g = new h2ot_gbm();
+  g->p = *p;
+  g->nrows = nrows;
+  g->nrows_global = nrows_global > 0 ? nrows_global : nrows;
+  g->row_offset = row_offset;
+  g->ncols = ncols;
+  g->nclass = p->family == H2OT_FAMILY_MULTINOMIAL ? p->nclass : (p->family == H2OT_FAMILY_BERNOULLI ? 2 : 1);
+  g->K = g->nclass == 2 ? 1 : g->nclass;
+  if (g->K < 1) {
+    delete g;
+    GFAIL(H2OT_ERR_INVALID, "multinomial needs nclass >= 2");
+  }
+  g->has_w = has_weights != 0;
+  g->has_off = has_offset != 0;
+  g->cols.resize(ncols);
+  g->varimp.assign(ncols, 0.f);
+  g->rand = Pcg(p->seed);
+  h2ot_config cfg{};
+  cfg.device = device;
+  cfg.ncols = ncols;
+  cfg.nrows = nrows;
+  cfg.row_offset = row_offset;
+  cfg.nrows_global = g->nrows_global;
+  cfg.nclass_trees = g->K;
+  cfg.nclass = g->nclass;
+  cfg.family = p->family;
+  cfg.has_weights = has_weights;
+  cfg.has_offset = has_offset;
+  const int rc = h2ot_create(&cfg, &g->eng);
+  if (rc != H2OT_OK) {
+    delete g;
+    return rc;
+  }
+  *out = g;
+  return H2OT_OK;
+}
+
+int h2ot_gbm_destroy(h2ot_gbm* g) {
+  if (!g) return H2OT_OK;
+  h2ot_destroy(g->eng);
+  delete g;
+  return H2OT_OK;
+}
+
+int h2ot_gbm_set_column(h2ot_gbm* g, int32_t col, const double* values, int32_t is_categorical, int32_t cardinality) {
+  if (!g || !values) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (col < 0 || col >= g->ncols) GFAIL(H2OT_ERR_INVALID, "column index out of range");
+  GTRY(h2ot_load_column(g->eng, col, 0, g->nrows, values));
+  g->cols[col].is_cat = is_categorical != 0;
+  g->cols[col].cardinality = cardinality;
+  g->cols[col].loaded = true;
+  return H2OT_OK;
+}
+int h2ot_gbm_set_response(h2ot_gbm* g, const double* y) {
+  if (!g || !y) GFAIL(H2OT_ERR_INVALID, "null argument");
+  g->y.assign(y, y + g->nrows);
+  return h2ot_load_response(g->eng, 0, g->nrows, y);
+}
+int h2ot_gbm_set_weights(h2ot_gbm* g, const double* w) {
+  if (!g || !w) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (!g->has_w) GFAIL(H2OT_ERR_INVALID, "created without weights");
+  g->w.assign(w, w + g->nrows);
+  return h2ot_load_weights(g->eng, 0, g->nrows, w);
+}
+int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o) {
+  if (!g || !o) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (!g->has_off) GFAIL(H2OT_ERR_INVALID, "created without offset");
+  g->off.assign(o, o + g->nrows);
+  return h2ot_load_offset(g->eng, 0, g->nrows, o);
+}
+
+int h2ot_gbm_comm_init(h2ot_gbm* g, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  g->world = world_size;
+  return h2ot_comm_init(g->eng, world_size, rank, id);
+}
+
+int h2ot_gbm_init(h2ot_gbm* g) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (g->inited) return H2OT_OK;
+  if ((int64_t)g->y.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "response not set");
+  if (g->has_w && (int64_t)g->w.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "weights not set");
+  if (g->has_off && (int64_t)g->off.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "offset not set");
+  GTRY(h2ot_finalize_frame(g->eng));
+  const int C = g->ncols;
+  // rollups, merged over ranks: [min as -min | max | nacnt | not_int]
+  std::vector<double> mx(2 * (size_t)C), sm(2 * (size_t)C);
+  for (int c = 0; c < C; c++) {
+    h2ot_column_info ci;
+    GTRY(h2ot_column_info_get(g->eng, c, &ci));
+    mx[c] = std::isnan(ci.min) ? -INFINITY : -ci.min;
+    mx[C + c] = std::isnan(ci.max) ? -INFINITY : ci.max;
+    sm[c] = (double)ci.nacnt;
+    sm[C + c] = ci.is_int ? 0.0 : 1.0;
+  }
+  GTRY(allreduce(g, mx.data(), 2 * (int64_t)C, 1));
+  GTRY(allreduce(g, sm.data(), 2 * (int64_t)C, 0));
+  for (int c = 0; c < C; c++) {
+    ColMeta& m = g->cols[c];
+    m.min = std::isinf(mx[c]) && mx[c] < 0 ? NAN : -mx[c];
+    m.max = std::isinf(mx[C + c]) && mx[C + c] < 0 ? NAN : mx[C + c];
+    m.nacnt = (int64_t)sm[c];
+    m.is_int = sm[C + c] == 0.0;
+  }
+  // weights bound (fixes the fixed-point scale of the w accumulator; must agree on every rank)
+  if (g->has_w) {
+    double wb = 0;
+    GTRY(h2ot_get_weight_bound(g->eng, &wb));
+    GTRY(allreduce(g, &wb, 1, 1));
+    GTRY(h2ot_set_weight_bound(g->eng, wb));
+  }
+  // GBM.init / initializeModelSpecifics (T/gbm/GBM.java:254-312)
+  g->mtry_per_tree = std::max(1, d2i(g->p.col_sample_rate_per_tree * C));
+  g->mtry = std::max(1, d2i(g->p.col_sample_rate * g->p.col_sample_rate_per_tree * C));
+  double nd[2] = {0, 0};  // InitialValue (T/SharedTree.java:1138-1185)
+  for (int64_t i = 0; i < g->nrows; i++) {
+    if (std::isnan(g->y[i])) continue;
+    const double w = g->has_w ? g->w[i] : 1.0;
+    if (w == 0) continue;
+    nd[0] += w * (g->y[i] - (g->has_off ? g->off[i] : 0.0));
+    nd[1] += w;
+  }
+  GTRY(allreduce(g, nd, 2, 0));
+  const double mean = nd[0] / nd[1];
+  if (g->nclass > 2) g->init_f = 0;
+  else if (g->p.family == H2OT_FAMILY_BERNOULLI) g->init_f = std::log(mean / (1 - mean));  // LogitFunction.link
+  else g->init_f = mean;
+  std::vector<double> f0(g->K, 0.0);
+  f0[0] = g->init_f;
+  int64_t skipped = 0;
+  GTRY(h2ot_init_model(g->eng, f0.data(), &skipped));
+  // the O(rows) host copies are not needed any more
+  std::vector<double>().swap(g->y);
+  std::vector<double>().swap(g->w);
+  std::vector<double>().swap(g->off);
+  g->inited = true;
+  return H2OT_OK;
+}
+
+int h2ot_gbm_train(h2ot_gbm* g, int32_t n_iterations) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (!g->inited) GTRY(h2ot_gbm_init(g));
+  const double t0 = now_s();
+  for (int i = 0; i < n_iterations; i++) GTRY(build_next_k_trees(g));
+  g->timing.total_s += now_s() - t0;
+  return H2OT_OK;
+}
+
+int h2ot_gbm_capture_levels(h2ot_gbm* g, int32_t on) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  g->capture = on != 0;
+  return H2OT_OK;
+}
+
+double h2ot_gbm_init_f(h2ot_gbm* g) { return g ? g->init_f : NAN; }
+int32_t h2ot_gbm_ntrees(h2ot_gbm* g) { return g ? (int32_t)g->trees.size() : 0; }
+int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k) { return (int32_t)g->trees[tree][k].nodes.size(); }
+int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k) { return g->trees[tree][k].leaves_start; }
+
+int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out) {
+  if (!g || !out || tree < 0 || tree >= (int)g->trees.size() || k < 0 || k >= g->K) GFAIL(H2OT_ERR_INVALID, "bad tree index");
+  const std::vector<Node>& ns = g->trees[tree][k].nodes;
+  for (size_t i = 0; i < ns.size(); i++) {
+    const Node& n = ns[i];
+    h2ot_tree_node& o = out[i];
+    memset(&o, 0, sizeof(o));
+    o.kind = n.kind;
+    o.pid = n.pid;
+    o.nid = n.nid;
+    o.nid0 = n.nids[0];
+    o.nid1 = n.nids[1];
+    o.splat = n.splat;
+    o.pred = n.pred;
+    o.has_split = n.has_split ? 1 : 0;
+    if (n.has_split) {
+      const h2ot_split& s = n.split;
+      o.col = s.col; o.bin = s.bin; o.nasplit = s.nasplit; o.equal = s.equal;
+      o.se = s.se; o.se0 = s.se0; o.se1 = s.se1; o.n0 = s.n0; o.n1 = s.n1; o.p0 = s.p0; o.p1 = s.p1;
+      o.tree_p0 = s.tree_p0; o.tree_p1 = s.tree_p1;
+      o.bs_nbits = s.bs_nbits; o.bs_bitoff = s.bs_bitoff; o.bs_nbytes = s.bs_nbytes;
+      memcpy(o.bs, s.bs, sizeof(o.bs));
+    } else {
+      o.col = -1;
+    }
+  }
+  return H2OT_OK;
+}
+
+int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out) {
+  if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
+  return h2ot_get_predictions(g->eng, k, out);
+}
+int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {
+  if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
+  std::copy(g->varimp.begin(), g->varimp.end(), out);
+  return H2OT_OK;
+}
+int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out) {
+  if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
+  *out = g->timing;
+  return H2OT_OK;
+}
+h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g) { return g ? g->eng : nullptr; }
+
+int32_t h2ot_gbm_ncaptures(h2ot_gbm* g) { return g ? (int32_t)g->captures.size() : 0; }
+int h2ot_gbm_capture_info(h2ot_gbm* g, int32_t i, int32_t* tree, int32_t* k, int32_t* leaf, int32_t* nleaves) {
+  if (!g || i < 0 || i >= (int)g->captures.size()) GFAIL(H2OT_ERR_INVALID, "bad capture index");
+  const Capture& c = g->captures[i];
+  if (tree) *tree = c.tree;
+  if (k) *k = c.k;
+  if (leaf) *leaf = c.leaf;
+  if (nleaves) *nleaves = c.nleaves;
+  return H2OT_OK;
+}
+int h2ot_gbm_capture_desc(h2ot_gbm* g, int32_t i, int32_t n, int32_t c, h2ot_hist_desc* desc, double* min2, double* maxIn,
+                          int32_t* has_vals, int64_t* nvals) {
+  if (!g || i < 0 || i >= (int)g->captures.size()) GFAIL(H2OT_ERR_INVALID, "bad capture index");
+  const Capture& cap = g->captures[i];
+  if (n < 0 || n >= cap.nleaves || c < 0 || c >= g->ncols) GFAIL(H2OT_ERR_INVALID, "bad (leaf, col)");
+  const size_t p = (size_t)n * g->ncols + c;
+  if (desc) *desc = cap.descs[p];
+  if (min2) *min2 = cap.min2[p];
+  if (maxIn) *maxIn = cap.max_in[p];
+  if (has_vals) *has_vals = cap.has[p];
+  if (nvals) *nvals = (cap.descs[p].flags & H2OT_DESC_ACTIVE) ? (int64_t)(cap.descs[p].nbin + 1) * 3 : 0;
+  return H2OT_OK;
+}
+int h2ot_gbm_capture_vals(h2ot_gbm* g, int32_t i, int32_t n, int32_t c, double* out) {
+  if (!g || i < 0 || i >= (int)g->captures.size() || !out) GFAIL(H2OT_ERR_INVALID, "bad capture index");
+  const Capture& cap = g->captures[i];
+  if (n < 0 || n >= cap.nleaves || c < 0 || c >= g->ncols) GFAIL(H2OT_ERR_INVALID, "bad (leaf, col)");
+  const size_t p = (size_t)n * g->ncols + c;
+  if (!(cap.descs[p].flags & H2OT_DESC_ACTIVE) || cap.offs[p] < 0) GFAIL(H2OT_ERR_INVALID, "histogram not present");
+  const int64_t nv = (int64_t)(cap.descs[p].nbin + 1) * 3;
+  std::copy(cap.vals.begin() + cap.offs[p], cap.vals.begin() + cap.offs[p] + nv, out);
+  return H2OT_OK;
+}
+int h2ot_gbm_capture_nids(h2ot_gbm* g, int32_t i, int32_t* out) {
+  if (!g || i < 0 || i >= (int)g->captures.size() || !out) GFAIL(H2OT_ERR_INVALID, "bad capture index");
+  std::copy(g->captures[i].nids.begin(), g->captures[i].nids.end(), out);
+  return H2OT_OK;
+}
+
+}  // extern "C"

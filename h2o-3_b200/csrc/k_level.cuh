@@ -364,6 +364,7 @@ struct FinalizeArgs {
   double* min2;        // [L*C]
   double* maxIn;       // [L*C]
   uint8_t* has_vals;   // [L*C]
+  double* wna;         // [L*C] weight of the NA bucket (DHistogram.wNA, T/DHistogram.java:84)
   double inv_sy, inv_syy, inv_sw;
 };
 
@@ -380,6 +381,7 @@ __global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
     const bool intopt = has && (d.flags & H2OT_DESC_INTOPT);
     a.min2[p] = mn ? dkey_inv(~mn) : (intopt ? 2147483647.0 : DBL_MAX);
     a.maxIn[p] = mx ? dkey_inv(mx) : (intopt ? -2147483648.0 : -DBL_MAX);
+    a.wna[p] = has ? __dmul_rn((double)a.acc[(d.gbin + d.nbin) * 3], a.inv_sw) : 0.0;
   }
   if (!has) return;
   for (int b = threadIdx.x; b <= d.nbin; b += blockDim.x) {

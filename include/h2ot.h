@@ -132,6 +132,7 @@ typedef struct h2ot_stats { /* diagnostics: device time per kernel family (ms) a
   int64_t h2d_bytes, d2h_bytes;
   int64_t hist_rows_cols;    /* sum over level passes of local rows x active columns */
   int64_t hist_algo_bytes;   /* algorithmic bytes of those passes (SURVEY.md section 8d formula) */
+  int64_t hist_launches;     /* histogram-accumulation kernel launches (ms_hist / hist_launches = mean launch time) */
 } h2ot_stats;
 
 /* ---- lifetime: one engine per model build per GPU (created after T/SharedTree.java:385, destroyed in the finally at :407-425) */
@@ -187,9 +188,10 @@ int h2ot_level_buffers(h2ot_engine* h, int32_t k, void** d_sums, int64_t* n_sums
 int h2ot_allreduce_level(h2ot_engine* h, int32_t k);
 /* postGlobal (T/ScoreBuildHistogram2.java:455-466): fixed-point -> fp64, reducePrecision (T/DHistogram.java:734-740).
  * Optional host copies (all nullable): vals packed per active (leaf,col) in [leaf][col] order, (nbin+1)*3 doubles each;
- * val_offsets[n_leaves*ncols] = start (in doubles) of each block or -1; min2/maxIn[n_leaves*ncols]; has_vals = _vals != null. */
+ * val_offsets[n_leaves*ncols] = start (in doubles) of each block or -1; min2/maxIn/wNA[n_leaves*ncols] (wNA = weight of the
+ * NA bucket, all the host needs for DHistogram.hasNABin in Split.nextLevelHistos, T/DTree.java:401); has_vals = _vals != null. */
 int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_vals_capacity, int64_t* out_val_offsets,
-                      double* out_min2, double* out_maxIn, uint8_t* out_has_vals);
+                      double* out_min2, double* out_maxIn, double* out_wNA, uint8_t* out_has_vals);
 /* DecidedNode ctor's bestCol / FindSplits / findBestSplitPoint / splat (T/DTree.java:616-726, 984-1487, 240-291)
  * on the histograms of the level just finished. out_splits[n_leaves]. */
 int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_split_improvement, h2ot_split* out_splits);
@@ -210,6 +212,10 @@ int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_
 int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]);
 int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
 int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op /*0 sum, 1 max*/);
+/* max |weight| over the local rows (known after h2ot_finalize_frame). With several ranks the host takes the max over
+ * ranks and sets it back, so that every rank uses the same fixed-point scale for the w accumulator. */
+int h2ot_get_weight_bound(h2ot_engine* h, double* out);
+int h2ot_set_weight_bound(h2ot_engine* h, double bound);
 
 /* ---- diagnostics / parity hooks */
 /* Per-row bin index of column col under desc (DHistogram.bin, T/DHistogram.java:272-306), uint16 codes to the host. */

@@ -1,0 +1,153 @@
+"""GPU parity tests of whole GBM builds (host driver over the C ABI) against the CPU oracle, level by level:
+the analogue of the reference's histogram-monitor test (TT/gbm/GBMTest.java:4722-4765)."""
+import numpy as np
+import pytest
+
+import h2ot_lib
+import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+NaN = float("nan")
+
+
+def _run_both(X, y, cats=None, w=None, off=None, capture=True, **kw):
+    P = h2ot_lib.pkg()
+    dist = kw.pop("distribution", "bernoulli")
+    nclass = kw.pop("nclass", 2 if dist == "bernoulli" else 1)
+    fam = {"gaussian": O.GAUSSIAN, "bernoulli": O.BERNOULLI, "multinomial": O.MULTINOMIAL}[dist]
+    op = O.default_params(family=fam, nclass=nclass, **kw)
+    om = O.Model(O.Frame(X, y, w=w, off=off, cat_cards=cats), op, capture=capture)
+    gm = P.GBM(distribution=dist, nclass=nclass, **kw)
+    gm.load([X[:, c] for c in range(X.shape[1])], y, weights=w, offset=off, categorical=cats)
+    gm.capture_levels(capture)
+    gm.train()
+    return gm, om
+
+
+def test_bernoulli_levels_trees_and_metrics_match_oracle():
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=11)
+    gm, om = _run_both(X, y, cats, ntrees=6, max_depth=5, nbins=20, seed=1234)
+    st = h2ot_lib.compare_models(gm, om)
+    assert st["levels"] >= 6 * 4 and st["hists"] > 100
+    # float-cast sums: the integer accumulation is exact, the oracle's sequential fp64 sum is not -> a handful of
+    # 1-ulp(float) differences at most
+    assert st["n_vals_diff"] <= 1e-3 * st["n_vals"], st
+    F_g, F_o = gm.predictions(), om.F()
+    assert abs(h2ot_lib.logloss(y, F_g) - h2ot_lib.logloss(y, F_o)) <= 1e-5
+    assert abs(h2ot_lib.auc(y, F_g) - h2ot_lib.auc(y, F_o)) <= 1e-5
+    assert np.allclose(gm.varimp(), om.varimp(), rtol=1e-5, atol=0)
+    gm.close()
+
+
+def test_config1_shape_100k_x_10():
+    """BASELINE.json configs[0]: GBM bernoulli, 100k x 10 numeric, ntrees=10, max_depth=5, nbins=20."""
+    rng = np.random.default_rng(42)
+    n, c = 100000, 10
+    X = rng.normal(size=(n, c)).astype(np.float32).astype(np.float64)
+    beta = rng.normal(size=c)
+    y = (rng.random(n) < 1 / (1 + np.exp(-(X @ beta + 0.5 * X[:, 0] * X[:, 1])))).astype(np.float64)
+    gm, om = _run_both(X, y, ntrees=10, max_depth=5, nbins=20, seed=1234, capture=False)
+    h2ot_lib.compare_models(gm, om, check_levels=False)
+    F_g, F_o = gm.predictions(), om.F()
+    assert abs(h2ot_lib.logloss(y, F_g) - h2ot_lib.logloss(y, F_o)) <= 1e-5
+    assert abs(h2ot_lib.auc(y, F_g) - h2ot_lib.auc(y, F_o)) <= 1e-5
+    gm.close()
+
+
+def test_gaussian_weights_offset():
+    X, _, cats = h2ot_lib.make_frame(n=20000, c=5, seed=5)
+    rng = np.random.default_rng(6)
+    y = np.nan_to_num(X[:, 0]) * 2 + np.nan_to_num(X[:, 2]) ** 2 + rng.normal(size=len(X)) * 0.1
+    y = y.astype(np.float32).astype(np.float64)
+    y[::501] = NaN  # NA responses are skipped everywhere
+    w = rng.integers(0, 3, len(X)).astype(np.float64)
+    off = (rng.random(len(X)) * 0.1).astype(np.float32).astype(np.float64)
+    gm, om = _run_both(X, y, cats, w=w, off=off, distribution="gaussian", ntrees=4, max_depth=4, nbins=32, seed=99)
+    h2ot_lib.compare_models(gm, om)
+    gm.close()
+
+
+def test_row_and_column_sampling():
+    X, y, cats = h2ot_lib.make_frame(n=25000, c=8, seed=21)
+    gm, om = _run_both(X, y, cats, ntrees=5, max_depth=5, nbins=20, seed=777, sample_rate=0.6, col_sample_rate=0.5,
+                       col_sample_rate_per_tree=0.8)
+    h2ot_lib.compare_models(gm, om)
+    gm.close()
+
+
+def test_multinomial_three_classes():
+    rng = np.random.default_rng(3)
+    n = 20000
+    X = rng.normal(size=(n, 5)).astype(np.float32).astype(np.float64)
+    X[rng.random(X.shape) < 0.01] = NaN
+    y = np.argmax(np.nan_to_num(X[:, :3]) + 0.5 * rng.normal(size=(n, 3)), axis=1).astype(np.float64)
+    gm, om = _run_both(X, y, distribution="multinomial", nclass=3, ntrees=4, max_depth=4, nbins=20, seed=31)
+    h2ot_lib.compare_models(gm, om, K=3)
+    gm.close()
+
+
+def test_high_cardinality_categorical_and_min_rows():
+    rng = np.random.default_rng(8)
+    n = 40000
+    card = 300
+    eff = rng.normal(size=card)
+    c0 = rng.integers(0, card, n).astype(np.float64)
+    c1 = rng.normal(size=n).astype(np.float32).astype(np.float64)
+    c2 = rng.integers(0, 2000, n).astype(np.float64)  # > nbins_cats levels: ordinal binned path
+    X = np.stack([c0, c1, c2], axis=1)
+    X[rng.random(X.shape) < 0.02] = NaN
+    y = (eff[np.nan_to_num(c0).astype(int)] + 0.5 * c1 + rng.normal(size=n) * 0.2).astype(np.float32).astype(np.float64)
+    gm, om = _run_both(X, y, {0: card, 2: 2000}, distribution="gaussian", ntrees=3, max_depth=4, nbins=20, nbins_cats=1024,
+                       min_rows=50.0, seed=5)
+    h2ot_lib.compare_models(gm, om)
+    gm.close()
+
+
+def test_pubdev6356_exact_predictions():
+    """TT/gbm/GBMTest.java:4160-4232: 100 rows of (1,1), 100 of (2,2) and 800 rows with NA response; a depth-2
+    learn_rate=1 gaussian tree must predict exactly 1.0 / 2.0."""
+    P = h2ot_lib.pkg()
+    N, cnt = 1000, 100
+    x = np.zeros(N)
+    y = np.full(N, NaN)
+    x[:cnt], y[:cnt] = 1, 1
+    x[cnt:2 * cnt], y[cnt:2 * cnt] = 2, 2
+    gm = P.GBM(distribution="gaussian", nclass=1, seed=42, max_depth=2, ntrees=1, learn_rate=1.0)
+    gm.load([x], y)
+    gm.train()
+    F = gm.predictions()
+    assert np.all(F[:cnt] == 1.0) and np.all(F[cnt:2 * cnt] == 2.0)
+    gm.close()
+
+
+def test_na_predictor_root_split_is_na_vs_rest():
+    """TT/SharedTreeTest.java:80-138 checkNAPredictor: root NAvsREST split, 3-node tree, zero training error."""
+    P = h2ot_lib.pkg()
+    x = np.array([NaN, 1, NaN, 1, NaN, 1])
+    y = np.array([0, 1, 0, 1, 0, 1], dtype=np.float64)
+    gm = P.GBM(distribution="bernoulli", seed=42, ntrees=1, learn_rate=1.0, min_rows=1.0)
+    gm.load([x], y)
+    gm.train()
+    t, _ = gm.tree(0)
+    assert len(t) == 3 and t[0].has_split and t[0].nasplit == P.NA_VS_REST
+    F = gm.predictions()
+    assert np.array_equal((1 / (1 + np.exp(-F)) > 0.5).astype(int), y.astype(int))
+    gm.close()
+
+
+def test_run_to_run_determinism():
+    """TT/gbm/GBMTest.java:4801-4866 protocol (scaled down): identical models from identical seeds, bit for bit."""
+    X, y, cats = h2ot_lib.make_frame(n=60000, c=6, seed=2)
+    P = h2ot_lib.pkg()
+    sigs = []
+    for _ in range(3):
+        gm = P.GBM(ntrees=3, max_depth=5, seed=1234, sample_rate=0.8)
+        gm.load([X[:, c] for c in range(X.shape[1])], y, categorical=cats)
+        gm.train()
+        sig = [gm.predictions().tobytes()]
+        for t in range(gm.ntrees):
+            nodes, _ = gm.tree(t)
+            sig.append(bytes(nodes))
+        sigs.append(sig)
+        gm.close()
+    assert sigs[0] == sigs[1] == sigs[2]
