@@ -114,6 +114,7 @@ struct h2ot_engine {
   int C = 0, K = 0;
   int sm_count = 148;
   int max_smem_optin = 0;
+  int split_smem_max = 0;
   cudaStream_t stream = nullptr;
   std::vector<Column> cols;
   DBuf<ColRef> d_cols;
@@ -291,7 +292,12 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   // opt in to the large dynamic shared memory carve-out once
   CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
   CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
-  CUDA_TRY(cudaFuncSetAttribute(find_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  {
+    cudaFuncAttributes fa;
+    CUDA_TRY(cudaFuncGetAttributes(&fa, find_split_kernel));
+    h->split_smem_max = h->max_smem_optin - (int)fa.sharedSizeBytes;  // the opt-in limit covers static + dynamic
+    CUDA_TRY(cudaFuncSetAttribute(find_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->split_smem_max));
+  }
   *out = h;
   return H2OT_OK;
 }
@@ -905,7 +911,7 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   const size_t n1 = (size_t)t.max_split_nbin + 1;
   size_t smem = 8 * 9 * n1;
   if (t.any_cat) smem += 8 * (3 * n1 + n1) + 4 * n1;
-  if (smem > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
+  if (smem > (size_t)h->split_smem_max) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
   if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
   SplitArgs sa{t.L, h->C, t.d_descs.p, t.d_vals.p, t.d_min2.p, t.d_maxIn.p, t.d_has.p, min_rows, min_split_improvement, t.d_cand.p};
   TRY(t_begin(h, &h->stats.ms_split));

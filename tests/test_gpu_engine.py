@@ -40,7 +40,7 @@ def test_bin_codes_bit_exact():
     """DHistogram.bin (T/DHistogram.java:272-306): bin codes must be bit-exact, incl. NA, +-Inf, -0.0, float-split check."""
     rng = np.random.default_rng(1)
     n = 100003
-    x = rng.normal(size=n).astype(np.float32).astype(np.float64) * 3
+    x = (rng.normal(size=n) * 3).astype(np.float32).astype(np.float64)
     x[:7] = [NaN, np.inf, -np.inf, -0.0, 0.0, x.min(), x.max()]
     x64 = rng.normal(size=n) * 1e3  # not fp32-exact -> F64 storage
     xi = rng.integers(-100, 100, n).astype(np.float64)
@@ -107,7 +107,7 @@ def test_root_level_histogram_matches_update_histo(weighted):
     r = results[0]
     rows = np.arange(n, dtype=np.int32) if w is None else np.nonzero(w != 0)[0].astype(np.int32)
     for c in range(X.shape[1]):
-        oh = _oracle_hist(args[c], X[:, c], work, w, rows, int_path=args[c][5])
+        oh = _oracle_hist(args[c], X[:, c], work[rows], w, rows, int_path=args[c][5])  # ys are gathered in leaf order
         ov = oh.vals()
         gv = r["vals"][r["offsets"][c]: r["offsets"][c] + ov.size]
         assert r["has_vals"][c] == 1
