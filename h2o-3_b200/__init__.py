@@ -107,7 +107,7 @@ ENGINE_SYMBOLS = [
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_set_tree",
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode",
+    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc",
 ]
 GBM_SYMBOLS = [
     "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
@@ -162,6 +162,7 @@ def load():
     L.h2ot_stats_get.argtypes = [vp, C.POINTER(Stats)]
     L.h2ot_stats_reset.argtypes = [vp]
     L.h2ot_set_hist_mode.argtypes = [vp, i32]
+    L.h2ot_hist_column_noalloc.argtypes = [vp, vp, vp, i64, i32, vp, dbl, vp, vp]
     L.h2ot_gbm_create.argtypes = [C.POINTER(GbmParams), i32, i64, i32, i64, i64, i32, i32, C.POINTER(vp)]
     L.h2ot_gbm_destroy.argtypes = [vp]
     L.h2ot_gbm_set_column.argtypes = [vp, i32, vp, i32, i32]
@@ -385,6 +386,16 @@ class Engine:
 
     def set_hist_mode(self, mode):
         _check(self.L.h2ot_set_hist_mode(self.h, mode))
+
+
+NOALLOC_MAX_LEAVES, NOALLOC_MAX_BINS = 64, 65536
+
+
+def hist_column_noalloc(d_x, d_work, d_leaf_code, n, descs, work_abs_bound, d_out_vals, stream=0):
+    """h2ot_hist_column_noalloc: all d_* are raw device addresses (int) on the current device; descs a ctypes HistDesc array."""
+    _check(load().h2ot_hist_column_noalloc(C.c_void_p(d_x), C.c_void_p(d_work), C.c_void_p(d_leaf_code) if d_leaf_code else None,
+                                           n, len(descs), C.cast(descs, C.c_void_p), work_abs_bound, C.c_void_p(d_out_vals),
+                                           C.c_void_p(stream) if stream else None))
 
 
 def make_desc(mn, max_ex, nbin, step=None, is_int=0, int_opt=False, check_float=False, init_na=False, order=0, active=True):

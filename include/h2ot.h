@@ -225,6 +225,24 @@ int h2ot_stats_reset(h2ot_engine* h);
 /* 0: shared-memory privatised histograms (default), 1: global (L2) atomics only — used by tests to cross-check. */
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
 
+/* ---- histogram of one column for callers that cannot allocate device memory.
+ * No counterpart in the reference: it exists for embedders whose process may not call cudaMalloc once it is running (a JVM or
+ * service that gave the whole GPU to its own pooling allocator, a real-time path where an allocation is an unbounded stall, a
+ * plug-in host that forbids allocation after start-up). The caller owns every buffer it passes — device pointers on the CURRENT
+ * device: d_x[n] (fp32 column, NaN == NA), d_work[n] (fp32 response/residual), d_leaf_code[n] (leaf of each row, >= n_leaves ==
+ * skip; NULL == all rows in leaf 0), d_out_vals (packed per leaf, (nbin+1)*3 doubles each: w, wY, wYY with the float cast of
+ * reducePrecision) — and descs[n_leaves] on the host (min, step, nbin are read). The kernel's accumulators live in a fixed
+ * 1.5 MiB device array inside the library (present on every GPU that loads it), so the call allocates nothing.
+ * Limits: n_leaves <= H2OT_NOALLOC_MAX_LEAVES and sum(nbin+1) <= H2OT_NOALLOC_MAX_BINS, else H2OT_ERR_UNSUPPORTED.
+ * The array is shared by all calls on a GPU and keeps the last call's contents; each call clears what it uses, so calls
+ * whose GPU work overlaps would corrupt each other: issue them one after another. The first call on a GPU resolves the
+ * array's address; make it before any stream capture. Work is enqueued on cuda_stream (a cudaStream_t, NULL == default
+ * stream) and the call returns after that stream has drained. Unit weights only. */
+#define H2OT_NOALLOC_MAX_LEAVES 64
+#define H2OT_NOALLOC_MAX_BINS 65536
+int h2ot_hist_column_noalloc(const float* d_x, const float* d_work, const uint16_t* d_leaf_code, int64_t n, int32_t n_leaves,
+                             const h2ot_hist_desc* descs, double work_abs_bound, double* d_out_vals, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif
