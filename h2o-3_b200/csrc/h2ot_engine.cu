@@ -73,6 +73,9 @@ struct TreeState {  // per class-tree k
   bool built = false, finished = false;
   std::vector<DescDev> h_descs;
   std::vector<GroupDev> h_groups;
+  std::vector<int32_t> h_group_cols;
+  int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
+  DBuf<int32_t> d_group_cols;
   int n_smem_groups = 0;
   size_t smem_bytes = 0;
   int64_t total_bins = 0, total_vals = 0;
@@ -89,6 +92,7 @@ struct TreeState {  // per class-tree k
   DBuf<float> d_pred;
   int max_split_nbin = 0;
   bool any_cat = false;
+  bool any_checkfloat = false;  // some descriptor of the level asks for the float-split correction (DRF)
 };
 
 // minimal NCCL surface, resolved with dlopen so that the library has no link-time NCCL dependency
@@ -290,8 +294,16 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   CUDA_TRY(cudaMemcpyAsync(h->d_nidsp.p, np_.data(), h->K * sizeof(int32_t*), cudaMemcpyHostToDevice, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   // opt in to the large dynamic shared memory carve-out once
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+#define H2OT_OPTIN(ST)                                                                                                                      \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
+  H2OT_OPTIN(H2OT_STORE_F32);
+  H2OT_OPTIN(H2OT_STORE_F64);
+  H2OT_OPTIN(H2OT_STORE_U8);
+  H2OT_OPTIN(H2OT_STORE_U16);
+#undef H2OT_OPTIN
   {
     cudaFuncAttributes fa;
     CUDA_TRY(cudaFuncGetAttributes(&fa, find_split_kernel));
@@ -319,7 +331,7 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.work) cudaFree(t.work);
     if (t.nids) cudaFree(t.nids);
     if (t.code) cudaFree(t.code);
-    t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release();
+    t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release(); t.d_group_cols.release();
     t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_min2.release(); t.d_maxIn.release(); t.d_wna.release();
     t.d_has.release(); t.d_cand.release(); t.d_best.release(); t.d_gamma.release(); t.d_pred.release();
   }
@@ -627,6 +639,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   t.total_vals = 0;
   t.max_split_nbin = 0;
   t.any_cat = false;
+  t.any_checkfloat = false;
   std::vector<int64_t> col_words(C, 0);
   for (int l = 0; l < L; l++)
     for (int c = 0; c < C; c++) {
@@ -653,74 +666,86 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       col_words[c] += (int64_t)(s.nbin + 1) * WPB;
       t.max_split_nbin = std::max(t.max_split_nbin, (int)s.nbin);
       if ((s.flags & H2OT_DESC_ISCAT) && s.step == 1.0) t.any_cat = true;
+      if (s.flags & H2OT_DESC_CHECKFLOAT) t.any_checkfloat = true;
     }
-  // ---- shared-memory groups
-  auto fixed_bytes = [&](int ncg) { return (size_t)ncg * L * (sizeof(DescS) + sizeof(MinMaxS)) + (size_t)ncg * sizeof(ColRef); };
+  // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
+  auto fixed_bytes = [&](int ncg, int storage) {
+    return (size_t)ncg * L * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
+           (size_t)ncg * (sizeof(ColRef) + sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
+  };
   const size_t full_budget = (size_t)h->max_smem_optin;
-  const size_t half_budget = 112 * 1024;
-  size_t budget = 0;
+  // the kernel runs one 1024-thread CTA per SM (64 registers/thread), so a CTA may use the whole opt-in carve-out
+  size_t budget = full_budget;
   if (h->smem_budget_kb > 0) budget = std::min<size_t>((size_t)h->smem_budget_kb * 1024, full_budget);
-  else {
-    size_t worst = 0;
-    for (int c = 0; c < C; c++)
-      if (col_words[c]) worst = std::max(worst, (size_t)col_words[c] * 4 + fixed_bytes(1));
-    budget = worst > half_budget ? full_budget : half_budget;
-  }
   t.h_groups.clear();
+  t.h_group_cols.clear();
   t.active_cols = 0;
-  std::vector<int> smem_cols, glob_cols;
+  std::vector<int> glob_cols;
+  std::vector<int> bucket[4];
   for (int c = 0; c < C; c++) {
     if (!col_words[c]) continue;
     t.active_cols++;
-    if (h->hist_mode == 1 || (size_t)col_words[c] * 4 + fixed_bytes(1) > full_budget) glob_cols.push_back(c);
-    else smem_cols.push_back(c);
+    const int st = h->cols[c].storage;
+    if (h->hist_mode == 1 || (size_t)col_words[c] * 4 + fixed_bytes(1, st) > full_budget) glob_cols.push_back(c);
+    else bucket[st].push_back(c);
   }
-  // greedy count, then even re-split over the same number of groups (keeps CTAs of one launch balanced)
-  auto pack = [&](size_t target_words, std::vector<GroupDev>& out) {
-    out.clear();
-    size_t i = 0;
-    while (i < smem_cols.size()) {
-      GroupDev g{smem_cols[i], smem_cols[i] + 1, 0, 0};
-      size_t words = 0;
-      int ncg = 0;
-      while (i < smem_cols.size()) {
-        const int c = smem_cols[i];
-        const int span = c + 1 - g.c_begin;  // groups are contiguous column ranges (inactive columns inside cost only descriptors)
-        const size_t nw = words + (size_t)col_words[c];
-        if (ncg > 0 && (nw * 4 + fixed_bytes(span) > budget || words >= target_words)) break;
-        words = nw;
-        ncg++;
-        g.c_end = c + 1;
-        i++;
-      }
-      g.smem_words = (int32_t)words;
-      out.push_back(g);
-    }
-  };
-  std::vector<GroupDev> groups;
-  pack(SIZE_MAX, groups);
-  if (groups.size() > 1) {
-    size_t total = 0;
-    for (int c : smem_cols) total += (size_t)col_words[c];
-    std::vector<GroupDev> even;
-    pack((total + groups.size() - 1) / groups.size(), even);
-    if (even.size() <= groups.size()) groups = even;
-  }
-  t.n_smem_groups = (int)groups.size();
   t.smem_bytes = 0;
-  for (GroupDev& g : groups) {
-    int off = 0;
-    for (int c = g.c_begin; c < g.c_end; c++)
-      for (int l = 0; l < L; l++) {
-        DescDev& d = t.h_descs[(size_t)l * C + c];
-        if (d.nbin < 0) continue;
-        d.smem_off = off;
-        off += (d.nbin + 1) * WPB;
+  for (int st = 0; st < 4; st++) {
+    t.bucket_begin[st] = (int)t.h_groups.size();
+    const std::vector<int>& cols = bucket[st];
+    if (cols.empty()) {
+      t.bucket_end[st] = t.bucket_begin[st];
+      continue;
+    }
+    // greedy count, then even re-split over the same number of groups (keeps the CTAs of one launch balanced)
+    auto pack = [&](size_t target_words, std::vector<std::vector<int>>& out) {
+      out.clear();
+      size_t i = 0;
+      while (i < cols.size()) {
+        std::vector<int> g;
+        size_t words = 0;
+        while (i < cols.size()) {
+          const int c = cols[i];
+          const size_t nw = words + (size_t)col_words[c];
+          if (!g.empty() && (nw * 4 + fixed_bytes((int)g.size() + 1, st) > budget || words >= target_words)) break;
+          words = nw;
+          g.push_back(c);
+          i++;
+        }
+        out.push_back(g);
       }
-    t.smem_bytes = std::max(t.smem_bytes, fixed_bytes(g.c_end - g.c_begin) + (size_t)g.smem_words * 4);
-    t.h_groups.push_back(g);
+    };
+    std::vector<std::vector<int>> groups, even;
+    pack(SIZE_MAX, groups);
+    if (groups.size() > 1) {
+      size_t total = 0;
+      for (int c : cols) total += (size_t)col_words[c];
+      pack((total + groups.size() - 1) / groups.size(), even);
+      if (even.size() <= groups.size()) groups = even;
+    }
+    for (const std::vector<int>& g : groups) {
+      GroupDev gd{(int32_t)t.h_group_cols.size(), (int32_t)g.size(), 0, 0, st, 0};
+      int off = 0;
+      for (int c : g) {
+        t.h_group_cols.push_back(c);
+        for (int l = 0; l < L; l++) {
+          DescDev& d = t.h_descs[(size_t)l * C + c];
+          if (d.nbin < 0) continue;
+          d.smem_off = off;
+          off += (d.nbin + 1) * WPB;
+        }
+      }
+      gd.smem_words = off;
+      t.smem_bytes = std::max(t.smem_bytes, fixed_bytes((int)g.size(), st) + (size_t)off * 4);
+      t.h_groups.push_back(gd);
+    }
+    t.bucket_end[st] = (int)t.h_groups.size();
   }
-  for (int c : glob_cols) t.h_groups.push_back(GroupDev{c, c + 1, 0, 1});
+  t.n_smem_groups = (int)t.h_groups.size();
+  for (int c : glob_cols) {
+    t.h_groups.push_back(GroupDev{(int32_t)t.h_group_cols.size(), 1, 0, 1, h->cols[c].storage, 0});
+    t.h_group_cols.push_back(c);
+  }
   return H2OT_OK;
 }
 
@@ -754,6 +779,8 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   TRY(h2d(h, t.d_descs.p, t.h_descs.data(), LC * sizeof(DescDev)));
   TRY(h2d(h, t.d_hdescs.p, descs, LC * sizeof(h2ot_hist_desc)));
   if (!t.h_groups.empty()) TRY(h2d(h, t.d_groups.p, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev)));
+  TRY(t.d_group_cols.ensure(std::max<size_t>(1, t.h_group_cols.size())));
+  if (!t.h_group_cols.empty()) TRY(h2d(h, t.d_group_cols.p, t.h_group_cols.data(), t.h_group_cols.size() * sizeof(int32_t)));
   CUDA_TRY(cudaMemsetAsync(t.d_sums.p, 0, ((size_t)t.total_bins * 3 + n_leaves) * sizeof(long long), h->stream));
   CUDA_TRY(cudaMemsetAsync(t.d_minmax.p, 0, LC * 2 * sizeof(unsigned long long), h->stream));
 
@@ -770,11 +797,8 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   ha.n_pad = h->n_pad;
   ha.L = n_leaves;
   ha.C = h->C;
-  ha.n_groups = t.n_smem_groups;
-  const int ctas_per_sm = t.smem_bytes <= 112 * 1024 ? 2 : 1;
-  ha.n_slices = std::max(1, (h->sm_count * ctas_per_sm) / std::max(1, t.n_smem_groups));
+  ha.group_cols = t.d_group_cols.p;
   const int64_t n_tiles = h->n_pad / kTileRows;
-  ha.n_slices = (int)std::min<int64_t>(ha.n_slices, std::max<int64_t>(1, n_tiles));
   ha.code = t.code;
   ha.work = t.work;
   ha.w = h->w;
@@ -789,19 +813,38 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
   ha.sw = std::ldexp(1.0, ew);
   TRY(t_begin(h, &h->stats.ms_hist));
-  if (t.n_smem_groups > 0) {
-    if (t.smem_bytes > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "shared-memory plan exceeds the device limit");
-    const int grid = t.n_smem_groups * ha.n_slices;
-    if (h->w) hist_smem_kernel<7, true><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
-    else hist_smem_kernel<5, false><<<grid, kHistThreads, t.smem_bytes, h->stream>>>(ha);
+  if (t.n_smem_groups > 0 && t.smem_bytes > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "shared-memory plan exceeds the device limit");
+  for (int st = 0; st < 4; st++) {
+    const int ng = t.bucket_end[st] - t.bucket_begin[st];
+    if (ng <= 0) continue;
+    ha.group_begin = t.bucket_begin[st];
+    ha.n_groups = ng;
+    ha.n_slices = (int)std::min<int64_t>(std::max(1, h->sm_count / ng), std::max<int64_t>(1, n_tiles));
+    const int grid = ng * ha.n_slices;
+    const size_t sm = t.smem_bytes;
+#define H2OT_LAUNCH_HIST(ST)                                                                                 \
+  if (h->w) {                                                                                                \
+    if (t.any_checkfloat) hist_smem_kernel<7, true, ST, true><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
+    else hist_smem_kernel<7, true, ST, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
+  } else {                                                                                                   \
+    if (t.any_checkfloat) hist_smem_kernel<5, false, ST, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
+    else hist_smem_kernel<5, false, ST, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                   \
+  }
+    switch (st) {
+      case H2OT_STORE_F32: H2OT_LAUNCH_HIST(H2OT_STORE_F32); break;
+      case H2OT_STORE_F64: H2OT_LAUNCH_HIST(H2OT_STORE_F64); break;
+      case H2OT_STORE_U8: H2OT_LAUNCH_HIST(H2OT_STORE_U8); break;
+      default: H2OT_LAUNCH_HIST(H2OT_STORE_U16); break;
+    }
+#undef H2OT_LAUNCH_HIST
     h->stats.launches++;
     h->stats.hist_launches++;
   }
   for (size_t g = t.n_smem_groups; g < t.h_groups.size(); g++) {
-    const GroupDev& gd = t.h_groups[g];
+    const int c = t.h_group_cols[t.h_groups[g].cols_off];
     const int grid = grid_for(h, h->n_pad / 4, 256, 8);
-    if (h->w) hist_global_kernel<true><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
-    else hist_global_kernel<false><<<grid, 256, 0, h->stream>>>(ha, gd.c_begin, gd.c_end);
+    if (h->w) hist_global_kernel<true><<<grid, 256, 0, h->stream>>>(ha, c, c + 1);
+    else hist_global_kernel<false><<<grid, 256, 0, h->stream>>>(ha, c, c + 1);
     h->stats.launches++;
     h->stats.hist_launches++;
   }

@@ -2,6 +2,8 @@
 // Replaces ScoreBuildHistogram2.setupLocal phases 1+2 and postGlobal
 // (T/ScoreBuildHistogram2.java:139-168, 192-310, 412-466; T/DHistogram.java:609-704, 734-740).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace h2ot {
@@ -17,9 +19,11 @@ struct DescDev {
   uint32_t pad;
 };
 struct GroupDev {
-  int32_t c_begin, c_end;  // column range [c_begin, c_end)
-  int32_t smem_words;      // histogram words needed by this group
-  int32_t mode;            // 0: shared-memory privatised, 1: global atomics
+  int32_t cols_off, ncols;  // the group's columns: group_cols[cols_off .. cols_off + ncols) (all of one storage type)
+  int32_t smem_words;       // histogram words needed by this group
+  int32_t mode;             // 0: shared-memory privatised, 1: global atomics
+  int32_t storage;          // H2OT_STORE_* shared by the group's columns
+  int32_t pad;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -114,6 +118,8 @@ __global__ void __launch_bounds__(256) score_decide_kernel(ScoreArgs a) {
 struct HistArgs {
   int64_t n_pad;
   int32_t L, C, n_groups, n_slices;
+  int32_t group_begin, pad0;
+  const int32_t* group_cols;
   const uint16_t* code;
   const float* work;
   const double* w;  // nullptr: unit weights
@@ -125,16 +131,20 @@ struct HistArgs {
   double sy, syy, sw;          // 2^k scales of wY, wYY, w
 };
 
-struct __align__(16) DescS {  // shared-memory copy, 32 B
-  double min, step;
-  int32_t nbin;  // -1 inactive
-  int32_t soff;
-  uint32_t flags;
-  uint32_t pad;
-};
-struct __align__(16) MinMaxS {
+// Shared-memory descriptor table of one CTA: one record of kTStride 32-bit words per (group column, leaf) pair
+// p = gc * L + leaf. A warp's lanes sit in different leaves once the tree is a few levels deep; the odd stride puts the
+// same word of up to 32 different records into 32 different banks (one wavefront per lookup), whereas 16/32-byte aligned
+// records would serialise on the few bank-quads they start in.
+enum { kTMinLo = 0, kTMinHi, kTStepLo, kTStepHi, kTPlace, kTNbin, kTKmin, kTKmax, kTStride = 9 };
+//   kTPlace: word offset of bin 0 in the CTA's histogram (kInactive: no histogram for this pair)
+//   kTKmin / kTKmax: ~key32 / key32 of the smallest / largest value seen (0: none) -- F32 / U8 / U16 storage
+struct __align__(16) MinMaxS {  // 64-bit keys, only for F64-stored columns
   unsigned long long mn, mx;
 };
+struct Double4 {
+  double2 a, b;
+};
+constexpr uint32_t kInactive = 0xFFFFFFFFu;
 
 constexpr int kHistThreads = 1024;
 constexpr int kRowsPerThread = 4;
@@ -174,41 +184,153 @@ __device__ __forceinline__ void load4(const ColRef& c, int64_t row, double (&x)[
   }
 }
 
+// ---- shared-memory access by 32-bit address, predicated in PTX: the compiler wraps every conditional atomic in a
+// BSSY / BRA / BSYNC sequence, which tripled the instruction count of the inner loop.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void red_add_u32(uint32_t addr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t atom_add_u32(uint32_t addr, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(addr), "r"(v) : "memory");
+  return old;
+}
+// [addr] += hi + carry(old + lo), skipped when that is zero
+__device__ __forceinline__ void red_add_hi(uint32_t addr, uint32_t old, uint32_t lo, uint32_t hi) {
+  asm volatile(
+      "{\n .reg .pred q;\n .reg .u32 t, h;\n add.cc.u32 t, %1, %2;\n addc.u32 h, %3, 0;\n setp.ne.u32 q, h, 0;\n"
+      " @q red.shared.add.u32 [%0], h;\n}" ::"r"(addr), "r"(old), "r"(lo), "r"(hi) : "memory");
+}
+// if (on && v > cur) [addr] = max([addr], v)
+__device__ __forceinline__ void red_max_if_gt(uint32_t addr, uint32_t v, uint32_t cur, uint32_t on) {
+  asm volatile(
+      "{\n .reg .pred q;\n setp.gt.u32 q, %1, %2;\n setp.ne.and.u32 q, %3, 0, q;\n @q red.shared.max.u32 [%0], %1;\n}" ::"r"(addr), "r"(v),
+      "r"(cur), "r"(on) : "memory");
+}
+
+// R (row, col) items of one thread, staged so that independent work overlaps: record lookups, fp64 bin arithmetic, then
+// the atomics grouped by word (the carries out of the low words are consumed last). Rows that take no part (skip code,
+// no histogram for the pair) are steered to a per-lane sink bin instead of branching around the atomics.
+// x: values as doubles; na: NA mask; key: order-preserving 32-bit keys (unused when KEY64).
+template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, int J0, int R>
+__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, const int (&leaf)[4],
+                                           const double (&x)[4], const bool (&na)[4], const uint32_t (&key)[4],
+                                           const long long (&qw)[4], const long long (&qy)[4], const long long (&qyy)[4]) {
+  uint32_t wd[4];
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) {
+    const bool row_on = leaf[j] != kSkipCode;
+    const int p = pbase + (row_on ? leaf[j] : 0);
+    const uint32_t rec = tab_a + (uint32_t)p * (kTStride * 4);
+    const uint32_t place = lds_u32(rec + kTPlace * 4);
+    const uint32_t on = (row_on && place != kInactive) ? 1u : 0u;
+    const int nbin = (int)lds_u32(rec + kTNbin * 4);
+    const double mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
+    const double st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
+    int b;
+    if (CHECKFLOAT) b = bin_of(x[j], mn, st, nbin, true);
+    else b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
+    b = na[j] ? nbin : b;
+    if (KEY64) {
+      if (on && !na[j]) {
+        const unsigned long long k = dkey(x[j]);
+        const MinMaxS m = mm64[p];
+        if (~k > m.mn) atomicMax(&mm64[p].mn, ~k);
+        if (k > m.mx) atomicMax(&mm64[p].mx, k);
+      }
+    } else {
+      const uint32_t live = (on && !na[j]) ? 1u : 0u;
+      red_max_if_gt(rec + kTKmin * 4, ~key[j], lds_u32(rec + kTKmin * 4), live);
+      red_max_if_gt(rec + kTKmax * 4, key[j], lds_u32(rec + kTKmax * 4), live);
+    }
+    wd[j] = on ? hist_a + (place + (uint32_t)(b * WPB)) * 4u : sink_a;
+  }
+  // low words first (their return values carry into the high words), then the high words
+  constexpr uint32_t OW = 0, OY = (HAS_W ? 2 : 1) * 4, OYY = (HAS_W ? 4 : 3) * 4;
+  uint32_t oy[4], oyy[4], ow[4];
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) {
+    if (HAS_W) ow[j] = atom_add_u32(wd[j] + OW, (uint32_t)qw[j]);
+    else red_add_u32(wd[j] + OW, 1u);
+  }
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) oy[j] = atom_add_u32(wd[j] + OY, (uint32_t)qy[j]);
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) oyy[j] = atom_add_u32(wd[j] + OYY, (uint32_t)qyy[j]);
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) {
+    if (HAS_W) red_add_hi(wd[j] + OW + 4, ow[j], (uint32_t)qw[j], (uint32_t)((unsigned long long)qw[j] >> 32));
+    red_add_hi(wd[j] + OY + 4, oy[j], (uint32_t)qy[j], (uint32_t)((unsigned long long)qy[j] >> 32));
+    red_add_hi(wd[j] + OYY + 4, oyy[j], (uint32_t)qyy[j], (uint32_t)((unsigned long long)qyy[j] >> 32));
+  }
+}
+
+#ifndef H2OT_ITEMS_IN_FLIGHT
+#define H2OT_ITEMS_IN_FLIGHT 2
+#endif
+constexpr int kItemsInFlight = H2OT_ITEMS_IN_FLIGHT;  // rows of a thread whose lookups / atomics are interleaved (2 or 4)
+
 // Shared-memory privatised histograms. One CTA = (column group, row-tile stride). Per bin WPB 32-bit words:
 //   unit weights (WPB 5): [cnt, wY.lo, wY.hi, wYY.lo, wYY.hi]
 //   weighted     (WPB 7): [w.lo, w.hi, wY.lo, wY.hi, wYY.lo, wYY.hi, pad]
-template <int WPB, bool HAS_W>
+// followed by 32 sink bins (one per lane) that swallow the adds of rows taking no part.
+template <int WPB, bool HAS_W, int STORAGE, bool CHECKFLOAT>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int g = blockIdx.x % a.n_groups;
+  constexpr bool KEY64 = STORAGE == H2OT_STORE_F64;
+  const int g = a.group_begin + blockIdx.x % a.n_groups;
   const int slice = blockIdx.x / a.n_groups;
   const GroupDev grp = a.groups[g];
-  const int ncg = grp.c_end - grp.c_begin;
+  const int ncg = grp.ncols;
   const int npairs = ncg * a.L;
-  DescS* descS = reinterpret_cast<DescS*>(smem_raw);
-  MinMaxS* mmS = reinterpret_cast<MinMaxS*>(descS + npairs);
-  ColRef* colS = reinterpret_cast<ColRef*>(mmS + npairs);
-  uint32_t* hist = reinterpret_cast<uint32_t*>(colS + ncg);
+  MinMaxS* mmS = reinterpret_cast<MinMaxS*>(smem_raw);
+  ColRef* colS = reinterpret_cast<ColRef*>(mmS + (KEY64 ? npairs : 0));
+  int32_t* cidxS = reinterpret_cast<int32_t*>(colS + ncg);
+  uint32_t* T = reinterpret_cast<uint32_t*>(cidxS + ncg + (ncg & 1));
+  uint32_t* hist = T + (size_t)kTStride * npairs;
+  uint32_t* sink = hist + grp.smem_words;
 
+  for (int i = threadIdx.x; i < ncg; i += blockDim.x) {
+    const int c = a.group_cols[grp.cols_off + i];
+    cidxS[i] = c;
+    colS[i] = a.cols[c];
+  }
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
     const int gc = p / a.L, l = p - gc * a.L;
-    const DescDev d = a.descs[(size_t)l * a.C + grp.c_begin + gc];
-    DescS s;
-    s.min = d.min; s.step = d.step; s.nbin = d.nbin; s.soff = d.smem_off; s.flags = d.flags; s.pad = 0;
-    descS[p] = s;
-    mmS[p].mn = 0ULL; mmS[p].mx = 0ULL;
+    const DescDev d = a.descs[(size_t)l * a.C + a.group_cols[grp.cols_off + gc]];
+    uint32_t* r = T + (size_t)p * kTStride;
+    r[kTMinLo] = (uint32_t)__double2loint(d.min);
+    r[kTMinHi] = (uint32_t)__double2hiint(d.min);
+    r[kTStepLo] = (uint32_t)__double2loint(d.step);
+    r[kTStepHi] = (uint32_t)__double2hiint(d.step);
+    r[kTPlace] = d.nbin < 0 ? kInactive : (uint32_t)d.smem_off;
+    r[kTNbin] = (uint32_t)max(d.nbin, 1);
+    r[kTKmin] = 0u;
+    r[kTKmax] = 0u;
+    if (KEY64) { mmS[p].mn = 0ULL; mmS[p].mx = 0ULL; }
   }
-  for (int i = threadIdx.x; i < ncg; i += blockDim.x) colS[i] = a.cols[grp.c_begin + i];
-  for (int i = threadIdx.x; i < grp.smem_words; i += blockDim.x) hist[i] = 0u;
+  for (int i = threadIdx.x; i < grp.smem_words + 32 * WPB; i += blockDim.x) hist[i] = 0u;
   __syncthreads();
+  const uint32_t hist_a = smem_addr(hist), tab_a = smem_addr(T);
+  const uint32_t sink_a = smem_addr(sink) + (threadIdx.x & 31) * (WPB * 4);
+
+  using RawT = typename std::conditional<STORAGE == H2OT_STORE_F32, uint4,
+               typename std::conditional<STORAGE == H2OT_STORE_U16, uint2,
+               typename std::conditional<STORAGE == H2OT_STORE_U8, unsigned int, Double4>::type>::type>::type;
+  constexpr int kElem = STORAGE == H2OT_STORE_F32 ? 4 : STORAGE == H2OT_STORE_F64 ? 8 : STORAGE == H2OT_STORE_U8 ? 1 : 2;
 
   const int64_t n_tiles = a.n_pad / kTileRows;
   for (int64_t tile = slice; tile < n_tiles; tile += a.n_slices) {
     const int64_t row = tile * kTileRows + (int64_t)threadIdx.x * kRowsPerThread;
-    const ushort4 cd = *reinterpret_cast<const ushort4*>(a.code + row);
+    const ushort4 cd = __ldg(reinterpret_cast<const ushort4*>(a.code + row));
     int leaf[4] = {cd.x, cd.y, cd.z, cd.w};
     if (leaf[0] == kSkipCode && leaf[1] == kSkipCode && leaf[2] == kSkipCode && leaf[3] == kSkipCode) continue;
-    const float4 yv = *reinterpret_cast<const float4*>(a.work + row);
+    const float4 yv = __ldg(reinterpret_cast<const float4*>(a.work + row));
     const float ys[4] = {yv.x, yv.y, yv.z, yv.w};
     long long qy[4], qyy[4], qw[4];
 #pragma unroll
@@ -229,35 +351,48 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
       qy[j] = __double2ll_rn(__dmul_rn(wy, a.sy));
       qyy[j] = __double2ll_rn(__dmul_rn(wyy, a.syy));
     }
-    for (int gc = 0; gc < ncg; gc++) {
-      double x[4];
-      load4(colS[gc], row, x);
-#pragma unroll
-      for (int j = 0; j < 4; j++) {
-        if (leaf[j] == kSkipCode) continue;
-        const int p = gc * a.L + leaf[j];
-        const DescS d = descS[p];
-        if (d.nbin < 0) continue;
-        int b;
-        if (isnan(x[j])) b = d.nbin;
-        else {
-          b = bin_of(x[j], d.min, d.step, d.nbin, (d.flags & H2OT_DESC_CHECKFLOAT) != 0);
-          const unsigned long long k = dkey(x[j]);
-          const MinMaxS m = mmS[p];
-          if (~k > m.mn) atomicMax(&mmS[p].mn, ~k);
-          if (k > m.mx) atomicMax(&mmS[p].mx, k);
-        }
-        uint32_t* wd = hist + d.soff + b * WPB;
-        if (HAS_W) {
-          smem_add64(wd, qw[j]);
-          smem_add64(wd + 2, qy[j]);
-          smem_add64(wd + 4, qyy[j]);
-        } else {
-          atomicAdd(wd, 1u);
-          smem_add64(wd + 1, qy[j]);
-          smem_add64(wd + 3, qyy[j]);
-        }
+    // software pipeline over the group's columns: the next column's 4 values are in flight while this one is binned
+    auto fetch = [&](int gc) -> RawT {
+      const char* base = reinterpret_cast<const char*>(colS[gc].data) + row * kElem;
+      if constexpr (STORAGE == H2OT_STORE_F64) {
+        Double4 r;
+        r.a = __ldcs(reinterpret_cast<const double2*>(base));
+        r.b = __ldcs(reinterpret_cast<const double2*>(base) + 1);
+        return r;
+      } else {
+        return __ldcs(reinterpret_cast<const RawT*>(base));
       }
+    };
+    RawT nxt = fetch(0);
+    for (int gc = 0; gc < ncg; gc++) {
+      const RawT cur = nxt;
+      if (gc + 1 < ncg) nxt = fetch(gc + 1);
+      const int pbase = gc * a.L;
+      double x[4];
+      bool na[4];
+      uint32_t key[4] = {0u, 0u, 0u, 0u};
+      if constexpr (STORAGE == H2OT_STORE_F32) {
+        const float xf[4] = {__uint_as_float(cur.x), __uint_as_float(cur.y), __uint_as_float(cur.z), __uint_as_float(cur.w)};
+#pragma unroll
+        for (int j = 0; j < 4; j++) { x[j] = (double)xf[j]; na[j] = xf[j] != xf[j]; key[j] = fkey(xf[j]); }
+      } else if constexpr (STORAGE == H2OT_STORE_U8) {
+        const double cb = colS[gc].base;
+        const unsigned xc[4] = {cur & 255u, (cur >> 8) & 255u, (cur >> 16) & 255u, cur >> 24};
+#pragma unroll
+        for (int j = 0; j < 4; j++) { x[j] = cb + (double)xc[j]; na[j] = xc[j] == 255u; key[j] = xc[j] + 1u; }
+      } else if constexpr (STORAGE == H2OT_STORE_U16) {
+        const double cb = colS[gc].base;
+        const unsigned xc[4] = {cur.x & 65535u, cur.x >> 16, cur.y & 65535u, cur.y >> 16};
+#pragma unroll
+        for (int j = 0; j < 4; j++) { x[j] = cb + (double)xc[j]; na[j] = xc[j] == 65535u; key[j] = xc[j] + 1u; }
+      } else {
+        x[0] = cur.a.x; x[1] = cur.a.y; x[2] = cur.b.x; x[3] = cur.b.y;
+#pragma unroll
+        for (int j = 0; j < 4; j++) na[j] = isnan(x[j]);
+      }
+      hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, leaf, x, na, key, qw, qy, qyy);
+      if (kItemsInFlight < 4)
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, leaf, x, na, key, qw, qy, qyy);
     }
   }
   __syncthreads();
@@ -265,12 +400,15 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   // deterministic merge: integer adds into the global fixed-point accumulators
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   for (int p = warp; p < npairs; p += nwarps) {
-    const DescS d = descS[p];
-    if (d.nbin < 0) continue;
+    const uint32_t* r = T + (size_t)p * kTStride;
+    const uint32_t place = r[kTPlace];
+    if (place == kInactive) continue;
+    const int nbin = (int)r[kTNbin];
     const int gc = p / a.L, l = p - gc * a.L;
-    const DescDev dd = a.descs[(size_t)l * a.C + grp.c_begin + gc];
-    for (int b = lane; b <= d.nbin; b += 32) {
-      const uint32_t* wd = hist + d.soff + b * WPB;
+    const size_t lc = (size_t)l * a.C + cidxS[gc];
+    const DescDev dd = a.descs[lc];
+    for (int b = lane; b <= nbin; b += 32) {
+      const uint32_t* wd = hist + place + b * WPB;
       long long vw, vy, vyy;
       if (HAS_W) {
         vw = (long long)(((unsigned long long)wd[1] << 32) | wd[0]);
@@ -287,10 +425,23 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
       if (vyy) atomicAdd(dst + 2, (unsigned long long)vyy);
     }
     if (lane == 0) {
-      const MinMaxS m = mmS[p];
-      unsigned long long* mm = a.minmax + ((size_t)l * a.C + grp.c_begin + gc) * 2;
-      if (m.mn) atomicMax(mm, m.mn);
-      if (m.mx) atomicMax(mm + 1, m.mx);
+      // block-local keys -> the global order-preserving 64-bit form {~dkey(min), dkey(max)} (rank independent)
+      unsigned long long gmn = 0ULL, gmx = 0ULL;
+      if (KEY64) {
+        gmn = mmS[p].mn;
+        gmx = mmS[p].mx;
+      } else {
+        const double cb = colS[gc].base;
+        const uint32_t kmin = r[kTKmin], kmax = r[kTKmax];
+        if (kmin) {
+          const uint32_t k = ~kmin;
+          gmn = ~dkey(STORAGE == H2OT_STORE_F32 ? (double)fkey_inv(k) : cb + (double)(k - 1u));
+        }
+        if (kmax) gmx = dkey(STORAGE == H2OT_STORE_F32 ? (double)fkey_inv(kmax) : cb + (double)(kmax - 1u));
+      }
+      unsigned long long* mm = a.minmax + lc * 2;
+      if (gmn) atomicMax(mm, gmn);
+      if (gmx) atomicMax(mm + 1, gmx);
     }
   }
 }
