@@ -104,7 +104,7 @@ ENGINE_SYMBOLS = [
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
     "h2ot_init_model", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
-    "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_set_tree",
+    "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_hist_column_noalloc",
@@ -150,6 +150,7 @@ def load():
     L.h2ot_allreduce_level.argtypes = [vp, i32]
     L.h2ot_finish_level.argtypes = [vp, i32, vp, i64, vp, vp, vp, vp, vp]
     L.h2ot_find_splits.argtypes = [vp, i32, dbl, dbl, vp]
+    L.h2ot_level_step.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp, dbl, dbl, vp, vp, vp, vp, vp]
     L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
     L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
     L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]

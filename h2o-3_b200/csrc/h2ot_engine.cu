@@ -85,9 +85,15 @@ struct TreeState {  // per class-tree k
   DBuf<GroupDev> d_groups;
   DBuf<long long> d_sums;  // [3*total_bins | L leaf_rows]
   DBuf<unsigned long long> d_minmax;
-  DBuf<double> d_vals, d_min2, d_maxIn, d_wna;
-  DBuf<uint8_t> d_has;
-  DBuf<h2ot_split> d_cand, d_best;
+  DBuf<double> d_vals;
+  // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
+  // [min2 | maxIn | wNA : LC doubles each][best split per leaf][has_vals : LC bytes]
+  DBuf<unsigned char> d_pack;
+  double *p_min2 = nullptr, *p_maxIn = nullptr, *p_wna = nullptr;
+  h2ot_split* p_best = nullptr;
+  uint8_t* p_has = nullptr;
+  size_t pack_bytes = 0;
+  DBuf<h2ot_split> d_cand;
   DBuf<long long> d_gamma;
   DBuf<float> d_pred;
   int max_split_nbin = 0;
@@ -126,6 +132,7 @@ struct h2ot_engine {
   double* w = nullptr;
   double* off = nullptr;
   double* resp_staging = nullptr;
+  double* staging_all = nullptr;
   double w_max = 1.0;
   bool frame_final = false;
   std::vector<TreeState> ts;
@@ -138,6 +145,10 @@ struct h2ot_engine {
   DBuf<RollupDev> d_rollup;
   h2ot_stats stats{};
   std::vector<Timer> timers;
+  std::vector<cudaEvent_t> event_pool;
+  bool defer_sync = false;
+  unsigned char* stage = nullptr;  // pinned host staging of h2ot_level_step
+  size_t stage_cap = 0;
   int hist_mode = 0;
   int smem_budget_kb = 0;  // 0: automatic
   Nccl nccl;
@@ -166,8 +177,14 @@ int check(h2ot_engine* h) {
 
 int t_begin(h2ot_engine* h, double* acc) {
   Timer t;
-  CUDA_TRY(cudaEventCreate(&t.a));
-  CUDA_TRY(cudaEventCreate(&t.b));
+  for (cudaEvent_t* e : {&t.a, &t.b}) {
+    if (!h->event_pool.empty()) {
+      *e = h->event_pool.back();
+      h->event_pool.pop_back();
+    } else {
+      CUDA_TRY(cudaEventCreate(e));
+    }
+  }
   t.acc = acc;
   CUDA_TRY(cudaEventRecord(t.a, h->stream));
   h->timers.push_back(t);
@@ -179,12 +196,13 @@ int t_end(h2ot_engine* h) {
 }
 // synchronise the stream and fold the per-family event times into the stats
 int finish_call(h2ot_engine* h) {
+  if (h->defer_sync) return H2OT_OK;  // inside h2ot_level_step: one synchronisation at the end of the whole level
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   for (Timer& t : h->timers) {
     float ms = 0;
     if (t.a && t.b && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) *t.acc += ms;
-    if (t.a) cudaEventDestroy(t.a);
-    if (t.b) cudaEventDestroy(t.b);
+    if (t.a) h->event_pool.push_back(t.a);
+    if (t.b) h->event_pool.push_back(t.b);
   }
   h->timers.clear();
   CUDA_TRY(cudaGetLastError());
@@ -295,10 +313,12 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   // opt in to the large dynamic shared memory carve-out once
 #define H2OT_OPTIN(ST)                                                                                                                      \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));   \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
   H2OT_OPTIN(H2OT_STORE_F32);
   H2OT_OPTIN(H2OT_STORE_F64);
   H2OT_OPTIN(H2OT_STORE_U8);
@@ -321,8 +341,8 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->nccl.comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->nccl.comm);
   for (Column& c : h->cols) {
     if (c.data) cudaFree(c.data);
-    if (c.staging) cudaFree(c.staging);
   }
+  if (h->staging_all) cudaFree(h->staging_all);
   if (h->resp) cudaFree(h->resp);
   if (h->w) cudaFree(h->w);
   if (h->off) cudaFree(h->off);
@@ -332,11 +352,13 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.nids) cudaFree(t.nids);
     if (t.code) cudaFree(t.code);
     t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release(); t.d_group_cols.release();
-    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_min2.release(); t.d_maxIn.release(); t.d_wna.release();
-    t.d_has.release(); t.d_cand.release(); t.d_best.release(); t.d_gamma.release(); t.d_pred.release();
+    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_pack.release();
+    t.d_cand.release(); t.d_gamma.release(); t.d_pred.release();
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
   h->d_rollup.release(); h->d_cols.release();
+  for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
+  if (h->stage) cudaFreeHost(h->stage);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return H2OT_OK;
@@ -354,10 +376,12 @@ int h2ot_load_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, const
   if (col < 0 || col >= h->C) H2OT_FAIL(H2OT_ERR_INVALID, "column index out of range");
   if (h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame already finalized");
   Column& c = h->cols[col];
-  if (!c.staging) {
-    CUDA_TRY(cudaMalloc(&c.staging, (size_t)h->n * sizeof(double)));
-    CUDA_TRY(cudaMemsetAsync(c.staging, 0xFF, (size_t)h->n * sizeof(double), h->stream));  // unloaded rows are NA
+  if (!h->staging_all) {  // one staging area for the whole frame (freed by h2ot_finalize_frame); unloaded rows are NA
+    const size_t bytes = (size_t)h->C * (size_t)h->n * sizeof(double);
+    CUDA_TRY(cudaMalloc(&h->staging_all, bytes));
+    CUDA_TRY(cudaMemsetAsync(h->staging_all, 0xFF, bytes, h->stream));
   }
+  c.staging = h->staging_all + (size_t)col * (size_t)h->n;
   return load_rows(h, c.staging, row0, n, values);
 }
 int h2ot_load_response(h2ot_engine* h, int64_t row0, int64_t n, const double* values) {
@@ -375,25 +399,31 @@ int h2ot_load_offset(h2ot_engine* h, int64_t row0, int64_t n, const double* valu
   return load_rows(h, h->off, row0, n, values);
 }
 
-static int rollup(h2ot_engine* h, const double* v, RollupDev* out) {
-  CUDA_TRY(cudaMemsetAsync(h->d_rollup.p, 0, sizeof(RollupDev), h->stream));
-  rollup_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(v, h->n, h->d_rollup.p);
-  h->stats.launches++;
-  CUDA_TRY(cudaMemcpyAsync(out, h->d_rollup.p, sizeof(RollupDev), cudaMemcpyDeviceToHost, h->stream));
-  CUDA_TRY(cudaStreamSynchronize(h->stream));
-  return H2OT_OK;
-}
-
 int h2ot_finalize_frame(h2ot_engine* h) {
   CHECK_ENGINE(h);
   if (h->frame_final) return H2OT_OK;
   TRY(t_begin(h, &h->stats.ms_ingest));
-  std::vector<ColRef> refs(h->C);
-  for (int ci = 0; ci < h->C; ci++) {
+  const int C = h->C;
+  for (int ci = 0; ci < C; ci++)
+    if (!h->cols[ci].staging) H2OT_FAIL(H2OT_ERR_INVALID, "column " + std::to_string(ci) + " was never loaded");
+  // rollups of every column (+ the weights), one round trip
+  TRY(h->d_rollup.ensure((size_t)C + 1));
+  CUDA_TRY(cudaMemsetAsync(h->d_rollup.p, 0, ((size_t)C + 1) * sizeof(RollupDev), h->stream));
+  for (int ci = 0; ci < C; ci++) {
+    rollup_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->cols[ci].staging, h->n, h->d_rollup.p + ci);
+    h->stats.launches++;
+  }
+  if (h->w) {
+    rollup_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->w, h->n, h->d_rollup.p + C);
+    h->stats.launches++;
+  }
+  std::vector<RollupDev> ru((size_t)C + 1);
+  CUDA_TRY(cudaMemcpyAsync(ru.data(), h->d_rollup.p, ru.size() * sizeof(RollupDev), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  std::vector<ColRef> refs(C);
+  for (int ci = 0; ci < C; ci++) {
     Column& c = h->cols[ci];
-    if (!c.staging) H2OT_FAIL(H2OT_ERR_INVALID, "column " + std::to_string(ci) + " was never loaded");
-    RollupDev r;
-    TRY(rollup(h, c.staging, &r));
+    const RollupDev& r = ru[ci];
     c.info.nacnt = (int64_t)r.nacnt;
     const bool any = r.max_key != 0;
     c.info.min = any ? dkey_inv(~r.min_key) : NAN;
@@ -413,9 +443,6 @@ int h2ot_finalize_frame(h2ot_engine* h) {
     CUDA_TRY(cudaMalloc(&c.data, (size_t)h->n_pad * esz));
     encode_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(c.staging, h->n, h->n_pad, storage, base, c.data);
     h->stats.launches++;
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
-    CUDA_TRY(cudaFree(c.staging));
-    c.staging = nullptr;
     c.finalized = true;
     refs[ci].data = c.data;
     refs[ci].base = base;
@@ -424,14 +451,17 @@ int h2ot_finalize_frame(h2ot_engine* h) {
   }
   CUDA_TRY(cudaMemcpyAsync(h->d_cols.p, refs.data(), refs.size() * sizeof(ColRef), cudaMemcpyHostToDevice, h->stream));
   if (h->w) {
-    RollupDev r;
-    TRY(rollup(h, h->w, &r));
+    const RollupDev& r = ru[C];
     h->w_max = r.max_key ? std::max(dkey_inv(r.max_key), -dkey_inv(~r.min_key)) : 1.0;
     if (!(h->w_max > 0)) h->w_max = 1.0;
   }
   TRY(t_end(h));
   h->frame_final = true;
-  return finish_call(h);
+  TRY(finish_call(h));
+  for (Column& c : h->cols) c.staging = nullptr;
+  CUDA_TRY(cudaFree(h->staging_all));
+  h->staging_all = nullptr;
+  return H2OT_OK;
 }
 
 int h2ot_column_info_get(h2ot_engine* h, int32_t col, h2ot_column_info* out) {
@@ -822,13 +852,15 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     ha.n_slices = (int)std::min<int64_t>(std::max(1, h->sm_count / ng), std::max<int64_t>(1, n_tiles));
     const int grid = ng * ha.n_slices;
     const size_t sm = t.smem_bytes;
-#define H2OT_LAUNCH_HIST(ST)                                                                                 \
-  if (h->w) {                                                                                                \
-    if (t.any_checkfloat) hist_smem_kernel<7, true, ST, true><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
-    else hist_smem_kernel<7, true, ST, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
-  } else {                                                                                                   \
-    if (t.any_checkfloat) hist_smem_kernel<5, false, ST, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
-    else hist_smem_kernel<5, false, ST, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                   \
+#define H2OT_LAUNCH_HIST(ST)                                                                                         \
+  if (h->w) {                                                                                                        \
+    if (t.any_checkfloat) hist_smem_kernel<7, true, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
+    else if (n_leaves == 1) hist_smem_kernel<7, true, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
+    else hist_smem_kernel<7, true, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
+  } else {                                                                                                           \
+    if (t.any_checkfloat) hist_smem_kernel<5, false, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
+    else if (n_leaves == 1) hist_smem_kernel<5, false, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);  \
+    else hist_smem_kernel<5, false, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
   }
     switch (st) {
       case H2OT_STORE_F32: H2OT_LAUNCH_HIST(H2OT_STORE_F32); break;
@@ -904,10 +936,16 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
   const size_t LC = (size_t)t.L * h->C;
   TRY(t.d_vals.ensure(std::max<int64_t>(1, t.total_vals)));
-  TRY(t.d_min2.ensure(LC));
-  TRY(t.d_maxIn.ensure(LC));
-  TRY(t.d_has.ensure(LC));
-  TRY(t.d_wna.ensure(LC));
+  {
+    const size_t o_best = 3 * LC * sizeof(double), o_has = o_best + (size_t)t.L * sizeof(h2ot_split);
+    t.pack_bytes = o_has + LC;
+    TRY(t.d_pack.ensure(t.pack_bytes));
+    t.p_min2 = reinterpret_cast<double*>(t.d_pack.p);
+    t.p_maxIn = t.p_min2 + LC;
+    t.p_wna = t.p_maxIn + LC;
+    t.p_best = reinterpret_cast<h2ot_split*>(t.d_pack.p + o_best);
+    t.p_has = t.d_pack.p + o_has;
+  }
   FinalizeArgs fa{};
   fa.L = t.L;
   fa.C = h->C;
@@ -916,10 +954,10 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   fa.minmax = t.d_minmax.p;
   fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3);
   fa.vals = t.d_vals.p;
-  fa.min2 = t.d_min2.p;
-  fa.maxIn = t.d_maxIn.p;
-  fa.has_vals = t.d_has.p;
-  fa.wna = t.d_wna.p;
+  fa.min2 = t.p_min2;
+  fa.maxIn = t.p_maxIn;
+  fa.has_vals = t.p_has;
+  fa.wna = t.p_wna;
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
   fa.inv_sy = std::ldexp(1.0, -t.ey);
@@ -933,10 +971,10 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
     if (out_vals_capacity < t.total_vals) H2OT_FAIL(H2OT_ERR_INVALID, "out_vals too small: need " + std::to_string(t.total_vals) + " doubles");
     TRY(d2h(h, out_vals, t.d_vals.p, (size_t)t.total_vals * sizeof(double)));
   }
-  if (out_min2) TRY(d2h(h, out_min2, t.d_min2.p, LC * sizeof(double)));
-  if (out_maxIn) TRY(d2h(h, out_maxIn, t.d_maxIn.p, LC * sizeof(double)));
-  if (out_wNA) TRY(d2h(h, out_wNA, t.d_wna.p, LC * sizeof(double)));
-  if (out_has_vals) TRY(d2h(h, out_has_vals, t.d_has.p, LC));
+  if (out_min2) TRY(d2h(h, out_min2, t.p_min2, LC * sizeof(double)));
+  if (out_maxIn) TRY(d2h(h, out_maxIn, t.p_maxIn, LC * sizeof(double)));
+  if (out_wNA) TRY(d2h(h, out_wNA, t.p_wna, LC * sizeof(double)));
+  if (out_has_vals) TRY(d2h(h, out_has_vals, t.p_has, LC));
   if (out_val_offsets)
     for (size_t i = 0; i < LC; i++) out_val_offsets[i] = t.h_descs[i].nbin >= 0 ? t.h_descs[i].voff : -1;
   t.finished = true;
@@ -950,20 +988,57 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   if (!t.finished) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_finish_level must run before h2ot_find_splits");
   const size_t LC = (size_t)t.L * h->C;
   TRY(t.d_cand.ensure(LC));
-  TRY(t.d_best.ensure(t.L));
   const size_t n1 = (size_t)t.max_split_nbin + 1;
   size_t smem = 8 * 9 * n1;
   if (t.any_cat) smem += 8 * (3 * n1 + n1) + 4 * n1;
   if (smem > (size_t)h->split_smem_max) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
   if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
-  SplitArgs sa{t.L, h->C, t.d_descs.p, t.d_vals.p, t.d_min2.p, t.d_maxIn.p, t.d_has.p, min_rows, min_split_improvement, t.d_cand.p};
+  SplitArgs sa{t.L, h->C, t.d_descs.p, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p};
   TRY(t_begin(h, &h->stats.ms_split));
   find_split_kernel<<<(unsigned)LC, kSplitThreads, smem, h->stream>>>(sa);
-  best_col_kernel<<<(t.L + 63) / 64, 64, 0, h->stream>>>(t.L, h->C, t.d_descs.p, t.d_hdescs.p, t.d_cand.p, t.d_best.p);
+  best_col_kernel<<<(t.L + 63) / 64, 64, 0, h->stream>>>(t.L, h->C, t.d_descs.p, t.d_hdescs.p, t.d_cand.p, t.p_best);
   h->stats.launches += 2;
   TRY(t_end(h));
-  if (out_splits) TRY(d2h(h, out_splits, t.d_best.p, (size_t)t.L * sizeof(h2ot_split)));
+  if (out_splits) TRY(d2h(h, out_splits, t.p_best, (size_t)t.L * sizeof(h2ot_split)));
   return finish_call(h);
+}
+
+int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                    const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes, const h2ot_hist_desc* descs,
+                    double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
+                    uint8_t* out_has_vals, h2ot_split* out_splits) {
+  CHECK_ENGINE(h);
+  h->defer_sync = true;
+  int rc = h2ot_build_level(h, k, leaf_offset, n_leaves, n_decided, decided, bitset_pool, bitset_bytes, descs);
+  if (rc == H2OT_OK) rc = h2ot_allreduce_level(h, k);
+  if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
+  if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
+  TreeState& t = h->ts[k];
+  if (rc == H2OT_OK && t.pack_bytes > h->stage_cap) {  // pinned staging for the packed results (grow-only)
+    if (h->stage) cudaFreeHost(h->stage);
+    h->stage = nullptr;
+    h->stage_cap = 0;
+    const size_t want = std::max<size_t>(t.pack_bytes * 2, 1 << 20);
+    if (cudaMallocHost(&h->stage, want) != cudaSuccess) {
+      set_error("cudaMallocHost failed for the level result staging buffer");
+      rc = H2OT_ERR_NOMEM;
+    } else {
+      h->stage_cap = want;
+    }
+  }
+  if (rc == H2OT_OK) rc = d2h(h, h->stage, t.d_pack.p, t.pack_bytes);
+  h->defer_sync = false;
+  const int rs = finish_call(h);  // also drains the stream after a failed stage
+  if (rc != H2OT_OK) return rc;
+  if (rs != H2OT_OK) return rs;
+  const size_t LC = (size_t)t.L * h->C;
+  const unsigned char* sp = h->stage;
+  if (out_min2) memcpy(out_min2, sp, LC * sizeof(double));
+  if (out_maxIn) memcpy(out_maxIn, sp + LC * sizeof(double), LC * sizeof(double));
+  if (out_wNA) memcpy(out_wNA, sp + 2 * LC * sizeof(double), LC * sizeof(double));
+  if (out_splits) memcpy(out_splits, sp + 3 * LC * sizeof(double), (size_t)t.L * sizeof(h2ot_split));
+  if (out_has_vals) memcpy(out_has_vals, sp + 3 * LC * sizeof(double) + (size_t)t.L * sizeof(h2ot_split), LC);
+  return H2OT_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ end of tree
@@ -988,7 +1063,10 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
   ga.family = h->cfg.family;
   ga.leaf_start = leaf_start;
   ga.n_leaf_nodes = n_leaf_nodes;
-  ga.rows_per_cta = 65536;
+  {  // enough CTAs to fill the GPU; at most 2^16 rows per CTA partial (the fixed-point split below assumes it)
+    const int64_t per = (h->n + (int64_t)h->sm_count * 8 - 1) / ((int64_t)h->sm_count * 8);
+    ga.rows_per_cta = (int32_t)std::min<int64_t>(65536, std::max<int64_t>(2048, (per + 255) / 256 * 256));
+  }
   ga.resp = h->resp;
   ga.w = h->w;
   ga.work = t.work;

@@ -442,8 +442,6 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     to_device_node(tree.ns[nid], dn.back(), pool);
   }
   tree.dirty.clear();
-  GTRY(h2ot_build_level(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data()));
-  if (g->world > 1) GTRY(h2ot_allreduce_level(g->eng, k));
   const size_t LC = (size_t)L * C;
   g->min2.resize(LC);
   g->max_in.resize(LC);
@@ -451,6 +449,8 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
   g->has.resize(LC);
   g->splits.resize(L);
   if (g->capture) {
+    GTRY(h2ot_build_level(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data()));
+    if (g->world > 1) GTRY(h2ot_allreduce_level(g->eng, k));
     Capture cap;
     cap.tree = g->ntrees_built;
     cap.k = k;
@@ -470,10 +470,12 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     cap.nids.resize((size_t)g->nrows);
     GTRY(h2ot_get_nids(g->eng, k, cap.nids.data()));
     g->captures.push_back(std::move(cap));
+    GTRY(h2ot_find_splits(g->eng, k, g->p.min_rows, g->p.min_split_improvement, g->splits.data()));
   } else {
-    GTRY(h2ot_finish_level(g->eng, k, nullptr, 0, nullptr, g->min2.data(), g->max_in.data(), g->w_na.data(), g->has.data()));
+    GTRY(h2ot_level_step(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data(),
+                         g->p.min_rows, g->p.min_split_improvement, g->min2.data(), g->max_in.data(), g->w_na.data(), g->has.data(),
+                         g->splits.data()));
   }
-  GTRY(h2ot_find_splits(g->eng, k, g->p.min_rows, g->p.min_split_improvement, g->splits.data()));
   g->timing.level_s += now_s() - t0;
   g->timing.levels++;
   int64_t ncol_active = 0;

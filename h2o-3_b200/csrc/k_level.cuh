@@ -217,21 +217,40 @@ __device__ __forceinline__ void red_max_if_gt(uint32_t addr, uint32_t v, uint32_
 // the atomics grouped by word (the carries out of the low words are consumed last). Rows that take no part (skip code,
 // no histogram for the pair) are steered to a per-lane sink bin instead of branching around the atomics.
 // x: values as doubles; na: NA mask; key: order-preserving 32-bit keys (unused when KEY64).
-template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, int J0, int R>
-__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, const int (&leaf)[4],
+struct RecRegs {  // one descriptor record in registers (root level: the same record serves every row of a column)
+  uint32_t place, kmin, kmax;
+  int nbin;
+  double mn, st;
+};
+__device__ __forceinline__ RecRegs load_rec(uint32_t rec) {
+  RecRegs r;
+  r.place = lds_u32(rec + kTPlace * 4);
+  r.nbin = (int)lds_u32(rec + kTNbin * 4);
+  r.mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
+  r.st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
+  r.kmin = lds_u32(rec + kTKmin * 4);
+  r.kmax = lds_u32(rec + kTKmax * 4);
+  return r;
+}
+
+template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, int J0, int R>
+__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, const RecRegs& shared_rec,
+                                           const int (&leaf)[4],
                                            const double (&x)[4], const bool (&na)[4], const uint32_t (&key)[4],
                                            const long long (&qw)[4], const long long (&qy)[4], const long long (&qyy)[4]) {
   uint32_t wd[4];
 #pragma unroll
   for (int j = J0; j < J0 + R; j++) {
     const bool row_on = leaf[j] != kSkipCode;
-    const int p = pbase + (row_on ? leaf[j] : 0);
+    const int p = pbase + ((row_on && !ONE_LEAF) ? leaf[j] : 0);
     const uint32_t rec = tab_a + (uint32_t)p * (kTStride * 4);
-    const uint32_t place = lds_u32(rec + kTPlace * 4);
+    RecRegs rr;
+    if (ONE_LEAF) rr = shared_rec;
+    else rr = load_rec(rec);
+    const uint32_t place = rr.place;
     const uint32_t on = (row_on && place != kInactive) ? 1u : 0u;
-    const int nbin = (int)lds_u32(rec + kTNbin * 4);
-    const double mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
-    const double st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
+    const int nbin = rr.nbin;
+    const double mn = rr.mn, st = rr.st;
     int b;
     if (CHECKFLOAT) b = bin_of(x[j], mn, st, nbin, true);
     else b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
@@ -245,8 +264,8 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
       }
     } else {
       const uint32_t live = (on && !na[j]) ? 1u : 0u;
-      red_max_if_gt(rec + kTKmin * 4, ~key[j], lds_u32(rec + kTKmin * 4), live);
-      red_max_if_gt(rec + kTKmax * 4, key[j], lds_u32(rec + kTKmax * 4), live);
+      red_max_if_gt(rec + kTKmin * 4, ~key[j], rr.kmin, live);
+      red_max_if_gt(rec + kTKmax * 4, key[j], rr.kmax, live);
     }
     wd[j] = on ? hist_a + (place + (uint32_t)(b * WPB)) * 4u : sink_a;
   }
@@ -279,7 +298,7 @@ constexpr int kItemsInFlight = H2OT_ITEMS_IN_FLIGHT;  // rows of a thread whose 
 //   unit weights (WPB 5): [cnt, wY.lo, wY.hi, wYY.lo, wYY.hi]
 //   weighted     (WPB 7): [w.lo, w.hi, wY.lo, wY.hi, wYY.lo, wYY.hi, pad]
 // followed by 32 sink bins (one per lane) that swallow the adds of rows taking no part.
-template <int WPB, bool HAS_W, int STORAGE, bool CHECKFLOAT>
+template <int WPB, bool HAS_W, int STORAGE, bool CHECKFLOAT, bool ONE_LEAF>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr bool KEY64 = STORAGE == H2OT_STORE_F64;
@@ -390,9 +409,11 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
 #pragma unroll
         for (int j = 0; j < 4; j++) na[j] = isnan(x[j]);
       }
-      hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, leaf, x, na, key, qw, qy, qyy);
+      RecRegs rec0{};
+      if (ONE_LEAF) rec0 = load_rec(tab_a + (uint32_t)pbase * (kTStride * 4));  // root level: one record per column
+      hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
       if (kItemsInFlight < 4)
-        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, leaf, x, na, key, qw, qy, qyy);
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
     }
   }
   __syncthreads();

@@ -196,6 +196,15 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
  * on the histograms of the level just finished. out_splits[n_leaves]. */
 int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_split_improvement, h2ot_split* out_splits);
 
+/* The whole level in one call and ONE host synchronisation: h2ot_build_level, h2ot_allreduce_level (no-op on one rank),
+ * h2ot_finish_level (without the histogram download) and h2ot_find_splits back to back on the engine's stream. What a
+ * caller that lets the device search the splits uses (host_gbm.cpp); the separate calls remain for callers that want the
+ * histograms themselves (the minimal drop-in of INTEGRATION.md section 2, step 3a). */
+int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                    const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes, const h2ot_hist_desc* descs,
+                    double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
+                    uint8_t* out_has_vals, h2ot_split* out_splits);
+
 /* ---- end of tree */
 /* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */
 int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,
