@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <vector>
 
@@ -107,6 +108,7 @@ struct Nccl {
   void* lib = nullptr;
   void* comm = nullptr;
   int world = 1, rank = 0;
+  bool shared = false;  // the communicator belongs to the process-wide table (never destroyed by an engine)
   int (*GetUniqueId)(void*) = nullptr;
   int (*CommInitRank)(void**, int, IdByValue, int) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
@@ -338,7 +340,7 @@ int h2ot_destroy(h2ot_engine* h) {
   if (!h) return H2OT_OK;
   cudaSetDevice(h->cfg.device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  if (h->nccl.comm && h->nccl.CommDestroy) h->nccl.CommDestroy(h->nccl.comm);
+  if (h->nccl.comm && h->nccl.CommDestroy && !h->nccl.shared) h->nccl.CommDestroy(h->nccl.comm);
   for (Column& c : h->cols) {
     if (c.data) cudaFree(c.data);
   }
@@ -1141,16 +1143,34 @@ int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]) {
   return H2OT_OK;
 }
 
+// A NCCL unique id can start exactly one communicator, so communicators are kept per process and keyed by their id:
+// every engine created with the same id (successive model builds of one job) shares the communicator. They live until
+// the process exits.
+static std::mutex g_comm_mutex;
+static std::map<std::string, void*> g_comms;
+
 int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]) {
   CHECK_ENGINE(h);
   if (world_size < 1 || rank < 0 || rank >= world_size) H2OT_FAIL(H2OT_ERR_INVALID, "bad world size / rank");
   h->nccl.world = world_size;
   h->nccl.rank = rank;
   if (world_size == 1) return H2OT_OK;
+  if (!id) H2OT_FAIL(H2OT_ERR_INVALID, "null communicator id");
   TRY(nccl_load(h->nccl));
+  std::lock_guard<std::mutex> lock(g_comm_mutex);
+  const std::string key(reinterpret_cast<const char*>(id), H2OT_COMM_ID_BYTES);
+  auto it = g_comms.find(key + ":" + std::to_string(h->cfg.device));
+  if (it != g_comms.end()) {
+    h->nccl.comm = it->second;
+    h->nccl.shared = true;
+    return H2OT_OK;
+  }
   IdByValue v;
   memcpy(v.internal, id, H2OT_COMM_ID_BYTES);
-  return nccl_check(h, h->nccl.CommInitRank(&h->nccl.comm, world_size, v, rank), "ncclCommInitRank");
+  TRY(nccl_check(h, h->nccl.CommInitRank(&h->nccl.comm, world_size, v, rank), "ncclCommInitRank"));
+  h->nccl.shared = true;
+  g_comms[key + ":" + std::to_string(h->cfg.device)] = h->nccl.comm;
+  return H2OT_OK;
 }
 
 int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op) {

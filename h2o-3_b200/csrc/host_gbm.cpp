@@ -815,7 +815,7 @@ int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* ou
       o.se = s.se; o.se0 = s.se0; o.se1 = s.se1; o.n0 = s.n0; o.n1 = s.n1; o.p0 = s.p0; o.p1 = s.p1;
       o.tree_p0 = s.tree_p0; o.tree_p1 = s.tree_p1;
       o.bs_nbits = s.bs_nbits; o.bs_bitoff = s.bs_bitoff; o.bs_nbytes = s.bs_nbytes;
-      memcpy(o.bs, s.bs, sizeof(o.bs));
+      memcpy(o.bs, s.bs, (size_t)std::max(0, std::min<int>(s.bs_nbytes, H2OT_MAX_BITSET_BYTES)));  // bytes past bs_nbytes are unspecified
     } else {
       o.col = -1;
     }

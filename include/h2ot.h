@@ -219,6 +219,8 @@ int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_
 /* ---- multi-GPU plumbing (one process per GPU; rows sharded; replaces the MRTask node tree, W/MRTask.java:695-756,871-930) */
 #define H2OT_COMM_ID_BYTES 128
 int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]);
+/* A communicator is created the first time an id is seen in the process and is shared by every later engine that passes
+ * the same id on the same device (an id can start only one NCCL communicator); it lives until the process exits. */
 int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
 int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op /*0 sum, 1 max*/);
 /* max |weight| over the local rows (known after h2ot_finalize_frame). With several ranks the host takes the max over
