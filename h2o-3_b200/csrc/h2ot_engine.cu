@@ -74,8 +74,10 @@ struct TreeState {  // per class-tree k
   bool built = false, finished = false;
   std::vector<DescDev> h_descs;
   std::vector<GroupDev> h_groups;
+  std::vector<double> h_conc;
   std::vector<int32_t> h_group_cols;
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
+  int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
   DBuf<int32_t> d_group_cols;
   int n_smem_groups = 0;
   size_t smem_bytes = 0;
@@ -88,9 +90,9 @@ struct TreeState {  // per class-tree k
   DBuf<unsigned long long> d_minmax;
   DBuf<double> d_vals;
   // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
-  // [min2 | maxIn | wNA : LC doubles each][best split per leaf][has_vals : LC bytes]
+  // [min2 | maxIn | wNA | conc : LC doubles each][best split per leaf][has_vals : LC bytes]
   DBuf<unsigned char> d_pack;
-  double *p_min2 = nullptr, *p_maxIn = nullptr, *p_wna = nullptr;
+  double *p_min2 = nullptr, *p_maxIn = nullptr, *p_wna = nullptr, *p_conc = nullptr;
   h2ot_split* p_best = nullptr;
   uint8_t* p_has = nullptr;
   size_t pack_bytes = 0;
@@ -150,6 +152,7 @@ struct h2ot_engine {
   std::vector<cudaEvent_t> event_pool;
   bool defer_sync = false;
   unsigned char* stage = nullptr;  // pinned host staging of h2ot_level_step
+  std::vector<double> col_conc;    // per column: chance that two rows of the root share a bin (0 until a root level ran)
   size_t stage_cap = 0;
   int hist_mode = 0;
   int smem_budget_kb = 0;  // 0: automatic
@@ -273,6 +276,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   if (const char* s = getenv("H2OT_SMEM_BUDGET_KB")) h->smem_budget_kb = atoi(s);
   CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   h->cols.resize(h->C);
+  h->col_conc.assign(h->C, 0.0);
   h->ts.resize(h->K);
   const size_t np = (size_t)h->n_pad;
   CUDA_TRY(cudaMalloc(&h->resp, np * sizeof(double)));
@@ -729,34 +733,60 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       t.bucket_end[st] = t.bucket_begin[st];
       continue;
     }
-    // greedy count, then even re-split over the same number of groups (keeps the CTAs of one launch balanced)
-    auto pack = [&](size_t target_words, std::vector<std::vector<int>>& out) {
-      out.clear();
-      size_t i = 0;
-      while (i < cols.size()) {
-        std::vector<int> g;
-        size_t words = 0;
-        while (i < cols.size()) {
-          const int c = cols[i];
-          const size_t nw = words + (size_t)col_words[c];
-          if (!g.empty() && (nw * 4 + fixed_bytes((int)g.size() + 1, st) > budget || words >= target_words)) break;
-          words = nw;
-          g.push_back(c);
-          i++;
+    // Cost model: a column's atomics serialise when rows of a warp share a bin; with c = chance that two rows of the
+    // root share a bin (measured by the last root level) and L leaves, cost ~ 1 + 8 c / L (fits the measured 3.6 vs 14
+    // wavefronts per atomic of continuous vs 3-valued columns). Groups: fewest that fit, filled longest-first onto the
+    // cheapest group (LPT); CTAs: shared out in proportion to the group costs so that all CTAs of the launch end together.
+    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / (double)L; };
+    std::vector<int> order(cols);
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost_of(x) > cost_of(y); });
+    size_t total_words = 0;
+    for (int c : cols) total_words += (size_t)col_words[c];
+    std::vector<std::vector<int>> groups;
+    std::vector<double> gcost;
+    for (size_t ng = std::max<size_t>(1, (total_words * 4 + budget - 1) / budget);; ng++) {
+      groups.assign(ng, {});
+      gcost.assign(ng, 0.0);
+      std::vector<size_t> gwords(ng, 0);
+      bool ok = true;
+      for (int c : order) {
+        int best = -1;
+        for (size_t g = 0; g < ng; g++) {
+          if ((gwords[g] + (size_t)col_words[c]) * 4 + fixed_bytes((int)groups[g].size() + 1, st) > budget) continue;
+          if (best < 0 || gcost[g] < gcost[best]) best = (int)g;
         }
-        out.push_back(g);
+        if (best < 0) { ok = false; break; }
+        groups[best].push_back(c);
+        gwords[best] += (size_t)col_words[c];
+        gcost[best] += cost_of(c);
       }
-    };
-    std::vector<std::vector<int>> groups, even;
-    pack(SIZE_MAX, groups);
-    if (groups.size() > 1) {
-      size_t total = 0;
-      for (int c : cols) total += (size_t)col_words[c];
-      pack((total + groups.size() - 1) / groups.size(), even);
-      if (even.size() <= groups.size()) groups = even;
+      if (ok) break;
+      if (ng > cols.size()) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "cannot place the level's histograms in shared memory");
     }
-    for (const std::vector<int>& g : groups) {
-      GroupDev gd{(int32_t)t.h_group_cols.size(), (int32_t)g.size(), 0, 0, st, 0};
+    double cost_sum = 0;
+    for (double v : gcost) cost_sum += v;
+    int cta = 0;
+    const int n_ctas = std::max<int>(h->sm_count, (int)groups.size());
+    std::vector<int> slices(groups.size(), 1);
+    {
+      int used = 0;
+      for (size_t g = 0; g < groups.size(); g++) {
+        slices[g] = std::max(1, (int)std::floor(n_ctas * gcost[g] / cost_sum));
+        used += slices[g];
+      }
+      // hand the remaining CTAs to the groups with the highest cost per CTA
+      for (; used < n_ctas; used++) {
+        size_t best = 0;
+        for (size_t g = 1; g < groups.size(); g++)
+          if (gcost[g] / slices[g] > gcost[best] / slices[best]) best = g;
+        slices[best]++;
+      }
+    }
+    for (size_t gi = 0; gi < groups.size(); gi++) {
+      std::vector<int>& g = groups[gi];
+      std::sort(g.begin(), g.end());
+      GroupDev gd{(int32_t)t.h_group_cols.size(), (int32_t)g.size(), 0, 0, st, slices[gi], cta, 0};
+      cta += slices[gi];
       int off = 0;
       for (int c : g) {
         t.h_group_cols.push_back(c);
@@ -771,11 +801,12 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       t.smem_bytes = std::max(t.smem_bytes, fixed_bytes((int)g.size(), st) + (size_t)off * 4);
       t.h_groups.push_back(gd);
     }
+    t.bucket_ctas[st] = cta;
     t.bucket_end[st] = (int)t.h_groups.size();
   }
   t.n_smem_groups = (int)t.h_groups.size();
   for (int c : glob_cols) {
-    t.h_groups.push_back(GroupDev{(int32_t)t.h_group_cols.size(), 1, 0, 1, h->cols[c].storage, 0});
+    t.h_groups.push_back(GroupDev{(int32_t)t.h_group_cols.size(), 1, 0, 1, h->cols[c].storage, 1, 0, 0});
     t.h_group_cols.push_back(c);
   }
   return H2OT_OK;
@@ -851,8 +882,9 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     if (ng <= 0) continue;
     ha.group_begin = t.bucket_begin[st];
     ha.n_groups = ng;
-    ha.n_slices = (int)std::min<int64_t>(std::max(1, h->sm_count / ng), std::max<int64_t>(1, n_tiles));
-    const int grid = ng * ha.n_slices;
+    ha.n_slices = 0;  // per group: GroupDev::n_slices
+    const int grid = t.bucket_ctas[st];
+    (void)n_tiles;
     const size_t sm = t.smem_bytes;
 #define H2OT_LAUNCH_HIST(ST)                                                                                         \
   if (h->w) {                                                                                                        \
@@ -939,12 +971,13 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   const size_t LC = (size_t)t.L * h->C;
   TRY(t.d_vals.ensure(std::max<int64_t>(1, t.total_vals)));
   {
-    const size_t o_best = 3 * LC * sizeof(double), o_has = o_best + (size_t)t.L * sizeof(h2ot_split);
+    const size_t o_best = 4 * LC * sizeof(double), o_has = o_best + (size_t)t.L * sizeof(h2ot_split);
     t.pack_bytes = o_has + LC;
     TRY(t.d_pack.ensure(t.pack_bytes));
     t.p_min2 = reinterpret_cast<double*>(t.d_pack.p);
     t.p_maxIn = t.p_min2 + LC;
     t.p_wna = t.p_maxIn + LC;
+    t.p_conc = t.p_wna + LC;
     t.p_best = reinterpret_cast<h2ot_split*>(t.d_pack.p + o_best);
     t.p_has = t.d_pack.p + o_has;
   }
@@ -960,6 +993,7 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   fa.maxIn = t.p_maxIn;
   fa.has_vals = t.p_has;
   fa.wna = t.p_wna;
+  fa.conc = t.p_conc;
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
   fa.inv_sy = std::ldexp(1.0, -t.ey);
@@ -977,10 +1011,18 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   if (out_maxIn) TRY(d2h(h, out_maxIn, t.p_maxIn, LC * sizeof(double)));
   if (out_wNA) TRY(d2h(h, out_wNA, t.p_wna, LC * sizeof(double)));
   if (out_has_vals) TRY(d2h(h, out_has_vals, t.p_has, LC));
+  if (t.L == 1 && !h->defer_sync) {
+    t.h_conc.resize(LC);
+    TRY(d2h(h, t.h_conc.data(), t.p_conc, LC * sizeof(double)));
+  }
   if (out_val_offsets)
     for (size_t i = 0; i < LC; i++) out_val_offsets[i] = t.h_descs[i].nbin >= 0 ? t.h_descs[i].voff : -1;
   t.finished = true;
-  return finish_call(h);
+  TRY(finish_call(h));
+  if (t.L == 1 && !h->defer_sync)
+    for (int c = 0; c < h->C; c++)
+      if (t.h_descs[c].nbin >= 0) h->col_conc[c] = t.h_conc[c];
+  return H2OT_OK;
 }
 
 int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_split_improvement, h2ot_split* out_splits) {
@@ -1038,8 +1080,13 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
   if (out_min2) memcpy(out_min2, sp, LC * sizeof(double));
   if (out_maxIn) memcpy(out_maxIn, sp + LC * sizeof(double), LC * sizeof(double));
   if (out_wNA) memcpy(out_wNA, sp + 2 * LC * sizeof(double), LC * sizeof(double));
-  if (out_splits) memcpy(out_splits, sp + 3 * LC * sizeof(double), (size_t)t.L * sizeof(h2ot_split));
-  if (out_has_vals) memcpy(out_has_vals, sp + 3 * LC * sizeof(double) + (size_t)t.L * sizeof(h2ot_split), LC);
+  if (out_splits) memcpy(out_splits, sp + 4 * LC * sizeof(double), (size_t)t.L * sizeof(h2ot_split));
+  if (out_has_vals) memcpy(out_has_vals, sp + 4 * LC * sizeof(double) + (size_t)t.L * sizeof(h2ot_split), LC);
+  if (t.L == 1) {  // root level: refresh the planner's per-column bin-concentration estimate
+    const double* conc = reinterpret_cast<const double*>(sp + 3 * LC * sizeof(double));
+    for (int c = 0; c < h->C; c++)
+      if (t.h_descs[c].nbin >= 0) h->col_conc[c] = conc[c];
+  }
   return H2OT_OK;
 }
 

@@ -23,6 +23,8 @@ struct GroupDev {
   int32_t smem_words;       // histogram words needed by this group
   int32_t mode;             // 0: shared-memory privatised, 1: global atomics
   int32_t storage;          // H2OT_STORE_* shared by the group's columns
+  int32_t n_slices;         // CTAs working on this group (proportional to its estimated cost)
+  int32_t cta_begin;        // first blockIdx.x of the group inside its launch
   int32_t pad;
 };
 
@@ -302,9 +304,10 @@ template <int WPB, bool HAS_W, int STORAGE, bool CHECKFLOAT, bool ONE_LEAF>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr bool KEY64 = STORAGE == H2OT_STORE_F64;
-  const int g = a.group_begin + blockIdx.x % a.n_groups;
-  const int slice = blockIdx.x / a.n_groups;
+  int g = a.group_begin;
+  while (g + 1 < a.group_begin + a.n_groups && (int)blockIdx.x >= a.groups[g + 1].cta_begin) g++;
   const GroupDev grp = a.groups[g];
+  const int slice = (int)blockIdx.x - grp.cta_begin;
   const int ncg = grp.ncols;
   const int npairs = ncg * a.L;
   MinMaxS* mmS = reinterpret_cast<MinMaxS*>(smem_raw);
@@ -344,7 +347,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   constexpr int kElem = STORAGE == H2OT_STORE_F32 ? 4 : STORAGE == H2OT_STORE_F64 ? 8 : STORAGE == H2OT_STORE_U8 ? 1 : 2;
 
   const int64_t n_tiles = a.n_pad / kTileRows;
-  for (int64_t tile = slice; tile < n_tiles; tile += a.n_slices) {
+  for (int64_t tile = slice; tile < n_tiles; tile += grp.n_slices) {
     const int64_t row = tile * kTileRows + (int64_t)threadIdx.x * kRowsPerThread;
     const ushort4 cd = __ldg(reinterpret_cast<const ushort4*>(a.code + row));
     int leaf[4] = {cd.x, cd.y, cd.z, cd.w};
@@ -537,6 +540,7 @@ struct FinalizeArgs {
   double* maxIn;       // [L*C]
   uint8_t* has_vals;   // [L*C]
   double* wna;         // [L*C] weight of the NA bucket (DHistogram.wNA, T/DHistogram.java:84)
+  double* conc;        // [L*C] sum_b (w_b / sum w)^2 : chance that two rows share a bin (cost model of the atomics), nullable
   double inv_sy, inv_syy, inv_sw;
 };
 
@@ -555,13 +559,33 @@ __global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
     a.maxIn[p] = mx ? dkey_inv(mx) : (intopt ? -2147483648.0 : -DBL_MAX);
     a.wna[p] = has ? __dmul_rn((double)a.acc[(d.gbin + d.nbin) * 3], a.inv_sw) : 0.0;
   }
-  if (!has) return;
+  if (!has) {
+    if (a.conc && threadIdx.x == 0) a.conc[p] = 0.0;
+    return;
+  }
+  double sw = 0, sww = 0;
   for (int b = threadIdx.x; b <= d.nbin; b += blockDim.x) {
     const long long* s = a.acc + (d.gbin + b) * 3;
     double* v = a.vals + d.voff + (size_t)b * 3;
     v[0] = __dmul_rn((double)s[0], a.inv_sw);
     v[1] = (double)(float)__dmul_rn((double)s[1], a.inv_sy);
     v[2] = (double)(float)__dmul_rn((double)s[2], a.inv_syy);
+    sw += (double)s[0];
+    sww += (double)s[0] * (double)s[0];
+  }
+  if (a.conc) {  // not part of the reference: feeds the planner's per-column cost estimate
+    __shared__ double r_w[128], r_ww[128];
+    r_w[threadIdx.x] = sw;
+    r_ww[threadIdx.x] = sww;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+      if ((int)threadIdx.x < o) {
+        r_w[threadIdx.x] += r_w[threadIdx.x + o];
+        r_ww[threadIdx.x] += r_ww[threadIdx.x + o];
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) a.conc[p] = r_w[0] > 0 ? r_ww[0] / (r_w[0] * r_w[0]) : 0.0;
   }
 }
 
