@@ -851,7 +851,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
                reinterpret_cast<unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3)};
   TRY(t_begin(h, &h->stats.ms_score));
-  score_decide_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(sa);
+  score_decide_kernel<<<grid_for(h, h->n_pad / 4, 256, 16), 256, 0, h->stream>>>(sa);
   h->stats.launches++;
   TRY(t_end(h));
 

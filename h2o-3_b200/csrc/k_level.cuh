@@ -64,49 +64,56 @@ __device__ __forceinline__ int child_node_id(const h2ot_decided_node& dn, const 
 
 constexpr int kScoreSmemLeaves = 4096;
 
+// One row of score_decide: returns the leaf-relative id (or -1) and updates nid in place.
+__device__ __forceinline__ int score_row(const ScoreArgs& a, int64_t row, int& nid_io) {
+  int nid = nid_io;
+  if (a.leaf == 0) return (nid == H2OT_DECIDED_ROW) ? -1 : 0;  // OOB rows are histogrammed at the root (q1)
+  if (nid == H2OT_DECIDED_ROW) return -1;
+  const bool oob = nid <= H2OT_OUT_OF_BAG;
+  if (oob) nid = -nid + H2OT_OUT_OF_BAG;
+  h2ot_decided_node dn = a.nodes[nid];
+  if (dn.col < 0) {  // leftover non-split
+    if (dn.pid < 0) return nid - a.leaf;
+    nid = dn.pid;
+    nid_io = oob ? (-nid + H2OT_OUT_OF_BAG) : nid;
+    dn = a.nodes[nid];
+  }
+  nid = child_node_id(dn, a.cols, a.bitsets, row);
+  if (nid != H2OT_DECIDED_ROW) {
+    if (oob) nid = -nid + H2OT_OUT_OF_BAG;  // stays OOB-encoded (negative): skipped below the root
+    nid_io = nid;
+  }
+  return nid - a.leaf;
+}
+
+// Four consecutive rows per thread: 128-bit loads / stores of the nid column, one 64-bit store of the four leaf codes.
 __global__ void __launch_bounds__(256) score_decide_kernel(ScoreArgs a) {
   __shared__ unsigned int s_cnt[kScoreSmemLeaves];
   const bool use_s = a.n_leaves <= kScoreSmemLeaves;
   if (use_s)
     for (int i = threadIdx.x; i < a.n_leaves; i += blockDim.x) s_cnt[i] = 0;
   __syncthreads();
-  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n_pad; row += (int64_t)gridDim.x * blockDim.x) {
-    int res = -1;
-    if (row < a.n) {
-      int nid = a.nids[row];
-      if (a.leaf == 0) {
-        res = (nid == H2OT_DECIDED_ROW) ? -1 : 0;  // OOB rows are histogrammed at the root (q1)
-      } else if (nid == H2OT_DECIDED_ROW) {
-        res = -1;
-      } else {
-        bool oob = nid <= H2OT_OUT_OF_BAG;
-        if (oob) nid = -nid + H2OT_OUT_OF_BAG;
-        h2ot_decided_node dn = a.nodes[nid];
-        bool done = false;
-        if (dn.col < 0) {          // leftover non-split
-          if (dn.pid < 0) { res = nid - a.leaf; done = true; }
-          else {
-            nid = dn.pid;
-            int xnid = oob ? (-nid + H2OT_OUT_OF_BAG) : nid;
-            a.nids[row] = xnid;
-            dn = a.nodes[nid];
-          }
-        }
-        if (!done) {
-          nid = child_node_id(dn, a.cols, a.bitsets, row);
-          if (nid != H2OT_DECIDED_ROW) {
-            if (oob) nid = -nid + H2OT_OUT_OF_BAG;
-            a.nids[row] = nid;
-          }
-          res = nid - a.leaf;
-        }
+  const int64_t nq = a.n_pad / 4;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row0 = q * 4;
+    int4 nv = *reinterpret_cast<const int4*>(a.nids + row0);
+    int nid[4] = {nv.x, nv.y, nv.z, nv.w};
+    const int old[4] = {nv.x, nv.y, nv.z, nv.w};
+    unsigned short code[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      int res = -1;
+      if (row0 + j < a.n) res = score_row(a, row0 + j, nid[j]);
+      const bool in = res >= 0 && res < a.n_leaves;
+      code[j] = in ? (unsigned short)res : (unsigned short)kSkipCode;
+      if (in) {
+        if (use_s) atomicAdd(&s_cnt[res], 1u);
+        else atomicAdd(&a.leaf_rows[res], 1ULL);
       }
     }
-    a.code[row] = (res >= 0 && res < a.n_leaves) ? (uint16_t)res : (uint16_t)kSkipCode;
-    if (res >= 0 && res < a.n_leaves) {
-      if (use_s) atomicAdd(&s_cnt[res], 1u);
-      else atomicAdd(&a.leaf_rows[res], 1ULL);
-    }
+    *reinterpret_cast<ushort4*>(a.code + row0) = make_ushort4(code[0], code[1], code[2], code[3]);
+    if (nid[0] != old[0] || nid[1] != old[1] || nid[2] != old[2] || nid[3] != old[3])
+      *reinterpret_cast<int4*>(a.nids + row0) = make_int4(nid[0], nid[1], nid[2], nid[3]);
   }
   __syncthreads();
   if (use_s)
