@@ -77,7 +77,8 @@ class Stats(C.Structure):
 
 class GbmParams(C.Structure):
     _fields_ = [("ntrees", C.c_int32), ("max_depth", C.c_int32), ("nbins", C.c_int32), ("nbins_cats", C.c_int32),
-                ("nbins_top_level", C.c_int32), ("family", C.c_int32), ("nclass", C.c_int32), ("reserved", C.c_int32),
+                ("nbins_top_level", C.c_int32), ("family", C.c_int32), ("nclass", C.c_int32), ("algo", C.c_int32),
+                ("mtries", C.c_int32), ("pad", C.c_int32),
                 ("min_rows", C.c_double), ("min_split_improvement", C.c_double), ("sample_rate", C.c_double),
                 ("col_sample_rate", C.c_double), ("col_sample_rate_per_tree", C.c_double),
                 ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
@@ -105,7 +106,8 @@ ENGINE_SYMBOLS = [
     "h2ot_init_model", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
-    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
+    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
+    "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_hist_column_noalloc",
 ]
@@ -113,7 +115,7 @@ GBM_SYMBOLS = [
     "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
-    "h2ot_gbm_predictions", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
+    "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
     "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
 ]
 
@@ -154,6 +156,10 @@ def load():
     L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
     L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
     L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]
+    L.h2ot_drf_init_model.argtypes = [vp]
+    L.h2ot_sample.argtypes = [vp, i32, i64, dbl]
+    L.h2ot_drf_collect_preds.argtypes = [vp, i32, i32, vp, i32, i32]
+    L.h2ot_get_oobt.argtypes = [vp, vp]
     L.h2ot_comm_unique_id.argtypes = [vp]
     L.h2ot_comm_init.argtypes = [vp, i32, i32, vp]
     L.h2ot_allreduce_host_f64.argtypes = [vp, vp, i64, i32]
@@ -181,6 +187,7 @@ def load():
     L.h2ot_gbm_tree_nodes.argtypes = [vp, i32, i32, vp]
     L.h2ot_gbm_predictions.argtypes = [vp, i32, vp]
     L.h2ot_gbm_varimp.argtypes = [vp, vp]
+    L.h2ot_gbm_oobt.argtypes = [vp, vp]
     L.h2ot_gbm_timing_get.argtypes = [vp, C.POINTER(GbmTiming)]
     L.h2ot_gbm_engine.argtypes = [vp]
     L.h2ot_gbm_engine.restype = vp
@@ -416,9 +423,10 @@ class GBM:
                  min_split_improvement=1e-5, sample_rate=1.0, col_sample_rate=1.0, col_sample_rate_per_tree=1.0,
                  col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
                  max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
-                 device=0):
+                 device=0, algo=0, mtries=-1):
         self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
-                                nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, reserved=0,
+                                nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, algo=algo,
+                                mtries=mtries, pad=0,
                                 min_rows=min_rows, min_split_improvement=min_split_improvement, sample_rate=sample_rate,
                                 col_sample_rate=col_sample_rate, col_sample_rate_per_tree=col_sample_rate_per_tree,
                                 col_sample_rate_change_per_level=col_sample_rate_change_per_level, learn_rate=learn_rate,
@@ -497,6 +505,11 @@ class GBM:
         _check(self.L.h2ot_gbm_predictions(self.g, k, _p(out)))
         return out
 
+    def oobt(self):
+        out = np.empty(self.nrows, dtype=np.float64)
+        _check(self.L.h2ot_gbm_oobt(self.g, _p(out)))
+        return out
+
     def varimp(self):
         out = np.zeros(self.ncols, dtype=np.float32)
         _check(self.L.h2ot_gbm_varimp(self.g, _p(out)))
@@ -531,3 +544,14 @@ class GBM:
         out = np.empty(self.nrows, dtype=np.int32)
         _check(self.L.h2ot_gbm_capture_nids(self.g, i, _p(out)))
         return out
+
+
+class DRF(GBM):
+    """Distributed random forest on the same engine. Parameter names and defaults follow H2ORandomForestEstimator /
+    DRFModel.DRFParameters (ntrees 50, max_depth 20, min_rows 1, nbins 20, sample_rate 0.632, mtries -1).
+    distribution: "bernoulli" == binomial (one tree per iteration), "multinomial", "gaussian" == regression.
+    predictions(k) holds the summed out-of-bag votes (Tree_k); divide by oobt() to score (T/drf/DRF.java:343-364)."""
+
+    def __init__(self, ntrees=50, max_depth=20, min_rows=1.0, nbins=20, sample_rate=0.632, mtries=-1, **kw):
+        super().__init__(ntrees=ntrees, max_depth=max_depth, min_rows=min_rows, nbins=nbins, sample_rate=sample_rate,
+                         algo=1, mtries=mtries, **kw)

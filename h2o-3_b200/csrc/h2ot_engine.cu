@@ -136,6 +136,7 @@ struct h2ot_engine {
   double* w = nullptr;
   double* off = nullptr;
   double* resp_staging = nullptr;
+  double* oobt = nullptr;  // DRF: OUT_BAG_TREES column
   double* staging_all = nullptr;
   double w_max = 1.0;
   bool frame_final = false;
@@ -352,6 +353,7 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->resp) cudaFree(h->resp);
   if (h->w) cudaFree(h->w);
   if (h->off) cudaFree(h->off);
+  if (h->oobt) cudaFree(h->oobt);
   for (TreeState& t : h->ts) {
     if (t.F) cudaFree(t.F);
     if (t.work) cudaFree(t.work);
@@ -1158,6 +1160,54 @@ int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_
   add_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
   h->stats.launches++;
   TRY(t_end(h));
+  return finish_call(h);
+}
+
+// ------------------------------------------------------------------------------------------------ DRF
+int h2ot_drf_init_model(h2ot_engine* h) {
+  CHECK_ENGINE(h);
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  if (!h->oobt) CUDA_TRY(cudaMalloc(&h->oobt, (size_t)h->n_pad * sizeof(double)));
+  DrfInitArgs a{h->n, h->n_pad, h->K, h->cfg.nclass, h->resp, h->d_Fp.p, h->d_workp.p, h->d_nidsp.p, h->oobt};
+  drf_init_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  return finish_call(h);
+}
+
+int h2ot_sample(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TRY(t_begin(h, &h->stats.ms_sample));
+  sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed, (float)sample_rate,
+                                                               sample_rate, h->resp, h->ts[k].nids);
+  h->stats.launches++;
+  TRY(t_end(h));
+  return finish_call(h);
+}
+
+int h2ot_drf_collect_preds(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, int32_t root_is_leaf, int32_t update_oobt) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (n_nodes <= 0 || !node_pred) H2OT_FAIL(H2OT_ERR_INVALID, "bad node_pred");
+  if (!h->oobt) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_drf_init_model must run first");
+  TreeState& t = h->ts[k];
+  if (!root_is_leaf && t.n_nodes == 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_set_tree must run before h2ot_drf_collect_preds");
+  TRY(t.nodes.ensure(1));
+  TRY(t.bitsets.ensure(16));
+  TRY(t.d_pred.ensure(n_nodes));
+  TRY(h2d(h, t.d_pred.p, node_pred, (size_t)n_nodes * sizeof(float)));
+  CollectArgs a{h->n, n_nodes, root_is_leaf, update_oobt, 0, h->w, t.nids, t.F, h->oobt, t.d_pred.p, t.nodes.p, t.bitsets.p, h->d_cols.p};
+  TRY(t_begin(h, &h->stats.ms_addtree));
+  drf_collect_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  return finish_call(h);
+}
+
+int h2ot_get_oobt(h2ot_engine* h, double* out) {
+  CHECK_ENGINE(h);
+  if (!h->oobt || !out) H2OT_FAIL(H2OT_ERR_INVALID, "no OUT_BAG_TREES column (not a DRF build) or null out");
+  TRY(d2h(h, out, h->oobt, (size_t)h->n * sizeof(double)));
   return finish_call(h);
 }
 

@@ -282,6 +282,8 @@ struct h2ot_gbm {
   std::vector<ColMeta> cols;
   std::vector<double> y, w, off;  // host copies of the O(rows) scalars needed once for init_f
   double init_f = 0;
+  std::vector<double> prior_class_dist;  // DRF classification (Model.Output._priorClassDist)
+  double work_bound = 1.0;               // DRF: max |Work| (fixed for the whole build)
   int mtry = 0, mtry_per_tree = 0;
   Pcg rand{0};
   int ntrees_built = 0;
@@ -310,7 +312,7 @@ bool use_int_opt(const ColMeta& v, const h2ot_gbm_params& p) {
 }
 
 // T/DHistogram.java:474-502
-std::vector<Hist> initial_hist(const h2ot_gbm* g, int nbins, int64_t seed) {
+std::vector<Hist> initial_hist(const h2ot_gbm* g, int nbins, int64_t seed, bool check_float) {
   std::vector<Hist> hs(g->ncols);
   for (int c = 0; c < g->ncols; c++) {
     const ColMeta& v = g->cols[c];
@@ -322,7 +324,7 @@ std::vector<Hist> initial_hist(const h2ot_gbm* g, int nbins, int64_t seed) {
     if (all_na || is_const) continue;
     const uint8_t type = (uint8_t)(v.is_cat ? 2 : (v.is_int ? 1 : 0));
     Hist h;
-    if (make_hist(h, nbins, g->p.nbins_cats, type, min_in, max_ex, use_int_opt(v, g->p), v.nacnt > 0, seed, false)) hs[c] = h;
+    if (make_hist(h, nbins, g->p.nbins_cats, type, min_in, max_ex, use_int_opt(v, g->p), v.nacnt > 0, seed, check_float)) hs[c] = h;
   }
   return hs;
 }
@@ -541,7 +543,7 @@ int build_next_k_trees(h2ot_gbm* g) {
   const int64_t rseed = g->rand.next_long();
   for (int k = 0; k < K; k++) {
     kt[k] = std::make_unique<Tree>(g->ncols, g->mtry, g->mtry_per_tree, rseed, g->p.col_sample_rate_change_per_level);
-    kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed));
+    kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed, false));
     GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, absmax[k]));
   }
   for (int depth = 0; depth < g->p.max_depth; depth++) {
@@ -625,6 +627,79 @@ int build_next_k_trees(h2ot_gbm* g) {
   return H2OT_OK;
 }
 
+// DRF.buildNextKTrees / growTrees / CollectPreds (T/drf/DRF.java:157-330)
+int build_next_k_trees_drf(h2ot_gbm* g) {
+  const int K = g->K;
+  std::vector<std::unique_ptr<Tree>> kt(K);
+  std::vector<int> leaves(K, 0);
+  const int adj_nbins = std::max(g->p.nbins_top_level, g->p.nbins);
+  const int64_t rseed = g->rand.next_long();
+  for (int k = 0; k < K; k++) {
+    kt[k] = std::make_unique<Tree>(g->ncols, g->mtry, g->mtry_per_tree, rseed, g->p.col_sample_rate_change_per_level);
+    kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed, true));  // _checkFloatSplits (:201)
+    GTRY(h2ot_begin_tree(g->eng, k, rseed, 1.0, g->work_bound));
+    GTRY(h2ot_sample(g->eng, k, rseed, g->p.sample_rate));  // always: NA responses go out of bag even at rate 1
+  }
+  for (int depth = 0; depth < g->p.max_depth; depth++) {
+    bool any = false;
+    for (int k = 0; k < K; k++) {
+      bool did = false;
+      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did));
+      any = any || did;
+    }
+    if (!any) break;
+  }
+  const bool classifier = g->nclass > 1;
+  std::vector<FinishedTree> outs(K);
+  for (int k = 0; k < K; k++) {  // leaf insertion with the split's child means (:222-248)
+    Tree& t = *kt[k];
+    const int leaf = leaves[k] = t.len();
+    for (int nid = 0; nid < leaf; nid++) {
+      if (t.ns[nid].kind != 1) continue;
+      if (!t.ns[nid].has_split) {
+        if (nid == 0) {
+          Node n;
+          n.kind = 2;
+          n.pid = kNoParent;
+          n.nid = 0;
+          n.pred = (float)(classifier ? g->prior_class_dist[k] : g->init_f);
+          t.ns[0] = n;
+          t.leaves++;
+        }
+        continue;
+      }
+      for (int i = 0; i < 2; i++) {
+        const int cn = t.ns[nid].nids[i];
+        if (cn == kUndecidedChild || t.ns[cn].kind == 0 || (t.ns[cn].kind == 1 && !t.ns[cn].has_split)) {
+          const int ln = t.new_leaf(nid);
+          t.ns[ln].pred = (float)(i == 0 ? t.ns[nid].split.p0 : t.ns[nid].split.p1);
+          t.ns[nid].nids[i] = ln;
+        }
+      }
+    }
+    const bool root_is_leaf = t.ns[0].kind == 2;
+    if (!root_is_leaf) {
+      std::vector<h2ot_decided_node> dn;
+      std::vector<uint8_t> pool;
+      for (int nid = 0; nid < leaf; nid++)
+        if (t.ns[nid].kind != 2) {  // decided nodes, and undecided ones (chopped for depth) as "no split" records
+          dn.emplace_back();
+          to_device_node(t.ns[nid], dn.back(), pool);
+        }
+      GTRY(h2ot_set_tree(g->eng, k, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size()));
+    }
+    std::vector<float> pred(t.len());
+    for (int i = 0; i < t.len(); i++) pred[i] = t.ns[i].pred;
+    GTRY(h2ot_drf_collect_preds(g->eng, k, t.len(), pred.data(), root_is_leaf ? 1 : 0, k == 0 ? 1 : 0));
+    outs[k].nodes = std::move(t.ns);
+    for (Node& n : outs[k].nodes) n.hs.clear();
+    outs[k].leaves_start = leaves[k];
+  }
+  g->trees.push_back(std::move(outs));
+  g->ntrees_built++;
+  return H2OT_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -635,6 +710,7 @@ int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int
   if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_MULTINOMIAL) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
   if (p->max_depth < 1 || p->nbins < 2 || p->nbins_cats < 2 || p->ntrees < 0) GFAIL(H2OT_ERR_INVALID, "bad tree parameters");
   if (p->nbins_cats > H2OT_MAX_BITSET_BYTES * 8) GFAIL(H2OT_ERR_UNSUPPORTED, "nbins_cats above 4096");
+  if (p->algo != H2OT_ALGO_GBM && p->algo != H2OT_ALGO_DRF) GFAIL(H2OT_ERR_UNSUPPORTED, "unknown algo");
   h2ot_gbm* g = new h2ot_gbm();
   g->p = *p;
   g->nrows = nrows;
@@ -746,9 +822,36 @@ int h2ot_gbm_init(h2ot_gbm* g) {
     GTRY(allreduce(g, &wb, 1, 1));
     GTRY(h2ot_set_weight_bound(g->eng, wb));
   }
-  // GBM.init / initializeModelSpecifics (T/gbm/GBM.java:254-312)
+  // GBM.init / initializeModelSpecifics (T/gbm/GBM.java:254-312) ; DRF: T/drf/DRF.java:114-153
+  const bool drf = g->p.algo == H2OT_ALGO_DRF;
   g->mtry_per_tree = std::max(1, d2i(g->p.col_sample_rate_per_tree * C));
-  g->mtry = std::max(1, d2i(g->p.col_sample_rate * g->p.col_sample_rate_per_tree * C));
+  if (!drf) g->mtry = std::max(1, d2i(g->p.col_sample_rate * g->p.col_sample_rate_per_tree * C));
+  else if (g->p.mtries == -2) g->mtry = C;
+  else if (g->p.mtries == -1) g->mtry = g->nclass > 1 ? std::max(d2i(std::sqrt((double)C)), 1) : std::max(C / 3, 1);
+  else g->mtry = g->p.mtries;
+  if (g->mtry < 1 || g->mtry > C) GFAIL(H2OT_ERR_INVALID, "computed mtry outside 1..ncols");
+  if (drf) {
+    // class prior and the bound of the work column, merged over ranks
+    std::vector<double> cls((size_t)std::max(1, g->nclass) + 1, 0.0);
+    double ymax = 0;
+    for (int64_t i = 0; i < g->nrows; i++) {
+      if (std::isnan(g->y[i])) continue;
+      const double w = g->has_w ? g->w[i] : 1.0;
+      if (g->nclass > 1) {
+        const int c = (int)g->y[i];
+        if (c >= 0 && c < g->nclass) cls[c] += w;
+        cls[g->nclass] += w;
+      } else {
+        ymax = std::max(ymax, (double)std::fabs((float)g->y[i]));
+      }
+    }
+    GTRY(allreduce(g, cls.data(), (int64_t)cls.size(), 0));
+    GTRY(allreduce(g, &ymax, 1, 1));
+    g->prior_class_dist.assign(std::max(1, g->nclass), 0.0);
+    if (g->nclass > 1)
+      for (int c = 0; c < g->nclass; c++) g->prior_class_dist[c] = cls[c] / cls[g->nclass];
+    g->work_bound = g->nclass > 1 ? 1.0 : (ymax > 0 ? ymax : 1.0);
+  }
   double nd[2] = {0, 0};  // InitialValue (T/SharedTree.java:1138-1185)
   for (int64_t i = 0; i < g->nrows; i++) {
     if (std::isnan(g->y[i])) continue;
@@ -759,13 +862,18 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   }
   GTRY(allreduce(g, nd, 2, 0));
   const double mean = nd[0] / nd[1];
-  if (g->nclass > 2) g->init_f = 0;
+  if (drf) g->init_f = g->nclass > 1 ? 0 : mean;  // T/drf/DRF.java:131
+  else if (g->nclass > 2) g->init_f = 0;
   else if (g->p.family == H2OT_FAMILY_BERNOULLI) g->init_f = std::log(mean / (1 - mean));  // LogitFunction.link
   else g->init_f = mean;
-  std::vector<double> f0(g->K, 0.0);
-  f0[0] = g->init_f;
-  int64_t skipped = 0;
-  GTRY(h2ot_init_model(g->eng, f0.data(), &skipped));
+  if (drf) {
+    GTRY(h2ot_drf_init_model(g->eng));
+  } else {
+    std::vector<double> f0(g->K, 0.0);
+    f0[0] = g->init_f;
+    int64_t skipped = 0;
+    GTRY(h2ot_init_model(g->eng, f0.data(), &skipped));
+  }
   // the O(rows) host copies are not needed any more
   std::vector<double>().swap(g->y);
   std::vector<double>().swap(g->w);
@@ -778,7 +886,7 @@ int h2ot_gbm_train(h2ot_gbm* g, int32_t n_iterations) {
   if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (!g->inited) GTRY(h2ot_gbm_init(g));
   const double t0 = now_s();
-  for (int i = 0; i < n_iterations; i++) GTRY(build_next_k_trees(g));
+  for (int i = 0; i < n_iterations; i++) GTRY(g->p.algo == H2OT_ALGO_DRF ? build_next_k_trees_drf(g) : build_next_k_trees(g));
   g->timing.total_s += now_s() - t0;
   return H2OT_OK;
 }
@@ -826,6 +934,10 @@ int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* ou
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_predictions(g->eng, k, out);
+}
+int h2ot_gbm_oobt(h2ot_gbm* g, double* out) {
+  if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
+  return h2ot_get_oobt(g->eng, out);
 }
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");

@@ -276,4 +276,65 @@ __global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------ DRF
+// DRF.initializeModelSpecifics (T/drf/DRF.java:139-153): Work_k <- 1 where the response is class k (classification),
+// Work_0 <- (float) response (regression); Tree_k <- 0, NIDs_k <- 0 (pad rows DECIDED), OUT_BAG_TREES <- 0.
+struct DrfInitArgs {
+  int64_t n, n_pad;
+  int32_t K, nclass;
+  const double* resp;
+  double* const* F;
+  float* const* work;
+  int32_t* const* nids;
+  double* oobt;
+};
+__global__ void __launch_bounds__(256) drf_init_kernel(DrfInitArgs a) {
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n_pad; row += (int64_t)gridDim.x * blockDim.x) {
+    const bool in = row < a.n;
+    const double y = in ? a.resp[row] : __longlong_as_double(0x7ff8000000000000LL);
+    for (int k = 0; k < a.K; k++) {
+      float wv = 0.f;
+      if (!isnan(y)) wv = a.nclass > 1 ? ((int)y == k ? 1.f : 0.f) : (float)y;
+      a.work[k][row] = wv;
+      a.F[k][row] = 0.0;
+      a.nids[k][row] = in ? 0 : H2OT_DECIDED_ROW;
+    }
+    a.oobt[row] = 0.0;
+  }
+}
+
+// DRF.CollectPreds (T/drf/DRF.java:255-330): rows the tree held out of bag receive its vote; every row's nid is reset.
+struct CollectArgs {
+  int64_t n;
+  int32_t n_nodes, root_is_leaf, update_oobt, pad;
+  const double* w;
+  int32_t* nids;
+  double* F;
+  double* oobt;
+  const float* node_pred;
+  const h2ot_decided_node* nodes;
+  const uint8_t* bitsets;
+  const ColRef* cols;
+};
+__global__ void __launch_bounds__(256) drf_collect_kernel(CollectArgs a) {
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    const double wv = a.w ? a.w[row] : 1.0;
+    int nid = a.nids[row];
+    const bool oob = nid <= H2OT_OUT_OF_BAG;
+    if (wv != 0.0 && oob) {
+      nid = -nid + H2OT_OUT_OF_BAG;
+      int leafnid = 0;
+      if (!a.root_is_leaf) {
+        h2ot_decided_node dn = a.nodes[nid];
+        if (dn.col < 0) dn = a.nodes[dn.pid];  // bottomed out or unable to decide: the parent's decision
+        leafnid = child_node_id(dn, a.cols, a.bitsets, row);
+      }
+      const float pred = (leafnid >= 0 && leafnid < a.n_nodes) ? a.node_pred[leafnid] : 0.f;
+      a.F[row] = (double)(float)__dadd_rn(a.F[row], (double)pred);
+    }
+    a.nids[row] = 0;
+    if (a.update_oobt && oob) a.oobt[row] = __dadd_rn(a.oobt[row], wv);
+  }
+}
+
 }  // namespace h2ot

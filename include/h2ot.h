@@ -216,6 +216,18 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
 /* GBM.AddTreeContributions (T/gbm/GBM.java:1410-1470): Tree_k <- (float)(Tree_k + pred[nid]); NIDs_k <- 0 / DECIDED_ROW. */
 int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred /*[n_nodes], leaf nids used*/);
 
+/* ---- DRF (T/drf/DRF.java). The level loop is the same; what differs is around it. */
+/* DRF.initializeModelSpecifics (:139-153) + the work vecs of SharedTree.java:364-385: Work_k <- class indicator (nclass > 1) or
+ * (float) response, Tree_k <- 0, NIDs_k <- 0, OUT_BAG_TREES <- 0. No row is marked DECIDED (that is GBM-only). */
+int h2ot_drf_init_model(h2ot_engine* h);
+/* Sample (T/Sample.java:22-36) unconditionally: DRF samples every tree, and rows with an NA response go out of bag even at rate 1. */
+int h2ot_sample(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate);
+/* DRF.CollectPreds (:255-330) for class-tree k after h2ot_set_tree: out-of-bag rows with weight != 0 get
+ * Tree_k <- (float)(Tree_k + pred[leaf]); every NIDs_k row <- 0; OUT_BAG_TREES += weight for out-of-bag rows when update_oobt
+ * (pass 1 for exactly one k per iteration). root_is_leaf: the tree never split (leaf id 0). */
+int h2ot_drf_collect_preds(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, int32_t root_is_leaf, int32_t update_oobt);
+int h2ot_get_oobt(h2ot_engine* h, double* out);
+
 /* ---- multi-GPU plumbing (one process per GPU; rows sharded; replaces the MRTask node tree, W/MRTask.java:695-756,871-930) */
 #define H2OT_COMM_ID_BYTES 128
 int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]);

@@ -19,8 +19,13 @@ extern "C" {
 
 typedef struct h2ot_gbm h2ot_gbm;
 
+#define H2OT_ALGO_GBM 0
+#define H2OT_ALGO_DRF 1 /* hex.tree.drf.DRF: family BERNOULLI == binomial (one tree, binomialOpt), MULTINOMIAL == nclass trees, GAUSSIAN == regression */
+
 typedef struct h2ot_gbm_params {
-  int32_t ntrees, max_depth, nbins, nbins_cats, nbins_top_level, family, nclass, reserved;
+  int32_t ntrees, max_depth, nbins, nbins_cats, nbins_top_level, family, nclass, algo;
+  int32_t mtries; /* DRF: -1 sqrt(ncols) / ncols/3, -2 all columns, else the count (T/drf/DRF.java:117-125) */
+  int32_t pad;
   double min_rows, min_split_improvement, sample_rate, col_sample_rate, col_sample_rate_per_tree,
       col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
   int64_t seed;
@@ -66,6 +71,7 @@ int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k);
 int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k);
 int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out);
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out);
+int h2ot_gbm_oobt(h2ot_gbm* g, double* out); /* DRF: OUT_BAG_TREES column */
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);

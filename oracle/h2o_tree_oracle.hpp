@@ -1256,6 +1256,7 @@ struct GBMModel {
   double init_f = 0;
   std::vector<std::vector<TreeOut>> trees;  // [tree][k]
   std::vector<std::vector<double>> F;       // Tree_k columns after training (float-valued), [k][row]
+  std::vector<double> oobt;                 // DRF: OUT_BAG_TREES column (sum of weights of the trees that held the row out)
   std::vector<LevelCapture> captures;
   std::vector<float> varimp;
   // timing of the restated CPU path (bench.py cpu_baseline leg only)
@@ -1551,6 +1552,142 @@ struct GBM {
     for (int t = 0; t < parms.ntrees; t++) buildNextKTrees();
     model.t_total_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     model.F = tree_;
+    return model;
+  }
+};
+
+// ----------------------------------------------------------------------------------------------
+// DRF driver — T/drf/DRF.java:114-330 on top of the shared level loop (SharedTree.buildLayer + SBH2).
+// Differences from GBM that matter for the hot path: the work columns are filled once (class indicator or
+// float(response)), histograms use the float-split correction (_checkFloatSplits, :201), every tree samples rows
+// (Sample also sends NA-response rows out of bag), per-node mtries column draws, leaf value = the split's child mean
+// (DecidedNode.pred, T/DTree.java:765), and only OUT-OF-BAG rows receive the tree's vote (CollectPreds :255-330).
+// ----------------------------------------------------------------------------------------------
+struct DRF : GBM {
+  std::vector<double> oobt;
+  std::vector<double> priorClassDist;
+
+  DRF(const Frame& f, const Params& p) : GBM(f, p) { oobt.assign(fr.nrows(), 0.0); }
+  bool isClassifier() const { return nclass > 1; }
+
+  void initDRF() {  // initializeModelSpecifics :114-153
+    const int ncols = fr.ncols();
+    mtry_per_tree = std::max(1, j_d2i(parms.col_sample_rate_per_tree * ncols));
+    if (parms.mtries == -2) mtry = ncols;
+    else if (parms.mtries == -1) mtry = isClassifier() ? std::max(j_d2i(std::sqrt((double)ncols)), 1) : std::max(ncols / 3, 1);
+    else mtry = parms.mtries;
+    model.init_f = isClassifier() ? 0 : getInitialValue();
+    // class prior (Model.Output._priorClassDist): weighted class frequencies over rows with a response
+    if (isClassifier()) {
+      priorClassDist.assign(nclass, 0.0);
+      double tot = 0;
+      for (int64_t i = 0; i < fr.nrows(); i++) {
+        if (std::isnan(fr.y[i])) continue;
+        double w = fr.w.empty() ? 1 : fr.w[i];
+        priorClassDist[(int)fr.y[i]] += w;
+        tot += w;
+      }
+      for (double& v : priorClassDist) v /= tot;
+    }
+    for (int64_t i = 0; i < fr.nrows(); i++) {  // fill work columns :139-153
+      if (std::isnan(fr.y[i])) continue;
+      if (isClassifier()) {
+        int cls = (int)fr.y[i];
+        if (cls < (int)work_.size()) work_[cls][i] = 1.0;
+      } else {
+        work_[0][i] = (float)fr.y[i];
+      }
+    }
+  }
+
+  void buildNextKTreesDRF() {  // :157-250
+    std::vector<std::unique_ptr<DTree>> ktrees(tree_.size());
+    std::vector<int> leaves(tree_.size(), 0);
+    std::vector<std::vector<std::vector<HistPtr>>> hcs(tree_.size());
+    int adj_nbins = std::max(parms.nbins_top_level, parms.nbins);
+    int64_t rseed = rand_.nextLong();
+    for (int k = 0; k < K; k++) {
+      ktrees[k] = std::make_unique<DTree>(fr.ncols(), mtry, mtry_per_tree, rseed, &parms);
+      hcs[k].resize(1);
+      hcs[k][0] = initialHist(fr, adj_nbins, rseed, parms, true);
+      ktrees[k]->newUndecided(NO_PARENT, hcs[k][0]);
+      hcs[k][0] = ktrees[k]->node(0)._hs;
+    }
+    for (int k = 0; k < K; k++) sample(k, *ktrees[k]);  // always (T/drf/DRF.java:206-210)
+    for (int depth = 0; depth < parms.max_depth; depth++) {
+      bool did_split = false;
+      for (int k = 0; k < K; k++)
+        if (buildLayerK(k, *ktrees[k], leaves[k], hcs[k])) did_split = true;
+      if (!did_split) break;
+    }
+    for (int k = 0; k < K; k++) {  // :222-248
+      DTree& tree = *ktrees[k];
+      int leaf = leaves[k] = tree.len();
+      for (int nid = 0; nid < leaf; nid++) {
+        if (tree.node(nid).kind != DECIDED) continue;
+        if (!tree.node(nid)._split) {
+          if (nid == 0) {
+            tree.newLeafAt(NO_PARENT, 0);
+            tree.node(0)._pred = (float)(isClassifier() ? priorClassDist[k] : model.init_f);
+          }
+          continue;
+        }
+        for (int i = 0; i < 2; i++) {
+          int cnid = tree.node(nid)._nids[i];
+          if (cnid == UNDECIDED_CHILD_NODE_ID || tree.node(cnid).kind == UNDECIDED ||
+              (tree.node(cnid).kind == DECIDED && !tree.node(cnid)._split)) {
+            int ln = tree.newLeaf(nid);
+            const Split& sp = *tree.node(nid)._split;
+            tree.node(ln)._pred = (float)(i == 0 ? sp._p0 : sp._p1);
+            tree.node(nid)._nids[i] = ln;
+          }
+        }
+      }
+    }
+    // CollectPreds :255-330 (votes / sse bookkeeping omitted: not part of the model)
+    for (int64_t row = 0; row < fr.nrows(); row++) {
+      double weight = fr.w.empty() ? 1 : fr.w[row];
+      const bool wasOOBRow = isOOBRow(nids_[0][row]);
+      for (int k = 0; k < K; k++) {
+        if (weight != 0) {
+          DTree& tree = *ktrees[k];
+          int nid = nids_[k][row];
+          if (wasOOBRow) {
+            nid = oob2Nid(nid);
+            if (tree.node(nid).kind == UNDECIDED) nid = tree.node(nid)._pid;
+            int leafnid;
+            if (tree.node(0).kind == LEAF) leafnid = 0;
+            else {
+              const Node* dn = &tree.node(nid);
+              if (!dn->_split) dn = &tree.node(tree.node(nid)._pid);
+              leafnid = getChildNodeID(*dn, fr, row);
+            }
+            double prediction = tree.node(leafnid)._pred;
+            tree_[k][row] = (float)(tree_[k][row] + prediction);
+          }
+        }
+        nids_[k][row] = 0;
+      }
+      if (wasOOBRow) oobt[row] += weight;
+    }
+    std::vector<TreeOut> outs(K);
+    for (int k = 0; k < K; k++) {
+      outs[k].nodes = ktrees[k]->_ns;
+      for (auto& n : outs[k].nodes) n._hs.clear();
+      outs[k].leaves_start = leaves[k];
+      outs[k].depth = ktrees[k]->_depth;
+    }
+    model.trees.push_back(std::move(outs));
+    ntrees_built++;
+  }
+
+  GBMModel& trainDRF() {
+    initDRF();
+    auto t0 = std::chrono::steady_clock::now();
+    for (int t = 0; t < parms.ntrees; t++) buildNextKTreesDRF();
+    model.t_total_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    model.F = tree_;
+    model.oobt = oobt;
     return model;
   }
 };

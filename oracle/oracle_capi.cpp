@@ -189,6 +189,26 @@ void* orc_gbm_train(void* f, const OrcParams* p, int capture) {
     return nullptr;
   }
 }
+// DRF (T/drf/DRF.java): family BERNOULLI == binomial (one tree, binomialOpt), MULTINOMIAL == nclass trees, GAUSSIAN == regression
+void* orc_drf_train(void* f, const OrcParams* p, int mtries, int capture) {
+  try {
+    Params q = to_params(p);
+    q.drf = true;
+    q.mtries = mtries;
+    DRF g(*(Frame*)f, q);
+    g.capture = capture != 0;
+    if (p->chunk_rows > 0) g.chunk_rows_ = p->chunk_rows;
+    g.trainDRF();
+    return new GBMModel(std::move(g.model));
+  } catch (const std::exception& e) {
+    fprintf(stderr, "orc_drf_train: %s\n", e.what());
+    return nullptr;
+  }
+}
+void orc_model_oobt(void* m, double* out) {
+  const std::vector<double>& o = ((GBMModel*)m)->oobt;
+  std::copy(o.begin(), o.end(), out);
+}
 void orc_model_free(void* m) { delete (GBMModel*)m; }
 double orc_model_init_f(void* m) { return ((GBMModel*)m)->init_f; }
 int orc_model_ntrees(void* m) { return (int)((GBMModel*)m)->trees.size(); }

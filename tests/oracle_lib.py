@@ -125,6 +125,9 @@ def lib():
         getattr(L, name).argtypes = [C.c_void_p, C.c_void_p]
     L.orc_gbm_train.argtypes = [C.c_void_p, C.POINTER(OrcParams), C.c_int]
     L.orc_gbm_train.restype = C.c_void_p
+    L.orc_drf_train.argtypes = [C.c_void_p, C.POINTER(OrcParams), C.c_int, C.c_int]
+    L.orc_drf_train.restype = C.c_void_p
+    L.orc_model_oobt.argtypes = [C.c_void_p, C.c_void_p]
     L.orc_model_free.argtypes = [C.c_void_p]
     L.orc_model_init_f.argtypes = [C.c_void_p]
     L.orc_model_init_f.restype = C.c_double
@@ -253,11 +256,14 @@ class Frame:
 
 
 class Model:
-    def __init__(self, frame, params, capture=False):
+    def __init__(self, frame, params, capture=False, drf=False, mtries=-1):
         self.L = lib()
         self.frame = frame
-        self.m = self.L.orc_gbm_train(frame.f, C.byref(params), int(capture))
-        assert self.m, "oracle GBM training failed"
+        if drf:
+            self.m = self.L.orc_drf_train(frame.f, C.byref(params), int(mtries), int(capture))
+        else:
+            self.m = self.L.orc_gbm_train(frame.f, C.byref(params), int(capture))
+        assert self.m, "oracle training failed"
 
     def __del__(self):
         if getattr(self, "m", None):
@@ -271,6 +277,11 @@ class Model:
     def F(self, k=0):
         out = np.empty(self.frame.nrows, dtype=np.float64)
         self.L.orc_model_F(self.m, k, ptr(out))
+        return out
+
+    def oobt(self):
+        out = np.empty(self.frame.nrows, dtype=np.float64)
+        self.L.orc_model_oobt(self.m, ptr(out))
         return out
 
     def timing(self):
