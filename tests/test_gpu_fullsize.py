@@ -1,0 +1,92 @@
+"""Full-size (BASELINE configs[1]: 11M x 28) checks through size-independent properties — the oracle would need minutes
+here. Per level of a real tree build:
+  * every active (leaf, col) histogram of a leaf holds the same total weight, sum(wY) and sum(wYY) (the rows of a leaf are
+    the same whatever the column: a checksum of checksums across 28 columns);
+  * the leaf totals add up to the number of in-bag rows and to the global sum of the work column;
+  * the shared-memory and the global-atomics kernels agree bit for bit (integer accumulation);
+  * a second run reproduces trees and predictions bit for bit.
+"""
+import numpy as np
+import pytest
+
+import h2ot_lib
+
+pytestmark = pytest.mark.gpu
+
+
+def test_higgs_shape_11m_x_28_level_invariants():
+    import importlib
+    bench = importlib.import_module("bench")
+    P = h2ot_lib.pkg()
+    N, C = 11_000_000, bench.NCOLS
+    cols, y, _ = bench.make_frame(N, 0, N, pinned=False)
+    sig = []
+    for run in range(2):
+        gm = P.GBM(distribution="bernoulli", ntrees=2, **bench.PARAMS)
+        gm.load(cols, y)
+        if run == 0:
+            gm.capture_levels(True)
+        gm.train()
+        sig.append((gm.predictions().tobytes(), [bytes(gm.tree(t)[0]) for t in range(gm.ntrees)]))
+        if run == 0:
+            assert gm.ncaptures() == 12
+            for i in range(gm.ncaptures()):
+                info = gm.capture_info(i)
+                tot_w = 0.0
+                for n in range(info["nleaves"]):
+                    sums = []
+                    for c in range(C):
+                        d, _, _, has, nv = gm.capture_desc(i, n, c)
+                        if not (d.flags & P.DESC_ACTIVE) or not has:
+                            continue
+                        v = gm.capture_vals(i, n, c, nv)
+                        sums.append((v[0::3].sum(), v[1::3].sum(), v[2::3].sum()))
+                    assert len(sums) >= 2
+                    s = np.array(sums)
+                    assert np.all(s[:, 0] == s[0, 0]), (i, n)            # counts: exact
+                    # wY / wYY: every bin was float-cast, so column totals agree to float precision of the bin sums
+                    assert np.ptp(s[:, 1]) <= 1e-6 * max(1.0, np.abs(s[:, 1]).max() + s[0, 2]), (i, n, s[:, 1])
+                    assert np.ptp(s[:, 2]) <= 1e-6 * s[0, 2], (i, n)
+                    tot_w += s[0, 0]
+                assert tot_w == N, (i, tot_w)
+        gm.close()
+    assert sig[0] == sig[1]
+
+
+def test_full_size_root_level_kernel_variants_agree():
+    import importlib
+    bench = importlib.import_module("bench")
+    P = h2ot_lib.pkg()
+    N, C = 11_000_000, bench.NCOLS
+    cols, y, _ = bench.make_frame(N, 0, N, pinned=False)
+    e = P.Engine(nrows=N, ncols=C)
+    for j in range(C):
+        e.load_column(j, cols[j])
+    e.load_response(y)
+    e.finalize_frame()
+    e.init_model([0.0])
+    work = (y - 0.53).astype(np.float32).astype(np.float64)
+    e.set_work(work)
+    e.begin_tree(0, 0, 1.0, float(np.max(np.abs(work))))
+    descs = (P.HistDesc * C)()
+    for j in range(C):
+        descs[j] = P.make_desc(float(np.min(cols[j])), float(np.nextafter(np.max(cols[j]), np.inf)), 1024, order=j)
+    res = []
+    for mode in (0, 1):
+        e.set_hist_mode(mode)
+        e.build_level(descs)
+        res.append(e.finish_level())
+    assert np.array_equal(res[0]["vals"], res[1]["vals"])
+    assert np.array_equal(res[0]["min2"], res[1]["min2"]) and np.array_equal(res[0]["maxIn"], res[1]["maxIn"])
+    v = res[0]["vals"]
+    for j in range(C):
+        blk = v[res[0]["offsets"][j]: res[0]["offsets"][j] + 1025 * 3]
+        assert blk[0::3].sum() == N
+        assert res[0]["min2"][j] == np.min(cols[j]) and res[0]["maxIn"][j] == np.max(cols[j])
+    # exact integer accumulation: the total of wY over all bins of a column equals the fp64 sum of the work column
+    # up to the float cast of each bin (<= 2^-24 relative per bin)
+    tot = float(np.sum(work))
+    for j in range(0, C, 9):
+        blk = v[res[0]["offsets"][j]: res[0]["offsets"][j] + 1025 * 3]
+        assert abs(blk[1::3].sum() - tot) <= 1e-6 * float(np.sum(np.abs(work)))
+    e.close()
