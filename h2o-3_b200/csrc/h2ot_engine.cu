@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -13,6 +14,7 @@
 #include "k_level.cuh"
 #include "k_rows.cuh"
 #include "k_split.cuh"
+#include "k_xreduce.cuh"
 
 namespace h2ot {
 
@@ -84,10 +86,18 @@ struct TreeState {  // per class-tree k
   int64_t total_bins = 0, total_vals = 0;
   int active_cols = 0;
   DBuf<DescDev> d_descs;
-  DBuf<h2ot_hist_desc> d_hdescs;
+  DBuf<unsigned char> d_lvl;  // per-level upload: [DescDev LC][GroupDev G][int32 group columns]
+  unsigned char* lvl_host = nullptr;
+  size_t lvl_host_cap = 0;
+  DescDev* p_descs = nullptr;
+  GroupDev* p_groups = nullptr;
+  int32_t* p_group_cols = nullptr;
   DBuf<GroupDev> d_groups;
   DBuf<long long> d_sums;  // [3*total_bins | L leaf_rows]
   DBuf<unsigned long long> d_minmax;
+  long long* sums = nullptr;          // this level's accumulators: d_sums / d_minmax, or the peer-mapped exchange buffer
+  unsigned long long* mm = nullptr;
+  bool in_xbuf = false;
   DBuf<double> d_vals;
   // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
   // [min2 | maxIn | wNA | conc : LC doubles each][best split per leaf][has_vals : LC bytes]
@@ -114,6 +124,7 @@ struct Nccl {
   int (*GetUniqueId)(void*) = nullptr;
   int (*CommInitRank)(void**, int, IdByValue, int) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
@@ -158,6 +169,15 @@ struct h2ot_engine {
   int hist_mode = 0;
   int smem_budget_kb = 0;  // 0: automatic
   Nccl nccl;
+  // peer-memory exchange (k_xreduce.cuh): [in: xr_cap words][out: xr_cap words][flags: kXrMaxWorld words]
+  bool xr_enabled = false, xr_failed = false, xr_coop = true;
+  unsigned long long* xr_buf = nullptr;
+  size_t xr_cap = 0;
+  XrPeers xr_peers{};
+  void* xr_opened[kXrMaxWorld] = {nullptr};
+  unsigned long long xr_epoch = 0;
+  int* xr_err = nullptr;
+  int* xr_err_host = nullptr;  // pinned mirror of xr_err, refreshed after every exchange
 };
 
 namespace {
@@ -180,6 +200,10 @@ int check(h2ot_engine* h) {
     int _r = (expr);            \
     if (_r != H2OT_OK) return _r; \
   } while (0)
+
+void xr_release(h2ot_engine* h);
+int xr_ensure(h2ot_engine* h, size_t words);
+int xr_allreduce(h2ot_engine* h, long long n_sums, long long n);
 
 int t_begin(h2ot_engine* h, double* acc) {
   Timer t;
@@ -212,6 +236,7 @@ int finish_call(h2ot_engine* h) {
   }
   h->timers.clear();
   CUDA_TRY(cudaGetLastError());
+  if (h->xr_err_host && *h->xr_err_host) H2OT_FAIL(H2OT_ERR_COMM, "peer-memory exchange timed out waiting for another rank");
   return H2OT_OK;
 }
 int h2d(h2ot_engine* h, void* dst, const void* src, size_t bytes) {
@@ -354,12 +379,16 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->w) cudaFree(h->w);
   if (h->off) cudaFree(h->off);
   if (h->oobt) cudaFree(h->oobt);
+  xr_release(h);
+  if (h->xr_err) cudaFree(h->xr_err);
+  if (h->xr_err_host) cudaFreeHost(h->xr_err_host);
   for (TreeState& t : h->ts) {
     if (t.F) cudaFree(t.F);
     if (t.work) cudaFree(t.work);
     if (t.nids) cudaFree(t.nids);
     if (t.code) cudaFree(t.code);
-    t.nodes.release(); t.bitsets.release(); t.d_descs.release(); t.d_hdescs.release(); t.d_groups.release(); t.d_group_cols.release();
+    t.nodes.release(); t.bitsets.release(); t.d_lvl.release();
+    if (t.lvl_host) cudaFreeHost(t.lvl_host);
     t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_pack.release();
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release();
   }
@@ -668,6 +697,121 @@ int upload_nodes(h2ot_engine* h, TreeState& t, int n_decided, const h2ot_decided
   return H2OT_OK;
 }
 
+
+int nccl_rc(h2ot_engine* h, int rc, const char* what) {
+  if (rc == 0) return H2OT_OK;
+  std::string m = std::string(what) + " failed: ";
+  m += h->nccl.GetErrorString ? h->nccl.GetErrorString(rc) : "nccl error";
+  H2OT_FAIL(H2OT_ERR_COMM, m);
+}
+
+void xr_release(h2ot_engine* h) {
+  for (int p = 0; p < kXrMaxWorld; p++)
+    if (h->xr_opened[p]) {
+      cudaIpcCloseMemHandle(h->xr_opened[p]);
+      h->xr_opened[p] = nullptr;
+    }
+  if (h->xr_buf) cudaFree(h->xr_buf);
+  h->xr_buf = nullptr;
+  h->xr_cap = 0;
+}
+
+// Makes sure the exchange buffer holds `words` 64-bit words per half. Growing is collective (every rank plans the same
+// level, so every rank grows at the same call): allocate, trade CUDA IPC handles over the NCCL communicator, map the peers.
+// H2OT_ERR_UNSUPPORTED: peer mapping is not possible here; the caller falls back to the NCCL collectives for good.
+int xr_ensure(h2ot_engine* h, size_t words) {
+  if (words <= h->xr_cap) return H2OT_OK;
+  const int W = h->nccl.world, R = h->nccl.rank;
+  if (W > kXrMaxWorld || !h->nccl.AllGather) {
+    h->xr_failed = true;
+    return H2OT_ERR_UNSUPPORTED;
+  }
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  xr_release(h);
+  const size_t cap = std::max<size_t>(words * 2, 1 << 16);
+  const size_t total = (2 * cap + kXrMaxWorld) * sizeof(unsigned long long);
+  CUDA_TRY(cudaMalloc(&h->xr_buf, total));
+  CUDA_TRY(cudaMemset(h->xr_buf, 0, total));
+  if (!h->xr_err) {
+    CUDA_TRY(cudaMalloc(&h->xr_err, sizeof(int)));
+    CUDA_TRY(cudaMemset(h->xr_err, 0, sizeof(int)));
+    CUDA_TRY(cudaMallocHost(&h->xr_err_host, sizeof(int)));
+    *h->xr_err_host = 0;
+  }
+  h->xr_epoch = 0;
+  cudaIpcMemHandle_t mine;
+  CUDA_TRY(cudaIpcGetMemHandle(&mine, h->xr_buf));
+  DBuf<unsigned char> d_handles;
+  TRY(d_handles.ensure((size_t)W * sizeof(cudaIpcMemHandle_t)));
+  CUDA_TRY(cudaMemcpy(d_handles.p + (size_t)R * sizeof(mine), &mine, sizeof(mine), cudaMemcpyHostToDevice));
+  TRY(nccl_rc(h, h->nccl.AllGather(d_handles.p + (size_t)R * sizeof(mine), d_handles.p, sizeof(mine), /*ncclUint8*/ 1, h->nccl.comm, h->stream),
+              "ncclAllGather(ipc handles)"));
+  std::vector<cudaIpcMemHandle_t> all(W);
+  CUDA_TRY(cudaMemcpyAsync(all.data(), d_handles.p, (size_t)W * sizeof(mine), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  d_handles.release();
+  bool ok = true;
+  for (int p = 0; p < W; p++) {
+    if (p == R) {
+      h->xr_peers.buf[p] = h->xr_buf;
+      continue;
+    }
+    void* ptr = nullptr;
+    if (cudaIpcOpenMemHandle(&ptr, all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      cudaGetLastError();
+      ok = false;
+      break;
+    }
+    h->xr_opened[p] = ptr;
+    h->xr_peers.buf[p] = static_cast<unsigned long long*>(ptr);
+  }
+  // all ranks must agree on the outcome
+  DBuf<int> d_ok;
+  TRY(d_ok.ensure(1));
+  const int mine_ok = ok ? 1 : 0;
+  CUDA_TRY(cudaMemcpy(d_ok.p, &mine_ok, sizeof(int), cudaMemcpyHostToDevice));
+  TRY(nccl_rc(h, h->nccl.AllReduce(d_ok.p, d_ok.p, 1, /*ncclInt32*/ 2, /*ncclMin*/ 3, h->nccl.comm, h->stream), "ncclAllReduce(ipc ok)"));
+  int all_ok = 0;
+  CUDA_TRY(cudaMemcpyAsync(&all_ok, d_ok.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  d_ok.release();
+  if (!all_ok) {
+    xr_release(h);
+    h->xr_failed = true;
+    return H2OT_ERR_UNSUPPORTED;
+  }
+  h->xr_cap = cap;
+  return H2OT_OK;
+}
+
+int xr_allreduce(h2ot_engine* h, long long n_sums, long long n) {
+  const int W = h->nccl.world, R = h->nccl.rank;
+  const size_t flag_off = 2 * h->xr_cap;
+  const unsigned long long timeout = 20ULL * 1000 * 1000 * 1000;  // ~10 s of SM clocks
+  const long long slice = (n + W - 1) / W;
+  const int g_rs = (int)std::max<long long>(1, std::min<long long>((slice + 255) / 256, (long long)h->sm_count * 4));
+  const int g_ag = (int)std::max<long long>(1, std::min<long long>((n + 255) / 256, (long long)h->sm_count * 4));
+  if (h->xr_coop) {  // one cooperative launch; the grid must be co-resident: at most 2 CTAs of 256 threads per SM here
+    size_t cap = h->xr_cap, fo = flag_off;
+    unsigned long long ep = h->xr_epoch + 1, to = timeout;
+    h->xr_epoch += 2;
+    int w = W, r = R;
+    int grid = (int)std::max<long long>(1, std::min<long long>((slice + 255) / 256, (long long)h->sm_count * 2));
+    void* args[] = {&h->xr_peers, &w, &r, &cap, &fo, &n_sums, &n, &ep, &to, &h->xr_err};
+    CUDA_TRY(cudaLaunchCooperativeKernel((const void*)xr_fused_kernel, dim3(grid), dim3(256), args, 0, h->stream));
+    h->stats.launches += 1;
+  } else {
+    xr_barrier_kernel<<<1, 32, 0, h->stream>>>(h->xr_peers, W, R, flag_off, ++h->xr_epoch, timeout, h->xr_err);
+    xr_reduce_scatter_kernel<<<g_rs, 256, 0, h->stream>>>(h->xr_peers, W, R, h->xr_cap, n_sums, n);
+    xr_barrier_kernel<<<1, 32, 0, h->stream>>>(h->xr_peers, W, R, flag_off, ++h->xr_epoch, timeout, h->xr_err);
+    xr_all_gather_kernel<<<g_ag, 256, 0, h->stream>>>(h->xr_peers, W, R, h->xr_cap, n);
+    h->stats.launches += 4;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->xr_err_host, h->xr_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_TRY(cudaGetLastError());
+  return H2OT_OK;
+}
+
 // Places every active (leaf, col) histogram: global bin offsets, packed-vals offsets, shared-memory groups.
 int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs) {
   const int C = h->C;
@@ -836,22 +980,52 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   t.L = n_leaves;
   t.leaf_offset = leaf_offset;
   const size_t LC = (size_t)n_leaves * h->C;
-  TRY(t.d_descs.ensure(LC));
-  TRY(t.d_hdescs.ensure(LC));
-  TRY(t.d_groups.ensure(std::max<size_t>(1, t.h_groups.size())));
-  TRY(t.d_sums.ensure((size_t)t.total_bins * 3 + n_leaves));
-  TRY(t.d_minmax.ensure(LC * 2));
-  TRY(h2d(h, t.d_descs.p, t.h_descs.data(), LC * sizeof(DescDev)));
-  TRY(h2d(h, t.d_hdescs.p, descs, LC * sizeof(h2ot_hist_desc)));
-  if (!t.h_groups.empty()) TRY(h2d(h, t.d_groups.p, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev)));
-  TRY(t.d_group_cols.ensure(std::max<size_t>(1, t.h_group_cols.size())));
-  if (!t.h_group_cols.empty()) TRY(h2d(h, t.d_group_cols.p, t.h_group_cols.data(), t.h_group_cols.size() * sizeof(int32_t)));
-  CUDA_TRY(cudaMemsetAsync(t.d_sums.p, 0, ((size_t)t.total_bins * 3 + n_leaves) * sizeof(long long), h->stream));
-  CUDA_TRY(cudaMemsetAsync(t.d_minmax.p, 0, LC * 2 * sizeof(unsigned long long), h->stream));
+  // this level's descriptors, groups and column lists travel in ONE copy from pinned staging
+  {
+    const size_t b_descs = LC * sizeof(DescDev), b_groups = std::max<size_t>(1, t.h_groups.size()) * sizeof(GroupDev);
+    const size_t b_cols = std::max<size_t>(1, t.h_group_cols.size()) * sizeof(int32_t);
+    const size_t total = b_descs + b_groups + b_cols;
+    TRY(t.d_lvl.ensure(total));
+    if (total > t.lvl_host_cap) {
+      if (t.lvl_host) cudaFreeHost(t.lvl_host);
+      t.lvl_host = nullptr;
+      t.lvl_host_cap = 0;
+      CUDA_TRY(cudaMallocHost(&t.lvl_host, total * 2));
+      t.lvl_host_cap = total * 2;
+    }
+    for (size_t i = 0; i < LC; i++) t.h_descs[i].pad = (uint32_t)(uint16_t)descs[i].order;  // bestCol tie order
+    memcpy(t.lvl_host, t.h_descs.data(), b_descs);
+    if (!t.h_groups.empty()) memcpy(t.lvl_host + b_descs, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev));
+    if (!t.h_group_cols.empty()) memcpy(t.lvl_host + b_descs + b_groups, t.h_group_cols.data(), t.h_group_cols.size() * sizeof(int32_t));
+    t.p_descs = reinterpret_cast<DescDev*>(t.d_lvl.p);
+    t.p_groups = reinterpret_cast<GroupDev*>(t.d_lvl.p + b_descs);
+    t.p_group_cols = reinterpret_cast<int32_t*>(t.d_lvl.p + b_descs + b_groups);
+    TRY(h2d(h, t.d_lvl.p, t.lvl_host, total));
+  }
+  {
+    const size_t ns = (size_t)t.total_bins * 3 + n_leaves, nm = LC * 2;
+    t.in_xbuf = false;
+    if (h->xr_enabled && !h->xr_failed && h->nccl.world > 1) {
+      const int rc = xr_ensure(h, ns + nm);
+      if (rc == H2OT_OK) {
+        t.sums = reinterpret_cast<long long*>(h->xr_buf);
+        t.mm = h->xr_buf + ns;
+        t.in_xbuf = true;
+      } else if (rc != H2OT_ERR_UNSUPPORTED) {
+        return rc;
+      }
+    }
+    if (!t.in_xbuf) {  // [sums | min/max keys] contiguous either way: one clear
+      TRY(t.d_sums.ensure(ns + nm));
+      t.sums = t.d_sums.p;
+      t.mm = reinterpret_cast<unsigned long long*>(t.d_sums.p + ns);
+    }
+    CUDA_TRY(cudaMemsetAsync(t.sums, 0, (ns + nm) * sizeof(long long), h->stream));
+  }
 
   // K2a
   ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
-               reinterpret_cast<unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3)};
+               reinterpret_cast<unsigned long long*>(t.sums + (size_t)t.total_bins * 3)};
   TRY(t_begin(h, &h->stats.ms_score));
   score_decide_kernel<<<grid_for(h, h->n_pad / 4, 256, 16), 256, 0, h->stream>>>(sa);
   h->stats.launches++;
@@ -862,16 +1036,16 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   ha.n_pad = h->n_pad;
   ha.L = n_leaves;
   ha.C = h->C;
-  ha.group_cols = t.d_group_cols.p;
+  ha.group_cols = t.p_group_cols;
   const int64_t n_tiles = h->n_pad / kTileRows;
   ha.code = t.code;
   ha.work = t.work;
   ha.w = h->w;
   ha.cols = h->d_cols.p;
-  ha.descs = t.d_descs.p;
-  ha.groups = t.d_groups.p;
-  ha.acc = t.d_sums.p;
-  ha.minmax = t.d_minmax.p;
+  ha.descs = t.p_descs;
+  ha.groups = t.p_groups;
+  ha.acc = t.sums;
+  ha.minmax = t.mm;
   ha.sy = std::ldexp(1.0, t.ey);
   ha.syy = std::ldexp(1.0, t.eyy);
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
@@ -938,9 +1112,9 @@ int h2ot_level_buffers(h2ot_engine* h, int32_t k, void** d_sums, int64_t* n_sums
   CHECK_K(h, k);
   TreeState& t = h->ts[k];
   if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
-  if (d_sums) *d_sums = t.d_sums.p;
+  if (d_sums) *d_sums = t.sums;
   if (n_sums) *n_sums = t.total_bins * 3 + t.L;
-  if (d_minmax) *d_minmax = t.d_minmax.p;
+  if (d_minmax) *d_minmax = t.mm;
   if (n_minmax) *n_minmax = (int64_t)t.L * h->C * 2;
   return H2OT_OK;
 }
@@ -959,8 +1133,12 @@ int h2ot_allreduce_level(h2ot_engine* h, int32_t k) {
   if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
   if (h->nccl.world <= 1 || !h->nccl.comm) return H2OT_OK;
   const size_t ns = (size_t)t.total_bins * 3 + t.L, nm = (size_t)t.L * h->C * 2;
-  TRY(nccl_check(h, h->nccl.AllReduce(t.d_sums.p, t.d_sums.p, ns, /*ncclInt64*/ 4, /*ncclSum*/ 0, h->nccl.comm, h->stream), "ncclAllReduce(sums)"));
-  TRY(nccl_check(h, h->nccl.AllReduce(t.d_minmax.p, t.d_minmax.p, nm, /*ncclUint64*/ 5, /*ncclMax*/ 2, h->nccl.comm, h->stream), "ncclAllReduce(minmax)"));
+  if (t.in_xbuf) {
+    TRY(xr_allreduce(h, (long long)ns, (long long)(ns + nm)));
+    return finish_call(h);
+  }
+  TRY(nccl_check(h, h->nccl.AllReduce(t.sums, t.sums, ns, /*ncclInt64*/ 4, /*ncclSum*/ 0, h->nccl.comm, h->stream), "ncclAllReduce(sums)"));
+  TRY(nccl_check(h, h->nccl.AllReduce(t.mm, t.mm, nm, /*ncclUint64*/ 5, /*ncclMax*/ 2, h->nccl.comm, h->stream), "ncclAllReduce(minmax)"));
   return finish_call(h);
 }
 
@@ -986,10 +1164,10 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   FinalizeArgs fa{};
   fa.L = t.L;
   fa.C = h->C;
-  fa.descs = t.d_descs.p;
-  fa.acc = t.d_sums.p;
-  fa.minmax = t.d_minmax.p;
-  fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.d_sums.p + (size_t)t.total_bins * 3);
+  fa.descs = t.p_descs;
+  fa.acc = t.sums;
+  fa.minmax = t.mm;
+  fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.sums + (size_t)t.total_bins * 3);
   fa.vals = t.d_vals.p;
   fa.min2 = t.p_min2;
   fa.maxIn = t.p_maxIn;
@@ -1039,10 +1217,10 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   if (t.any_cat) smem += 8 * (3 * n1 + n1) + 4 * n1;
   if (smem > (size_t)h->split_smem_max) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
   if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
-  SplitArgs sa{t.L, h->C, t.d_descs.p, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p};
+  SplitArgs sa{t.L, h->C, t.p_descs, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p};
   TRY(t_begin(h, &h->stats.ms_split));
   find_split_kernel<<<(unsigned)LC, kSplitThreads, smem, h->stream>>>(sa);
-  best_col_kernel<<<(t.L + 63) / 64, 64, 0, h->stream>>>(t.L, h->C, t.d_descs.p, t.d_hdescs.p, t.d_cand.p, t.p_best);
+  best_col_kernel<<<t.L, 32, 0, h->stream>>>(t.L, h->C, t.p_descs, t.d_cand.p, t.p_best);
   h->stats.launches += 2;
   TRY(t_end(h));
   if (out_splits) TRY(d2h(h, out_splits, t.p_best, (size_t)t.L * sizeof(h2ot_split)));
@@ -1054,8 +1232,12 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
                     double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
                     uint8_t* out_has_vals, h2ot_split* out_splits) {
   CHECK_ENGINE(h);
+  static const bool trace = getenv("H2OT_TRACE") != nullptr;
+  auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double tr0 = trace ? now() : 0;
   h->defer_sync = true;
   int rc = h2ot_build_level(h, k, leaf_offset, n_leaves, n_decided, decided, bitset_pool, bitset_bytes, descs);
+  const double tr1 = trace ? now() : 0;
   if (rc == H2OT_OK) rc = h2ot_allreduce_level(h, k);
   if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
   if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
@@ -1074,7 +1256,12 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
   }
   if (rc == H2OT_OK) rc = d2h(h, h->stage, t.d_pack.p, t.pack_bytes);
   h->defer_sync = false;
+  const double tr2 = trace ? now() : 0;
   const int rs = finish_call(h);  // also drains the stream after a failed stage
+  if (trace) {
+    const double tr3 = now();
+    fprintf(stderr, "[h2ot] level L=%d: enqueue build %.3f ms, enqueue rest %.3f ms, wait %.3f ms\n", n_leaves, tr1 - tr0, tr2 - tr1, tr3 - tr2);
+  }
   if (rc != H2OT_OK) return rc;
   if (rs != H2OT_OK) return rs;
   const size_t LC = (size_t)t.L * h->C;
@@ -1224,6 +1411,7 @@ static int nccl_load(Nccl& n) {
   n.GetUniqueId = (int (*)(void*))dlsym(n.lib, "ncclGetUniqueId");
   n.CommInitRank = (int (*)(void**, int, IdByValue, int))dlsym(n.lib, "ncclCommInitRank");
   n.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(n.lib, "ncclAllReduce");
+  n.AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(n.lib, "ncclAllGather");
   n.CommDestroy = (int (*)(void*))dlsym(n.lib, "ncclCommDestroy");
   n.GetErrorString = (const char* (*)(int))dlsym(n.lib, "ncclGetErrorString");
   if (!n.GetUniqueId || !n.CommInitRank || !n.AllReduce) H2OT_FAIL(H2OT_ERR_COMM, "libnccl is missing required symbols");
@@ -1257,6 +1445,11 @@ int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8
   std::lock_guard<std::mutex> lock(g_comm_mutex);
   const std::string key(reinterpret_cast<const char*>(id), H2OT_COMM_ID_BYTES);
   auto it = g_comms.find(key + ":" + std::to_string(h->cfg.device));
+  {
+    const char* e = getenv("H2OT_XREDUCE");
+    h->xr_enabled = !(e && e[0] == '0');
+    h->xr_coop = !(e && e[0] == '2');  // 2: the four-kernel sequence instead of the cooperative launch
+  }
   if (it != g_comms.end()) {
     h->nccl.comm = it->second;
     h->nccl.shared = true;

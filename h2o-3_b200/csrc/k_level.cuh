@@ -16,7 +16,7 @@ struct DescDev {
   int64_t gbin;      // global bin offset (3 int64 accumulators per bin)
   int64_t voff;      // offset (doubles) of the block in the packed vals output
   uint32_t flags;    // H2OT_DESC_*
-  uint32_t pad;
+  uint32_t pad;      // low 16 bits: h2ot_hist_desc::order
 };
 struct GroupDev {
   int32_t cols_off, ncols;  // the group's columns: group_cols[cols_off .. cols_off + ncols) (all of one storage type)

@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     double* dst = tid == 0 ? wlo : (tid == 1 ? wYlo : wYYlo);
     double s = 0.0;
     dst[0] = 0.0;
+#pragma unroll 8
     for (int b = 1; b <= nbins; b++) {
       s = __dadd_rn(s, v[3 * (b - 1) + tid]);
       dst[b] = s;
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     double* dst = j == 0 ? whi : (j == 1 ? wYhi : wYYhi);
     double s = 0.0;
     dst[nbins] = 0.0;
+#pragma unroll 8
     for (int b = nbins - 1; b >= 0; b--) {
       s = __dadd_rn(s, v[3 * b + j]);
       dst[b] = s;
@@ -358,38 +360,50 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
   out->tree_p1 = tree_p1;
 }
 
-// DecidedNode.bestCol (T/DTree.java:616-656): first strictly smaller se() in _scoreCols order.
-__global__ void best_col_kernel(int L, int C, const DescDev* descs, const h2ot_hist_desc* hdescs, const h2ot_split* cand,
-                                h2ot_split* best_out) {
-  const int l = blockIdx.x * blockDim.x + threadIdx.x;
-  if (l >= L) return;
-  int bc = -1;
+// DecidedNode.bestCol (T/DTree.java:616-656): first strictly smaller se() in _scoreCols order. One warp per leaf: lanes take
+// columns, a shuffle reduction keeps the lexicographic minimum of (se, position in _scoreCols), the warp copies the winner.
+__global__ void __launch_bounds__(32) best_col_kernel(int L, int C, const DescDev* descs, const h2ot_split* cand, h2ot_split* best_out) {
+  const int l = blockIdx.x;
+  const int lane = threadIdx.x;
+  int bc = -1, border = 0x7fffffff;
   double bse = 0;
-  int border = 0;
-  for (int c = 0; c < C; c++) {
+  for (int c = lane; c < C; c += 32) {
     const h2ot_split& s = cand[(size_t)l * C + c];
     if (s.col < 0) continue;
-    if ((descs[(size_t)l * C + c].flags & H2OT_DESC_CHECKFLOAT) && isnan(s.splat)) continue;  // :644-651
+    const DescDev& d = descs[(size_t)l * C + c];
+    if ((d.flags & H2OT_DESC_CHECKFLOAT) && isnan(s.splat)) continue;  // :644-651
     const double se = __dadd_rn(s.se0, s.se1);
-    const int order = hdescs[(size_t)l * C + c].order;
+    const int order = (int)(int16_t)(uint16_t)d.pad;  // position in the leaf's _scoreCols
     if (bc < 0 || se < bse || (se == bse && order < border)) {
       bc = c;
       bse = se;
       border = order;
     }
   }
+  for (int o = 16; o > 0; o >>= 1) {
+    const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+    const int oo = __shfl_xor_sync(0xffffffffu, border, o);
+    const double os = __shfl_xor_sync(0xffffffffu, bse, o);
+    if (oc >= 0 && (bc < 0 || os < bse || (os == bse && oo < border))) {
+      bc = oc;
+      bse = os;
+      border = oo;
+    }
+  }
   h2ot_split* o = best_out + l;
   if (bc < 0) {
-    o->col = -1;
-    o->splat = __int_as_float(0x7fc00000);
+    if (lane == 0) {
+      o->col = -1;
+      o->splat = __int_as_float(0x7fc00000);
+    }
     return;
   }
-  const h2ot_split& s = cand[(size_t)l * C + bc];
-  o->col = s.col; o->bin = s.bin; o->nasplit = s.nasplit; o->equal = s.equal; o->splat = s.splat;
-  o->bs_nbits = s.bs_nbits; o->bs_bitoff = s.bs_bitoff; o->bs_nbytes = s.bs_nbytes;
-  o->se = s.se; o->se0 = s.se0; o->se1 = s.se1; o->n0 = s.n0; o->n1 = s.n1;
-  o->p0 = s.p0; o->p1 = s.p1; o->tree_p0 = s.tree_p0; o->tree_p1 = s.tree_p1;
-  for (int i = 0; i < s.bs_nbytes; i++) o->bs[i] = s.bs[i];
+  // copy header + statistics (104 bytes) and the used part of the bitset, word-wise
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(cand + (size_t)l * C + bc);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(o);
+  const int nbytes = cand[(size_t)l * C + bc].bs_nbytes;
+  const int nwords = 26 + (nbytes + 3) / 4;  // offsetof(h2ot_split, bs) == 104
+  for (int i = lane; i < nwords; i += 32) dst[i] = src[i];
 }
 
 }  // namespace h2ot

@@ -151,3 +151,57 @@ def test_run_to_run_determinism():
         sigs.append(sig)
         gm.close()
     assert sigs[0] == sigs[1] == sigs[2]
+
+
+def test_wide_frame_epsilon_shape():
+    """BASELINE configs[4] (Epsilon-shape wide dense frame, nbins 64), scaled down in rows: 2000 columns force many column
+    groups per level and a 2000 x 1025-bin root level."""
+    rng = np.random.default_rng(12)
+    n, c = 3000, 2000
+    X = rng.normal(size=(n, c)).astype(np.float32)
+    X /= np.linalg.norm(X, axis=1, keepdims=True)
+    X = X.astype(np.float64)
+    beta = np.zeros(c)
+    beta[:20] = rng.normal(size=20) * 8
+    y = (rng.random(n) < 1 / (1 + np.exp(-(X @ beta)))).astype(np.float64)
+    gm, om = _run_both(X, y, ntrees=2, max_depth=5, nbins=64, seed=3, capture=False)
+    h2ot_lib.compare_models(gm, om, check_levels=False)
+    gm.close()
+
+
+def test_covtype_shape_seven_classes():
+    """BASELINE configs[4] (covtype-shape: 10 numeric + 44 binary columns, 7 imbalanced classes, nbins 64), scaled down in rows."""
+    rng = np.random.default_rng(13)
+    n = 30000
+    num = rng.normal(size=(n, 10)).astype(np.float32).astype(np.float64) * [1, 2, 3, 1, 1, 5, 1, 1, 1, 4]
+    binary = (rng.random((n, 44)) < rng.random(44) * 0.3).astype(np.float64)
+    X = np.concatenate([num, binary], axis=1)
+    score = np.stack([num[:, k % 10] * (1 + 0.2 * k) + binary[:, k] * 2 + rng.normal(size=n) for k in range(7)], axis=1) + \
+        np.array([2.0, 2.5, 0.5, -1, 0, -0.5, -1.5])
+    y = np.argmax(score, axis=1).astype(np.float64)
+    gm, om = _run_both(X, y, distribution="multinomial", nclass=7, ntrees=2, max_depth=5, nbins=64, seed=17, capture=False)
+    h2ot_lib.compare_models(gm, om, K=7, check_levels=False)
+    gm.close()
+
+
+def test_airlines_shape_mixed_with_high_cardinality_cats():
+    """BASELINE configs[3] (airlines-shape: 8 integer columns, some with NAs, 4 categoricals two of which exceed nbins_cats),
+    gaussian, scaled down in rows."""
+    rng = np.random.default_rng(14)
+    n = 60000
+    cols = [rng.integers(1987, 2009, n), rng.integers(1, 13, n), rng.integers(1, 32, n), rng.integers(1, 8, n),
+            rng.integers(0, 2400, n), rng.integers(0, 2400, n), rng.integers(30, 5000, n), rng.integers(0, 600, n)]
+    cards = [300, 300, 5000, 20000]
+    cats = {}
+    for i, card in enumerate(cards):
+        z = np.minimum(rng.zipf(1.3, n) - 1, card - 1)
+        cols.append(z)
+        cats[8 + i] = card
+    X = np.stack(cols, axis=1).astype(np.float64)
+    X[rng.random(n) < 0.02, 4] = NaN
+    X[rng.random(n) < 0.02, 7] = NaN
+    eff = rng.normal(size=300)
+    y = (0.01 * (X[:, 6] - 800) / 100 + eff[X[:, 8].astype(int)] + 0.3 * (X[:, 3] == 5) + rng.normal(size=n)).astype(np.float32).astype(np.float64)
+    gm, om = _run_both(X, y, cats, distribution="gaussian", ntrees=3, max_depth=5, nbins=20, nbins_cats=1024, seed=21, capture=True)
+    h2ot_lib.compare_models(gm, om)
+    gm.close()
