@@ -50,6 +50,29 @@ __global__ void __launch_bounds__(1024) k_match(int iters, int nkeys, unsigned* 
   if(acc==0xdeadbeef) out[0]=acc;
 }
 
+// Does a warp shuffle compete with shared-memory atomics for the same pipe? 4 random ATOMS.ADD per iteration plus
+// MODE 0: nothing, 1: six LDS.32 of a 32-entry table indexed by a random lane id, 2: six SHFL from a random lane.
+template<int MODE>
+__global__ void __launch_bounds__(1024) k_mix(int iters, int words, unsigned* out){
+  extern __shared__ uint32_t sm[];
+  for(int i=threadIdx.x;i<words+256;i+=blockDim.x) sm[i]=i;
+  __syncthreads();
+  uint32_t s = blockIdx.x*1315423911u + threadIdx.x*2654435761u + 4242u;
+  uint32_t acc=0;
+  uint32_t r0=threadIdx.x*7u, r1=threadIdx.x*11u, r2=threadIdx.x*13u, r3=threadIdx.x, r4=threadIdx.x*3u, r5=threadIdx.x*5u;
+  for(int it=0; it<iters; it++){
+    uint32_t r = lcg(s);
+    uint32_t src = r & 31u;
+    if(MODE==1){ const uint32_t* t = sm + words; acc += t[src] + t[32+src] + t[64+src] + t[96+src] + t[128+src] + t[160+src]; }
+    if(MODE==2){ acc += __shfl_sync(0xffffffffu, r0, src) + __shfl_sync(0xffffffffu, r1, src) + __shfl_sync(0xffffffffu, r2, src)
+                      + __shfl_sync(0xffffffffu, r3, src) + __shfl_sync(0xffffffffu, r4, src) + __shfl_sync(0xffffffffu, r5, src); }
+    uint32_t idx = ((r>>5) + acc) % (uint32_t)(words-4);
+    atomicAdd(&sm[idx], r|1u); atomicAdd(&sm[idx+1], r); atomicAdd(&sm[idx+2], r); atomicAdd(&sm[idx+3], r);
+  }
+  __syncthreads();
+  if(threadIdx.x==0) out[blockIdx.x]=sm[0]+acc;
+}
+
 template<class F> float timeit(F f){
   cudaEvent_t a,b; cudaEventCreate(&a); cudaEventCreate(&b);
   f(); cudaDeviceSynchronize();
@@ -84,6 +107,16 @@ int main(){
     double ops=(double)ctas*256*1024;
     printf("gmem footprint %6zu KB: RED.ADD.U64 %7.1f Gops/s | RED.ADD.U32 %7.1f Gops/s | ATOM.MAX.U64 %7.1f Gops/s\n", bytes>>10, ops/ms0*1e-6, ops/ms1*1e-6, ops/ms2*1e-6);
     cudaFree(g);
+  }
+  {
+    int words=41120; size_t smem=(size_t)(words+256)*4;
+    CK(cudaFuncSetAttribute(k_mix<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220*1024));
+    CK(cudaFuncSetAttribute(k_mix<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220*1024));
+    CK(cudaFuncSetAttribute(k_mix<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220*1024));
+    float m0=timeit([&]{k_mix<0><<<sms,1024,smem>>>(2048,words,out);});
+    float m1=timeit([&]{k_mix<1><<<sms,1024,smem>>>(2048,words,out);});
+    float m2=timeit([&]{k_mix<2><<<sms,1024,smem>>>(2048,words,out);});
+    printf("mix 4xATOMS per iter: alone %.3f ms | +6 LDS.32 (random lane of a 32-entry table) %.3f ms | +6 SHFL (random lane) %.3f ms\n", m0, m1, m2);
   }
   for(int nk : {4, 64, 1024}){
     float ms=timeit([&]{k_match<<<sms,1024>>>(2048,nk,out);});
