@@ -234,6 +234,7 @@ class Engine:
         self.L = load()
         self.nrows, self.ncols, self.K = int(nrows), int(ncols), int(nclass_trees)
         self._owned = _handle is None
+        self._last_descs = ()
         if _handle is not None:
             self.h = C.c_void_p(_handle)
             return
@@ -353,7 +354,7 @@ class Engine:
         return dict(vals=vals, offsets=offs, min2=min2, maxIn=max_in, wNA=wna, has_vals=has)
 
     def find_splits(self, min_rows, min_split_improvement, k=0):
-        n_leaves = len(self._last_descs) // self.ncols
+        n_leaves = max(1, len(self._last_descs) // self.ncols)
         out = (Split * n_leaves)()
         _check(self.L.h2ot_find_splits(self.h, k, min_rows, min_split_improvement, C.cast(out, C.c_void_p)))
         return out

@@ -231,6 +231,7 @@ int finish_call(h2ot_engine* h) {
   for (Timer& t : h->timers) {
     float ms = 0;
     if (t.a && t.b && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) *t.acc += ms;
+    else cudaGetLastError();  // a call that failed half way leaves an unrecorded event behind: not an error of this call
     if (t.a) h->event_pool.push_back(t.a);
     if (t.b) h->event_pool.push_back(t.b);
   }

@@ -63,14 +63,18 @@ def run_oracle(name):
     rec = dict(init_f=m.init_f, trees=[[tree_record(m.tree(t, k)) for k in range(K)] for t in range(m.ntrees)])
     # histogram counts are exact in every implementation: digest of the w column of every captured histogram
     h = hashlib.sha256()
+    ncap = 0
     for i in range(m.ncaptures()):
         c = m.capture(i)
+        if c["nleaves"] == 0:  # the reference's pass over a tree with no undecided leaf left: builds nothing (see tests/h2ot_lib.py)
+            continue
+        ncap += 1
         h.update(c["nids"].tobytes())
         for v in c["vals"]:
             if v.size:
                 h.update(np.ascontiguousarray(v[0::3]).tobytes())
     rec["levels_digest"] = h.hexdigest()
-    rec["ncaptures"] = m.ncaptures()
+    rec["ncaptures"] = ncap
     rec["F_f32_digest"] = [hashlib.sha256(m.F(k).astype(np.float32).tobytes()).hexdigest() for k in range(K)]
     rec["F_head"] = [[float(v) for v in m.F(k)[:32]] for k in range(K)]
     rec["F_sum"] = [float(np.sum(m.F(k))) for k in range(K)]

@@ -51,10 +51,15 @@ def compare_models(gm, om, K=1, check_levels=True, rel=1e-6):
     assert gm.init_f == om.init_f or abs(gm.init_f - om.init_f) <= 1e-15 * max(1.0, abs(om.init_f))
     stats = dict(levels=0, hists=0, max_rel=0.0, n_vals=0, n_vals_diff=0)
     if check_levels:
-        assert gm.ncaptures() == om.ncaptures()
+        # The reference launches ScoreBuildHistogram2 even when a tree has no undecided leaf left (T/SharedTree.java:671-683):
+        # that pass builds nothing and only walks rows of dead-end nodes back to their parents, which GammaPass / CollectPreds
+        # undo anyway (they take "the parent's decision"). The engine's host driver skips it, so such captures are dropped here.
+        ocaps = [om.capture(i) for i in range(om.ncaptures())]
+        ocaps = [c for c in ocaps if c["nleaves"] > 0]
+        assert gm.ncaptures() == len(ocaps)
         for i in range(gm.ncaptures()):
             gi = gm.capture_info(i)
-            oc = om.capture(i)
+            oc = ocaps[i]
             assert (gi["tree"], gi["k"], gi["leaf"], gi["nleaves"]) == (oc["tree"], oc["k"], oc["leaf"], oc["nleaves"]), (gi, i)
             assert np.array_equal(gm.capture_nids(i), oc["nids"]), "row->nid assignment differs at capture %d" % i
             ncols = gm.ncols
