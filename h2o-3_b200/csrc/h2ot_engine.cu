@@ -977,10 +977,49 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   if (leaf_offset > 0 && t.n_nodes == 0) H2OT_FAIL(H2OT_ERR_INVALID, "no decided nodes uploaded for a non-root level");
   TRY(t.nodes.ensure(1));
   TRY(t.bitsets.ensure(16));
-  TRY(plan_level(h, t, n_leaves, descs));
   t.L = n_leaves;
   t.leaf_offset = leaf_offset;
   const size_t LC = (size_t)n_leaves * h->C;
+  // Payload of the level, laid out [rows per leaf : L][w, wY, wYY per bin : 3 x bins][min/max keys : 2 x LC]. Its size needs
+  // only the bin counts, so it is cleared and score_decide is launched before the (host-side) planning of the histogram pass.
+  {
+    int64_t bins = 0;
+    for (size_t i = 0; i < LC; i++) {
+      if (!(descs[i].flags & H2OT_DESC_ACTIVE)) continue;
+      // validated here, before any kernel touches the row state
+      if (descs[i].nbin < 1 || descs[i].nbin > 65534) H2OT_FAIL(H2OT_ERR_INVALID, "nbin out of range (1..65534)");
+      if (!(descs[i].step > 0) || std::isinf(descs[i].step)) H2OT_FAIL(H2OT_ERR_INVALID, "histogram step must be positive and finite");
+      bins += descs[i].nbin + 1;
+    }
+    const size_t ns = (size_t)bins * 3 + n_leaves, nm = LC * 2;
+    t.in_xbuf = false;
+    if (h->xr_enabled && !h->xr_failed && h->nccl.world > 1) {
+      const int rc = xr_ensure(h, ns + nm);
+      if (rc == H2OT_OK) {
+        t.sums = reinterpret_cast<long long*>(h->xr_buf);
+        t.mm = h->xr_buf + ns;
+        t.in_xbuf = true;
+      } else if (rc != H2OT_ERR_UNSUPPORTED) {
+        return rc;
+      }
+    }
+    if (!t.in_xbuf) {
+      TRY(t.d_sums.ensure(ns + nm));
+      t.sums = t.d_sums.p;
+      t.mm = reinterpret_cast<unsigned long long*>(t.d_sums.p + ns);
+    }
+    CUDA_TRY(cudaMemsetAsync(t.sums, 0, (ns + nm) * sizeof(long long), h->stream));
+  }
+  // K2a
+  {
+    ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
+                 reinterpret_cast<unsigned long long*>(t.sums)};
+    TRY(t_begin(h, &h->stats.ms_score));
+    score_decide_kernel<<<grid_for(h, h->n_pad / 4, 256, 16), 256, 0, h->stream>>>(sa);
+    h->stats.launches++;
+    TRY(t_end(h));
+  }
+  TRY(plan_level(h, t, n_leaves, descs));
   // this level's descriptors, groups and column lists travel in ONE copy from pinned staging
   {
     const size_t b_descs = LC * sizeof(DescDev), b_groups = std::max<size_t>(1, t.h_groups.size()) * sizeof(GroupDev);
@@ -1003,35 +1042,6 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     t.p_group_cols = reinterpret_cast<int32_t*>(t.d_lvl.p + b_descs + b_groups);
     TRY(h2d(h, t.d_lvl.p, t.lvl_host, total));
   }
-  {
-    const size_t ns = (size_t)t.total_bins * 3 + n_leaves, nm = LC * 2;
-    t.in_xbuf = false;
-    if (h->xr_enabled && !h->xr_failed && h->nccl.world > 1) {
-      const int rc = xr_ensure(h, ns + nm);
-      if (rc == H2OT_OK) {
-        t.sums = reinterpret_cast<long long*>(h->xr_buf);
-        t.mm = h->xr_buf + ns;
-        t.in_xbuf = true;
-      } else if (rc != H2OT_ERR_UNSUPPORTED) {
-        return rc;
-      }
-    }
-    if (!t.in_xbuf) {  // [sums | min/max keys] contiguous either way: one clear
-      TRY(t.d_sums.ensure(ns + nm));
-      t.sums = t.d_sums.p;
-      t.mm = reinterpret_cast<unsigned long long*>(t.d_sums.p + ns);
-    }
-    CUDA_TRY(cudaMemsetAsync(t.sums, 0, (ns + nm) * sizeof(long long), h->stream));
-  }
-
-  // K2a
-  ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
-               reinterpret_cast<unsigned long long*>(t.sums + (size_t)t.total_bins * 3)};
-  TRY(t_begin(h, &h->stats.ms_score));
-  score_decide_kernel<<<grid_for(h, h->n_pad / 4, 256, 16), 256, 0, h->stream>>>(sa);
-  h->stats.launches++;
-  TRY(t_end(h));
-
   // K2b
   HistArgs ha{};
   ha.n_pad = h->n_pad;
@@ -1045,7 +1055,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   ha.cols = h->d_cols.p;
   ha.descs = t.p_descs;
   ha.groups = t.p_groups;
-  ha.acc = t.sums;
+  ha.acc = t.sums + n_leaves;
   ha.minmax = t.mm;
   ha.sy = std::ldexp(1.0, t.ey);
   ha.syy = std::ldexp(1.0, t.eyy);
@@ -1166,9 +1176,9 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   fa.L = t.L;
   fa.C = h->C;
   fa.descs = t.p_descs;
-  fa.acc = t.sums;
+  fa.acc = t.sums + t.L;
   fa.minmax = t.mm;
-  fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.sums + (size_t)t.total_bins * 3);
+  fa.leaf_rows = reinterpret_cast<const unsigned long long*>(t.sums);
   fa.vals = t.d_vals.p;
   fa.min2 = t.p_min2;
   fa.maxIn = t.p_maxIn;
