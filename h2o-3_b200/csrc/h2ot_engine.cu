@@ -854,7 +854,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
   auto fixed_bytes = [&](int ncg, int storage) {
     return (size_t)ncg * L * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
+           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
   };
   const size_t full_budget = (size_t)h->max_smem_optin;
   // the kernel runs one 1024-thread CTA per SM (64 registers/thread), so a CTA may use the whole opt-in carve-out

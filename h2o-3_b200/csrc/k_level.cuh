@@ -144,8 +144,10 @@ struct HistArgs {
 // p = gc * L + leaf. A warp's lanes sit in different leaves once the tree is a few levels deep; the odd stride puts the
 // same word of up to 32 different records into 32 different banks (one wavefront per lookup), whereas 16/32-byte aligned
 // records would serialise on the few bank-quads they start in.
-enum { kTMinLo = 0, kTMinHi, kTStepLo, kTStepHi, kTPlace, kTNbin, kTKmin, kTKmax, kTStride = 9 };
-//   kTPlace: word offset of bin 0 in the CTA's histogram (kInactive: no histogram for this pair)
+enum { kTPlace = 0, kTMinLo, kTMinHi, kTStepLo, kTStepHi, kTKmin, kTKmax, kTStride = 7 };
+//   kTPlace: bits 0..15 word offset of bin 0 in the CTA's histogram (0xFFFF: no histogram for this pair), bits 16..31 nbin
+//   kTMinLo / kTMinHi: _min as fp64 halves -- or, for a column all of whose minima are fp32-exact (always the case for
+//                      f32-stored columns: minima are observed values or float split points), the float bits in kTMinLo alone
 //   kTKmin / kTKmax: ~key32 / key32 of the smallest / largest value seen (0: none) -- F32 / U8 / U16 storage
 struct __align__(16) MinMaxS {  // 64-bit keys, only for F64-stored columns
   unsigned long long mn, mx;
@@ -153,7 +155,7 @@ struct __align__(16) MinMaxS {  // 64-bit keys, only for F64-stored columns
 struct Double4 {
   double2 a, b;
 };
-constexpr uint32_t kInactive = 0xFFFFFFFFu;
+constexpr uint32_t kInactive = 0xFFFFu;  // place field of a pair without a histogram
 
 constexpr int kHistThreads = 1024;
 constexpr int kRowsPerThread = 4;
@@ -231,18 +233,21 @@ struct RecRegs {  // one descriptor record in registers (root level: the same re
   int nbin;
   double mn, st;
 };
+template <bool MN32>
 __device__ __forceinline__ RecRegs load_rec(uint32_t rec) {
   RecRegs r;
-  r.place = lds_u32(rec + kTPlace * 4);
-  r.nbin = (int)lds_u32(rec + kTNbin * 4);
-  r.mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
+  const uint32_t pn = lds_u32(rec + kTPlace * 4);
+  r.place = pn & 0xFFFFu;
+  r.nbin = (int)(pn >> 16);
+  if (MN32) r.mn = (double)__uint_as_float(lds_u32(rec + kTMinLo * 4));
+  else r.mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
   r.st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
   r.kmin = lds_u32(rec + kTKmin * 4);
   r.kmax = lds_u32(rec + kTKmax * 4);
   return r;
 }
 
-template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, int J0, int R>
+template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, bool MN32, int J0, int R>
 __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, const RecRegs& shared_rec,
                                            const int (&leaf)[4],
                                            const double (&x)[4], const bool (&na)[4], const uint32_t (&key)[4],
@@ -255,7 +260,7 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
     const uint32_t rec = tab_a + (uint32_t)p * (kTStride * 4);
     RecRegs rr;
     if (ONE_LEAF) rr = shared_rec;
-    else rr = load_rec(rec);
+    else rr = load_rec<MN32>(rec);
     const uint32_t place = rr.place;
     const uint32_t on = (row_on && place != kInactive) ? 1u : 0u;
     const int nbin = rr.nbin;
@@ -320,15 +325,18 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   MinMaxS* mmS = reinterpret_cast<MinMaxS*>(smem_raw);
   ColRef* colS = reinterpret_cast<ColRef*>(mmS + (KEY64 ? npairs : 0));
   int32_t* cidxS = reinterpret_cast<int32_t*>(colS + ncg);
-  uint32_t* T = reinterpret_cast<uint32_t*>(cidxS + ncg + (ncg & 1));
+  int32_t* mn32S = cidxS + ncg;  // per group column: 1 when every active minimum of the column is fp32-exact
+  uint32_t* T = reinterpret_cast<uint32_t*>(mn32S + ncg);
   uint32_t* hist = T + (size_t)kTStride * npairs;
   uint32_t* sink = hist + grp.smem_words;
 
   for (int i = threadIdx.x; i < ncg; i += blockDim.x) {
     const int c = a.group_cols[grp.cols_off + i];
     cidxS[i] = c;
+    mn32S[i] = 1;
     colS[i] = a.cols[c];
   }
+  __syncthreads();
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
     const int gc = p / a.L, l = p - gc * a.L;
     const DescDev d = a.descs[(size_t)l * a.C + a.group_cols[grp.cols_off + gc]];
@@ -337,11 +345,19 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     r[kTMinHi] = (uint32_t)__double2hiint(d.min);
     r[kTStepLo] = (uint32_t)__double2loint(d.step);
     r[kTStepHi] = (uint32_t)__double2hiint(d.step);
-    r[kTPlace] = d.nbin < 0 ? kInactive : (uint32_t)d.smem_off;
-    r[kTNbin] = (uint32_t)max(d.nbin, 1);
+    r[kTPlace] = (d.nbin < 0 ? kInactive : (uint32_t)d.smem_off) | ((uint32_t)max(d.nbin, 1) << 16);
     r[kTKmin] = 0u;
     r[kTKmax] = 0u;
     if (KEY64) { mmS[p].mn = 0ULL; mmS[p].mx = 0ULL; }
+    if (d.nbin >= 0 && (double)(float)d.min != d.min) mn32S[gc] = 0;  // benign race: every writer stores 0
+  }
+  __syncthreads();
+  for (int p = threadIdx.x; p < npairs; p += blockDim.x) {  // columns with fp32-exact minima keep the float bits in kTMinLo
+    const int gc = p / a.L;
+    if (mn32S[gc]) {
+      uint32_t* r = T + (size_t)p * kTStride;
+      r[kTMinLo] = __float_as_uint((float)__hiloint2double((int)r[kTMinHi], (int)r[kTMinLo]));
+    }
   }
   for (int i = threadIdx.x; i < grp.smem_words + 32 * WPB; i += blockDim.x) hist[i] = 0u;
   __syncthreads();
@@ -420,10 +436,17 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
         for (int j = 0; j < 4; j++) na[j] = isnan(x[j]);
       }
       RecRegs rec0{};
-      if (ONE_LEAF) rec0 = load_rec(tab_a + (uint32_t)pbase * (kTStride * 4));  // root level: one record per column
-      hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
-      if (kItemsInFlight < 4)
-        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+      if (mn32S[gc]) {  // uniform per column
+        if (ONE_LEAF) rec0 = load_rec<true>(tab_a + (uint32_t)pbase * (kTStride * 4));  // root level: one record per column
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+        if (kItemsInFlight < 4)
+          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+      } else {
+        if (ONE_LEAF) rec0 = load_rec<false>(tab_a + (uint32_t)pbase * (kTStride * 4));
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+        if (kItemsInFlight < 4)
+          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+      }
     }
   }
   __syncthreads();
@@ -432,9 +455,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   for (int p = warp; p < npairs; p += nwarps) {
     const uint32_t* r = T + (size_t)p * kTStride;
-    const uint32_t place = r[kTPlace];
+    const uint32_t place = r[kTPlace] & 0xFFFFu;
     if (place == kInactive) continue;
-    const int nbin = (int)r[kTNbin];
+    const int nbin = (int)(r[kTPlace] >> 16);
     const int gc = p / a.L, l = p - gc * a.L;
     const size_t lc = (size_t)l * a.C + cidxS[gc];
     const DescDev dd = a.descs[lc];
