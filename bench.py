@@ -261,6 +261,7 @@ def run_b200(args):
     barrier()
     s0 = eng.stats()
     t0s = gm.timing()
+    t0s = type('T', (), dict(levels=t0s.levels, level_s=t0s.level_s, total_s=t0s.total_s, hist_rows_cols=t0s.hist_rows_cols))
     snap0 = {f: getattr(s0, f) for f, _ in s0._fields_}
     rc0 = t0s.hist_rows_cols
     clk = ClockSampler(local)
@@ -299,7 +300,10 @@ def run_b200(args):
                 "kernel_rows_x_cols_per_s": d["hist_rows_cols"] / (hist_ms * 1e-3) if hist_ms > 0 else 0.0,
                 "stage_ms_per_step": {k: d[k] / args.steps for k in ("ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals",
                                                                         "ms_gamma", "ms_addtree")}}
-    levels_per_step = (gm.timing().levels - t0s.levels) / args.steps
+    t1s = gm.timing()
+    levels_per_step = (t1s.levels - t0s.levels) / args.steps
+    roofline["host_ms_per_step"] = {"inside_level_calls": 1e3 * (t1s.level_s - t0s.level_s) / args.steps,
+                                    "whole_step_wall": 1e3 * (t1s.total_s - t0s.total_s) / args.steps}
     gm.close()
 
     # ---------------- end-to-end arm: whole job from pinned host buffers through the public API
