@@ -336,10 +336,11 @@ def run_b200(args):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "sec_per_tree": ms * 1e-3 / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int64 fixed-point accumulation of f64 products (bins computed in f64)", "data": "synthetic",
+            "vs_baseline": None, "dtype": "int64", "data": "synthetic",
             "config": {"workload": "GBM bernoulli Higgs-shape %dx%d, max_depth 6, nbins 256, nbins_top_level 1024 (BASELINE configs[1])" % (N, NCOLS),
                        "rows": N, "cols": NCOLS, "levels_per_step": levels_per_step, "parallelism": "rows sharded over %d GPU(s)" % world,
                        "l2": "inputs larger than L2 (frame %.2f GB resident)" % (N * NCOLS * 4 / 1e9),
+                       "arithmetic": "bins in f64 (reference formula), sums of w, w*y, w*y*y as int64 fixed point, float-cast like reducePrecision",
                        **{k: PARAMS[k] for k in ("max_depth", "nbins", "nbins_top_level")}},
             "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
         }

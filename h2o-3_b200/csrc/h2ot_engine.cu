@@ -80,22 +80,18 @@ struct TreeState {  // per class-tree k
   std::vector<int32_t> h_group_cols;
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
   int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
-  DBuf<int32_t> d_group_cols;
   int n_smem_groups = 0;
   size_t smem_bytes = 0;
   int64_t total_bins = 0, total_vals = 0;
   int active_cols = 0;
-  DBuf<DescDev> d_descs;
   DBuf<unsigned char> d_lvl;  // per-level upload: [DescDev LC][GroupDev G][int32 group columns]
   unsigned char* lvl_host = nullptr;
   size_t lvl_host_cap = 0;
   DescDev* p_descs = nullptr;
   GroupDev* p_groups = nullptr;
   int32_t* p_group_cols = nullptr;
-  DBuf<GroupDev> d_groups;
   DBuf<long long> d_sums;  // [3*total_bins | L leaf_rows]
-  DBuf<unsigned long long> d_minmax;
-  long long* sums = nullptr;          // this level's accumulators: d_sums / d_minmax, or the peer-mapped exchange buffer
+  long long* sums = nullptr;          // this level's payload: d_sums, or the peer-mapped exchange buffer
   unsigned long long* mm = nullptr;
   bool in_xbuf = false;
   DBuf<double> d_vals;
@@ -390,7 +386,7 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.code) cudaFree(t.code);
     t.nodes.release(); t.bitsets.release(); t.d_lvl.release();
     if (t.lvl_host) cudaFreeHost(t.lvl_host);
-    t.d_sums.release(); t.d_minmax.release(); t.d_vals.release(); t.d_pack.release();
+    t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release();
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
