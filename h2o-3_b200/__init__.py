@@ -103,7 +103,7 @@ class GbmTiming(C.Structure):
 ENGINE_SYMBOLS = [
     "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
-    "h2ot_init_model", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
+    "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
@@ -142,6 +142,7 @@ def load():
     L.h2ot_finalize_frame.argtypes = [vp]
     L.h2ot_column_info_get.argtypes = [vp, i32, C.POINTER(ColumnInfo)]
     L.h2ot_init_model.argtypes = [vp, vp, C.POINTER(i64)]
+    L.h2ot_initial_stats.argtypes = [vp, C.POINTER(dbl), C.POINTER(dbl), vp, C.POINTER(dbl)]
     for n in ("h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_get_nids", "h2ot_set_nids"):
         getattr(L, n).argtypes = [vp, i32, vp]
     L.h2ot_set_work.argtypes = [vp, i32, vp, dbl]

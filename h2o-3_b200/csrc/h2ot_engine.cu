@@ -537,6 +537,41 @@ int h2ot_init_model(h2ot_engine* h, const double* init_f, int64_t* out_skipped) 
   return H2OT_OK;
 }
 
+int h2ot_initial_stats(h2ot_engine* h, double* out_num, double* out_den, double* out_class_weight, double* out_abs_max) {
+  CHECK_ENGINE(h);
+  const int grid = grid_for(h, h->n, 256);
+  const int nc = h->cfg.nclass > 1 ? h->cfg.nclass : 0;
+  DBuf<double> tmp;
+  TRY(tmp.ensure((size_t)grid * 2 + nc + 1));
+  CUDA_TRY(cudaMemsetAsync(tmp.p, 0, ((size_t)grid * 2 + nc + 1) * sizeof(double), h->stream));
+  InitStatsArgs a{h->n, h->cfg.nclass, 0, h->resp, h->w, h->off, tmp.p, tmp.p + (size_t)grid * 2,
+                  reinterpret_cast<unsigned int*>(tmp.p + (size_t)grid * 2 + nc)};
+  init_stats_kernel<<<grid, 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  std::vector<double> hbuf((size_t)grid * 2 + nc + 1);
+  TRY(d2h(h, hbuf.data(), tmp.p, hbuf.size() * sizeof(double)));
+  const int rc = finish_call(h);
+  tmp.release();
+  if (rc != H2OT_OK) return rc;
+  double num = 0, den = 0;
+  for (int b = 0; b < grid; b++) {  // fixed order
+    num += hbuf[2 * (size_t)b];
+    den += hbuf[2 * (size_t)b + 1];
+  }
+  if (out_num) *out_num = num;
+  if (out_den) *out_den = den;
+  if (out_class_weight)
+    for (int c = 0; c < nc; c++) out_class_weight[c] = hbuf[(size_t)grid * 2 + c];
+  if (out_abs_max) {
+    unsigned int bits;
+    memcpy(&bits, &hbuf[(size_t)grid * 2 + nc], sizeof(bits));
+    float f;
+    memcpy(&f, &bits, sizeof(f));
+    *out_abs_max = (double)f;
+  }
+  return H2OT_OK;
+}
+
 int h2ot_set_predictions(h2ot_engine* h, int32_t k, const double* f) {
   CHECK_ENGINE(h);
   CHECK_K(h, k);

@@ -280,7 +280,7 @@ struct h2ot_gbm {
   bool has_w = false, has_off = false, inited = false;
   int world = 1;
   std::vector<ColMeta> cols;
-  std::vector<double> y, w, off;  // host copies of the O(rows) scalars needed once for init_f
+  bool have_y = false, have_w = false, have_off = false;
   double init_f = 0;
   std::vector<double> prior_class_dist;  // DRF classification (Model.Output._priorClassDist)
   double work_bound = 1.0;               // DRF: max |Work| (fixed for the whole build)
@@ -766,19 +766,19 @@ int h2ot_gbm_set_column(h2ot_gbm* g, int32_t col, const double* values, int32_t 
 }
 int h2ot_gbm_set_response(h2ot_gbm* g, const double* y) {
   if (!g || !y) GFAIL(H2OT_ERR_INVALID, "null argument");
-  g->y.assign(y, y + g->nrows);
+  g->have_y = true;
   return h2ot_load_response(g->eng, 0, g->nrows, y);
 }
 int h2ot_gbm_set_weights(h2ot_gbm* g, const double* w) {
   if (!g || !w) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (!g->has_w) GFAIL(H2OT_ERR_INVALID, "created without weights");
-  g->w.assign(w, w + g->nrows);
+  g->have_w = true;
   return h2ot_load_weights(g->eng, 0, g->nrows, w);
 }
 int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o) {
   if (!g || !o) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (!g->has_off) GFAIL(H2OT_ERR_INVALID, "created without offset");
-  g->off.assign(o, o + g->nrows);
+  g->have_off = true;
   return h2ot_load_offset(g->eng, 0, g->nrows, o);
 }
 
@@ -791,9 +791,9 @@ int h2ot_gbm_comm_init(h2ot_gbm* g, int32_t world_size, int32_t rank, const uint
 int h2ot_gbm_init(h2ot_gbm* g) {
   if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (g->inited) return H2OT_OK;
-  if ((int64_t)g->y.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "response not set");
-  if (g->has_w && (int64_t)g->w.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "weights not set");
-  if (g->has_off && (int64_t)g->off.size() != g->nrows) GFAIL(H2OT_ERR_INVALID, "offset not set");
+  if (!g->have_y) GFAIL(H2OT_ERR_INVALID, "response not set");
+  if (g->has_w && !g->have_w) GFAIL(H2OT_ERR_INVALID, "weights not set");
+  if (g->has_off && !g->have_off) GFAIL(H2OT_ERR_INVALID, "offset not set");
   GTRY(h2ot_finalize_frame(g->eng));
   const int C = g->ncols;
   // rollups, merged over ranks: [min as -min | max | nacnt | not_int]
@@ -830,37 +830,25 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   else if (g->p.mtries == -1) g->mtry = g->nclass > 1 ? std::max(d2i(std::sqrt((double)C)), 1) : std::max(C / 3, 1);
   else g->mtry = g->p.mtries;
   if (g->mtry < 1 || g->mtry > C) GFAIL(H2OT_ERR_INVALID, "computed mtry outside 1..ncols");
-  if (drf) {
-    // class prior and the bound of the work column, merged over ranks
+  // InitialValue (T/SharedTree.java:1138-1185) and, for DRF, the class prior and the bound of the work column: one device
+  // reduction over the resident response / weights / offset, merged over ranks
+  double nd[2] = {0, 0};
+  {
     std::vector<double> cls((size_t)std::max(1, g->nclass) + 1, 0.0);
     double ymax = 0;
-    for (int64_t i = 0; i < g->nrows; i++) {
-      if (std::isnan(g->y[i])) continue;
-      const double w = g->has_w ? g->w[i] : 1.0;
-      if (g->nclass > 1) {
-        const int c = (int)g->y[i];
-        if (c >= 0 && c < g->nclass) cls[c] += w;
-        cls[g->nclass] += w;
-      } else {
-        ymax = std::max(ymax, (double)std::fabs((float)g->y[i]));
-      }
+    GTRY(h2ot_initial_stats(g->eng, &nd[0], &nd[1], g->nclass > 1 ? cls.data() : nullptr, &ymax));
+    GTRY(allreduce(g, nd, 2, 0));
+    if (drf) {
+      GTRY(allreduce(g, cls.data(), (int64_t)g->nclass, 0));
+      GTRY(allreduce(g, &ymax, 1, 1));
+      g->prior_class_dist.assign(std::max(1, g->nclass), 0.0);
+      double tot = 0;
+      for (int c = 0; c < g->nclass; c++) tot += cls[c];
+      if (g->nclass > 1)
+        for (int c = 0; c < g->nclass; c++) g->prior_class_dist[c] = cls[c] / tot;
+      g->work_bound = g->nclass > 1 ? 1.0 : (ymax > 0 ? ymax : 1.0);
     }
-    GTRY(allreduce(g, cls.data(), (int64_t)cls.size(), 0));
-    GTRY(allreduce(g, &ymax, 1, 1));
-    g->prior_class_dist.assign(std::max(1, g->nclass), 0.0);
-    if (g->nclass > 1)
-      for (int c = 0; c < g->nclass; c++) g->prior_class_dist[c] = cls[c] / cls[g->nclass];
-    g->work_bound = g->nclass > 1 ? 1.0 : (ymax > 0 ? ymax : 1.0);
   }
-  double nd[2] = {0, 0};  // InitialValue (T/SharedTree.java:1138-1185)
-  for (int64_t i = 0; i < g->nrows; i++) {
-    if (std::isnan(g->y[i])) continue;
-    const double w = g->has_w ? g->w[i] : 1.0;
-    if (w == 0) continue;
-    nd[0] += w * (g->y[i] - (g->has_off ? g->off[i] : 0.0));
-    nd[1] += w;
-  }
-  GTRY(allreduce(g, nd, 2, 0));
   const double mean = nd[0] / nd[1];
   if (drf) g->init_f = g->nclass > 1 ? 0 : mean;  // T/drf/DRF.java:131
   else if (g->nclass > 2) g->init_f = 0;
@@ -874,10 +862,6 @@ int h2ot_gbm_init(h2ot_gbm* g) {
     int64_t skipped = 0;
     GTRY(h2ot_init_model(g->eng, f0.data(), &skipped));
   }
-  // the O(rows) host copies are not needed any more
-  std::vector<double>().swap(g->y);
-  std::vector<double>().swap(g->w);
-  std::vector<double>().swap(g->off);
   g->inited = true;
   return H2OT_OK;
 }

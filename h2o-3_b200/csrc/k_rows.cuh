@@ -90,6 +90,55 @@ __global__ void __launch_bounds__(256) init_rows_kernel(InitArgs a) {
   if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(a.skipped, cnt);
 }
 
+// ------------------------------------------------------------------------------------------ initial value
+// SharedTree.InitialValue (T/SharedTree.java:1138-1185): sum w (y - offset) and sum w over rows with a response and w != 0,
+// plus what DRF's set-up needs: weight per class and max |(float) y|. Block partials are written out and summed by the host in
+// block order, so the result does not depend on scheduling.
+struct InitStatsArgs {
+  int64_t n;
+  int32_t nclass, pad;
+  const double* resp;
+  const double* w;
+  const double* off;
+  double* partial;         // [gridDim.x][2] : num, den
+  double* class_w;         // [nclass] (nclass > 1), atomically accumulated
+  unsigned int* ymax_bits; // float bits of max |(float) y|
+};
+__global__ void __launch_bounds__(256) init_stats_kernel(InitStatsArgs a) {
+  double num = 0, den = 0;
+  float ymax = 0.f;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    const double y = a.resp[row];
+    if (isnan(y)) continue;
+    const double wv = a.w ? a.w[row] : 1.0;
+    ymax = fmaxf(ymax, fabsf((float)y));
+    if (a.nclass > 1) {
+      const int c = (int)y;
+      if (c >= 0 && c < a.nclass && wv != 0.0) atomicAdd(&a.class_w[c], wv);
+    }
+    if (wv == 0.0) continue;
+    num += __dmul_rn(wv, __dsub_rn(y, a.off ? a.off[row] : 0.0));
+    den += wv;
+  }
+  __shared__ double s_num[256], s_den[256];
+  s_num[threadIdx.x] = num;
+  s_den[threadIdx.x] = den;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      s_num[threadIdx.x] += s_num[threadIdx.x + o];
+      s_den[threadIdx.x] += s_den[threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    a.partial[2 * blockIdx.x] = s_num[0];
+    a.partial[2 * blockIdx.x + 1] = s_den[0];
+  }
+  for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+  if ((threadIdx.x & 31) == 0 && ymax > 0.f) atomicMax(a.ymax_bits, __float_as_uint(ymax));
+}
+
 // ------------------------------------------------------------------------------------------ residuals
 struct ResidArgs {
   int64_t n;

@@ -156,6 +156,10 @@ int h2ot_column_info_get(h2ot_engine* h, int32_t col, h2ot_column_info* out);
 /* ---- model state sync with the Java work vecs (Tree_k / Work_k / NIDs_k; T/SharedTree.java:364-385,464-475) */
 /* GBM.initializeModelSpecifics (T/gbm/GBM.java:282-311): Tree_k <- init_f[k]; rows with w==0 or NA response <- DECIDED_ROW. */
 int h2ot_init_model(h2ot_engine* h, const double* init_f /*[K]*/, int64_t* out_skipped);
+/* SharedTree.InitialValue (T/SharedTree.java:1138-1185) on the resident response / weights / offset: num = sum w (y - offset),
+ * den = sum w over rows with a response and w != 0 (local rows; sum over ranks before dividing). Optional extras for DRF's set-up:
+ * class_weight[nclass] = sum of w per response class, abs_max = max |(float) y|. All outputs nullable. */
+int h2ot_initial_stats(h2ot_engine* h, double* out_num, double* out_den, double* out_class_weight, double* out_abs_max);
 int h2ot_set_predictions(h2ot_engine* h, int32_t k, const double* f);
 int h2ot_get_predictions(h2ot_engine* h, int32_t k, double* f);
 int h2ot_get_work(h2ot_engine* h, int32_t k, double* work);
@@ -181,7 +185,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
                      const h2ot_hist_desc* descs);
 /* Device buffers of the level just built, for the cross-rank exchange that replaces MRTask.reduce /
  * ScoreBuildHistogram.reduce / DHistogram.add (T/ScoreBuildHistogram.java:74-88, T/DHistogram.java:434-447):
- * sums[n_sums] int64 (allreduce SUM) and minmax[n_minmax] uint64 order-preserving keys laid out so that
+ * sums[n_sums] int64 (allreduce SUM; rows per leaf first, then w, wY, wYY per bin) and minmax[n_minmax] uint64 order-preserving keys laid out so that
  * an allreduce MAX merges both bounds (min is stored complemented). Single rank: skip. */
 int h2ot_level_buffers(h2ot_engine* h, int32_t k, void** d_sums, int64_t* n_sums, void** d_minmax, int64_t* n_minmax);
 /* Built-in exchange over NCCL (h2ot_comm_init must have been called); no-op for world size 1. */
