@@ -145,6 +145,7 @@ struct h2ot_engine {
   double* resp_staging = nullptr;
   double* oobt = nullptr;  // DRF: OUT_BAG_TREES column
   double* staging_all = nullptr;
+  unsigned char* col_block = nullptr;  // all encoded columns (each 256-byte aligned)
   double w_max = 1.0;
   bool frame_final = false;
   std::vector<TreeState> ts;
@@ -369,8 +370,9 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   if (h->nccl.comm && h->nccl.CommDestroy && !h->nccl.shared) h->nccl.CommDestroy(h->nccl.comm);
   for (Column& c : h->cols) {
-    if (c.data) cudaFree(c.data);
+    c.data = nullptr;
   }
+  if (h->col_block) cudaFree(h->col_block);
   if (h->staging_all) cudaFree(h->staging_all);
   if (h->resp) cudaFree(h->resp);
   if (h->w) cudaFree(h->w);
@@ -455,6 +457,24 @@ int h2ot_finalize_frame(h2ot_engine* h) {
   CUDA_TRY(cudaMemcpyAsync(ru.data(), h->d_rollup.p, ru.size() * sizeof(RollupDev), cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   std::vector<ColRef> refs(C);
+  std::vector<size_t> col_off(C, 0);
+  size_t block_bytes = 0;
+  for (int ci = 0; ci < C; ci++) {  // storage decision first, so that all encoded columns share ONE allocation
+    const RollupDev& r = ru[ci];
+    const bool any = r.max_key != 0;
+    const bool is_int = !r.not_int;
+    int storage = r.not_f32 ? H2OT_STORE_F64 : H2OT_STORE_F32;
+    if (any && is_int) {
+      const double span = dkey_inv(r.max_key) - dkey_inv(~r.min_key);
+      if (span < 255) storage = H2OT_STORE_U8;
+      else if (span < 65535) storage = H2OT_STORE_U16;
+    }
+    h->cols[ci].storage = storage;
+    const size_t esz = storage == H2OT_STORE_F32 ? 4 : storage == H2OT_STORE_F64 ? 8 : storage == H2OT_STORE_U8 ? 1 : 2;
+    col_off[ci] = block_bytes;
+    block_bytes += ((size_t)h->n_pad * esz + 255) / 256 * 256;
+  }
+  CUDA_TRY(cudaMalloc(&h->col_block, std::max<size_t>(block_bytes, 256)));
   for (int ci = 0; ci < C; ci++) {
     Column& c = h->cols[ci];
     const RollupDev& r = ru[ci];
@@ -473,8 +493,7 @@ int h2ot_finalize_frame(h2ot_engine* h) {
     c.storage = storage;
     c.base = base;
     c.info.storage = storage;
-    const size_t esz = storage == H2OT_STORE_F32 ? 4 : storage == H2OT_STORE_F64 ? 8 : storage == H2OT_STORE_U8 ? 1 : 2;
-    CUDA_TRY(cudaMalloc(&c.data, (size_t)h->n_pad * esz));
+    c.data = h->col_block + col_off[ci];
     encode_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(c.staging, h->n, h->n_pad, storage, base, c.data);
     h->stats.launches++;
     c.finalized = true;
