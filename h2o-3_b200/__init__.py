@@ -106,7 +106,7 @@ ENGINE_SYMBOLS = [
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
-    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
+    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_hist_column_noalloc",
@@ -115,7 +115,7 @@ GBM_SYMBOLS = [
     "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
-    "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
+    "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
     "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
 ]
 
@@ -189,6 +189,8 @@ def load():
     L.h2ot_gbm_predictions.argtypes = [vp, i32, vp]
     L.h2ot_gbm_varimp.argtypes = [vp, vp]
     L.h2ot_gbm_oobt.argtypes = [vp, vp]
+    L.h2ot_gbm_score.argtypes = [vp, C.POINTER(dbl), C.POINTER(dbl)]
+    L.h2ot_score_metrics.argtypes = [vp, vp]
     L.h2ot_gbm_timing_get.argtypes = [vp, C.POINTER(GbmTiming)]
     L.h2ot_gbm_engine.argtypes = [vp]
     L.h2ot_gbm_engine.restype = vp
@@ -511,6 +513,12 @@ class GBM:
         out = np.empty(self.nrows, dtype=np.float64)
         _check(self.L.h2ot_gbm_oobt(self.g, _p(out)))
         return out
+
+    def score(self):
+        """Training MSE / logloss computed on the device from the resident Tree_k columns (hex.tree.Score)."""
+        mse, ll = C.c_double(), C.c_double()
+        _check(self.L.h2ot_gbm_score(self.g, C.byref(mse), C.byref(ll)))
+        return dict(mse=mse.value, logloss=ll.value)
 
     def varimp(self):
         out = np.zeros(self.ncols, dtype=np.float32)

@@ -1411,6 +1411,31 @@ int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_
   return finish_call(h);
 }
 
+int h2ot_score_metrics(h2ot_engine* h, h2ot_metrics* out) {
+  CHECK_ENGINE(h);
+  if (!out) H2OT_FAIL(H2OT_ERR_INVALID, "null out");
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  const int grid = grid_for(h, h->n, 256);
+  DBuf<double> tmp;
+  TRY(tmp.ensure((size_t)grid * 4));
+  ScoreArgs2 a{h->n, h->K, h->cfg.nclass, h->cfg.family, 0, h->resp, h->w, h->off, h->d_Fp.p, tmp.p};
+  score_metrics_kernel<<<grid, 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  std::vector<double> hb((size_t)grid * 4);
+  TRY(d2h(h, hb.data(), tmp.p, hb.size() * sizeof(double)));
+  const int rc = finish_call(h);
+  tmp.release();
+  if (rc != H2OT_OK) return rc;
+  double acc[4] = {0, 0, 0, 0};
+  for (int b = 0; b < grid; b++)
+    for (int q = 0; q < 4; q++) acc[q] += hb[(size_t)b * 4 + q];
+  out->count = acc[0];
+  out->wcount = acc[1];
+  out->sumsqe = acc[2];
+  out->logloss = acc[3];
+  return H2OT_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ DRF
 int h2ot_drf_init_model(h2ot_engine* h) {
   CHECK_ENGINE(h);

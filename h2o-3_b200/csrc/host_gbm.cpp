@@ -923,6 +923,17 @@ int h2ot_gbm_oobt(h2ot_gbm* g, double* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_oobt(g->eng, out);
 }
+int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (g->p.algo != H2OT_ALGO_GBM) GFAIL(H2OT_ERR_UNSUPPORTED, "device scoring covers GBM only");
+  h2ot_metrics m{};
+  GTRY(h2ot_score_metrics(g->eng, &m));
+  double v[3] = {m.wcount, m.sumsqe, m.logloss};
+  GTRY(allreduce(g, v, 3, 0));
+  if (out_mse) *out_mse = v[1] / v[0];
+  if (out_logloss) *out_logloss = v[2] / v[0];
+  return H2OT_OK;
+}
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   std::copy(g->varimp.begin(), g->varimp.end(), out);

@@ -325,6 +325,67 @@ __global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------ training metrics
+// hex.tree.Score (T/Score.java:57-141) for GBM on the resident Tree_k columns: score2 / score1 (T/SharedTree.java:782-789,
+// T/gbm/GBM.java:1486-1513) then ModelMetrics{Regression,Binomial,Multinomial}.MetricBuilder.perRow — the squared-error and
+// log-loss sums (H/ModelMetricsBinomial.java perRow, MathUtils.logloss). Block partials in block order: deterministic.
+struct ScoreArgs2 {
+  int64_t n;
+  int32_t K, nclass, family, pad;
+  const double* resp;
+  const double* w;
+  const double* off;
+  const double* const* F;
+  double* partial;  // [gridDim.x][4] : count, wcount, sumsqe, logloss
+};
+__global__ void __launch_bounds__(256) score_metrics_kernel(ScoreArgs2 a) {
+  double cnt = 0, wc = 0, sse = 0, ll = 0;
+  const double kMaxLL = 34.538776394910684;  // -log(1e-15)
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    const double y = a.resp[row];
+    if (isnan(y)) continue;
+    const double wv = a.w ? a.w[row] : 1.0;
+    if (wv == 0.0 || isnan(wv)) continue;
+    const double f = a.F[0][row] + (a.off ? a.off[row] : 0.0);
+    double err;
+    if (a.family == H2OT_FAMILY_GAUSSIAN) {
+      err = y - f;
+    } else {
+      const int iact = (int)y;
+      double pact;
+      if (a.family == H2OT_FAMILY_BERNOULLI) {
+        if (iact != 0 && iact != 1) continue;
+        const double p1 = 1.0 / (1.0 + fmin(1e19, exp(-f)));
+        pact = iact == 1 ? p1 : 1.0 - p1;
+      } else {
+        double maxval = f;
+        for (int k = 1; k < a.nclass; k++) maxval = fmax(maxval, a.F[k][row]);
+        double dsum = 0, eact = 0;
+        for (int k = 0; k < a.nclass; k++) {
+          const double e = exp((k == 0 ? f : a.F[k][row]) - maxval);
+          dsum += e;
+          if (k == iact) eact = e;
+        }
+        pact = (iact >= 0 && iact < a.nclass) ? eact / dsum : 0.0;
+      }
+      err = 1.0 - pact;
+      ll += wv * fmin(kMaxLL, -log(1.0 - err));
+    }
+    sse += wv * err * err;
+    cnt += 1.0;
+    wc += wv;
+  }
+  __shared__ double sh[4][256];
+  sh[0][threadIdx.x] = cnt; sh[1][threadIdx.x] = wc; sh[2][threadIdx.x] = sse; sh[3][threadIdx.x] = ll;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+      for (int q = 0; q < 4; q++) sh[q][threadIdx.x] += sh[q][threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x < 4) a.partial[4 * blockIdx.x + threadIdx.x] = sh[threadIdx.x][0];
+}
+
 // ------------------------------------------------------------------------------------------ DRF
 // DRF.initializeModelSpecifics (T/drf/DRF.java:139-153): Work_k <- 1 where the response is class k (classification),
 // Work_0 <- (float) response (regression); Tree_k <- 0, NIDs_k <- 0 (pad rows DECIDED), OUT_BAG_TREES <- 0.

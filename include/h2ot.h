@@ -220,6 +220,19 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
 /* GBM.AddTreeContributions (T/gbm/GBM.java:1410-1470): Tree_k <- (float)(Tree_k + pred[nid]); NIDs_k <- 0 / DECIDED_ROW. */
 int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred /*[n_nodes], leaf nids used*/);
 
+/* ---- training metrics on the resident frame: hex.tree.Score (T/Score.java:57-141) for GBM. The link-space
+ * predictions Tree_k (+ offset) are turned into class probabilities as score1/score2 do (T/gbm/GBM.java:1486-1513,
+ * T/SharedTree.java:782-789) and fed to MetricBuilder.perRow (H/ModelMetricsBinomial.java, ModelMetricsMultinomial, ModelMetricsRegression):
+ * sums over local rows with a response and weight != 0. MSE = sumsqe / wcount, logloss = logloss / wcount (after summing over ranks).
+ * AUC and confusion matrices stay on the host. */
+typedef struct h2ot_metrics {
+  double count;   /* rows scored */
+  double wcount;  /* sum of weights */
+  double sumsqe;  /* sum w * err^2 ; err = y - f (gaussian) or 1 - p(actual class) */
+  double logloss; /* sum w * min(-log(1e-15), -log(p(actual class))) ; 0 for gaussian */
+} h2ot_metrics;
+int h2ot_score_metrics(h2ot_engine* h, h2ot_metrics* out);
+
 /* ---- DRF (T/drf/DRF.java). The level loop is the same; what differs is around it. */
 /* DRF.initializeModelSpecifics (:139-153) + the work vecs of SharedTree.java:364-385: Work_k <- class indicator (nclass > 1) or
  * (float) response, Tree_k <- 0, NIDs_k <- 0, OUT_BAG_TREES <- 0. No row is marked DECIDED (that is GBM-only). */

@@ -72,6 +72,8 @@ int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k);
 int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out);
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out);
 int h2ot_gbm_oobt(h2ot_gbm* g, double* out); /* DRF: OUT_BAG_TREES column */
+/* Training metrics of the current GBM model over all ranks (h2ot_score_metrics + sum): out_mse, out_logloss nullable */
+int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss);
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);

@@ -205,3 +205,47 @@ def test_airlines_shape_mixed_with_high_cardinality_cats():
     gm, om = _run_both(X, y, cats, distribution="gaussian", ntrees=3, max_depth=5, nbins=20, nbins_cats=1024, seed=21, capture=True)
     h2ot_lib.compare_models(gm, om)
     gm.close()
+
+
+def test_device_scoring_matches_metric_builders():
+    """hex.tree.Score on the device: MSE / logloss from the resident Tree_k columns equal the
+    MetricBuilder.perRow sums restated in numpy on the same predictions (H/ModelMetricsBinomial.java perRow, MathUtils.logloss)."""
+    P = h2ot_lib.pkg()
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=44)
+    y[::211] = NaN
+    w = np.random.default_rng(2).integers(0, 3, len(y)).astype(np.float64)
+    ok = ~np.isnan(y) & (w != 0)
+    gm = P.GBM(distribution="bernoulli", ntrees=5, max_depth=4, seed=3)
+    gm.load([X[:, c] for c in range(X.shape[1])], y, weights=w, categorical=cats)
+    gm.train()
+    F = gm.predictions()
+    p1 = 1 / (1 + np.minimum(1e19, np.exp(-F[ok])))
+    pact = np.where(y[ok] == 1, p1, 1 - p1)
+    want_ll = np.sum(w[ok] * np.minimum(-np.log(1e-15), -np.log(pact))) / np.sum(w[ok])
+    want_mse = np.sum(w[ok] * (1 - pact) ** 2) / np.sum(w[ok])
+    got = gm.score()
+    assert abs(got["logloss"] - want_ll) <= 1e-12 * want_ll and abs(got["mse"] - want_mse) <= 1e-12 * want_mse
+    gm.close()
+    # multinomial
+    rng = np.random.default_rng(3)
+    n = 20000
+    X = rng.normal(size=(n, 4)).astype(np.float32).astype(np.float64)
+    y = np.argmax(X[:, :3] + 0.5 * rng.normal(size=(n, 3)), axis=1).astype(np.float64)
+    gm = P.GBM(distribution="multinomial", nclass=3, ntrees=3, max_depth=3, seed=3)
+    gm.load([X[:, c] for c in range(4)], y)
+    gm.train()
+    Fk = np.stack([gm.predictions(k) for k in range(3)], axis=1)
+    e = np.exp(Fk - Fk.max(axis=1, keepdims=True))
+    p = e / e.sum(axis=1, keepdims=True)
+    pact = p[np.arange(n), y.astype(int)]
+    got = gm.score()
+    assert abs(got["logloss"] - np.mean(-np.log(pact))) <= 1e-12 and abs(got["mse"] - np.mean((1 - pact) ** 2)) <= 1e-12
+    gm.close()
+    # gaussian
+    yg = (X[:, 0] * 2 + X[:, 1]).astype(np.float32).astype(np.float64)
+    gm = P.GBM(distribution="gaussian", nclass=1, ntrees=3, max_depth=3, seed=3)
+    gm.load([X[:, c] for c in range(4)], yg)
+    gm.train()
+    got = gm.score()
+    assert abs(got["mse"] - np.mean((yg - gm.predictions()) ** 2)) <= 1e-12 * got["mse"] and got["logloss"] == 0.0
+    gm.close()
