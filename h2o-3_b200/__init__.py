@@ -117,6 +117,8 @@ GBM_SYMBOLS = [
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
     "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
     "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
+    "h2ot_hostcheck_hist", "h2ot_hostcheck_find_max_ex", "h2ot_hostcheck_pcg_next_long", "h2ot_hostcheck_pcg_bounded",
+    "h2ot_hostcheck_score_cols",
 ]
 
 _lib = None
@@ -200,6 +202,15 @@ def load():
                                         C.POINTER(i32), C.POINTER(i64)]
     L.h2ot_gbm_capture_vals.argtypes = [vp, i32, i32, i32, vp]
     L.h2ot_gbm_capture_nids.argtypes = [vp, i32, vp]
+    L.h2ot_hostcheck_hist.argtypes = [i32, i32, i32, dbl, dbl, C.POINTER(i32), C.POINTER(dbl)]
+    L.h2ot_hostcheck_find_max_ex.argtypes = [dbl, i32]
+    L.h2ot_hostcheck_find_max_ex.restype = dbl
+    L.h2ot_hostcheck_pcg_next_long.argtypes = [i64, i32]
+    L.h2ot_hostcheck_pcg_next_long.restype = i64
+    L.h2ot_hostcheck_pcg_bounded.argtypes = [i64, i32, i32, vp]
+    L.h2ot_hostcheck_pcg_bounded.restype = None
+    L.h2ot_hostcheck_score_cols.argtypes = [i32, i32, i32, i64, dbl, i32, vp, i32, vp, vp]
+    L.h2ot_hostcheck_score_cols.restype = None
     _lib = L
     return L
 

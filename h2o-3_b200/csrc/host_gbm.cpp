@@ -946,6 +946,42 @@ int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out) {
 }
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g) { return g ? g->eng : nullptr; }
 
+// ---- host-logic probes (no device needed): let the CPU test-suite compare this file's DHistogram / DTree / PCG bookkeeping
+// with an independent CPU restatement of the reference
+int h2ot_hostcheck_hist(int32_t nbins, int32_t nbins_cats, int32_t is_int, double min, double max_ex, int32_t* out_nbin, double* out_step) {
+  Hist h;
+  if (!make_hist(h, nbins, nbins_cats, (uint8_t)is_int, min, max_ex, false, false, 0, false)) return 0;
+  if (out_nbin) *out_nbin = h.nbin;
+  if (out_step) *out_step = h.step;
+  return 1;
+}
+double h2ot_hostcheck_find_max_ex(double max_in, int32_t is_int) { return Hist::find_max_ex_of(max_in, is_int); }
+int64_t h2ot_hostcheck_pcg_next_long(int64_t seed, int32_t nth) {
+  Pcg r(seed);
+  int64_t v = 0;
+  for (int i = 0; i <= nth; i++) v = r.next_long();
+  return v;
+}
+void h2ot_hostcheck_pcg_bounded(int64_t seed, int32_t bound, int32_t n, int32_t* out) {
+  Pcg r(seed);
+  for (int i = 0; i < n; i++) out[i] = r.next_bounded(bound);
+}
+// n_nodes successive UndecidedNode constructions on one tree (all with the same present-mask): out[i*ncols ..] = the node's
+// _scoreCols padded with -1; out_null[i] = 1 when _scoreCols == null (all columns)
+void h2ot_hostcheck_score_cols(int32_t ncols, int32_t mtry, int32_t mtry_per_tree, int64_t seed, double change_per_level, int32_t depth,
+                               const uint8_t* present, int32_t n_nodes, int32_t* out, int32_t* out_null) {
+  Tree t(ncols, mtry, mtry_per_tree, seed, change_per_level);
+  t.depth = depth;
+  for (int i = 0; i < n_nodes; i++) {
+    std::vector<Hist> hs(ncols);
+    for (int c = 0; c < ncols; c++) hs[c].present = present[c] != 0;
+    const int nid = t.new_undecided(kNoParent, std::move(hs));
+    const Node& n = t.ns[nid];
+    out_null[i] = n.score_cols_null ? 1 : 0;
+    for (int c = 0; c < ncols; c++) out[(size_t)i * ncols + c] = c < (int)n.score_cols.size() ? n.score_cols[c] : -1;
+  }
+}
+
 int32_t h2ot_gbm_ncaptures(h2ot_gbm* g) { return g ? (int32_t)g->captures.size() : 0; }
 int h2ot_gbm_capture_info(h2ot_gbm* g, int32_t i, int32_t* tree, int32_t* k, int32_t* leaf, int32_t* nleaves) {
   if (!g || i < 0 || i >= (int)g->captures.size()) GFAIL(H2OT_ERR_INVALID, "bad capture index");

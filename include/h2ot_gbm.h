@@ -78,6 +78,16 @@ int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);
 
+/* host-logic probes for the CPU test-suite (no device involved): the DHistogram ctor rule (T/DHistogram.java:190-269; returns 0
+ * for StepOutOfRangeException), find_maxEx (:453-459), the PCG generator (water/util/RandomUtils.java:50-119) and the per-node
+ * column draws of UndecidedNode.scoreCols (T/DTree.java:462-499) exactly as this driver computes them */
+int h2ot_hostcheck_hist(int32_t nbins, int32_t nbins_cats, int32_t is_int, double min, double max_ex, int32_t* out_nbin, double* out_step);
+double h2ot_hostcheck_find_max_ex(double max_in, int32_t is_int);
+int64_t h2ot_hostcheck_pcg_next_long(int64_t seed, int32_t nth);
+void h2ot_hostcheck_pcg_bounded(int64_t seed, int32_t bound, int32_t n, int32_t* out);
+void h2ot_hostcheck_score_cols(int32_t ncols, int32_t mtry, int32_t mtry_per_tree, int64_t seed, double change_per_level, int32_t depth,
+                               const uint8_t* present, int32_t n_nodes, int32_t* out, int32_t* out_null);
+
 /* captured levels */
 int32_t h2ot_gbm_ncaptures(h2ot_gbm* g);
 int h2ot_gbm_capture_info(h2ot_gbm* g, int32_t i, int32_t* tree, int32_t* k, int32_t* leaf, int32_t* nleaves);

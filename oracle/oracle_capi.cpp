@@ -108,6 +108,23 @@ long long orc_pcg_next_long(long long seed, int nth) {
   for (int i = 0; i <= nth; i++) v = r.nextLong();
   return v;
 }
+// UndecidedNode.scoreCols (T/DTree.java:462-499) for n_nodes successive nodes of one tree with the same present-mask
+void orc_tree_score_cols(int ncols, int mtry, int mtry_per_tree, long long seed, double change_per_level, int depth,
+                         const unsigned char* present, int n_nodes, int* out, int* out_null) {
+  Params p;
+  p.col_sample_rate_change_per_level = change_per_level;
+  DTree t(ncols, mtry, mtry_per_tree, seed, &p);
+  t._depth = depth;
+  for (int i = 0; i < n_nodes; i++) {
+    std::vector<HistPtr> hs(ncols);
+    for (int c = 0; c < ncols; c++)
+      if (present[c]) hs[c] = std::make_shared<DHistogram>(2, 2, 0, 0.0, 1.0, false, false, 0.0, 0, false);
+    int nid = t.newUndecided(NO_PARENT, hs);
+    const Node& n = t.node(nid);
+    out_null[i] = n._scoreColsNull ? 1 : 0;
+    for (int c = 0; c < ncols; c++) out[(size_t)i * ncols + c] = c < (int)n._scoreCols.size() ? n._scoreCols[c] : -1;
+  }
+}
 // T/Sample.java:22-36 on rows [row0,row0+n): out[i]=1 if the row is sampled OUT.
 void orc_sample(long long tree_seed, double rate, long long row0, long long n, unsigned char* out) {
   PCGRNG rand(tree_seed);

@@ -113,6 +113,9 @@ def lib():
     L.orc_pcg_ints.argtypes = [C.c_longlong, C.c_int, C.c_int, C.c_void_p]
     L.orc_pcg_next_long.argtypes = [C.c_longlong, C.c_int]
     L.orc_pcg_next_long.restype = C.c_longlong
+    L.orc_tree_score_cols.argtypes = [C.c_int, C.c_int, C.c_int, C.c_longlong, C.c_double, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                      C.c_void_p]
+    L.orc_tree_score_cols.restype = None
     L.orc_sample.argtypes = [C.c_longlong, C.c_double, C.c_longlong, C.c_longlong, C.c_void_p]
     L.orc_java_random_intopt_inputs.argtypes = [C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]
     L.orc_equals_within_one_small_ulp_f.argtypes = [C.c_float, C.c_float]
