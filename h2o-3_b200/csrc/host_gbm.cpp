@@ -19,6 +19,8 @@
 #include <cfloat>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -434,6 +436,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
       col_active[c] = 1;
     }
   }
+  const double t_descs_done = now_s();
   // decided nodes the device does not have yet
   std::vector<h2ot_decided_node> dn;
   std::vector<uint8_t> pool;
@@ -478,7 +481,8 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
                          g->p.min_rows, g->p.min_split_improvement, g->min2.data(), g->max_in.data(), g->w_na.data(), g->has.data(),
                          g->splits.data()));
   }
-  g->timing.level_s += now_s() - t0;
+  const double t_call_end = now_s();
+  g->timing.level_s += t_call_end - t0;
   g->timing.levels++;
   int64_t ncol_active = 0;
   for (int c = 0; c < C; c++) ncol_active += col_active[c];
@@ -523,6 +527,10 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
   }
   leaf_offset = tmax;
   if (did_split) tree.depth++;
+  static const bool trace = getenv("H2OT_TRACE") != nullptr;
+  if (trace)
+    fprintf(stderr, "[h2ot-host] L=%d: descs+call %.3f ms (call starts %.3f ms after entry), decide %.3f ms\n", L, 1e3 * (t_call_end - t0),
+            1e3 * (t_descs_done - t0), 1e3 * (now_s() - t_call_end));
   return H2OT_OK;
 }
 
