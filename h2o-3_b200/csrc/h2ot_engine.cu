@@ -1359,12 +1359,13 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
   CUDA_TRY(cudaMemsetAsync(t.d_gamma.p, 0, (size_t)n_leaf_nodes * 4 * sizeof(long long), h->stream));
   GammaArgs ga{};
   ga.n = h->n;
+  ga.n_pad = h->n_pad;
   ga.family = h->cfg.family;
   ga.leaf_start = leaf_start;
   ga.n_leaf_nodes = n_leaf_nodes;
   {  // enough CTAs to fill the GPU; at most 2^16 rows per CTA partial (the fixed-point split below assumes it)
     const int64_t per = (h->n + (int64_t)h->sm_count * 8 - 1) / ((int64_t)h->sm_count * 8);
-    ga.rows_per_cta = (int32_t)std::min<int64_t>(65536, std::max<int64_t>(2048, (per + 255) / 256 * 256));
+    ga.rows_per_cta = (int32_t)std::min<int64_t>(65536, std::max<int64_t>(2048, (per + 1023) / 1024 * 1024));
   }
   ga.resp = h->resp;
   ga.w = h->w;

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(256) sample_kernel(int64_t n, int64_t row_offs
 
 // ------------------------------------------------------------------------------------------ gamma
 struct GammaArgs {
-  int64_t n;
+  int64_t n, n_pad;
   int32_t family, leaf_start, n_leaf_nodes, rows_per_cta;
   const double* resp;
   const double* w;
@@ -240,6 +240,39 @@ struct GammaArgs {
 constexpr int kGammaSmemLeaves = 2048;
 constexpr int kGammaSplitBits = 24;
 
+// One row of GammaPass: final descent (writes the leaf nid) and the row's contribution to its leaf's sums.
+__device__ __forceinline__ void gamma_row(const GammaArgs& a, int64_t row, int nid, double y, double wv, float work, int& nid_out, int& idx,
+                                          long long& qn, long long& qd) {
+  idx = -1;
+  nid_out = nid;
+  if (wv == 0.0 || isnan(y)) return;
+  const bool oob = nid <= H2OT_OUT_OF_BAG;
+  if (oob) nid = -nid + H2OT_OUT_OF_BAG;
+  if (nid < 0) return;
+  h2ot_decided_node dn = a.nodes[nid];
+  if (dn.col < 0) dn = a.nodes[dn.pid];
+  const int leafnid = child_node_id(dn, a.cols, a.bitsets, row);
+  nid_out = leafnid;
+  if (oob) return;
+  const int i = leafnid - a.leaf_start;
+  if (i < 0 || i >= a.n_leaf_nodes) return;
+  const double z = (double)work;
+  const double num = __dmul_rn(wv, z);
+  double den;
+  if (a.family == H2OT_FAMILY_GAUSSIAN) den = wv;
+  else if (a.family == H2OT_FAMILY_BERNOULLI) {
+    const double ff = __dsub_rn(y, z);
+    den = __dmul_rn(__dmul_rn(wv, ff), __dsub_rn(1.0, ff));
+  } else {
+    const double az = fabs(z);
+    den = __dmul_rn(wv, __dmul_rn(az, __dsub_rn(1.0, az)));
+  }
+  qn = __double2ll_rn(__dmul_rn(num, a.s_num));
+  qd = __double2ll_rn(__dmul_rn(den, a.s_den));
+  idx = i;
+}
+
+// Four consecutive rows per thread (independent load chains in flight); rows_per_cta is a multiple of 1024.
 __global__ void __launch_bounds__(256) gamma_kernel(GammaArgs a) {
   __shared__ uint32_t s_acc[kGammaSmemLeaves * 4];
   const bool use_s = a.n_leaf_nodes <= kGammaSmemLeaves;
@@ -247,45 +280,37 @@ __global__ void __launch_bounds__(256) gamma_kernel(GammaArgs a) {
     for (int i = threadIdx.x; i < a.n_leaf_nodes * 4; i += blockDim.x) s_acc[i] = 0;
   __syncthreads();
   const int64_t lo = (int64_t)blockIdx.x * a.rows_per_cta;
-  const int64_t hi = min(a.n, lo + (int64_t)a.rows_per_cta);
-  for (int64_t row = lo + threadIdx.x; row < hi; row += blockDim.x) {
-    const double wv = a.w ? a.w[row] : 1.0;
-    if (wv == 0.0) continue;
-    const double y = a.resp[row];
-    if (isnan(y)) continue;
-    int nid = a.nids[row];
-    const bool oob = nid <= H2OT_OUT_OF_BAG;
-    if (oob) nid = -nid + H2OT_OUT_OF_BAG;
-    if (nid < 0) continue;
-    h2ot_decided_node dn = a.nodes[nid];
-    if (dn.col < 0) dn = a.nodes[dn.pid];
-    const int leafnid = child_node_id(dn, a.cols, a.bitsets, row);
-    a.nids[row] = leafnid;
-    if (oob) continue;
-    const int idx = leafnid - a.leaf_start;
-    if (idx < 0 || idx >= a.n_leaf_nodes) continue;
-    const double z = (double)a.work[row];
-    const double num = __dmul_rn(wv, z);
-    double den;
-    if (a.family == H2OT_FAMILY_GAUSSIAN) den = wv;
-    else if (a.family == H2OT_FAMILY_BERNOULLI) {
-      const double ff = __dsub_rn(y, z);
-      den = __dmul_rn(__dmul_rn(wv, ff), __dsub_rn(1.0, ff));
-    } else {
-      const double az = fabs(z);
-      den = __dmul_rn(wv, __dmul_rn(az, __dsub_rn(1.0, az)));
+  const int64_t hi = min(a.n_pad, lo + (int64_t)a.rows_per_cta);
+  for (int64_t row0 = lo + (int64_t)threadIdx.x * 4; row0 < hi; row0 += (int64_t)blockDim.x * 4) {
+    const int4 nv = *reinterpret_cast<const int4*>(a.nids + row0);
+    const float4 wk = *reinterpret_cast<const float4*>(a.work + row0);
+    const double2 y01 = *reinterpret_cast<const double2*>(a.resp + row0), y23 = *reinterpret_cast<const double2*>(a.resp + row0 + 2);
+    const int nid[4] = {nv.x, nv.y, nv.z, nv.w};
+    const float wrk[4] = {wk.x, wk.y, wk.z, wk.w};
+    const double ys[4] = {y01.x, y01.y, y23.x, y23.y};
+    int out[4], idx[4];
+    long long qn[4], qd[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const bool in = row0 + j < a.n;
+      const double wv = !in ? 0.0 : (a.w ? a.w[row0 + j] : 1.0);
+      gamma_row(a, row0 + j, nid[j], ys[j], wv, wrk[j], out[j], idx[j], qn[j], qd[j]);
     }
-    const long long qn = __double2ll_rn(__dmul_rn(num, a.s_num));
-    const long long qd = __double2ll_rn(__dmul_rn(den, a.s_den));
-    if (use_s) {
-      smem_add64(&s_acc[idx * 4], qn);
-      smem_add64(&s_acc[idx * 4 + 2], qd);
-    } else {
-      unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc + (size_t)idx * 4);
-      atomicAdd(g, (unsigned long long)(qn >> kGammaSplitBits));
-      atomicAdd(g + 1, (unsigned long long)(qn & ((1LL << kGammaSplitBits) - 1)));
-      atomicAdd(g + 2, (unsigned long long)(qd >> kGammaSplitBits));
-      atomicAdd(g + 3, (unsigned long long)(qd & ((1LL << kGammaSplitBits) - 1)));
+    if (out[0] != nid[0] || out[1] != nid[1] || out[2] != nid[2] || out[3] != nid[3])
+      *reinterpret_cast<int4*>(a.nids + row0) = make_int4(out[0], out[1], out[2], out[3]);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      if (idx[j] < 0) continue;
+      if (use_s) {
+        smem_add64(&s_acc[idx[j] * 4], qn[j]);
+        smem_add64(&s_acc[idx[j] * 4 + 2], qd[j]);
+      } else {
+        unsigned long long* g = reinterpret_cast<unsigned long long*>(a.acc + (size_t)idx[j] * 4);
+        atomicAdd(g, (unsigned long long)(qn[j] >> kGammaSplitBits));
+        atomicAdd(g + 1, (unsigned long long)(qn[j] & ((1LL << kGammaSplitBits) - 1)));
+        atomicAdd(g + 2, (unsigned long long)(qd[j] >> kGammaSplitBits));
+        atomicAdd(g + 3, (unsigned long long)(qd[j] & ((1LL << kGammaSplitBits) - 1)));
+      }
     }
   }
   __syncthreads();
