@@ -22,7 +22,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libh2otree_b200.so")
 
 OK = 0
-FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2}
+FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2, "poisson": 3, "gamma": 4, "tweedie": 5}
 NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT, LEFT, RIGHT = 0, 1, 2, 3, 4, 5
 DECIDED_ROW, OUT_OF_BAG = -1, -2
 STORE_F32, STORE_F64, STORE_U8, STORE_U16 = 0, 1, 2, 3
@@ -40,7 +40,7 @@ class H2OTError(RuntimeError):
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("ncols", C.c_int32), ("nrows", C.c_int64), ("row_offset", C.c_int64),
                 ("nrows_global", C.c_int64), ("nclass_trees", C.c_int32), ("nclass", C.c_int32), ("family", C.c_int32),
-                ("has_weights", C.c_int32), ("has_offset", C.c_int32), ("reserved", C.c_int32)]
+                ("has_weights", C.c_int32), ("has_offset", C.c_int32), ("reserved", C.c_int32), ("tweedie_power", C.c_double)]
 
 
 class HistDesc(C.Structure):
@@ -82,7 +82,8 @@ class GbmParams(C.Structure):
                 ("min_rows", C.c_double), ("min_split_improvement", C.c_double), ("sample_rate", C.c_double),
                 ("col_sample_rate", C.c_double), ("col_sample_rate_per_tree", C.c_double),
                 ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
-                ("learn_rate_annealing", C.c_double), ("max_abs_leafnode_pred", C.c_double), ("seed", C.c_int64)]
+                ("learn_rate_annealing", C.c_double), ("max_abs_leafnode_pred", C.c_double), ("seed", C.c_int64),
+                ("tweedie_power", C.c_double)]
 
 
 class TreeNode(C.Structure):
@@ -104,7 +105,7 @@ ENGINE_SYMBOLS = [
     "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
-    "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_begin_tree", "h2ot_build_level",
+    "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_get_gamma_bounds", "h2ot_set_gamma_bounds", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
@@ -149,6 +150,8 @@ def load():
         getattr(L, n).argtypes = [vp, i32, vp]
     L.h2ot_set_work.argtypes = [vp, i32, vp, dbl]
     L.h2ot_compute_residuals.argtypes = [vp, vp]
+    L.h2ot_get_gamma_bounds.argtypes = [vp, vp]
+    L.h2ot_set_gamma_bounds.argtypes = [vp, vp]
     L.h2ot_begin_tree.argtypes = [vp, i32, i64, dbl, dbl]
     L.h2ot_build_level.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp]
     L.h2ot_level_buffers.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(i64), C.POINTER(vp), C.POINTER(i64)]
@@ -254,7 +257,7 @@ class Engine:
             return
         cfg = Config(device=device, ncols=ncols, nrows=nrows, row_offset=row_offset, nrows_global=nrows_global,
                      nclass_trees=nclass_trees, nclass=nclass, family=FAMILY[family] if isinstance(family, str) else family,
-                     has_weights=int(has_weights), has_offset=int(has_offset), reserved=0)
+                     has_weights=int(has_weights), has_offset=int(has_offset), reserved=0, tweedie_power=1.5)
         self.h = C.c_void_p()
         _check(self.L.h2ot_create(C.byref(cfg), C.byref(self.h)))
 
@@ -332,7 +335,7 @@ class Engine:
 
     # ---- per tree / per level
     def compute_residuals(self):
-        out = np.zeros(self.K, dtype=np.float64)
+        out = np.zeros(self.K + 2, dtype=np.float64)
         _check(self.L.h2ot_compute_residuals(self.h, _p(out)))
         return out
 
@@ -438,7 +441,7 @@ class GBM:
                  min_split_improvement=1e-5, sample_rate=1.0, col_sample_rate=1.0, col_sample_rate_per_tree=1.0,
                  col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
                  max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
-                 device=0, algo=0, mtries=-1):
+                 device=0, algo=0, mtries=-1, tweedie_power=1.5):
         self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
                                 nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, algo=algo,
                                 mtries=mtries, pad=0,
@@ -446,7 +449,7 @@ class GBM:
                                 col_sample_rate=col_sample_rate, col_sample_rate_per_tree=col_sample_rate_per_tree,
                                 col_sample_rate_change_per_level=col_sample_rate_change_per_level, learn_rate=learn_rate,
                                 learn_rate_annealing=learn_rate_annealing, max_abs_leafnode_pred=max_abs_leafnode_pred,
-                                seed=seed)
+                                seed=seed, tweedie_power=tweedie_power)
         self.device = device
         self.L = load()
         self.g = None

@@ -147,6 +147,7 @@ struct h2ot_engine {
   double* staging_all = nullptr;
   unsigned char* col_block = nullptr;  // all encoded columns (each 256-byte aligned)
   double w_max = 1.0;
+  double gamma_bound[2] = {1.0, 1.0};  // max |gammaNum / w|, max |gammaDenom / w| of the current residuals
   bool frame_final = false;
   std::vector<TreeState> ts;
   // device pointer tables
@@ -280,6 +281,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   if (!cfg || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
   if (cfg->nrows <= 0 || cfg->ncols <= 0 || cfg->nclass_trees <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "nrows/ncols/nclass_trees must be positive");
   if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
+  if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_TWEEDIE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -289,6 +291,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   h2ot_engine* h = new h2ot_engine();
   h->cfg = *cfg;
   if (h->cfg.nrows_global <= 0) h->cfg.nrows_global = cfg->nrows;
+  if (!(h->cfg.tweedie_power > 1.0 && h->cfg.tweedie_power < 2.0)) h->cfg.tweedie_power = 1.5;
   h->n = cfg->nrows;
   h->n_pad = (cfg->nrows + kRowPad - 1) / kRowPad * kRowPad;
   h->C = cfg->ncols;
@@ -333,7 +336,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   TRY(h->d_Fp.ensure(h->K));
   TRY(h->d_workp.ensure(h->K));
   TRY(h->d_nidsp.ensure(h->K));
-  TRY(h->d_absmax.ensure(h->K));
+  TRY(h->d_absmax.ensure(h->K + 2));
   TRY(h->d_scalar.ensure(8));
   TRY(h->d_rollup.ensure(1));
   TRY(h->d_cols.ensure(h->C));
@@ -563,7 +566,7 @@ int h2ot_initial_stats(h2ot_engine* h, double* out_num, double* out_den, double*
   DBuf<double> tmp;
   TRY(tmp.ensure((size_t)grid * 2 + nc + 1));
   CUDA_TRY(cudaMemsetAsync(tmp.p, 0, ((size_t)grid * 2 + nc + 1) * sizeof(double), h->stream));
-  InitStatsArgs a{h->n, h->cfg.nclass, 0, h->resp, h->w, h->off, tmp.p, tmp.p + (size_t)grid * 2,
+  InitStatsArgs a{h->n, h->cfg.nclass, h->cfg.family, h->cfg.tweedie_power, h->resp, h->w, h->off, tmp.p, tmp.p + (size_t)grid * 2,
                   reinterpret_cast<unsigned int*>(tmp.p + (size_t)grid * 2 + nc)};
   init_stats_kernel<<<grid, 256, 0, h->stream>>>(a);
   h->stats.launches++;
@@ -645,21 +648,39 @@ int h2ot_set_nids(h2ot_engine* h, int32_t k, const int32_t* nids) {
 int h2ot_compute_residuals(h2ot_engine* h, double* out_abs_max) {
   CHECK_ENGINE(h);
   if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
-  CUDA_TRY(cudaMemsetAsync(h->d_absmax.p, 0, h->K * sizeof(unsigned int), h->stream));
-  ResidArgs a{h->n, h->K, h->cfg.nclass, h->cfg.family, h->resp, h->w, h->off, h->d_Fp.p, h->d_workp.p, h->d_absmax.p};
+  CUDA_TRY(cudaMemsetAsync(h->d_absmax.p, 0, (h->K + 2) * sizeof(unsigned int), h->stream));
+  ResidArgs a{h->n, h->K, h->cfg.nclass, h->cfg.family, h->resp, h->w, h->off, h->d_Fp.p, h->d_workp.p, h->d_absmax.p, h->cfg.tweedie_power};
   TRY(t_begin(h, &h->stats.ms_residuals));
   residuals_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
   h->stats.launches++;
   TRY(t_end(h));
-  std::vector<unsigned int> bits(h->K);
-  TRY(d2h(h, bits.data(), h->d_absmax.p, h->K * sizeof(unsigned int)));
+  std::vector<unsigned int> bits(h->K + 2);
+  TRY(d2h(h, bits.data(), h->d_absmax.p, (h->K + 2) * sizeof(unsigned int)));
   TRY(finish_call(h));
+  for (int q = 0; q < 2; q++) {
+    float f;
+    memcpy(&f, &bits[h->K + q], 4);
+    h->gamma_bound[q] = f > 0 ? (double)f : 1.0;
+  }
   for (int k = 0; k < h->K; k++) {
     float f;
     memcpy(&f, &bits[k], 4);
     if (out_abs_max) out_abs_max[k] = (double)f;
     h->ts[k].work_bound = (double)f;
   }
+  return H2OT_OK;
+}
+
+int h2ot_get_gamma_bounds(h2ot_engine* h, double out[2]) {
+  if (!h || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  out[0] = h->gamma_bound[0];
+  out[1] = h->gamma_bound[1];
+  return H2OT_OK;
+}
+int h2ot_set_gamma_bounds(h2ot_engine* h, const double in[2]) {
+  if (!h || !in || !(in[0] > 0) || !(in[1] > 0)) H2OT_FAIL(H2OT_ERR_INVALID, "gamma bounds must be positive");
+  h->gamma_bound[0] = in[0];
+  h->gamma_bound[1] = in[1];
   return H2OT_OK;
 }
 
@@ -1375,9 +1396,11 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
   ga.bitsets = t.bitsets.p;
   ga.cols = h->d_cols.p;
   ga.acc = t.d_gamma.p;
-  const double b = t.work_bound > 0 ? t.work_bound : 1.0;
-  const int e_num = exponent_for(h->w_max * b, 17);  // <= 2^16 rows per CTA partial, one spare bit
-  const int e_den = exponent_for(h->w_max, 17);
+  const int e_num = exponent_for(h->w_max * h->gamma_bound[0], 17);  // <= 2^16 rows per CTA partial, one spare bit
+  const int e_den = exponent_for(h->w_max * h->gamma_bound[1], 17);
+  ga.F = t.F;
+  ga.off = h->off;
+  ga.tweedie_power = h->cfg.tweedie_power;
   ga.s_num = std::ldexp(1.0, e_num);
   ga.s_den = std::ldexp(1.0, e_den);
   const int grid = (int)((h->n + ga.rows_per_cta - 1) / ga.rows_per_cta);

@@ -542,9 +542,11 @@ int allreduce(h2ot_gbm* g, double* v, int64_t n, int op) {
 // GBM.buildNextKTrees (T/gbm/GBM.java:464-591)
 int build_next_k_trees(h2ot_gbm* g) {
   const int K = g->K;
-  std::vector<double> absmax(K, 0.0);
+  std::vector<double> absmax(K + 2, 0.0);
   GTRY(h2ot_compute_residuals(g->eng, absmax.data()));
-  GTRY(allreduce(g, absmax.data(), K, 1));
+  GTRY(h2ot_get_gamma_bounds(g->eng, absmax.data() + K));
+  GTRY(allreduce(g, absmax.data(), K + 2, 1));
+  GTRY(h2ot_set_gamma_bounds(g->eng, absmax.data() + K));
   std::vector<std::unique_ptr<Tree>> kt(K);
   std::vector<int> leaves(K, 0);
   const int adj_nbins = std::max(g->p.nbins_top_level, g->p.nbins);
@@ -606,7 +608,11 @@ int build_next_k_trees(h2ot_gbm* g) {
     std::vector<double> num(nleaf), den(nleaf);
     GTRY(h2ot_gamma_pass(g->eng, k, leaves[k], nleaf, num.data(), den.data()));
     for (int i = 0; i < nleaf; i++) {
-      const double gamma = den[i] == 0 ? 0 : num[i] / den[i];
+      double gamma = den[i] == 0 ? 0 : num[i] / den[i];
+      if (den[i] != 0 && g->p.family >= H2OT_FAMILY_POISSON) {  // GammaPass.gamma(double): link for poisson / gamma / tweedie
+        const double x = std::fmax(0.0, gamma);
+        gamma = x == 0 ? -19.0 : std::fmax(-19.0, std::log(x));  // LogExpUtil.log
+      }
       double gf = eff_lr * m1class * gamma;
       if (g->p.family == H2OT_FAMILY_MULTINOMIAL) {
         if (gf > 1e4) gf = 1e4f;
@@ -715,7 +721,8 @@ extern "C" {
 int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int32_t ncols, int64_t row_offset, int64_t nrows_global,
                     int32_t has_weights, int32_t has_offset, h2ot_gbm** out) {
   if (!p || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
-  if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_MULTINOMIAL) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
+  if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_TWEEDIE) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
+  if (p->algo == H2OT_ALGO_DRF && p->family > H2OT_FAMILY_MULTINOMIAL) GFAIL(H2OT_ERR_UNSUPPORTED, "DRF takes gaussian / bernoulli / multinomial");
   if (p->max_depth < 1 || p->nbins < 2 || p->nbins_cats < 2 || p->ntrees < 0) GFAIL(H2OT_ERR_INVALID, "bad tree parameters");
   if (p->nbins_cats > H2OT_MAX_BITSET_BYTES * 8) GFAIL(H2OT_ERR_UNSUPPORTED, "nbins_cats above 4096");
   if (p->algo != H2OT_ALGO_GBM && p->algo != H2OT_ALGO_DRF) GFAIL(H2OT_ERR_UNSUPPORTED, "unknown algo");
@@ -747,6 +754,7 @@ int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int
   cfg.family = p->family;
   cfg.has_weights = has_weights;
   cfg.has_offset = has_offset;
+  cfg.tweedie_power = p->tweedie_power;
   const int rc = h2ot_create(&cfg, &g->eng);
   if (rc != H2OT_OK) {
     delete g;
@@ -861,7 +869,10 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   if (drf) g->init_f = g->nclass > 1 ? 0 : mean;  // T/drf/DRF.java:131
   else if (g->nclass > 2) g->init_f = 0;
   else if (g->p.family == H2OT_FAMILY_BERNOULLI) g->init_f = std::log(mean / (1 - mean));  // LogitFunction.link
-  else g->init_f = mean;
+  else if (g->p.family >= H2OT_FAMILY_POISSON) {  // LogFunction.link == LogExpUtil.log
+    const double x = std::fmax(0.0, mean);
+    g->init_f = x == 0 ? -19.0 : std::fmax(-19.0, std::log(x));
+  } else g->init_f = mean;
   if (drf) {
     GTRY(h2ot_drf_init_model(g->eng));
   } else {

@@ -94,9 +94,12 @@ __global__ void __launch_bounds__(256) init_rows_kernel(InitArgs a) {
 // SharedTree.InitialValue (T/SharedTree.java:1138-1185): sum w (y - offset) and sum w over rows with a response and w != 0,
 // plus what DRF's set-up needs: weight per class and max |(float) y|. Block partials are written out and summed by the host in
 // block order, so the result does not depend on scheduling.
+__device__ __forceinline__ double exp_cap(double x) { return fmin(1e19, exp(x)); }  // LogExpUtil.exp (H/DistributionFactory.java:534)
+
 struct InitStatsArgs {
   int64_t n;
-  int32_t nclass, pad;
+  int32_t nclass, family;
+  double tweedie_power;
   const double* resp;
   const double* w;
   const double* off;
@@ -117,8 +120,21 @@ __global__ void __launch_bounds__(256) init_stats_kernel(InitStatsArgs a) {
       if (c >= 0 && c < a.nclass && wv != 0.0) atomicAdd(&a.class_w[c], wv);
     }
     if (wv == 0.0) continue;
-    num += __dmul_rn(wv, __dsub_rn(y, a.off ? a.off[row] : 0.0));
-    den += wv;
+    const double o = a.off ? a.off[row] : 0.0;
+    // Distribution.initFNum / initFDenom (H/DistributionFactory.java)
+    if (a.family == H2OT_FAMILY_POISSON) {
+      num += __dmul_rn(wv, y);
+      den += __dmul_rn(wv, exp_cap(o));
+    } else if (a.family == H2OT_FAMILY_GAMMA) {
+      num += __dmul_rn(__dmul_rn(wv, y), exp_cap(-o));
+      den += wv;
+    } else if (a.family == H2OT_FAMILY_TWEEDIE) {
+      num += __dmul_rn(__dmul_rn(wv, y), exp_cap(__dmul_rn(o, 1.0 - a.tweedie_power)));
+      den += __dmul_rn(wv, exp_cap(__dmul_rn(o, 2.0 - a.tweedie_power)));
+    } else {
+      num += __dmul_rn(wv, __dsub_rn(y, o));
+      den += wv;
+    }
   }
   __shared__ double s_num[256], s_den[256];
   s_num[threadIdx.x] = num;
@@ -148,7 +164,8 @@ struct ResidArgs {
   const double* off;
   const double* const* F;  // [K] Tree_k (fp64: holds the double init_f until a row's first update, float valued after)
   float* const* work;      // [K]
-  unsigned int* absmax;   // [K] float bits of max |work|
+  unsigned int* absmax;   // [K + 2] float bits of max |work| per class-tree, then max |gammaNum / w| and max |gammaDenom / w|
+  double tweedie_power;
 };
 
 __device__ __forceinline__ double tree_val(const ResidArgs& a, int k, int64_t row) {
@@ -156,7 +173,7 @@ __device__ __forceinline__ double tree_val(const ResidArgs& a, int k, int64_t ro
 }
 
 __global__ void __launch_bounds__(256) residuals_kernel(ResidArgs a) {
-  float amaxk = 0.f;
+  float amaxk = 0.f, gnum = 0.f, gden = 0.f;
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
     const double wv = a.w ? a.w[row] : 1.0;
     if (wv == 0.0) continue;
@@ -180,12 +197,39 @@ __global__ void __launch_bounds__(256) residuals_kernel(ResidArgs a) {
       }
     } else {
       double r;
+      // per-row magnitude of the GammaPass terms (upper bounds, rounded up): they scale the fixed-point leaf sums
+      double tn = 0, td = 1.0;
       if (a.family == H2OT_FAMILY_BERNOULLI) r = y - 1.0 / (1.0 + fmin(1e19, exp(-f)));  // LogitFunction.linkInv
-      else r = y - f;
+      else if (a.family == H2OT_FAMILY_POISSON) {
+        const double ef = exp_cap(f);
+        r = y - ef;
+        tn = fabs(y);
+        td = fabs(y) + fabs((double)(float)r) + 1.0;  // gammaDenom = w (y - z), z the float-rounded residual
+      } else if (a.family == H2OT_FAMILY_GAMMA) {
+        r = __dsub_rn(__dmul_rn(y, exp_cap(-f)), 1.0);
+      } else if (a.family == H2OT_FAMILY_TWEEDIE) {
+        const double e1 = exp_cap(__dmul_rn(f, 1.0 - a.tweedie_power)), e2 = exp_cap(__dmul_rn(f, 2.0 - a.tweedie_power));
+        r = __dsub_rn(__dmul_rn(y, e1), e2);
+        tn = fabs(__dmul_rn(y, e1));
+        td = e2;
+      } else r = y - f;
       const float rf = (float)r;
       a.work[0][row] = rf;
       amaxk = fmaxf(amaxk, fabsf(rf));
+      if (a.family == H2OT_FAMILY_GAMMA) tn = (double)fabsf(rf) + 1.0;
+      else if (a.family != H2OT_FAMILY_POISSON && a.family != H2OT_FAMILY_TWEEDIE) tn = (double)fabsf(rf);
+      gnum = fmaxf(gnum, __double2float_ru(tn));
+      gden = fmaxf(gden, __double2float_ru(td));
     }
+  }
+  if (a.family == H2OT_FAMILY_MULTINOMIAL) { gnum = 1.f; gden = 1.f; }
+  for (int o = 16; o > 0; o >>= 1) {
+    gnum = fmaxf(gnum, __shfl_xor_sync(0xffffffffu, gnum, o));
+    gden = fmaxf(gden, __shfl_xor_sync(0xffffffffu, gden, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (gnum > 0.f) atomicMax(&a.absmax[a.K], __float_as_uint(gnum));
+    if (gden > 0.f) atomicMax(&a.absmax[a.K + 1], __float_as_uint(gden));
   }
   for (int o = 16; o > 0; o >>= 1) amaxk = fmaxf(amaxk, __shfl_xor_sync(0xffffffffu, amaxk, o));
   // one bound shared by all K class-trees (max over k) keeps the kernel simple
@@ -236,6 +280,9 @@ struct GammaArgs {
   const ColRef* cols;
   long long* acc;  // [n_leaf_nodes][4] : num.hi, num.lo, den.hi, den.lo (fixed point, split at bit 24)
   double s_num, s_den;
+  const double* F;    // Tree_k (tweedie needs f = Tree_k + offset)
+  const double* off;
+  double tweedie_power;
 };
 constexpr int kGammaSmemLeaves = 2048;
 constexpr int kGammaSplitBits = 24;
@@ -257,12 +304,22 @@ __device__ __forceinline__ void gamma_row(const GammaArgs& a, int64_t row, int n
   const int i = leafnid - a.leaf_start;
   if (i < 0 || i >= a.n_leaf_nodes) return;
   const double z = (double)work;
-  const double num = __dmul_rn(wv, z);
+  double num = __dmul_rn(wv, z);
   double den;
   if (a.family == H2OT_FAMILY_GAUSSIAN) den = wv;
   else if (a.family == H2OT_FAMILY_BERNOULLI) {
     const double ff = __dsub_rn(y, z);
     den = __dmul_rn(__dmul_rn(wv, ff), __dsub_rn(1.0, ff));
+  } else if (a.family == H2OT_FAMILY_POISSON) {  // gammaNum = w y, gammaDenom = w (y - z)
+    num = __dmul_rn(wv, y);
+    den = __dmul_rn(wv, __dsub_rn(y, z));
+  } else if (a.family == H2OT_FAMILY_GAMMA) {  // w (z + 1), w
+    num = __dmul_rn(wv, __dadd_rn(z, 1.0));
+    den = wv;
+  } else if (a.family == H2OT_FAMILY_TWEEDIE) {  // w y exp(f (1 - p)), w exp(f (2 - p))
+    const double f = a.F[row] + (a.off ? a.off[row] : 0.0);
+    num = __dmul_rn(__dmul_rn(wv, y), exp_cap(__dmul_rn(f, 1.0 - a.tweedie_power)));
+    den = __dmul_rn(wv, exp_cap(__dmul_rn(f, 2.0 - a.tweedie_power)));
   } else {
     const double az = fabs(z);
     den = __dmul_rn(wv, __dmul_rn(az, __dsub_rn(1.0, az)));
@@ -375,6 +432,8 @@ __global__ void __launch_bounds__(256) score_metrics_kernel(ScoreArgs2 a) {
     double err;
     if (a.family == H2OT_FAMILY_GAUSSIAN) {
       err = y - f;
+    } else if (a.family >= H2OT_FAMILY_POISSON) {
+      err = y - exp_cap(f);  // ModelMetricsRegression on the response scale: ds[0] = linkInv(f)
     } else {
       const int iact = (int)y;
       double pact;

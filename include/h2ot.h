@@ -37,6 +37,9 @@ extern "C" {
 #define H2OT_FAMILY_GAUSSIAN 0
 #define H2OT_FAMILY_BERNOULLI 1
 #define H2OT_FAMILY_MULTINOMIAL 2
+#define H2OT_FAMILY_POISSON 3  /* H/DistributionFactory.java:274-307 (log link) */
+#define H2OT_FAMILY_GAMMA 4    /* :309-341 */
+#define H2OT_FAMILY_TWEEDIE 5  /* :343-379, power in h2ot_config.tweedie_power (1 < p < 2) */
 
 /* T/DHistogram.java:152-168 NASplitDir */
 #define H2OT_NA_NONE 0
@@ -70,6 +73,7 @@ typedef struct h2ot_config {
   int32_t has_weights;
   int32_t has_offset;
   int32_t reserved;
+  double tweedie_power;  /* H2OT_FAMILY_TWEEDIE only (Model.Parameters._tweedie_power, default 1.5) */
 } h2ot_config;
 
 /* Per (leaf, column) histogram descriptor == the DHistogram fields the CPU kernel reads
@@ -171,6 +175,10 @@ int h2ot_set_nids(h2ot_engine* h, int32_t k, const int32_t* nids);
 /* GBM.ComputePredAndRes (T/gbm/GBM.java:1032-1081): Work_k <- (float) negHalfGradient for all K.
  * out_abs_max[k] receives max |Work_k| over local rows (fixes the fixed-point scale; nullable). */
 int h2ot_compute_residuals(h2ot_engine* h, double* out_abs_max /*[K]*/);
+/* Bounds of the per-row GammaPass terms |gammaNum / w| and |gammaDenom / w| seen by the last h2ot_compute_residuals (they fix
+ * the fixed-point scale of the leaf sums). With several ranks take the max over ranks and set it back before h2ot_gamma_pass. */
+int h2ot_get_gamma_bounds(h2ot_engine* h, double out[2]);
+int h2ot_set_gamma_bounds(h2ot_engine* h, const double in[2]);
 /* Starts class-tree k: clears its node table, fixes the accumulator scale from work_abs_bound
  * (>= max |Work_k| over ALL ranks), and runs Sample (T/Sample.java:22-36) when sample_rate < 1. */
 int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate, double work_abs_bound);

@@ -29,6 +29,7 @@ typedef struct h2ot_gbm_params {
   double min_rows, min_split_improvement, sample_rate, col_sample_rate, col_sample_rate_per_tree,
       col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
   int64_t seed;
+  double tweedie_power; /* family H2OT_FAMILY_TWEEDIE (default 1.5 when <= 0) */
 } h2ot_gbm_params;
 
 /* Flat view of one DTree node (DecidedNode / LeafNode, T/DTree.java:587-965) */

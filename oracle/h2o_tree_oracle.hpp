@@ -199,7 +199,7 @@ struct IcedBitSet {
 // ----------------------------------------------------------------------------------------------
 // Parameters (T/SharedTreeModel.java:51-98, T/gbm/GBMModel.java:24-41 defaults)
 // ----------------------------------------------------------------------------------------------
-enum Family { GAUSSIAN = 0, BERNOULLI = 1, MULTINOMIAL = 2 };
+enum Family { GAUSSIAN = 0, BERNOULLI = 1, MULTINOMIAL = 2, POISSON = 3, GAMMA = 4, TWEEDIE = 5 };
 enum NASplitDir { NA_None = 0, NAvsREST = 1, NALeft = 2, NARight = 3, Left = 4, Right = 5 };  // T/DHistogram.java:152-168
 
 struct Params {
@@ -223,6 +223,7 @@ struct Params {
   bool drf = false;
   int mtries = -1;  // DRF only
   int nthreads = 1; // CPU threads for the SBH2 restatement (baseline timing)
+  double tweedie_power = 1.5;  // H/Model.java Parameters._tweedie_power
 };
 
 // ----------------------------------------------------------------------------------------------
@@ -1219,12 +1220,45 @@ inline double link(int family, double f) {
     default: return log_(f);
   }
 }
-inline double negHalfGradient(int family, double y, double f) { return y - linkInv(family, f); }
-inline double gammaNum(int, double w, double, double z, double) { return w * z; }
-inline double gammaDenom(int family, double w, double y, double z, double) {
+// H/DistributionFactory.java: Gaussian :73-103, Bernoulli :105-134, Multinomial :243-272, Poisson :274-307, Gamma :309-341,
+// Tweedie :343-379 (p == _tweediePower)
+inline double negHalfGradient(int family, double y, double f, double p = 1.5) {
+  switch (family) {
+    case GAMMA: return y * exp_(-f) - 1;
+    case TWEEDIE: return y * exp_(f * (1 - p)) - exp_(f * (2 - p));
+    default: return y - linkInv(family, f);
+  }
+}
+inline double initFNum(int family, double w, double o, double y, double p = 1.5) {
+  switch (family) {
+    case POISSON: return w * y;
+    case GAMMA: return w * y * exp_(-o);
+    case TWEEDIE: return w * y * exp_(o * (1 - p));
+    default: return w * (y - o);
+  }
+}
+inline double initFDenom(int family, double w, double o, double, double p = 1.5) {
+  switch (family) {
+    case POISSON: return w * exp_(o);
+    case TWEEDIE: return w * exp_(o * (2 - p));
+    default: return w;
+  }
+}
+inline double gammaNum(int family, double w, double y, double z, double f, double p = 1.5) {
+  switch (family) {
+    case POISSON: return w * y;
+    case GAMMA: return w * (z + 1);
+    case TWEEDIE: return w * y * exp_(f * (1 - p));
+    default: return w * z;
+  }
+}
+inline double gammaDenom(int family, double w, double y, double z, double f, double p = 1.5) {
   switch (family) {
     case GAUSSIAN: return w;
     case BERNOULLI: { double ff = y - z; return w * ff * (1 - ff); }
+    case POISSON: return w * (y - z);
+    case GAMMA: return w;
+    case TWEEDIE: return w * exp_(f * (2 - p));
     default: { double absz = std::fabs(z); return w * (absz * (1 - absz)); }
   }
 }
@@ -1298,8 +1332,8 @@ struct GBM {
       if (w == 0) continue;
       double y = fr.y[i];
       double o = fr.off.empty() ? 0 : fr.off[i];
-      num += w * (y - o);
-      denom += w;
+      num += dist::initFNum(parms.family, w, o, y, parms.tweedie_power);
+      denom += dist::initFDenom(parms.family, w, o, y, parms.tweedie_power);
     }
     if (parms.family == MULTINOMIAL) return -0.5 * dist::link(BERNOULLI, num / denom);
     return dist::link(parms.family, num / denom);
@@ -1346,7 +1380,7 @@ struct GBM {
           }
         }
       } else {
-        work_[0][row] = (float)dist::negHalfGradient(parms.family, y, f);
+        work_[0][row] = (float)dist::negHalfGradient(parms.family, y, f, parms.tweedie_power);
       }
     }
   }
@@ -1497,8 +1531,8 @@ struct GBM {
         double z = work_[k][row];
         double f = tree_[k][row] + (fr.off.empty() ? 0 : fr.off[row]);
         int idx = leafnid - leaf;
-        num[k][idx] += dist::gammaNum(parms.family, w, y, z, f);
-        denom[k][idx] += dist::gammaDenom(parms.family, w, y, z, f);
+        num[k][idx] += dist::gammaNum(parms.family, w, y, z, f, parms.tweedie_power);
+        denom[k][idx] += dist::gammaDenom(parms.family, w, y, z, f, parms.tweedie_power);
       }
     }
     // fitBestConstants :813-847
@@ -1509,6 +1543,8 @@ struct GBM {
       for (int i = 0; i < tree.len() - leaves[k]; i++) {
         Node& leafNode = tree.node(leaves[k] + i);
         double gamma = denom[k][i] == 0 ? 0 : num[k][i] / denom[k][i];
+        if (denom[k][i] != 0 && (parms.family == POISSON || parms.family == GAMMA || parms.family == TWEEDIE))
+          gamma = dist::link(parms.family, gamma);  // GammaPass.gamma(double) :1315-1323
         double gf = eff_lr * m1class * gamma;
         if (parms.family == MULTINOMIAL) {
           if (gf > 1e4) gf = 1e4f;

@@ -169,6 +169,7 @@ struct OrcParams {
       col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
   long long seed;
   long long chunk_rows;
+  double tweedie_power;
 };
 static Params to_params(const OrcParams* p) {
   Params q;
@@ -190,6 +191,7 @@ static Params to_params(const OrcParams* p) {
   q.learn_rate_annealing = p->learn_rate_annealing;
   q.max_abs_leafnode_pred = p->max_abs_leafnode_pred;
   q.seed = p->seed;
+  if (p->tweedie_power > 0) q.tweedie_power = p->tweedie_power;
   return q;
 }
 

@@ -48,7 +48,8 @@ def compare_models(gm, om, K=1, check_levels=True, rel=1e-6):
     bit-exact nids / descriptors / tree structure, histogram sums within `rel` of the oracle's."""
     P = pkg()
     assert gm.ntrees == om.ntrees
-    assert gm.init_f == om.init_f or abs(gm.init_f - om.init_f) <= 1e-15 * max(1.0, abs(om.init_f))
+    # sums of non-exact terms (offsets through exp, non-float responses) depend on the summation order, in the reference too
+    assert gm.init_f == om.init_f or abs(gm.init_f - om.init_f) <= 1e-12 * max(1.0, abs(om.init_f))
     stats = dict(levels=0, hists=0, max_rel=0.0, n_vals=0, n_vals_diff=0)
     if check_levels:
         # The reference launches ScoreBuildHistogram2 even when a tree has no undecided leaf left (T/SharedTree.java:671-683):

@@ -34,7 +34,7 @@ def test_struct_layouts_match_header_sizes():
     assert C.sizeof(P.HistDesc) == 32
     assert C.sizeof(P.DecidedNode) == 48
     assert C.sizeof(P.Split) == 32 + 72 + 512
-    assert C.sizeof(P.Config) == 56
+    assert C.sizeof(P.Config) == 64
 
 
 def test_no_cpu_fallback_without_device():

@@ -249,3 +249,32 @@ def test_device_scoring_matches_metric_builders():
     got = gm.score()
     assert abs(got["mse"] - np.mean((yg - gm.predictions()) ** 2)) <= 1e-12 * got["mse"] and got["logloss"] == 0.0
     gm.close()
+
+
+@pytest.mark.parametrize("dist", ["poisson", "gamma", "tweedie"])
+def test_log_link_distributions(dist):
+    """SURVEY 8f row 4 (first part): poisson / gamma / tweedie (H/DistributionFactory.java:274-379) — initFNum/initFDenom,
+    negHalfGradient, gammaNum/gammaDenom with the log link applied to the leaf ratio (GammaPass.gamma, T/gbm/GBM.java:1315-1323)."""
+    P = h2ot_lib.pkg()
+    rng = np.random.default_rng({"poisson": 1, "gamma": 2, "tweedie": 3}[dist])
+    n = 25000
+    X, _, cats = h2ot_lib.make_frame(n=n, c=6, seed=77)
+    mu = np.exp(0.4 * np.nan_to_num(X[:, 0]) - 0.3 * np.nan_to_num(X[:, 1]) + 0.5)
+    if dist == "poisson":
+        y = rng.poisson(mu).astype(np.float64)
+    elif dist == "gamma":
+        y = (rng.gamma(2.0, mu / 2.0) + 0.01).astype(np.float32).astype(np.float64)
+    else:
+        y = np.where(rng.random(n) < 0.4, 0.0, rng.gamma(2.0, mu / 2.0)).astype(np.float32).astype(np.float64)
+    w = rng.integers(0, 3, n).astype(np.float64)
+    off = (rng.random(n) * 0.2).astype(np.float32).astype(np.float64) if dist != "gamma" else None
+    fam = {"poisson": O.POISSON, "gamma": O.GAMMA, "tweedie": O.TWEEDIE}[dist]
+    kw = dict(ntrees=4, max_depth=4, nbins=20, seed=11)
+    op = O.default_params(family=fam, nclass=1, tweedie_power=1.3, **kw)
+    om = O.Model(O.Frame(X, y, w=w, off=off, cat_cards=cats), op, capture=True)
+    gm = P.GBM(distribution=dist, nclass=1, tweedie_power=1.3, **kw)
+    gm.load([X[:, c] for c in range(X.shape[1])], y, weights=w, offset=off, categorical=cats)
+    gm.capture_levels(True)
+    gm.train()
+    h2ot_lib.compare_models(gm, om)
+    gm.close()
