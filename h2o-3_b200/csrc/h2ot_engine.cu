@@ -923,6 +923,10 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       if (s.flags & H2OT_DESC_CHECKFLOAT) t.any_checkfloat = true;
     }
   // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
+  auto fixed_bytes_l = [&](int ncg, int storage, int nleaves) {
+    return (size_t)ncg * nleaves * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
+           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);
+  };
   auto fixed_bytes = [&](int ncg, int storage) {
     return (size_t)ncg * L * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
            (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
@@ -935,33 +939,44 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   t.h_group_cols.clear();
   t.active_cols = 0;
   std::vector<int> glob_cols;
-  std::vector<int> bucket[4];
+  std::vector<int> bucket[4], split_cols[4];
   for (int c = 0; c < C; c++) {
     if (!col_words[c]) continue;
     t.active_cols++;
     const int st = h->cols[c].storage;
-    if (h->hist_mode == 1 || (size_t)col_words[c] * 4 + fixed_bytes(1, st) > full_budget) glob_cols.push_back(c);
-    else bucket[st].push_back(c);
+    if (h->hist_mode == 1) glob_cols.push_back(c);
+    else if ((size_t)col_words[c] * 4 + fixed_bytes(1, st) > budget) {
+      // too big for one CTA. Dense column (most leaves histogram it): cut into leaf ranges, each range's CTAs scan all rows
+      // (measured 2.5 / 5.2 ms at 64 / 128 leaves x 257 bins vs 15 / 11 ms with L2 atomics). Sparse column (per-node mtries):
+      // few rows take part at all, where the L2-atomics kernel that simply skips them is faster (DRF depth 12: 11.9 vs 14.5 ms).
+      int act = 0;
+      for (int l = 0; l < L; l++) act += t.h_descs[(size_t)l * C + c].nbin >= 0 ? 1 : 0;
+      if (2 * act < L) glob_cols.push_back(c);
+      else split_cols[st].push_back(c);
+    } else bucket[st].push_back(c);
   }
   t.smem_bytes = 0;
   for (int st = 0; st < 4; st++) {
     t.bucket_begin[st] = (int)t.h_groups.size();
     const std::vector<int>& cols = bucket[st];
-    if (cols.empty()) {
+    if (cols.empty() && split_cols[st].empty()) {
       t.bucket_end[st] = t.bucket_begin[st];
+      t.bucket_ctas[st] = 0;
       continue;
     }
+    std::vector<std::vector<int>> groups;
+    std::vector<double> gcost;
+    std::vector<std::pair<int, int>> granges;  // leaf range [begin, count) of each group
+    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / (double)L; };
+    if (!cols.empty()) {
     // Cost model: a column's atomics serialise when rows of a warp share a bin; with c = chance that two rows of the
     // root share a bin (measured by the last root level) and L leaves, cost ~ 1 + 8 c / L (fits the measured 3.6 vs 14
     // wavefronts per atomic of continuous vs 3-valued columns). Groups: fewest that fit, filled longest-first onto the
     // cheapest group (LPT); CTAs: shared out in proportion to the group costs so that all CTAs of the launch end together.
-    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / (double)L; };
     std::vector<int> order(cols);
     std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost_of(x) > cost_of(y); });
     size_t total_words = 0;
     for (int c : cols) total_words += (size_t)col_words[c];
-    std::vector<std::vector<int>> groups;
-    std::vector<double> gcost;
     for (size_t ng = std::max<size_t>(1, (total_words * 4 + budget - 1) / budget);; ng++) {
       groups.assign(ng, {});
       gcost.assign(ng, 0.0);
@@ -980,6 +995,37 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       }
       if (ok) break;
       if (ng > cols.size()) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "cannot place the level's histograms in shared memory");
+    }
+    granges.assign(groups.size(), std::make_pair(0, L));
+    }  // !cols.empty()
+    // a column whose leaves x bins exceed shared memory: one group per leaf range that fits (rows of other ranges are skipped)
+    for (int c : split_cols[st]) {
+      size_t widest = 0;
+      for (int l = 0; l < L; l++) widest = std::max(widest, (size_t)std::max(t.h_descs[(size_t)l * C + c].nbin + 1, 0) * WPB);
+      if (widest * 4 + fixed_bytes_l(1, st, 1) > full_budget) {  // a single (leaf, column) histogram is too wide: L2 atomics
+        glob_cols.push_back(c);
+        continue;
+      }
+      int l0 = 0;
+      while (l0 < L) {
+        size_t words = 0;
+        int l1 = l0;
+        while (l1 < L) {
+          const DescDev& d = t.h_descs[(size_t)l1 * C + c];
+          const size_t nw = words + (d.nbin >= 0 ? (size_t)(d.nbin + 1) * WPB : 0);
+          if (l1 > l0 && nw * 4 + fixed_bytes_l(1, st, l1 + 1 - l0) > budget) break;
+          words = nw;
+          l1++;
+        }
+        if (words * 4 + fixed_bytes_l(1, st, l1 - l0) > full_budget)
+          H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "one (leaf, column) histogram exceeds shared memory");
+        if (words > 0) {
+          groups.push_back({c});
+          gcost.push_back(cost_of(c) * (double)(l1 - l0) / (double)L);
+          granges.push_back(std::make_pair(l0, l1 - l0));
+        }
+        l0 = l1;
+      }
     }
     double cost_sum = 0;
     for (double v : gcost) cost_sum += v;
@@ -1003,12 +1049,12 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     for (size_t gi = 0; gi < groups.size(); gi++) {
       std::vector<int>& g = groups[gi];
       std::sort(g.begin(), g.end());
-      GroupDev gd{(int32_t)t.h_group_cols.size(), (int32_t)g.size(), 0, 0, st, slices[gi], cta, 0};
+      GroupDev gd{(int32_t)t.h_group_cols.size(), (int32_t)g.size(), 0, 0, st, slices[gi], cta, granges[gi].first, granges[gi].second, 0};
       cta += slices[gi];
       int off = 0;
       for (int c : g) {
         t.h_group_cols.push_back(c);
-        for (int l = 0; l < L; l++) {
+        for (int l = granges[gi].first; l < granges[gi].first + granges[gi].second; l++) {
           DescDev& d = t.h_descs[(size_t)l * C + c];
           if (d.nbin < 0) continue;
           d.smem_off = off;
@@ -1016,7 +1062,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
         }
       }
       gd.smem_words = off;
-      t.smem_bytes = std::max(t.smem_bytes, fixed_bytes((int)g.size(), st) + (size_t)off * 4);
+      t.smem_bytes = std::max(t.smem_bytes, fixed_bytes_l((int)g.size(), st, granges[gi].second) + (size_t)off * 4);
       t.h_groups.push_back(gd);
     }
     t.bucket_ctas[st] = cta;
@@ -1024,7 +1070,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   }
   t.n_smem_groups = (int)t.h_groups.size();
   for (int c : glob_cols) {
-    t.h_groups.push_back(GroupDev{(int32_t)t.h_group_cols.size(), 1, 0, 1, h->cols[c].storage, 1, 0, 0});
+    t.h_groups.push_back(GroupDev{(int32_t)t.h_group_cols.size(), 1, 0, 1, h->cols[c].storage, 1, 0, 0, L, 0});
     t.h_group_cols.push_back(c);
   }
   return H2OT_OK;

@@ -25,6 +25,8 @@ struct GroupDev {
   int32_t storage;          // H2OT_STORE_* shared by the group's columns
   int32_t n_slices;         // CTAs working on this group (proportional to its estimated cost)
   int32_t cta_begin;        // first blockIdx.x of the group inside its launch
+  int32_t l_begin, l_count; // leaves [l_begin, l_begin + l_count) handled by the group: all of them unless one column's
+                            // histograms exceed shared memory, then the column is cut into leaf ranges (one group each)
   int32_t pad;
 };
 
@@ -195,6 +197,10 @@ __device__ __forceinline__ void load4(const ColRef& c, int64_t row, double (&x)[
   }
 }
 
+// DHistogram.bin with the float-split correction (DRF), kept out of line: inlined it pushes the histogram loop past 64
+// registers and the spills go through the same L1 pipe as the atomics
+__device__ __noinline__ int bin_checkfloat(double x, double mn, double step, int nbin) { return bin_of(x, mn, step, nbin, true); }
+
 // ---- shared-memory access by 32-bit address, predicated in PTX: the compiler wraps every conditional atomic in a
 // BSSY / BRA / BSYNC sequence, which tripled the instruction count of the inner loop.
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -265,10 +271,15 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
     const uint32_t on = (row_on && place != kInactive) ? 1u : 0u;
     const int nbin = rr.nbin;
     const double mn = rr.mn, st = rr.st;
-    int b;
-    if (CHECKFLOAT) b = bin_of(x[j], mn, st, nbin, true);
-    else b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
-    b = na[j] ? nbin : b;
+    int b = nbin;
+    if (CHECKFLOAT) {
+      // the float-split correction costs two fp64 divisions; with per-node mtries most (leaf, column) pairs have no histogram,
+      // so it is only evaluated for rows that take part (a divergent branch is cheaper than dividing for nothing)
+      if (on && !na[j]) b = bin_checkfloat(x[j], mn, st, nbin);
+    } else {
+      b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
+      b = na[j] ? nbin : b;
+    }
     if (KEY64) {
       if (on && !na[j]) {
         const unsigned long long k = dkey(x[j]);
@@ -321,7 +332,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   const GroupDev grp = a.groups[g];
   const int slice = (int)blockIdx.x - grp.cta_begin;
   const int ncg = grp.ncols;
-  const int npairs = ncg * a.L;
+  const int LG = grp.l_count;  // leaves of this group
+  const int npairs = ncg * LG;
   MinMaxS* mmS = reinterpret_cast<MinMaxS*>(smem_raw);
   ColRef* colS = reinterpret_cast<ColRef*>(mmS + (KEY64 ? npairs : 0));
   int32_t* cidxS = reinterpret_cast<int32_t*>(colS + ncg);
@@ -338,7 +350,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   }
   __syncthreads();
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
-    const int gc = p / a.L, l = p - gc * a.L;
+    const int gc = p / LG, l = grp.l_begin + (p - gc * LG);
     const DescDev d = a.descs[(size_t)l * a.C + a.group_cols[grp.cols_off + gc]];
     uint32_t* r = T + (size_t)p * kTStride;
     r[kTMinLo] = (uint32_t)__double2loint(d.min);
@@ -353,7 +365,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   }
   __syncthreads();
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {  // columns with fp32-exact minima keep the float bits in kTMinLo
-    const int gc = p / a.L;
+    const int gc = p / LG;
     if (mn32S[gc]) {
       uint32_t* r = T + (size_t)p * kTStride;
       r[kTMinLo] = __float_as_uint((float)__hiloint2double((int)r[kTMinHi], (int)r[kTMinLo]));
@@ -374,6 +386,11 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     const int64_t row = tile * kTileRows + (int64_t)threadIdx.x * kRowsPerThread;
     const ushort4 cd = __ldg(reinterpret_cast<const ushort4*>(a.code + row));
     int leaf[4] = {cd.x, cd.y, cd.z, cd.w};
+#pragma unroll
+    for (int j = 0; j < 4; j++) {  // group-relative leaf; rows of other leaf ranges take no part here
+      const int rel = leaf[j] - grp.l_begin;
+      leaf[j] = (leaf[j] != kSkipCode && (unsigned)rel < (unsigned)LG) ? rel : kSkipCode;
+    }
     if (leaf[0] == kSkipCode && leaf[1] == kSkipCode && leaf[2] == kSkipCode && leaf[3] == kSkipCode) continue;
     const float4 yv = __ldg(reinterpret_cast<const float4*>(a.work + row));
     const float ys[4] = {yv.x, yv.y, yv.z, yv.w};
@@ -412,7 +429,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     for (int gc = 0; gc < ncg; gc++) {
       const RawT cur = nxt;
       if (gc + 1 < ncg) nxt = fetch(gc + 1);
-      const int pbase = gc * a.L;
+      const int pbase = gc * LG;
       double x[4];
       bool na[4];
       uint32_t key[4] = {0u, 0u, 0u, 0u};
@@ -458,7 +475,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     const uint32_t place = r[kTPlace] & 0xFFFFu;
     if (place == kInactive) continue;
     const int nbin = (int)(r[kTPlace] >> 16);
-    const int gc = p / a.L, l = p - gc * a.L;
+    const int gc = p / LG, l = grp.l_begin + (p - gc * LG);
     const size_t lc = (size_t)l * a.C + cidxS[gc];
     const DescDev dd = a.descs[lc];
     for (int b = lane; b <= nbin; b += 32) {

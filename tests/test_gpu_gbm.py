@@ -278,3 +278,19 @@ def test_log_link_distributions(dist):
     gm.train()
     h2ot_lib.compare_models(gm, om)
     gm.close()
+
+
+def test_deep_levels_split_into_leaf_ranges(monkeypatch):
+    """Levels whose leaves x bins exceed shared memory are cut into leaf-range groups (and a tiny budget forces the same
+    path at shallow levels): results must not depend on the grouping."""
+    X, y, cats = h2ot_lib.make_frame(n=40000, c=5, seed=61)
+    kw = dict(ntrees=2, max_depth=8, nbins=256, min_rows=1.0, seed=5)
+    gm, om = _run_both(X, y, cats, **kw)            # depth 8 x 257 bins: leaf ranges from level 6 on
+    h2ot_lib.compare_models(gm, om)
+    sig = [gm.predictions().tobytes()] + [bytes(gm.tree(t)[0]) for t in range(gm.ntrees)]
+    gm.close()
+    monkeypatch.setenv("H2OT_SMEM_BUDGET_KB", "24")  # one column per group, leaf ranges from level 3 on
+    gm2, _ = _run_both(X, y, cats, **kw)
+    h2ot_lib.compare_models(gm2, om)
+    assert sig == [gm2.predictions().tobytes()] + [bytes(gm2.tree(t)[0]) for t in range(gm2.ntrees)]
+    gm2.close()

@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--rows", type=int, default=11_000_000)
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--configs", default="1:1024,2:512,4:256,8:256,16:256,32:256")
+    ap.add_argument("--mode", type=int, default=0, help="1: force the global-atomics kernel")
     args = ap.parse_args()
     importlib.import_module("h2o-3_b200.build").build()
     P = importlib.import_module("h2o-3_b200")
@@ -32,6 +33,7 @@ def main():
     e.load_response(y)
     e.finalize_frame()
     e.init_model([0.0])
+    e.set_hist_mode(args.mode)
     rng = np.random.default_rng(0)
     work = (y - 0.53).astype(np.float32).astype(np.float64) + (rng.random(n) * 1e-3).astype(np.float32)
     e.set_work(work)
