@@ -562,11 +562,12 @@ int h2ot_init_model(h2ot_engine* h, const double* init_f, int64_t* out_skipped) 
 int h2ot_initial_stats(h2ot_engine* h, double* out_num, double* out_den, double* out_class_weight, double* out_abs_max) {
   CHECK_ENGINE(h);
   const int grid = grid_for(h, h->n, 256);
-  const int nc = h->cfg.nclass > 1 ? h->cfg.nclass : 0;
+  const int nc = (out_class_weight && h->cfg.nclass > 1) ? h->cfg.nclass : 0;
+  if (nc > kInitStatsClasses) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "class weights are computed for at most 1024 classes");
   DBuf<double> tmp;
   TRY(tmp.ensure((size_t)grid * 2 + nc + 1));
   CUDA_TRY(cudaMemsetAsync(tmp.p, 0, ((size_t)grid * 2 + nc + 1) * sizeof(double), h->stream));
-  InitStatsArgs a{h->n, h->cfg.nclass, h->cfg.family, h->cfg.tweedie_power, h->resp, h->w, h->off, tmp.p, tmp.p + (size_t)grid * 2,
+  InitStatsArgs a{h->n, h->cfg.nclass, h->cfg.family, h->cfg.tweedie_power, h->resp, h->w, h->off, tmp.p, nc ? tmp.p + (size_t)grid * 2 : nullptr,
                   reinterpret_cast<unsigned int*>(tmp.p + (size_t)grid * 2 + nc)};
   init_stats_kernel<<<grid, 256, 0, h->stream>>>(a);
   h->stats.launches++;

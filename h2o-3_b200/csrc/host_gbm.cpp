@@ -852,7 +852,7 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   {
     std::vector<double> cls((size_t)std::max(1, g->nclass) + 1, 0.0);
     double ymax = 0;
-    GTRY(h2ot_initial_stats(g->eng, &nd[0], &nd[1], g->nclass > 1 ? cls.data() : nullptr, &ymax));
+    GTRY(h2ot_initial_stats(g->eng, &nd[0], &nd[1], (drf && g->nclass > 1) ? cls.data() : nullptr, &ymax));
     GTRY(allreduce(g, nd, 2, 0));
     if (drf) {
       GTRY(allreduce(g, cls.data(), (int64_t)g->nclass, 0));

@@ -107,7 +107,12 @@ struct InitStatsArgs {
   double* class_w;         // [nclass] (nclass > 1), atomically accumulated
   unsigned int* ymax_bits; // float bits of max |(float) y|
 };
+constexpr int kInitStatsClasses = 1024;  // classes with block-private sums (power of two); nclass above that is rejected by the host
 __global__ void __launch_bounds__(256) init_stats_kernel(InitStatsArgs a) {
+  __shared__ double s_cls[kInitStatsClasses];
+  if (a.class_w)
+    for (int i = threadIdx.x; i < kInitStatsClasses; i += blockDim.x) s_cls[i] = 0.0;
+  __syncthreads();
   double num = 0, den = 0;
   float ymax = 0.f;
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
@@ -115,9 +120,9 @@ __global__ void __launch_bounds__(256) init_stats_kernel(InitStatsArgs a) {
     if (isnan(y)) continue;
     const double wv = a.w ? a.w[row] : 1.0;
     ymax = fmaxf(ymax, fabsf((float)y));
-    if (a.nclass > 1) {
+    if (a.class_w && wv != 0.0) {  // class prior (DRF only): block-private sums, flushed once per block
       const int c = (int)y;
-      if (c >= 0 && c < a.nclass && wv != 0.0) atomicAdd(&a.class_w[c], wv);
+      if (c >= 0 && c < a.nclass) atomicAdd(&s_cls[c & (kInitStatsClasses - 1)], wv);
     }
     if (wv == 0.0) continue;
     const double o = a.off ? a.off[row] : 0.0;
@@ -153,6 +158,9 @@ __global__ void __launch_bounds__(256) init_stats_kernel(InitStatsArgs a) {
   }
   for (int o = 16; o > 0; o >>= 1) ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
   if ((threadIdx.x & 31) == 0 && ymax > 0.f) atomicMax(a.ymax_bits, __float_as_uint(ymax));
+  if (a.class_w)
+    for (int i = threadIdx.x; i < a.nclass && i < kInitStatsClasses; i += blockDim.x)
+      if (s_cls[i] != 0.0) atomicAdd(&a.class_w[i], s_cls[i]);
 }
 
 // ------------------------------------------------------------------------------------------ residuals
