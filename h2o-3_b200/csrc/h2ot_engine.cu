@@ -926,16 +926,27 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
   auto fixed_bytes_l = [&](int ncg, int storage, int nleaves) {
     return (size_t)ncg * nleaves * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);
+           (size_t)ncg * (sizeof(ColRef) + 3 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);
   };
   auto fixed_bytes = [&](int ncg, int storage) {
     return (size_t)ncg * L * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
+           (size_t)ncg * (sizeof(ColRef) + 3 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
   };
   const size_t full_budget = (size_t)h->max_smem_optin;
   // the kernel runs one 1024-thread CTA per SM (64 registers/thread), so a CTA may use the whole opt-in carve-out
   size_t budget = full_budget;
   if (h->smem_budget_kb > 0) budget = std::min<size_t>((size_t)h->smem_budget_kb * 1024, full_budget);
+  // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses: give them 2 or 4
+  // replicas of their histograms (lanes pick one by lane id; the replicas are summed when the CTA merges) where that fits.
+  std::vector<int> col_rep(C, 1);
+  for (int c = 0; c < C; c++) {
+    if (!col_words[c] || h->hist_mode == 1) continue;
+    const double excess = 8.0 * h->col_conc[c] / (double)L;
+    int rep = excess >= 1.0 ? 4 : (excess >= 0.4 ? 2 : 1);
+    while (rep > 1 && (size_t)col_words[c] * rep * 4 + fixed_bytes(1, h->cols[c].storage) > budget / 2) rep >>= 1;
+    col_rep[c] = rep;
+    col_words[c] *= rep;
+  }
   t.h_groups.clear();
   t.h_group_cols.clear();
   t.active_cols = 0;
@@ -968,7 +979,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     std::vector<std::vector<int>> groups;
     std::vector<double> gcost;
     std::vector<std::pair<int, int>> granges;  // leaf range [begin, count) of each group
-    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / (double)L; };
+    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / ((double)L * col_rep[c]); };
     if (!cols.empty()) {
     // Cost model: a column's atomics serialise when rows of a warp share a bin; with c = chance that two rows of the
     // root share a bin (measured by the last root level) and L leaves, cost ~ 1 + 8 c / L (fits the measured 3.6 vs 14
@@ -1054,12 +1065,13 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       cta += slices[gi];
       int off = 0;
       for (int c : g) {
-        t.h_group_cols.push_back(c);
+        const int lg = col_rep[c] == 4 ? 2 : (col_rep[c] == 2 ? 1 : 0);
+        t.h_group_cols.push_back(c | (lg << 24));
         for (int l = granges[gi].first; l < granges[gi].first + granges[gi].second; l++) {
           DescDev& d = t.h_descs[(size_t)l * C + c];
           if (d.nbin < 0) continue;
           d.smem_off = off;
-          off += (d.nbin + 1) * WPB;
+          off += (d.nbin + 1) * WPB * col_rep[c];
         }
       }
       gd.smem_words = off;
@@ -1212,7 +1224,7 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     h->stats.hist_launches++;
   }
   for (size_t g = t.n_smem_groups; g < t.h_groups.size(); g++) {
-    const int c = t.h_group_cols[t.h_groups[g].cols_off];
+    const int c = t.h_group_cols[t.h_groups[g].cols_off] & 0xFFFFFF;
     const int grid = grid_for(h, h->n_pad / 4, 256, 8);
     if (h->w) hist_global_kernel<true><<<grid, 256, 0, h->stream>>>(ha, c, c + 1);
     else hist_global_kernel<false><<<grid, 256, 0, h->stream>>>(ha, c, c + 1);

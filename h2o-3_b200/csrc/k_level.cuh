@@ -254,7 +254,7 @@ __device__ __forceinline__ RecRegs load_rec(uint32_t rec) {
 }
 
 template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, bool MN32, int J0, int R>
-__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, const RecRegs& shared_rec,
+__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, int replica, const RecRegs& shared_rec,
                                            const int (&leaf)[4],
                                            const double (&x)[4], const bool (&na)[4], const uint32_t (&key)[4],
                                            const long long (&qw)[4], const long long (&qy)[4], const long long (&qyy)[4]) {
@@ -292,7 +292,8 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
       red_max_if_gt(rec + kTKmin * 4, ~key[j], rr.kmin, live);
       red_max_if_gt(rec + kTKmax * 4, key[j], rr.kmax, live);
     }
-    wd[j] = on ? hist_a + (place + (uint32_t)(b * WPB)) * 4u : sink_a;
+    // replica r of a pair sits r * (nbin + 1) bins after replica 0 (replica == 0 unless the planner replicated the column)
+    wd[j] = on ? hist_a + (place + (uint32_t)((replica * (nbin + 1) + b) * WPB)) * 4u : sink_a;
   }
   // low words first (their return values carry into the high words), then the high words
   constexpr uint32_t OW = 0, OY = (HAS_W ? 2 : 1) * 4, OYY = (HAS_W ? 4 : 3) * 4;
@@ -338,20 +339,23 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   ColRef* colS = reinterpret_cast<ColRef*>(mmS + (KEY64 ? npairs : 0));
   int32_t* cidxS = reinterpret_cast<int32_t*>(colS + ncg);
   int32_t* mn32S = cidxS + ncg;  // per group column: 1 when every active minimum of the column is fp32-exact
-  uint32_t* T = reinterpret_cast<uint32_t*>(mn32S + ncg);
+  int32_t* repS = mn32S + ncg;   // per group column: histogram replicas (1, 2 or 4; lanes pick one by lane id)
+  uint32_t* T = reinterpret_cast<uint32_t*>(repS + ncg);
   uint32_t* hist = T + (size_t)kTStride * npairs;
   uint32_t* sink = hist + grp.smem_words;
 
   for (int i = threadIdx.x; i < ncg; i += blockDim.x) {
-    const int c = a.group_cols[grp.cols_off + i];
+    const int cv = a.group_cols[grp.cols_off + i];  // column | log2(replicas) << 24
+    const int c = cv & 0xFFFFFF;
     cidxS[i] = c;
+    repS[i] = 1 << (cv >> 24);
     mn32S[i] = 1;
     colS[i] = a.cols[c];
   }
   __syncthreads();
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
     const int gc = p / LG, l = grp.l_begin + (p - gc * LG);
-    const DescDev d = a.descs[(size_t)l * a.C + a.group_cols[grp.cols_off + gc]];
+    const DescDev d = a.descs[(size_t)l * a.C + (a.group_cols[grp.cols_off + gc] & 0xFFFFFF)];
     uint32_t* r = T + (size_t)p * kTStride;
     r[kTMinLo] = (uint32_t)__double2loint(d.min);
     r[kTMinHi] = (uint32_t)__double2hiint(d.min);
@@ -453,16 +457,17 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
         for (int j = 0; j < 4; j++) na[j] = isnan(x[j]);
       }
       RecRegs rec0{};
+      const int replica = (int)(threadIdx.x & 31) & (repS[gc] - 1);
       if (mn32S[gc]) {  // uniform per column
         if (ONE_LEAF) rec0 = load_rec<true>(tab_a + (uint32_t)pbase * (kTStride * 4));  // root level: one record per column
-        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, leaf, x, na, key, qw, qy, qyy);
         if (kItemsInFlight < 4)
-          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, true, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, leaf, x, na, key, qw, qy, qyy);
       } else {
         if (ONE_LEAF) rec0 = load_rec<false>(tab_a + (uint32_t)pbase * (kTStride * 4));
-        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+        hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, leaf, x, na, key, qw, qy, qyy);
         if (kItemsInFlight < 4)
-          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, rec0, leaf, x, na, key, qw, qy, qyy);
+          hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, false, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, leaf, x, na, key, qw, qy, qyy);
       }
     }
   }
@@ -478,17 +483,20 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     const int gc = p / LG, l = grp.l_begin + (p - gc * LG);
     const size_t lc = (size_t)l * a.C + cidxS[gc];
     const DescDev dd = a.descs[lc];
+    const int nrep = repS[gc];
     for (int b = lane; b <= nbin; b += 32) {
-      const uint32_t* wd = hist + place + b * WPB;
-      long long vw, vy, vyy;
-      if (HAS_W) {
-        vw = (long long)(((unsigned long long)wd[1] << 32) | wd[0]);
-        vy = (long long)(((unsigned long long)wd[3] << 32) | wd[2]);
-        vyy = (long long)(((unsigned long long)wd[5] << 32) | wd[4]);
-      } else {
-        vw = (long long)wd[0];
-        vy = (long long)(((unsigned long long)wd[2] << 32) | wd[1]);
-        vyy = (long long)(((unsigned long long)wd[4] << 32) | wd[3]);
+      long long vw = 0, vy = 0, vyy = 0;
+      for (int r = 0; r < nrep; r++) {
+        const uint32_t* wd = hist + place + (r * (nbin + 1) + b) * WPB;
+        if (HAS_W) {
+          vw += (long long)(((unsigned long long)wd[1] << 32) | wd[0]);
+          vy += (long long)(((unsigned long long)wd[3] << 32) | wd[2]);
+          vyy += (long long)(((unsigned long long)wd[5] << 32) | wd[4]);
+        } else {
+          vw += (long long)wd[0];
+          vy += (long long)(((unsigned long long)wd[2] << 32) | wd[1]);
+          vyy += (long long)(((unsigned long long)wd[4] << 32) | wd[3]);
+        }
       }
       unsigned long long* dst = reinterpret_cast<unsigned long long*>(a.acc + (dd.gbin + b) * 3);
       if (vw) atomicAdd(dst, (unsigned long long)vw);
