@@ -72,7 +72,8 @@ class Stats(C.Structure):
                 ("ms_split", C.c_double), ("ms_residuals", C.c_double), ("ms_gamma", C.c_double),
                 ("ms_addtree", C.c_double), ("ms_sample", C.c_double), ("ms_ingest", C.c_double),
                 ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-                ("hist_rows_cols", C.c_int64), ("hist_algo_bytes", C.c_int64), ("hist_launches", C.c_int64)]
+                ("hist_rows_cols", C.c_int64), ("hist_algo_bytes", C.c_int64), ("hist_launches", C.c_int64),
+                ("sparse_launches", C.c_int64)]
 
 
 class GbmParams(C.Structure):

@@ -12,6 +12,7 @@
 
 #include "common.cuh"
 #include "k_level.cuh"
+#include "k_sparse.cuh"
 #include "k_rows.cuh"
 #include "k_split.cuh"
 #include "k_xreduce.cuh"
@@ -81,6 +82,8 @@ struct TreeState {  // per class-tree k
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
   int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
   int n_smem_groups = 0;
+  int n_sparse_groups = 0, sparse_ctas = 0;  // leaf-range groups of hist_sparse_kernel (levels with per-node column sampling)
+  double sparse_bytes_per_row = 0, sparse_cols_per_row = 0;
   size_t smem_bytes = 0;
   int64_t total_bins = 0, total_vals = 0;
   int active_cols = 0;
@@ -357,6 +360,10 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   H2OT_OPTIN(H2OT_STORE_U8);
   H2OT_OPTIN(H2OT_STORE_U16);
 #undef H2OT_OPTIN
+  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<5, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<5, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<7, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<7, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
   {
     cudaFuncAttributes fa;
     CUDA_TRY(cudaFuncGetAttributes(&fa, find_split_kernel));
@@ -936,6 +943,84 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // the kernel runs one 1024-thread CTA per SM (64 registers/thread), so a CTA may use the whole opt-in carve-out
   size_t budget = full_budget;
   if (h->smem_budget_kb > 0) budget = std::min<size_t>((size_t)h->smem_budget_kb * 1024, full_budget);
+  // ---- sparse level (per-node mtries / col_sample_rate): most (leaf, column) pairs have no histogram. Leaf-range groups for
+  // hist_sparse_kernel: a CTA owns consecutive leaves whose histograms + records fit shared memory and gathers, per row, only
+  // that row's leaf's columns (the column-major kernel would test rows x all columns, and re-scan per leaf range).
+  t.n_sparse_groups = 0;
+  t.sparse_ctas = 0;
+  if (h->hist_mode == 0 && L >= 2) {
+    int64_t pairs = 0, pair_bytes = 0;
+    int cols_act = 0;
+    bool any64 = false;
+    for (int c = 0; c < C; c++) cols_act += col_words[c] ? 1 : 0;
+    std::vector<int> m_leaf(L, 0);
+    std::vector<size_t> w_leaf(L, 0);
+    for (int l = 0; l < L; l++)
+      for (int c = 0; c < C; c++) {
+        const DescDev& d = t.h_descs[(size_t)l * C + c];
+        if (d.nbin < 0) continue;
+        pairs++;
+        m_leaf[l]++;
+        w_leaf[l] += (size_t)(d.nbin + 1) * WPB;
+        const int st = h->cols[c].storage;
+        pair_bytes += st == H2OT_STORE_F32 ? 4 : st == H2OT_STORE_F64 ? 8 : st == H2OT_STORE_U8 ? 1 : 2;
+        any64 |= st == H2OT_STORE_F64;
+      }
+    if (pairs > 0 && pairs * 5 <= (int64_t)L * cols_act * 4) {  // at most 80 % of the (leaf, column) pairs are active
+      const size_t col_bytes = C <= kSparseColsSmem ? (size_t)C * sizeof(ColRef) : 0;
+      auto fixed_sparse = [&](int leaves, int M) {
+        return (size_t)leaves * M * (kSStride * sizeof(uint32_t) + (any64 ? sizeof(MinMaxS) : 0)) + col_bytes + kSparseQueueWords * sizeof(uint32_t) + 64;
+      };
+      const size_t sbudget = (size_t)h->max_smem_optin;
+      std::vector<GroupDev> sg;
+      bool ok = true;
+      size_t smem_max = 0;
+      for (int l0 = 0; l0 < L && ok;) {
+        size_t words = 0;
+        int M = 1, l1 = l0;
+        while (l1 < L) {
+          const int Mn = std::max(M, m_leaf[l1]);
+          if ((words + w_leaf[l1]) * 4 + fixed_sparse(l1 + 1 - l0, Mn) > sbudget || words + w_leaf[l1] >= 0xFFFFu) break;
+          words += w_leaf[l1];
+          M = Mn;
+          l1++;
+        }
+        if (l1 == l0) { ok = false; break; }  // one leaf alone does not fit: leave the level to the column-major planner
+        sg.push_back(GroupDev{0, M, (int32_t)words, 2, any64 ? 1 : 0, 1, 0, l0, l1 - l0, 0});
+        smem_max = std::max(smem_max, words * 4 + fixed_sparse(l1 - l0, M));
+        l0 = l1;
+      }
+      if (ok) {
+        const int G = (int)sg.size();
+        const int n_ctas = std::max(h->sm_count, G);
+        int cta = 0;
+        for (int gi = 0; gi < G; gi++) {
+          sg[gi].n_slices = n_ctas / G + (gi < n_ctas % G ? 1 : 0);
+          sg[gi].cta_begin = cta;
+          cta += sg[gi].n_slices;
+          int off = 0;
+          for (int l = sg[gi].l_begin; l < sg[gi].l_begin + sg[gi].l_count; l++)
+            for (int c = 0; c < C; c++) {
+              DescDev& d = t.h_descs[(size_t)l * C + c];
+              if (d.nbin < 0) continue;
+              d.smem_off = off;
+              off += (d.nbin + 1) * WPB;
+            }
+        }
+        t.h_groups = sg;
+        t.h_group_cols.clear();
+        t.active_cols = cols_act;
+        t.n_sparse_groups = G;
+        t.sparse_ctas = cta;
+        t.n_smem_groups = G;
+        t.smem_bytes = smem_max;
+        t.sparse_bytes_per_row = (double)pair_bytes / L;
+        t.sparse_cols_per_row = (double)pairs / L;
+        for (int st = 0; st < 4; st++) t.bucket_begin[st] = t.bucket_end[st] = t.bucket_ctas[st] = 0;
+        return H2OT_OK;
+      }
+    }
+  }
   // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses: give them 2 or 4
   // replicas of their histograms (lanes pick one by lane id; the replicas are summed when the CTA merges) where that fits.
   std::vector<int> col_rep(C, 1);
@@ -1194,6 +1279,23 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   ha.sw = std::ldexp(1.0, ew);
   TRY(t_begin(h, &h->stats.ms_hist));
   if (t.n_smem_groups > 0 && t.smem_bytes > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "shared-memory plan exceeds the device limit");
+  if (t.n_sparse_groups > 0) {
+    ha.group_begin = 0;
+    ha.n_groups = t.n_sparse_groups;
+    ha.n_slices = 0;
+    const int grid = t.sparse_ctas;
+    const size_t sm = t.smem_bytes;
+    if (h->w) {
+      if (t.any_checkfloat) hist_sparse_kernel<7, true, true><<<grid, kHistThreads, sm, h->stream>>>(ha);
+      else hist_sparse_kernel<7, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);
+    } else {
+      if (t.any_checkfloat) hist_sparse_kernel<5, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);
+      else hist_sparse_kernel<5, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);
+    }
+    h->stats.launches++;
+    h->stats.hist_launches++;
+    h->stats.sparse_launches++;
+  }
   for (int st = 0; st < 4; st++) {
     const int ng = t.bucket_end[st] - t.bucket_begin[st];
     if (ng <= 0) continue;
@@ -1242,7 +1344,12 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     const int st = h->cols[c].storage;
     bytes_per_row += st == H2OT_STORE_F32 ? 4 : st == H2OT_STORE_F64 ? 8 : st == H2OT_STORE_U8 ? 1 : 2;
   }
-  h->stats.hist_rows_cols += h->n * (int64_t)t.active_cols;
+  if (t.n_sparse_groups > 0) {  // a row needs only its own leaf's columns: average over the leaves
+    bytes_per_row = 4 + 4 + (leaf_offset > 0 ? 4 : 0) + (h->w ? 4 : 0) + (int64_t)std::llround(t.sparse_bytes_per_row);
+    h->stats.hist_rows_cols += (int64_t)std::llround((double)h->n * t.sparse_cols_per_row);
+  } else {
+    h->stats.hist_rows_cols += h->n * (int64_t)t.active_cols;
+  }
   h->stats.hist_algo_bytes += h->n * bytes_per_row + t.total_bins * 24;
   t.built = true;
   return finish_call(h);
@@ -1683,7 +1790,7 @@ int h2ot_set_weight_bound(h2ot_engine* h, double bound) {
   return H2OT_OK;
 }
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode) {
-  if (!h || mode < 0 || mode > 1) H2OT_FAIL(H2OT_ERR_INVALID, "bad mode");
+  if (!h || mode < 0 || mode > 2) H2OT_FAIL(H2OT_ERR_INVALID, "bad mode");
   h->hist_mode = mode;
   return H2OT_OK;
 }

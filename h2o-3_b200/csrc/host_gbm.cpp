@@ -66,7 +66,12 @@ inline double ulp_d(double d) {  // Math.ulp(double)
   d = std::fabs(d);
   if (std::isinf(d)) return d;
   if (d == DBL_MAX) return std::ldexp(1.0, 971);
-  return std::nextafter(d, INFINITY) - d;
+  uint64_t u;  // next representable value above a finite d >= 0: the bit pattern plus one (no libm call on this hot host path)
+  memcpy(&u, &d, sizeof u);
+  u++;
+  double nx;
+  memcpy(&nx, &u, sizeof nx);
+  return nx - d;
 }
 inline bool within_one_small_ulp(double a, double b) {  // water/util/MathUtils.java:391-397
   if (std::isnan(a) && std::isnan(b)) return true;
@@ -180,6 +185,7 @@ struct Tree {
   std::vector<int> cols;
   std::vector<Node> ns;
   std::vector<int> dirty;  // decided nodes whose device copy is stale
+  std::vector<int> draw_scratch;
 
   Tree(int ncols_, int mtrys_, int mtrys_per_tree_, int64_t seed_, double change)
       : ncols(ncols_), seed(seed_), mtrys(mtrys_), mtrys_per_tree(mtrys_per_tree_), change_per_level(change), rand(seed_) {
@@ -206,16 +212,19 @@ struct Tree {
   }
   // UndecidedNode ctor + scoreCols (:443-499)
   int new_undecided(int pid, std::vector<Hist> hs) {
-    Node n;
+    if (ns.capacity() == ns.size()) ns.reserve(std::max<size_t>(1024, ns.size() * 4));  // a Node carries its split record (bitset included)
+    ns.emplace_back();
+    Node& n = ns.back();
     n.kind = 0;
     n.pid = pid;
-    n.nid = len();
+    n.nid = len() - 1;
     n.hs = std::move(hs);
     const int hslen = (int)n.hs.size();
     if (actual_mtries() == hslen && mtrys_per_tree == hslen) {
       n.score_cols_null = true;
     } else {
-      std::vector<int> c(cols.size());
+      std::vector<int>& c = draw_scratch;
+      c.resize(cols.size());
       int l = 0;
       for (size_t i = 0; i < cols.size(); i++) {
         if (!n.hs[cols[i]].present) continue;
@@ -234,8 +243,7 @@ struct Tree {
       n.score_cols_null = false;
       n.score_cols.assign(c.begin() + l, c.begin() + choices);
     }
-    ns.push_back(std::move(n));
-    return ns.back().nid;
+    return n.nid;
   }
   void do_not_split(int nid) {  // :504-511
     const int pid = ns[nid].pid;
@@ -248,13 +256,14 @@ struct Tree {
       }
   }
   int new_leaf(int pid) {
-    Node n;
+    if (ns.capacity() == ns.size()) ns.reserve(std::max<size_t>(1024, ns.size() * 4));
+    ns.emplace_back();
+    Node& n = ns.back();
     n.kind = 2;
     n.pid = pid;
-    n.nid = len();
-    ns.push_back(n);
+    n.nid = len() - 1;
     leaves++;
-    return ns.back().nid;
+    return n.nid;
   }
 };
 
@@ -488,10 +497,17 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
   for (int c = 0; c < C; c++) ncol_active += col_active[c];
   g->timing.hist_rows_cols += (double)g->nrows_global * (double)ncol_active;
 
-  // onCompletion: DecidedNode ctor per leaf (T/DTree.java:703-726)
+  // onCompletion: DecidedNode ctor per leaf (T/DTree.java:703-726). First the children's histogram descriptors
+  // (nextLevelHistos: 2 x ncols DHistogram.make per split), then node ids and the per-node column draws (tree._rand) in leaf
+  // order. (Preparing the descriptors on several host threads was measured and dropped: the hand-over of the descriptor
+  // vectors between cores cost what the threads saved, 1.42 vs 1.16 ms at 614 leaves.)
+  struct Kids { std::vector<Hist> hs, nh[2]; };
+  std::vector<Kids> kids((size_t)L);
   for (int l = 0; l < L; l++) {
     const int nid = leaf_offset + l;
-    std::vector<Hist> hs = std::move(tree.ns[nid].hs);
+    Kids& kd = kids[(size_t)l];
+    kd.hs = std::move(tree.ns[nid].hs);
+    std::vector<Hist>& hs = kd.hs;
     for (int c = 0; c < C && !hs.empty(); c++) {
       Hist& h = hs[c];
       const size_t i = (size_t)l * C + c;
@@ -501,13 +517,21 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
       h.max_in = g->max_in[i];
       h.w_na = g->w_na[i];
     }
+    const h2ot_split& s = g->splits[l];
+    if (s.col < 0 || hs.empty()) continue;
+    for (int way = 0; way < 2; way++) kd.nh[way] = next_level_histos(g, s, hs, way, (double)s.splat);
+  }
+  const double t_kids_done = now_s();
+  for (int l = 0; l < L; l++) {
+    const int nid = leaf_offset + l;
+    Kids& kd = kids[(size_t)l];
     Node& dnode = tree.ns[nid];
     dnode.kind = 1;
     dnode.hs.clear();
     dnode.score_cols.clear();
     const h2ot_split& s = g->splits[l];
     tree.dirty.push_back(nid);
-    if (s.col < 0 || hs.empty()) {
+    if (s.col < 0 || kd.hs.empty()) {
       dnode.has_split = false;
       dnode.splat = NAN;
       dnode.nids[0] = dnode.nids[1] = kUndecidedChild;
@@ -520,8 +544,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     did_split = true;
     g->varimp[s.col] += (float)(s.se - (s.se0 + s.se1));  // T/SharedTree.java:697-700
     for (int way = 0; way < 2; way++) {
-      std::vector<Hist> nh = next_level_histos(g, s, hs, way, (double)s.splat);
-      const int child = nh.empty() ? kUndecidedChild : tree.new_undecided(nid, std::move(nh));
+      const int child = kd.nh[way].empty() ? kUndecidedChild : tree.new_undecided(nid, std::move(kd.nh[way]));
       tree.ns[nid].nids[way] = child;
     }
   }
@@ -529,8 +552,8 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
   if (did_split) tree.depth++;
   static const bool trace = getenv("H2OT_TRACE") != nullptr;
   if (trace)
-    fprintf(stderr, "[h2ot-host] L=%d: descs+call %.3f ms (call starts %.3f ms after entry), decide %.3f ms\n", L, 1e3 * (t_call_end - t0),
-            1e3 * (t_descs_done - t0), 1e3 * (now_s() - t_call_end));
+    fprintf(stderr, "[h2ot-host] L=%d: descs+call %.3f ms (call starts %.3f ms after entry), decide %.3f ms (children's descriptors %.3f)\n", L,
+            1e3 * (t_call_end - t0), 1e3 * (t_descs_done - t0), 1e3 * (now_s() - t_call_end), 1e3 * (t_kids_done - t_call_end));
   return H2OT_OK;
 }
 

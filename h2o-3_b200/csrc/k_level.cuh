@@ -200,6 +200,20 @@ __device__ __forceinline__ void load4(const ColRef& c, int64_t row, double (&x)[
 // DHistogram.bin with the float-split correction (DRF), kept out of line: inlined it pushes the histogram loop past 64
 // registers and the spills go through the same L1 pipe as the atomics
 __device__ __noinline__ int bin_checkfloat(double x, double mn, double step, int nbin) { return bin_of(x, mn, step, nbin, true); }
+// Same result without the two fp64 divisions for values that sit well inside their bin. The correction compares x with the
+// FLOAT-rounded edges of its bin, float(min + i/step): an edge moves by at most 2^-24 |edge| (+ fp64 noise) when rounded, i.e. by
+// less than g = 2^-22 (|min| step + nbin) bin widths, so a value whose fractional position is inside (g, 1 - g) keeps the
+// truncated index. Everything else (edges, +-Inf, below-min) takes the exact path. Not applied to the last bin, where the
+// reference skips the correction as well (idx + 1 < length fails).
+__device__ __forceinline__ int bin_checkfloat_fast(double x, double mn, double step, int nbin) {
+  const double pos = __dmul_rn(__dsub_rn(x, mn), step);
+  const int idx = __double2int_rz(pos);
+  if (idx >= nbin - 1) return nbin - 1;
+  const double frac = pos - (double)idx;
+  const double g = 2.384185791015625e-07 * (fabs(mn) * step + (double)nbin);  // 2^-22
+  if (frac > g && frac < 1.0 - g) return idx;
+  return bin_checkfloat(x, mn, step, nbin);
+}
 
 // ---- shared-memory access by 32-bit address, predicated in PTX: the compiler wraps every conditional atomic in a
 // BSSY / BRA / BSYNC sequence, which tripled the instruction count of the inner loop.
@@ -275,7 +289,11 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
     if (CHECKFLOAT) {
       // the float-split correction costs two fp64 divisions; with per-node mtries most (leaf, column) pairs have no histogram,
       // so it is only evaluated for rows that take part (a divergent branch is cheaper than dividing for nothing)
-      if (on && !na[j]) b = bin_checkfloat(x[j], mn, st, nbin);
+      // (the sign bit of the record's step carries the descriptor's H2OT_DESC_CHECKFLOAT flag)
+      if (on && !na[j]) {
+        const double sa = fabs(st);
+        b = st < 0 ? bin_checkfloat_fast(x[j], mn, sa, nbin) : max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), sa)), nbin - 1));
+      }
     } else {
       b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
       b = na[j] ? nbin : b;
@@ -360,7 +378,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     r[kTMinLo] = (uint32_t)__double2loint(d.min);
     r[kTMinHi] = (uint32_t)__double2hiint(d.min);
     r[kTStepLo] = (uint32_t)__double2loint(d.step);
-    r[kTStepHi] = (uint32_t)__double2hiint(d.step);
+    r[kTStepHi] = (uint32_t)__double2hiint(d.step) | ((CHECKFLOAT && (d.flags & H2OT_DESC_CHECKFLOAT)) ? 0x80000000u : 0u);
     r[kTPlace] = (d.nbin < 0 ? kInactive : (uint32_t)d.smem_off) | ((uint32_t)max(d.nbin, 1) << 16);
     r[kTKmin] = 0u;
     r[kTKmax] = 0u;

@@ -137,6 +137,7 @@ typedef struct h2ot_stats { /* diagnostics: device time per kernel family (ms) a
   int64_t hist_rows_cols;    /* sum over level passes of local rows x active columns */
   int64_t hist_algo_bytes;   /* algorithmic bytes of those passes (SURVEY.md section 8d formula) */
   int64_t hist_launches;     /* histogram-accumulation kernel launches (ms_hist / hist_launches = mean launch time) */
+  int64_t sparse_launches;   /* of those: launches of the leaf-major kernel used on levels with per-node column sampling */
 } h2ot_stats;
 
 /* ---- lifetime: one engine per model build per GPU (created after T/SharedTree.java:385, destroyed in the finally at :407-425) */
@@ -270,7 +271,8 @@ int h2ot_set_weight_bound(h2ot_engine* h, double bound);
 int h2ot_debug_bin_codes(h2ot_engine* h, int32_t col, const h2ot_hist_desc* desc, uint16_t* out_codes);
 int h2ot_stats_get(h2ot_engine* h, h2ot_stats* out);
 int h2ot_stats_reset(h2ot_engine* h);
-/* 0: shared-memory privatised histograms (default), 1: global (L2) atomics only — used by tests to cross-check. */
+/* 0: default (shared-memory privatised histograms; leaf-major sparse kernel on levels with per-node column sampling),
+ * 1: global (L2) atomics only, 2: column-major shared-memory kernels only — 1 and 2 are used by tests to cross-check. */
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
 
 /* ---- histogram of one column for callers that cannot allocate device memory.

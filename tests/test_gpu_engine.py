@@ -311,3 +311,81 @@ def test_sampler_bit_exact():
         want_nids = np.where((want == 1) | np.isnan(y), P.OUT_OF_BAG, want_nids)
         assert np.array_equal(got, want_nids)
         e.close()
+
+
+@pytest.mark.parametrize("weighted,check_float", [(False, False), (False, True), (True, True)])
+def test_sparse_level_kernels_agree(weighted, check_float):
+    """A level where every leaf histograms its own few columns (UndecidedNode.scoreCols, T/DTree.java:443-499; q8:
+    T/ScoreBuildHistogram2.java:421-422): the leaf-major kernel (mode 0 picks it), the column-major shared-memory
+    kernels (mode 2) and the L2-atomics kernel (mode 1) must give identical bits, and match updateHisto
+    (T/DHistogram.java:609-658) per (leaf, column)."""
+    rng = np.random.default_rng(11)
+    n, L, per_leaf = 260001, 150, 3
+    cols = [rng.normal(size=n).astype(np.float32).astype(np.float64) for _ in range(5)]
+    cols += [rng.lognormal(size=n), rng.normal(size=n) * 1e-3 + 7.0]                       # f64 storage
+    cols += [rng.integers(0, 9, n).astype(np.float64), rng.integers(-3, 200, n).astype(np.float64)]      # u8
+    cols += [rng.integers(0, 5000, n).astype(np.float64), rng.integers(-900, 30000, n).astype(np.float64)]  # u16
+    cols += [rng.choice([0.0, 1.09, 2.17], n).astype(np.float32).astype(np.float64)]
+    X = np.stack(cols, axis=1)
+    X[rng.random(X.shape) < 0.03] = NaN
+    C_ = X.shape[1]
+    is_int = [0] * 7 + [1] * 4 + [0]
+    work = (rng.random(n) - 0.5).astype(np.float32).astype(np.float64)
+    w = rng.integers(0, 3, n).astype(np.float64) if weighted else None
+    P, e = _engine(X, w=w)
+    e.set_work(work)
+    e.begin_tree(0, 0, 1.0, float(np.max(np.abs(work)) * (2.0 if weighted else 1.0)))
+    # rows sit directly in leaves 1..L: a root-like decided node without a split keeps its rows (nid - leaf_offset)
+    leaf_of = rng.integers(0, L, n).astype(np.int32)
+    nids = (leaf_of + 1).astype(np.int32)
+    skipped = rng.random(n) < 0.2
+    nids[skipped] = P.DECIDED_ROW
+    if weighted:
+        nids[w == 0] = P.DECIDED_ROW
+    e.set_nids(nids)
+    dn = (P.DecidedNode * (L + 1))()
+    for i in range(L + 1):
+        dn[i] = P.DecidedNode(nid=i, pid=-1, col=-1, equal=0, nasplit=P.NA_NONE, splat=NaN, child=(C.c_int32 * 2)(-1, -1))
+    descs = (P.HistDesc * (L * C_))()
+    spec = {}
+    for l in range(L):
+        for j, c in enumerate(rng.choice(C_, per_leaf, replace=False)):
+            v = X[:, c]
+            lo, hi = np.nanmin(v), np.nanmax(v)
+            maxEx = O.lib().orc_find_maxEx(hi, is_int[c])
+            nbins = int(rng.choice([20, 64, 256]))
+            a = (nbins, 1024, is_int[c], lo, maxEx, False, True)
+            oh = O.Hist(*a)
+            spec[(l, int(c))] = a
+            descs[l * C_ + int(c)] = P.make_desc(lo, maxEx, oh.nbin, step=oh.step, is_int=is_int[c], init_na=True, order=j,
+                                                 check_float=check_float and is_int[c] == 0)
+    results, launches = [], []
+    for mode in (0, 2, 1):
+        e.set_hist_mode(mode)
+        e.stats_reset()
+        e.build_level(descs, leaf_offset=1, decided=dn)
+        results.append(e.finish_level())
+        launches.append(e.stats().sparse_launches)
+        assert np.array_equal(e.get_nids(), nids)
+    assert launches == [1, 0, 0]
+    for r in results[1:]:
+        assert np.array_equal(results[0]["vals"], r["vals"])
+        assert np.array_equal(results[0]["min2"], r["min2"]) and np.array_equal(results[0]["maxIn"], r["maxIn"])
+        assert np.array_equal(results[0]["has_vals"], r["has_vals"])
+    r = results[0]
+    live = nids != P.DECIDED_ROW
+    for (l, c) in list(spec)[::7]:
+        rows = np.nonzero(live & (leaf_of == l))[0].astype(np.int32)
+        if check_float and is_int[c] == 0:
+            continue  # the float-split correction is checked against the oracle in test_bin_codes_bit_exact
+        oh = _oracle_hist(spec[(l, c)], X[:, c], work[rows], w, rows)
+        ov = oh.vals()
+        off = r["offsets"][l * C_ + c]
+        gv = r["vals"][off: off + ov.size]
+        assert np.array_equal(gv[0::3], ov[0::3]), (l, c)
+        for j in (1, 2):
+            scale = max(np.max(np.abs(ov[j::3])), 1e-300)
+            assert np.max(np.abs(gv[j::3] - ov[j::3])) <= 1e-6 * scale, (l, c, j)
+        if rows.size and np.any(~np.isnan(X[rows, c])):
+            assert r["min2"][l * C_ + c] == oh.min2 and r["maxIn"][l * C_ + c] == oh.maxIn, (l, c)
+    e.close()
