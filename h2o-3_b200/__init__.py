@@ -111,10 +111,10 @@ ENGINE_SYMBOLS = [
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc",
+    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column",
 ]
 GBM_SYMBOLS = [
-    "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
+    "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
     "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
@@ -143,6 +143,10 @@ def load():
     for n in ("h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset"):
         getattr(L, n).argtypes = [vp, i64, i64, vp]
     L.h2ot_load_column.argtypes = [vp, i32, i64, i64, vp]
+    L.h2ot_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
+    L.h2ot_debug_get_column.argtypes = [vp, i32, i64, i64, vp]
+    L.h2ot_gbm_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
+    L.h2ot_gbm_chunks_done.argtypes = [vp, i32, i32, i32]
     L.h2ot_finalize_frame.argtypes = [vp]
     L.h2ot_column_info_get.argtypes = [vp, i32, C.POINTER(ColumnInfo)]
     L.h2ot_init_model.argtypes = [vp, vp, C.POINTER(i64)]
@@ -277,6 +281,18 @@ class Engine:
     def load_column(self, col, values, row0=0):
         v = _f64(values)
         _check(self.L.h2ot_load_column(self.h, col, row0, v.size, _p(v)))
+
+    def load_chunk(self, col, codec, mem, row0, n):
+        """One H2O chunk (its _mem bytes) decoded on the device into rows [row0, row0 + n) of column col (-1 response,
+        -2 weights, -3 offset)."""
+        m = np.ascontiguousarray(mem, dtype=np.uint8)
+        _check(self.L.h2ot_load_chunk(self.h, col, row0, n, codec, _p(m), m.size))
+
+    def get_column(self, col, row0=0, n=None):
+        n = self.nrows - row0 if n is None else n
+        out = np.empty(n, dtype=np.float64)
+        _check(self.L.h2ot_debug_get_column(self.h, col, row0, n, _p(out)))
+        return out
 
     def load_response(self, y, row0=0):
         v = _f64(y)
@@ -491,6 +507,37 @@ class GBM:
         if offset is not None:
             v = _f64(offset)
             _check(self.L.h2ot_gbm_set_offset(self.g, _p(v)))
+        _check(self.L.h2ot_gbm_init(self.g))
+        return self
+
+    def load_chunks(self, nrows, columns, y, weights=None, offset=None, categorical=None):
+        """Like load(), from H2O chunks: every column (and y / weights / offset) is a list of (codec, mem_bytes, n_rows) in row
+        order -- what a Java caller has in Vec.chunkForChunkIdx(i)._mem. Decoded on the device (h2ot_load_chunk)."""
+        self.close()
+        ncols = len(columns)
+        self.nrows, self.ncols = nrows, ncols
+        self.g = C.c_void_p()
+        _check(self.L.h2ot_gbm_create(C.byref(self.params), self.device, nrows, ncols, 0, 0,
+                                      int(weights is not None), int(offset is not None), C.byref(self.g)))
+        categorical = categorical or {}
+
+        def push(col, chunks, is_cat=0, card=0):
+            row0 = 0
+            for codec, mem, n in chunks:
+                m = np.ascontiguousarray(mem, dtype=np.uint8)
+                _check(self.L.h2ot_gbm_load_chunk(self.g, col, row0, n, codec, _p(m), m.size))
+                row0 += n
+            if row0 != nrows:
+                raise ValueError("chunks of column %d cover %d of %d rows" % (col, row0, nrows))
+            _check(self.L.h2ot_gbm_chunks_done(self.g, col, is_cat, card))
+
+        for c, chunks in enumerate(columns):
+            push(c, chunks, int(c in categorical), int(categorical.get(c, 0)))
+        push(-1, y)
+        if weights is not None:
+            push(-2, weights)
+        if offset is not None:
+            push(-3, offset)
         _check(self.L.h2ot_gbm_init(self.g))
         return self
 

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libh2otree_b200.so")
 SOURCES = ["h2ot_engine.cu", "h2ot_noalloc.cu", "host_gbm.cpp"]
-HEADERS = ["common.cuh", "k_level.cuh", "k_sparse.cuh", "k_xreduce.cuh", "k_rows.cuh", "k_split.cuh", "../../include/h2ot.h", "../../include/h2ot_gbm.h"]
+HEADERS = ["common.cuh", "k_level.cuh", "k_sparse.cuh", "k_ingest.cuh", "k_xreduce.cuh", "k_rows.cuh", "k_split.cuh", "../../include/h2ot.h", "../../include/h2ot_gbm.h"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: the fp64 arithmetic of DHistogram.bin / findBestSplitPoint must round like the JVM (no FMA contraction)
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false", "-Xcompiler",

@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include "k_level.cuh"
 #include "k_sparse.cuh"
+#include "k_ingest.cuh"
 #include "k_rows.cuh"
 #include "k_split.cuh"
 #include "k_xreduce.cuh"
@@ -148,6 +149,8 @@ struct h2ot_engine {
   double* resp_staging = nullptr;
   double* oobt = nullptr;  // DRF: OUT_BAG_TREES column
   double* staging_all = nullptr;
+  DBuf<uint8_t> d_chunk;  // device copy of the Chunk._mem being decoded (h2ot_load_chunk), grow-only
+  DBuf<int32_t> d_chunk_err;
   unsigned char* col_block = nullptr;  // all encoded columns (each 256-byte aligned)
   double w_max = 1.0;
   double gamma_bound[2] = {1.0, 1.0};  // max |gammaNum / w|, max |gammaDenom / w| of the current residuals
@@ -384,6 +387,8 @@ int h2ot_destroy(h2ot_engine* h) {
   }
   if (h->col_block) cudaFree(h->col_block);
   if (h->staging_all) cudaFree(h->staging_all);
+  h->d_chunk.release();
+  h->d_chunk_err.release();
   if (h->resp) cudaFree(h->resp);
   if (h->w) cudaFree(h->w);
   if (h->off) cudaFree(h->off);
@@ -443,6 +448,151 @@ int h2ot_load_offset(h2ot_engine* h, int64_t row0, int64_t n, const double* valu
   CHECK_ENGINE(h);
   if (!h->off) H2OT_FAIL(H2OT_ERR_INVALID, "engine was created without an offset column");
   return load_rows(h, h->off, row0, n, values);
+}
+
+namespace {
+inline int32_t rd_i32(const uint8_t* p) { int32_t v; memcpy(&v, p, 4); return v; }
+inline int64_t rd_i64(const uint8_t* p) { int64_t v; memcpy(&v, p, 8); return v; }
+inline double rd_f64(const uint8_t* p) { double v; memcpy(&v, p, 8); return v; }
+// PrettyPrint.pow10(int) for exp >= 0 (W/util/PrettyPrint.java:80-129): a table up to 1e10, Math.pow(10, exp) beyond -- exact
+// powers of ten are representable up to 1e22, past that the C library's pow stands in for the JVM's
+inline double pow10_nonneg(int e) {
+  static const double t[] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15,
+                             1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+  return e <= 22 ? t[e] : std::pow(10.0, (double)e);
+}
+}  // namespace
+
+int h2ot_load_chunk(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, int32_t codec, const uint8_t* mem, int64_t mem_len) {
+  CHECK_ENGINE(h);
+  if (!mem || mem_len < 0 || n < 0 || row0 < 0 || row0 + n > h->n) H2OT_FAIL(H2OT_ERR_INVALID, "bad chunk / row range out of bounds");
+  double* dst = nullptr;
+  if (col >= 0) {
+    if (col >= h->C) H2OT_FAIL(H2OT_ERR_INVALID, "column index out of range");
+    if (h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame already finalized");
+  } else if (col == H2OT_COL_RESPONSE) {
+    dst = h->resp;
+  } else if (col == H2OT_COL_WEIGHTS) {
+    if (!h->w) H2OT_FAIL(H2OT_ERR_INVALID, "engine was created without a weights column");
+    dst = h->w;
+  } else if (col == H2OT_COL_OFFSET) {
+    if (!h->off) H2OT_FAIL(H2OT_ERR_INVALID, "engine was created without an offset column");
+    dst = h->off;
+  } else {
+    H2OT_FAIL(H2OT_ERR_INVALID, "column index out of range");
+  }
+  // ---- header, as Chunk.initFromBytes reads it; the chunk's own row count must be n
+  ChunkArgs a{};
+  a.codec = codec;
+  a.n = n;
+  int64_t rows = -1;
+  auto cs_header = [&](int log) -> bool {  // CSChunk.initFromBytes :57-64
+    if (mem_len < kCSOff) return false;
+    a.bias = rd_i64(mem);
+    const int x = rd_i32(mem + 8), sz = rd_i32(mem + 12);
+    a.decimal = sz < 0 ? 1 : 0;
+    if ((sz < 0 ? -sz - 1 : sz) != log) return false;
+    const int e = a.decimal ? -x : x;  // _scale = PrettyPrint.pow10(1, e): e < 0 ? 1 / pow10(-e) : 1 * pow10(e)
+    if (e < -330 || e > 330) return false;
+    a.scale = e < 0 ? 1.0 / pow10_nonneg(-e) : pow10_nonneg(e);
+    rows = (mem_len - kCSOff) >> log;
+    return ((mem_len - kCSOff) & ((1 << log) - 1)) == 0;
+  };
+  bool ok = true;
+  switch (codec) {
+    case H2OT_CODEC_C0D: ok = mem_len == 12; if (ok) { a.con = rd_f64(mem); rows = rd_i32(mem + 8); } break;
+    case H2OT_CODEC_C0L: ok = mem_len == 12; if (ok) { a.con = (double)rd_i64(mem); rows = rd_i32(mem + 8); } break;
+    case H2OT_CODEC_C1:
+    case H2OT_CODEC_C1N: rows = mem_len; break;
+    case H2OT_CODEC_C1S: ok = cs_header(0); break;
+    case H2OT_CODEC_C2: ok = (mem_len & 1) == 0; rows = mem_len >> 1; break;
+    case H2OT_CODEC_C2S: ok = cs_header(1); break;
+    case H2OT_CODEC_C4:
+    case H2OT_CODEC_C4F: ok = (mem_len & 3) == 0; rows = mem_len >> 2; break;
+    case H2OT_CODEC_C4S: ok = cs_header(2); break;
+    case H2OT_CODEC_C8:
+    case H2OT_CODEC_C8D: ok = (mem_len & 7) == 0; rows = mem_len >> 3; break;
+    case H2OT_CODEC_CBS:  // CBSChunk.initFromBytes :155-160
+      ok = mem_len >= 2 && (mem[1] == 1 || mem[1] == 2) && mem[0] < 8;
+      if (ok) { a.bpv = mem[1]; rows = ((mem_len - 2) * 8 - mem[0]) / a.bpv; }
+      break;
+    case H2OT_CODEC_CUD:  // CUDChunk.initFromBytes :91-96, computeByteSize :14-18
+      ok = mem_len >= 8;
+      if (ok) {
+        rows = rd_i32(mem);
+        a.nuniq = rd_i32(mem + 4);
+        ok = a.nuniq >= 0 && a.nuniq <= 256 && rows >= 0 && mem_len >= 8 + ((int64_t)a.nuniq << 3) + rows;
+        for (int64_t i = 0; ok && i < rows; i++) ok = (int)(int8_t)mem[8 + ((int64_t)a.nuniq << 3) + i] + 128 < a.nuniq;
+      }
+      break;
+    case H2OT_CODEC_CXI:
+    case H2OT_CODEC_CXF:  // CXIChunk.initFromBytes :58-66
+      ok = mem_len >= 8;
+      if (ok) {
+        rows = rd_i32(mem);
+        a.id_sz = mem[4];
+        a.val_sz = mem[5];
+        a.na_sparse = mem[6] == 1 ? 1 : 0;
+        const int id = a.id_sz, vs = a.val_sz;
+        if (codec == H2OT_CODEC_CXI) ok = (id == 2 && (vs == 0 || vs == 2)) || (id == 4 && (vs == 0 || vs == 4 || vs == 8));
+        else ok = id == 4 && (vs == 4 || vs == 8);
+        if (ok) {
+          ok = (mem_len - 8) % (id + vs) == 0;
+          a.n_elems = (mem_len - 8) / (id + vs);
+        }
+      }
+      break;
+    default: H2OT_FAIL(H2OT_ERR_INVALID, "unknown chunk codec");
+  }
+  if (!ok) H2OT_FAIL(H2OT_ERR_INVALID, "malformed chunk (header and byte length disagree, or an unknown element layout)");
+  if (rows != n) H2OT_FAIL(H2OT_ERR_INVALID, "chunk holds " + std::to_string(rows) + " rows, caller said " + std::to_string(n));
+  if (col >= 0) {
+    Column& c = h->cols[col];
+    if (!h->staging_all) {
+      const size_t bytes = (size_t)h->C * (size_t)h->n * sizeof(double);
+      CUDA_TRY(cudaMalloc(&h->staging_all, bytes));
+      CUDA_TRY(cudaMemsetAsync(h->staging_all, 0xFF, bytes, h->stream));
+    }
+    c.staging = h->staging_all + (size_t)col * (size_t)h->n;
+    dst = c.staging;
+  }
+  if (n == 0) return H2OT_OK;
+  TRY(h->d_chunk.ensure((size_t)std::max<int64_t>(mem_len, 16)));
+  TRY(h->d_chunk_err.ensure(1));
+  TRY(h2d(h, h->d_chunk.p, mem, (size_t)mem_len));
+  CUDA_TRY(cudaMemsetAsync(h->d_chunk_err.p, 0, sizeof(int32_t), h->stream));
+  a.mem = h->d_chunk.p;
+  a.dst = dst + row0;
+  a.err = h->d_chunk_err.p;
+  chunk_decode_kernel<<<grid_for(h, n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  if ((codec == H2OT_CODEC_CXI || codec == H2OT_CODEC_CXF) && a.n_elems > 0) {
+    chunk_scatter_kernel<<<grid_for(h, a.n_elems, 256), 256, 0, h->stream>>>(a);
+    h->stats.launches++;
+    int32_t err = 0;
+    CUDA_TRY(cudaMemcpyAsync(&err, h->d_chunk_err.p, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    TRY(finish_call(h));
+    if (err) H2OT_FAIL(H2OT_ERR_INVALID, "sparse chunk: row id out of range");
+    return H2OT_OK;
+  }
+  return finish_call(h);
+}
+
+int h2ot_debug_get_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, double* out) {
+  CHECK_ENGINE(h);
+  if (col < 0 || col >= h->C || !out || row0 < 0 || n < 0 || row0 + n > h->n) H2OT_FAIL(H2OT_ERR_INVALID, "bad column / row range");
+  if (!h->cols[col].finalized) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  if (n == 0) return H2OT_OK;
+  DBuf<double> tmp;
+  TRY(tmp.ensure((size_t)n));
+  ColRef cr{h->cols[col].data, h->cols[col].base, h->cols[col].storage, 0};
+  column_values_kernel<<<grid_for(h, n, 256), 256, 0, h->stream>>>(cr, row0, n, tmp.p);
+  h->stats.launches++;
+  int rc = d2h(h, out, tmp.p, (size_t)n * sizeof(double));
+  if (rc == H2OT_OK) rc = finish_call(h);
+  else cudaStreamSynchronize(h->stream);
+  tmp.release();
+  return rc;
 }
 
 int h2ot_finalize_frame(h2ot_engine* h) {

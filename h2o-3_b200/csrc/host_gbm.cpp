@@ -803,6 +803,31 @@ int h2ot_gbm_set_column(h2ot_gbm* g, int32_t col, const double* values, int32_t 
   g->cols[col].loaded = true;
   return H2OT_OK;
 }
+int h2ot_gbm_load_chunk(h2ot_gbm* g, int32_t col, int64_t row0, int64_t n, int32_t codec, const uint8_t* mem, int64_t mem_len) {
+  if (!g || !mem) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (col >= g->ncols) GFAIL(H2OT_ERR_INVALID, "column index out of range");
+  return h2ot_load_chunk(g->eng, col, row0, n, codec, mem, mem_len);
+}
+int h2ot_gbm_chunks_done(h2ot_gbm* g, int32_t col, int32_t is_categorical, int32_t cardinality) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (col >= g->ncols) GFAIL(H2OT_ERR_INVALID, "column index out of range");
+  if (col >= 0) {
+    g->cols[col].is_cat = is_categorical != 0;
+    g->cols[col].cardinality = cardinality;
+    g->cols[col].loaded = true;
+  } else if (col == H2OT_COL_RESPONSE) {
+    g->have_y = true;
+  } else if (col == H2OT_COL_WEIGHTS) {
+    if (!g->has_w) GFAIL(H2OT_ERR_INVALID, "created without weights");
+    g->have_w = true;
+  } else if (col == H2OT_COL_OFFSET) {
+    if (!g->has_off) GFAIL(H2OT_ERR_INVALID, "created without offset");
+    g->have_off = true;
+  } else {
+    GFAIL(H2OT_ERR_INVALID, "column index out of range");
+  }
+  return H2OT_OK;
+}
 int h2ot_gbm_set_response(h2ot_gbm* g, const double* y) {
   if (!g || !y) GFAIL(H2OT_ERR_INVALID, "null argument");
   g->have_y = true;

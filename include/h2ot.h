@@ -154,6 +154,35 @@ int h2ot_load_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, const
 int h2ot_load_response(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
 int h2ot_load_weights(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
 int h2ot_load_offset(h2ot_engine* h, int64_t row0, int64_t n, const double* values);
+
+/* ---- frame ingest straight from H2O's compressed chunks: the host hands over Chunk._mem as is and the
+ * decode that Chunk.atd_impl / getDoubles would do on the CPU runs on the device. One codec id per Chunk subclass
+ * (W/fvec/<name>.java); layouts are little endian (UnsafeUtils, x86). */
+enum {
+  H2OT_CODEC_C0D = 0,  /* W/fvec/C0DChunk.java:11-31   [double con][int len]: every row == con (NaN == all NA) */
+  H2OT_CODEC_C0L = 1,  /* W/fvec/C0LChunk.java:8-22    [long con][int len] */
+  H2OT_CODEC_C1 = 2,   /* W/fvec/C1Chunk.java:8-23     unsigned bytes, 0xFF == NA */
+  H2OT_CODEC_C1N = 3,  /* W/fvec/C1NChunk.java:8-12    unsigned bytes, no NA */
+  H2OT_CODEC_C1S = 4,  /* W/fvec/C1SChunk.java:31-33 + W/fvec/CSChunk.java:18-62: [long bias][int scale][int szLog | decimal] then unsigned bytes */
+  H2OT_CODEC_C2 = 5,   /* W/fvec/C2Chunk.java:9-21     shorts, Short.MIN_VALUE == NA */
+  H2OT_CODEC_C2S = 6,  /* W/fvec/C2SChunk.java:32-37 + CSChunk: header then shorts */
+  H2OT_CODEC_C4 = 7,   /* W/fvec/C4Chunk.java:9-19     ints, Integer.MIN_VALUE == NA */
+  H2OT_CODEC_C4S = 8,  /* W/fvec/C4SChunk.java:24-30 + CSChunk: header then ints */
+  H2OT_CODEC_C4F = 9,  /* W/fvec/C4FChunk.java:8-18    floats, NaN == NA */
+  H2OT_CODEC_C8 = 10,  /* W/fvec/C8Chunk.java:8-19     longs, Long.MIN_VALUE == NA */
+  H2OT_CODEC_C8D = 11, /* W/fvec/C8DChunk.java:8-16    doubles */
+  H2OT_CODEC_CBS = 12, /* W/fvec/CBSChunk.java:9-80    [gap][bpv] then 1 or 2 bits per row, 2 == NA */
+  H2OT_CODEC_CUD = 13, /* W/fvec/CUDChunk.java:12-47   [int len][int nuniq][nuniq doubles][len bytes: index - 128] */
+  H2OT_CODEC_CXI = 14, /* W/fvec/CXIChunk.java:7-120   sparse ints: [int len][id size][value size][NA-sparse] then (id, value) pairs */
+  H2OT_CODEC_CXF = 15  /* W/fvec/CXFChunk.java:7-36    sparse float / double values */
+};
+#define H2OT_COL_RESPONSE (-1)
+#define H2OT_COL_WEIGHTS (-2)
+#define H2OT_COL_OFFSET (-3)
+/* Decodes n rows of one chunk into rows [row0, row0 + n) of predictor `col` (or the response / weights / offset column).
+ * mem, mem_len: the chunk's byte array (host memory). n must equal the chunk's own row count (as Chunk.initFromBytes derives
+ * it); a malformed chunk (sizes that disagree, an unknown sparse element layout, ids out of range) is H2OT_ERR_INVALID. */
+int h2ot_load_chunk(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, int32_t codec, const uint8_t* mem, int64_t mem_len);
 /* rollups (min/max/isInt/naCnt) + lossless narrow encoding of every loaded column, resident in HBM */
 int h2ot_finalize_frame(h2ot_engine* h);
 int h2ot_column_info_get(h2ot_engine* h, int32_t col, h2ot_column_info* out);
@@ -269,6 +298,9 @@ int h2ot_set_weight_bound(h2ot_engine* h, double bound);
 /* ---- diagnostics / parity hooks */
 /* Per-row bin index of column col under desc (DHistogram.bin, T/DHistogram.java:272-306), uint16 codes to the host. */
 int h2ot_debug_bin_codes(h2ot_engine* h, int32_t col, const h2ot_hist_desc* desc, uint16_t* out_codes);
+/* Rows [row0, row0 + n) of a finalized predictor column, decoded back to doubles (NaN == NA): storage is lossless, so this is
+ * what was loaded (tests compare it with Chunk.atd of the oracle). */
+int h2ot_debug_get_column(h2ot_engine* h, int32_t col, int64_t row0, int64_t n, double* out);
 int h2ot_stats_get(h2ot_engine* h, h2ot_stats* out);
 int h2ot_stats_reset(h2ot_engine* h);
 /* 0: default (shared-memory privatised histograms; leaf-major sparse kernel on levels with per-node column sampling),

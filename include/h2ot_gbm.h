@@ -56,6 +56,11 @@ int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int
 int h2ot_gbm_destroy(h2ot_gbm* g);
 /* one call per column: full local column, NaN == NA; categorical columns carry integer level codes */
 int h2ot_gbm_set_column(h2ot_gbm* g, int32_t col, const double* values, int32_t is_categorical, int32_t cardinality);
+/* The same column handed over as H2O chunks (include/h2ot.h: h2ot_load_chunk): one call per Chunk of the Vec, row0 = the chunk's
+ * first row (Chunk._start). col may be H2OT_COL_RESPONSE / H2OT_COL_WEIGHTS / H2OT_COL_OFFSET. Call h2ot_gbm_chunks_done(col, ...)
+ * once all chunks of a column are in. */
+int h2ot_gbm_load_chunk(h2ot_gbm* g, int32_t col, int64_t row0, int64_t n, int32_t codec, const uint8_t* mem, int64_t mem_len);
+int h2ot_gbm_chunks_done(h2ot_gbm* g, int32_t col, int32_t is_categorical, int32_t cardinality);
 int h2ot_gbm_set_response(h2ot_gbm* g, const double* y);
 int h2ot_gbm_set_weights(h2ot_gbm* g, const double* w);
 int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o);

@@ -2,6 +2,7 @@
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg can drive it through
 // ctypes. Never linked into, or called from, the product library (h2o-3_b200/).
 #include "h2o_tree_oracle.hpp"
+#include "h2o_chunk_oracle.hpp"
 
 using namespace h2o_oracle;
 
@@ -312,5 +313,44 @@ void orc_capture_nids(void* m, int i, int* out) {
   const auto& v = ((GBMModel*)m)->captures[i].nids_after;
   std::copy(v.begin(), v.end(), out);
 }
+
+// ---- chunk codecs (h2o_chunk_oracle.hpp)
+static int64_t copy_out(const std::vector<uint8_t>& m, uint8_t* out, int64_t cap) {
+  if ((int64_t)m.size() > cap) return -(int64_t)m.size();
+  if (!m.empty()) std::memcpy(out, m.data(), m.size());
+  return (int64_t)m.size();
+}
+int64_t orc_chunk_rows(int codec, const uint8_t* mem, int64_t len) { return orc_chunk::rows_of(codec, mem, len); }
+// Chunk.getDoubles: every row through atd_impl
+void orc_chunk_decode(int codec, const uint8_t* mem, int64_t len, int64_t n, double* out) {
+  for (int64_t i = 0; i < n; i++) out[i] = orc_chunk::atd(codec, mem, len, i);
+}
+int64_t orc_chunk_enc_int(int log, int64_t n, const int64_t* v, const uint8_t* na, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_int(log, std::vector<int64_t>(v, v + n), std::vector<uint8_t>(na, na + n)), out, cap);
+}
+int64_t orc_chunk_enc_scaled(int log, int64_t n, const int64_t* man, const int32_t* exp, const uint8_t* na, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_scaled(log, std::vector<int64_t>(man, man + n), std::vector<int32_t>(exp, exp + n),
+                                        std::vector<uint8_t>(na, na + n)), out, cap);
+}
+int64_t orc_chunk_enc_c0(int is_long, double dcon, int64_t lcon, int32_t len, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_c0(is_long != 0, dcon, lcon, len), out, cap);
+}
+int64_t orc_chunk_enc_cbs(int64_t n, const uint8_t* v, const uint8_t* na, int bpv, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_cbs(std::vector<uint8_t>(v, v + n), std::vector<uint8_t>(na, na + n), bpv), out, cap);
+}
+int64_t orc_chunk_enc_cud(int64_t n, const double* v, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_cud(std::vector<double>(v, v + n)), out, cap);
+}
+int64_t orc_chunk_enc_cxi(int32_t len, int id_sz, int val_sz, int na_sparse, int64_t nnz, const int32_t* ids, const int64_t* vals,
+                          const uint8_t* na, uint8_t* out, int64_t cap) {
+  return copy_out(orc_chunk::enc_cxi(len, id_sz, val_sz, na_sparse != 0, std::vector<int32_t>(ids, ids + nnz),
+                                     std::vector<int64_t>(vals, vals + nnz), std::vector<uint8_t>(na, na + nnz)), out, cap);
+}
+int64_t orc_chunk_enc_cxf(int32_t len, int valsz, int na_sparse, int64_t nnz, const int32_t* ids, const double* vals, uint8_t* out,
+                          int64_t cap) {
+  return copy_out(orc_chunk::enc_cxf(len, valsz, na_sparse != 0, std::vector<int32_t>(ids, ids + nnz), std::vector<double>(vals, vals + nnz)),
+                  out, cap);
+}
+double orc_pow10(int64_t m, int e) { return orc_chunk::pow10(m, e); }
 
 }  // extern "C"

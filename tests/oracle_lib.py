@@ -72,7 +72,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    src_m = max(os.path.getmtime(os.path.join(ORACLE_DIR, f)) for f in ("h2o_tree_oracle.hpp", "oracle_capi.cpp"))
+    src_m = max(os.path.getmtime(os.path.join(ORACLE_DIR, f)) for f in ("h2o_tree_oracle.hpp", "h2o_chunk_oracle.hpp", "oracle_capi.cpp"))
     if not os.path.exists(_SO) or os.path.getmtime(_SO) < src_m:
         build()
     L = C.CDLL(_SO)
