@@ -83,6 +83,9 @@ struct TreeState {  // per class-tree k
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
   int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
   int n_smem_groups = 0;
+  // rows expected in each leaf of the level being planned: the parents' split counts (n0 / n1) of the previous level_step
+  std::vector<double> prev_n0, prev_n1, est_rows;
+  int prev_leaf_offset = -1;
   int n_sparse_groups = 0, sparse_ctas = 0;  // leaf-range groups of hist_sparse_kernel (levels with per-node column sampling)
   double sparse_bytes_per_row = 0, sparse_cols_per_row = 0;
   size_t smem_bytes = 0;
@@ -849,6 +852,7 @@ int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_
   t.n_nodes = 0;
   t.built = t.finished = false;
   t.L = 0;
+  t.prev_leaf_offset = -1;
   if (work_abs_bound > 0) t.work_bound = work_abs_bound;
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const double b = t.work_bound > 0 ? t.work_bound : 1.0;
@@ -1144,8 +1148,36 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
         const int G = (int)sg.size();
         const int n_ctas = std::max(h->sm_count, G);
         int cta = 0;
+        // CTA shares: every group scans all leaf codes (1 unit per row) and works on its own rows (~6 units per row and
+        // column); its rows are estimated from the parents' split counts, evenly when those are unknown
+        std::vector<double> gcost((size_t)G, 0.0);
+        {
+          double tot = 0;
+          for (double v : t.est_rows) tot += v;
+          double cost_sum = 0;
+          for (int gi = 0; gi < G; gi++) {
+            double frac = (double)sg[gi].l_count / L;
+            if (tot > 0) {
+              double r = 0;
+              for (int l = sg[gi].l_begin; l < sg[gi].l_begin + sg[gi].l_count; l++) r += t.est_rows[(size_t)l];
+              frac = r / tot;
+            }
+            gcost[(size_t)gi] = 1.0 + 6.0 * sg[gi].ncols * frac;
+            cost_sum += gcost[(size_t)gi];
+          }
+          int used = 0;
+          for (int gi = 0; gi < G; gi++) {
+            sg[gi].n_slices = std::max(1, (int)std::floor(n_ctas * gcost[(size_t)gi] / cost_sum));
+            used += sg[gi].n_slices;
+          }
+          for (; used < n_ctas; used++) {
+            int best = 0;
+            for (int gi = 1; gi < G; gi++)
+              if (gcost[(size_t)gi] / sg[gi].n_slices > gcost[(size_t)best] / sg[best].n_slices) best = gi;
+            sg[best].n_slices++;
+          }
+        }
         for (int gi = 0; gi < G; gi++) {
-          sg[gi].n_slices = n_ctas / G + (gi < n_ctas % G ? 1 : 0);
           sg[gi].cta_begin = cta;
           cta += sg[gi].n_slices;
           int off = 0;
@@ -1384,6 +1416,18 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     h->stats.launches++;
     TRY(t_end(h));
   }
+  t.est_rows.assign((size_t)n_leaves, 0.0);
+  if (t.prev_leaf_offset >= 0 && decided)
+    for (int i = 0; i < n_decided; i++) {
+      const h2ot_decided_node& dn = decided[i];
+      const int pl = dn.nid - t.prev_leaf_offset;
+      if (dn.col < 0 || pl < 0 || pl >= (int)t.prev_n0.size()) continue;
+      for (int w = 0; w < 2; w++) {
+        const int ch = dn.child[w] - leaf_offset;
+        if (ch >= 0 && ch < n_leaves) t.est_rows[(size_t)ch] = w == 0 ? t.prev_n0[(size_t)pl] : t.prev_n1[(size_t)pl];
+      }
+    }
+  t.prev_leaf_offset = -1;  // consumed; set again by the level_step that ends this level
   TRY(plan_level(h, t, n_leaves, descs));
   // this level's descriptors, groups and column lists travel in ONE copy from pinned staging
   {
@@ -1669,6 +1713,17 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
   if (out_wNA) memcpy(out_wNA, sp + 2 * LC * sizeof(double), LC * sizeof(double));
   if (out_splits) memcpy(out_splits, sp + 4 * LC * sizeof(double), (size_t)t.L * sizeof(h2ot_split));
   if (out_has_vals) memcpy(out_has_vals, sp + 4 * LC * sizeof(double) + (size_t)t.L * sizeof(h2ot_split), LC);
+  {  // the children's row counts steer the next level's CTA shares (sparse levels)
+    t.prev_n0.resize((size_t)t.L);
+    t.prev_n1.resize((size_t)t.L);
+    t.prev_leaf_offset = t.leaf_offset;
+    for (int l = 0; l < t.L; l++) {
+      h2ot_split sv;
+      memcpy(&sv, sp + 4 * LC * sizeof(double) + (size_t)l * sizeof(h2ot_split), sizeof(sv));
+      t.prev_n0[(size_t)l] = sv.col >= 0 ? sv.n0 : 0.0;
+      t.prev_n1[(size_t)l] = sv.col >= 0 ? sv.n1 : 0.0;
+    }
+  }
   if (t.L == 1) {  // root level: refresh the planner's per-column bin-concentration estimate
     const double* conc = reinterpret_cast<const double*>(sp + 3 * LC * sizeof(double));
     for (int c = 0; c < h->C; c++)
