@@ -26,7 +26,7 @@ FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2, "poisson": 3, "gamma"
 NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT, LEFT, RIGHT = 0, 1, 2, 3, 4, 5
 DECIDED_ROW, OUT_OF_BAG = -1, -2
 STORE_F32, STORE_F64, STORE_U8, STORE_U16 = 0, 1, 2, 3
-DESC_ACTIVE, DESC_ISINT, DESC_ISCAT, DESC_INTOPT, DESC_CHECKFLOAT, DESC_INITNA = 1, 2, 4, 8, 16, 32
+DESC_ACTIVE, DESC_ISINT, DESC_ISCAT, DESC_INTOPT, DESC_CHECKFLOAT, DESC_INITNA, DESC_SPLITPTS, DESC_ABSOLUTE = 1, 2, 4, 8, 16, 32, 64, 128
 MAX_BITSET_BYTES = 512
 COMM_ID_BYTES = 128
 
@@ -45,7 +45,8 @@ class Config(C.Structure):
 
 class HistDesc(C.Structure):
     _fields_ = [("min", C.c_double), ("maxEx", C.c_double), ("step", C.c_double), ("nbin", C.c_int32),
-                ("order", C.c_int16), ("flags", C.c_uint8), ("pad", C.c_uint8)]
+                ("order", C.c_int16), ("flags", C.c_uint8), ("pad", C.c_uint8),
+                ("splitpts_off", C.c_int32), ("splitpts_n", C.c_int32)]
 
 
 class DecidedNode(C.Structure):
@@ -111,7 +112,7 @@ ENGINE_SYMBOLS = [
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column",
+    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points",
 ]
 GBM_SYMBOLS = [
     "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
@@ -144,6 +145,7 @@ def load():
         getattr(L, n).argtypes = [vp, i64, i64, vp]
     L.h2ot_load_column.argtypes = [vp, i32, i64, i64, vp]
     L.h2ot_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
+    L.h2ot_set_split_points.argtypes = [vp, i32, vp, i64]
     L.h2ot_debug_get_column.argtypes = [vp, i32, i64, i64, vp]
     L.h2ot_gbm_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
     L.h2ot_gbm_chunks_done.argtypes = [vp, i32, i32, i32]
@@ -419,6 +421,11 @@ class Engine:
         _check(self.L.h2ot_debug_bin_codes(self.h, col, C.byref(desc), _p(out)))
         return out
 
+    def set_split_points(self, points, k=0):
+        """Pool of split points for the next build_level / level_step (descriptors refer to it by offset and count)."""
+        v = _f64(points)
+        _check(self.L.h2ot_set_split_points(self.h, k, _p(v), v.size))
+
     def stats(self):
         s = Stats()
         _check(self.L.h2ot_stats_get(self.h, C.byref(s)))
@@ -441,13 +448,17 @@ def hist_column_noalloc(d_x, d_work, d_leaf_code, n, descs, work_abs_bound, d_ou
                                            C.c_void_p(stream) if stream else None))
 
 
-def make_desc(mn, max_ex, nbin, step=None, is_int=0, int_opt=False, check_float=False, init_na=False, order=0, active=True):
-    """HistDesc for the UniformAdaptive layout. step defaults to nbin/(maxEx-min) (T/DHistogram.java:253)."""
+def make_desc(mn, max_ex, nbin, step=None, is_int=0, int_opt=False, check_float=False, init_na=False, order=0, active=True,
+              splitpts=None, absolute=False):
+    """HistDesc. step defaults to nbin/(maxEx-min) (T/DHistogram.java:253). splitpts=(offset, count) places the node's
+    _splitPts in the pool of Engine.set_split_points (histogram_type Random / QuantilesGlobal / UniformRobust)."""
     if step is None:
         step = nbin / (max_ex - mn)
     flags = (DESC_ACTIVE if active else 0) | (DESC_ISINT if is_int > 0 else 0) | (DESC_ISCAT if is_int == 2 else 0) | \
-        (DESC_INTOPT if int_opt else 0) | (DESC_CHECKFLOAT if check_float else 0) | (DESC_INITNA if init_na else 0)
-    return HistDesc(min=mn, maxEx=max_ex, step=step, nbin=nbin, order=order, flags=flags, pad=0)
+        (DESC_INTOPT if int_opt else 0) | (DESC_CHECKFLOAT if check_float else 0) | (DESC_INITNA if init_na else 0) | \
+        (DESC_SPLITPTS if splitpts is not None else 0) | (DESC_ABSOLUTE if absolute else 0)
+    off, cnt = splitpts if splitpts is not None else (0, 0)
+    return HistDesc(min=mn, maxEx=max_ex, step=step, nbin=nbin, order=order, flags=flags, pad=0, splitpts_off=off, splitpts_n=cnt)
 
 
 class GBM:

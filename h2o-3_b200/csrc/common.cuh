@@ -105,6 +105,46 @@ __device__ __forceinline__ int bin_of(double x, double mn, double step, int nbin
   return idx;
 }
 
+// ---------------------------------------------------------------------------------------------
+// DHistogram.bin / binAt with split points (histogram_type Random / QuantilesGlobal / UniformRobust):
+// T/DHistogram.java:281-286, 308-312. pts: the node's _splitPts (n of them), zero_pos: _zeroSplitPntPos
+// (Arrays.binarySearch(_splitPts, 0.0), negative when absent), absolute: _absoluteSplitPts.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double bin_at_pts(double mn, double step, int b, const double* pts, bool absolute) {
+  if (absolute) return pts[b];
+  return __dadd_rn(mn, __ddiv_rn(pts ? pts[b] : (double)b, step));
+}
+// java.util.Arrays.binarySearch for a key that is neither NaN nor a zero (those never get here): same probe sequence, so
+// the same index among duplicates
+__device__ __forceinline__ int jbinary_search(const double* a, int n, double key) {
+  int low = 0, high = n - 1;
+  while (low <= high) {
+    const int mid = (int)(((unsigned)low + (unsigned)high) >> 1);
+    const double v = a[mid];
+    if (v < key) low = mid + 1;
+    else if (v > key) high = mid - 1;
+    else return mid;
+  }
+  return -(low + 1);
+}
+__device__ __forceinline__ int bin_splitpts(double x, double mn, double step, int nbin, const double* pts, int n, int zero_pos,
+                                            bool absolute, bool checkFloat) {
+  if (isinf(x)) return x < 0 ? 0 : nbin - 1;
+  const double pos = absolute ? x : __dmul_rn(__dsub_rn(x, mn), step);
+  int idx = pos == 0.0 ? zero_pos : jbinary_search(pts, n, pos);
+  if (idx < 0) idx = -idx - 2;
+  if (checkFloat && idx + 1 < nbin) {  // :287-301 with _splitPtsFloat[i] = (float) binAt(i)
+    const float splitAt = (float)bin_at_pts(mn, step, idx + 1, pts, absolute);
+    if (x >= (double)splitAt) idx++;
+    if (idx > 0) {
+      const float cur = (float)bin_at_pts(mn, step, idx, pts, absolute);
+      if (!(x >= (double)cur)) idx--;
+    }
+  }
+  if (idx == nbin) idx--;
+  return max(0, min(idx, nbin - 1));  // the reference asserts the range; clamp so that a violated precondition cannot corrupt memory
+}
+
 // 64-bit signed accumulate into two adjacent 32-bit shared-memory words (lo, hi). Shared memory has
 // native atomics only for 32-bit integers on sm_100a (64-bit / fp adds compile to CAS loops), so the
 // carry is propagated by hand; integer adds commute, so the result is order independent.

@@ -83,6 +83,9 @@ struct TreeState {  // per class-tree k
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
   int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
   int n_smem_groups = 0;
+  std::vector<double> h_sp;  // split points of the next level (h2ot_set_split_points), -0.0 canonicalised
+  DBuf<double> d_sp;
+  bool sp_dirty = false, any_splitpts = false;
   // rows expected in each leaf of the level being planned: the parents' split counts (n0 / n1) of the previous level_step
   std::vector<double> prev_n0, prev_n1, est_rows;
   int prev_leaf_offset = -1;
@@ -366,10 +369,17 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   H2OT_OPTIN(H2OT_STORE_U8);
   H2OT_OPTIN(H2OT_STORE_U16);
 #undef H2OT_OPTIN
-  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<5, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
-  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<5, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
-  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<7, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
-  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<7, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));
+#define H2OT_OPTIN_SPARSE(W, HW, CF, SP) \
+  CUDA_TRY(cudaFuncSetAttribute(hist_sparse_kernel<W, HW, CF, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
+  H2OT_OPTIN_SPARSE(5, false, false, false);
+  H2OT_OPTIN_SPARSE(5, false, true, false);
+  H2OT_OPTIN_SPARSE(7, true, false, false);
+  H2OT_OPTIN_SPARSE(7, true, true, false);
+  H2OT_OPTIN_SPARSE(5, false, false, true);
+  H2OT_OPTIN_SPARSE(5, false, true, true);
+  H2OT_OPTIN_SPARSE(7, true, false, true);
+  H2OT_OPTIN_SPARSE(7, true, true, true);
+#undef H2OT_OPTIN_SPARSE
   {
     cudaFuncAttributes fa;
     CUDA_TRY(cudaFuncGetAttributes(&fa, find_split_kernel));
@@ -407,7 +417,7 @@ int h2ot_destroy(h2ot_engine* h) {
     t.nodes.release(); t.bitsets.release(); t.d_lvl.release();
     if (t.lvl_host) cudaFreeHost(t.lvl_host);
     t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
-    t.d_cand.release(); t.d_gamma.release(); t.d_pred.release();
+    t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_sp.release();
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
   h->d_rollup.release(); h->d_cols.release();
@@ -1046,6 +1056,28 @@ int xr_allreduce(h2ot_engine* h, long long n_sums, long long n) {
   return H2OT_OK;
 }
 
+// split-point fields of one descriptor: placement in the pool and _zeroSplitPntPos = Arrays.binarySearch(_splitPts, 0.0)
+// (T/DHistogram.java:389-401; -0.0 is already stored as 0.0)
+int desc_split_points(const TreeState& t, const h2ot_hist_desc& s, DescDev& d) {
+  if (s.splitpts_off < 0 || s.splitpts_n < 1 || (size_t)s.splitpts_off + (size_t)s.splitpts_n > t.h_sp.size())
+    H2OT_FAIL(H2OT_ERR_INVALID, "descriptor's split points lie outside the pool given to h2ot_set_split_points");
+  d.sp_off = s.splitpts_off;
+  d.sp_n = s.splitpts_n;
+  const double* a = t.h_sp.data() + s.splitpts_off;
+  int low = 0, high = s.splitpts_n - 1;
+  while (low <= high) {
+    const int mid = (int)(((unsigned)low + (unsigned)high) >> 1);
+    if (a[mid] < 0.0) low = mid + 1;
+    else if (a[mid] > 0.0) high = mid - 1;
+    else {
+      d.zero_pos = mid;
+      return H2OT_OK;
+    }
+  }
+  d.zero_pos = -(low + 1);
+  return H2OT_OK;
+}
+
 // Places every active (leaf, col) histogram: global bin offsets, packed-vals offsets, shared-memory groups.
 int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs) {
   const int C = h->C;
@@ -1056,6 +1088,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   t.max_split_nbin = 0;
   t.any_cat = false;
   t.any_checkfloat = false;
+  t.any_splitpts = false;
   std::vector<int64_t> col_words(C, 0);
   for (int l = 0; l < L; l++)
     for (int c = 0; c < C; c++) {
@@ -1075,6 +1108,10 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       if (s.nbin < 1 || s.nbin > 65534) H2OT_FAIL(H2OT_ERR_INVALID, "nbin out of range (1..65534)");
       if (!(s.step > 0) || std::isinf(s.step)) H2OT_FAIL(H2OT_ERR_INVALID, "histogram step must be positive and finite");
       d.nbin = s.nbin;
+      if (s.flags & H2OT_DESC_SPLITPTS) {
+        TRY(desc_split_points(t, s, d));
+        t.any_splitpts = true;
+      }
       d.gbin = t.total_bins;
       d.voff = t.total_vals;
       t.total_bins += s.nbin + 1;
@@ -1102,7 +1139,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // that row's leaf's columns (the column-major kernel would test rows x all columns, and re-scan per leaf range).
   t.n_sparse_groups = 0;
   t.sparse_ctas = 0;
-  if (h->hist_mode == 0 && L >= 2) {
+  if ((h->hist_mode == 0 && L >= 2) || (t.any_splitpts && h->hist_mode != 1)) {
     int64_t pairs = 0, pair_bytes = 0;
     int cols_act = 0;
     bool any64 = false;
@@ -1120,7 +1157,8 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
         pair_bytes += st == H2OT_STORE_F32 ? 4 : st == H2OT_STORE_F64 ? 8 : st == H2OT_STORE_U8 ? 1 : 2;
         any64 |= st == H2OT_STORE_F64;
       }
-    if (pairs > 0 && pairs * 5 <= (int64_t)L * cols_act * 4) {  // at most 80 % of the (leaf, column) pairs are active
+    // (levels whose descriptors carry split points always take this kernel: it is the one that bins by binary search)
+    if (pairs > 0 && (t.any_splitpts || pairs * 5 <= (int64_t)L * cols_act * 4)) {  // at most 80 % of the (leaf, column) pairs are active
       const size_t col_bytes = C <= kSparseColsSmem ? (size_t)C * sizeof(ColRef) : 0;
       auto fixed_sparse = [&](int leaves, int M) {
         return (size_t)leaves * M * (kSStride * sizeof(uint32_t) + (any64 ? sizeof(MinMaxS) : 0)) + col_bytes + kSparseQueueWords * sizeof(uint32_t) + 64;
@@ -1207,7 +1245,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // replicas of their histograms (lanes pick one by lane id; the replicas are summed when the CTA merges) where that fits.
   std::vector<int> col_rep(C, 1);
   for (int c = 0; c < C; c++) {
-    if (!col_words[c] || h->hist_mode == 1) continue;
+    if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
     const double excess = 8.0 * h->col_conc[c] / (double)L;
     int rep = excess >= 1.0 ? 4 : (excess >= 0.4 ? 2 : 1);
     while (rep > 1 && (size_t)col_words[c] * rep * 4 + fixed_bytes(1, h->cols[c].storage) > budget / 2) rep >>= 1;
@@ -1223,7 +1261,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     if (!col_words[c]) continue;
     t.active_cols++;
     const int st = h->cols[c].storage;
-    if (h->hist_mode == 1) glob_cols.push_back(c);
+    if (h->hist_mode == 1 || t.any_splitpts) glob_cols.push_back(c);  // (split points: the sparse plan above did not fit)
     else if ((size_t)col_words[c] * 4 + fixed_bytes(1, st) > budget) {
       // too big for one CTA. Dense column (most leaves histogram it): cut into leaf ranges, each range's CTAs scan all rows
       // (measured 2.5 / 5.2 ms at 64 / 128 leaves x 257 bins vs 15 / 11 ms with L2 atomics). Sparse column (per-node mtries):
@@ -1360,6 +1398,18 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
 
 extern "C" {
 
+int h2ot_set_split_points(h2ot_engine* h, int32_t k, const double* points, int64_t n) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (n < 0 || (n > 0 && !points) || n > (int64_t)1 << 30) H2OT_FAIL(H2OT_ERR_INVALID, "bad split point pool");
+  TreeState& t = h->ts[k];
+  t.h_sp.assign(points, points + n);
+  for (double& v : t.h_sp)
+    if (v == 0.0) v = 0.0;  // -0.0 -> 0.0 (T/DHistogram.java:389-401)
+  t.sp_dirty = true;
+  return H2OT_OK;
+}
+
 int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
                      const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
                      const h2ot_hist_desc* descs) {
@@ -1471,6 +1521,15 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const int ew = h->w ? exponent_for(h->w_max, bitsN) : 0;
   ha.sw = std::ldexp(1.0, ew);
+  ha.sp = nullptr;
+  if (t.any_splitpts) {
+    if (t.sp_dirty) {
+      TRY(t.d_sp.ensure(std::max<size_t>(t.h_sp.size(), 1)));
+      TRY(h2d(h, t.d_sp.p, t.h_sp.data(), t.h_sp.size() * sizeof(double)));
+      t.sp_dirty = false;
+    }
+    ha.sp = t.d_sp.p;
+  }
   TRY(t_begin(h, &h->stats.ms_hist));
   if (t.n_smem_groups > 0 && t.smem_bytes > (size_t)h->max_smem_optin) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "shared-memory plan exceeds the device limit");
   if (t.n_sparse_groups > 0) {
@@ -1479,13 +1538,16 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     ha.n_slices = 0;
     const int grid = t.sparse_ctas;
     const size_t sm = t.smem_bytes;
-    if (h->w) {
-      if (t.any_checkfloat) hist_sparse_kernel<7, true, true><<<grid, kHistThreads, sm, h->stream>>>(ha);
-      else hist_sparse_kernel<7, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);
-    } else {
-      if (t.any_checkfloat) hist_sparse_kernel<5, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);
-      else hist_sparse_kernel<5, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);
+#define H2OT_LAUNCH_SPARSE(SP)                                                                                    \
+    if (h->w) {                                                                                                    \
+      if (t.any_checkfloat) hist_sparse_kernel<7, true, true, SP><<<grid, kHistThreads, sm, h->stream>>>(ha);      \
+      else hist_sparse_kernel<7, true, false, SP><<<grid, kHistThreads, sm, h->stream>>>(ha);                      \
+    } else {                                                                                                       \
+      if (t.any_checkfloat) hist_sparse_kernel<5, false, true, SP><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
+      else hist_sparse_kernel<5, false, false, SP><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
     }
+    if (t.any_splitpts) { H2OT_LAUNCH_SPARSE(true) } else { H2OT_LAUNCH_SPARSE(false) }
+#undef H2OT_LAUNCH_SPARSE
     h->stats.launches++;
     h->stats.hist_launches++;
     h->stats.sparse_launches++;
@@ -1659,7 +1721,8 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   if (t.any_cat) smem += 8 * (3 * n1 + n1) + 4 * n1;
   if (smem > (size_t)h->split_smem_max) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
   if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
-  SplitArgs sa{t.L, h->C, t.p_descs, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p};
+  SplitArgs sa{t.L, h->C, t.p_descs, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p,
+               t.any_splitpts ? t.d_sp.p : nullptr};
   TRY(t_begin(h, &h->stats.ms_split));
   find_split_kernel<<<(unsigned)LC, kSplitThreads, smem, h->stream>>>(sa);
   best_col_kernel<<<t.L, 32, 0, h->stream>>>(t.L, h->C, t.p_descs, t.d_cand.p, t.p_best);
@@ -1965,8 +2028,23 @@ int h2ot_debug_bin_codes(h2ot_engine* h, int32_t col, const h2ot_hist_desc* desc
   DBuf<uint16_t> tmp;
   TRY(tmp.ensure(h->n));
   ColRef cr{h->cols[col].data, h->cols[col].base, h->cols[col].storage, 0};
-  bin_codes_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, cr, desc->min, desc->step, desc->nbin,
-                                                                 (desc->flags & H2OT_DESC_CHECKFLOAT) ? 1 : 0, tmp.p);
+  DescDev dd{};
+  dd.min = desc->min;
+  dd.step = desc->step;
+  dd.nbin = desc->nbin;
+  dd.flags = desc->flags;
+  const double* sp = nullptr;
+  if (desc->flags & H2OT_DESC_SPLITPTS) {  // against class-tree 0's pool (h2ot_set_split_points)
+    TreeState& t = h->ts[0];
+    TRY(desc_split_points(t, *desc, dd));
+    if (t.sp_dirty) {
+      TRY(t.d_sp.ensure(std::max<size_t>(t.h_sp.size(), 1)));
+      TRY(h2d(h, t.d_sp.p, t.h_sp.data(), t.h_sp.size() * sizeof(double)));
+      t.sp_dirty = false;
+    }
+    sp = t.d_sp.p;
+  }
+  bin_codes_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, cr, dd, sp, tmp.p);
   h->stats.launches++;
   TRY(d2h(h, out_codes, tmp.p, (size_t)h->n * sizeof(uint16_t)));
   int r = finish_call(h);

@@ -17,7 +17,18 @@ struct DescDev {
   int64_t voff;      // offset (doubles) of the block in the packed vals output
   uint32_t flags;    // H2OT_DESC_*
   uint32_t pad;      // low 16 bits: h2ot_hist_desc::order
+  int32_t sp_off;    // H2OT_DESC_SPLITPTS: first split point in the level's pool (HistArgs::sp)
+  int32_t sp_n;      // number of split points
+  int32_t zero_pos;  // _zeroSplitPntPos (Arrays.binarySearch(_splitPts, 0.0), negative if absent)
+  int32_t pad2;
 };
+// DHistogram.bin of a non-NA value under one descriptor, any histogram type
+__device__ __forceinline__ int bin_desc(const DescDev& d, const double* sp, double x) {
+  if (d.flags & H2OT_DESC_SPLITPTS)
+    return bin_splitpts(x, d.min, d.step, d.nbin, sp + d.sp_off, d.sp_n, d.zero_pos, (d.flags & H2OT_DESC_ABSOLUTE) != 0,
+                        (d.flags & H2OT_DESC_CHECKFLOAT) != 0);
+  return bin_of(x, d.min, d.step, d.nbin, (d.flags & H2OT_DESC_CHECKFLOAT) != 0);
+}
 struct GroupDev {
   int32_t cols_off, ncols;  // the group's columns: group_cols[cols_off .. cols_off + ncols) (all of one storage type)
   int32_t smem_words;       // histogram words needed by this group
@@ -140,6 +151,7 @@ struct HistArgs {
   long long* acc;              // [total_bins][3] fixed point
   unsigned long long* minmax;  // [L][C][2] : {~dkey(min2), dkey(maxIn)}, 0 == untouched
   double sy, syy, sw;          // 2^k scales of wY, wYY, w
+  const double* sp;            // the level's split-point pool (descriptors with H2OT_DESC_SPLITPTS), else nullptr
 };
 
 // Shared-memory descriptor table of one CTA: one record of kTStride 32-bit words per (group column, leaf) pair
@@ -584,7 +596,7 @@ __global__ void __launch_bounds__(256) hist_global_kernel(HistArgs a, int c_begi
         int b;
         if (isnan(x[j])) b = d.nbin;
         else {
-          b = bin_of(x[j], d.min, d.step, d.nbin, (d.flags & H2OT_DESC_CHECKFLOAT) != 0);
+          b = bin_desc(d, a.sp, x[j]);
           const unsigned long long k = dkey(x[j]);
           unsigned long long* mm = a.minmax + ((size_t)leaf[j] * a.C + c) * 2;
           if (~k > mm[0]) atomicMax(mm, ~k);
@@ -663,10 +675,10 @@ __global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
 }
 
 // per-row bin codes of one column under one descriptor (parity hook for DHistogram.bin)
-__global__ void bin_codes_kernel(int64_t n, ColRef col, double mn, double step, int nbin, int checkFloat, uint16_t* out) {
+__global__ void bin_codes_kernel(int64_t n, ColRef col, DescDev d, const double* sp, uint16_t* out) {
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (int64_t)gridDim.x * blockDim.x) {
     double x = load_value(col, row);
-    out[row] = (uint16_t)(isnan(x) ? nbin : bin_of(x, mn, step, nbin, checkFloat != 0));
+    out[row] = (uint16_t)(isnan(x) ? d.nbin : bin_desc(d, sp, x));
   }
 }
 

@@ -9,13 +9,15 @@
 
 namespace h2ot {
 
-// one record per (leaf of the range, slot): the leaf's j-th active column. 9 words: odd stride, so the same word of 32
+// one record per (leaf of the range, slot): the leaf's j-th active column. 11 words: odd stride, so the same word of 32
 // different records sits in 32 different banks.
-enum { kSPlace = 0, kSMinLo, kSMinHi, kSStepLo, kSStepHi, kSKmin, kSKmax, kSCol, kSStride = 9 };
+enum { kSPlace = 0, kSMinLo, kSMinHi, kSStepLo, kSStepHi, kSKmin, kSKmax, kSCol, kSSpOff, kSSpN, kSZero, kSStride = 11 };
+//   kSSpOff: first split point of the pair in HistArgs::sp, 0xFFFFFFFF when the pair bins uniformly; kSSpN: their number, bit 31 =
+//   absolute points; kSZero: _zeroSplitPntPos. Only read by the SPLITPTS instantiations.
 constexpr int kSparseQueueWords = (kHistThreads / 32) * (64 + 32);  // compaction queues of the CTA's warps
 constexpr int kSparseColsSmem = 512;  // ColRef table is staged in shared memory up to this many frame columns
 
-template <int WPB, bool HAS_W, bool CHECKFLOAT>
+template <int WPB, bool HAS_W, bool CHECKFLOAT, bool SPLITPTS>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_sparse_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   int g = a.group_begin;
@@ -57,6 +59,12 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_sparse_kernel(HistArgs a
         r[kSKmin] = 0u;
         r[kSKmax] = 0u;
         r[kSCol] = (uint32_t)c;
+        if (SPLITPTS) {
+          const bool sp = (d.flags & H2OT_DESC_SPLITPTS) != 0;
+          r[kSSpOff] = sp ? (uint32_t)d.sp_off : 0xFFFFFFFFu;
+          r[kSSpN] = (uint32_t)d.sp_n | ((d.flags & H2OT_DESC_ABSOLUTE) ? 0x80000000u : 0u);
+          r[kSZero] = (uint32_t)d.zero_pos;
+        }
         if (any64) { mmS[p].mn = 0ULL; mmS[p].mx = 0ULL; }
       }
       cnt += __popc(m);
@@ -124,7 +132,13 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_sparse_kernel(HistArgs a
       int b = nbin;
       if (!na) {
         const double sa = CHECKFLOAT ? fabs(st) : st;  // sign bit of the record's step == the descriptor's H2OT_DESC_CHECKFLOAT
-        if (CHECKFLOAT && st < 0) b = bin_checkfloat_fast(x, mn, sa, nbin);
+        uint32_t spo = 0xFFFFFFFFu;
+        if (SPLITPTS) spo = lds_u32(rec + kSSpOff * 4);
+        if (SPLITPTS && spo != 0xFFFFFFFFu) {
+          const uint32_t spn = lds_u32(rec + kSSpN * 4);
+          b = bin_splitpts(x, mn, sa, nbin, a.sp + spo, (int)(spn & 0x7FFFFFFFu), (int)lds_u32(rec + kSZero * 4), (spn >> 31) != 0,
+                           CHECKFLOAT && st < 0);
+        } else if (CHECKFLOAT && st < 0) b = bin_checkfloat_fast(x, mn, sa, nbin);
         else b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x, mn), sa)), nbin - 1));
         if (cr.storage == H2OT_STORE_F64) {
           const unsigned long long k = dkey(x);

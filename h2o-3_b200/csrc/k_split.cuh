@@ -26,6 +26,7 @@ struct SplitArgs {
   const uint8_t* has_vals;
   double min_rows, min_split_improvement;
   h2ot_split* cand;  // [L*C]
+  const double* sp;  // the level's split-point pool or nullptr
 };
 
 constexpr int kSplitThreads = 128;
@@ -334,8 +335,11 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     while (x >= 0 && orig[3 * x] == 0) x--;
     int n = bestb;
     while (n < nbins && orig[3 * n] == 0) n++;
-    double lo = __dadd_rn(d.min, __ddiv_rn((double)(x + 1), d.step));
-    double hi = __dadd_rn(d.min, __ddiv_rn((double)n, d.step));
+    // binAt (T/DHistogram.java:308-312): through the node's split points when it has them
+    const double* pts = (d.flags & H2OT_DESC_SPLITPTS) ? a.sp + d.sp_off : nullptr;
+    const bool absolute = (d.flags & H2OT_DESC_ABSOLUTE) != 0;
+    double lo = bin_at_pts(d.min, d.step, x + 1, pts, absolute);
+    double hi = bin_at_pts(d.min, d.step, n, pts, absolute);
     if (d.flags & H2OT_DESC_ISINT) {
       lo = d.step == 1 ? __dsub_rn(lo, 1.0) : floor(lo);
       hi = d.step == 1 ? hi : ceil(hi);

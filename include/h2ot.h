@@ -86,6 +86,8 @@ typedef struct h2ot_hist_desc {
   int16_t order;   /* position of the column in the leaf's _scoreCols (column index if null): bestCol tie order, T/DTree.java:631-654 */
   uint8_t flags;   /* H2OT_DESC_* */
   uint8_t pad;
+  int32_t splitpts_off; /* H2OT_DESC_SPLITPTS: index of _splitPts[0] in the pool given to h2ot_set_split_points */
+  int32_t splitpts_n;   /* _splitPts.length (== nbin for Random / QuantilesGlobal, nbin + 1 for UniformRobust's custom points) */
 } h2ot_hist_desc;
 #define H2OT_DESC_ACTIVE 1      /* DHistogram non-null AND column in the leaf's _scoreCols (T/ScoreBuildHistogram2.java:421-426) */
 #define H2OT_DESC_ISINT 2       /* _isInt > 0 */
@@ -93,6 +95,9 @@ typedef struct h2ot_hist_desc {
 #define H2OT_DESC_INTOPT 8      /* _intOpt (only changes the untouched _min2/_maxIn sentinels, T/DHistogram.java:677-703) */
 #define H2OT_DESC_CHECKFLOAT 16 /* _checkFloatSplits (DRF, T/drf/DRF.java:201) */
 #define H2OT_DESC_INITNA 32     /* _initNA */
+#define H2OT_DESC_SPLITPTS 64   /* _splitPts != null: bin by Arrays.binarySearch over the split points (histogram_type Random /
+                                   QuantilesGlobal / UniformRobust, T/DHistogram.java:283-286) instead of (int)pos */
+#define H2OT_DESC_ABSOLUTE 128  /* _absoluteSplitPts: the points are column values, not positions relative to _min in steps */
 
 /* One DecidedNode as score_decide / GammaPass read it (T/DTree.java:587-763). */
 typedef struct h2ot_decided_node {
@@ -212,6 +217,11 @@ int h2ot_set_gamma_bounds(h2ot_engine* h, const double in[2]);
 /* Starts class-tree k: clears its node table, fixes the accumulator scale from work_abs_bound
  * (>= max |Work_k| over ALL ranks), and runs Sample (T/Sample.java:22-36) when sample_rate < 1. */
 int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate, double work_abs_bound);
+
+/* Split points of the NEXT h2ot_build_level / h2ot_level_step of class-tree k: one pool of doubles, referenced by the
+ * descriptors' splitpts_off / splitpts_n (DHistogram._splitPts as DHistogram.init leaves them, T/DHistogram.java:343-401).
+ * The pool is copied; -0.0 is stored as 0.0 like the reference does (:389-401). */
+int h2ot_set_split_points(h2ot_engine* h, int32_t k, const double* points, int64_t n);
 
 /* ---- per level: the drop-in for new ScoreBuildHistogram2(...).dfork2(fr2) (T/SharedTree.java:681-682).
  * decided[0..n_decided): the DecidedNodes created by the previous level's onCompletion (nid order);

@@ -229,7 +229,67 @@ struct Params {
 // ----------------------------------------------------------------------------------------------
 // DHistogram — T/DHistogram.java
 // ----------------------------------------------------------------------------------------------
+// java.util.Arrays.binarySearch(double[], double): <, > first, then Double.doubleToLongBits order (-0.0 < 0.0, NaN last)
+inline int j_binarySearch(const std::vector<double>& a, double key) {
+  int low = 0, high = (int)a.size() - 1;
+  while (low <= high) {
+    const int mid = (int)(((unsigned)low + (unsigned)high) >> 1);
+    const double midVal = a[mid];
+    if (midVal < key) low = mid + 1;
+    else if (midVal > key) high = mid - 1;
+    else {
+      auto bits = [](double d) { int64_t b; if (std::isnan(d)) return (int64_t)0x7ff8000000000000LL; memcpy(&b, &d, 8); return b; };
+      const int64_t midBits = bits(midVal), keyBits = bits(key);
+      if (midBits == keyBits) return mid;
+      else if (midBits < keyBits) low = mid + 1;
+      else high = mid - 1;
+    }
+  }
+  return -(low + 1);
+}
+// W/util/ArrayUtils.java:1985-2002
+inline std::vector<double> limitToRange(const std::vector<double>& pts, double min, double maxEx) {
+  int start = j_binarySearch(pts, min);
+  if (start < 0) start = -start - 1;
+  if (start == (int)pts.size()) start--;
+  if (pts[start] > min && start > 0) start--;
+  int end = j_binarySearch(pts, maxEx);
+  if (end < 0) end = -end - 1;
+  if (end < start) end = start;
+  return std::vector<double>(pts.begin() + start, pts.begin() + end);
+}
+// W/util/ArrayUtils.java:1933-1952
+inline std::vector<double> padUniformly(const std::vector<double>& orig, int newLength) {
+  const int origLength = (int)orig.size();
+  if (newLength <= origLength || origLength <= 1) return orig;
+  const int extraPoints = newLength - origLength;
+  const int extraPointsPerBin = extraPoints / (origLength - 1);
+  std::vector<double> res((size_t)newLength);
+  int pos = 0;
+  const int rem = extraPoints - extraPointsPerBin * (origLength - 1);
+  for (int i = 0; i < origLength - 1; ++i) {
+    const double startPos = orig[i];
+    const double delta = orig[i + 1] - startPos;
+    const int ext = extraPointsPerBin + (i < rem ? 1 : 0);
+    res[pos++] = startPos;
+    for (int j = 0; j < ext; ++j) res[pos++] = startPos + (j + 0.5) / ext * delta;
+  }
+  res[pos] = orig[origLength - 1];
+  return res;
+}
+
+// SharedTreeModel.SharedTreeParameters.HistogramType (T/SharedTreeModel.java); RoundRobin resolves to one of the others
+enum HistoType { HT_UniformAdaptive = 0, HT_Random = 1, HT_QuantilesGlobal = 2, HT_UniformRobust = 3 };
+
 struct DHistogram {
+  // split points (T/DHistogram.java:56-66): Random -> relative positions in [0, nbin); QuantilesGlobal / custom -> absolute values
+  int _histoType = HT_UniformAdaptive;
+  std::vector<double> _splitPts;          // empty == Java null
+  std::vector<double> _globalSplitPts;    // what DKV.getGet(_globalSplitPointsKey).splitPts would hold (empty == none)
+  bool _globalCanRefine = true;
+  std::vector<double> _customSplitPoints;
+  bool _absoluteSplitPts = false;
+  int _zeroSplitPntPos = 0;
   uint8_t _isInt = 0;  // 0 float, 1 int, 2 categorical
   bool _intOpt = false;
   uint16_t _nbin = 0;  // Java char
@@ -285,12 +345,66 @@ struct DHistogram {
   int actNBins() const { return nbins() + (hasNABin() ? 1 : 0); }    // :317-319
   double bins(int b) const { return w(b); }
 
-  // :308-312 (no split points)
-  double binAt(int b) const { return _min + b / _step; }
+  // :308-312
+  double binAt(int b) const {
+    if (_absoluteSplitPts) return _splitPts[b];
+    return _min + (_splitPts.empty() ? b : _splitPts[b]) / _step;
+  }
+  // :742-749
+  static std::vector<double> makeRandomSplitPoints(int nbin, PCGRNG& rng) {
+    std::vector<double> splitPts((size_t)nbin);
+    splitPts[0] = 0;
+    for (int i = 1; i < nbin; i++) splitPts[i] = (double)(rng.nextFloat() * (float)nbin);  // float * int in float
+    std::sort(splitPts.begin(), splitPts.end());
+    return splitPts;
+  }
 
-  // :343-417 (UniformAdaptive branch)
+  // :343-417
   void init() {
     assert(!_has_vals);
+    if (_histoType == HT_Random) {  // every node makes the same split points (:347-352)
+      const double d = ((_step + 0.324) * _min + 8.3425) + 89.342 * _maxEx;
+      int64_t bits;
+      memcpy(&bits, &d, 8);
+      const int64_t seed = (int64_t)((uint64_t)bits + (uint64_t)0xDECAF * (uint64_t)_nbin + (uint64_t)0xC0FFEE * (uint64_t)_isInt + (uint64_t)_seed);
+      PCGRNG rng(seed);
+      _splitPts = makeRandomSplitPoints(_nbin, rng);
+    } else if (_histoType == HT_QuantilesGlobal) {  // :353-376
+      if (!_globalSplitPts.empty()) {
+        _splitPts = limitToRange(_globalSplitPts, _min, _maxEx);
+        if (_globalCanRefine && _splitPts.size() > 1 && (int)_splitPts.size() < _nbin) _splitPts = padUniformly(_splitPts, _nbin);
+        if (_splitPts.size() <= 1) {
+          _splitPts.clear();
+          _histoType = HT_UniformAdaptive;
+        } else {
+          _absoluteSplitPts = true;
+          _nbin = (uint16_t)_splitPts.size();
+        }
+      }
+    } else if (_histoType == HT_UniformRobust) {  // :378-385, 419-430
+      if (!_customSplitPoints.empty()) {
+        _splitPts = limitToRange(_customSplitPoints, _min, _maxEx);
+        if (_splitPts.size() <= 1) {
+          _splitPts.clear();
+          _histoType = HT_UniformAdaptive;
+        } else {
+          _absoluteSplitPts = true;
+          _nbin = (uint16_t)(_splitPts.size() - 1);
+        }
+      } else {
+        _histoType = HT_UniformAdaptive;
+      }
+    }
+    if (!_splitPts.empty()) {  // :389-401 canonical zero, cached position of zero
+      _zeroSplitPntPos = j_binarySearch(_splitPts, 0.0);
+      if (_zeroSplitPntPos < 0) {
+        const int nzPos = j_binarySearch(_splitPts, -0.0);
+        if (nzPos >= 0) {
+          _splitPts[nzPos] = 0.0;
+          _zeroSplitPntPos = nzPos;
+        }
+      }
+    }
     _vals.assign((size_t)_vals_dim * _nbin + _vals_dim, 0.0);
     _has_vals = true;
     if (_checkFloatSplits) {
@@ -303,8 +417,14 @@ struct DHistogram {
   int bin(double col_data) const {
     if (std::isnan(col_data)) return _nbin;
     if (std::isinf(col_data)) return col_data < 0 ? 0 : _nbin - 1;
-    double pos = (col_data - _min) * _step;
-    int idx1 = j_d2i(pos);
+    double pos = _absoluteSplitPts ? col_data : ((col_data - _min) * _step);
+    int idx1;
+    if (!_splitPts.empty()) {
+      idx1 = pos == 0.0 ? _zeroSplitPntPos : j_binarySearch(_splitPts, pos);
+      if (idx1 < 0) idx1 = -idx1 - 2;
+    } else {
+      idx1 = j_d2i(pos);
+    }
     if (!_splitPtsFloat.empty()) {
       if (idx1 + 1 < (int)_splitPtsFloat.size()) {
         float splitAt = _splitPtsFloat[idx1 + 1];

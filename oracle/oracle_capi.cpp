@@ -18,6 +18,33 @@ void* orc_hist_new(int nbins, int nbins_cats, int isInt, double min, double maxE
     return nullptr;
   }
 }
+// histogram types other than UniformAdaptive: histoType (HistoType), and for QuantilesGlobal the global split points of the
+// column / for UniformRobust the custom split points of the node (T/DHistogram.java:343-430); applied by orc_hist_init
+void orc_hist_set_type(void* h, int histoType, const double* pts, int npts, int canRefine) {
+  DHistogram* d = (DHistogram*)h;
+  d->_histoType = histoType;
+  d->_globalCanRefine = canRefine != 0;
+  std::vector<double> v(pts ? pts : nullptr, pts ? pts + npts : nullptr);
+  if (histoType == HT_QuantilesGlobal) d->_globalSplitPts = v;
+  if (histoType == HT_UniformRobust) d->_customSplitPoints = v;
+}
+int orc_hist_split_points(void* h, double* out) {  // _splitPts after init (canonical zero included); returns the count
+  const DHistogram* d = (const DHistogram*)h;
+  if (out) std::copy(d->_splitPts.begin(), d->_splitPts.end(), out);
+  return (int)d->_splitPts.size();
+}
+int orc_hist_absolute(void* h) { return ((DHistogram*)h)->_absoluteSplitPts ? 1 : 0; }
+int orc_hist_type(void* h) { return ((DHistogram*)h)->_histoType; }
+int orc_limit_to_range(const double* pts, int n, double min, double maxEx, double* out) {
+  const std::vector<double> r = limitToRange(std::vector<double>(pts, pts + n), min, maxEx);
+  std::copy(r.begin(), r.end(), out);
+  return (int)r.size();
+}
+int orc_pad_uniformly(const double* pts, int n, int newLength, double* out) {
+  const std::vector<double> r = padUniformly(std::vector<double>(pts, pts + n), newLength);
+  std::copy(r.begin(), r.end(), out);
+  return (int)r.size();
+}
 void orc_hist_free(void* h) { delete (DHistogram*)h; }
 void orc_hist_init(void* h) { ((DHistogram*)h)->init(); }
 int orc_hist_nbin(void* h) { return ((DHistogram*)h)->_nbin; }

@@ -46,6 +46,7 @@ class OrcHistDesc(C.Structure):
 
 
 GAUSSIAN, BERNOULLI, MULTINOMIAL, POISSON, GAMMA, TWEEDIE = 0, 1, 2, 3, 4, 5
+HT_UniformAdaptive, HT_Random, HT_QuantilesGlobal, HT_UniformRobust = 0, 1, 2, 3
 NA_None, NAvsREST, NALeft, NARight, Left, Right = 0, 1, 2, 3, 4, 5
 
 
@@ -175,6 +176,27 @@ class Hist:
     def init(self):
         self.L.orc_hist_init(self.h)
         return self
+
+    def set_type(self, histo_type, pts=None, can_refine=True):
+        """HistogramType (HT_*) and, for QuantilesGlobal / UniformRobust, the global / custom split points; before init()."""
+        self.L.orc_hist_set_type.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        self.L.orc_hist_set_type.restype = None
+        v = None if pts is None else np.ascontiguousarray(pts, dtype=np.float64)
+        self.L.orc_hist_set_type(self.h, histo_type, ptr(v), 0 if v is None else len(v), int(can_refine))
+        return self
+
+    def split_points(self):
+        self.L.orc_hist_split_points.argtypes = [C.c_void_p, C.c_void_p]
+        n = self.L.orc_hist_split_points(self.h, None)
+        out = np.empty(n, dtype=np.float64)
+        self.L.orc_hist_split_points.restype = C.c_int
+        self.L.orc_hist_split_points(self.h, ptr(out))
+        return out
+
+    @property
+    def absolute(self):
+        self.L.orc_hist_absolute.argtypes = [C.c_void_p]
+        return bool(self.L.orc_hist_absolute(self.h))
 
     nbin = property(lambda s: s.L.orc_hist_nbin(s.h))
     step = property(lambda s: s.L.orc_hist_step(s.h))

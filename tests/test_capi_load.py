@@ -31,7 +31,7 @@ def test_library_builds_and_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header_sizes():
     P = h2ot_lib.pkg()
-    assert C.sizeof(P.HistDesc) == 32
+    assert C.sizeof(P.HistDesc) == 40
     assert C.sizeof(P.DecidedNode) == 48
     assert C.sizeof(P.Split) == 32 + 72 + 512
     assert C.sizeof(P.Config) == 64

@@ -389,3 +389,144 @@ def test_sparse_level_kernels_agree(weighted, check_float):
         if rows.size and np.any(~np.isnan(X[rows, c])):
             assert r["min2"][l * C_ + c] == oh.min2 and r["maxIn"][l * C_ + c] == oh.maxIn, (l, c)
     e.close()
+
+
+def _sp_hist(kind, nbins, isint, lo, maxEx, check_float, seed, pts=None):
+    """Oracle DHistogram with split points: kind 'random' (HT_Random), 'global' (QuantilesGlobal), 'custom' (UniformRobust)."""
+    oh = O.Hist(nbins, 1024, isint, lo, maxEx, False, True, 1e-5, seed, check_float)
+    oh.set_type({"random": O.HT_Random, "global": O.HT_QuantilesGlobal, "custom": O.HT_UniformRobust}[kind], pts)
+    return oh.init()
+
+
+def test_split_point_binning_levels_and_splits():
+    """histogram_type Random / QuantilesGlobal / UniformRobust: DHistogram.bin through Arrays.binarySearch over _splitPts
+    (T/DHistogram.java:281-286), binAt through the points (:308-312). Bin codes bit-exact vs the oracle; a level of several
+    leaves built by the leaf-major kernel == the L2-atomics kernel == updateHisto; split search (splat through binAt) ==
+    findBestSplitPoint."""
+    rng = np.random.default_rng(31)
+    n = 120001
+    X = np.stack([
+        rng.normal(size=n).astype(np.float32).astype(np.float64),
+        rng.lognormal(size=n),
+        rng.integers(-40, 4000, n).astype(np.float64),
+        np.round(rng.normal(size=n), 1),   # many values exactly on decimal grid points, zeros included
+    ], axis=1)
+    X[rng.random(X.shape) < 0.03] = NaN
+    C_ = X.shape[1]
+    is_int = [0, 0, 1, 0]
+    y = (np.nan_to_num(X[:, 0]) > 0.2).astype(np.float64) + 0.2 * np.nan_to_num(X[:, 3]) + rng.normal(size=n) * 0.3
+    work = y.astype(np.float32).astype(np.float64)
+    P, e = _engine(X)
+    e.set_work(work)
+    e.begin_tree(0, 0, 1.0, float(np.max(np.abs(work))))
+
+    def hist_for(c, kind, nbins, check_float, seed):
+        v = X[:, c]
+        lo, hi = np.nanmin(v), np.nanmax(v)
+        maxEx = O.lib().orc_find_maxEx(hi, is_int[c])
+        pts = None
+        if kind == "global":
+            pts = np.unique(np.nanquantile(v, np.linspace(0, 1, nbins + 5)))
+        if kind == "custom":
+            pts = np.unique(np.concatenate([[lo], np.nanquantile(v, np.linspace(0.05, 0.95, nbins)), [maxEx]]))
+        return _sp_hist(kind, nbins, is_int[c], lo, maxEx, check_float, seed, pts), lo, maxEx
+
+    # ---- 1. bin codes
+    for c in range(C_):
+        for kind in ("random", "global", "custom"):
+            for nbins in (20, 257):
+                for cf in ((False, True) if is_int[c] == 0 else (False,)):
+                    oh, lo, maxEx = hist_for(c, kind, nbins, cf, seed=1234 + c)
+                    sp = oh.split_points()
+                    assert sp.size > 1 and oh.absolute == (kind != "random")
+                    e.set_split_points(np.concatenate([[123.0, -5.0], sp]))  # the pool may hold other nodes' points too
+                    d = P.make_desc(lo, maxEx, oh.nbin, step=oh.step, is_int=is_int[c], check_float=cf, splitpts=(2, sp.size),
+                                    absolute=oh.absolute)
+                    got = e.bin_codes(c, d).astype(np.int32)
+                    want = oh.bin_many(X[:, c])
+                    assert np.array_equal(got, want), (c, kind, nbins, cf, int(np.sum(got != want)))
+
+    # ---- 2. a level of L leaves, every (leaf, column) with its own split points; sparse kernel == global kernel == oracle
+    L = 6
+    leaf_of = rng.integers(0, L, n).astype(np.int32)
+    nids = (leaf_of + 1).astype(np.int32)
+    nids[rng.random(n) < 0.1] = P.DECIDED_ROW
+    e.set_nids(nids)
+    dn = (P.DecidedNode * (L + 1))()
+    for i in range(L + 1):
+        dn[i] = P.DecidedNode(nid=i, pid=-1, col=-1, equal=0, nasplit=P.NA_NONE, splat=NaN, child=(C.c_int32 * 2)(-1, -1))
+    descs = (P.HistDesc * (L * C_))()
+    pool, hists = [], {}
+    kinds = ["random", "global", "custom", "uniform"]
+    for l in range(L):
+        for c in range(C_):
+            kind = kinds[(l + c) % 4]
+            cf = is_int[c] == 0 and (l % 2 == 1)
+            if kind == "uniform":
+                v = X[:, c]
+                lo, hi = np.nanmin(v), np.nanmax(v)
+                maxEx = O.lib().orc_find_maxEx(hi, is_int[c])
+                oh = O.Hist(64, 1024, is_int[c], lo, maxEx, False, True, 1e-5, 0, cf).init()
+                descs[l * C_ + c] = P.make_desc(lo, maxEx, oh.nbin, step=oh.step, is_int=is_int[c], init_na=True, check_float=cf, order=c)
+            else:
+                oh, lo, maxEx = hist_for(c, kind, 50, cf, seed=77 * l + c)
+                sp = oh.split_points()
+                off = sum(len(p) for p in pool)
+                pool.append(sp)
+                descs[l * C_ + c] = P.make_desc(lo, maxEx, oh.nbin, step=oh.step, is_int=is_int[c], init_na=True, check_float=cf, order=c,
+                                                splitpts=(off, sp.size), absolute=oh.absolute)
+            hists[(l, c)] = oh
+    e.set_split_points(np.concatenate(pool))
+    results = []
+    for mode in (0, 1):
+        e.set_hist_mode(mode)
+        e.stats_reset()
+        e.build_level(descs, leaf_offset=1, decided=dn)
+        results.append(e.finish_level())
+        assert e.stats().sparse_launches == (1 if mode == 0 else 0)
+    e.set_hist_mode(0)
+    assert np.array_equal(results[0]["vals"], results[1]["vals"])
+    assert np.array_equal(results[0]["min2"], results[1]["min2"]) and np.array_equal(results[0]["maxIn"], results[1]["maxIn"])
+    r = results[0]
+    live = nids != P.DECIDED_ROW
+    for (l, c), oh in hists.items():
+        rows = np.nonzero(live & (leaf_of == l))[0].astype(np.int32)
+        oh.update(None, X[:, c], work[rows], rows)
+        oh.reduce_precision()
+        ov = oh.vals()
+        off = r["offsets"][l * C_ + c]
+        gv = r["vals"][off: off + ov.size]
+        assert np.array_equal(gv[0::3], ov[0::3]), (l, c)
+        for j in (1, 2):
+            assert np.max(np.abs(gv[j::3] - ov[j::3])) <= 1e-6 * max(np.max(np.abs(ov[j::3])), 1e-300), (l, c, j)
+        assert r["min2"][l * C_ + c] == oh.min2 and r["maxIn"][l * C_ + c] == oh.maxIn
+
+    # ---- 3. split search on one column at a time (root level): splat goes through binAt of the split points
+    e.set_nids(np.zeros(n, dtype=np.int32))
+    for c in (0, 1, 2, 3):
+        for kind in ("random", "global", "custom"):
+            for cf in ((False, True) if is_int[c] == 0 else (False,)):
+                oh, lo, maxEx = hist_for(c, kind, 40, cf, seed=5 + c)
+                sp = oh.split_points()
+                e.set_split_points(sp)
+                d1 = (P.HistDesc * C_)()
+                for j in range(C_):
+                    d1[j] = P.make_desc(0.0, 1.0, 1, active=False)
+                d1[c] = P.make_desc(lo, maxEx, oh.nbin, step=oh.step, is_int=is_int[c], init_na=True, check_float=cf, order=0,
+                                    splitpts=(0, sp.size), absolute=oh.absolute)
+                e.build_level(d1)
+                rr = e.finish_level()
+                oh.set_vals(rr["vals"][: (oh.nbin + 1) * 3])
+                for min_rows in (1.0, 50.0):
+                    got = e.find_splits(min_rows, 1e-5)[0]
+                    want = oh.find_split(c, min_rows)
+                    if want is None:
+                        assert got.col == -1, (c, kind, min_rows)
+                        continue
+                    want_splat = oh.splat_numeric(want.bin, want.nasplit) if (want.nasplit != O.NAvsREST and want.equal in (0, 1)) else -1.0
+                    if cf and np.isnan(want_splat):
+                        assert got.col == -1
+                        continue
+                    assert _split_tuple(got) == _split_tuple(want), (c, kind, cf, min_rows, _split_tuple(got), _split_tuple(want))
+                    assert np.float32(got.splat).tobytes() == np.float32(want_splat).tobytes(), (c, kind, cf, got.splat, want_splat)
+    e.close()

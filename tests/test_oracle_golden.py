@@ -3,7 +3,10 @@
 Each test cites the reference test it replays (paths relative to /root/reference,
 TT/ = h2o-algos/src/test/java/hex/tree/). No GPU, no reference files needed at run time.
 """
+import ctypes as C
 import math
+
+import pytest
 
 import numpy as np
 
@@ -294,3 +297,62 @@ def test_multinomial_runs_and_improves():
     F = np.stack([m.F(k) for k in range(3)], axis=1)
     acc = float(np.mean(np.argmax(F, axis=1) == y))
     assert acc > 0.6
+
+
+# ---- histogram types with split points (T/DHistogram.java:283-300, 343-430; TT/HistogramTest.java:111-157, 210-269)
+def _limit(pts, mn, mx):
+    L = O.lib()
+    L.orc_limit_to_range.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p]
+    p = np.ascontiguousarray(pts, dtype=np.float64)
+    out = np.empty(len(p), dtype=np.float64)
+    n = L.orc_limit_to_range(O.ptr(p), len(p), mn, mx, O.ptr(out))
+    return list(out[:n])
+
+
+def _pad(pts, n_new):
+    L = O.lib()
+    L.orc_pad_uniformly.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    p = np.ascontiguousarray(pts, dtype=np.float64)
+    out = np.empty(max(len(p), n_new), dtype=np.float64)
+    n = L.orc_pad_uniformly(O.ptr(p), len(p), n_new, O.ptr(out))
+    return list(out[:n])
+
+
+def test_limit_to_range_and_pad_uniformly_golden():
+    """HistogramTest.testShrinking5-9, testPadding, testPadding2, testPadding3: exact arrays."""
+    b = [0.3, 0.31, 0.32, 0.4, 0.7]
+    assert _limit(b, 0.31, 0.9) == [0.31, 0.32, 0.4, 0.7]
+    assert _limit(b, 0.305, 0.9) == [0.3, 0.31, 0.32, 0.4, 0.7]
+    assert _limit(b, 0.305, 0.699) == [0.3, 0.31, 0.32, 0.4]
+    assert _limit(b, 0.7, 0.9) == [0.7]
+    assert _limit(b, 0.8, 0.9) == [0.7]
+    assert _pad(b, 9) == [0.3, 0.305, 0.31, 0.315, 0.32, 0.36, 0.4, 0.55, 0.7]
+    assert _pad(b, 10) == [0.3, 0.3025, 0.3075, 0.31, 0.315, 0.32, 0.36, 0.4, 0.55, 0.7]
+    assert _pad(b, 8) == [0.3, 0.305, 0.31, 0.315, 0.32, 0.36, 0.4, 0.7]
+
+
+@pytest.mark.parametrize("histo_type", [O.HT_UniformAdaptive, O.HT_Random, O.HT_QuantilesGlobal])
+def test_splits_bin_and_binAt_agree_for_every_histogram_type(histo_type):
+    """HistogramTest.testSplits (:111-157): nbins 13 on [1, 6.900000000000001); scanning the range, the first value that lands in
+    bin b must be binAt(b) to 1e-6 -- for UniformAdaptive, Random (any seed) and QuantilesGlobal with the test's 13 points."""
+    pts = [1, 1.5, 2, 2.5, 3, 4, 5, 6.1, 6.2, 6.3, 6.7, 6.8, 6.85]
+    for seed in ([0] if histo_type != O.HT_Random else [1, -77, 123456789012345]):
+        h = O.Hist(13, 13, 0, 1.0, 6.900000000000001, seed=seed)
+        h.set_type(histo_type, pts if histo_type == O.HT_QuantilesGlobal else None)
+        h.init()
+        assert h.nbin == 13
+        sp = h.split_points()
+        if histo_type == O.HT_QuantilesGlobal:
+            assert h.absolute and list(sp) == [float(p) for p in pts]
+        if histo_type == O.HT_Random:
+            assert not h.absolute and len(sp) == 13 and sp[0] == 0 and np.all(np.diff(sp) >= 0) and sp[-1] < 13
+        N = 2_000_000
+        x = 1.0 + np.arange(N, dtype=np.float64) / N * (6.900000000000001 - 1.0)
+        b = h.bin_many(x)
+        assert b.min() == 0 and b.max() <= 12 and np.all(np.diff(b) >= 0)
+        l2 = np.array([h.binAt(i) for i in range(13)])
+        first = np.searchsorted(b, np.arange(13), side="left")
+        for i in range(13):
+            if first[i] < N and b[first[i]] == i:  # Random can leave a bin empty (two equal split points)
+                assert abs(x[first[i]] - l2[i]) <= 1e-5, (i, x[first[i]], l2[i])
+        assert h.bin(1.0) == 0 and h.bin(float("nan")) == 13 and h.bin(float("inf")) == 12
