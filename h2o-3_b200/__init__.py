@@ -80,7 +80,7 @@ class Stats(C.Structure):
 class GbmParams(C.Structure):
     _fields_ = [("ntrees", C.c_int32), ("max_depth", C.c_int32), ("nbins", C.c_int32), ("nbins_cats", C.c_int32),
                 ("nbins_top_level", C.c_int32), ("family", C.c_int32), ("nclass", C.c_int32), ("algo", C.c_int32),
-                ("mtries", C.c_int32), ("pad", C.c_int32),
+                ("mtries", C.c_int32), ("histogram_type", C.c_int32),
                 ("min_rows", C.c_double), ("min_split_improvement", C.c_double), ("sample_rate", C.c_double),
                 ("col_sample_rate", C.c_double), ("col_sample_rate_per_tree", C.c_double),
                 ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
@@ -469,10 +469,10 @@ class GBM:
                  min_split_improvement=1e-5, sample_rate=1.0, col_sample_rate=1.0, col_sample_rate_per_tree=1.0,
                  col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
                  max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
-                 device=0, algo=0, mtries=-1, tweedie_power=1.5):
+                 device=0, algo=0, mtries=-1, tweedie_power=1.5, histogram_type="AUTO"):
         self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
                                 nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, algo=algo,
-                                mtries=mtries, pad=0,
+                                mtries=mtries, histogram_type={"AUTO": 0, "UniformAdaptive": 0, "Random": 1}[histogram_type],
                                 min_rows=min_rows, min_split_improvement=min_split_improvement, sample_rate=sample_rate,
                                 col_sample_rate=col_sample_rate, col_sample_rate_per_tree=col_sample_rate_per_tree,
                                 col_sample_rate_change_per_level=col_sample_rate_change_per_level, learn_rate=learn_rate,

@@ -100,6 +100,9 @@ struct Pcg {
     const uint64_t lo = next_int();
     return (int64_t)((hi << 32) | lo);
   }
+  float next_float() {  // java.util.Random.nextFloat over PCGRNG.next(24) (:86)
+    return (float)(int32_t)(next_long() & ((1LL << 24) - 1)) / (float)(1 << 24);
+  }
   int32_t next_bounded(int32_t bound) {  // :88-118
     const uint64_t threshold = (uint64_t)((-(int64_t)bound) % (int64_t)bound) & 0xFFFFFFFFULL;
     for (;;) {
@@ -305,6 +308,7 @@ struct h2ot_gbm {
   h2ot_gbm_timing timing{};
   // scratch
   std::vector<h2ot_hist_desc> descs;
+  std::vector<double> split_pts;  // histogram_type Random: the level's split points
   std::vector<double> min2, max_in, w_na;
   std::vector<uint8_t> has;
   std::vector<h2ot_split> splits;
@@ -314,6 +318,7 @@ namespace {
 
 // T/DHistogram.java:526-554
 bool use_int_opt(const ColMeta& v, const h2ot_gbm_params& p) {
+  if (p.histogram_type == 1) return false;  // Random: no integer fast path (T/DHistogram.java:537-542)
   if (v.is_cat) return v.cardinality < p.nbins_cats;
   if (v.is_int) {
     const double len = v.max - v.min;
@@ -421,6 +426,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
   const double t0 = now_s();
   // descriptors of the undecided leaves
   g->descs.assign((size_t)L * C, h2ot_hist_desc{});
+  g->split_pts.clear();
   int64_t active_pairs = 0;
   std::vector<char> col_active(C, 0);
   for (int l = 0; l < L; l++) {
@@ -441,10 +447,26 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
       d.order = order[c];
       d.flags = H2OT_DESC_ACTIVE | (h.is_int > 0 ? H2OT_DESC_ISINT : 0) | (h.is_int == 2 ? H2OT_DESC_ISCAT : 0) |
                 (h.int_opt ? H2OT_DESC_INTOPT : 0) | (h.check_float ? H2OT_DESC_CHECKFLOAT : 0) | (h.init_na ? H2OT_DESC_INITNA : 0);
+      if (g->p.histogram_type == 1) {  // Random: DHistogram.init draws the node's split points (T/DHistogram.java:347-352, 742-749)
+        const double sd = ((h.step + 0.324) * h.min + 8.3425) + 89.342 * h.max_ex;
+        int64_t bits;
+        memcpy(&bits, &sd, sizeof bits);
+        Pcg rng((int64_t)((uint64_t)bits + 0xDECAFULL * (uint64_t)h.nbin + 0xC0FFEEULL * (uint64_t)h.is_int + (uint64_t)h.seed));
+        const size_t off = g->split_pts.size();
+        g->split_pts.resize(off + (size_t)h.nbin);
+        double* pts = g->split_pts.data() + off;
+        pts[0] = 0;
+        for (int i = 1; i < h.nbin; i++) pts[i] = (double)(rng.next_float() * (float)h.nbin);
+        std::sort(pts, pts + h.nbin);
+        d.flags |= H2OT_DESC_SPLITPTS;
+        d.splitpts_off = (int32_t)off;
+        d.splitpts_n = h.nbin;
+      }
       active_pairs++;
       col_active[c] = 1;
     }
   }
+  if (g->p.histogram_type == 1) GTRY(h2ot_set_split_points(g->eng, k, g->split_pts.data(), (int64_t)g->split_pts.size()));
   const double t_descs_done = now_s();
   // decided nodes the device does not have yet
   std::vector<h2ot_decided_node> dn;

@@ -25,7 +25,9 @@ typedef struct h2ot_gbm h2ot_gbm;
 typedef struct h2ot_gbm_params {
   int32_t ntrees, max_depth, nbins, nbins_cats, nbins_top_level, family, nclass, algo;
   int32_t mtries; /* DRF: -1 sqrt(ncols) / ncols/3, -2 all columns, else the count (T/drf/DRF.java:117-125) */
-  int32_t pad;
+  int32_t histogram_type; /* SharedTreeParameters._histogram_type: 0 AUTO / UniformAdaptive, 1 Random (per-node random split points,
+                             T/DHistogram.java:347-352, 742-749); QuantilesGlobal / UniformRobust need split points from outside
+                             this driver (h2ot_set_split_points serves them at the engine level) */
   double min_rows, min_split_improvement, sample_rate, col_sample_rate, col_sample_rate_per_tree,
       col_sample_rate_change_per_level, learn_rate, learn_rate_annealing, max_abs_leafnode_pred;
   int64_t seed;

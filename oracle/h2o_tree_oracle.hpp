@@ -224,6 +224,7 @@ struct Params {
   int mtries = -1;  // DRF only
   int nthreads = 1; // CPU threads for the SBH2 restatement (baseline timing)
   double tweedie_power = 1.5;  // H/Model.java Parameters._tweedie_power
+  int histogram_type = 0;      // HistoType: 0 UniformAdaptive (== AUTO), 1 Random (T/SharedTreeModel.java HistogramType)
 };
 
 // ----------------------------------------------------------------------------------------------
@@ -310,8 +311,9 @@ struct DHistogram {
   DHistogram() = default;
   // ctor :190-269 (UniformAdaptive only; constraints/uplift/custom split points are out of scope)
   DHistogram(int nbins, int nbins_cats, uint8_t isInt, double min, double maxEx, bool intOpt, bool initNA,
-             double minSplitImprovement, int64_t seed, bool checkFloatSplits) {
+             double minSplitImprovement, int64_t seed, bool checkFloatSplits, int histoType = 0) {
     if (!(maxEx > min)) throw std::runtime_error("DHistogram: maxEx <= min");
+    _histoType = histoType;
     _isInt = isInt;
     _min = min;
     _maxEx = maxEx;
@@ -624,7 +626,7 @@ struct Split {
       nhists[j] = std::make_shared<DHistogram>(adj_nbins, parms.nbins_cats, h->_isInt, min, maxEx, h->_intOpt, hasNAs,
                                                parms.min_split_improvement,
                                                (int64_t)((uint64_t)h->_seed * 0xDECAFULL + (uint64_t)(way + 1)),
-                                               h->_checkFloatSplits);
+                                               h->_checkFloatSplits, parms.histogram_type);
       cnt++;
     }
     if (cnt == 0) return {};
@@ -1071,6 +1073,7 @@ struct Frame {
 
 // T/DHistogram.java:526-554
 inline bool useIntOpt(const Column& v, const Params& parms) {
+  if (parms.histogram_type != HT_UniformAdaptive && parms.histogram_type != HT_UniformRobust) return false;  // :537-542
   if (v.isCat) return v.cardinality < parms.nbins_cats;
   if (v.isInt) {
     double min = v.min, max = v.max;
@@ -1095,7 +1098,7 @@ inline std::vector<HistPtr> initialHist(const Frame& fr, int nbins, int64_t seed
       if (v.nacnt == vlen || v.isConstNoNA()) hs[c] = nullptr;
       else
         hs[c] = std::make_shared<DHistogram>(nbins, parms.nbins_cats, type, minIn, maxEx, intOpt, v.nacnt > 0,
-                                             parms.min_split_improvement, seed, checkFloatSplits);
+                                             parms.min_split_improvement, seed, checkFloatSplits, parms.histogram_type);
     } catch (const std::range_error&) {
       hs[c] = nullptr;
     }

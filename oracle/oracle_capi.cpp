@@ -198,6 +198,7 @@ struct OrcParams {
   long long seed;
   long long chunk_rows;
   double tweedie_power;
+  long long histogram_type;  // HistoType
 };
 static Params to_params(const OrcParams* p) {
   Params q;
@@ -220,6 +221,7 @@ static Params to_params(const OrcParams* p) {
   q.max_abs_leafnode_pred = p->max_abs_leafnode_pred;
   q.seed = p->seed;
   if (p->tweedie_power > 0) q.tweedie_power = p->tweedie_power;
+  q.histogram_type = (int)p->histogram_type;
   return q;
 }
 

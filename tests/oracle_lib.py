@@ -36,7 +36,8 @@ class OrcParams(C.Structure):
                 ("col_sample_rate", C.c_double), ("col_sample_rate_per_tree", C.c_double),
                 ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
                 ("learn_rate_annealing", C.c_double), ("max_abs_leafnode_pred", C.c_double),
-                ("seed", C.c_longlong), ("chunk_rows", C.c_longlong), ("tweedie_power", C.c_double)]
+                ("seed", C.c_longlong), ("chunk_rows", C.c_longlong), ("tweedie_power", C.c_double),
+                ("histogram_type", C.c_longlong)]
 
 
 class OrcHistDesc(C.Structure):
@@ -56,7 +57,7 @@ def default_params(**kw):
                   nclass=2, nthreads=1, min_rows=10.0, min_split_improvement=1e-5, sample_rate=1.0,
                   col_sample_rate=1.0, col_sample_rate_per_tree=1.0, col_sample_rate_change_per_level=1.0,
                   learn_rate=0.1, learn_rate_annealing=1.0, max_abs_leafnode_pred=float(np.finfo(np.float64).max),
-                  seed=1234, chunk_rows=0, tweedie_power=1.5)
+                  seed=1234, chunk_rows=0, tweedie_power=1.5, histogram_type=0)
     for k, v in kw.items():
         setattr(p, k, v)
     return p

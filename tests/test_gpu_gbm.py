@@ -15,7 +15,9 @@ def _run_both(X, y, cats=None, w=None, off=None, capture=True, **kw):
     dist = kw.pop("distribution", "bernoulli")
     nclass = kw.pop("nclass", 2 if dist == "bernoulli" else 1)
     fam = {"gaussian": O.GAUSSIAN, "bernoulli": O.BERNOULLI, "multinomial": O.MULTINOMIAL}[dist]
-    op = O.default_params(family=fam, nclass=nclass, **kw)
+    ht = kw.pop("histogram_type", "AUTO")
+    op = O.default_params(family=fam, nclass=nclass, histogram_type={"AUTO": 0, "Random": 1}[ht], **kw)
+    kw["histogram_type"] = ht
     om = O.Model(O.Frame(X, y, w=w, off=off, cat_cards=cats), op, capture=capture)
     gm = P.GBM(distribution=dist, nclass=nclass, **kw)
     gm.load([X[:, c] for c in range(X.shape[1])], y, weights=w, offset=off, categorical=cats)
@@ -294,3 +296,19 @@ def test_deep_levels_split_into_leaf_ranges(monkeypatch):
     h2ot_lib.compare_models(gm2, om)
     assert sig == [gm2.predictions().tobytes()] + [bytes(gm2.tree(t)[0]) for t in range(gm2.ntrees)]
     gm2.close()
+
+
+@pytest.mark.parametrize("with_cat", [False, True])
+def test_random_histogram_type_matches_oracle(with_cat):
+    """histogram_type = Random (T/DHistogram.java:347-352, 742-749): every node draws its own sorted random split points from a
+    PCG seeded by its range, bins by binary search and splits at binAt of those points. Levels, trees and predictions must
+    match the oracle like the uniform build does (integer columns lose the integer fast path, :537-542)."""
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=13, with_cat=with_cat)
+    gm, om = _run_both(X, y, cats, ntrees=5, max_depth=5, nbins=20, seed=4321, histogram_type="Random")
+    st = h2ot_lib.compare_models(gm, om)
+    assert st["levels"] >= 5 * 4 and st["hists"] > 80
+    # and it is not the uniform model
+    gu, _ = _run_both(X, y, cats, ntrees=5, max_depth=5, nbins=20, seed=4321, capture=False)
+    assert not np.array_equal(gm.predictions(), gu.predictions())
+    gm.close()
+    gu.close()
