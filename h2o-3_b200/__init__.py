@@ -112,10 +112,10 @@ ENGINE_SYMBOLS = [
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points",
+    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree",
 ]
 GBM_SYMBOLS = [
-    "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
+    "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
     "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
@@ -146,6 +146,8 @@ def load():
     L.h2ot_load_column.argtypes = [vp, i32, i64, i64, vp]
     L.h2ot_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
     L.h2ot_set_split_points.argtypes = [vp, i32, vp, i64]
+    L.h2ot_score_tree.argtypes = [vp, i32, i32, i32, vp]
+    L.h2ot_gbm_predict.argtypes = [vp, i64, vp, vp]
     L.h2ot_debug_get_column.argtypes = [vp, i32, i64, i64, vp]
     L.h2ot_gbm_load_chunk.argtypes = [vp, i32, i64, i64, i32, vp, i64]
     L.h2ot_gbm_chunks_done.argtypes = [vp, i32, i32, i32]
@@ -580,6 +582,15 @@ class GBM:
     def predictions(self, k=0):
         out = np.empty(self.nrows, dtype=np.float64)
         _check(self.L.h2ot_gbm_predictions(self.g, k, _p(out)))
+        return out
+
+    def predict(self, columns):
+        """Link-space scores of NEW rows: array [K, nrows] (GBM: init_f + sum of the trees; DRF: sum of the trees' votes)."""
+        cols = [_f64(c) for c in columns]
+        n = cols[0].size
+        ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+        out = np.empty((self.K, n), dtype=np.float64)
+        _check(self.L.h2ot_gbm_predict(self.g, n, C.cast(ptrs, C.c_void_p), _p(out)))
         return out
 
     def oobt(self):

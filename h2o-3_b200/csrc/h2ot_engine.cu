@@ -1869,6 +1869,26 @@ int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_
   return finish_call(h);
 }
 
+int h2ot_score_tree(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_nodes, const float* node_pred) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (n_nodes <= 0 || !node_pred || leaf_start < 0) H2OT_FAIL(H2OT_ERR_INVALID, "bad node_pred / leaf_start");
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  TreeState& t = h->ts[k];
+  // a root-only tree has no decided node at all: every row takes node_pred[0]
+  if (t.n_nodes == 0 && leaf_start > 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_set_tree must run before h2ot_score_tree");
+  TRY(t.nodes.ensure(1));
+  TRY(t.bitsets.ensure(16));
+  TRY(t.d_pred.ensure(n_nodes));
+  TRY(h2d(h, t.d_pred.p, node_pred, (size_t)n_nodes * sizeof(float)));
+  ScoreTreeArgs a{h->n, n_nodes, std::min(leaf_start, t.n_nodes), t.nodes.p, t.bitsets.p, h->d_cols.p, t.F, t.d_pred.p};
+  TRY(t_begin(h, &h->stats.ms_addtree));
+  score_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  return finish_call(h);
+}
+
 int h2ot_score_metrics(h2ot_engine* h, h2ot_metrics* out) {
   CHECK_ENGINE(h);
   if (!out) H2OT_FAIL(H2OT_ERR_INVALID, "null out");

@@ -292,6 +292,7 @@ struct h2ot_gbm {
   int64_t nrows = 0, nrows_global = 0, row_offset = 0;
   int ncols = 0, K = 1, nclass = 1;
   bool has_w = false, has_off = false, inited = false;
+  int device = 0;
   int world = 1;
   std::vector<ColMeta> cols;
   bool have_y = false, have_w = false, have_off = false;
@@ -785,6 +786,7 @@ int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int
   }
   g->has_w = has_weights != 0;
   g->has_off = has_offset != 0;
+  g->device = device;
   g->cols.resize(ncols);
   g->varimp.assign(ncols, 0.f);
   g->rand = Pcg(p->seed);
@@ -1008,6 +1010,59 @@ int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_predictions(g->eng, k, out);
 }
+int h2ot_gbm_predict(h2ot_gbm* g, int64_t nrows, const double* const* columns, double* out) {
+  if (!g || !columns || !out || nrows <= 0) GFAIL(H2OT_ERR_INVALID, "bad argument");
+  if (!g->inited) GFAIL(H2OT_ERR_INVALID, "model not initialised");
+  h2ot_config cfg{};
+  cfg.device = g->device;
+  cfg.ncols = g->ncols;
+  cfg.nrows = nrows;
+  cfg.nrows_global = nrows;
+  cfg.nclass_trees = g->K;
+  cfg.nclass = g->nclass;
+  cfg.family = g->p.family;
+  cfg.tweedie_power = g->p.tweedie_power;
+  h2ot_engine* e = nullptr;
+  GTRY(h2ot_create(&cfg, &e));
+  auto run = [&]() -> int {
+    for (int c = 0; c < g->ncols; c++) {
+      if (!columns[c]) GFAIL(H2OT_ERR_INVALID, "null column");
+      GTRY(h2ot_load_column(e, c, 0, nrows, columns[c]));
+    }
+    std::vector<double> zeros((size_t)nrows, 0.0);
+    GTRY(h2ot_load_response(e, 0, nrows, zeros.data()));
+    GTRY(h2ot_finalize_frame(e));
+    std::vector<double> f0((size_t)g->K, 0.0);
+    GTRY(h2ot_init_model(e, f0.data(), nullptr));
+    for (const std::vector<FinishedTree>& tk : g->trees)
+      for (int k = 0; k < g->K; k++) {
+        const FinishedTree& ft = tk[(size_t)k];
+        std::vector<h2ot_decided_node> dn;
+        std::vector<uint8_t> pool;
+        std::vector<float> pred(ft.nodes.size());
+        for (size_t i = 0; i < ft.nodes.size(); i++) {
+          pred[i] = ft.nodes[i].pred;
+          if ((int)i < ft.leaves_start && ft.nodes[i].kind == 1) {
+            dn.emplace_back();
+            to_device_node(ft.nodes[i], dn.back(), pool);
+          }
+        }
+        GTRY(h2ot_set_tree(e, k, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size()));
+        GTRY(h2ot_score_tree(e, k, ft.nodes[0].kind == 2 ? 0 : ft.leaves_start, (int)pred.size(), pred.data()));
+      }
+    for (int k = 0; k < g->K; k++) {
+      double* o = out + (size_t)k * (size_t)nrows;
+      GTRY(h2ot_get_predictions(e, k, o));
+      if (g->p.algo == H2OT_ALGO_GBM && g->init_f != 0)
+        for (int64_t r = 0; r < nrows; r++) o[r] += g->init_f;
+    }
+    return H2OT_OK;
+  };
+  const int rc = run();
+  h2ot_destroy(e);
+  return rc;
+}
+
 int h2ot_gbm_oobt(h2ot_gbm* g, double* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_oobt(g->eng, out);

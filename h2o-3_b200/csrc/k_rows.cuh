@@ -415,6 +415,30 @@ __global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------ score a finished tree
+// SharedTreeMojoModel.scoreTree on the node table: root to leaf per row, prediction added in double.
+struct ScoreTreeArgs {
+  int64_t n;
+  int32_t n_nodes, leaf_start;
+  const h2ot_decided_node* nodes;
+  const uint8_t* bitsets;
+  const ColRef* cols;
+  double* F;
+  const float* node_pred;
+};
+__global__ void __launch_bounds__(256) score_tree_kernel(ScoreTreeArgs a) {
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
+    int nid = 0;
+    for (int depth = 0; depth < 64 && nid >= 0 && nid < a.leaf_start && nid < a.n_nodes; depth++) {
+      const h2ot_decided_node dn = a.nodes[nid];
+      if (dn.col < 0) break;  // a root that never split is the leaf
+      nid = child_node_id(dn, a.cols, a.bitsets, row);
+    }
+    const float pred = (nid >= 0 && nid < a.n_nodes) ? a.node_pred[nid] : 0.f;
+    a.F[row] = __dadd_rn(a.F[row], (double)pred);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ training metrics
 // hex.tree.Score (T/Score.java:57-141) for GBM on the resident Tree_k columns: score2 / score1 (T/SharedTree.java:782-789,
 // T/gbm/GBM.java:1486-1513) then ModelMetrics{Regression,Binomial,Multinomial}.MetricBuilder.perRow — the squared-error and

@@ -268,6 +268,14 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
 /* GBM.AddTreeContributions (T/gbm/GBM.java:1410-1470): Tree_k <- (float)(Tree_k + pred[nid]); NIDs_k <- 0 / DECIDED_ROW. */
 int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred /*[n_nodes], leaf nids used*/);
 
+/* ---- scoring a frame with finished trees: SharedTreeMojoModel.scoreTree + scoreTreeRange's
+ * `preds[k] += tree value` (h2o-genmodel .../algos/tree/SharedTreeMojoModel.java:129-240, 1043-1076). Every row of the engine's frame
+ * walks the tree given to h2ot_set_tree from the root (nid 0) to a leaf (nid >= leaf_start, or a root that never split) with the
+ * DecidedNode.getChildNodeID rules, and Tree_k <- Tree_k + (double)node_pred[leaf] WITHOUT the per-tree float rounding of
+ * AddTreeContributions. An engine holding a validation / test frame (h2ot_init_model with 0, then one call per tree in build
+ * order, then + init_f as GbmMojoModel.score0 does) reproduces the model's link-space predictions on new rows. NIDs_k is untouched. */
+int h2ot_score_tree(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_nodes, const float* node_pred);
+
 /* ---- training metrics on the resident frame: hex.tree.Score (T/Score.java:57-141) for GBM. The link-space
  * predictions Tree_k (+ offset) are turned into class probabilities as score1/score2 do (T/gbm/GBM.java:1486-1513,
  * T/SharedTree.java:782-789) and fed to MetricBuilder.perRow (H/ModelMetricsBinomial.java, ModelMetricsMultinomial, ModelMetricsRegression):

@@ -80,6 +80,12 @@ int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k);
 int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out);
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out);
 int h2ot_gbm_oobt(h2ot_gbm* g, double* out); /* DRF: OUT_BAG_TREES column */
+/* Scores NEW rows with the trees built so far (SharedTreeMojoModel.scoreAllTrees, h2o-genmodel .../SharedTreeMojoModel.java:1043-1076):
+ * columns[c] -> nrows doubles (NaN == NA), same column order / categorical coding as the training frame. out[k * nrows + r] =
+ * sum over trees of tree_k(row r) in double, in build order, plus init_f for GBM (GbmMojoModel.score0 adds it after the sum); for DRF
+ * the plain sum of the trees' votes (DrfMojoModel.score0 divides by the number of trees). Runs on the model's device with a
+ * temporary engine (h2ot_score_tree); link-space, no probabilities. */
+int h2ot_gbm_predict(h2ot_gbm* g, int64_t nrows, const double* const* columns, double* out);
 /* Training metrics of the current GBM model over all ranks (h2ot_score_metrics + sum): out_mse, out_logloss nullable */
 int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss);
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out);

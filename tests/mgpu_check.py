@@ -41,7 +41,11 @@ def main():
     ok = True
     for case, kw in (("bernoulli+sampling", dict(distribution="bernoulli", ntrees=4, max_depth=5, nbins=20, sample_rate=0.7, col_sample_rate=0.8, seed=11)),
                      ("gaussian+weights", dict(distribution="gaussian", nclass=1, ntrees=3, max_depth=4, nbins=32, seed=5)),
-                     ("multinomial", dict(distribution="multinomial", nclass=3, ntrees=2, max_depth=4, nbins=20, seed=7))):
+                     ("multinomial", dict(distribution="multinomial", nclass=3, ntrees=2, max_depth=4, nbins=20, seed=7)),
+                     ("drf mtries+oob", dict(_cls="DRF", distribution="bernoulli", ntrees=3, max_depth=8, mtries=2, sample_rate=0.63, seed=9)),
+                     ("random histograms", dict(distribution="bernoulli", ntrees=3, max_depth=4, nbins=20, histogram_type="Random", seed=3))):
+        kw = dict(kw)
+        Model = getattr(P, kw.pop("_cls", "GBM"))
         n = 120001
         X, y, cats = h2ot_lib.make_frame(n=n, c=6, seed=3)
         w = None
@@ -53,7 +57,7 @@ def main():
             y = (np.argmax(np.nan_to_num(X[:, :3]), axis=1)).astype(np.float64)
             K = 3
         r0, r1 = (n * rank) // world, (n * (rank + 1)) // world
-        gm = P.GBM(device=local, **kw)
+        gm = Model(device=local, **kw)
         gm.load([X[r0:r1, c] for c in range(X.shape[1])], y[r0:r1], weights=None if w is None else w[r0:r1], categorical=cats,
                 row_offset=r0, nrows_global=n, comm=(world, rank, uid))
         gm.train()
@@ -64,7 +68,7 @@ def main():
         preds = [gm.predictions(k) for k in range(K)]
         single_ok = True
         if rank == 0:
-            g1 = P.GBM(device=local, **kw)
+            g1 = Model(device=local, **kw)
             g1.load([X[:, c] for c in range(X.shape[1])], y, weights=w, categorical=cats)
             g1.train()
             single_ok = tree_bytes(g1, K) == mine

@@ -313,23 +313,27 @@ def test_sampler_bit_exact():
         e.close()
 
 
-@pytest.mark.parametrize("weighted,check_float", [(False, False), (False, True), (True, True)])
-def test_sparse_level_kernels_agree(weighted, check_float):
+@pytest.mark.parametrize("weighted,check_float,wide", [(False, False, False), (False, True, False), (True, True, False), (False, False, True)])
+def test_sparse_level_kernels_agree(weighted, check_float, wide):
     """A level where every leaf histograms its own few columns (UndecidedNode.scoreCols, T/DTree.java:443-499; q8:
     T/ScoreBuildHistogram2.java:421-422): the leaf-major kernel (mode 0 picks it), the column-major shared-memory
     kernels (mode 2) and the L2-atomics kernel (mode 1) must give identical bits, and match updateHisto
     (T/DHistogram.java:609-658) per (leaf, column)."""
     rng = np.random.default_rng(11)
-    n, L, per_leaf = 260001, 150, 3
+    n, L, per_leaf = (60001, 150, 3) if wide else (260001, 150, 3)
     cols = [rng.normal(size=n).astype(np.float32).astype(np.float64) for _ in range(5)]
     cols += [rng.lognormal(size=n), rng.normal(size=n) * 1e-3 + 7.0]                       # f64 storage
     cols += [rng.integers(0, 9, n).astype(np.float64), rng.integers(-3, 200, n).astype(np.float64)]      # u8
     cols += [rng.integers(0, 5000, n).astype(np.float64), rng.integers(-900, 30000, n).astype(np.float64)]  # u16
     cols += [rng.choice([0.0, 1.09, 2.17], n).astype(np.float32).astype(np.float64)]
+    is_int = [0] * 7 + [1] * 4 + [0]
+    if wide:  # more than 512 columns: the kernel reads the column table from global memory instead of shared memory
+        for j in range(600):
+            cols.append(rng.integers(0, 50, n).astype(np.float64) if j % 2 else rng.normal(size=n).astype(np.float32).astype(np.float64))
+            is_int.append(1 if j % 2 else 0)
     X = np.stack(cols, axis=1)
     X[rng.random(X.shape) < 0.03] = NaN
     C_ = X.shape[1]
-    is_int = [0] * 7 + [1] * 4 + [0]
     work = (rng.random(n) - 0.5).astype(np.float32).astype(np.float64)
     w = rng.integers(0, 3, n).astype(np.float64) if weighted else None
     P, e = _engine(X, w=w)

@@ -312,3 +312,36 @@ def test_random_histogram_type_matches_oracle(with_cat):
     assert not np.array_equal(gm.predictions(), gu.predictions())
     gm.close()
     gu.close()
+
+
+@pytest.mark.parametrize("dist", ["bernoulli", "multinomial"])
+def test_predict_new_rows_matches_score_tree(dist):
+    """Scoring NEW rows (SharedTreeMojoModel.scoreTree / scoreAllTrees + GbmMojoModel.score0's `+ init_f`): the device walks every
+    finished tree root to leaf and sums the float leaf values in double, in build order -- bit for bit what the oracle's
+    scoreTree gives row by row, NAs and never-seen categorical levels included."""
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=91)
+    K = 1
+    if dist == "multinomial":
+        y = np.argmax(np.nan_to_num(X[:, :3]), axis=1).astype(np.float64)
+        K = 3
+    gm, om = _run_both(X, y, cats, capture=False, distribution=dist, nclass=3 if K == 3 else 2, ntrees=6, max_depth=5, nbins=20, seed=77)
+    rng = np.random.default_rng(92)
+    m = 3000
+    Xn = rng.normal(size=(m, 6)).astype(np.float32).astype(np.float64) * 1.5
+    Xn[:, 3] = rng.integers(-10, 60, m)
+    Xn[:, 4] = rng.integers(0, 20, m)          # levels 12..19 were never seen in training
+    Xn[rng.random((m, 6)) < 0.05] = NaN
+    got = gm.predict([Xn[:, c] for c in range(6)])
+    assert got.shape == (K, m)
+    want = np.zeros((K, m))
+    for r in range(m):
+        for k in range(K):
+            s = 0.0
+            for t in range(om.ntrees):
+                s += float(om.score_tree(t, k, Xn[r]))
+            want[k, r] = s + (om.init_f if K == 1 else 0.0)
+    assert np.array_equal(got, want), int(np.sum(got != want))
+    # on the training rows themselves the sum differs from Tree_k only by the per-tree float rounding of AddTreeContributions
+    tr = gm.predict([X[:, c] for c in range(6)])
+    assert np.max(np.abs(tr[0] - gm.predictions(0))) < 1e-5
+    gm.close()
