@@ -248,6 +248,16 @@ struct Tree {
     }
     return n.nid;
   }
+  // an UndecidedNode whose histograms nobody will read (children made by the last level of the tree: they turn into leaves)
+  int new_undecided_stub(int pid) {
+    if (ns.capacity() == ns.size()) ns.reserve(std::max<size_t>(1024, ns.size() * 4));
+    ns.emplace_back();
+    Node& n = ns.back();
+    n.kind = 0;
+    n.pid = pid;
+    n.nid = len() - 1;
+    return n.nid;
+  }
   void do_not_split(int nid) {  // :504-511
     const int pid = ns[nid].pid;
     if (pid == kNoParent) return;
@@ -347,13 +357,16 @@ std::vector<Hist> initial_hist(const h2ot_gbm* g, int nbins, int64_t seed, bool 
 }
 
 // Split.nextLevelHistos (T/DTree.java:312-417; no constraints). Empty result == Java null.
-std::vector<Hist> next_level_histos(const h2ot_gbm* g, const h2ot_split& s, const std::vector<Hist>& cur, int way, double splat) {
+// any_only: stop at the first column that gets a histogram and return a one-element vector (the caller only asks whether the child
+// exists -- the last level of a tree, whose children become leaves whatever their histograms would have been).
+std::vector<Hist> next_level_histos(const h2ot_gbm* g, const h2ot_split& s, const std::vector<Hist>& cur, int way, double splat,
+                                    bool any_only = false) {
   const double n = way == 0 ? s.n0 : s.n1;
   if (n < g->p.min_rows) return {};
   const double se = way == 0 ? s.se0 : s.se1;
   if (se <= 1e-30) return {};
   int cnt = 0;
-  std::vector<Hist> nh(cur.size());
+  std::vector<Hist> nh(any_only ? 1 : cur.size());
   for (size_t j = 0; j < cur.size(); j++) {
     const Hist& h = cur[j];
     if (!h.present) continue;
@@ -390,6 +403,10 @@ std::vector<Hist> next_level_histos(const h2ot_gbm* g, const h2ot_split& s, cons
     if (!make_hist(c, adj_nbins, g->p.nbins_cats, h.is_int, min, max_ex, h.int_opt, has_nas,
                    (int64_t)((uint64_t)h.seed * 0xDECAFULL + (uint64_t)(way + 1)), h.check_float))
       continue;
+    if (any_only) {
+      nh[0] = c;
+      return nh;
+    }
     nh[j] = c;
     cnt++;
   }
@@ -418,7 +435,10 @@ void to_device_node(const Node& n, h2ot_decided_node& d, std::vector<uint8_t>& p
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 // One ScoreBuildHistogram2 pass + ScoreBuildOneTree.onCompletion for class-tree k (T/SharedTree.java:661-710).
-int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_split) {
+// last_level: the tree stops after this level (depth == max_depth - 1), so the children only need to exist with the right node
+// ids; their histograms and column draws (tree._rand is not used again) are skipped -- the widest level of a deep tree otherwise
+// spends more host time describing children nobody splits than the GPU spends on the level.
+int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_split, bool last_level = false) {
   did_split = false;
   const int C = g->ncols;
   const int tmax = tree.len();
@@ -542,7 +562,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     }
     const h2ot_split& s = g->splits[l];
     if (s.col < 0 || hs.empty()) continue;
-    for (int way = 0; way < 2; way++) kd.nh[way] = next_level_histos(g, s, hs, way, (double)s.splat);
+    for (int way = 0; way < 2; way++) kd.nh[way] = next_level_histos(g, s, hs, way, (double)s.splat, last_level);
   }
   const double t_kids_done = now_s();
   for (int l = 0; l < L; l++) {
@@ -567,7 +587,8 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     did_split = true;
     g->varimp[s.col] += (float)(s.se - (s.se0 + s.se1));  // T/SharedTree.java:697-700
     for (int way = 0; way < 2; way++) {
-      const int child = kd.nh[way].empty() ? kUndecidedChild : tree.new_undecided(nid, std::move(kd.nh[way]));
+      const int child = kd.nh[way].empty() ? kUndecidedChild
+                                           : (last_level ? tree.new_undecided_stub(nid) : tree.new_undecided(nid, std::move(kd.nh[way])));
       tree.ns[nid].nids[way] = child;
     }
   }
@@ -606,7 +627,7 @@ int build_next_k_trees(h2ot_gbm* g) {
     bool any = false;
     for (int k = 0; k < K; k++) {
       bool did = false;
-      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did));
+      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, depth == g->p.max_depth - 1));
       any = any || did;
     }
     if (!any) break;
@@ -704,7 +725,7 @@ int build_next_k_trees_drf(h2ot_gbm* g) {
     bool any = false;
     for (int k = 0; k < K; k++) {
       bool did = false;
-      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did));
+      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, depth == g->p.max_depth - 1));
       any = any || did;
     }
     if (!any) break;
