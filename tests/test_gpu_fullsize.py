@@ -90,3 +90,29 @@ def test_full_size_root_level_kernel_variants_agree():
         blk = v[res[0]["offsets"][j]: res[0]["offsets"][j] + 1025 * 3]
         assert abs(blk[1::3].sum() - tot) <= 1e-6 * float(np.sum(np.abs(work)))
     e.close()
+
+
+def test_full_size_drf_sparse_and_column_major_kernels_grow_the_same_trees():
+    """BASELINE configs[2] shape (DRF, 11M x 28, mtries 5, sample 0.63; depth 9 here): the leaf-major kernel (default) and the
+    column-major kernels (hist mode 2) must grow bit-identical trees and out-of-bag votes, and the default build must have
+    used the leaf-major kernel on the levels below the root."""
+    import importlib
+    bench = importlib.import_module("bench")
+    P = h2ot_lib.pkg()
+    N = 11_000_000
+    cols, y, _ = bench.make_frame(N, 0, N, pinned=False)
+    sig, sparse = [], []
+    for mode in (0, 2):
+        gm = P.DRF(distribution="bernoulli", ntrees=2, max_depth=9, mtries=5, sample_rate=0.63, min_rows=1.0, nbins=20, seed=1234)
+        gm.load(cols, y)
+        eng = gm.engine()
+        eng.set_hist_mode(mode)
+        eng.stats_reset()
+        gm.train()
+        sparse.append(eng.stats().sparse_launches)
+        nodes = [gm.tree(t)[0] for t in range(gm.ntrees)]
+        sig.append((gm.predictions().tobytes(), gm.oobt().tobytes(), [len(n) for n in nodes],
+                    [[(x.col, x.bin, x.nasplit, x.nid0, x.nid1, np.float32(x.splat).tobytes(), np.float32(x.pred).tobytes()) for x in n] for n in nodes]))
+        gm.close()
+    assert sparse[0] >= 2 * 7 and sparse[1] == 0, sparse
+    assert sig[0] == sig[1]
