@@ -1247,7 +1247,10 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   for (int c = 0; c < C; c++) {
     if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
     const double excess = 8.0 * h->col_conc[c] / (double)L;
-    int rep = excess >= 1.0 ? 4 : (excess >= 0.4 ? 2 : 1);
+    int rep = 1;
+    while (rep < 32 && excess / rep >= 0.4) rep <<= 1;
+    // more than 4 copies only for tiny histograms (binary / few-valued columns: one copy per lane costs a few hundred bytes)
+    while (rep > 4 && (size_t)col_words[c] * rep * 4 > 16384) rep >>= 1;
     while (rep > 1 && (size_t)col_words[c] * rep * 4 + fixed_bytes(1, h->cols[c].storage) > budget / 2) rep >>= 1;
     col_rep[c] = rep;
     col_words[c] *= rep;
@@ -1370,7 +1373,8 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       cta += slices[gi];
       int off = 0;
       for (int c : g) {
-        const int lg = col_rep[c] == 4 ? 2 : (col_rep[c] == 2 ? 1 : 0);
+        int lg = 0;
+        while ((1 << lg) < col_rep[c]) lg++;
         t.h_group_cols.push_back(c | (lg << 24));
         for (int l = granges[gi].first; l < granges[gi].first + granges[gi].second; l++) {
           DescDev& d = t.h_descs[(size_t)l * C + c];

@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY (see oracle/README.md): CPU restatement of H2O's numeric chunk codecs -- the byte layouts that
+// TEST INFRASTRUCTURE ONLY: CPU restatement of H2O's numeric chunk codecs -- the byte layouts that
 // NewChunk.compress writes and the values Chunk.atd_impl reads back. Nothing under h2o-3_b200/ may include this file.
 // Pinned by the reference's own unit-test vectors (tests/test_oracle_chunks.py: C1ChunkTest, C2ChunkTest, C4ChunkTest,
 // C1SChunkTest.test_inflate_impl / test_precision, C2SChunkTest, C4SChunkTest, CBSChunkTest): the encoders below restate the
