@@ -83,6 +83,10 @@ struct TreeState {  // per class-tree k
   int bucket_begin[4] = {0, 0, 0, 0}, bucket_end[4] = {0, 0, 0, 0};  // smem groups per storage type
   int bucket_ctas[4] = {0, 0, 0, 0};                                  // CTAs of each storage type's launch
   int n_smem_groups = 0;
+  unsigned char* stage = nullptr;  // pinned host staging of this class-tree's level results (h2ot_level_step[_begin/_end])
+  size_t stage_cap = 0;
+  cudaEvent_t done_ev = nullptr;   // recorded after the results' download was enqueued
+  bool step_pending = false;
   std::vector<double> h_sp;  // split points of the next level (h2ot_set_split_points), -0.0 canonicalised
   DBuf<double> d_sp;
   bool sp_dirty = false, any_splitpts = false;
@@ -173,9 +177,8 @@ struct h2ot_engine {
   std::vector<Timer> timers;
   std::vector<cudaEvent_t> event_pool;
   bool defer_sync = false;
-  unsigned char* stage = nullptr;  // pinned host staging of h2ot_level_step
   std::vector<double> col_conc;    // per column: chance that two rows of the root share a bin (0 until a root level ran)
-  size_t stage_cap = 0;
+  int steps_pending = 0;  // h2ot_level_step_begin calls not yet ended
   int hist_mode = 0;
   int smem_budget_kb = 0;  // 0: automatic
   Nccl nccl;
@@ -416,13 +419,14 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.code) cudaFree(t.code);
     t.nodes.release(); t.bitsets.release(); t.d_lvl.release();
     if (t.lvl_host) cudaFreeHost(t.lvl_host);
+    if (t.stage) cudaFreeHost(t.stage);
+    if (t.done_ev) cudaEventDestroy(t.done_ev);
     t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_sp.release();
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
   h->d_rollup.release(); h->d_cols.release();
   for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
-  if (h->stage) cudaFreeHost(h->stage);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return H2OT_OK;
@@ -1736,11 +1740,12 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   return finish_call(h);
 }
 
-int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
-                    const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes, const h2ot_hist_desc* descs,
-                    double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
-                    uint8_t* out_has_vals, h2ot_split* out_splits) {
+int h2ot_level_step_begin(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                          const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
+                          const h2ot_hist_desc* descs, double min_rows, double min_split_improvement) {
   CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (h->ts[k].step_pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_level_step_begin: the previous step of this class-tree was not ended");
   static const bool trace = getenv("H2OT_TRACE") != nullptr;
   auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double tr0 = trace ? now() : 0;
@@ -1751,30 +1756,62 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
   if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
   if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
   TreeState& t = h->ts[k];
-  if (rc == H2OT_OK && t.pack_bytes > h->stage_cap) {  // pinned staging for the packed results (grow-only)
-    if (h->stage) cudaFreeHost(h->stage);
-    h->stage = nullptr;
-    h->stage_cap = 0;
+  if (rc == H2OT_OK && t.pack_bytes > t.stage_cap) {  // pinned staging for the packed results (grow-only)
+    if (t.stage) {  // (a download of an earlier step into it has been waited for by that step's _end)
+      cudaFreeHost(t.stage);
+    }
+    t.stage = nullptr;
+    t.stage_cap = 0;
     const size_t want = std::max<size_t>(t.pack_bytes * 2, 1 << 20);
-    if (cudaMallocHost(&h->stage, want) != cudaSuccess) {
+    if (cudaMallocHost(&t.stage, want) != cudaSuccess) {
       set_error("cudaMallocHost failed for the level result staging buffer");
       rc = H2OT_ERR_NOMEM;
     } else {
-      h->stage_cap = want;
+      t.stage_cap = want;
     }
   }
-  if (rc == H2OT_OK) rc = d2h(h, h->stage, t.d_pack.p, t.pack_bytes);
-  h->defer_sync = false;
-  const double tr2 = trace ? now() : 0;
-  const int rs = finish_call(h);  // also drains the stream after a failed stage
-  if (trace) {
-    const double tr3 = now();
-    fprintf(stderr, "[h2ot] level L=%d: enqueue build %.3f ms, enqueue rest %.3f ms, wait %.3f ms\n", n_leaves, tr1 - tr0, tr2 - tr1, tr3 - tr2);
+  if (rc == H2OT_OK) rc = d2h(h, t.stage, t.d_pack.p, t.pack_bytes);
+  if (rc == H2OT_OK && !t.done_ev && cudaEventCreateWithFlags(&t.done_ev, cudaEventDisableTiming) != cudaSuccess) {
+    set_error("cudaEventCreate failed");
+    rc = H2OT_ERR_CUDA;
   }
-  if (rc != H2OT_OK) return rc;
+  if (rc == H2OT_OK && cudaEventRecord(t.done_ev, h->stream) != cudaSuccess) {
+    set_error("cudaEventRecord failed");
+    rc = H2OT_ERR_CUDA;
+  }
+  h->defer_sync = false;
+  if (trace) fprintf(stderr, "[h2ot] level L=%d k=%d: enqueue build %.3f ms, enqueue rest %.3f ms\n", n_leaves, k, tr1 - tr0, now() - tr1);
+  if (rc != H2OT_OK) {
+    if (h->steps_pending == 0) finish_call(h);  // drain the stream after a failed stage
+    return rc;
+  }
+  t.step_pending = true;
+  h->steps_pending++;
+  return H2OT_OK;
+}
+
+int h2ot_level_step_end(h2ot_engine* h, int32_t k, double* out_min2, double* out_maxIn, double* out_wNA, uint8_t* out_has_vals,
+                        h2ot_split* out_splits) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  if (!t.step_pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_level_step_end without h2ot_level_step_begin");
+  t.step_pending = false;
+  h->steps_pending--;
+  int rs = H2OT_OK;
+  if (h->steps_pending == 0) {
+    rs = finish_call(h);  // the last pending step: drain the stream, fold the kernel timers, check the exchange
+  } else if (cudaEventSynchronize(t.done_ev) != cudaSuccess) {  // other class-trees' levels keep running behind this one
+    set_error("cudaEventSynchronize failed waiting for a level");
+    rs = H2OT_ERR_CUDA;
+  }
+  if (rs == H2OT_OK && h->xr_err_host && *h->xr_err_host) {
+    set_error("peer-memory exchange timed out waiting for another rank");
+    rs = H2OT_ERR_COMM;
+  }
   if (rs != H2OT_OK) return rs;
   const size_t LC = (size_t)t.L * h->C;
-  const unsigned char* sp = h->stage;
+  const unsigned char* sp = t.stage;
   if (out_min2) memcpy(out_min2, sp, LC * sizeof(double));
   if (out_maxIn) memcpy(out_maxIn, sp + LC * sizeof(double), LC * sizeof(double));
   if (out_wNA) memcpy(out_wNA, sp + 2 * LC * sizeof(double), LC * sizeof(double));
@@ -1797,6 +1834,15 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
       if (t.h_descs[c].nbin >= 0) h->col_conc[c] = conc[c];
   }
   return H2OT_OK;
+}
+
+int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                    const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes, const h2ot_hist_desc* descs,
+                    double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
+                    uint8_t* out_has_vals, h2ot_split* out_splits) {
+  TRY(h2ot_level_step_begin(h, k, leaf_offset, n_leaves, n_decided, decided, bitset_pool, bitset_bytes, descs, min_rows,
+                            min_split_improvement));
+  return h2ot_level_step_end(h, k, out_min2, out_maxIn, out_wNA, out_has_vals, out_splits);
 }
 
 // ------------------------------------------------------------------------------------------------ end of tree

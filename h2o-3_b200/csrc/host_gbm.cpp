@@ -318,11 +318,17 @@ struct h2ot_gbm {
   std::vector<Capture> captures;
   h2ot_gbm_timing timing{};
   // scratch
-  std::vector<h2ot_hist_desc> descs;
-  std::vector<double> split_pts;  // histogram_type Random: the level's split points
-  std::vector<double> min2, max_in, w_na;
-  std::vector<uint8_t> has;
-  std::vector<h2ot_split> splits;
+  // per class-tree scratch of the level in flight (the K levels of a multinomial iteration are enqueued side by side)
+  struct LevelScratch {
+    std::vector<h2ot_hist_desc> descs;
+    std::vector<double> split_pts;  // histogram_type Random: the level's split points
+    std::vector<double> min2, max_in, w_na;
+    std::vector<uint8_t> has;
+    std::vector<h2ot_split> splits;
+    std::vector<char> col_active;
+    double t0 = 0, t_descs_done = 0;
+  };
+  std::vector<LevelScratch> scr;
 };
 
 namespace {
@@ -438,18 +444,24 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 // last_level: the tree stops after this level (depth == max_depth - 1), so the children only need to exist with the right node
 // ids; their histograms and column draws (tree._rand is not used again) are skipped -- the widest level of a deep tree otherwise
 // spends more host time describing children nobody splits than the GPU spends on the level.
-int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_split, bool last_level = false) {
+// phase 0: the whole level; 1: descriptors + enqueue only (h2ot_level_step_begin); 2: wait for the results + onCompletion.
+int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_split, bool last_level = false, int phase = 0) {
+  if ((int)g->scr.size() < g->K) g->scr.resize((size_t)g->K);
+  h2ot_gbm::LevelScratch& sc = g->scr[(size_t)k];
   did_split = false;
   const int C = g->ncols;
   const int tmax = tree.len();
   const int L = tmax - leaf_offset;
   if (L <= 0) return H2OT_OK;
-  const double t0 = now_s();
+  const size_t LC = (size_t)L * C;
+  std::vector<char>& col_active = sc.col_active;
+  if (phase != 2) {
+  sc.t0 = now_s();
   // descriptors of the undecided leaves
-  g->descs.assign((size_t)L * C, h2ot_hist_desc{});
-  g->split_pts.clear();
+  sc.descs.assign((size_t)L * C, h2ot_hist_desc{});
+  sc.split_pts.clear();
   int64_t active_pairs = 0;
-  std::vector<char> col_active(C, 0);
+  col_active.assign(C, 0);
   for (int l = 0; l < L; l++) {
     const Node& u = tree.ns[leaf_offset + l];
     std::vector<int16_t> order(C, -1);
@@ -458,7 +470,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     else
       for (size_t i = 0; i < u.score_cols.size(); i++) order[u.score_cols[i]] = (int16_t)i;
     for (int c = 0; c < C; c++) {
-      h2ot_hist_desc& d = g->descs[(size_t)l * C + c];
+      h2ot_hist_desc& d = sc.descs[(size_t)l * C + c];
       if (u.hs.empty() || !u.hs[c].present || order[c] < 0) continue;
       const Hist& h = u.hs[c];
       d.min = h.min;
@@ -473,9 +485,9 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
         int64_t bits;
         memcpy(&bits, &sd, sizeof bits);
         Pcg rng((int64_t)((uint64_t)bits + 0xDECAFULL * (uint64_t)h.nbin + 0xC0FFEEULL * (uint64_t)h.is_int + (uint64_t)h.seed));
-        const size_t off = g->split_pts.size();
-        g->split_pts.resize(off + (size_t)h.nbin);
-        double* pts = g->split_pts.data() + off;
+        const size_t off = sc.split_pts.size();
+        sc.split_pts.resize(off + (size_t)h.nbin);
+        double* pts = sc.split_pts.data() + off;
         pts[0] = 0;
         for (int i = 1; i < h.nbin; i++) pts[i] = (double)(rng.next_float() * (float)h.nbin);
         std::sort(pts, pts + h.nbin);
@@ -487,8 +499,8 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
       col_active[c] = 1;
     }
   }
-  if (g->p.histogram_type == 1) GTRY(h2ot_set_split_points(g->eng, k, g->split_pts.data(), (int64_t)g->split_pts.size()));
-  const double t_descs_done = now_s();
+  if (g->p.histogram_type == 1) GTRY(h2ot_set_split_points(g->eng, k, sc.split_pts.data(), (int64_t)sc.split_pts.size()));
+  sc.t_descs_done = now_s();
   // decided nodes the device does not have yet
   std::vector<h2ot_decided_node> dn;
   std::vector<uint8_t> pool;
@@ -499,40 +511,43 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     to_device_node(tree.ns[nid], dn.back(), pool);
   }
   tree.dirty.clear();
-  const size_t LC = (size_t)L * C;
-  g->min2.resize(LC);
-  g->max_in.resize(LC);
-  g->w_na.resize(LC);
-  g->has.resize(LC);
-  g->splits.resize(L);
+  sc.min2.resize(LC);
+  sc.max_in.resize(LC);
+  sc.w_na.resize(LC);
+  sc.has.resize(LC);
+  sc.splits.resize(L);
   if (g->capture) {
-    GTRY(h2ot_build_level(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data()));
+    GTRY(h2ot_build_level(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), sc.descs.data()));
     if (g->world > 1) GTRY(h2ot_allreduce_level(g->eng, k));
     Capture cap;
     cap.tree = g->ntrees_built;
     cap.k = k;
     cap.leaf = leaf_offset;
     cap.nleaves = L;
-    cap.descs = g->descs;
+    cap.descs = sc.descs;
     int64_t nvals = 0;
-    for (const h2ot_hist_desc& d : g->descs)
+    for (const h2ot_hist_desc& d : sc.descs)
       if (d.flags & H2OT_DESC_ACTIVE) nvals += (int64_t)(d.nbin + 1) * 3;
     cap.vals.resize((size_t)std::max<int64_t>(1, nvals));
     cap.offs.resize(LC);
-    GTRY(h2ot_finish_level(g->eng, k, cap.vals.data(), (int64_t)cap.vals.size(), cap.offs.data(), g->min2.data(), g->max_in.data(),
-                           g->w_na.data(), g->has.data()));
-    cap.min2 = g->min2;
-    cap.max_in = g->max_in;
-    cap.has = g->has;
+    GTRY(h2ot_finish_level(g->eng, k, cap.vals.data(), (int64_t)cap.vals.size(), cap.offs.data(), sc.min2.data(), sc.max_in.data(),
+                           sc.w_na.data(), sc.has.data()));
+    cap.min2 = sc.min2;
+    cap.max_in = sc.max_in;
+    cap.has = sc.has;
     cap.nids.resize((size_t)g->nrows);
     GTRY(h2ot_get_nids(g->eng, k, cap.nids.data()));
     g->captures.push_back(std::move(cap));
-    GTRY(h2ot_find_splits(g->eng, k, g->p.min_rows, g->p.min_split_improvement, g->splits.data()));
+    GTRY(h2ot_find_splits(g->eng, k, g->p.min_rows, g->p.min_split_improvement, sc.splits.data()));
   } else {
-    GTRY(h2ot_level_step(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), g->descs.data(),
-                         g->p.min_rows, g->p.min_split_improvement, g->min2.data(), g->max_in.data(), g->w_na.data(), g->has.data(),
-                         g->splits.data()));
+    GTRY(h2ot_level_step_begin(g->eng, k, leaf_offset, L, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size(), sc.descs.data(),
+                               g->p.min_rows, g->p.min_split_improvement));
+    if (phase == 1) return H2OT_OK;
   }
+  }  // phase != 2
+  if (!g->capture)
+    GTRY(h2ot_level_step_end(g->eng, k, sc.min2.data(), sc.max_in.data(), sc.w_na.data(), sc.has.data(), sc.splits.data()));
+  const double t0 = sc.t0, t_descs_done = sc.t_descs_done;
   const double t_call_end = now_s();
   g->timing.level_s += t_call_end - t0;
   g->timing.levels++;
@@ -554,13 +569,13 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     for (int c = 0; c < C && !hs.empty(); c++) {
       Hist& h = hs[c];
       const size_t i = (size_t)l * C + c;
-      if (!h.present || !(g->descs[i].flags & H2OT_DESC_ACTIVE)) continue;
-      h.has_vals = g->has[i] != 0;
-      h.min2 = g->min2[i];
-      h.max_in = g->max_in[i];
-      h.w_na = g->w_na[i];
+      if (!h.present || !(sc.descs[i].flags & H2OT_DESC_ACTIVE)) continue;
+      h.has_vals = sc.has[i] != 0;
+      h.min2 = sc.min2[i];
+      h.max_in = sc.max_in[i];
+      h.w_na = sc.w_na[i];
     }
-    const h2ot_split& s = g->splits[l];
+    const h2ot_split& s = sc.splits[l];
     if (s.col < 0 || hs.empty()) continue;
     for (int way = 0; way < 2; way++) kd.nh[way] = next_level_histos(g, s, hs, way, (double)s.splat, last_level);
   }
@@ -572,7 +587,7 @@ int build_layer_k(h2ot_gbm* g, int k, Tree& tree, int& leaf_offset, bool& did_sp
     dnode.kind = 1;
     dnode.hs.clear();
     dnode.score_cols.clear();
-    const h2ot_split& s = g->splits[l];
+    const h2ot_split& s = sc.splits[l];
     tree.dirty.push_back(nid);
     if (s.col < 0 || kd.hs.empty()) {
       dnode.has_split = false;
@@ -625,10 +640,23 @@ int build_next_k_trees(h2ot_gbm* g) {
   }
   for (int depth = 0; depth < g->p.max_depth; depth++) {
     bool any = false;
-    for (int k = 0; k < K; k++) {
+    const bool last = depth == g->p.max_depth - 1;
+    if (K > 1 && !g->capture) {
+      // the K class-trees' levels are enqueued back to back; while the host turns tree k's splits into its next level the
+      // device works on the levels of the trees behind it
       bool did = false;
-      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, depth == g->p.max_depth - 1));
-      any = any || did;
+      for (int k = 0; k < K; k++) GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last, 1));
+      for (int k = 0; k < K; k++) {
+        did = false;
+        GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last, 2));
+        any = any || did;
+      }
+    } else {
+      for (int k = 0; k < K; k++) {
+        bool did = false;
+        GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last));
+        any = any || did;
+      }
     }
     if (!any) break;
   }
@@ -723,10 +751,23 @@ int build_next_k_trees_drf(h2ot_gbm* g) {
   }
   for (int depth = 0; depth < g->p.max_depth; depth++) {
     bool any = false;
-    for (int k = 0; k < K; k++) {
+    const bool last = depth == g->p.max_depth - 1;
+    if (K > 1 && !g->capture) {
+      // the K class-trees' levels are enqueued back to back; while the host turns tree k's splits into its next level the
+      // device works on the levels of the trees behind it
       bool did = false;
-      GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, depth == g->p.max_depth - 1));
-      any = any || did;
+      for (int k = 0; k < K; k++) GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last, 1));
+      for (int k = 0; k < K; k++) {
+        did = false;
+        GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last, 2));
+        any = any || did;
+      }
+    } else {
+      for (int k = 0; k < K; k++) {
+        bool did = false;
+        GTRY(build_layer_k(g, k, *kt[k], leaves[k], did, last));
+        any = any || did;
+      }
     }
     if (!any) break;
   }

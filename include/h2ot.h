@@ -257,6 +257,17 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
                     double min_rows, double min_split_improvement, double* out_min2, double* out_maxIn, double* out_wNA,
                     uint8_t* out_has_vals, h2ot_split* out_splits);
 
+/* The same level in two halves, for callers that build the K class-trees of a multinomial iteration side by side: _begin
+ * enqueues the whole level of class-tree k and returns without waiting (its inputs have been copied); _end waits for THAT level's
+ * results only, so the levels of the other class-trees keep the device busy while the host turns these splits into the next
+ * level's descriptors. One _begin per class-tree may be outstanding; no other call on the handle between a _begin and its _end
+ * except _begin / _end of other class-trees. */
+int h2ot_level_step_begin(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
+                          const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
+                          const h2ot_hist_desc* descs, double min_rows, double min_split_improvement);
+int h2ot_level_step_end(h2ot_engine* h, int32_t k, double* out_min2, double* out_maxIn, double* out_wNA, uint8_t* out_has_vals,
+                        h2ot_split* out_splits);
+
 /* ---- end of tree */
 /* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */
 int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,
