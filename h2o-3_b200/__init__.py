@@ -579,8 +579,11 @@ class GBM:
         _check(self.L.h2ot_gbm_tree_nodes(self.g, t, k, C.cast(out, C.c_void_p)))
         return out, self.L.h2ot_gbm_tree_leaves_start(self.g, t, k)
 
-    def predictions(self, k=0):
-        out = np.empty(self.nrows, dtype=np.float64)
+    def predictions(self, k=0, out=None):
+        """Tree_k column (link space). out: optional float64[nrows] buffer to fill (e.g. pinned host memory)."""
+        if out is None:
+            out = np.empty(self.nrows, dtype=np.float64)
+        assert out.dtype == np.float64 and out.size == self.nrows and out.flags["C_CONTIGUOUS"]
         _check(self.L.h2ot_gbm_predictions(self.g, k, _p(out)))
         return out
 
