@@ -168,6 +168,8 @@ def load():
     L.h2ot_finish_level.argtypes = [vp, i32, vp, i64, vp, vp, vp, vp, vp]
     L.h2ot_find_splits.argtypes = [vp, i32, dbl, dbl, vp]
     L.h2ot_level_step.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp, dbl, dbl, vp, vp, vp, vp, vp]
+    L.h2ot_level_step_begin.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp, dbl, dbl]
+    L.h2ot_level_step_end.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
     L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
     L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]

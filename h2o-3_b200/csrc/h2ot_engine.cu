@@ -35,11 +35,7 @@ struct DBuf {  // grow-only device buffer
     if (p) CUDA_TRY(cudaFree(p));
     p = nullptr;
     cap = 0;
-    // per-level buffers double from level to level: head room (4x up to 16 MB, 2x up to 256 MB, 1.25x beyond) and a 1 MB floor keep the first tree of a
-    // build from paying a cudaFree + cudaMalloc (each an implicit device synchronisation) per buffer and level
-    const size_t bytes = n * sizeof(T);
-    size_t want = bytes > ((size_t)256 << 20) ? n + n / 4 : (bytes > ((size_t)16 << 20) ? n * 2 : std::max<size_t>(n * 4, ((size_t)1 << 20) / sizeof(T)));
-    want = std::max<size_t>(want, 16);
+    size_t want = std::max<size_t>(n, 16);
     CUDA_TRY(cudaMalloc(&p, want * sizeof(T)));
     cap = want;
     return H2OT_OK;
@@ -1501,9 +1497,8 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
       if (t.lvl_host) cudaFreeHost(t.lvl_host);
       t.lvl_host = nullptr;
       t.lvl_host_cap = 0;
-      const size_t want = std::max<size_t>(total * 4, (size_t)1 << 20);  // pinned allocations are slow: few, generous ones
-      CUDA_TRY(cudaMallocHost(&t.lvl_host, want));
-      t.lvl_host_cap = want;
+      CUDA_TRY(cudaMallocHost(&t.lvl_host, total * 2));
+      t.lvl_host_cap = total * 2;
     }
     for (size_t i = 0; i < LC; i++) t.h_descs[i].pad = (uint32_t)(uint16_t)descs[i].order;  // bestCol tie order
     memcpy(t.lvl_host, t.h_descs.data(), b_descs);
@@ -1767,7 +1762,7 @@ int h2ot_level_step_begin(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_
     }
     t.stage = nullptr;
     t.stage_cap = 0;
-    const size_t want = std::max<size_t>(t.pack_bytes * 4, 1 << 20);
+    const size_t want = std::max<size_t>(t.pack_bytes * 2, 1 << 20);
     if (cudaMallocHost(&t.stage, want) != cudaSuccess) {
       set_error("cudaMallocHost failed for the level result staging buffer");
       rc = H2OT_ERR_NOMEM;

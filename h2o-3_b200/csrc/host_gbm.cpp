@@ -401,7 +401,10 @@ std::vector<Hist> next_level_histos(const h2ot_gbm* g, const h2ot_split& s, cons
     }
     if (min > max_ex) continue;
     if (within_one_small_ulp(min, max_ex)) continue;
-    if (std::isinf(adj_nbins / (max_ex - min))) continue;
+    {  // Double.isInfinite(adj_nbins / (maxEx - min)): only a denormal-sized range can overflow the quotient -- no division otherwise
+      const double range = max_ex - min;
+      if (range < 1e-280 && std::isinf(adj_nbins / range)) continue;
+    }
     if (h.is_int > 0 && !(min + 1 < max_ex)) continue;
     const bool has_nas = ((s.nasplit == H2OT_NA_LEFT && way == 0) || (s.nasplit == H2OT_NA_RIGHT && way == 1)) && h.has_na_bin();
     Hist c;

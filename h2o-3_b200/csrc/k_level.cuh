@@ -221,6 +221,9 @@ __device__ __forceinline__ int bin_checkfloat_fast(double x, double mn, double s
   const double pos = __dmul_rn(__dsub_rn(x, mn), step);
   const int idx = __double2int_rz(pos);
   if (idx >= nbin - 1) return nbin - 1;
+  // x == min exactly (every row holding the node's smallest value of a few-valued column): bin 0 cannot be left downwards, and
+  // upwards only if float(min + 1/step) <= min, i.e. a bin narrower than half a float ulp of min
+  if (pos == 0.0 && step * fabs(mn) < 4194304.0 && step < 1e37) return 0;
   const double frac = pos - (double)idx;
   const double g = 2.384185791015625e-07 * (fabs(mn) * step + (double)nbin);  // 2^-22
   if (frac > g && frac < 1.0 - g) return idx;

@@ -158,3 +158,49 @@ def test_error_codes_and_messages():
     e.close()
     with pytest.raises(P.H2OTError):
         P.GBM(distribution="bernoulli", nbins_cats=100000).load([np.zeros(10)], np.zeros(10))
+
+
+def test_two_half_level_step_protocol():
+    """h2ot_level_step_begin / _end: one outstanding begin per class-tree, end only after begin; two class-trees side by side give
+    what the one-call level step gives."""
+    P = h2ot_lib.pkg()
+    L = P.load()
+    rng = np.random.default_rng(8)
+    n = 5000
+    X = rng.normal(size=(n, 2)).astype(np.float32).astype(np.float64)
+    e = P.Engine(nrows=n, ncols=2, nclass_trees=2, nclass=3, family="multinomial")
+    for c in range(2):
+        e.load_column(c, X[:, c])
+    e.load_response(rng.integers(0, 3, n).astype(np.float64))
+    e.finalize_frame()
+    e.init_model([0.0, 0.0])
+    for k in range(2):
+        e.set_work(rng.normal(size=n).astype(np.float32).astype(np.float64), k=k)
+        e.begin_tree(k, 0, 1.0, 5.0)
+    descs = (P.HistDesc * 2)()
+    descs[0] = P.make_desc(-6.0, 6.0, 32, init_na=True, order=0)
+    descs[1] = P.make_desc(-6.0, 6.0, 16, init_na=True, order=1)
+    LC = 2
+
+    def end(k):
+        m2, mi, wn = np.zeros(LC), np.zeros(LC), np.zeros(LC)
+        hv = np.zeros(LC, dtype=np.uint8)
+        sp = (P.Split * 1)()
+        rc = L.h2ot_level_step_end(e.h, k, m2.ctypes.data, mi.ctypes.data, wn.ctypes.data, hv.ctypes.data, C.cast(sp, C.c_void_p))
+        return rc, (m2.tobytes(), mi.tobytes(), wn.tobytes(), hv.tobytes(), bytes(sp))
+
+    def begin(k):
+        return L.h2ot_level_step_begin(e.h, k, 0, 1, 0, None, None, 0, C.cast(descs, C.c_void_p), 1.0, 1e-5)
+
+    assert end(0)[0] == -1                      # nothing begun
+    assert begin(0) == 0 and begin(0) == -1     # second begin of the same class-tree
+    assert begin(1) == 0
+    r0, a0 = end(0)
+    r1, a1 = end(1)
+    assert r0 == 0 and r1 == 0 and end(1)[0] == -1
+    assert a0 != a1                             # different work columns
+    for k, want in ((0, a0), (1, a1)):          # again, one tree at a time: the same bytes
+        assert begin(k) == 0
+        rc, got = end(k)
+        assert rc == 0 and got == want
+    e.close()
