@@ -300,11 +300,12 @@ def run_b200(args):
                 "kernel_rows_x_cols_per_s": d["hist_rows_cols"] / (hist_ms * 1e-3) if hist_ms > 0 else 0.0,
                 "stage_ms_per_step": {k: d[k] / args.steps for k in ("ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals",
                                                                         "ms_gamma", "ms_addtree")}}
-    # secondary ceiling (SURVEY 8d asks for it): the kernel is bound by shared-memory atomics, 5 per (row, column) item with unit
-    # weights; the part sustains ~2090 G ATOMS.ADD/s (tools/ubench_atomics2.cu, profiles/r01_ubench_atomics2_b200.txt)
+    # secondary ceiling (SURVEY 8d asks for it): the kernel's time goes into shared-memory atomics, 5 per (row, column) item with
+    # unit weights; random-bin ATOMS.ADD runs at 12.4 lanes/clk/SM = 3490 G/s on this part (conflict free: 31 lanes/clk/SM;
+    # tools/ubench_atomics2.cu "clean" lines, profiles/r01_ubench_atomics2_b200.txt)
     atoms = 5.0 * d["hist_rows_cols"] / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
-    roofline["smem_atomics"] = {"achieved": atoms, "peak": 2090.0, "unit": "Gatom/s", "frac": atoms / 2090.0,
-                                "peak_source": "measured, tools/ubench_atomics2.cu on B200"}
+    roofline["smem_atomics"] = {"achieved": atoms, "peak": 3490.0, "unit": "Gatom/s", "frac": atoms / 3490.0,
+                                "peak_source": "measured, tools/ubench_atomics2.cu (random-bin pattern) on B200"}
     t1s = gm.timing()
     levels_per_step = (t1s.levels - t0s.levels) / args.steps
     roofline["host_ms_per_step"] = {"inside_level_calls": 1e3 * (t1s.level_s - t0s.level_s) / args.steps,
