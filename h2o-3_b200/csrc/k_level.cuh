@@ -246,11 +246,12 @@ __device__ __forceinline__ uint32_t atom_add_u32(uint32_t addr, uint32_t v) {
   asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(addr), "r"(v) : "memory");
   return old;
 }
-// [addr] += hi + carry(old + lo), skipped when that is zero
+// [addr] += hi + carry(old + lo). Unconditional: the high halves are non-zero for nearly every row (negative values, values
+// past 2^32), and ptxas turns a predicated shared-memory atomic into a BSSY / BRA / BSYNC block that costs more than the add.
 __device__ __forceinline__ void red_add_hi(uint32_t addr, uint32_t old, uint32_t lo, uint32_t hi) {
-  asm volatile(
-      "{\n .reg .pred q;\n .reg .u32 t, h;\n add.cc.u32 t, %1, %2;\n addc.u32 h, %3, 0;\n setp.ne.u32 q, h, 0;\n"
-      " @q red.shared.add.u32 [%0], h;\n}" ::"r"(addr), "r"(old), "r"(lo), "r"(hi) : "memory");
+  asm volatile("{\n .reg .u32 t, h;\n add.cc.u32 t, %1, %2;\n addc.u32 h, %3, 0;\n red.shared.add.u32 [%0], h;\n}" ::"r"(addr), "r"(old),
+               "r"(lo), "r"(hi)
+               : "memory");
 }
 // if (on && v > cur) [addr] = max([addr], v)
 __device__ __forceinline__ void red_max_if_gt(uint32_t addr, uint32_t v, uint32_t cur, uint32_t on) {
@@ -321,9 +322,11 @@ __device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint
         if (k > m.mx) atomicMax(&mm64[p].mx, k);
       }
     } else {
-      const uint32_t live = (on && !na[j]) ? 1u : 0u;
-      red_max_if_gt(rec + kTKmin * 4, ~key[j], rr.kmin, live);
-      red_max_if_gt(rec + kTKmax * 4, key[j], rr.kmax, live);
+      // min / max keys: a new extreme is rare once a tile or two have gone by, so ONE branch guards both updates
+      if (on && !na[j] && (~key[j] > rr.kmin || key[j] > rr.kmax)) {
+        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmin * 4), "r"(~key[j]) : "memory");
+        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmax * 4), "r"(key[j]) : "memory");
+      }
     }
     // replica r of a pair sits r * (nbin + 1) bins after replica 0 (replica == 0 unless the planner replicated the column)
     wd[j] = on ? hist_a + (place + (uint32_t)((replica * (nbin + 1) + b) * WPB)) * 4u : sink_a;
