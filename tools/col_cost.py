@@ -37,4 +37,19 @@ for name, sel in list(kinds.items()) + [("all", list(range(C)))]:
         e.build_level(descs)
         s = e.stats()
     print("%-26s %2d columns: %.3f ms per level, %.4f ms per column" % (name, len(sel), s.ms_hist, s.ms_hist / len(sel)))
+print("per column (alone at the root, 1024 bins):")
+for c in range(C):
+    descs = (P.HistDesc * C)()
+    for j in range(C):
+        v = cols[j]
+        lo, hi = float(np.nanmin(v)), float(np.nanmax(v))
+        descs[j] = P.make_desc(lo, np.nextafter(hi, np.inf), 1024, init_na=False, order=j, active=j == c)
+    for rep in range(3):
+        e.stats_reset()
+        e.build_level(descs)
+        s = e.stats()
+    v = cols[c][:400000]
+    b = np.minimum(((v - v.min()) * (1024 / (np.nextafter(v.max(), np.inf) - v.min()))).astype(np.int64), 1023)
+    p = np.bincount(b, minlength=1024) / b.size
+    print("  col %2d  %6d distinct  share-a-bin prob %.4f : %.4f ms" % (c, nuniq[c], float((p * p).sum()), s.ms_hist))
 e.close()
