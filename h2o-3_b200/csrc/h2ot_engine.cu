@@ -8,6 +8,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <queue>
 #include <vector>
 
 #include "common.cuh"
@@ -1304,21 +1305,44 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cost_of(x) > cost_of(y); });
     size_t total_words = 0;
     for (int c : cols) total_words += (size_t)col_words[c];
-    for (size_t ng = std::max<size_t>(1, (total_words * 4 + budget - 1) / budget);; ng++) {
+    // first guess of the group count from the bytes a column really takes (bins + its records); a min-heap on the group cost
+    // makes a placement O(log groups) (wide frames: 2000 columns spread over ~200 groups), and a failed attempt grows the
+    // count geometrically
+    const size_t per_col_fixed = fixed_bytes(2, st) - fixed_bytes(1, st);
+    size_t ng0 = (total_words * 4 + cols.size() * per_col_fixed + (budget - fixed_bytes(0, st)) - 1) / (budget - fixed_bytes(0, st));
+    for (size_t ng = std::max<size_t>(1, ng0);; ng += std::max<size_t>(1, ng / 16)) {
       groups.assign(ng, {});
       gcost.assign(ng, 0.0);
       std::vector<size_t> gwords(ng, 0);
+      typedef std::pair<double, int> Ent;
+      std::priority_queue<Ent, std::vector<Ent>, std::greater<Ent>> heap;
+      for (size_t g = 0; g < ng; g++) heap.push(Ent(0.0, (int)g));
       bool ok = true;
+      auto fits = [&](size_t g, int c) { return (gwords[g] + (size_t)col_words[c]) * 4 + fixed_bytes((int)groups[g].size() + 1, st) <= budget; };
       for (int c : order) {
         int best = -1;
-        for (size_t g = 0; g < ng; g++) {
-          if ((gwords[g] + (size_t)col_words[c]) * 4 + fixed_bytes((int)groups[g].size() + 1, st) > budget) continue;
-          if (best < 0 || gcost[g] < gcost[best]) best = (int)g;
+        if (!heap.empty() && fits((size_t)heap.top().second, c)) {
+          best = heap.top().second;
+          heap.pop();
+        } else {  // the cheapest group is full for this column: look at all of them
+          for (size_t g = 0; g < ng; g++) {
+            if (!fits(g, c)) continue;
+            if (best < 0 || gcost[g] < gcost[best]) best = (int)g;
+          }
+          if (best >= 0) {  // take it out of the heap (rebuild: rare)
+            std::vector<Ent> keep;
+            while (!heap.empty()) {
+              if (heap.top().second != best) keep.push_back(heap.top());
+              heap.pop();
+            }
+            for (const Ent& e : keep) heap.push(e);
+          }
         }
         if (best < 0) { ok = false; break; }
         groups[best].push_back(c);
         gwords[best] += (size_t)col_words[c];
         gcost[best] += cost_of(c);
+        heap.push(Ent(gcost[best], best));
       }
       if (ok) break;
       if (ng > cols.size()) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "cannot place the level's histograms in shared memory");
