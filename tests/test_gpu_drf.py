@@ -62,3 +62,19 @@ def test_drf_multinomial():
     h2ot_lib.compare_models(gm, om, K=4)
     assert np.array_equal(gm.oobt(), om.oobt())
     gm.close()
+
+
+def test_drf_very_deep_tree_many_leaf_ranges():
+    """Depth 16 with min_rows 1: hundreds of leaves per level, so the leaf-major kernel works through several leaf ranges per
+    level; the tree must still be the oracle's, node for node."""
+    rng = np.random.default_rng(77)
+    n = 60000
+    X = rng.normal(size=(n, 6)).astype(np.float32).astype(np.float64)
+    X[:, 4] = rng.integers(0, 50, n)
+    X[rng.random(X.shape) < 0.01] = NaN
+    y = (np.nan_to_num(X[:, 0]) * np.nan_to_num(X[:, 1]) + 0.3 * rng.normal(size=n) > 0).astype(np.float64)
+    gm, om = _run_both(X, y, capture=False, mtries=2, ntrees=1, max_depth=16, nbins=20, min_rows=1.0, sample_rate=0.8, seed=5)
+    h2ot_lib.compare_models(gm, om, check_levels=False)
+    assert len(gm.tree(0)[0]) > 2000
+    assert np.array_equal(gm.oobt(), om.oobt())
+    gm.close()
