@@ -1254,12 +1254,9 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     const double excess = 8.0 * h->col_conc[c] / (double)L;
     int rep = 1;
     while (rep < 32 && excess / rep >= 0.4) rep <<= 1;
-    static const int min_rep = [] { const char* e = getenv("H2OT_MIN_REP"); return e ? atoi(e) : 1; }();  // experiment knob
-    if (rep < min_rep) rep = min_rep;
     // as many copies as one CTA can hold for the column alone (a few-valued column then gets a group of its own: measured on the
     // Higgs shape a 3-valued column costs 3.5x a continuous one without copies, 2.4x with 4)
-    static const int cap_div = [] { const char* e = getenv("H2OT_REP_CAP_DIV"); return e ? std::max(1, atoi(e)) : 1; }();
-    while (rep > 1 && (size_t)col_words[c] * rep * 4 + fixed_bytes(1, h->cols[c].storage) > (budget - 4096) / cap_div) rep >>= 1;
+    while (rep > 1 && (size_t)col_words[c] * rep * 4 + fixed_bytes(1, h->cols[c].storage) > budget - 4096) rep >>= 1;
     col_rep[c] = rep;
     col_words[c] *= rep;
   }
