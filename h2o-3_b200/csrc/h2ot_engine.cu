@@ -296,6 +296,8 @@ int h2ot_device_count(int32_t* out) {
 int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   if (!cfg || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
   if (cfg->nrows <= 0 || cfg->ncols <= 0 || cfg->nclass_trees <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "nrows/ncols/nclass_trees must be positive");
+  if (cfg->nrows > ((int64_t)1 << 32) - 2 * kRowPad)  // row ids travel as 32-bit values inside the level kernels; a shard is far smaller anyway
+    H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "more than 2^32 rows on one GPU: shard the rows over more engines");
   if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
   if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_TWEEDIE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
   int ndev = 0;
