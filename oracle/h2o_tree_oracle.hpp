@@ -259,6 +259,26 @@ inline std::vector<double> limitToRange(const std::vector<double>& pts, double m
   if (end < start) end = start;
   return std::vector<double>(pts.begin() + start, pts.begin() + end);
 }
+// W/util/ArrayUtils.java:1955-1983 (used by GlobalQuantilesCalc and GuidedSplitPoints before the points reach DHistogram)
+inline std::vector<double> makeUniqueAndLimitToRange(const std::vector<double>& splitPoints, double min, double maxEx) {
+  double last = splitPoints[0];
+  std::vector<double> out;
+  for (size_t i = 0; i < splitPoints.size(); ++i) {
+    const double pos = splitPoints[i];
+    if (pos >= min && out.empty()) {
+      out.push_back(min);
+      if (pos > min) out.push_back(pos);
+      last = pos;
+    } else if (pos > maxEx) {
+      break;
+    } else if (pos > min && pos < maxEx && (i == 0 || pos != last)) {
+      out.push_back(pos);
+      last = pos;
+    }
+  }
+  if (out.empty()) return std::vector<double>{min};
+  return out;
+}
 // W/util/ArrayUtils.java:1933-1952
 inline std::vector<double> padUniformly(const std::vector<double>& orig, int newLength) {
   const int origLength = (int)orig.size();

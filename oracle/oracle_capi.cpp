@@ -40,6 +40,11 @@ int orc_limit_to_range(const double* pts, int n, double min, double maxEx, doubl
   std::copy(r.begin(), r.end(), out);
   return (int)r.size();
 }
+int orc_make_unique_and_limit(const double* pts, int n, double min, double maxEx, double* out) {
+  const std::vector<double> r = makeUniqueAndLimitToRange(std::vector<double>(pts, pts + n), min, maxEx);
+  std::copy(r.begin(), r.end(), out);
+  return (int)r.size();
+}
 int orc_pad_uniformly(const double* pts, int n, int newLength, double* out) {
   const std::vector<double> r = padUniformly(std::vector<double>(pts, pts + n), newLength);
   std::copy(r.begin(), r.end(), out);

@@ -318,6 +318,24 @@ def _pad(pts, n_new):
     return list(out[:n])
 
 
+def _uniq(pts, mn, mx):
+    L = O.lib()
+    L.orc_make_unique_and_limit.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p]
+    p = np.ascontiguousarray(pts, dtype=np.float64)
+    out = np.empty(len(p) + 2, dtype=np.float64)
+    n = L.orc_make_unique_and_limit(O.ptr(p), len(p), mn, mx, O.ptr(out))
+    return list(out[:n])
+
+
+def test_make_unique_and_limit_to_range_golden():
+    """HistogramTest.testShrinking .. testShrinking4 (:210-229): exact arrays."""
+    assert _uniq([0.2, 0.28, 0.31, 0.32, 0.32, 0.4, 0.7, 0.81, 0.84], 0.3, 0.8) == [0.3, 0.31, 0.32, 0.4, 0.7]
+    long_ = [-0.3, 0.2, 0.28, 0.28, 0.3, 0.3, 0.31, 0.32, 0.32, 0.4, 0.7, 0.7, 0.8, 0.8, 0.81, 0.84]
+    assert _uniq(long_, 0.3, 0.8) == [0.3, 0.31, 0.32, 0.4, 0.7]
+    assert _uniq(long_, 0.3, 0.9) == [0.3, 0.31, 0.32, 0.4, 0.7, 0.8, 0.81, 0.84]
+    assert _uniq([0.31, 0.32, 0.32, 0.4, 0.7, 0.7], 0.3, 0.9) == [0.3, 0.31, 0.32, 0.4, 0.7]
+
+
 def test_limit_to_range_and_pad_uniformly_golden():
     """HistogramTest.testShrinking5-9, testPadding, testPadding2, testPadding3: exact arrays."""
     b = [0.3, 0.31, 0.32, 0.4, 0.7]
