@@ -8,6 +8,7 @@
  *       -Lh2o-3_b200 -lh2otree_b200 -o libh2otree_jni.so
  */
 #include <jni.h>
+#include <stdint.h>
 
 #include "h2ot.h"
 
