@@ -1,12 +1,14 @@
 #!/usr/bin/env python
-"""bench.py — the hex.tree histogram hot path on B200: GBM bernoulli on a Higgs-shape synthetic frame
-(BASELINE.json configs[1]: 11M x 28 numeric, max_depth 6, nbins 256, nbins_top_level 1024).
+"""bench.py — the hex.tree histogram hot path on B200. Default workload: GBM bernoulli on a Higgs-shape synthetic frame
+(BASELINE.json configs[1]: 11M x 28 numeric, max_depth 6, nbins 256, nbins_top_level 1024); `--config` selects the other
+BASELINE configurations (c1 100k x 10, c3 DRF depth 12 mtries 5, c4 airlines shape 100M x 12 with categoricals, c5a covtype shape
+7 classes, c5b Epsilon shape 400k x 2000 7 classes), each with the same roofline / e2e / cpu_baseline treatment.
 
-One "step" = one boosting iteration (GBM.buildNextKTrees: residuals, <=6 level passes of score_decide + histogram
-build + split search, GammaPass, AddTreeContributions) on the frame resident in HBM.
+One "step" = one boosting iteration (GBM.buildNextKTrees: residuals, <=max_depth level passes of score_decide + histogram
+build + split search, GammaPass, AddTreeContributions; K class-trees for multinomial; DRF: one tree) on the frame resident in HBM.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W]            # this engine
-  python bench.py --impl reference [--steps K] [--warmup W]      # CPU restatement of the reference path (oracle port)
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config c2]   # this engine
+  python bench.py --impl reference [--steps K] [--warmup W]           # CPU restatement of the reference path (oracle port), same config
 
 Prints ONE JSON line (rank 0). `value` = rows x active-cols histogrammed per second over the K timed steps (all ranks);
 `e2e` = the same metric for a whole job from pinned HOST buffers (frame upload + encode + init + K trees + read-back
@@ -29,6 +31,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "hist_build_rows_x_cols_per_s"
 UNIT = "rows*cols/s"
+ATOMS_PER_ITEM = 5.0  # shared-memory atomics per (row, column) item in hist_smem_kernel with unit weights
 PARAMS = dict(max_depth=6, nbins=256, nbins_top_level=1024, nbins_cats=1024, min_rows=10.0, learn_rate=0.1, seed=1234)
 NCOLS = 28
 
@@ -49,17 +52,19 @@ def higgs_like_column(col, nrows, seed=42):
     return v.astype(np.float32).astype(np.float64)
 
 
-def make_frame(nrows, r0, r1, pinned):
-    """Returns (columns[NCOLS] of float64 arrays for global rows [r0,r1), y). pinned: allocate in pinned host memory."""
-    n = r1 - r0
-    cols = []
+def _buffers(n, ncols, pinned):
     if pinned:
         import torch
-        hold = [torch.empty(n, dtype=torch.float64, pin_memory=True) for _ in range(NCOLS + 1)]
-        bufs = [h.numpy() for h in hold]
-    else:
-        hold = None
-        bufs = [np.empty(n, dtype=np.float64) for _ in range(NCOLS + 1)]
+        hold = [torch.empty(n, dtype=torch.float64, pin_memory=True) for _ in range(ncols + 1)]
+        return [h.numpy() for h in hold], hold
+    return [np.empty(n, dtype=np.float64) for _ in range(ncols + 1)], None
+
+
+def make_frame(nrows, r0, r1, pinned):
+    """Higgs shape. Returns (columns[NCOLS] of float64 arrays for global rows [r0,r1), y, keep-alive). pinned: pinned host memory."""
+    n = r1 - r0
+    cols = []
+    bufs, hold = _buffers(n, NCOLS, pinned)
     logit = np.zeros(nrows, dtype=np.float64)
     for c in range(NCOLS):
         v = higgs_like_column(c, nrows)
@@ -77,6 +82,104 @@ def make_frame(nrows, r0, r1, pinned):
     u = np.random.default_rng([42, 1000]).random(nrows)
     bufs[NCOLS][:] = (u < 1.0 / (1.0 + np.exp(-logit)))[r0:r1]
     return cols, bufs[NCOLS], hold
+
+
+def _frame_c1(nrows, r0, r1, pinned):
+    """BASELINE configs[0]: 100k x 10 numeric, bernoulli."""
+    bufs, hold = _buffers(r1 - r0, 10, pinned)
+    rng = np.random.default_rng(7)
+    X = rng.normal(size=(nrows, 10)).astype(np.float32).astype(np.float64)
+    y = (rng.random(nrows) < 1 / (1 + np.exp(-(X[:, 0] - 0.5 * X[:, 1] + 0.3 * X[:, 2] * X[:, 3])))).astype(np.float64)
+    for c in range(10):
+        bufs[c][:] = X[r0:r1, c]
+    bufs[10][:] = y[r0:r1]
+    return bufs[:10], bufs[10], hold
+
+
+def _frame_c4(nrows, r0, r1, pinned):
+    """BASELINE configs[3] shape: airlines-like, 8 integer columns (two with NAs) + 4 Zipf categoricals (300 / 300 / 5000 / 20000 levels)."""
+    bufs, hold = _buffers(r1 - r0, 12, pinned)
+    ranges = [(1987, 2008), (1, 12), (1, 31), (1, 7), (0, 2400), (0, 2400), (-60, 600), (11, 4983)]
+    cards = [300, 300, 5000, 20000]
+    y = np.zeros(nrows)
+    for c in range(12):
+        rng = np.random.default_rng([43, c])
+        if c < 8:
+            lo, hi = ranges[c]
+            v = rng.integers(lo, hi + 1, nrows).astype(np.float64)
+            if c in (4, 6):
+                v[rng.random(nrows) < 0.02] = np.nan
+            if c in (5, 6):
+                y += np.nan_to_num(v) * (0.01 if c == 5 else 0.5)
+        else:
+            v = np.minimum(rng.zipf(1.3, nrows) - 1, cards[c - 8] - 1).astype(np.float64)
+            y += (v % 7) * 2.0
+        bufs[c][:] = v[r0:r1]
+        del v
+    y += np.random.default_rng([43, 100]).normal(size=nrows) * 10
+    bufs[12][:] = y.astype(np.float32)[r0:r1]
+    return bufs[:12], bufs[12], hold
+
+
+def _frame_c5a(nrows, r0, r1, pinned):
+    """BASELINE configs[4] covtype shape: 10 numeric + 44 binary columns, 7 classes."""
+    bufs, hold = _buffers(r1 - r0, 54, pinned)
+    rng = np.random.default_rng(44)
+    X = [rng.normal(size=nrows).astype(np.float32).astype(np.float64) for _ in range(10)] + [(rng.random(nrows) < 0.1).astype(np.float64) for _ in range(44)]
+    z = np.stack([X[k] + 0.5 * X[(k + 3) % 10] for k in range(7)], axis=1)
+    y = np.argmax(z + rng.gumbel(size=z.shape), axis=1).astype(np.float64)
+    for c in range(54):
+        bufs[c][:] = X[c][r0:r1]
+    bufs[54][:] = y[r0:r1]
+    return bufs[:54], bufs[54], hold
+
+
+def _frame_c5b(nrows, r0, r1, pinned):
+    """BASELINE configs[4] Epsilon shape: 2000 dense fp32 columns, unit-norm rows, 7 classes."""
+    Cc = 2000
+    bufs, hold = _buffers(r1 - r0, Cc, pinned)
+    rng = np.random.default_rng(45)
+    X = rng.normal(size=(Cc, nrows)).astype(np.float32)
+    X /= np.sqrt((X.astype(np.float64) ** 2).sum(axis=0)).astype(np.float32)
+    z = np.stack([X[k * 3] * 40 + X[k * 3 + 1] * 20 for k in range(7)], axis=1)
+    y = np.argmax(z + rng.gumbel(size=z.shape), axis=1).astype(np.float64)
+    for c in range(Cc):
+        bufs[c][:] = X[c, r0:r1]
+    bufs[Cc][:] = y[r0:r1]
+    return bufs[:Cc], bufs[Cc], hold
+
+
+# name -> workload. "model": keyword arguments of the product's GBM / DRF; "oracle": the matching oracle parameters.
+WORKLOADS = {
+    "c1": dict(rows=100_000, ncols=10, frame=_frame_c1, cls="GBM", cats={}, K=1,
+               text="GBM bernoulli synthetic %dx%d numeric, max_depth 5, nbins 20 (BASELINE configs[0])",
+               model=dict(distribution="bernoulli", max_depth=5, nbins=20, min_rows=10.0, learn_rate=0.1, seed=1234)),
+    "c2": dict(rows=11_000_000, ncols=NCOLS, frame=make_frame, cls="GBM", cats={}, K=1,
+               text="GBM bernoulli Higgs-shape %dx%d, max_depth 6, nbins 256, nbins_top_level 1024 (BASELINE configs[1])",
+               model=dict(distribution="bernoulli", **PARAMS)),
+    "c3": dict(rows=11_000_000, ncols=NCOLS, frame=make_frame, cls="DRF", cats={}, K=1,
+               text="DRF Higgs-shape %dx%d, max_depth 12, mtries 5, sample_rate 0.63, nbins 20 (BASELINE configs[2])",
+               model=dict(distribution="bernoulli", max_depth=12, mtries=5, sample_rate=0.63, min_rows=1.0, nbins=20, seed=1234)),
+    "c4": dict(rows=100_000_000, ncols=12, frame=_frame_c4, cls="GBM", cats={8: 300, 9: 300, 10: 5000, 11: 20000}, K=1,
+               text="GBM gaussian airlines-shape %dx%d mixed, 4 categoricals up to 20000 levels, max_depth 5, nbins 20, nbins_cats 1024 (BASELINE configs[3])",
+               model=dict(distribution="gaussian", nclass=1, max_depth=5, nbins=20, nbins_cats=1024, seed=1234)),
+    "c5a": dict(rows=581_012, ncols=54, frame=_frame_c5a, cls="GBM", cats={}, K=7,
+                text="GBM multinomial 7-class covtype-shape %dx%d, max_depth 5, nbins 64 (BASELINE configs[4])",
+                model=dict(distribution="multinomial", nclass=7, max_depth=5, nbins=64, seed=1234)),
+    "c5b": dict(rows=400_000, ncols=2000, frame=_frame_c5b, cls="GBM", cats={}, K=7,
+                text="GBM multinomial 7-class Epsilon-shape %dx%d dense, max_depth 5, nbins 64 (BASELINE configs[4])",
+                model=dict(distribution="multinomial", nclass=7, max_depth=5, nbins=64, seed=1234)),
+}
+
+
+def oracle_model(O, fr, wl, ntrees, threads, chunk):
+    """The oracle's build of workload wl (C++ restatement of the reference CPU path): returns an oracle Model."""
+    m = dict(wl["model"])
+    fam = {"bernoulli": O.BERNOULLI, "gaussian": O.GAUSSIAN, "multinomial": O.MULTINOMIAL}[m.pop("distribution")]
+    nclass = m.pop("nclass", 2)
+    mtries = m.pop("mtries", -1)
+    p = O.default_params(family=fam, nclass=nclass, ntrees=ntrees, nthreads=threads, chunk_rows=chunk, **m)
+    return O.Model(fr, p, drf=wl["cls"] == "DRF", mtries=mtries)
 
 
 class ClockSampler:
@@ -141,32 +244,34 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
-    """dram bytes per histogram-kernel launch from the committed ncu capture (profiles/hist_traffic.json), else None."""
+def ncu_traffic(config, rows_per_gpu):
+    """dram bytes per histogram-kernel launch from the committed ncu capture (profiles/hist_traffic.json) -- only when that
+    capture was taken on this config and this many rows per GPU; otherwise None (the bytes scale with the shard)."""
     p = os.path.join(ROOT, "profiles", "hist_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("dram_bytes_per_launch")
+            j = json.load(open(p))
+            if j.get("config", "c2") == config and int(j.get("rows_per_gpu", 11_000_000)) == int(rows_per_gpu):
+                return j.get("dram_bytes_per_launch")
         except Exception:
             return None
     return None
 
 
-def cpu_baseline(nrows_sample, budget_s, threads):
+def cpu_baseline(wl, nrows_sample, budget_s, threads):
     """Oracle port (C++ restatement of the reference CPU path, NOT the JVM) on the first nrows_sample rows, all host
-    threads; runs whole trees until ~budget_s of work. Returns (rows*cols/s, sec/tree, trees, wall)."""
+    threads; runs whole iterations until ~budget_s of work. Returns (rows*cols/s, sec/iteration, iterations, wall)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
-    cols, y, _ = make_frame(nrows_sample, 0, nrows_sample, pinned=False)
+    cols, y, _ = wl["frame"](nrows_sample, 0, nrows_sample, False)
     X = np.stack(cols, axis=1)
-    fr = O.Frame(X, y)
+    fr = O.Frame(X, y, cat_cards=wl["cats"])
     del X, cols
     trees, wall, rowcols = 0, 0.0, 0.0
     nt = 1
+    chunk = max(4096, nrows_sample // (4 * max(1, threads)))
     while True:
-        p = O.default_params(family=O.BERNOULLI, nclass=2, ntrees=nt, nthreads=threads,
-                             chunk_rows=max(4096, nrows_sample // (4 * max(1, threads))), **PARAMS)
-        m = O.Model(fr, p)
+        m = oracle_model(O, fr, wl, nt, threads, chunk)
         t_hist, t_total, rc = m.timing()
         trees, wall, rowcols = nt, t_total, rc
         del m
@@ -177,48 +282,65 @@ def cpu_baseline(nrows_sample, budget_s, threads):
 
 
 def run_reference(args):
+    """Reference arm: the oracle's multithreaded restatement of the reference CPU path (no JVM here) on the SAME config
+    and the same number of rows as the engine's arm, all host threads."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    wl = WORKLOADS[args.config]
+    rows = args.rows or wl["rows"]
     threads = os.cpu_count() or 1
-    sample = min(args.rows, args.ref_rows)
+    sample = min(rows, args.ref_rows) if args.ref_rows else rows
     steps, warm = max(1, args.steps), max(0, args.warmup)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
-    cols, y, _ = make_frame(sample, 0, sample, pinned=False)
+    cols, y, _ = wl["frame"](sample, 0, sample, False)
     X = np.stack(cols, axis=1)
-    fr = O.Frame(X, y)
+    fr = O.Frame(X, y, cat_cards=wl["cats"])
     del X, cols
     chunk = max(4096, sample // (4 * threads))
-    # each step = one boosting iteration on the sample; the oracle trains from scratch, so run warm+steps trees once
-    # and time only the last `steps` of them by differencing two runs (trees are identical up to that point)
+    # each step = one boosting iteration; the oracle trains from scratch, so run warm and warm+steps iterations and time the
+    # last `steps` of them by differencing the two runs (the trees are identical up to that point)
     t_w = 0.0
     rc_w = 0.0
     if warm > 0:
-        mw = O.Model(fr, O.default_params(family=O.BERNOULLI, nclass=2, ntrees=warm, nthreads=threads, chunk_rows=chunk, **PARAMS))
+        mw = oracle_model(O, fr, wl, warm, threads, chunk)
         _, t_w, rc_w = mw.timing()
         del mw
-    m = O.Model(fr, O.default_params(family=O.BERNOULLI, nclass=2, ntrees=warm + steps, nthreads=threads, chunk_rows=chunk, **PARAMS))
+    m = oracle_model(O, fr, wl, warm + steps, threads, chunk)
     _, t_all, rc_all = m.timing()
     dt = max(1e-9, t_all - t_w)
     rc = rc_all - rc_w
     val = rc / dt
+    what = "all %d rows" % sample if sample == rows else "first %d of %d rows" % (sample, rows)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": 1e3 * dt / steps, "sec_per_tree": dt / steps, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "GBM bernoulli Higgs-shape %dx%d (bounded sample of 11Mx28) depth 6 nbins 256" % (sample, NCOLS),
-                   "rows": sample, "cols": NCOLS, **{k: PARAMS[k] for k in ("max_depth", "nbins", "nbins_top_level")}},
+        "config": {"workload": wl["text"] % (sample, wl["ncols"]), "name": args.config, "rows": sample, "cols": wl["ncols"],
+                   **{k: v for k, v in wl["model"].items() if k in ("max_depth", "nbins", "nbins_top_level", "mtries", "sample_rate")}},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": "first %d rows of the 11Mx28 frame, %d trees timed after %d warm-up trees; C++ restatement of "
-                                   "the reference CPU path (no JVM on this box)" % (sample, steps, warm)},
+                         "sample": "%s of the frame, %d iterations timed after %d warm-up iterations; C++ restatement of "
+                                   "the reference CPU path (no JVM on this box)" % (what, steps, warm)},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
 
 
+def tree_bytes(gm, K):
+    out = []
+    for t in range(gm.ntrees):
+        for k in range(K):
+            nodes, ls = gm.tree(t, k)
+            out.append(bytes(nodes))
+            out.append(int(ls).to_bytes(4, "little", signed=True))
+    return b"".join(out)
+
+
 def run_b200(args):
+    import hashlib
+
     import torch
     import torch.distributed as dist
 
@@ -231,9 +353,11 @@ def run_b200(args):
     importlib.import_module("h2o-3_b200.build").build()
     P = importlib.import_module("h2o-3_b200")
 
-    N = args.rows
+    wl = WORKLOADS[args.config]
+    N = args.rows or wl["rows"]
+    K = wl["K"]
     r0, r1 = (N * rank) // world, (N * (rank + 1)) // world
-    cols, y, hold = make_frame(N, r0, r1, pinned=True)
+    cols, y, hold = wl["frame"](N, r0, r1, True)
     comm = None
     if world > 1:
         uid = torch.zeros(P.COMM_ID_BYTES, dtype=torch.uint8)
@@ -248,13 +372,12 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def new_gbm():
-        g = P.GBM(distribution="bernoulli", ntrees=args.steps + args.warmup, device=local, **PARAMS)
-        return g
+    def new_gbm(ntrees=None, device=local):
+        return getattr(P, wl["cls"])(ntrees=ntrees or (args.steps + args.warmup), device=device, **wl["model"])
 
     # ---------------- device-resident arm: W warm-up + K timed boosting iterations
     gm = new_gbm()
-    gm.load(cols, y, row_offset=r0, nrows_global=N, comm=comm)
+    gm.load(cols, y, categorical=wl["cats"], row_offset=r0, nrows_global=N, comm=comm)
     eng = gm.engine()
     for _ in range(args.warmup):
         gm.train(1)
@@ -292,7 +415,7 @@ def run_b200(args):
     hist_ms = d["ms_hist"]
     n_hl = max(1, d["hist_launches"])
     ach = d["hist_algo_bytes"] / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
-    traffic = ncu_traffic()
+    traffic = ncu_traffic(args.config, r1 - r0)
     roofline = {"bound": "hbm", "kernel": "hist_smem_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": d["hist_algo_bytes"] / n_hl, "ms_per_launch": hist_ms / n_hl,
@@ -300,28 +423,55 @@ def run_b200(args):
                 "kernel_rows_x_cols_per_s": d["hist_rows_cols"] / (hist_ms * 1e-3) if hist_ms > 0 else 0.0,
                 "stage_ms_per_step": {k: d[k] / args.steps for k in ("ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals",
                                                                         "ms_gamma", "ms_addtree")}}
-    # secondary ceiling (SURVEY 8d asks for it): the kernel's time goes into shared-memory atomics, 5 per (row, column) item with
-    # unit weights; random-bin ATOMS.ADD runs at 12.4 lanes/clk/SM = 3490 G/s on this part (conflict free: 31 lanes/clk/SM;
+    # secondary ceiling (SURVEY 8d asks for it): the kernel's time goes into shared-memory atomics, ATOMS_PER_ITEM per (row, column)
+    # item with unit weights; random-bin ATOMS.ADD runs at 12.4 lanes/clk/SM = 3490 G/s on this part (conflict free: 31 lanes/clk/SM;
     # tools/ubench_atomics2.cu "clean" lines, profiles/r01_ubench_atomics2_b200.txt)
-    atoms = 5.0 * d["hist_rows_cols"] / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
-    roofline["smem_atomics"] = {"achieved": atoms, "peak": 3490.0, "unit": "Gatom/s", "frac": atoms / 3490.0,
+    atoms = ATOMS_PER_ITEM * d["hist_rows_cols"] / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
+    roofline["smem_atomics"] = {"achieved": atoms, "peak": 3490.0, "unit": "Gatom/s", "frac": atoms / 3490.0, "atomics_per_item": ATOMS_PER_ITEM,
                                 "peak_source": "measured, tools/ubench_atomics2.cu (random-bin pattern) on B200"}
     t1s = gm.timing()
     levels_per_step = (t1s.levels - t0s.levels) / args.steps
     roofline["host_ms_per_step"] = {"inside_level_calls": 1e3 * (t1s.level_s - t0s.level_s) / args.steps,
                                     "whole_step_wall": 1e3 * (t1s.total_s - t0s.total_s) / args.steps}
+    # ---------------- parity of the sharded build: every rank's trees must be the same bytes, and the same bytes as a
+    # single-GPU build of the whole frame (rank 0 builds it after the timed region; GBMTest.java:1085-1143 is the protocol)
+    parity = None
+    mine = tree_bytes(gm, K)
+    my_preds = [gm.predictions(k) for k in range(K)] if wl["cls"] == "GBM" else None
     gm.close()
+    if world > 1:
+        digests = [None] * world
+        dist.all_gather_object(digests, hashlib.sha256(mine).hexdigest())
+        same = all(x == digests[0] for x in digests)
+        single = None
+        if rank == 0:
+            fcols, fy, _ = wl["frame"](N, 0, N, False)
+            g1 = new_gbm()
+            g1.load(fcols, fy, categorical=wl["cats"])
+            g1.train()
+            single = tree_bytes(g1, K) == mine
+            if my_preds is not None:
+                for k in range(K):
+                    single = single and bool(np.array_equal(g1.predictions(k)[r0:r1], my_preds[k]))
+            g1.close()
+            del fcols, fy
+            parity = {"trees_identical_across_ranks": bool(same), "trees_identical_to_1gpu": bool(single), "trees": args.steps + args.warmup,
+                      "sha256": digests[0][:16]}
+        barrier()
+    else:
+        parity = {"trees_identical_across_ranks": True, "trees_identical_to_1gpu": True, "trees": args.steps + args.warmup,
+                  "sha256": hashlib.sha256(mine).hexdigest()[:16]}
 
     # ---------------- end-to-end arm: whole job from pinned host buffers through the public API
     barrier()
-    g2 = new_gbm()
+    g2 = new_gbm(ntrees=args.steps)
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     pred_hold = torch.empty(len(y), dtype=torch.float64).pin_memory()  # results land in pinned memory, like the inputs leave it
     f0.record()
-    g2.load(cols, y, row_offset=r0, nrows_global=N, comm=comm)
+    g2.load(cols, y, categorical=wl["cats"], row_offset=r0, nrows_global=N, comm=comm)
     g2.train(args.steps)
     preds = g2.predictions(out=pred_hold.numpy())
-    ntree_nodes = sum(len(g2.tree(t)[0]) for t in range(g2.ntrees))
+    ntree_nodes = sum(len(g2.tree(t, k)[0]) for t in range(g2.ntrees) for k in range(K))
     f1.record()
     barrier()
     ms2 = f0.elapsed_time(f1)
@@ -333,30 +483,33 @@ def run_b200(args):
         ms2 = float(t2[0])
     e2e = {"value": rc2 / (ms2 * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(st2.h2d_bytes / args.steps),
            "d2h_bytes_per_step": int(st2.d2h_bytes / args.steps), "ms_total": ms2, "sec_per_tree": ms2 * 1e-3 / args.steps,
-           "what": "GBM.load (frame upload from pinned host + rollups + encode) + init + %d trees + read-back of the predictions (into pinned memory) and "
+           "what": "load (frame upload from pinned host + rollups + encode) + init + %d iterations + read-back of the predictions (into pinned memory) and "
                    "the trees (%d nodes)" % (args.steps, ntree_nodes)}
     assert np.isfinite(preds).all()
     g2.close()
 
     line = None
     if rank == 0:
+        bpe = sum(1 for _ in cols) and 4
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "sec_per_tree": ms * 1e-3 / args.steps, "higher_is_better": True, "scaling": "strong",
+            "ms_per_step": ms / args.steps, "sec_per_tree": ms * 1e-3 / args.steps / K, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": "GBM bernoulli Higgs-shape %dx%d, max_depth 6, nbins 256, nbins_top_level 1024 (BASELINE configs[1])" % (N, NCOLS),
-                       "rows": N, "cols": NCOLS, "levels_per_step": levels_per_step, "parallelism": "rows sharded over %d GPU(s)" % world,
-                       "l2": "inputs larger than L2 (frame %.2f GB resident)" % (N * NCOLS * 4 / 1e9),
+            "config": {"workload": wl["text"] % (N, wl["ncols"]), "name": args.config,
+                       "rows": N, "cols": wl["ncols"], "levels_per_step": levels_per_step, "parallelism": "rows sharded over %d GPU(s)" % world,
+                       "l2": "inputs larger than L2 (frame %.2f GB resident per GPU)" % ((r1 - r0) * wl["ncols"] * bpe / 1e9) if (r1 - r0) * wl["ncols"] * bpe > 126e6
+                             else "frame %.0f MB per GPU fits L2: a step still streams it once per level and rewrites nids, residuals and predictions in between" % ((r1 - r0) * wl["ncols"] * bpe / 1e6),
                        "arithmetic": "bins in f64 (reference formula), sums of w, w*y, w*y*y as int64 fixed point, float-cast like reducePrecision",
-                       **{k: PARAMS[k] for k in ("max_depth", "nbins", "nbins_top_level")}},
-            "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
+                       **{k: v for k, v in wl["model"].items() if k in ("max_depth", "nbins", "nbins_top_level", "mtries", "sample_rate")}},
+            "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "clocks": clocks, "parity": parity,
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, spt, trees, wall = cpu_baseline(min(N, args.ref_rows), args.cpu_budget_s, threads)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sec_per_tree_on_sample": spt,
-                                    "sample": "first %d rows of the frame, %d trees, %.1f s wall; C++ restatement of the reference CPU "
-                                              "path (oracle), not the JVM (no JDK on this box)" % (min(N, args.ref_rows), trees, wall)}
+            sample = min(N, args.ref_rows) if args.ref_rows else N
+            v, spt, trees, wall = cpu_baseline(wl, sample, args.cpu_budget_s, threads)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sec_per_tree_on_sample": spt / K,
+                                    "sample": "%s rows of the frame, %d iterations, %.1f s wall; C++ restatement of the reference CPU "
+                                              "path (oracle), not the JVM (no JDK on this box)" % ("all %d" % sample if sample == N else "first %d" % sample, trees, wall)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -369,9 +522,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--rows", type=int, default=11_000_000)
-    ap.add_argument("--ref-rows", type=int, default=1_100_000, help="rows of the bounded CPU sample")
-    ap.add_argument("--cpu-budget-s", type=float, default=15.0)
+    ap.add_argument("--config", default="c2", choices=sorted(WORKLOADS), help="BASELINE configuration (default c2 = configs[1])")
+    ap.add_argument("--rows", type=int, default=0, help="global rows (default: the configuration's own)")
+    ap.add_argument("--ref-rows", type=int, default=0, help="rows of the CPU arm / cpu_baseline (default 0: all rows, the same config)")
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -1,5 +1,13 @@
-"""Full-size (BASELINE configs[1]: 11M x 28) checks through size-independent properties — the oracle would need minutes
-here. Per level of a real tree build:
+"""Full-size checks of the BASELINE configurations.
+
+Against the oracle, level by level (nids bit-exact, w exact, wY / wYY within one float ulp per bin, identical descriptors,
+splits and trees) -- the protocol of GBMTest's histogram monitor (h2o-algos/src/test/java/hex/tree/gbm/GBMTest.java:4722-4765):
+  * configs[1] (C2): one depth-6 GBM tree on the 11M x 28 Higgs-shape frame (+ a second tree without captures);
+  * configs[2] (C3): two DRF trees, depth 12, mtries 5, sample_rate 0.63 on the same frame;
+  * configs[3] (C4): airlines-shape 10M x 12 with 300 / 300 / 5000 / 20000-level categoricals, gaussian, depth 5.
+The oracle runs on all host cores (a tree of C2 takes it about a second per million rows and core).
+
+And through size-independent properties. Per level of a real tree build:
   * every active (leaf, col) histogram of a leaf holds the same total weight, sum(wY) and sum(wYY) (the rows of a leaf are
     the same whatever the column: a checksum of checksums across 28 columns);
   * the leaf totals add up to the number of in-bag rows and to the global sum of the work column;
@@ -116,3 +124,123 @@ def test_full_size_drf_sparse_and_column_major_kernels_grow_the_same_trees():
         gm.close()
     assert sparse[0] >= 2 * 7 and sparse[1] == 0, sparse
     assert sig[0] == sig[1]
+
+
+def _oracle_threads():
+    import os
+    return max(1, os.cpu_count() or 1)
+
+
+def test_c2_11m_x_28_one_tree_matches_oracle_level_by_level():
+    """BASELINE configs[1] at full size against the oracle: every level of the first tree (nids of all 11M rows, every
+    (leaf, column) histogram, min/max, descriptors, splits), then a second tree on the updated residuals (trees + predictions)."""
+    import importlib
+    bench = importlib.import_module("bench")
+    import oracle_lib as O
+    P = h2ot_lib.pkg()
+    N = 11_000_000
+    cols, y, _ = bench.make_frame(N, 0, N, pinned=False)
+    kw = {k: v for k, v in bench.PARAMS.items() if k != "seed"}
+    gm = P.GBM(distribution="bernoulli", ntrees=2, seed=1234, **kw)
+    gm.load(cols, y)
+    gm.capture_levels(True)
+    gm.train(1)
+    gm.capture_levels(False)
+    gm.train(1)
+    X = np.stack(cols, axis=1)
+    fr = O.Frame(X, y)
+    del X
+    nt = _oracle_threads()
+    for ntrees, capture in ((1, True), (2, False)):
+        om = O.Model(fr, O.default_params(family=O.BERNOULLI, nclass=2, ntrees=ntrees, nthreads=nt, chunk_rows=max(4096, N // (4 * nt)),
+                                          seed=1234, **kw), capture=capture)
+        if capture:
+            # the product captured the first tree only: compare its levels, its tree and nothing of the second tree
+            class FirstTree:
+                ntrees = 1
+                init_f = gm.init_f
+                ncols = gm.ncols
+                ncaptures = gm.ncaptures
+                capture_info = gm.capture_info
+                capture_nids = gm.capture_nids
+                capture_desc = gm.capture_desc
+                capture_vals = gm.capture_vals
+                tree = gm.tree
+
+                @staticmethod
+                def predictions(k=0):
+                    return om.F(k)  # predictions are compared after the second tree
+            st = h2ot_lib.compare_models(FirstTree, om)
+            assert st["levels"] == 6 and st["hists"] == 63 * 28, st
+            assert st["n_vals_diff"] <= 2e-2 * st["n_vals"], st
+        else:
+            h2ot_lib.compare_models(gm, om, check_levels=False)
+        del om
+    gm.close()
+
+
+def test_c3_drf_11m_x_28_depth12_mtries5_matches_oracle():
+    """BASELINE configs[2] at full size: DRF, depth 12, mtries 5, sample_rate 0.63 -- two trees, every level against the oracle."""
+    import importlib
+    bench = importlib.import_module("bench")
+    import oracle_lib as O
+    P = h2ot_lib.pkg()
+    N = 11_000_000
+    cols, y, _ = bench.make_frame(N, 0, N, pinned=False)
+    kw = dict(ntrees=2, max_depth=12, nbins=20, min_rows=1.0, sample_rate=0.63, seed=1234)
+    gm = P.DRF(distribution="bernoulli", mtries=5, **kw)
+    gm.load(cols, y)
+    gm.capture_levels(True)
+    gm.train()
+    X = np.stack(cols, axis=1)
+    fr = O.Frame(X, y)
+    del X
+    nt = _oracle_threads()
+    om = O.Model(fr, O.default_params(family=O.BERNOULLI, nclass=2, nthreads=nt, chunk_rows=max(4096, N // (4 * nt)), **kw),
+                 capture=True, drf=True, mtries=5)
+    st = h2ot_lib.compare_models(gm, om)
+    assert st["levels"] >= 2 * 12, st
+    assert np.array_equal(gm.oobt(), om.oobt())
+    gm.close()
+
+
+def test_c4_airlines_shape_10m_x_12_matches_oracle():
+    """BASELINE configs[3] shape at 10M rows (one GPU's share of the 100M x 12 frame on 8 GPUs is 12.5M): 8 integer columns
+    (two with NAs) + 4 Zipf categoricals with 300 / 300 / 5000 / 20000 levels, gaussian, depth 5, nbins 20, nbins_cats 1024."""
+    import oracle_lib as O
+    P = h2ot_lib.pkg()
+    N = 10_000_000
+    rng = np.random.default_rng(42)
+    ranges = [(1987, 2008), (1, 12), (1, 31), (1, 7), (0, 2400), (0, 2400), (-60, 600), (11, 4983)]
+    cards = [300, 300, 5000, 20000]
+    cols, cats = [], {}
+    y = np.zeros(N)
+    for c in range(12):
+        if c < 8:
+            lo, hi = ranges[c]
+            v = rng.integers(lo, hi + 1, N).astype(np.float64)
+            if c in (4, 6):
+                v[rng.random(N) < 0.02] = np.nan
+            if c in (5, 6):
+                y += np.nan_to_num(v) * (0.01 if c == 5 else 0.5)
+        else:
+            card = cards[c - 8]
+            v = np.minimum(rng.zipf(1.3, N) - 1, card - 1).astype(np.float64)
+            y += (v % 7) * 2.0
+            cats[c] = card
+        cols.append(v)
+    y += rng.normal(size=N) * 10
+    y = y.astype(np.float32).astype(np.float64)
+    kw = dict(ntrees=2, max_depth=5, nbins=20, nbins_cats=1024, seed=1234)
+    gm = P.GBM(distribution="gaussian", nclass=1, **kw)
+    gm.load(cols, y, categorical=cats)
+    gm.capture_levels(True)
+    gm.train()
+    X = np.stack(cols, axis=1)
+    fr = O.Frame(X, y, cat_cards=cats)
+    del X
+    nt = _oracle_threads()
+    om = O.Model(fr, O.default_params(family=O.GAUSSIAN, nclass=1, nthreads=nt, chunk_rows=max(4096, N // (4 * nt)), **kw), capture=True)
+    st = h2ot_lib.compare_models(gm, om)
+    assert st["levels"] == 10, st
+    gm.close()
