@@ -110,7 +110,7 @@ ENGINE_SYMBOLS = [
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_get_gamma_bounds", "h2ot_set_gamma_bounds", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
-    "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64",
+    "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64", "h2ot_reserve_exchange",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end",
 ]
@@ -180,6 +180,7 @@ def load():
     L.h2ot_comm_unique_id.argtypes = [vp]
     L.h2ot_comm_init.argtypes = [vp, i32, i32, vp]
     L.h2ot_allreduce_host_f64.argtypes = [vp, vp, i64, i32]
+    L.h2ot_reserve_exchange.argtypes = [vp, i64, i64, i64]
     L.h2ot_get_weight_bound.argtypes = [vp, C.POINTER(dbl)]
     L.h2ot_set_weight_bound.argtypes = [vp, dbl]
     L.h2ot_debug_bin_codes.argtypes = [vp, i32, C.POINTER(HistDesc), vp]

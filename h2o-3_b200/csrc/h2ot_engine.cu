@@ -181,6 +181,7 @@ struct h2ot_engine {
   std::vector<double> col_conc;    // per column: chance that two rows of the root share a bin (0 until a root level ran)
   int steps_pending = 0;  // h2ot_level_step_begin calls not yet ended
   int hist_mode = 0;
+  bool no_agg = false;             // H2OT_NO_AGG=1: never aggregate few-valued columns inside the warp (A/B timing)
   int smem_budget_kb = 0;  // 0: automatic
   Nccl nccl;
   // peer-memory exchange (k_xreduce.cuh): [in: xr_cap words][out: xr_cap words][flags: kXrMaxWorld words]
@@ -192,6 +193,10 @@ struct h2ot_engine {
   unsigned long long xr_epoch = 0;
   int* xr_err = nullptr;
   int* xr_err_host = nullptr;  // pinned mirror of xr_err, refreshed after every exchange
+  // persistent scratch of the small host-side all-reduces (h2ot_allreduce_host_f64) and of the rank barrier
+  DBuf<double> ar_dev;
+  double* ar_host = nullptr;  // pinned
+  size_t ar_host_cap = 0;
 };
 
 namespace {
@@ -216,6 +221,7 @@ int check(h2ot_engine* h) {
   } while (0)
 
 void xr_release(h2ot_engine* h);
+int xr_rank_barrier(h2ot_engine* h);
 int xr_ensure(h2ot_engine* h, size_t words);
 int xr_allreduce(h2ot_engine* h, long long n_sums, long long n);
 
@@ -271,11 +277,13 @@ int grid_for(h2ot_engine* h, int64_t n, int block, int per_sm = 8) {
   int64_t cap = (int64_t)h->sm_count * per_sm;
   return (int)std::max<int64_t>(1, std::min(need, cap));
 }
-int exponent_for(double bound, int bitsN) {  // 2^e scale such that N * bound * 2^e <= 2^62
+// 2^e scale such that N * bound * 2^e <= 2^62 and, when cap_bits > 0, bound * 2^e <= 2^cap_bits
+int exponent_for(double bound, int bitsN, int cap_bits = 0) {
   if (!(bound > 0) || std::isinf(bound)) bound = 1.0;
   int e2;
   std::frexp(bound, &e2);  // bound <= 2^e2
   int e = 62 - bitsN - e2;
+  if (cap_bits > 0) e = std::min(e, cap_bits - e2);
   return std::max(-900, std::min(900, e));
 }
 
@@ -319,6 +327,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   h->sm_count = prop.multiProcessorCount;
   h->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
   if (const char* s = getenv("H2OT_SMEM_BUDGET_KB")) h->smem_budget_kb = atoi(s);
+  if (const char* s = getenv("H2OT_NO_AGG")) h->no_agg = atoi(s) != 0;
   CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   h->cols.resize(h->C);
   h->col_conc.assign(h->C, 0.0);
@@ -364,12 +373,12 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   // opt in to the large dynamic shared memory carve-out once
 #define H2OT_OPTIN(ST)                                                                                                                      \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));   \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));   \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
   H2OT_OPTIN(H2OT_STORE_F32);
   H2OT_OPTIN(H2OT_STORE_F64);
   H2OT_OPTIN(H2OT_STORE_U8);
@@ -400,7 +409,10 @@ int h2ot_destroy(h2ot_engine* h) {
   if (!h) return H2OT_OK;
   cudaSetDevice(h->cfg.device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  xr_release(h);  // collective when peers have mapped the buffer: needs the communicator
   if (h->nccl.comm && h->nccl.CommDestroy && !h->nccl.shared) h->nccl.CommDestroy(h->nccl.comm);
+  h->ar_dev.release();
+  if (h->ar_host) cudaFreeHost(h->ar_host);
   for (Column& c : h->cols) {
     c.data = nullptr;
   }
@@ -412,7 +424,6 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->w) cudaFree(h->w);
   if (h->off) cudaFree(h->off);
   if (h->oobt) cudaFree(h->oobt);
-  xr_release(h);
   if (h->xr_err) cudaFree(h->xr_err);
   if (h->xr_err_host) cudaFreeHost(h->xr_err_host);
   for (TreeState& t : h->ts) {
@@ -874,7 +885,9 @@ int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const double b = t.work_bound > 0 ? t.work_bound : 1.0;
   t.ey = exponent_for(h->w_max * b, bitsN);
-  t.eyy = exponent_for(h->w_max * b * b, bitsN);
+  // unit weights: the high half of a wYY addend shares a 32-bit word with the row count in the shared-memory histograms
+  // (k_level.cuh, kCntShift), which holds for addends below 2^38 -- the width every frame of 2^24 rows or more has anyway
+  t.eyy = exponent_for(h->w_max * b * b, bitsN, h->w ? 0 : 38);
   if (sample_rate < 1.0) {
     TRY(t_begin(h, &h->stats.ms_sample));
     sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed,
@@ -956,12 +969,31 @@ int nccl_rc(h2ot_engine* h, int rc, const char* what) {
   H2OT_FAIL(H2OT_ERR_COMM, m);
 }
 
+// Every rank has finished all work it enqueued before this call (a one-word all-reduce on the stream, then a synchronise:
+// the collective completes on this rank only once every rank's stream has reached it).
+int xr_rank_barrier(h2ot_engine* h) {
+  if (h->nccl.world <= 1 || !h->nccl.comm || !h->nccl.AllReduce) return H2OT_OK;
+  TRY(h->ar_dev.ensure(64));
+  TRY(nccl_rc(h, h->nccl.AllReduce(h->ar_dev.p, h->ar_dev.p, 1, /*ncclFloat64*/ 8, /*ncclSum*/ 0, h->nccl.comm, h->stream), "ncclAllReduce(barrier)"));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return H2OT_OK;
+}
+
+// Unmaps the peers' exchange buffers and frees this rank's. A buffer that other processes have mapped must not be freed
+// while a peer may still read it or still holds the mapping, so the release is collective: barrier (nobody reads any more),
+// close the imported handles, barrier (nobody holds a mapping of ours any more), free.
 void xr_release(h2ot_engine* h) {
+  const bool shared = h->xr_buf && h->nccl.world > 1;
+  if (shared) {
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    xr_rank_barrier(h);
+  }
   for (int p = 0; p < kXrMaxWorld; p++)
     if (h->xr_opened[p]) {
       cudaIpcCloseMemHandle(h->xr_opened[p]);
       h->xr_opened[p] = nullptr;
     }
+  if (shared) xr_rank_barrier(h);
   if (h->xr_buf) cudaFree(h->xr_buf);
   h->xr_buf = nullptr;
   h->xr_cap = 0;
@@ -978,7 +1010,7 @@ int xr_ensure(h2ot_engine* h, size_t words) {
     return H2OT_ERR_UNSUPPORTED;
   }
   CUDA_TRY(cudaStreamSynchronize(h->stream));
-  xr_release(h);
+  xr_release(h);  // collective: every rank grows at the same call, and nobody frees a buffer a peer still reads or maps
   const size_t cap = std::max<size_t>(words * 2, 1 << 16);
   const size_t total = (2 * cap + kXrMaxWorld) * sizeof(unsigned long long);
   CUDA_TRY(cudaMalloc(&h->xr_buf, total));
@@ -1088,7 +1120,8 @@ int desc_split_points(const TreeState& t, const h2ot_hist_desc& s, DescDev& d) {
 // Places every active (leaf, col) histogram: global bin offsets, packed-vals offsets, shared-memory groups.
 int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs) {
   const int C = h->C;
-  const int WPB = h->w ? 7 : 5;
+  const int WPB = h->w ? 7 : 5;                      // leaf-major kernel (k_sparse.cuh): interleaved words per bin
+  const int WPD = h->w ? kPlanesW : kPlanesUnit;     // column-major kernel (k_level.cuh): accumulator planes per pair
   t.h_descs.assign((size_t)L * C, DescDev{});
   t.total_bins = 0;
   t.total_vals = 0;
@@ -1123,7 +1156,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       d.voff = t.total_vals;
       t.total_bins += s.nbin + 1;
       t.total_vals += (int64_t)(s.nbin + 1) * 3;
-      col_words[c] += (int64_t)(s.nbin + 1) * WPB;
+      col_words[c] += (int64_t)(s.nbin + 1);  // bins; scaled to words below, where the kernel is known
       t.max_split_nbin = std::max(t.max_split_nbin, (int)s.nbin);
       if ((s.flags & H2OT_DESC_ISCAT) && s.step == 1.0) t.any_cat = true;
       if (s.flags & H2OT_DESC_CHECKFLOAT) t.any_checkfloat = true;
@@ -1131,12 +1164,9 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
   auto fixed_bytes_l = [&](int ncg, int storage, int nleaves) {
     return (size_t)ncg * nleaves * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + 3 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);
+           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * kPlanesW * sizeof(uint32_t);  // + the per-lane sink words
   };
-  auto fixed_bytes = [&](int ncg, int storage) {
-    return (size_t)ncg * L * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + 3 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
-  };
+  auto fixed_bytes = [&](int ncg, int storage) { return fixed_bytes_l(ncg, storage, L); };
   const size_t full_budget = (size_t)h->max_smem_optin;
   // the kernel runs one 1024-thread CTA per SM (64 registers/thread), so a CTA may use the whole opt-in carve-out
   size_t budget = full_budget;
@@ -1248,11 +1278,18 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       }
     }
   }
-  // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses: give them 2 or 4
-  // replicas of their histograms (lanes pick one by lane id; the replicas are summed when the CTA merges) where that fits.
-  std::vector<int> col_rep(C, 1);
+  // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses. With unit weights the
+  // worst of them (a warp's 32 rows expected on 4 words or fewer: binary and few-valued columns on the first levels) are
+  // aggregated inside the warp before shared memory is touched; the others get 2 to 32 replicas of their histograms (lanes
+  // pick one by lane id; the replicas are summed when the CTA merges) where that fits.
+  std::vector<int> col_rep(C, 1), col_agg(C, 0);
   for (int c = 0; c < C; c++) {
+    col_words[c] *= WPD;
     if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
+    if (!h->w && h->col_conc[c] * 32.0 / (double)L >= 4.0 && !h->no_agg) {
+      col_agg[c] = 1;
+      continue;
+    }
     const double excess = 8.0 * h->col_conc[c] / (double)L;
     int rep = 1;
     while (rep < 32 && excess / rep >= 0.4) rep <<= 1;
@@ -1294,7 +1331,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     std::vector<std::vector<int>> groups;
     std::vector<double> gcost;
     std::vector<std::pair<int, int>> granges;  // leaf range [begin, count) of each group
-    auto cost_of = [&](int c) { return 1.0 + 8.0 * h->col_conc[c] / ((double)L * col_rep[c]); };
+    auto cost_of = [&](int c) { return col_agg[c] ? 1.0 : 1.0 + 8.0 * h->col_conc[c] / ((double)L * col_rep[c]); };
     if (!cols.empty()) {
     // Cost model: a column's atomics serialise when rows of a warp share a bin; with c = chance that two rows of the
     // root share a bin (measured by the last root level) and L leaves, cost ~ 1 + 8 c / L (fits the measured 3.6 vs 14
@@ -1351,7 +1388,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     // a column whose leaves x bins exceed shared memory: one group per leaf range that fits (rows of other ranges are skipped)
     for (int c : split_cols[st]) {
       size_t widest = 0;
-      for (int l = 0; l < L; l++) widest = std::max(widest, (size_t)std::max(t.h_descs[(size_t)l * C + c].nbin + 1, 0) * WPB);
+      for (int l = 0; l < L; l++) widest = std::max(widest, (size_t)std::max(t.h_descs[(size_t)l * C + c].nbin + 1, 0) * WPD);
       if (widest * 4 + fixed_bytes_l(1, st, 1) > full_budget) {  // a single (leaf, column) histogram is too wide: L2 atomics
         glob_cols.push_back(c);
         continue;
@@ -1362,7 +1399,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
         int l1 = l0;
         while (l1 < L) {
           const DescDev& d = t.h_descs[(size_t)l1 * C + c];
-          const size_t nw = words + (d.nbin >= 0 ? (size_t)(d.nbin + 1) * WPB : 0);
+          const size_t nw = words + (d.nbin >= 0 ? (size_t)(d.nbin + 1) * WPD : 0);
           if (l1 > l0 && nw * 4 + fixed_bytes_l(1, st, l1 + 1 - l0) > budget) break;
           words = nw;
           l1++;
@@ -1405,12 +1442,12 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       for (int c : g) {
         int lg = 0;
         while ((1 << lg) < col_rep[c]) lg++;
-        t.h_group_cols.push_back(c | (lg << 24));
+        t.h_group_cols.push_back(c | (lg << 24) | (col_agg[c] << 29));
         for (int l = granges[gi].first; l < granges[gi].first + granges[gi].second; l++) {
           DescDev& d = t.h_descs[(size_t)l * C + c];
           if (d.nbin < 0) continue;
           d.smem_off = off;
-          off += (d.nbin + 1) * WPB * col_rep[c];
+          off += (d.nbin + 1) * WPD * col_rep[c];
         }
       }
       gd.smem_words = off;
@@ -1595,15 +1632,15 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     const int grid = t.bucket_ctas[st];
     (void)n_tiles;
     const size_t sm = t.smem_bytes;
-#define H2OT_LAUNCH_HIST(ST)                                                                                         \
-  if (h->w) {                                                                                                        \
-    if (t.any_checkfloat) hist_smem_kernel<7, true, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
-    else if (n_leaves == 1) hist_smem_kernel<7, true, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
-    else hist_smem_kernel<7, true, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
-  } else {                                                                                                           \
-    if (t.any_checkfloat) hist_smem_kernel<5, false, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
-    else if (n_leaves == 1) hist_smem_kernel<5, false, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);  \
-    else hist_smem_kernel<5, false, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
+#define H2OT_LAUNCH_HIST(ST)                                                                                      \
+  if (h->w) {                                                                                                     \
+    if (t.any_checkfloat) hist_smem_kernel<true, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
+    else if (n_leaves == 1) hist_smem_kernel<true, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
+    else hist_smem_kernel<true, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
+  } else {                                                                                                        \
+    if (t.any_checkfloat) hist_smem_kernel<false, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
+    else if (n_leaves == 1) hist_smem_kernel<false, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);  \
+    else hist_smem_kernel<false, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
   }
     switch (st) {
       case H2OT_STORE_F32: H2OT_LAUNCH_HIST(H2OT_STORE_F32); break;
@@ -2106,14 +2143,32 @@ int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8
 int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op) {
   CHECK_ENGINE(h);
   if (h->nccl.world <= 1 || !h->nccl.comm) return H2OT_OK;
-  DBuf<double> tmp;
-  TRY(tmp.ensure(n));
-  TRY(h2d(h, tmp.p, inout, (size_t)n * sizeof(double)));
-  TRY(nccl_check(h, h->nccl.AllReduce(tmp.p, tmp.p, (size_t)n, /*ncclFloat64*/ 8, op == 1 ? 2 : 0, h->nccl.comm, h->stream), "ncclAllReduce(f64)"));
-  TRY(d2h(h, inout, tmp.p, (size_t)n * sizeof(double)));
-  int r = finish_call(h);
-  tmp.release();
+  if (n <= 0 || !inout) H2OT_FAIL(H2OT_ERR_INVALID, "bad arguments");
+  // persistent device + pinned scratch: this runs twice per tree, an allocation per call would cost more than the collective
+  TRY(h->ar_dev.ensure(std::max<size_t>((size_t)n, 64)));
+  if ((size_t)n > h->ar_host_cap) {
+    if (h->ar_host) cudaFreeHost(h->ar_host);
+    h->ar_host = nullptr;
+    h->ar_host_cap = 0;
+    const size_t cap = std::max<size_t>((size_t)n * 2, 256);
+    CUDA_TRY(cudaMallocHost(&h->ar_host, cap * sizeof(double)));
+    h->ar_host_cap = cap;
+  }
+  memcpy(h->ar_host, inout, (size_t)n * sizeof(double));
+  TRY(h2d(h, h->ar_dev.p, h->ar_host, (size_t)n * sizeof(double)));
+  TRY(nccl_check(h, h->nccl.AllReduce(h->ar_dev.p, h->ar_dev.p, (size_t)n, /*ncclFloat64*/ 8, op == 1 ? 2 : 0, h->nccl.comm, h->stream), "ncclAllReduce(f64)"));
+  TRY(d2h(h, h->ar_host, h->ar_dev.p, (size_t)n * sizeof(double)));
+  const int r = finish_call(h);
+  if (r == H2OT_OK) memcpy(inout, h->ar_host, (size_t)n * sizeof(double));
   return r;
+}
+
+int h2ot_reserve_exchange(h2ot_engine* h, int64_t max_level_bins, int64_t max_level_pairs, int64_t max_leaves) {
+  CHECK_ENGINE(h);
+  if (max_level_bins < 0 || max_level_pairs < 0 || max_leaves < 0) H2OT_FAIL(H2OT_ERR_INVALID, "negative sizes");
+  if (!(h->xr_enabled && !h->xr_failed && h->nccl.world > 1)) return H2OT_OK;
+  const int rc = xr_ensure(h, (size_t)max_level_bins * 3 + (size_t)max_leaves + (size_t)max_level_pairs * 2);
+  return rc == H2OT_ERR_UNSUPPORTED ? H2OT_OK : rc;  // no peer mapping here: the NCCL collectives serve the build
 }
 
 // ------------------------------------------------------------------------------------------------ diagnostics

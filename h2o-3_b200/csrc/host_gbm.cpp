@@ -975,6 +975,28 @@ int h2ot_gbm_init(h2ot_gbm* g) {
     GTRY(allreduce(g, &wb, 1, 1));
     GTRY(h2ot_set_weight_bound(g->eng, wb));
   }
+  // Size the cross-rank exchange of the level histograms once, for the widest level this model can have: 2^d leaves at depth
+  // d, each column with max(nbins_top_level >> d, nbins) bins (nbins_cats for categoricals, fewer for narrow integer columns)
+  // plus the NA bucket. Levels beyond the cap (very deep forests) regrow the buffer when they get there.
+  if (g->world > 1) {
+    int64_t best_bins = 0, best_leaves = 1;
+    const int64_t cap_words = (int64_t)32 << 20;
+    for (int d = 0; d < g->p.max_depth; d++) {
+      const int64_t leaves = (int64_t)1 << std::min(d, 40);
+      int64_t per_leaf = 0;
+      for (int c = 0; c < C; c++) {
+        const ColMeta& m = g->cols[c];
+        int64_t nb = m.is_cat ? g->p.nbins_cats : std::max(g->p.nbins_top_level >> std::min(d, 30), g->p.nbins);
+        if ((m.is_int || m.is_cat) && !std::isnan(m.min)) nb = std::min<int64_t>(nb, (int64_t)std::max(1.0, (m.is_cat ? m.cardinality : m.max - m.min + 1)));
+        per_leaf += nb + 1;
+      }
+      const int64_t words = leaves * per_leaf * 3 + leaves * (2 * C + 1);
+      if (words > cap_words) break;
+      if (leaves * per_leaf > best_bins) best_bins = leaves * per_leaf;
+      best_leaves = std::max(best_leaves, leaves);
+    }
+    GTRY(h2ot_reserve_exchange(g->eng, best_bins, best_leaves * C, best_leaves));
+  }
   // GBM.init / initializeModelSpecifics (T/gbm/GBM.java:254-312) ; DRF: T/drf/DRF.java:114-153
   const bool drf = g->p.algo == H2OT_ALGO_DRF;
   g->mtry_per_tree = std::max(1, d2i(g->p.col_sample_rate_per_tree * C));

@@ -319,6 +319,14 @@ int h2ot_comm_unique_id(uint8_t out_id[H2OT_COMM_ID_BYTES]);
  * the same id on the same device (an id can start only one NCCL communicator); it lives until the process exits. */
 int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
 int h2ot_allreduce_host_f64(h2ot_engine* h, double* inout, int64_t n, int32_t op /*0 sum, 1 max*/);
+/* Sizes the buffer the ranks exchange their level histograms through (the MRTask.reduce of ScoreBuildHistogram2,
+ * h2o-algos/src/main/java/hex/tree/ScoreBuildHistogram.java:74-88) once, for the widest level the model can have:
+ * max_level_bins = bins (NA buckets included) over all (leaf, column) histograms of one level, max_level_pairs = leaves x columns,
+ * max_leaves = leaves of one level. COLLECTIVE: every rank calls it with the same numbers, after h2ot_comm_init. Optional -- a level
+ * that outgrows the buffer regrows it (also collectively: all ranks reach that level together) -- but mapping the peers' buffers
+ * costs milliseconds, which belongs in the set-up and not in the first trees. No-op on one GPU or with H2OT_XREDUCE=0.
+ * h2ot_destroy of engines that share a communicator is collective as well (the mapped buffers are released in step). */
+int h2ot_reserve_exchange(h2ot_engine* h, int64_t max_level_bins, int64_t max_level_pairs, int64_t max_leaves);
 /* max |weight| over the local rows (known after h2ot_finalize_frame). With several ranks the host takes the max over
  * ranks and sets it back, so that every rank uses the same fixed-point scale for the w accumulator. */
 int h2ot_get_weight_bound(h2ot_engine* h, double* out);

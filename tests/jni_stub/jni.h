@@ -1,0 +1,44 @@
+/* Stand-in for <jni.h> with only the types and JNIEnv entries integration/h2otree_jni.c uses. It exists so that the shim can be
+ * syntax- and type-checked in an image without a JDK (tests/test_capi_load.py); it is NOT a JNI implementation. The names,
+ * argument orders and types follow the JNI specification (Java Native Interface 6.0, chapter 4 "JNI Functions"). */
+#ifndef H2OT_JNI_STUB_H
+#define H2OT_JNI_STUB_H
+#include <stdint.h>
+typedef int32_t jint;
+typedef int64_t jlong;
+typedef int8_t jbyte;
+typedef uint8_t jboolean;
+typedef float jfloat;
+typedef double jdouble;
+typedef jint jsize;
+typedef void* jobject;
+typedef jobject jclass;
+typedef jobject jarray;
+typedef jarray jbyteArray;
+typedef jarray jintArray;
+typedef jarray jlongArray;
+typedef jarray jfloatArray;
+typedef jarray jdoubleArray;
+#define JNIEXPORT
+#define JNICALL
+#define JNI_ABORT 2
+struct JNINativeInterface_;
+typedef const struct JNINativeInterface_* JNIEnv;
+struct JNINativeInterface_ {
+  jclass (*FindClass)(JNIEnv*, const char*);
+  jint (*ThrowNew)(JNIEnv*, jclass, const char*);
+  jsize (*GetArrayLength)(JNIEnv*, jarray);
+  void* (*GetDirectBufferAddress)(JNIEnv*, jobject);
+  jbyte* (*GetByteArrayElements)(JNIEnv*, jbyteArray, jboolean*);
+  jint* (*GetIntArrayElements)(JNIEnv*, jintArray, jboolean*);
+  jlong* (*GetLongArrayElements)(JNIEnv*, jlongArray, jboolean*);
+  jfloat* (*GetFloatArrayElements)(JNIEnv*, jfloatArray, jboolean*);
+  jdouble* (*GetDoubleArrayElements)(JNIEnv*, jdoubleArray, jboolean*);
+  void (*ReleaseByteArrayElements)(JNIEnv*, jbyteArray, jbyte*, jint);
+  void (*ReleaseIntArrayElements)(JNIEnv*, jintArray, jint*, jint);
+  void (*ReleaseLongArrayElements)(JNIEnv*, jlongArray, jlong*, jint);
+  void (*ReleaseFloatArrayElements)(JNIEnv*, jfloatArray, jfloat*, jint);
+  void (*ReleaseDoubleArrayElements)(JNIEnv*, jdoubleArray, jdouble*, jint);
+  void (*SetDoubleArrayRegion)(JNIEnv*, jdoubleArray, jsize, jsize, const jdouble*);
+};
+#endif

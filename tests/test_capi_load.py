@@ -53,3 +53,19 @@ def test_product_does_not_reference_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "oracle" not in txt.lower() or f == "__init__.py" and "oracle" not in txt.lower(), f
+
+
+def test_jni_shim_compiles_against_stub_header():
+    """integration/h2otree_jni.c is the C side of the Java binding INTEGRATION.md declares. No JDK exists in this image, so it is
+    type-checked against a stand-in jni.h (tests/jni_stub) -- and every native method of the Java class must have its wrapper."""
+    import subprocess
+    shim = os.path.join(ROOT, "integration", "h2otree_jni.c")
+    r = subprocess.run(["gcc", "-std=c11", "-Wall", "-Werror", "-Wno-unused-parameter", "-fsyntax-only", "-I" + os.path.join(ROOT, "tests", "jni_stub"),
+                        "-I" + os.path.join(ROOT, "include"), shim], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    java = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    natives = set(re.findall(r"public static native \w+\s+(\w+)\(", java))
+    assert len(natives) >= 30
+    src = open(shim).read()
+    wrapped = set(re.findall(r"Java_hex_tree_gpu_H2OTreeB200_(\w+)\(", src)) | set(re.findall(r"\bFN\((\w+)\)", src))
+    assert natives <= wrapped, sorted(natives - wrapped)

@@ -366,15 +366,15 @@ int main(int argc, char** argv){
     printf("%-78s %8.3f ms  %6.3f ns/Kitem  %6.2f SM-clk per warp-item (32 items) @1.9GHz  %7.1f Gitem/s\n", name, ms, ms * 1e6 / (items / 1e3),
            ms * 1e-3 * clk * sms / (items / 32.0), items / ms * 1e-6);
   };
-  CK(cudaFuncSetAttribute(root_kernel<5,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<4,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<4,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<3,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<3,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<0,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<0,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<4,0,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  CK(cudaFuncSetAttribute(root_kernel<4,1,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<5,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<4,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<4,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<3,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<3,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<0,0,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<0,1,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<4,0,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+  CK(cudaFuncSetAttribute(root_kernel<4,1,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   {
     const int idx[9] = {0, 1, 2, 3, 4, 5, 6, 7, 8};
     set_cols(idx, 9, 1024);
@@ -388,9 +388,9 @@ int main(int argc, char** argv){
     report("4 atomics, planes, fp32 pre-filter", timeit([&]{ root_kernel<4,1,0><<<sms, 1024, s4>>>(a); }), items);
     report("3 atomics [y32][yy32][cnt|carries], fp64", timeit([&]{ root_kernel<3,0,0><<<sms, 1024, s3>>>(a); }), items);
     report("3 atomics, fp32 pre-filter", timeit([&]{ root_kernel<3,1,0><<<sms, 1024, s3>>>(a); }), items);
-    CK(cudaFuncSetAttribute(root_kernel<0,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(root_kernel<4,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(root_kernel<3,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CK(cudaFuncSetAttribute(root_kernel<0,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    CK(cudaFuncSetAttribute(root_kernel<4,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    CK(cudaFuncSetAttribute(root_kernel<3,0,0,2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     report("no atomics, fp64, TWO columns prefetched", timeit([&]{ root_kernel<0,0,0,2><<<sms, 1024, s3>>>(a); }), items);
     report("4 atomics, planes, fp64, TWO columns prefetched", timeit([&]{ root_kernel<4,0,0,2><<<sms, 1024, s4>>>(a); }), items);
     report("3 atomics, fp64, TWO columns prefetched", timeit([&]{ root_kernel<3,0,0,2><<<sms, 1024, s3>>>(a); }), items);
@@ -418,10 +418,10 @@ int main(int argc, char** argv){
     set_cols(idx, 7, 256);
     const double items = (double)n_pad * 7;
     printf("--- level 5: 32 leaves x 257 bins, one column per CTA (7 columns x 21 CTAs), records in shared memory\n");
-    CK(cudaFuncSetAttribute(deep_kernel<5,6,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(deep_kernel<4,6,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(deep_kernel<4,4,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CK(cudaFuncSetAttribute(deep_kernel<4,4,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CK(cudaFuncSetAttribute(deep_kernel<5,6,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    CK(cudaFuncSetAttribute(deep_kernel<4,6,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    CK(cudaFuncSetAttribute(deep_kernel<4,4,0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    CK(cudaFuncSetAttribute(deep_kernel<4,4,1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     const size_t s5 = (size_t)(257 * 5 * 32 + 12 * 32 + 128) * 4, s4 = (size_t)(257 * 4 * 32 + 12 * 32 + 128) * 4;
     report("5 atomics, six 32-bit record loads, value test for min/max (round 1)", timeit([&]{ deep_kernel<5,6,0><<<147, 1024, s5>>>(a, 7); }), items);
     report("4 atomics, six 32-bit record loads", timeit([&]{ deep_kernel<4,6,0><<<147, 1024, s4>>>(a, 7); }), items);
