@@ -112,13 +112,13 @@ ENGINE_SYMBOLS = [
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64", "h2ot_reserve_exchange",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end",
+    "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end",
 ]
 GBM_SYMBOLS = [
     "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
-    "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
+    "h2ot_gbm_tree_compress", "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_auc", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
     "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
     "h2ot_hostcheck_hist", "h2ot_hostcheck_find_max_ex", "h2ot_hostcheck_pcg_next_long", "h2ot_hostcheck_pcg_bounded",
     "h2ot_hostcheck_score_cols",
@@ -204,9 +204,12 @@ def load():
     L.h2ot_gbm_tree_leaves_start.argtypes = [vp, i32, i32]
     L.h2ot_gbm_tree_nodes.argtypes = [vp, i32, i32, vp]
     L.h2ot_gbm_predictions.argtypes = [vp, i32, vp]
+    L.h2ot_gbm_tree_compress.argtypes = [vp, i32, i32, vp, i64, C.POINTER(i64), vp, i64, C.POINTER(i64)]
     L.h2ot_gbm_varimp.argtypes = [vp, vp]
     L.h2ot_gbm_oobt.argtypes = [vp, vp]
     L.h2ot_gbm_score.argtypes = [vp, C.POINTER(dbl), C.POINTER(dbl)]
+    L.h2ot_gbm_auc.argtypes = [vp, C.POINTER(dbl), C.POINTER(i32), vp, vp, vp, C.POINTER(i64)]
+    L.h2ot_auc_builders.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i64), vp]
     L.h2ot_score_metrics.argtypes = [vp, vp]
     L.h2ot_gbm_timing_get.argtypes = [vp, C.POINTER(GbmTiming)]
     L.h2ot_gbm_engine.argtypes = [vp]
@@ -582,6 +585,15 @@ class GBM:
         _check(self.L.h2ot_gbm_tree_nodes(self.g, t, k, C.cast(out, C.c_void_p)))
         return out, self.L.h2ot_gbm_tree_leaves_start(self.g, t, k)
 
+    def compressed_tree(self, t, k=0):
+        """(CompressedTree._bits, auxiliary bytes) of tree (t, k): DTree.compress, the stream SharedTreeMojoModel.scoreTree reads."""
+        nb, na = C.c_int64(0), C.c_int64(0)
+        _check(self.L.h2ot_gbm_tree_compress(self.g, t, k, None, 0, C.byref(nb), None, 0, C.byref(na)))
+        bits = np.zeros(max(1, nb.value), dtype=np.uint8)
+        aux = np.zeros(max(1, na.value), dtype=np.uint8)
+        _check(self.L.h2ot_gbm_tree_compress(self.g, t, k, _p(bits), bits.size, C.byref(nb), _p(aux), aux.size, C.byref(na)))
+        return bits[:nb.value].tobytes(), aux[:na.value].tobytes()
+
     def predictions(self, k=0, out=None):
         """Tree_k column (link space). out: optional float64[nrows] buffer to fill (e.g. pinned host memory)."""
         if out is None:
@@ -609,6 +621,14 @@ class GBM:
         mse, ll = C.c_double(), C.c_double()
         _check(self.L.h2ot_gbm_score(self.g, C.byref(mse), C.byref(ll)))
         return dict(mse=mse.value, logloss=ll.value)
+
+    def auc(self):
+        """Training AUC as hex.AUC2 computes it: per-chunk AUCBuilders on the device, folded with AUCBuilder.reduce.
+        Returns dict(auc, ths, tps, fps, chunk_rows)."""
+        a, n, cr = C.c_double(), C.c_int32(), C.c_int64()
+        ths, tps, fps = (np.zeros(400) for _ in range(3))
+        _check(self.L.h2ot_gbm_auc(self.g, C.byref(a), C.byref(n), _p(ths), _p(tps), _p(fps), C.byref(cr)))
+        return dict(auc=a.value, ths=ths[:n.value], tps=tps[:n.value], fps=fps[:n.value], chunk_rows=cr.value)
 
     def varimp(self):
         out = np.zeros(self.ncols, dtype=np.float32)

@@ -18,6 +18,7 @@
 #include "k_rows.cuh"
 #include "k_split.cuh"
 #include "k_xreduce.cuh"
+#include "k_auc.cuh"
 
 namespace h2ot {
 
@@ -2025,6 +2026,35 @@ int h2ot_score_metrics(h2ot_engine* h, h2ot_metrics* out) {
   out->sumsqe = acc[2];
   out->logloss = acc[3];
   return H2OT_OK;
+}
+
+int h2ot_auc_builders(h2ot_engine* h, int32_t max_chunks, int32_t* out_n_chunks, int64_t* out_chunk_rows, double* out) {
+  CHECK_ENGINE(h);
+  if (!out || !out_n_chunks || !out_chunk_rows || max_chunks < 1) H2OT_FAIL(H2OT_ERR_INVALID, "bad arguments");
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  if (h->cfg.family != H2OT_FAMILY_BERNOULLI) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "AUC2 is the binomial metric: bernoulli models only");
+  // two warps (chunks) per SM unless the caller wants fewer; chunks of whole 32-row groups
+  int64_t n_chunks = std::min<int64_t>(max_chunks, (int64_t)h->sm_count * 2);
+  int64_t chunk_rows = (h->n + n_chunks - 1) / n_chunks;
+  chunk_rows = std::max<int64_t>(32, (chunk_rows + 31) / 32 * 32);
+  n_chunks = (h->n + chunk_rows - 1) / chunk_rows;
+  const size_t stride = 1 + 4 * (size_t)kAucBins;
+  DBuf<double> tmp;
+  TRY(tmp.ensure((size_t)n_chunks * stride));
+  const size_t smem = (size_t)kAucWarpsPerCta * 4 * (kAucCap + 1) * sizeof(double);
+  CUDA_TRY(cudaFuncSetAttribute(auc_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  AucArgs a{h->n, chunk_rows, (int32_t)n_chunks, h->cfg.family, h->cfg.nclass, h->resp, h->w, h->off, h->ts[0].F, tmp.p};
+  // spread the chunks over the SMs: one warp per CTA first, more warps per CTA only when there are more chunks than SMs
+  const int grid = (int)((n_chunks + kAucWarpsPerCta - 1) / kAucWarpsPerCta);
+  auc_build_kernel<<<grid, 32 * kAucWarpsPerCta, smem, h->stream>>>(a);
+  h->stats.launches++;
+  CUDA_TRY(cudaGetLastError());
+  TRY(d2h(h, out, tmp.p, (size_t)n_chunks * stride * sizeof(double)));
+  const int rc = finish_call(h);
+  tmp.release();
+  *out_n_chunks = (int32_t)n_chunks;
+  *out_chunk_rows = chunk_rows;
+  return rc;
 }
 
 // ------------------------------------------------------------------------------------------------ DRF

@@ -303,7 +303,7 @@ struct h2ot_gbm {
   int ncols = 0, K = 1, nclass = 1;
   bool has_w = false, has_off = false, inited = false;
   int device = 0;
-  int world = 1;
+  int world = 1, rank = 0;
   std::vector<ColMeta> cols;
   bool have_y = false, have_w = false, have_off = false;
   double init_f = 0;
@@ -938,6 +938,7 @@ int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o) {
 int h2ot_gbm_comm_init(h2ot_gbm* g, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]) {
   if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
   g->world = world_size;
+  g->rank = rank;
   return h2ot_comm_init(g->eng, world_size, rank, id);
 }
 
@@ -1093,6 +1094,114 @@ int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* ou
   return H2OT_OK;
 }
 
+// DTree.compress (T/DTree.java:972-982): the byte stream SharedTreeMojoModel.scoreTree walks, plus the auxiliary stream
+// (_abAux, :905-916). DecidedNode.size / compress (:845-933), LeafNode.compress (:918-921), IcedBitSet.compress2 / compress3
+// (W/util/IcedBitSet.java:92-111). Children are always created after their parent, so one backwards sweep over the node table
+// gives every subtree's size, node count and type byte; an explicit stack then writes the nodes in pre-order.
+// Two-call protocol: with bits_cap / aux_cap too small nothing is written and the needed lengths come back.
+int h2ot_gbm_tree_compress(h2ot_gbm* g, int32_t tree, int32_t k, uint8_t* bits, int64_t bits_cap, int64_t* bits_len, uint8_t* aux,
+                           int64_t aux_cap, int64_t* aux_len) {
+  if (!g || tree < 0 || tree >= (int)g->trees.size() || k < 0 || k >= g->K) GFAIL(H2OT_ERR_INVALID, "bad tree index");
+  const std::vector<Node>& ns = g->trees[tree][k].nodes;
+  const int n = (int)ns.size();
+  if (n == 0) GFAIL(H2OT_ERR_INVALID, "empty tree");
+  std::vector<int64_t> size((size_t)n, 0);
+  std::vector<int32_t> inner((size_t)n, 0);  // decided nodes of the subtree (leaves count 0)
+  std::vector<uint8_t> type((size_t)n, 0);
+  int64_t n_decided = 0;
+  for (int i = n - 1; i >= 0; i--) {
+    const Node& nd = ns[(size_t)i];
+    if (nd.kind == 2) {
+      size[(size_t)i] = 4;
+      continue;
+    }
+    if (nd.kind != 1 || !nd.has_split) continue;  // unreachable leftovers (a child that never split was replaced by a leaf)
+    const h2ot_split& sp = nd.split;
+    const int l = nd.nids[0], r = nd.nids[1];
+    if (l <= i || r <= i || l >= n || r >= n || size[(size_t)l] == 0 || size[(size_t)r] == 0) GFAIL(H2OT_ERR_INVALID, "tree is not finished");
+    uint8_t ty = sp.equal == 0 ? 0 : (sp.equal == 1 ? 4 : (sp.equal == 2 ? 8 : 12));
+    int64_t sz = (sp.equal == 3 ? 9 + sp.bs_nbytes : 7) + 1;  // type, column, split value or group, NA direction
+    if (sp.nasplit == H2OT_NA_VS_REST) sz -= 4;
+    if (ns[(size_t)l].kind == 2) ty |= 48;
+    else {
+      const int64_t lsz = size[(size_t)l];
+      const int slen = lsz < 256 ? 0 : (lsz < 65535 ? 1 : (lsz < (1 << 24) ? 2 : 3));
+      ty |= (uint8_t)slen;
+      sz += slen + 1;
+    }
+    if (ns[(size_t)r].kind == 2) ty |= (uint8_t)(48 << 2);
+    size[(size_t)i] = sz + size[(size_t)l] + size[(size_t)r];
+    inner[(size_t)i] = 1 + inner[(size_t)l] + inner[(size_t)r];
+    type[(size_t)i] = ty;
+    n_decided++;
+  }
+  const bool stump = ns[0].kind == 2;
+  const int64_t need_bits = size[0] + (stump ? 3 : 0), need_aux = (int64_t)inner[0] * 40;
+  (void)n_decided;
+  if (bits_len) *bits_len = need_bits;
+  if (aux_len) *aux_len = need_aux;
+  if (!bits || bits_cap < need_bits || (aux && aux_cap < need_aux)) return H2OT_OK;
+  uint8_t* b = bits;
+  uint8_t* a = aux;
+  auto put = [](uint8_t*& p, uint32_t v, int nbytes) {
+    for (int i = 0; i < nbytes; i++) *p++ = (uint8_t)(v >> (8 * i));  // AutoBuffer writes in native (little-endian) order
+  };
+  auto putf = [&](uint8_t*& p, float f) {
+    uint32_t v;
+    memcpy(&v, &f, 4);
+    put(p, v, 4);
+  };
+  if (stump) {
+    put(b, 0, 1);
+    put(b, 65535, 2);
+  }
+  std::vector<int> stack;
+  stack.push_back(0);
+  while (!stack.empty()) {
+    const int i = stack.back();
+    stack.pop_back();
+    const Node& nd = ns[(size_t)i];
+    if (nd.kind == 2) {
+      putf(b, nd.pred);
+      continue;
+    }
+    const h2ot_split& sp = nd.split;
+    put(b, type[(size_t)i], 1);
+    put(b, (uint32_t)sp.col, 2);
+    put(b, (uint32_t)sp.nasplit, 1);
+    if (sp.nasplit != H2OT_NA_VS_REST) {
+      if (sp.equal == 0 || sp.equal == 1) putf(b, nd.splat);
+      else if (sp.equal == 2) {
+        for (int j = 0; j < 4; j++) put(b, sp.bs[j], 1);
+      } else {
+        put(b, (uint32_t)sp.bs_bitoff, 2);
+        put(b, (uint32_t)sp.bs_nbits, 4);
+        for (int j = 0; j < sp.bs_nbytes; j++) put(b, sp.bs[j], 1);
+      }
+    }
+    if (a) {
+      put(a, (uint32_t)nd.nid, 4);
+      put(a, (uint32_t)inner[(size_t)nd.nids[0]], 4);
+      putf(a, (float)sp.n0);
+      putf(a, (float)sp.n1);
+      putf(a, (float)sp.p0);
+      putf(a, (float)sp.p1);
+      putf(a, (float)sp.se0);
+      putf(a, (float)sp.se1);
+      put(a, (uint32_t)nd.nids[0], 4);
+      put(a, (uint32_t)nd.nids[1], 4);
+    }
+    if ((type[(size_t)i] & 48) == 0) {
+      const int64_t lsz = size[(size_t)nd.nids[0]];
+      put(b, (uint32_t)lsz, lsz < 256 ? 1 : (lsz < 65535 ? 2 : (lsz < (1 << 24) ? 3 : 4)));
+    }
+    stack.push_back(nd.nids[1]);  // the left subtree is written first
+    stack.push_back(nd.nids[0]);
+  }
+  if (b - bits != need_bits || (aux && a - aux != need_aux)) GFAIL(H2OT_ERR_INVALID, "compressed tree size differs from DecidedNode.size()");
+  return H2OT_OK;
+}
+
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_predictions(g->eng, k, out);
@@ -1163,6 +1272,148 @@ int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss) {
   GTRY(allreduce(g, v, 3, 0));
   if (out_mse) *out_mse = v[1] / v[0];
   if (out_logloss) *out_logloss = v[2] / v[0];
+  return H2OT_OK;
+}
+// ---- AUC2 on the host side of the seam (h2o-core/src/main/java/hex/AUC2.java): the device fills one AUCBuilder per chunk of rows
+// (h2ot_auc_builders == AUC_Impl.map); here they are folded like MRTask.reduce does -- AUCBuilder.reduce (:448-472), mergeOneBin
+// (:483-505), find_smallest_impl (:523-554), dups (:556-565) -- and the AUC2 constructor + compute_auc (:158-190, 262-277) turn
+// the final builder into the number the model reports.
+namespace {
+struct AucFold {
+  int n = 0, ssx = -1;
+  double ths[2 * H2OT_AUC_BINS], sqe[2 * H2OT_AUC_BINS], tps[2 * H2OT_AUC_BINS], fps[2 * H2OT_AUC_BINS];
+  double k(int i) const { return tps[i] + fps[i]; }
+  static double delta_error(double ths1, double n1, double ths0, double n0) {
+    const double delta = (double)((float)ths1 - (float)ths0);
+    if (delta == 0) return 0;
+    return delta * delta * n0 * n1 / (n0 + n1);
+  }
+  static double combine(double ths1, double n1, double ths0, double n0) {
+    const double c = (ths0 * n0 + ths1 * n1) / (n0 + n1);
+    return (std::isnan(c) || std::isinf(c)) ? (ths0 + ths1) / 2 : c;
+  }
+  int smallest() {
+    if (ssx != -1) return ssx;
+    if (n == 1) return ssx = 0;
+    double best = DBL_MAX;
+    int at = -1;
+    for (int i = 0; i + 1 < n; i++) {
+      const double derr = delta_error(ths[i + 1], k(i + 1), ths[i], k(i));
+      if (derr == 0) return ssx = i;
+      const double s = sqe[i] + sqe[i + 1] + derr;
+      if (s < best) { at = i; best = s; }
+    }
+    if (at == -1) {
+      at = 0;
+      double md = ths[1] - ths[0];
+      for (int i = 1; i + 1 < n; i++)
+        if (ths[i + 1] - ths[i] < md) { md = ths[i + 1] - ths[i]; at = i; }
+    }
+    return ssx = at;
+  }
+  bool dups() {
+    for (int i = 0; i + 1 < n; i++)
+      if (delta_error(ths[i + 1], k(i + 1), ths[i], k(i)) == 0) { ssx = i; return true; }
+    return false;
+  }
+  void merge_one() {
+    const int s = smallest();
+    const double k0 = k(s), k1 = k(s + 1);
+    sqe[s] = sqe[s] + sqe[s + 1] + delta_error(ths[s + 1], k1, ths[s], k0);
+    ths[s] = combine(ths[s], k0, ths[s + 1], k1);
+    tps[s] += tps[s + 1];
+    fps[s] += fps[s + 1];
+    for (int i = s + 1; i + 1 < n; i++) { ths[i] = ths[i + 1]; sqe[i] = sqe[i + 1]; tps[i] = tps[i + 1]; fps[i] = fps[i + 1]; }
+    n--;
+    ssx = -1;
+  }
+  // this <- reduce(this, other)
+  void reduce(int on, const double* oths, const double* osqe, const double* otps, const double* ofps) {
+    int x = n - 1, y = on - 1;
+    while (x + y + 1 >= 0) {
+      const bool self = y < 0 || (x >= 0 && ths[x] >= oths[y]);
+      const int d = x + y + 1;
+      if (self) { ths[d] = ths[x]; sqe[d] = sqe[x]; tps[d] = tps[x]; fps[d] = fps[x]; x--; }
+      else { ths[d] = oths[y]; sqe[d] = osqe[y]; tps[d] = otps[y]; fps[d] = ofps[y]; y--; }
+    }
+    n += on;
+    ssx = -1;
+    while (n > H2OT_AUC_BINS || dups()) merge_one();
+  }
+  double auc() const {
+    if (n < 1) return NAN;
+    double p = 0, q = 0;
+    std::vector<double> tp(n), fp(n);
+    for (int i = 0; i < n; i++) {  // reversed: thresholds from 1 down to 0, rolled up
+      p += tps[n - 1 - i];
+      q += fps[n - 1 - i];
+      tp[i] = p;
+      fp[i] = q;
+    }
+    if (fp[n - 1] == 0) return 1.0;
+    if (tp[n - 1] == 0) return 0.0;
+    double tp0 = 0, fp0 = 0, area = 0;
+    for (int i = 0; i < n; i++) {
+      area += (fp[i] - fp0) * (tp[i] + tp0) / 2.0;
+      tp0 = tp[i];
+      fp0 = fp[i];
+    }
+    return area / p / q;
+  }
+};
+}  // namespace
+
+int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_ths, double* out_tps, double* out_fps, int64_t* out_chunk_rows) {
+  if (!g || !out_auc) GFAIL(H2OT_ERR_INVALID, "null argument");
+  if (g->p.algo != H2OT_ALGO_GBM || g->p.family != H2OT_FAMILY_BERNOULLI) GFAIL(H2OT_ERR_UNSUPPORTED, "AUC2 covers bernoulli GBM");
+  const int max_chunks = 4096;
+  std::vector<double> buf((size_t)max_chunks * H2OT_AUC_STRIDE);
+  int32_t nch = 0;
+  int64_t chunk_rows = 0;
+  GTRY(h2ot_auc_builders(g->eng, max_chunks, &nch, &chunk_rows, buf.data()));
+  if (out_chunk_rows) *out_chunk_rows = chunk_rows;
+  std::unique_ptr<AucFold> f(new AucFold());
+  for (int c = 0; c < nch; c++) {
+    const double* o = buf.data() + (size_t)c * H2OT_AUC_STRIDE;
+    const int on = (int)o[0];
+    const double* oths = o + 1;
+    const double* otps = o + 1 + H2OT_AUC_BINS;
+    const double* ofps = o + 1 + 2 * H2OT_AUC_BINS;
+    const double* osqe = o + 1 + 3 * H2OT_AUC_BINS;
+    if (c == 0) {
+      f->n = on;
+      for (int i = 0; i < on; i++) { f->ths[i] = oths[i]; f->sqe[i] = osqe[i]; f->tps[i] = otps[i]; f->fps[i] = ofps[i]; }
+    } else f->reduce(on, oths, osqe, otps, ofps);
+  }
+  if (g->world > 1) {  // every rank's folded builder travels to every rank (slots of a summed array), then folds in rank order
+    const size_t stride = 1 + 4 * (size_t)H2OT_AUC_BINS;
+    std::vector<double> all((size_t)g->world * stride, 0.0);
+    double* mine = all.data() + (size_t)g->rank * stride;
+    mine[0] = f->n;
+    for (int i = 0; i < f->n; i++) {
+      mine[1 + i] = f->ths[i];
+      mine[1 + H2OT_AUC_BINS + i] = f->tps[i];
+      mine[1 + 2 * H2OT_AUC_BINS + i] = f->fps[i];
+      mine[1 + 3 * H2OT_AUC_BINS + i] = f->sqe[i];
+    }
+    GTRY(allreduce(g, all.data(), (int64_t)all.size(), 0));
+    f.reset(new AucFold());
+    for (int r = 0; r < g->world; r++) {
+      const double* o = all.data() + (size_t)r * stride;
+      const int on = (int)o[0];
+      if (r == 0) {
+        f->n = on;
+        for (int i = 0; i < on; i++) { f->ths[i] = o[1 + i]; f->tps[i] = o[1 + H2OT_AUC_BINS + i]; f->fps[i] = o[1 + 2 * H2OT_AUC_BINS + i]; f->sqe[i] = o[1 + 3 * H2OT_AUC_BINS + i]; }
+      } else f->reduce(on, o + 1, o + 1 + 3 * H2OT_AUC_BINS, o + 1 + H2OT_AUC_BINS, o + 1 + 2 * H2OT_AUC_BINS);
+    }
+  }
+  *out_auc = f->auc();
+  if (out_nbins) *out_nbins = f->n;
+  for (int i = 0; i < f->n; i++) {
+    if (out_ths) out_ths[i] = f->ths[i];
+    if (out_tps) out_tps[i] = f->tps[i];
+    if (out_fps) out_fps[i] = f->fps[i];
+  }
   return H2OT_OK;
 }
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {

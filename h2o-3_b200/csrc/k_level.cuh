@@ -375,7 +375,7 @@ __device__ __forceinline__ void hist_items(const HistArgs& a, const ColCtx& cx, 
       // of the reference differ: those items take the exact path.
       const int iv = __float2int_rz(__fmul_rn(__fsub_rn((float)x[j], __uint_as_float(q.y)), __uint_as_float(q.z)));
       bb = iv >> 11;
-      if (((iv + 1) & 2047) <= 1) bb = bin_exact_rec<false>(rec, cx.xbase + (double)x[j], nbin);
+      if (on && !na[j] && ((iv + 1) & 2047) <= 1) bb = bin_exact_rec<false>(rec, cx.xbase + (double)x[j], nbin);
       bb = max(0, min(bb, nbin - 1));
     }
     // min / max of the pair: only values in (or beyond) the end bins seen so far can move them
@@ -437,10 +437,10 @@ __device__ __forceinline__ void hist_items(const HistArgs& a, const ColCtx& cx, 
       if (!has) break;
       const int leader = __ffs(has) - 1;
       uint32_t mine = 0u, mine_ps = 0u;
-      int mine_j = 0;
+      int mine_leaf = 0;  // (selected in the unrolled loop: a run-time index would push leaf[] into local memory)
 #pragma unroll
       for (int j = J0 + R - 1; j >= J0; j--)
-        if ((todo >> j) & 1u) { mine = wd[j]; mine_ps = ps[j]; mine_j = j; }
+        if ((todo >> j) & 1u) { mine = wd[j]; mine_ps = ps[j]; mine_leaf = leaf[j]; }
       const uint32_t wl = __shfl_sync(0xFFFFFFFFu, mine, leader);
       long long sy = 0, sv = 0;
       unsigned cnt = 0u;
@@ -468,7 +468,7 @@ __device__ __forceinline__ void hist_items(const HistArgs& a, const ColCtx& cx, 
         const uint32_t w3 = wl + 3 * mine_ps;
         const uint32_t o3 = atom_add_u32(w3, h);
         if (o3 + h >= kSpillAt) {
-          const int lf = ONE_LEAF ? 0 : leaf[mine_j];
+          const int lf = ONE_LEAF ? 0 : mine_leaf;
           const uint32_t pn = lds_u32(cx.tab_a + (uint32_t)(cx.pbase + lf) * (kTStride * 4));
           const uint32_t bin0 = cx.hist_a + ((pn & 0xFFFFu) + (uint32_t)((cx.replica * NPL + 3) * (int)((pn >> 16) + 1))) * 4u;
           spill_cnt_word(w3, bin0, a.acc, a.descs[(size_t)(cx.l_begin + lf) * a.C + cx.c].gbin);
@@ -565,7 +565,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
       const int rel = leaf[j] - grp.l_begin;
       leaf[j] = (leaf[j] != kSkipCode && (unsigned)rel < (unsigned)LG) ? rel : kSkipCode;
     }
-    if (leaf[0] == kSkipCode && leaf[1] == kSkipCode && leaf[2] == kSkipCode && leaf[3] == kSkipCode) continue;
+    // a warp none of whose rows takes part skips the tile; the decision is warp-uniform because the item loop below uses
+    // warp-wide votes and reductions (a lane on its own must not leave)
+    if (__all_sync(0xFFFFFFFFu, leaf[0] == kSkipCode && leaf[1] == kSkipCode && leaf[2] == kSkipCode && leaf[3] == kSkipCode)) continue;
     const float4 yv = __ldg(reinterpret_cast<const float4*>(a.work + row));
     const float ys[4] = {yv.x, yv.y, yv.z, yv.w};
     long long qy[4], qyy[4], qw[4];

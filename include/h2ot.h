@@ -291,7 +291,7 @@ int h2ot_score_tree(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_nod
  * predictions Tree_k (+ offset) are turned into class probabilities as score1/score2 do (T/gbm/GBM.java:1486-1513,
  * T/SharedTree.java:782-789) and fed to MetricBuilder.perRow (H/ModelMetricsBinomial.java, ModelMetricsMultinomial, ModelMetricsRegression):
  * sums over local rows with a response and weight != 0. MSE = sumsqe / wcount, logloss = logloss / wcount (after summing over ranks).
- * AUC and confusion matrices stay on the host. */
+ * The AUC comes from h2ot_auc_builders below; confusion matrices stay on the host. */
 typedef struct h2ot_metrics {
   double count;   /* rows scored */
   double wcount;  /* sum of weights */
@@ -299,6 +299,16 @@ typedef struct h2ot_metrics {
   double logloss; /* sum w * min(-log(1e-15), -log(p(actual class))) ; 0 for gaussian */
 } h2ot_metrics;
 int h2ot_score_metrics(h2ot_engine* h, h2ot_metrics* out);
+/* AUC2.AUCBuilder (h2o-core/src/main/java/hex/AUC2.java:356-581) over the resident bernoulli model: the local rows are cut into
+ * at most max_chunks chunks of *out_chunk_rows consecutive rows (a multiple of 32; the last one may be short) and every chunk's
+ * rows go, in row order, through perRow(p1, actual, weight) of a builder of its own -- what AUC_Impl.map does per Chunk (:343-350).
+ * out[c * H2OT_AUC_STRIDE]: number of bins n of chunk c, then ths[400], tps[400], fps[400], sqe[400] (the builder's arrays:
+ * ascending bin centres, true / false positive weights, squared error inside the bin; first n valid).
+ * The caller folds the builders in chunk order with AUCBuilder.reduce (:448-472) and, across ranks, in rank order. Rows without a
+ * response or with weight 0 are skipped (ModelMetricsBinomial.MetricBuilderBinomial.perRow). */
+#define H2OT_AUC_BINS 400
+#define H2OT_AUC_STRIDE (1 + 4 * H2OT_AUC_BINS)
+int h2ot_auc_builders(h2ot_engine* h, int32_t max_chunks, int32_t* out_n_chunks, int64_t* out_chunk_rows, double* out);
 
 /* ---- DRF (T/drf/DRF.java). The level loop is the same; what differs is around it. */
 /* DRF.initializeModelSpecifics (:139-153) + the work vecs of SharedTree.java:364-385: Work_k <- class indicator (nclass > 1) or

@@ -78,6 +78,13 @@ int32_t h2ot_gbm_ntrees(h2ot_gbm* g);
 int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k);
 int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k);
 int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out);
+/* DTree.compress (h2o-algos/src/main/java/hex/tree/DTree.java:845-933, 972-982; IcedBitSet.compress2/3,
+ * h2o-core/src/main/java/water/util/IcedBitSet.java:92-111): CompressedTree._bits of tree (tree, k) -- the byte stream
+ * SharedTreeMojoModel.scoreTree and the MOJO writer consume -- and, when aux != NULL, the auxiliary stream (DTree._abAux: per
+ * decided node, in the same pre-order, {nid, decided nodes in the left subtree, n0, n1, p0, p1, se0, se1, nid0, nid1}, 40 bytes).
+ * Little-endian like AutoBuffer on x86. Call once with bits == NULL to get the lengths, then with buffers of at least that size. */
+int h2ot_gbm_tree_compress(h2ot_gbm* g, int32_t tree, int32_t k, uint8_t* bits, int64_t bits_cap, int64_t* bits_len, uint8_t* aux,
+                           int64_t aux_cap, int64_t* aux_len);
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out);
 int h2ot_gbm_oobt(h2ot_gbm* g, double* out); /* DRF: OUT_BAG_TREES column */
 /* Scores NEW rows with the trees built so far (SharedTreeMojoModel.scoreAllTrees, h2o-genmodel .../SharedTreeMojoModel.java:1043-1076):
@@ -88,6 +95,11 @@ int h2ot_gbm_oobt(h2ot_gbm* g, double* out); /* DRF: OUT_BAG_TREES column */
 int h2ot_gbm_predict(h2ot_gbm* g, int64_t nrows, const double* const* columns, double* out);
 /* Training metrics of the current GBM model over all ranks (h2ot_score_metrics + sum): out_mse, out_logloss nullable */
 int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss);
+/* AUC of the current bernoulli GBM on its training rows, computed like hex.AUC2 (h2o-core/src/main/java/hex/AUC2.java): the device
+ * builds one AUCBuilder per chunk of rows (h2ot_auc_builders), this call folds them in row order -- and across ranks in rank
+ * order -- with AUCBuilder.reduce and evaluates AUC2.compute_auc. out_ths / out_tps / out_fps (nullable, 400 doubles each) receive
+ * the final builder's bins, *out_nbins their number, *out_chunk_rows the rows per chunk the device used. */
+int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_ths, double* out_tps, double* out_fps, int64_t* out_chunk_rows);
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);

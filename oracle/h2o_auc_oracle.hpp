@@ -172,8 +172,9 @@ struct AUCBuilder {
   }
 };
 
-// One builder per chunk of `chunk_rows` consecutive rows (rows with a NaN prediction or actual are skipped, AUC2.java:347-349),
-// folded left to right. Returns the final builder.
+// One builder per chunk of `chunk_rows` consecutive rows, folded left to right. Rows with a NaN prediction or actual are skipped
+// (AUC2.java:347-349), and so are rows of weight 0 / NaN (MetricBuilderBinomial.perRow returns before _auc.perRow,
+// h2o-core/src/main/java/hex/ModelMetricsBinomial.java). Returns the final builder.
 inline AUCBuilder aucOverChunks(const double* pred, const double* act, const double* w, int64_t n, int64_t chunk_rows) {
   AUCBuilder total;
   bool first = true;
@@ -182,6 +183,7 @@ inline AUCBuilder aucOverChunks(const double* pred, const double* act, const dou
     const int64_t r1 = r0 + chunk_rows < n ? r0 + chunk_rows : n;
     for (int64_t r = r0; r < r1; r++) {
       if (std::isnan(pred[r]) || std::isnan(act[r])) continue;
+      if (w && (w[r] == 0 || std::isnan(w[r]))) continue;
       b.perRow(pred[r], (int)act[r], w ? w[r] : 1.0);
     }
     if (first) { total = b; first = false; }

@@ -3,6 +3,8 @@
 // ctypes. Never linked into, or called from, the product library (h2o-3_b200/).
 #include "h2o_tree_oracle.hpp"
 #include "h2o_chunk_oracle.hpp"
+#include "h2o_compress_oracle.hpp"
+#include "h2o_auc_oracle.hpp"
 
 using namespace h2o_oracle;
 
@@ -310,6 +312,35 @@ void orc_model_tree_nodes(void* m, int t, int k, OrcNode* out) {
 float orc_model_score_tree(void* m, int t, int k, const double* x) {
   const TreeOut& tr = ((GBMModel*)m)->trees[t][k];
   return scoreTree(tr, [&](int c) { return x[c]; });
+}
+
+// DTree.compress of tree (t, k): returns the number of bytes; copies them when out != nullptr (aux: the _abAux stream)
+long long orc_model_tree_compress(void* m, int t, int k, int aux, unsigned char* out) {
+  try {
+    const CompressedTreeBytes c = compressTree(((GBMModel*)m)->trees[t][k]);
+    const std::vector<uint8_t>& v = aux ? c.aux : c.bits;
+    if (out) memcpy(out, v.data(), v.size());
+    return (long long)v.size();
+  } catch (...) {
+    return -1;
+  }
+}
+// SharedTreeMojoModel.scoreTree over compressed bytes, for n rows of a row-major [n][ncols] matrix
+void orc_score_compressed(const unsigned char* bits, long long len, const double* X, long long n, int ncols, float* out) {
+  const std::vector<uint8_t> v(bits, bits + len);
+  for (long long r = 0; r < n; r++) out[r] = scoreCompressedTree(v, [&](int c) { return X[r * ncols + c]; });
+}
+// AUC2: one AUCBuilder per chunk of chunk_rows consecutive rows, folded left to right; returns the AUC and the builder's bins
+double orc_auc2(const double* pred, const double* act, const double* w, long long n, long long chunk_rows, int* out_nbins, double* out_ths,
+                double* out_tps, double* out_fps) {
+  const AUCBuilder b = aucOverChunks(pred, act, w, n, chunk_rows);
+  if (out_nbins) *out_nbins = b._n;
+  for (int i = 0; i < b._n; i++) {
+    if (out_ths) out_ths[i] = b._ths[i];
+    if (out_tps) out_tps[i] = b._tps[i];
+    if (out_fps) out_fps[i] = b._fps[i];
+  }
+  return b.auc();
 }
 
 // ---- level captures (histogram-monitor analogue)

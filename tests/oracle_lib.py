@@ -74,7 +74,8 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    src_m = max(os.path.getmtime(os.path.join(ORACLE_DIR, f)) for f in ("h2o_tree_oracle.hpp", "h2o_chunk_oracle.hpp", "oracle_capi.cpp"))
+    src_m = max(os.path.getmtime(os.path.join(ORACLE_DIR, f)) for f in ("h2o_tree_oracle.hpp", "h2o_chunk_oracle.hpp", "h2o_compress_oracle.hpp",
+                                                                         "h2o_auc_oracle.hpp", "oracle_capi.cpp"))
     if not os.path.exists(_SO) or os.path.getmtime(_SO) < src_m:
         build()
     L = C.CDLL(_SO)
@@ -146,6 +147,12 @@ def lib():
     L.orc_model_tree_nodes.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     L.orc_model_score_tree.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     L.orc_model_score_tree.restype = C.c_float
+    L.orc_model_tree_compress.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    L.orc_model_tree_compress.restype = C.c_longlong
+    L.orc_score_compressed.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
+    L.orc_score_compressed.restype = None
+    L.orc_auc2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_longlong, c_int_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_auc2.restype = C.c_double
     L.orc_model_ncaptures.argtypes = [C.c_void_p]
     L.orc_capture_info.argtypes = [C.c_void_p, C.c_int, c_int_p, c_int_p, c_int_p, c_int_p]
     L.orc_capture_desc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(OrcHistDesc)]
@@ -333,6 +340,17 @@ class Model:
         x = np.ascontiguousarray(x, dtype=np.float64)
         return self.L.orc_model_score_tree(self.m, t, k, ptr(x))
 
+    def compressed_tree(self, t, k=0):
+        """(bits, aux) of DTree.compress for tree (t, k)."""
+        out = []
+        for aux in (0, 1):
+            n = self.L.orc_model_tree_compress(self.m, t, k, aux, None)
+            assert n >= 0, "DecidedNode.compress: size() differs from the bytes written"
+            b = np.zeros(max(1, n), dtype=np.uint8)
+            self.L.orc_model_tree_compress(self.m, t, k, aux, ptr(b))
+            out.append(b[:n].tobytes())
+        return tuple(out)
+
     def ncaptures(self):
         return self.L.orc_model_ncaptures(self.m)
 
@@ -354,3 +372,23 @@ class Model:
         nids = np.empty(self.frame.nrows, dtype=np.int32)
         self.L.orc_capture_nids(self.m, i, ptr(nids))
         return dict(tree=t.value, k=k.value, leaf=leaf.value, nleaves=nl.value, descs=descs, vals=vals, nids=nids)
+
+
+def score_compressed(bits, X):
+    """SharedTreeMojoModel.scoreTree over CompressedTree bytes for every row of X ([n, ncols] float64, NaN == NA)."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    b = np.frombuffer(bits, dtype=np.uint8).copy()
+    out = np.empty(X.shape[0], dtype=np.float32)
+    lib().orc_score_compressed(ptr(b), len(bits), ptr(X), X.shape[0], X.shape[1], ptr(out))
+    return out
+
+
+def auc2(pred, act, w=None, chunk_rows=1 << 62):
+    """AUC2 with one AUCBuilder per chunk_rows consecutive rows, folded left to right. Returns (auc, ths, tps, fps)."""
+    pred = np.ascontiguousarray(pred, dtype=np.float64)
+    act = np.ascontiguousarray(act, dtype=np.float64)
+    w = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
+    n = C.c_int(0)
+    ths, tps, fps = (np.zeros(800) for _ in range(3))
+    a = lib().orc_auc2(ptr(pred), ptr(act), ptr(w), len(pred), min(int(chunk_rows), 1 << 62), C.byref(n), ptr(ths), ptr(tps), ptr(fps))
+    return a, ths[:n.value], tps[:n.value], fps[:n.value]

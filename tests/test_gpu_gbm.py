@@ -345,3 +345,76 @@ def test_predict_new_rows_matches_score_tree(dist):
     tr = gm.predict([X[:, c] for c in range(6)])
     assert np.max(np.abs(tr[0] - gm.predictions(0))) < 1e-5
     gm.close()
+
+
+@pytest.mark.parametrize("case", ["numeric+small-cat", "wide-cat", "multinomial"])
+def test_compressed_tree_bytes_match_dtree_compress(case):
+    """DTree.compress (T/DTree.java:845-933, 972-982): the CompressedTree bytes the host driver emits for the trees grown on the
+    device equal the oracle's restatement byte for byte (main and auxiliary stream), and scoring NEW rows by walking those bytes
+    the way SharedTreeMojoModel.scoreTree does reproduces the device's own scoring of the node table (h2ot_score_tree)."""
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=57)
+    K, kw = 1, dict(ntrees=4, max_depth=5, nbins=20, seed=19)
+    cats = dict(cats)
+    if case == "wide-cat":
+        rng = np.random.default_rng(3)
+        X = np.concatenate([X, rng.integers(0, 90, (len(X), 1)).astype(np.float64)], axis=1)  # bitsets beyond 32 bits: compress3
+        cats[6] = 90
+        y = ((X[:, 6] % 7 < 3) ^ (y > 0)).astype(np.float64)
+    elif case == "multinomial":
+        y = np.argmax(np.nan_to_num(X[:, :3]), axis=1).astype(np.float64)
+        K = 3
+        kw.update(distribution="multinomial", nclass=3)
+    else:
+        kw.update(nbins_cats=8)  # 12 levels in 8 bins: group splits over binned levels
+    gm, om = _run_both(X, y, cats, capture=False, **kw)
+    rng = np.random.default_rng(58)
+    Xn = X[rng.integers(0, len(X), 4000)].copy()
+    Xn[rng.random(Xn.shape) < 0.05] = NaN
+    Xn[:50, 4] = 15  # a level the training frame never had
+    total = np.zeros((K, len(Xn)))
+    kinds = set()
+    for t in range(gm.ntrees):
+        for k in range(K):
+            bits, aux = gm.compressed_tree(t, k)
+            obits, oaux = om.compressed_tree(t, k)
+            assert bits == obits, (t, k, len(bits), len(obits))
+            assert aux == oaux, (t, k)
+            total[k] += O.score_compressed(bits, Xn).astype(np.float64)
+            for n in gm.tree(t, k)[0]:
+                if n.has_split:
+                    kinds.add(n.equal)
+    got = gm.predict([Xn[:, c] for c in range(Xn.shape[1])])
+    assert np.array_equal(got, total + (gm.init_f if K == 1 else 0.0))
+    if case == "wide-cat":
+        assert 3 in kinds
+    if case == "numeric+small-cat":
+        assert 0 in kinds and 2 in kinds
+    gm.close()
+
+
+def test_device_auc2_matches_the_streaming_builder():
+    """hex.AUC2 on the device (h2ot_auc_builders + the host fold): one AUCBuilder per chunk of rows, folded in row order. Against
+    the oracle's AUCBuilder run over the same chunking: identical bins and AUC when the device's p1 are fed to the oracle is not
+    possible (p1 stays on the device), so the oracle gets p1 = 1 / (1 + exp(-F)) from the downloaded scores -- exp may differ from
+    the device's by an ulp, which can move a bin centre in its last bits but not a count: counts must match exactly whenever no bin
+    was merged, and the AUC within 1e-9 always; the exact (sorted) AUC bounds AUC2's own histogram error (< 1e-3)."""
+    X, y, cats = h2ot_lib.make_frame(n=60000, c=6, seed=23)
+    y[::97] = NaN  # rows without a response are not scored
+    w = np.random.default_rng(4).integers(0, 3, len(y)).astype(np.float64)  # zero weights are skipped
+    for weights, ntrees in ((None, 1), (w, 6)):
+        gm, om = _run_both(X, y, cats, w=weights, capture=False, ntrees=ntrees, max_depth=3 if ntrees == 1 else 5, nbins=20, seed=5)
+        r = gm.auc()
+        F = gm.predictions()
+        p1 = 1.0 / (1.0 + np.minimum(1e19, np.exp(-F)))
+        a, ths, tps, fps = O.auc2(p1, y, w=weights, chunk_rows=r["chunk_rows"])
+        assert abs(r["auc"] - a) <= 1e-9, (r["auc"], a)
+        ok = ~np.isnan(y) & ((weights if weights is not None else np.ones(len(y))) > 0)
+        ww = (weights if weights is not None else np.ones(len(y)))[ok]
+        assert r["tps"].sum() == (ww * y[ok]).sum() and r["fps"].sum() == (ww * (1 - y[ok])).sum()
+        assert len(r["ths"]) == len(ths)
+        if ntrees == 1:  # a depth-3 tree: at most 8 distinct predictions, nothing is ever merged
+            assert len(ths) <= 8 and np.array_equal(r["tps"], tps) and np.array_equal(r["fps"], fps)
+            assert np.allclose(r["ths"], ths, rtol=1e-15, atol=0)
+        if weights is None:
+            assert abs(r["auc"] - h2ot_lib.auc(y[ok], F[ok])) < 1e-3
+        gm.close()

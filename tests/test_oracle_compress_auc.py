@@ -1,0 +1,83 @@
+"""Oracle restatements of DTree.compress / SharedTreeMojoModel.scoreTree (oracle/h2o_compress_oracle.hpp) and of AUC2
+(oracle/h2o_auc_oracle.hpp), pinned on the CPU by the reference's own invariants (no byte vectors exist in the reference:
+CompressedTreeTest trains on smalldata/logreg/prostate.csv, which is not shipped):
+  * DecidedNode.size() == bytes written (the assert at DTree.java:929) -- checked inside the oracle, -1 on violation;
+  * scoreTree over the bytes == the walk over the node table for every row (CompressedTreeTest.testNodeIdAssignment's check),
+    including bitset splits in both formats (compress2: <= 32 levels, compress3: offset + length), NA-vs-rest splits and stumps;
+  * with at most 400 distinct predictions AUCBuilder never merges bins and AUC2's trapezoid sum is the exact AUC (AUC2.java:36, 262-277);
+  * a single builder and per-chunk builders folded by reduce() agree when nothing has to be merged.
+"""
+import numpy as np
+
+import h2ot_lib
+import oracle_lib as O
+
+NaN = float("nan")
+
+
+def _model(X, y, cats, **kw):
+    p = O.default_params(family=O.BERNOULLI, nclass=2, **kw)
+    return O.Model(O.Frame(X, y, cat_cards=cats), p)
+
+
+def test_compressed_bytes_score_like_the_node_table():
+    X, y, cats = h2ot_lib.make_frame(n=6000, c=6, seed=3)
+    X[:, 5] = np.where(np.arange(len(X)) % 3 == 0, NaN, X[:, 5])  # a column with many NAs: NA-vs-rest candidates
+    cats = dict(cats)
+    rng = np.random.default_rng(0)
+    Xw = np.concatenate([X, rng.integers(0, 90, (len(X), 1)).astype(np.float64)], axis=1)  # 90 levels: bitsets beyond 32 bits
+    cats[6] = 90
+    yw = ((Xw[:, 6] % 7 < 3) ^ (y > 0)).astype(np.float64)
+    seen = set()
+    for XX, yy, cc, kw in ((X, y, cats, dict(ntrees=4, max_depth=5, nbins=20, nbins_cats=8, seed=7)),
+                           (Xw, yw, cats, dict(ntrees=4, max_depth=6, nbins=20, nbins_cats=1024, seed=11)),
+                           (X, y, cats, dict(ntrees=1, max_depth=3, nbins=20, min_rows=1e9, seed=1))):  # stump
+        om = _model(XX, yy, {k: v for k, v in cc.items() if k < XX.shape[1]}, **kw)
+        for t in range(om.ntrees):
+            bits, aux = om.compressed_tree(t)
+            nodes = om.tree(t)
+            n_dec = sum(1 for n in nodes if n.kind == 1 and n.has_split and _reachable(nodes, n.nid))
+            assert len(aux) == 40 * n_dec
+            got = O.score_compressed(bits, XX)
+            want = np.array([om.score_tree(t, 0, XX[r]) for r in range(len(XX))], dtype=np.float32)
+            assert np.array_equal(got, want)
+            for n in nodes:
+                if n.kind == 1 and n.has_split:
+                    seen.add((n.split.equal, n.split.nasplit == O.NAvsREST))
+            if len(nodes) == 1:
+                seen.add("stump")
+                assert bits[:3] == b"\x00\xff\xff" and len(bits) == 7
+    assert (0, False) in seen and (2, False) in seen and (3, False) in seen and "stump" in seen, seen
+
+
+def _reachable(nodes, nid):
+    while nodes[nid].pid >= 0:
+        p = nodes[nodes[nid].pid]
+        if nid not in (p.nid0, p.nid1):
+            return False
+        nid = p.nid
+    return nid == 0
+
+
+def test_auc2_is_exact_without_merges_and_chunking_agrees():
+    rng = np.random.default_rng(5)
+    n = 20000
+    act = (rng.random(n) < 0.3).astype(np.float64)
+    pred = np.round(np.clip(0.3 + 0.25 * (act - 0.3) + 0.2 * rng.standard_normal(n), 0, 1), 2)  # <= 101 distinct values
+    a1, ths, tps, fps = O.auc2(pred, act)
+    assert len(ths) == len(np.unique(pred)) and np.array_equal(ths, np.unique(pred))
+    assert tps.sum() == act.sum() and fps.sum() == n - act.sum()
+    assert abs(a1 - h2ot_lib.auc(act, pred)) < 1e-12
+    a2, ths2, tps2, fps2 = O.auc2(pred, act, chunk_rows=1500)
+    # reduce() merges the chunks' equal thresholds through combine_centers, which may move a centre by an ulp; counts are exact
+    assert np.allclose(ths, ths2, rtol=1e-14, atol=0) and np.array_equal(tps, tps2) and np.array_equal(fps, fps2) and a1 == a2
+    w = rng.integers(0, 3, n).astype(np.float64)
+    a3, _, tps3, fps3 = O.auc2(pred, act, w=w, chunk_rows=777)
+    assert tps3.sum() == (w * act).sum() and fps3.sum() == (w * (1 - act)).sum()
+    # continuous predictions: 400 bins, within the streaming histogram's own error of the exact value, and always in (0, 1)
+    predc = np.clip(0.3 + 0.25 * (act - 0.3) + 0.2 * rng.standard_normal(n), 0, 1)
+    a4, ths4, _, _ = O.auc2(predc, act, chunk_rows=4096)
+    assert len(ths4) == 400 and np.all(np.diff(ths4) > 0)
+    assert abs(a4 - h2ot_lib.auc(act, predc)) < 1e-3
+    # edge cases: one class only (AUC2.java:263-264)
+    assert O.auc2(pred, np.ones(n))[0] == 1.0 and O.auc2(pred, np.zeros(n))[0] == 0.0
