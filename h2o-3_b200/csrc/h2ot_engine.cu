@@ -374,12 +374,12 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   // opt in to the large dynamic shared memory carve-out once
 #define H2OT_OPTIN(ST)                                                                                                                      \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));   \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<false, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
-  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<true, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin)); \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));   \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<5, false, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin));  \
+  CUDA_TRY(cudaFuncSetAttribute(hist_smem_kernel<7, true, ST, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin))
   H2OT_OPTIN(H2OT_STORE_F32);
   H2OT_OPTIN(H2OT_STORE_F64);
   H2OT_OPTIN(H2OT_STORE_U8);
@@ -886,9 +886,7 @@ int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_
   const int bitsN = ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1);
   const double b = t.work_bound > 0 ? t.work_bound : 1.0;
   t.ey = exponent_for(h->w_max * b, bitsN);
-  // unit weights: the high half of a wYY addend shares a 32-bit word with the row count in the shared-memory histograms
-  // (k_level.cuh, kCntShift), which holds for addends below 2^38 -- the width every frame of 2^24 rows or more has anyway
-  t.eyy = exponent_for(h->w_max * b * b, bitsN, h->w ? 0 : 38);
+  t.eyy = exponent_for(h->w_max * b * b, bitsN);
   if (sample_rate < 1.0) {
     TRY(t_begin(h, &h->stats.ms_sample));
     sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed,
@@ -1121,8 +1119,7 @@ int desc_split_points(const TreeState& t, const h2ot_hist_desc& s, DescDev& d) {
 // Places every active (leaf, col) histogram: global bin offsets, packed-vals offsets, shared-memory groups.
 int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs) {
   const int C = h->C;
-  const int WPB = h->w ? 7 : 5;                      // leaf-major kernel (k_sparse.cuh): interleaved words per bin
-  const int WPD = h->w ? kPlanesW : kPlanesUnit;     // column-major kernel (k_level.cuh): accumulator planes per pair
+  const int WPB = h->w ? 7 : 5;
   t.h_descs.assign((size_t)L * C, DescDev{});
   t.total_bins = 0;
   t.total_vals = 0;
@@ -1157,7 +1154,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
       d.voff = t.total_vals;
       t.total_bins += s.nbin + 1;
       t.total_vals += (int64_t)(s.nbin + 1) * 3;
-      col_words[c] += (int64_t)(s.nbin + 1);  // bins; scaled to words below, where the kernel is known
+      col_words[c] += (int64_t)(s.nbin + 1) * WPB;
       t.max_split_nbin = std::max(t.max_split_nbin, (int)s.nbin);
       if ((s.flags & H2OT_DESC_ISCAT) && s.step == 1.0) t.any_cat = true;
       if (s.flags & H2OT_DESC_CHECKFLOAT) t.any_checkfloat = true;
@@ -1165,7 +1162,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   // ---- shared-memory groups: columns of one storage type per group (the kernel is specialised on it)
   auto fixed_bytes_l = [&](int ncg, int storage, int nleaves) {
     return (size_t)ncg * nleaves * (kTStride * sizeof(uint32_t) + (storage == H2OT_STORE_F64 ? sizeof(MinMaxS) : 0)) +
-           (size_t)ncg * (sizeof(ColRef) + 2 * sizeof(int32_t)) + 16 + 32 * kPlanesW * sizeof(uint32_t);  // + the per-lane sink words
+           (size_t)ncg * (sizeof(ColRef) + 3 * sizeof(int32_t)) + 16 + 32 * 7 * sizeof(uint32_t);  // + the per-lane sink bins
   };
   auto fixed_bytes = [&](int ncg, int storage) { return fixed_bytes_l(ncg, storage, L); };
   const size_t full_budget = (size_t)h->max_smem_optin;
@@ -1280,14 +1277,15 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     }
   }
   // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses. With unit weights the
-  // worst of them (a warp's 32 rows expected on 4 words or fewer: binary and few-valued columns on the first levels) are
-  // aggregated inside the warp before shared memory is touched; the others get 2 to 32 replicas of their histograms (lanes
+  // worst of them (a warp's 32 rows expected on 4 bins or fewer: binary and few-valued columns on the first levels) are
+  // aggregated inside the warp before shared memory is touched -- on frames of 2^17 rows or more, whose fixed-point addends
+  // stay below 2^44 (the aggregation sums them in 24-bit limbs); the others get 2 to 32 replicas of their histograms (lanes
   // pick one by lane id; the replicas are summed when the CTA merges) where that fits.
   std::vector<int> col_rep(C, 1), col_agg(C, 0);
+  const bool agg_ok = !h->w && !h->no_agg && !t.any_checkfloat && ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1) >= 18;
   for (int c = 0; c < C; c++) {
-    col_words[c] *= WPD;
     if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
-    if (!h->w && h->col_conc[c] * 32.0 / (double)L >= 4.0 && !h->no_agg) {
+    if (agg_ok && h->col_conc[c] * 32.0 / (double)L >= 4.0) {
       col_agg[c] = 1;
       continue;
     }
@@ -1389,7 +1387,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     // a column whose leaves x bins exceed shared memory: one group per leaf range that fits (rows of other ranges are skipped)
     for (int c : split_cols[st]) {
       size_t widest = 0;
-      for (int l = 0; l < L; l++) widest = std::max(widest, (size_t)std::max(t.h_descs[(size_t)l * C + c].nbin + 1, 0) * WPD);
+      for (int l = 0; l < L; l++) widest = std::max(widest, (size_t)std::max(t.h_descs[(size_t)l * C + c].nbin + 1, 0) * WPB);
       if (widest * 4 + fixed_bytes_l(1, st, 1) > full_budget) {  // a single (leaf, column) histogram is too wide: L2 atomics
         glob_cols.push_back(c);
         continue;
@@ -1400,7 +1398,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
         int l1 = l0;
         while (l1 < L) {
           const DescDev& d = t.h_descs[(size_t)l1 * C + c];
-          const size_t nw = words + (d.nbin >= 0 ? (size_t)(d.nbin + 1) * WPD : 0);
+          const size_t nw = words + (d.nbin >= 0 ? (size_t)(d.nbin + 1) * WPB : 0);
           if (l1 > l0 && nw * 4 + fixed_bytes_l(1, st, l1 + 1 - l0) > budget) break;
           words = nw;
           l1++;
@@ -1448,7 +1446,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
           DescDev& d = t.h_descs[(size_t)l * C + c];
           if (d.nbin < 0) continue;
           d.smem_off = off;
-          off += (d.nbin + 1) * WPD * col_rep[c];
+          off += (d.nbin + 1) * WPB * col_rep[c];
         }
       }
       gd.smem_words = off;
@@ -1635,13 +1633,13 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     const size_t sm = t.smem_bytes;
 #define H2OT_LAUNCH_HIST(ST)                                                                                      \
   if (h->w) {                                                                                                     \
-    if (t.any_checkfloat) hist_smem_kernel<true, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
-    else if (n_leaves == 1) hist_smem_kernel<true, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
-    else hist_smem_kernel<true, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
+    if (t.any_checkfloat) hist_smem_kernel<7, true, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);     \
+    else if (n_leaves == 1) hist_smem_kernel<7, true, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);   \
+    else hist_smem_kernel<7, true, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                     \
   } else {                                                                                                        \
-    if (t.any_checkfloat) hist_smem_kernel<false, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
-    else if (n_leaves == 1) hist_smem_kernel<false, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);  \
-    else hist_smem_kernel<false, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
+    if (t.any_checkfloat) hist_smem_kernel<5, false, ST, true, false><<<grid, kHistThreads, sm, h->stream>>>(ha);    \
+    else if (n_leaves == 1) hist_smem_kernel<5, false, ST, false, true><<<grid, kHistThreads, sm, h->stream>>>(ha);  \
+    else hist_smem_kernel<5, false, ST, false, false><<<grid, kHistThreads, sm, h->stream>>>(ha);                    \
   }
     switch (st) {
       case H2OT_STORE_F32: H2OT_LAUNCH_HIST(H2OT_STORE_F32); break;

@@ -155,20 +155,14 @@ struct HistArgs {
 };
 
 // Shared-memory descriptor table of one CTA: one record of kTStride 32-bit words per (group column, leaf) pair
-// p = gc * L + leaf. Records are 48 bytes apart: a 128-bit lookup by 32 lanes sitting in 32 different leaves touches banks
-// 12 i .. 12 i + 3 (mod 32), and 8 consecutive records cover the 32 banks exactly once, so the lookup takes the minimal four
-// wavefronts (one when the lanes share a few leaves, as on the first levels: identical addresses are broadcast).
-//   hot quad (one ld.shared.v4 per item):
-//     kTPlace : bits 0..15 word offset of the pair's accumulators in the CTA's histogram (0xFFFF: none), bits 16..31 nbin
-//     kTMin32 : _min as float bits            } fp32 pre-filter of DHistogram.bin: trunc((x - min32) * st32) with st32 = step * 2^11;
-//     kTSt32  : float(step) * 2048, or NaN    } the 11 fraction bits tell whether the fp64 result could differ (then the exact
-//               when the pair is not eligible } path runs). NaN sends every item of the pair down the exact path.
-//     kTSnap  : [lowest bin seen : 16 | highest bin seen : 16], a (possibly stale) copy of kTBinLo / kTBinHi: only items whose bin
-//               is at or beyond these can move the pair's min / max, everything else skips the key updates
-//   cold words: kTKmin / kTKmax ~key32 / key32 of the smallest / largest value (0: none; F32 / U8 / U16 storage),
-//     kTStepLo / kTStepHi the fp64 step (sign bit: the descriptor's H2OT_DESC_CHECKFLOAT), kTBinLo / kTBinHi the bin range seen,
-//     kTMinLo / kTMinHi the fp64 _min
-enum { kTPlace = 0, kTMin32, kTSt32, kTSnap, kTKmin, kTKmax, kTStepLo, kTStepHi, kTBinLo, kTBinHi, kTMinLo, kTMinHi, kTStride = 12 };
+// p = gc * L + leaf. A warp's lanes sit in different leaves once the tree is a few levels deep; the odd stride puts the
+// same word of up to 32 different records into 32 different banks (one wavefront per lookup), whereas 16/32-byte aligned
+// records would serialise on the few bank-quads they start in.
+enum { kTPlace = 0, kTMinLo, kTMinHi, kTStepLo, kTStepHi, kTKmin, kTKmax, kTStride = 7 };
+//   kTPlace: bits 0..15 word offset of bin 0 in the CTA's histogram (0xFFFF: no histogram for this pair), bits 16..31 nbin
+//   kTMinLo / kTMinHi: _min as fp64 halves -- or, for a column all of whose minima are fp32-exact (always the case for
+//                      f32-stored columns: minima are observed values or float split points), the float bits in kTMinLo alone
+//   kTKmin / kTKmax: ~key32 / key32 of the smallest / largest value seen (0: none) -- F32 / U8 / U16 storage
 struct __align__(16) MinMaxS {  // 64-bit keys, only for F64-stored columns
   unsigned long long mn, mx;
 };
@@ -180,19 +174,6 @@ constexpr uint32_t kInactive = 0xFFFFu;  // place field of a pair without a hist
 constexpr int kHistThreads = 1024;
 constexpr int kRowsPerThread = 4;
 constexpr int kTileRows = kHistThreads * kRowsPerThread;  // == kRowPad
-
-// Accumulator planes of one (leaf, column) pair with nbin + 1 bins (the last one is the NA bucket), each plane nbin + 1 words:
-//   unit weights (kPlanesUnit):  [wY.lo][wY.hi][wYY.lo][cnt << 19 | wYY.hi]
-//   weighted (kPlanesW):         [w.lo][w.hi][wY.lo][wY.hi][wYY.lo][wYY.hi]
-// int64 fixed point kept as 32-bit halves (shared memory has native atomics for 32-bit integers only; 64-bit and fp adds are CAS
-// loops). Plane-major, so that the banks of one atomic instruction follow the bins (uniform over the 32 banks) whatever the
-// number of planes. With unit weights the row count shares a word with the high half of wYY -- four atomics per item instead
-// of five: the count field holds 13 bits and the wYY.hi field 19; an add that leaves the count at kSpillAt or more empties the
-// word into the global accumulators (atom.exch, then two global atomics; rare: a bin has to take 2048 rows of one CTA first).
-// Every thread has at most four unchecked adds outstanding, so between the add that reaches kSpillAt and the exchange that
-// follows it at most 4096 more rows can land: count < 2048 + 4096 < 2^13, wYY.hi < 6144 * 65 < 2^19 for 38-bit addends.
-constexpr int kPlanesUnit = 4, kPlanesW = 6;
-constexpr uint32_t kCntShift = 19, kHiMask = (1u << kCntShift) - 1u, kSpillAt = 2048u << kCntShift;
 
 // Loads 4 consecutive rows of one column as doubles (NaN == NA). 128-bit / 64-bit / 32-bit vector loads.
 __device__ __forceinline__ void load4(const ColRef& c, int64_t row, double (&x)[4]) {
@@ -249,17 +230,12 @@ __device__ __forceinline__ int bin_checkfloat_fast(double x, double mn, double s
   return bin_checkfloat(x, mn, step, nbin);
 }
 
-// ---- shared-memory access by 32-bit address, in PTX: the compiler wraps every conditional atomic in a
+// ---- shared-memory access by 32-bit address, predicated in PTX: the compiler wraps every conditional atomic in a
 // BSSY / BRA / BSYNC sequence, which tripled the instruction count of the inner loop.
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
 __device__ __forceinline__ void red_add_u32(uint32_t addr, uint32_t v) {
@@ -284,163 +260,95 @@ __device__ __forceinline__ void red_max_if_gt(uint32_t addr, uint32_t v, uint32_
       "r"(cur), "r"(on) : "memory");
 }
 
-// DHistogram.bin in fp64 from the record's cold words (pairs that are not eligible for the fp32 pre-filter, and the few items
-// of eligible pairs that sit within 2^-11 of a bin edge). Out of line: it runs for a fraction of a percent of the items.
-template <bool CHECKFLOAT>
-__device__ __noinline__ int bin_exact_rec(uint32_t rec, double x, int nbin) {
-  const double mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
-  const double st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
-  if (CHECKFLOAT && st < 0) return bin_checkfloat_fast(x, mn, -st, nbin);
-  return max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x, mn), fabs(st))), nbin - 1));  // +-Inf saturate onto the end bins
-}
-
-// An item whose bin is at or beyond the pair's bin range seen so far: it may hold a new smallest / largest value. Rare once a
-// tile has gone by (the end bins of a node's range hold a fraction of a percent of its rows).
-__device__ __noinline__ void minmax_slow32(uint32_t rec, uint32_t key, int bin) {
-  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmin * 4), "r"(~key) : "memory");
-  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmax * 4), "r"(key) : "memory");
-  asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(rec + kTBinLo * 4), "r"((uint32_t)bin) : "memory");
-  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTBinHi * 4), "r"((uint32_t)bin) : "memory");
-}
-__device__ __noinline__ void minmax_slow64(uint32_t rec, MinMaxS* mm, double x, int bin) {
-  const unsigned long long k = dkey(x);
-  atomicMax(&mm->mn, ~k);
-  atomicMax(&mm->mx, k);
-  asm volatile("red.shared.min.u32 [%0], %1;" ::"r"(rec + kTBinLo * 4), "r"((uint32_t)bin) : "memory");
-  asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTBinHi * 4), "r"((uint32_t)bin) : "memory");
-}
-
-// The count | wYY.hi word of one bin has reached kSpillAt rows: empty it into the global accumulators. w3: the word's address,
-// bin0_w3: the address of bin 0's word in the same plane; gbin: the pair's first global bin.
-__device__ __noinline__ void spill_cnt_word(uint32_t w3, uint32_t bin0_w3, long long* acc, long long gbin) {
-  uint32_t g;
-  asm volatile("atom.shared.exch.b32 %0, [%1], %2;" : "=r"(g) : "r"(w3), "r"(0u) : "memory");
-  if (g) {
-    unsigned long long* dst = reinterpret_cast<unsigned long long*>(acc + (gbin + (long long)((w3 - bin0_w3) >> 2)) * 3);
-    atomicAdd(dst, (unsigned long long)(g >> kCntShift));
-    atomicAdd(dst + 2, (unsigned long long)(g & kHiMask) << 32);
-  }
-}
-
-#ifndef H2OT_ITEMS_IN_FLIGHT
-#define H2OT_ITEMS_IN_FLIGHT 2
-#endif
-constexpr int kItemsInFlight = H2OT_ITEMS_IN_FLIGHT;  // rows of a thread whose lookups / atomics are interleaved (2 or 4)
-
-// What one thread knows about the column it is working on (uniform over the CTA)
-struct ColCtx {
-  uint32_t hist_a, tab_a, sink_a;  // shared-memory addresses: histogram words, record table, this lane's sink word
-  int pbase;                       // first record of the column: gc * LG
-  int replica;                     // this lane's copy of the column's bins
-  int c;                           // frame column
-  int l_begin;                     // first leaf of the group
-  double xbase;                    // U8 / U16 storage: value = xbase + code (the items carry the codes); 0 otherwise
-  bool agg;                        // few-valued column: aggregate the warp's rows per distinct bin before touching shared memory
+// R (row, col) items of one thread, staged so that independent work overlaps: record lookups, fp64 bin arithmetic, then
+// the atomics grouped by word (the carries out of the low words are consumed last). Rows that take no part (skip code,
+// no histogram for the pair) are steered to a per-lane sink bin instead of branching around the atomics.
+// x: values as doubles; na: NA mask; key: order-preserving 32-bit keys (unused when KEY64).
+struct RecRegs {  // one descriptor record in registers (root level: the same record serves every row of a column)
+  uint32_t place, kmin, kmax;
+  int nbin;
+  double mn, st;
 };
+template <bool MN32>
+__device__ __forceinline__ RecRegs load_rec(uint32_t rec) {
+  RecRegs r;
+  const uint32_t pn = lds_u32(rec + kTPlace * 4);
+  r.place = pn & 0xFFFFu;
+  r.nbin = (int)(pn >> 16);
+  if (MN32) r.mn = (double)__uint_as_float(lds_u32(rec + kTMinLo * 4));
+  else r.mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
+  r.st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
+  r.kmin = lds_u32(rec + kTKmin * 4);
+  r.kmax = lds_u32(rec + kTKmax * 4);
+  return r;
+}
 
-// R (row, col) items of one thread, staged so that independent work overlaps: record lookups, bin arithmetic, then the atomics
-// grouped by plane (the carries out of the low words are consumed last). Rows that take no part (skip code, no histogram for
-// the pair) add into a per-lane sink word instead of branching around the atomics.
-template <bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, int J0, int R, class XT>
-__device__ __forceinline__ void hist_items(const HistArgs& a, const ColCtx& cx, MinMaxS* mm64, const uint4& rec0, const int (&leaf)[4],
-                                           const XT (&x)[4], const uint32_t (&key)[4], const bool (&na)[4],
+template <int WPB, bool HAS_W, bool KEY64, bool CHECKFLOAT, bool ONE_LEAF, bool MN32, bool AGG, int J0, int R>
+__device__ __forceinline__ void hist_items(uint32_t hist_a, uint32_t tab_a, uint32_t sink_a, MinMaxS* mm64, int pbase, int replica, const RecRegs& shared_rec,
+                                           const int (&leaf)[4],
+                                           const double (&x)[4], const bool (&na)[4], const uint32_t (&key)[4],
                                            const long long (&qw)[4], const long long (&qy)[4], const long long (&qyy)[4]) {
-  constexpr int NPL = HAS_W ? kPlanesW : kPlanesUnit;
-  uint32_t wd[4], ps[4], on4[4];
+  uint32_t wd[4];
 #pragma unroll
   for (int j = J0; j < J0 + R; j++) {
     const bool row_on = leaf[j] != kSkipCode;
-    const int p = cx.pbase + ((row_on && !ONE_LEAF) ? leaf[j] : 0);
-    const uint32_t rec = cx.tab_a + (uint32_t)p * (kTStride * 4);
-    const uint4 q = ONE_LEAF ? rec0 : lds_v4(rec);
-    const uint32_t place = q.x & 0xFFFFu;
-    const int nbin = (int)(q.x >> 16);
-    const bool on = row_on && place != kInactive;
-    int bb;
-    if (CHECKFLOAT || KEY64) {
-      // fp64 all the way (DRF's float-split correction, f64-stored columns); the correction costs two fp64 divisions near bin
-      // edges, so it is only evaluated for rows that take part
-      bb = 0;
+    const int p = pbase + ((row_on && !ONE_LEAF) ? leaf[j] : 0);
+    const uint32_t rec = tab_a + (uint32_t)p * (kTStride * 4);
+    RecRegs rr;
+    if (ONE_LEAF) rr = shared_rec;
+    else rr = load_rec<MN32>(rec);
+    const uint32_t place = rr.place;
+    const uint32_t on = (row_on && place != kInactive) ? 1u : 0u;
+    const int nbin = rr.nbin;
+    const double mn = rr.mn, st = rr.st;
+    int b = nbin;
+    if (CHECKFLOAT) {
+      // the float-split correction costs two fp64 divisions; with per-node mtries most (leaf, column) pairs have no histogram,
+      // so it is only evaluated for rows that take part (a divergent branch is cheaper than dividing for nothing)
+      // (the sign bit of the record's step carries the descriptor's H2OT_DESC_CHECKFLOAT flag)
       if (on && !na[j]) {
-        const double mn = __hiloint2double((int)lds_u32(rec + kTMinHi * 4), (int)lds_u32(rec + kTMinLo * 4));
-        const double st = __hiloint2double((int)lds_u32(rec + kTStepHi * 4), (int)lds_u32(rec + kTStepLo * 4));
-        const double xd = KEY64 ? (double)x[j] : cx.xbase + (double)x[j];
-        bb = (CHECKFLOAT && st < 0) ? bin_checkfloat_fast(xd, mn, -st, nbin)
-                                    : max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(xd, mn), fabs(st))), nbin - 1));
+        const double sa = fabs(st);
+        b = st < 0 ? bin_checkfloat_fast(x[j], mn, sa, nbin) : max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), sa)), nbin - 1));
       }
     } else {
-      // fp32 pre-filter: x (a float value, or a U8 / U16 code) and min32 (= _min, or _min - base for codes) are exact floats, so
-      // (x - min32) * st32 is within 3 * 2^-24 relative of the real product, i.e. within nbin * 2^11 * 1.8e-7 < 1 of it in units of
-      // 2^-11 bins (eligible pairs have nbin <= 2048). Only if the 11 fraction bits are all 0 or all 1 can the fp64 truncation
-      // of the reference differ: those items take the exact path.
-      const int iv = __float2int_rz(__fmul_rn(__fsub_rn((float)x[j], __uint_as_float(q.y)), __uint_as_float(q.z)));
-      bb = iv >> 11;
-      if (on && !na[j] && ((iv + 1) & 2047) <= 1) bb = bin_exact_rec<false>(rec, cx.xbase + (double)x[j], nbin);
-      bb = max(0, min(bb, nbin - 1));
+      b = max(0, min(__double2int_rz(__dmul_rn(__dsub_rn(x[j], mn), st)), nbin - 1));  // +-Inf saturate onto the end bins
+      b = na[j] ? nbin : b;
     }
-    // min / max of the pair: only values in (or beyond) the end bins seen so far can move them
-    if (on && !na[j] && (bb <= (int)(q.w >> 16) || bb >= (int)(q.w & 0xFFFFu))) {
-      if (KEY64) minmax_slow64(rec, mm64 + p, (double)x[j], bb);
-      else minmax_slow32(rec, key[j], bb);
-    }
-    const int b = na[j] ? nbin : bb;
-    // replica r of a pair sits r * NPL planes after replica 0 (replica == 0 unless the planner replicated the column)
-    ps[j] = on ? (uint32_t)(nbin + 1) * 4u : 128u;
-    wd[j] = on ? cx.hist_a + (place + (uint32_t)(cx.replica * NPL * (nbin + 1) + b)) * 4u : cx.sink_a;
-    on4[j] = on ? 1u : 0u;
-  }
-  if (HAS_W) {
-    uint32_t ow[4], oy[4], oyy[4];
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) ow[j] = atom_add_u32(wd[j], (uint32_t)qw[j]);
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) oy[j] = atom_add_u32(wd[j] + 2 * ps[j], (uint32_t)qy[j]);
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) oyy[j] = atom_add_u32(wd[j] + 4 * ps[j], (uint32_t)qyy[j]);
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) {
-      red_add_hi(wd[j] + ps[j], ow[j], (uint32_t)qw[j], (uint32_t)((unsigned long long)qw[j] >> 32));
-      red_add_hi(wd[j] + 3 * ps[j], oy[j], (uint32_t)qy[j], (uint32_t)((unsigned long long)qy[j] >> 32));
-      red_add_hi(wd[j] + 5 * ps[j], oyy[j], (uint32_t)qyy[j], (uint32_t)((unsigned long long)qyy[j] >> 32));
-    }
-  } else if (!cx.agg) {
-    uint32_t oy[4], oyy[4];
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) oy[j] = atom_add_u32(wd[j], (uint32_t)qy[j]);
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) oyy[j] = atom_add_u32(wd[j] + 2 * ps[j], (uint32_t)qyy[j]);
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) red_add_hi(wd[j] + ps[j], oy[j], (uint32_t)qy[j], (uint32_t)((unsigned long long)qy[j] >> 32));
-#pragma unroll
-    for (int j = J0; j < J0 + R; j++) {
-      const uint32_t lo = (uint32_t)qyy[j];
-      const uint32_t h = (uint32_t)((unsigned long long)qyy[j] >> 32) + ((uint32_t)(oyy[j] + lo) < lo ? 1u : 0u) + (1u << kCntShift);
-      const uint32_t w3 = wd[j] + 3 * ps[j];
-      const uint32_t o3 = atom_add_u32(w3, h);
-      if (on4[j] && o3 + h >= kSpillAt) {
-        const int l = cx.l_begin + (ONE_LEAF ? 0 : leaf[j]);
-        const uint32_t pn = lds_u32(cx.tab_a + (uint32_t)(cx.pbase + (ONE_LEAF ? 0 : leaf[j])) * (kTStride * 4));
-        const uint32_t bin0 = cx.hist_a + ((pn & 0xFFFFu) + (uint32_t)((cx.replica * NPL + 3) * (int)((pn >> 16) + 1))) * 4u;
-        spill_cnt_word(w3, bin0, a.acc, a.descs[(size_t)l * a.C + cx.c].gbin);
+    if (KEY64) {
+      if (on && !na[j]) {
+        const unsigned long long k = dkey(x[j]);
+        const MinMaxS m = mm64[p];
+        if (~k > m.mn) atomicMax(&mm64[p].mn, ~k);
+        if (k > m.mx) atomicMax(&mm64[p].mx, k);
+      }
+    } else {
+      // min / max keys: a new extreme is rare once a tile or two have gone by, so ONE branch guards both updates
+      if (on && !na[j] && (~key[j] > rr.kmin || key[j] > rr.kmax)) {
+        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmin * 4), "r"(~key[j]) : "memory");
+        asm volatile("red.shared.max.u32 [%0], %1;" ::"r"(rec + kTKmax * 4), "r"(key[j]) : "memory");
       }
     }
-  } else {
-    // Few-valued column: the warp's rows pile up on a handful of words, and same-address atomics serialise (a 3-valued column
-    // cost 3.5x a continuous one). Per distinct word among the warp's R x 32 items: every thread sums its own rows of that word,
-    // five REDUX give the warp's totals (26-bit limbs keep each of them inside 32 bits), and one lane adds them.
+    // replica r of a pair sits r * (nbin + 1) bins after replica 0 (replica == 0 unless the planner replicated the column)
+    wd[j] = on ? hist_a + (place + (uint32_t)((replica * (nbin + 1) + b) * WPB)) * 4u : sink_a;
+  }
+  constexpr uint32_t OW = 0, OY = (HAS_W ? 2 : 1) * 4, OYY = (HAS_W ? 4 : 3) * 4;
+  if (AGG && !HAS_W) {
+    // Few-valued column: the warp's rows pile up on a handful of bins, and same-address atomics serialise (a 3-valued column
+    // cost 3.5x a continuous one). Per distinct bin among the warp's R x 32 items: every thread sums its own rows of that bin,
+    // five REDUX give the warp's totals (24-bit limbs keep each of them inside 32 bits for addends below 2^46, which the
+    // planner guarantees before it flags a column: frames of 2^18 rows or more), and one lane adds them.
     const unsigned lane = threadIdx.x & 31u;
     unsigned todo = 0u;
 #pragma unroll
-    for (int j = J0; j < J0 + R; j++) todo |= on4[j] << j;
+    for (int j = J0; j < J0 + R; j++) todo |= (wd[j] != sink_a ? 1u : 0u) << j;
     while (true) {
       const unsigned has = __ballot_sync(0xFFFFFFFFu, todo != 0u);
       if (!has) break;
       const int leader = __ffs(has) - 1;
-      uint32_t mine = 0u, mine_ps = 0u;
-      int mine_leaf = 0;  // (selected in the unrolled loop: a run-time index would push leaf[] into local memory)
+      uint32_t mine = 0u;
 #pragma unroll
       for (int j = J0 + R - 1; j >= J0; j--)
-        if ((todo >> j) & 1u) { mine = wd[j]; mine_ps = ps[j]; mine_leaf = leaf[j]; }
+        if ((todo >> j) & 1u) mine = wd[j];
       const uint32_t wl = __shfl_sync(0xFFFFFFFFu, mine, leader);
       long long sy = 0, sv = 0;
       unsigned cnt = 0u;
@@ -452,39 +360,55 @@ __device__ __forceinline__ void hist_items(const HistArgs& a, const ColCtx& cx, 
         cnt += in ? 1u : 0u;
         todo &= in ? ~(1u << j) : ~0u;
       }
-      const unsigned t_ylo = __reduce_add_sync(0xFFFFFFFFu, (unsigned)sy & 0x3FFFFFFu);
-      const int t_yhi = __reduce_add_sync(0xFFFFFFFFu, (int)(sy >> 26));
-      const unsigned t_vlo = __reduce_add_sync(0xFFFFFFFFu, (unsigned)sv & 0x3FFFFFFu);
-      const unsigned t_vhi = __reduce_add_sync(0xFFFFFFFFu, (unsigned)((unsigned long long)sv >> 26));
+      const unsigned t_ylo = __reduce_add_sync(0xFFFFFFFFu, (unsigned)sy & 0xFFFFFFu);
+      const int t_yhi = __reduce_add_sync(0xFFFFFFFFu, (int)(sy >> 24));
+      const unsigned t_vlo = __reduce_add_sync(0xFFFFFFFFu, (unsigned)sv & 0xFFFFFFu);
+      const unsigned t_vhi = __reduce_add_sync(0xFFFFFFFFu, (unsigned)((unsigned long long)sv >> 24));
       const unsigned t_cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
       if ((int)lane == leader) {
-        const long long ty = ((long long)t_yhi << 26) + (long long)t_ylo;
-        const unsigned long long tv = ((unsigned long long)t_vhi << 26) + (unsigned long long)t_vlo;
-        const uint32_t o1 = atom_add_u32(wl, (uint32_t)ty);
-        const uint32_t o2 = atom_add_u32(wl + 2 * mine_ps, (uint32_t)tv);
-        red_add_hi(wl + mine_ps, o1, (uint32_t)ty, (uint32_t)((unsigned long long)ty >> 32));
-        const uint32_t lo = (uint32_t)tv;
-        const uint32_t h = (uint32_t)(tv >> 32) + ((uint32_t)(o2 + lo) < lo ? 1u : 0u) + (t_cnt << kCntShift);
-        const uint32_t w3 = wl + 3 * mine_ps;
-        const uint32_t o3 = atom_add_u32(w3, h);
-        if (o3 + h >= kSpillAt) {
-          const int lf = ONE_LEAF ? 0 : mine_leaf;
-          const uint32_t pn = lds_u32(cx.tab_a + (uint32_t)(cx.pbase + lf) * (kTStride * 4));
-          const uint32_t bin0 = cx.hist_a + ((pn & 0xFFFFu) + (uint32_t)((cx.replica * NPL + 3) * (int)((pn >> 16) + 1))) * 4u;
-          spill_cnt_word(w3, bin0, a.acc, a.descs[(size_t)(cx.l_begin + lf) * a.C + cx.c].gbin);
-        }
+        const long long ty = ((long long)t_yhi << 24) + (long long)t_ylo;
+        const unsigned long long tv = ((unsigned long long)t_vhi << 24) + (unsigned long long)t_vlo;
+        red_add_u32(wl + OW, t_cnt);
+        const uint32_t o1 = atom_add_u32(wl + OY, (uint32_t)ty);
+        const uint32_t o2 = atom_add_u32(wl + OYY, (uint32_t)tv);
+        red_add_hi(wl + OY + 4, o1, (uint32_t)ty, (uint32_t)((unsigned long long)ty >> 32));
+        red_add_hi(wl + OYY + 4, o2, (uint32_t)tv, (uint32_t)(tv >> 32));
       }
     }
+    return;
+  }
+  // low words first (their return values carry into the high words), then the high words
+  uint32_t oy[4], oyy[4], ow[4];
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) {
+    if (HAS_W) ow[j] = atom_add_u32(wd[j] + OW, (uint32_t)qw[j]);
+    else red_add_u32(wd[j] + OW, 1u);
+  }
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) oy[j] = atom_add_u32(wd[j] + OY, (uint32_t)qy[j]);
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) oyy[j] = atom_add_u32(wd[j] + OYY, (uint32_t)qyy[j]);
+#pragma unroll
+  for (int j = J0; j < J0 + R; j++) {
+    if (HAS_W) red_add_hi(wd[j] + OW + 4, ow[j], (uint32_t)qw[j], (uint32_t)((unsigned long long)qw[j] >> 32));
+    red_add_hi(wd[j] + OY + 4, oy[j], (uint32_t)qy[j], (uint32_t)((unsigned long long)qy[j] >> 32));
+    red_add_hi(wd[j] + OYY + 4, oyy[j], (uint32_t)qyy[j], (uint32_t)((unsigned long long)qyy[j] >> 32));
   }
 }
 
-// Shared-memory privatised histograms. One CTA = (column group, row-tile stride); see the accumulator planes above. After the
-// histogram words come 32 x 6 sink words (lane-owned, six planes 128 bytes apart) that swallow the adds of rows taking no part.
-template <bool HAS_W, int STORAGE, bool CHECKFLOAT, bool ONE_LEAF>
+#ifndef H2OT_ITEMS_IN_FLIGHT
+#define H2OT_ITEMS_IN_FLIGHT 2
+#endif
+constexpr int kItemsInFlight = H2OT_ITEMS_IN_FLIGHT;  // rows of a thread whose lookups / atomics are interleaved (2 or 4)
+
+// Shared-memory privatised histograms. One CTA = (column group, row-tile stride). Per bin WPB 32-bit words:
+//   unit weights (WPB 5): [cnt, wY.lo, wY.hi, wYY.lo, wYY.hi]
+//   weighted     (WPB 7): [w.lo, w.hi, wY.lo, wY.hi, wYY.lo, wYY.hi, pad]
+// followed by 32 sink bins (one per lane) that swallow the adds of rows taking no part.
+template <int WPB, bool HAS_W, int STORAGE, bool CHECKFLOAT, bool ONE_LEAF>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr bool KEY64 = STORAGE == H2OT_STORE_F64;
-  constexpr int NPL = HAS_W ? kPlanesW : kPlanesUnit;
   int g = a.group_begin;
   while (g + 1 < a.group_begin + a.n_groups && (int)blockIdx.x >= a.groups[g + 1].cta_begin) g++;
   const GroupDev grp = a.groups[g];
@@ -492,71 +416,58 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
   const int ncg = grp.ncols;
   const int LG = grp.l_count;  // leaves of this group
   const int npairs = ncg * LG;
-  uint32_t* T = reinterpret_cast<uint32_t*>(smem_raw);  // 16-byte aligned records first
-  MinMaxS* mmS = reinterpret_cast<MinMaxS*>(T + (size_t)kTStride * npairs);
+  MinMaxS* mmS = reinterpret_cast<MinMaxS*>(smem_raw);
   ColRef* colS = reinterpret_cast<ColRef*>(mmS + (KEY64 ? npairs : 0));
   int32_t* cidxS = reinterpret_cast<int32_t*>(colS + ncg);
-  int32_t* repS = cidxS + ncg;  // per group column: histogram replicas (lanes pick one by lane id) | 0x100 when aggregated
-  uint32_t* hist = reinterpret_cast<uint32_t*>(repS + ncg);
+  int32_t* mn32S = cidxS + ncg;  // per group column: 1 when every active minimum of the column is fp32-exact
+  int32_t* repS = mn32S + ncg;   // per group column: histogram replicas (1, 2 or 4; lanes pick one by lane id)
+  uint32_t* T = reinterpret_cast<uint32_t*>(repS + ncg);
+  uint32_t* hist = T + (size_t)kTStride * npairs;
   uint32_t* sink = hist + grp.smem_words;
 
   for (int i = threadIdx.x; i < ncg; i += blockDim.x) {
     const int cv = a.group_cols[grp.cols_off + i];  // column | log2(replicas) << 24 | aggregate << 29
     const int c = cv & 0xFFFFFF;
     cidxS[i] = c;
-    repS[i] = (1 << ((cv >> 24) & 31)) | (((cv >> 29) & 1) << 8);
+    repS[i] = (1 << ((cv >> 24) & 31)) | (((cv >> 29) & 1) << 8);  // replicas | 0x100: aggregate inside the warp
+    mn32S[i] = 1;
     colS[i] = a.cols[c];
   }
+  __syncthreads();
   for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
     const int gc = p / LG, l = grp.l_begin + (p - gc * LG);
-    const int c = a.group_cols[grp.cols_off + gc] & 0xFFFFFF;
-    const DescDev d = a.descs[(size_t)l * a.C + c];
-    const ColRef cr = a.cols[c];
+    const DescDev d = a.descs[(size_t)l * a.C + (a.group_cols[grp.cols_off + gc] & 0xFFFFFF)];
     uint32_t* r = T + (size_t)p * kTStride;
-    const bool chk = CHECKFLOAT && (d.flags & H2OT_DESC_CHECKFLOAT);
     r[kTMinLo] = (uint32_t)__double2loint(d.min);
     r[kTMinHi] = (uint32_t)__double2hiint(d.min);
     r[kTStepLo] = (uint32_t)__double2loint(d.step);
-    r[kTStepHi] = (uint32_t)__double2hiint(d.step) | (chk ? 0x80000000u : 0u);
+    r[kTStepHi] = (uint32_t)__double2hiint(d.step) | ((CHECKFLOAT && (d.flags & H2OT_DESC_CHECKFLOAT)) ? 0x80000000u : 0u);
     r[kTPlace] = (d.nbin < 0 ? kInactive : (uint32_t)d.smem_off) | ((uint32_t)max(d.nbin, 1) << 16);
     r[kTKmin] = 0u;
     r[kTKmax] = 0u;
-    r[kTBinLo] = 0xFFFFu;
-    r[kTBinHi] = 0u;
-    r[kTSnap] = 0xFFFF0000u;
-    // fp32 pre-filter: the pair's min (relative to the column's base for U8 / U16 codes, which are exact floats themselves)
-    // must be an exact float, the scaled step a normal float, nbin <= 2048 (error bound of the pre-filter) and the offset
-    // below 2^20 bins (so that the fp64 rounding of min - base stays far inside that bound)
-    const bool coded = STORAGE == H2OT_STORE_U8 || STORAGE == H2OT_STORE_U16;
-    const double mrel = coded ? d.min - cr.base : d.min;
-    const float mn32 = (float)mrel, st32 = (float)d.step;
-    const bool ok = !KEY64 && !chk && d.nbin >= 1 && d.nbin <= 2048 && (double)mn32 == mrel && d.step > 1e-30 && d.step < 1e30 &&
-                    (!coded || fabs(mrel) * d.step < 1048576.0);
-    r[kTMin32] = __float_as_uint(mn32);
-    r[kTSt32] = ok ? __float_as_uint(st32 * 2048.0f) : 0x7FC00000u;
     if (KEY64) { mmS[p].mn = 0ULL; mmS[p].mx = 0ULL; }
+    if (d.nbin >= 0 && (double)(float)d.min != d.min) mn32S[gc] = 0;  // benign race: every writer stores 0
   }
-  for (int i = threadIdx.x; i < grp.smem_words + 32 * kPlanesW; i += blockDim.x) hist[i] = 0u;
   __syncthreads();
-  ColCtx cx;
-  cx.hist_a = smem_addr(hist);
-  cx.tab_a = smem_addr(T);
-  cx.sink_a = smem_addr(sink) + (threadIdx.x & 31) * 4;
-  cx.l_begin = grp.l_begin;
+  for (int p = threadIdx.x; p < npairs; p += blockDim.x) {  // columns with fp32-exact minima keep the float bits in kTMinLo
+    const int gc = p / LG;
+    if (mn32S[gc]) {
+      uint32_t* r = T + (size_t)p * kTStride;
+      r[kTMinLo] = __float_as_uint((float)__hiloint2double((int)r[kTMinHi], (int)r[kTMinLo]));
+    }
+  }
+  for (int i = threadIdx.x; i < grp.smem_words + 32 * WPB; i += blockDim.x) hist[i] = 0u;
+  __syncthreads();
+  const uint32_t hist_a = smem_addr(hist), tab_a = smem_addr(T);
+  const uint32_t sink_a = smem_addr(sink) + (threadIdx.x & 31) * (WPB * 4);
 
   using RawT = typename std::conditional<STORAGE == H2OT_STORE_F32, uint4,
                typename std::conditional<STORAGE == H2OT_STORE_U16, uint2,
                typename std::conditional<STORAGE == H2OT_STORE_U8, unsigned int, Double4>::type>::type>::type;
-  using XT = typename std::conditional<KEY64, double, float>::type;
   constexpr int kElem = STORAGE == H2OT_STORE_F32 ? 4 : STORAGE == H2OT_STORE_F64 ? 8 : STORAGE == H2OT_STORE_U8 ? 1 : 2;
 
   const int64_t n_tiles = a.n_pad / kTileRows;
   for (int64_t tile = slice; tile < n_tiles; tile += grp.n_slices) {
-    // refresh the bin-range snapshots the items test against (a stale one only sends more items down the slow path)
-    for (int p = threadIdx.x; p < npairs; p += blockDim.x) {
-      uint32_t* r = T + (size_t)p * kTStride;
-      r[kTSnap] = (r[kTBinLo] << 16) | r[kTBinHi];
-    }
     const int64_t row = tile * kTileRows + (int64_t)threadIdx.x * kRowsPerThread;
     const ushort4 cd = __ldg(reinterpret_cast<const ushort4*>(a.code + row));
     int leaf[4] = {cd.x, cd.y, cd.z, cd.w};
@@ -565,8 +476,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
       const int rel = leaf[j] - grp.l_begin;
       leaf[j] = (leaf[j] != kSkipCode && (unsigned)rel < (unsigned)LG) ? rel : kSkipCode;
     }
-    // a warp none of whose rows takes part skips the tile; the decision is warp-uniform because the item loop below uses
-    // warp-wide votes and reductions (a lane on its own must not leave)
+    // a warp none of whose rows takes part skips the tile; the decision is warp-uniform because the item loop of a few-valued
+    // column uses warp-wide votes and reductions (a lane on its own must not leave)
     if (__all_sync(0xFFFFFFFFu, leaf[0] == kSkipCode && leaf[1] == kSkipCode && leaf[2] == kSkipCode && leaf[3] == kSkipCode)) continue;
     const float4 yv = __ldg(reinterpret_cast<const float4*>(a.work + row));
     const float ys[4] = {yv.x, yv.y, yv.z, yv.w};
@@ -588,8 +499,6 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
       }
       qy[j] = __double2ll_rn(__dmul_rn(wy, a.sy));
       qyy[j] = __double2ll_rn(__dmul_rn(wyy, a.syy));
-      // the count | wYY.hi packing needs addends below 2^38; the scale guarantees it for |y| within the declared bound
-      if (!HAS_W) qyy[j] = min(qyy[j], (1LL << 38) - 1);
     }
     // software pipeline over the group's columns: the next column's 4 values are in flight while this one is binned
     auto fetch = [&](int gc) -> RawT {
@@ -607,36 +516,51 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     for (int gc = 0; gc < ncg; gc++) {
       const RawT cur = nxt;
       if (gc + 1 < ncg) nxt = fetch(gc + 1);
-      cx.pbase = gc * LG;
-      cx.c = cidxS[gc];
-      cx.xbase = (STORAGE == H2OT_STORE_U8 || STORAGE == H2OT_STORE_U16) ? colS[gc].base : 0.0;
-      XT x[4];
+      const int pbase = gc * LG;
+      double x[4];
       bool na[4];
       uint32_t key[4] = {0u, 0u, 0u, 0u};
       if constexpr (STORAGE == H2OT_STORE_F32) {
-        x[0] = __uint_as_float(cur.x); x[1] = __uint_as_float(cur.y); x[2] = __uint_as_float(cur.z); x[3] = __uint_as_float(cur.w);
+        const float xf[4] = {__uint_as_float(cur.x), __uint_as_float(cur.y), __uint_as_float(cur.z), __uint_as_float(cur.w)};
 #pragma unroll
-        for (int j = 0; j < 4; j++) { na[j] = x[j] != x[j]; key[j] = fkey(x[j]); }
+        for (int j = 0; j < 4; j++) { x[j] = (double)xf[j]; na[j] = xf[j] != xf[j]; key[j] = fkey(xf[j]); }
       } else if constexpr (STORAGE == H2OT_STORE_U8) {
+        const double cb = colS[gc].base;
         const unsigned xc[4] = {cur & 255u, (cur >> 8) & 255u, (cur >> 16) & 255u, cur >> 24};
 #pragma unroll
-        for (int j = 0; j < 4; j++) { x[j] = (float)xc[j]; na[j] = xc[j] == 255u; key[j] = xc[j] + 1u; }
+        for (int j = 0; j < 4; j++) { x[j] = cb + (double)xc[j]; na[j] = xc[j] == 255u; key[j] = xc[j] + 1u; }
       } else if constexpr (STORAGE == H2OT_STORE_U16) {
+        const double cb = colS[gc].base;
         const unsigned xc[4] = {cur.x & 65535u, cur.x >> 16, cur.y & 65535u, cur.y >> 16};
 #pragma unroll
-        for (int j = 0; j < 4; j++) { x[j] = (float)xc[j]; na[j] = xc[j] == 65535u; key[j] = xc[j] + 1u; }
+        for (int j = 0; j < 4; j++) { x[j] = cb + (double)xc[j]; na[j] = xc[j] == 65535u; key[j] = xc[j] + 1u; }
       } else {
         x[0] = cur.a.x; x[1] = cur.a.y; x[2] = cur.b.x; x[3] = cur.b.y;
 #pragma unroll
         for (int j = 0; j < 4; j++) na[j] = isnan(x[j]);
       }
+      RecRegs rec0{};
       const int rs = repS[gc];
-      cx.replica = (int)(threadIdx.x & 31) & ((rs & 0xFF) - 1);
-      cx.agg = !HAS_W && (rs & 0x100) != 0;
-      uint4 rec0 = make_uint4(0u, 0u, 0u, 0u);
-      if (ONE_LEAF) rec0 = lds_v4(cx.tab_a + (uint32_t)cx.pbase * (kTStride * 4));  // root level: one record per column
-      hist_items<HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 0, kItemsInFlight>(a, cx, mmS, rec0, leaf, x, key, na, qw, qy, qyy);
-      if (kItemsInFlight < 4) hist_items<HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, 2, 2>(a, cx, mmS, rec0, leaf, x, key, na, qw, qy, qyy);
+      const int replica = (int)(threadIdx.x & 31) & ((rs & 0xFF) - 1);
+      constexpr bool kCanAgg = !HAS_W && !CHECKFLOAT;  // (the planner never flags a column of a weighted or float-split build)
+      const bool agg = kCanAgg && (rs & 0x100) != 0;   // uniform per column
+#define H2OT_ITEMS(MN32_, AGG_)                                                                                                         \
+  do {                                                                                                                                  \
+    if (ONE_LEAF) rec0 = load_rec<MN32_>(tab_a + (uint32_t)pbase * (kTStride * 4)); /* root level: one record per column */            \
+    hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, MN32_, AGG_, 0, kItemsInFlight>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, \
+                                                                                        leaf, x, na, key, qw, qy, qyy);                 \
+    if (kItemsInFlight < 4)                                                                                                             \
+      hist_items<WPB, HAS_W, KEY64, CHECKFLOAT, ONE_LEAF, MN32_, AGG_, 2, 2>(hist_a, tab_a, sink_a, mmS, pbase, replica, rec0, leaf, x,   \
+                                                                             na, key, qw, qy, qyy);                                     \
+  } while (0)
+      if (mn32S[gc]) {  // uniform per column
+        if (agg) H2OT_ITEMS(true, kCanAgg);
+        else H2OT_ITEMS(true, false);
+      } else {
+        if (agg) H2OT_ITEMS(false, kCanAgg);
+        else H2OT_ITEMS(false, false);
+      }
+#undef H2OT_ITEMS
     }
   }
   __syncthreads();
@@ -652,19 +576,18 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_smem_kernel(HistArgs a) 
     const size_t lc = (size_t)l * a.C + cidxS[gc];
     const DescDev dd = a.descs[lc];
     const int nrep = repS[gc] & 0xFF;
-    const int pl = nbin + 1;
     for (int b = lane; b <= nbin; b += 32) {
       long long vw = 0, vy = 0, vyy = 0;
-      for (int rr = 0; rr < nrep; rr++) {
-        const uint32_t* wd = hist + place + rr * NPL * pl + b;
+      for (int r = 0; r < nrep; r++) {
+        const uint32_t* wd = hist + place + (r * (nbin + 1) + b) * WPB;
         if (HAS_W) {
-          vw += (long long)(((unsigned long long)wd[pl] << 32) | wd[0]);
-          vy += (long long)(((unsigned long long)wd[3 * pl] << 32) | wd[2 * pl]);
-          vyy += (long long)(((unsigned long long)wd[5 * pl] << 32) | wd[4 * pl]);
+          vw += (long long)(((unsigned long long)wd[1] << 32) | wd[0]);
+          vy += (long long)(((unsigned long long)wd[3] << 32) | wd[2]);
+          vyy += (long long)(((unsigned long long)wd[5] << 32) | wd[4]);
         } else {
-          vy += (long long)(((unsigned long long)wd[pl] << 32) | wd[0]);
-          vw += (long long)(wd[3 * pl] >> kCntShift);
-          vyy += (long long)(((unsigned long long)(wd[3 * pl] & kHiMask) << 32) | wd[2 * pl]);
+          vw += (long long)wd[0];
+          vy += (long long)(((unsigned long long)wd[2] << 32) | wd[1]);
+          vyy += (long long)(((unsigned long long)wd[4] << 32) | wd[3]);
         }
       }
       unsigned long long* dst = reinterpret_cast<unsigned long long*>(a.acc + (dd.gbin + b) * 3);

@@ -43,9 +43,10 @@ def make_frame(n=20000, c=6, seed=7, na_frac=0.02, with_cat=True, with_int=True)
     return X, y, cats
 
 
-def compare_models(gm, om, K=1, check_levels=True, rel=1e-6):
+def compare_models(gm, om, K=1, check_levels=True, rel=1e-6, ybound=1.0):
     """gm: product GBM (trained, maybe with captures); om: oracle Model. Asserts parity:
-    bit-exact nids / descriptors / tree structure, histogram sums within `rel` of the oracle's."""
+    bit-exact nids / descriptors / tree structure, histogram sums within `rel` of the oracle's -- and per bin within one float
+    ulp + the fixed-point quantum of the engine's accumulators (ybound: a bound on |work| of the build, 1 for classification)."""
     P = pkg()
     assert gm.ntrees == om.ntrees
     # sums of non-exact terms (offsets through exp, non-float responses) depend on the summation order, in the reference too
@@ -85,10 +86,14 @@ def compare_models(gm, om, K=1, check_levels=True, rel=1e-6):
                     # the oracle itself, which is relative to sum|y| <= sqrt(w * wYY) of the bin, not to a cancelled sum.
                     assert np.array_equal(gv[0::3], ov[0::3]), (i, n, c)
                     noise = 1e-13 * np.sqrt(np.abs(ov[0::3] * ov[2::3])) + 1e-300
+                    # The engine adds round(v * 2^e) as int64 with 2^e ~ 2^61 / (rows * bound): a value is off by at most half
+                    # that quantum (values within 2^-14 of the bound are exact for float inputs at 16M rows, more below), so a bin of
+                    # w rows by at most w * rows * bound * 2^-61 -- far below a float ulp unless the bin's own values are tiny.
+                    quantum = ov[0::3] * float(gm.nrows) * 2.0 ** -60
                     for j in (1, 2):
                         g_, o_ = gv[j::3], ov[j::3]
                         ulp = np.spacing(np.maximum(np.abs(g_), np.abs(o_)).astype(np.float32)).astype(np.float64)
-                        bad = np.abs(g_ - o_) > ulp + (noise if j == 1 else noise * 0)
+                        bad = np.abs(g_ - o_) > ulp + (noise if j == 1 else noise * 0) + quantum * (ybound if j == 1 else ybound * ybound)
                         assert not bad.any(), (i, n, c, j, int(bad.sum()), g_[bad][:4], o_[bad][:4])
                         scale = max(1e-300, float(np.max(np.abs(o_))))
                         d = float(np.max(np.abs(g_ - o_))) / scale

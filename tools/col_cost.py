@@ -36,6 +36,8 @@ for name, sel in list(kinds.items()) + [("all", list(range(C)))]:
         e.stats_reset()
         e.build_level(descs)
         s = e.stats()
+        if rep == 0:
+            e.finish_level(want_vals=False)  # feeds the planner's per-column bin concentration (replicas / warp aggregation)
     print("%-26s %2d columns: %.3f ms per level, %.4f ms per column" % (name, len(sel), s.ms_hist, s.ms_hist / len(sel)))
 print("per column (alone at the root, 1024 bins):")
 for c in range(C):
@@ -48,6 +50,8 @@ for c in range(C):
         e.stats_reset()
         e.build_level(descs)
         s = e.stats()
+        if rep == 0:
+            e.finish_level(want_vals=False)
     v = cols[c][:400000]
     b = np.minimum(((v - v.min()) * (1024 / (np.nextafter(v.max(), np.inf) - v.min()))).astype(np.int64), 1023)
     p = np.bincount(b, minlength=1024) / b.size

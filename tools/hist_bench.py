@@ -57,6 +57,8 @@ def main():
             for j in range(c):
                 descs[l * c + j] = P.make_desc(lo[j], hi[j], nb, order=j)
         e.build_level(descs, leaf_offset=leaf0, decided=dn)  # warm-up
+        if L == 1:
+            e.finish_level(want_vals=False)  # the root level feeds the planner's per-column bin concentration
         e.stats_reset()
         for _ in range(args.reps):
             e.build_level(descs, leaf_offset=leaf0, decided=dn)
