@@ -110,6 +110,7 @@ struct TreeState {  // per class-tree k
   long long* sums = nullptr;          // this level's payload: d_sums, or the peer-mapped exchange buffer
   unsigned long long* mm = nullptr;
   bool in_xbuf = false;
+  bool level_failed = false;  // a level call failed after score_decide had moved the rows: the tree has to be restarted
   DBuf<double> d_vals;
   // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
   // [min2 | maxIn | wNA | conc : LC doubles each][best split per leaf][has_vals : LC bytes]
@@ -192,6 +193,7 @@ struct h2ot_engine {
   XrPeers xr_peers{};
   void* xr_opened[kXrMaxWorld] = {nullptr};
   unsigned long long xr_epoch = 0;
+  int xr_owner = -1;  // class-tree whose level lives in xr_buf between its build and its finish (one at a time)
   int* xr_err = nullptr;
   int* xr_err_host = nullptr;  // pinned mirror of xr_err, refreshed after every exchange
   // persistent scratch of the small host-side all-reduces (h2ot_allreduce_host_f64) and of the rank barrier
@@ -302,20 +304,8 @@ int h2ot_device_count(int32_t* out) {
   return H2OT_OK;
 }
 
-int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
-  if (!cfg || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
-  if (cfg->nrows <= 0 || cfg->ncols <= 0 || cfg->nclass_trees <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "nrows/ncols/nclass_trees must be positive");
-  if (cfg->nrows > ((int64_t)1 << 32) - 2 * kRowPad)  // row ids travel as 32-bit values inside the level kernels; a shard is far smaller anyway
-    H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "more than 2^32 rows on one GPU: shard the rows over more engines");
-  if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
-  if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_TWEEDIE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
-  int ndev = 0;
-  cudaError_t e = cudaGetDeviceCount(&ndev);
-  if (e != cudaSuccess || ndev == 0)
-    H2OT_FAIL(H2OT_ERR_CUDA, std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
-  if (cfg->device < 0 || cfg->device >= ndev) H2OT_FAIL(H2OT_ERR_INVALID, "device ordinal out of range");
-  CUDA_TRY(cudaSetDevice(cfg->device));
-  h2ot_engine* h = new h2ot_engine();
+int h2ot_destroy(h2ot_engine* h);
+static int create_into(const h2ot_config* cfg, h2ot_engine* h) {
   h->cfg = *cfg;
   if (h->cfg.nrows_global <= 0) h->cfg.nrows_global = cfg->nrows;
   if (!(h->cfg.tweedie_power > 1.0 && h->cfg.tweedie_power < 2.0)) h->cfg.tweedie_power = 1.5;
@@ -401,6 +391,30 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
     CUDA_TRY(cudaFuncGetAttributes(&fa, find_split_kernel));
     h->split_smem_max = h->max_smem_optin - (int)fa.sharedSizeBytes;  // the opt-in limit covers static + dynamic
     CUDA_TRY(cudaFuncSetAttribute(find_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->split_smem_max));
+  }
+  return H2OT_OK;
+}
+
+int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
+  if (!cfg || !out) H2OT_FAIL(H2OT_ERR_INVALID, "null argument");
+  if (cfg->nrows <= 0 || cfg->ncols <= 0 || cfg->nclass_trees <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "nrows/ncols/nclass_trees must be positive");
+  if (cfg->nrows > ((int64_t)1 << 32) - 2 * kRowPad)  // row ids travel as 32-bit values inside the level kernels; a shard is far smaller anyway
+    H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "more than 2^32 rows on one GPU: shard the rows over more engines");
+  if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
+  if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_TWEEDIE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    H2OT_FAIL(H2OT_ERR_CUDA, std::string("no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev) H2OT_FAIL(H2OT_ERR_INVALID, "device ordinal out of range");
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  h2ot_engine* h = new h2ot_engine();
+  const int rc = create_into(cfg, h);
+  if (rc != H2OT_OK) {  // give back whatever was allocated before the failure (out of memory on a large shard, most likely)
+    const std::string why = g_last_error;
+    h2ot_destroy(h);
+    set_error(why);
+    return rc;
   }
   *out = h;
   return H2OT_OK;
@@ -880,6 +894,8 @@ int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_
   TreeState& t = h->ts[k];
   t.n_nodes = 0;
   t.built = t.finished = false;
+  t.level_failed = false;
+  if (h->xr_owner == k) h->xr_owner = -1;
   t.L = 0;
   t.prev_leaf_offset = -1;
   if (work_abs_bound > 0) t.work_bound = work_abs_bound;
@@ -1489,6 +1505,8 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
   if (n_leaves <= 0 || n_leaves > 65534) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "n_leaves must be in 1..65534");
   if (!descs) H2OT_FAIL(H2OT_ERR_INVALID, "null descs");
   TreeState& t = h->ts[k];
+  if (t.level_failed)
+    H2OT_FAIL(H2OT_ERR_INVALID, "an earlier level of this tree failed after the rows had been moved to its leaves: restart the tree with h2ot_begin_tree");
   t.built = t.finished = false;
   TRY(upload_nodes(h, t, n_decided, decided, bitset_pool, bitset_bytes, false));
   if (leaf_offset > 0 && t.n_nodes == 0) H2OT_FAIL(H2OT_ERR_INVALID, "no decided nodes uploaded for a non-root level");
@@ -1511,11 +1529,16 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     const size_t ns = (size_t)bins * 3 + n_leaves, nm = LC * 2;
     t.in_xbuf = false;
     if (h->xr_enabled && !h->xr_failed && h->nccl.world > 1) {
+      // every class-tree's level is accumulated in the ONE exchange buffer the peers have mapped: a second class-tree may build
+      // only after the first one's h2ot_finish_level has copied its level out (the level_step calls do that by themselves)
+      if (h->xr_owner >= 0 && h->xr_owner != k)
+        H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_build_level: another class-tree's level is still in the exchange buffer; call h2ot_finish_level for it first");
       const int rc = xr_ensure(h, ns + nm);
       if (rc == H2OT_OK) {
         t.sums = reinterpret_cast<long long*>(h->xr_buf);
         t.mm = h->xr_buf + ns;
         t.in_xbuf = true;
+        h->xr_owner = k;
       } else if (rc != H2OT_ERR_UNSUPPORTED) {
         return rc;
       }
@@ -1548,7 +1571,16 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
       }
     }
   t.prev_leaf_offset = -1;  // consumed; set again by the level_step that ends this level
-  TRY(plan_level(h, t, n_leaves, descs));
+  // (score_decide is already in flight -- it overlaps this host-side planning -- so a plan that cannot be made leaves NIDs_k one
+  // level ahead of the caller's tree: the tree is marked and has to be restarted with h2ot_begin_tree + h2ot_set_nids / a new build)
+  {
+    const int prc = plan_level(h, t, n_leaves, descs);
+    if (prc != H2OT_OK) {
+      t.level_failed = true;
+      if (h->xr_owner == k) h->xr_owner = -1;
+      return prc;
+    }
+  }
   // this level's descriptors, groups and column lists travel in ONE copy from pinned staging
   {
     const size_t b_descs = LC * sizeof(DescDev), b_groups = std::max<size_t>(1, t.h_groups.size()) * sizeof(GroupDev);
@@ -1722,6 +1754,7 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   CHECK_K(h, k);
   TreeState& t = h->ts[k];
   if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
+  if (t.in_xbuf && h->xr_owner == k) h->xr_owner = -1;  // the finalize kernel enqueued below reads the payload in stream order
   const size_t LC = (size_t)t.L * h->C;
   TRY(t.d_vals.ensure(std::max<int64_t>(1, t.total_vals)));
   {

@@ -365,8 +365,10 @@ int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
  * Limits: n_leaves <= H2OT_NOALLOC_MAX_LEAVES and sum(nbin+1) <= H2OT_NOALLOC_MAX_BINS, else H2OT_ERR_UNSUPPORTED.
  * The array is shared by all calls on a GPU and keeps the last call's contents; each call clears what it uses, so calls
  * whose GPU work overlaps would corrupt each other: issue them one after another. The first call on a GPU resolves the
- * array's address; make it before any stream capture. Work is enqueued on cuda_stream (a cudaStream_t, NULL == default
- * stream) and the call returns after that stream has drained. Unit weights only. */
+ * array's address. Work is enqueued on cuda_stream (a cudaStream_t, NULL == default stream) and the call returns after that
+ * stream has drained: it synchronises the stream, so it must not be issued on a stream that is being captured. Unit weights only.
+ * work_abs_bound: at least max |d_work[i]| over the rows that take part (0 == 1.0). It fixes the fixed-point scale of the
+ * sums: a smaller value than the true maximum overflows the 64-bit accumulators silently; a NaN in d_work poisons its bin. */
 #define H2OT_NOALLOC_MAX_LEAVES 64
 #define H2OT_NOALLOC_MAX_BINS 65536
 int h2ot_hist_column_noalloc(const float* d_x, const float* d_work, const uint16_t* d_leaf_code, int64_t n, int32_t n_leaves,

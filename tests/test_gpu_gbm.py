@@ -386,7 +386,9 @@ def test_compressed_tree_bytes_match_dtree_compress(case):
             for lo, hi in ((0, 8), (32, 40)):
                 assert np.array_equal(ga[:, lo:hi], oa[:, lo:hi]), (t, k)
             gf, of = ga[:, 8:32].copy().view(np.float32), oa[:, 8:32].copy().view(np.float32)
-            assert np.allclose(gf, of, rtol=3e-6, atol=0), (t, k, float(np.max(np.abs(gf - of) / np.maximum(np.abs(of), 1e-30))))
+            bad = np.argwhere(~np.isclose(gf, of, rtol=3e-6, atol=0))
+            assert bad.size == 0, (t, k, bad[:4].tolist(), [(float(gf[i, j]), float(of[i, j])) for i, j in bad[:4]],
+                                   ga[bad[0][0], :8].view(np.int32).tolist())
             total[k] += O.score_compressed(bits, Xn).astype(np.float64)
             for n in gm.tree(t, k)[0]:
                 if n.has_split:
