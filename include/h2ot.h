@@ -227,7 +227,12 @@ int h2ot_set_split_points(h2ot_engine* h, int32_t k, const double* points, int64
  * decided[0..n_decided): the DecidedNodes created by the previous level's onCompletion (nid order);
  * descs[n_leaves][ncols]: the UndecidedNodes' DHistograms for nids leaf_offset..leaf_offset+n_leaves-1.
  * Runs score_decide (T/ScoreBuildHistogram2.java:139-168,201-211) then the histogram build
- * (T/DHistogram.java:609-704) for every active (leaf, col). Results stay on the device. */
+ * (T/DHistogram.java:609-704) for every active (leaf, col). Results stay on the device.
+ * With several ranks and the peer-memory exchange, the level of every class-tree is accumulated in ONE buffer the peers have mapped:
+ * h2ot_build_level(k') before h2ot_finish_level(k) of another class-tree fails with H2OT_ERR_INVALID (h2ot_level_step[_begin] keep
+ * that order by themselves). If the call fails after the rows have been moved (a histogram that cannot be placed: H2OT_ERR_UNSUPPORTED
+ * / H2OT_ERR_INVALID from the planner), NIDs_k is one level ahead of the caller's tree: every later level call of this class-tree
+ * fails until h2ot_begin_tree restarts it. */
 int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_leaves, int32_t n_decided,
                      const h2ot_decided_node* decided, const uint8_t* bitset_pool, int64_t bitset_bytes,
                      const h2ot_hist_desc* descs);
