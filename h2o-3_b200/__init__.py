@@ -112,7 +112,7 @@ ENGINE_SYMBOLS = [
     "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64", "h2ot_reserve_exchange",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
-    "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end",
+    "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end", "h2ot_tree_levels_begin", "h2ot_tree_levels_end",
 ]
 GBM_SYMBOLS = [
     "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
@@ -170,6 +170,8 @@ def load():
     L.h2ot_level_step.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp, dbl, dbl, vp, vp, vp, vp, vp]
     L.h2ot_level_step_begin.argtypes = [vp, i32, i32, i32, i32, vp, vp, i64, vp, dbl, dbl]
     L.h2ot_level_step_end.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    L.h2ot_tree_levels_begin.argtypes = [vp, i32, i32, vp, dbl, dbl, i32, i32]
+    L.h2ot_tree_levels_end.argtypes = [vp, i32, vp, vp]
     L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
     L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
     L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]

@@ -19,6 +19,7 @@
 #include "k_split.cuh"
 #include "k_xreduce.cuh"
 #include "k_auc.cuh"
+#include "k_next.cuh"
 
 namespace h2ot {
 
@@ -99,6 +100,7 @@ struct TreeState {  // per class-tree k
   double sparse_bytes_per_row = 0, sparse_cols_per_row = 0;
   size_t smem_bytes = 0;
   int64_t total_bins = 0, total_vals = 0;
+  size_t payload_words = 0;  // 64-bit words of the level's payload (sums + leaf rows + min/max keys)
   int active_cols = 0;
   DBuf<unsigned char> d_lvl;  // per-level upload: [DescDev LC][GroupDev G][int32 group columns]
   unsigned char* lvl_host = nullptr;
@@ -111,6 +113,30 @@ struct TreeState {  // per class-tree k
   unsigned long long* mm = nullptr;
   bool in_xbuf = false;
   bool level_failed = false;  // a level call failed after score_decide had moved the rows: the tree has to be restarted
+  // ---- levels enqueued back to back with the step between them on the device (h2ot_tree_levels_begin / _end, k_next.cuh)
+  struct DevLoop {
+    bool active = false;        // h2ot_build_level is being driven by the device loop
+    int depth = 0, max_depth = 0;
+    int nbins = 0, nbins_cats = 0;
+    double min_rows = 0;
+    DBuf<unsigned char> lvl_alt, pack_alt;   // the previous level's descriptors / results (ping-pong with d_lvl / d_pack)
+    DBuf<double> maxex[2];                   // _maxEx of the levels' histograms [slot][col] (ping-pong)
+    DBuf<uint8_t> exists;                    // [static id]
+    DBuf<h2ot_split> tree_splits;            // [static id]
+    DBuf<int32_t> nb_caps;                   // [depth][col] largest nbin the level's layout holds
+    DBuf<int32_t> err;
+    std::vector<unsigned char*> lvl_stage;   // pinned staging of each level's upload (the levels are enqueued ahead of the GPU)
+    std::vector<size_t> lvl_stage_cap;
+    unsigned char* out_stage = nullptr;      // pinned: splits, exists, err, root concentration
+    size_t out_stage_cap = 0;
+    // the previous level as the step kernel reads it
+    const DescDev* prev_descs = nullptr;
+    const double *prev_min2 = nullptr, *prev_maxIn = nullptr, *prev_wna = nullptr, *prev_maxex = nullptr;
+    const uint8_t* prev_has = nullptr;
+    const h2ot_split* prev_best = nullptr;
+    bool pending = false;
+    size_t o_exists = 0, o_err = 0, o_conc = 0;  // offsets inside out_stage
+  } dev;
   DBuf<double> d_vals;
   // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
   // [min2 | maxIn | wNA | conc : LC doubles each][best split per leaf][has_vals : LC bytes]
@@ -452,6 +478,10 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.done_ev) cudaEventDestroy(t.done_ev);
     t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_sp.release();
+    t.dev.lvl_alt.release(); t.dev.pack_alt.release(); t.dev.maxex[0].release(); t.dev.maxex[1].release(); t.dev.exists.release();
+    t.dev.tree_splits.release(); t.dev.nb_caps.release(); t.dev.err.release();
+    for (unsigned char* sp : t.dev.lvl_stage) if (sp) cudaFreeHost(sp);
+    if (t.dev.out_stage) cudaFreeHost(t.dev.out_stage);
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
   h->d_rollup.release(); h->d_cols.release();
@@ -1548,17 +1578,23 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
       t.sums = t.d_sums.p;
       t.mm = reinterpret_cast<unsigned long long*>(t.d_sums.p + ns);
     }
-    CUDA_TRY(cudaMemsetAsync(t.sums, 0, (ns + nm) * sizeof(long long), h->stream));
+    t.payload_words = ns + nm;
   }
-  // K2a
-  {
+  // K2a: clear the payload and move the rows to this level's leaves. Launched here, ahead of the (host-side) planning it overlaps
+  // with -- unless the device loop drives the level: then the step kernel that creates this level's nodes has to run first, and
+  // it needs the planned layout (below).
+  auto launch_score = [&]() -> int {
+    CUDA_TRY(cudaMemsetAsync(t.sums, 0, t.payload_words * sizeof(long long), h->stream));
     ScoreArgs sa{h->n, h->n_pad, leaf_offset, n_leaves, t.nids, t.code, t.nodes.p, t.bitsets.p, h->d_cols.p,
                  reinterpret_cast<unsigned long long*>(t.sums)};
     TRY(t_begin(h, &h->stats.ms_score));
     score_decide_kernel<<<grid_for(h, h->n_pad / 4, 256, 16), 256, 0, h->stream>>>(sa);
     h->stats.launches++;
     TRY(t_end(h));
-  }
+    return H2OT_OK;
+  };
+  const bool dev_step = t.dev.active && t.dev.depth > 0;
+  if (!dev_step) TRY(launch_score());
   t.est_rows.assign((size_t)n_leaves, 0.0);
   if (t.prev_leaf_offset >= 0 && decided)
     for (int i = 0; i < n_decided; i++) {
@@ -1587,21 +1623,71 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     const size_t b_cols = std::max<size_t>(1, t.h_group_cols.size()) * sizeof(int32_t);
     const size_t total = b_descs + b_groups + b_cols;
     TRY(t.d_lvl.ensure(total));
-    if (total > t.lvl_host_cap) {
-      if (t.lvl_host) cudaFreeHost(t.lvl_host);
-      t.lvl_host = nullptr;
-      t.lvl_host_cap = 0;
-      CUDA_TRY(cudaMallocHost(&t.lvl_host, total * 2));
-      t.lvl_host_cap = total * 2;
+    unsigned char* stage = nullptr;
+    if (t.dev.active) {
+      // the device loop enqueues its levels ahead of the GPU: every level keeps its own pinned staging until the tree is done
+      const size_t d = (size_t)t.dev.depth;
+      if (t.dev.lvl_stage.size() <= d) {
+        t.dev.lvl_stage.resize(d + 1, nullptr);
+        t.dev.lvl_stage_cap.resize(d + 1, 0);
+      }
+      if (total > t.dev.lvl_stage_cap[d]) {
+        if (t.dev.lvl_stage[d]) cudaFreeHost(t.dev.lvl_stage[d]);
+        t.dev.lvl_stage[d] = nullptr;
+        t.dev.lvl_stage_cap[d] = 0;
+        CUDA_TRY(cudaMallocHost(&t.dev.lvl_stage[d], total * 2));
+        t.dev.lvl_stage_cap[d] = total * 2;
+      }
+      stage = t.dev.lvl_stage[d];
+    } else {
+      if (total > t.lvl_host_cap) {
+        if (t.lvl_host) cudaFreeHost(t.lvl_host);
+        t.lvl_host = nullptr;
+        t.lvl_host_cap = 0;
+        CUDA_TRY(cudaMallocHost(&t.lvl_host, total * 2));
+        t.lvl_host_cap = total * 2;
+      }
+      stage = t.lvl_host;
     }
     for (size_t i = 0; i < LC; i++) t.h_descs[i].pad = (uint32_t)(uint16_t)descs[i].order;  // bestCol tie order
-    memcpy(t.lvl_host, t.h_descs.data(), b_descs);
-    if (!t.h_groups.empty()) memcpy(t.lvl_host + b_descs, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev));
-    if (!t.h_group_cols.empty()) memcpy(t.lvl_host + b_descs + b_groups, t.h_group_cols.data(), t.h_group_cols.size() * sizeof(int32_t));
+    memcpy(stage, t.h_descs.data(), b_descs);
+    if (!t.h_groups.empty()) memcpy(stage + b_descs, t.h_groups.data(), t.h_groups.size() * sizeof(GroupDev));
+    if (!t.h_group_cols.empty()) memcpy(stage + b_descs + b_groups, t.h_group_cols.data(), t.h_group_cols.size() * sizeof(int32_t));
     t.p_descs = reinterpret_cast<DescDev*>(t.d_lvl.p);
     t.p_groups = reinterpret_cast<GroupDev*>(t.d_lvl.p + b_descs);
     t.p_group_cols = reinterpret_cast<int32_t*>(t.d_lvl.p + b_descs + b_groups);
-    TRY(h2d(h, t.d_lvl.p, t.lvl_host, total));
+    TRY(h2d(h, t.d_lvl.p, stage, total));
+  }
+  if (dev_step) {
+    // the step from the previous level: its splits become this level's nodes and descriptors (the layout fields of the
+    // descriptors just uploaded stay, everything else is written by the kernel), then the rows can move
+    TreeState::DevLoop& dv = t.dev;
+    NextArgs na{};
+    na.C = h->C;
+    na.Lp = n_leaves / 2;
+    na.parent_base = na.Lp - 1;
+    na.last_level = 0;
+    na.nbins = dv.nbins;
+    na.nbins_cats = dv.nbins_cats;
+    na.min_rows = dv.min_rows;
+    na.pdescs = dv.prev_descs;
+    na.pmaxex = dv.prev_maxex;
+    na.best = dv.prev_best;
+    na.min2 = dv.prev_min2;
+    na.maxIn = dv.prev_maxIn;
+    na.wna = dv.prev_wna;
+    na.has_vals = dv.prev_has;
+    na.ndescs = t.p_descs;
+    na.nmaxex = dv.maxex[dv.depth & 1].p;
+    na.nb_cap = dv.nb_caps.p + (size_t)dv.depth * h->C;
+    na.nodes = t.nodes.p;
+    na.bitsets = t.bitsets.p;
+    na.exists = dv.exists.p;
+    na.tree_splits = dv.tree_splits.p;
+    na.err = dv.err.p;
+    next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
+    h->stats.launches++;
+    TRY(launch_score());
   }
   // K2b
   HistArgs ha{};
@@ -1938,6 +2024,204 @@ int h2ot_level_step(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_le
   TRY(h2ot_level_step_begin(h, k, leaf_offset, n_leaves, n_decided, decided, bitset_pool, bitset_bytes, descs, min_rows,
                             min_split_improvement));
   return h2ot_level_step_end(h, k, out_min2, out_maxIn, out_wNA, out_has_vals, out_splits);
+}
+
+// ------------------------------------------------------------------------------------------------ whole tree, levels back to back
+// All levels of class-tree k enqueued without a host round trip in between: the step from one level to the next
+// (DecidedNode constructor + Split.nextLevelHistos, k_next.cuh) runs on the device, node ids are the slots of a complete
+// binary tree, and every level is planned for all of its 2^d slots with the widest histograms they can have.
+int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h2ot_hist_desc* root_descs, double min_rows,
+                           double min_split_improvement, int32_t nbins, int32_t nbins_cats) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (!root_descs) H2OT_FAIL(H2OT_ERR_INVALID, "null descs");
+  if (max_depth < 1 || max_depth > 10) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_levels: max_depth must be in 1..10");
+  TreeState& t = h->ts[k];
+  TreeState::DevLoop& dv = t.dev;
+  if (dv.pending || t.step_pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_begin: the previous tree / level of this class-tree was not ended");
+  const int C = h->C, D = max_depth;
+  const size_t S = ((size_t)1 << (D + 1)) - 1;  // static ids: levels 0 .. D (the last one only as children that exist or not)
+  for (int c = 0; c < C; c++)
+    if ((root_descs[c].flags & H2OT_DESC_ACTIVE) && (root_descs[c].flags & (H2OT_DESC_SPLITPTS | H2OT_DESC_CHECKFLOAT)))
+      H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_levels: uniform-adaptive histograms without the float-split correction only");
+  // ---- buffers of the whole tree, sized once
+  TRY(t.nodes.ensure(S));
+  TRY(t.bitsets.ensure(S * H2OT_MAX_BITSET_BYTES));
+  TRY(dv.exists.ensure(S));
+  TRY(dv.tree_splits.ensure(S));
+  TRY(dv.err.ensure(1));
+  TRY(dv.nb_caps.ensure((size_t)D * C));
+  TRY(dv.maxex[0].ensure(((size_t)1 << (D - 1)) * C));
+  TRY(dv.maxex[1].ensure(((size_t)1 << (D - 1)) * C));
+  const size_t n_splits = ((size_t)1 << D) - 1;  // nodes of levels 0 .. D-1
+  dv.o_exists = n_splits * sizeof(h2ot_split);
+  dv.o_err = dv.o_exists + ((S + 7) & ~(size_t)7);
+  dv.o_conc = dv.o_err + 8;
+  const size_t out_bytes = dv.o_conc + (size_t)C * sizeof(double);
+  if (out_bytes > dv.out_stage_cap) {
+    if (dv.out_stage) cudaFreeHost(dv.out_stage);
+    dv.out_stage = nullptr;
+    dv.out_stage_cap = 0;
+    CUDA_TRY(cudaMallocHost(&dv.out_stage, out_bytes));
+    dv.out_stage_cap = out_bytes;
+  }
+  // widest histogram a column can have at each depth (DHistogram ctor rule: max(parent nbin >> 1, nbins); categoricals keep theirs)
+  std::vector<int32_t> caps((size_t)D * C, 0);
+  for (int c = 0; c < C; c++) {
+    int nb = (root_descs[c].flags & H2OT_DESC_ACTIVE) ? root_descs[c].nbin : 0;
+    for (int d = 0; d < D; d++) {
+      caps[(size_t)d * C + c] = nb;
+      if (nb > 0 && !(root_descs[c].flags & H2OT_DESC_ISCAT)) nb = std::max(nb >> 1, nbins);
+      if (nb > 0 && (root_descs[c].flags & H2OT_DESC_ISCAT)) nb = std::min(std::max(nb, 1), nbins_cats);
+    }
+  }
+  CUDA_TRY(cudaMemsetAsync(t.nodes.p, 0xFF, S * sizeof(h2ot_decided_node), h->stream));  // col = pid = -1
+  CUDA_TRY(cudaMemsetAsync(dv.exists.p, 0, S, h->stream));
+  CUDA_TRY(cudaMemsetAsync(dv.exists.p, 1, 1, h->stream));  // the root
+  CUDA_TRY(cudaMemsetAsync(dv.err.p, 0, sizeof(int32_t), h->stream));
+  // (pageable sources: these two small copies are staged by the runtime before the call returns)
+  CUDA_TRY(cudaMemcpyAsync(dv.nb_caps.p, caps.data(), caps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  {
+    std::vector<double> mx(C);
+    for (int c = 0; c < C; c++) mx[c] = root_descs[c].maxEx;
+    CUDA_TRY(cudaMemcpyAsync(dv.maxex[0].p, mx.data(), (size_t)C * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  }
+  t.n_nodes = (int)S;
+  t.h_nodes.clear();
+  t.h_bitsets.clear();
+  dv.max_depth = D;
+  dv.nbins = nbins;
+  dv.nbins_cats = nbins_cats;
+  dv.min_rows = min_rows;
+  dv.active = true;
+  h->defer_sync = true;
+  int rc = H2OT_OK;
+  std::vector<h2ot_hist_desc> tmpl;
+  for (int d = 0; d < D && rc == H2OT_OK; d++) {
+    const int L = 1 << d;
+    dv.depth = d;
+    const h2ot_hist_desc* descs = root_descs;
+    if (d > 0) {
+      std::swap(t.d_lvl, dv.lvl_alt);    // the previous level's descriptors and results stay readable for the step kernel
+      std::swap(t.d_pack, dv.pack_alt);
+      tmpl.assign((size_t)L * C, h2ot_hist_desc{});
+      for (int l = 0; l < L; l++)
+        for (int c = 0; c < C; c++) {
+          const int nb = caps[(size_t)d * C + c];
+          if (nb <= 0) continue;
+          h2ot_hist_desc& e = tmpl[(size_t)l * C + c];
+          e = root_descs[c];
+          e.nbin = nb;
+          e.min = 0;
+          e.maxEx = 1;
+          e.step = 1.0;  // (categorical columns: the planner sizes the split search for a sorted-group scan when step == 1)
+          e.order = (int16_t)c;
+          e.flags = (uint8_t)(root_descs[c].flags & ~H2OT_DESC_INITNA);
+        }
+      descs = tmpl.data();
+    }
+    rc = h2ot_build_level(h, k, L - 1, L, 0, nullptr, nullptr, 0, descs);
+    if (rc == H2OT_OK) rc = h2ot_allreduce_level(h, k);
+    if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
+    if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
+    if (rc != H2OT_OK) break;
+    if (d == 0 && cudaMemcpyAsync(dv.out_stage + dv.o_conc, t.p_conc, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
+      set_error("cudaMemcpyAsync failed");
+      rc = H2OT_ERR_CUDA;
+      break;
+    }
+    dv.prev_descs = t.p_descs;
+    dv.prev_min2 = t.p_min2;
+    dv.prev_maxIn = t.p_maxIn;
+    dv.prev_wna = t.p_wna;
+    dv.prev_has = t.p_has;
+    dv.prev_best = t.p_best;
+    dv.prev_maxex = dv.maxex[d & 1].p;
+  }
+  if (rc == H2OT_OK) {  // the last level's nodes and whether their children exist
+    NextArgs na{};
+    na.C = C;
+    na.Lp = 1 << (D - 1);
+    na.parent_base = na.Lp - 1;
+    na.last_level = 1;
+    na.nbins = nbins;
+    na.nbins_cats = nbins_cats;
+    na.min_rows = min_rows;
+    na.pdescs = dv.prev_descs;
+    na.pmaxex = dv.prev_maxex;
+    na.best = dv.prev_best;
+    na.min2 = dv.prev_min2;
+    na.maxIn = dv.prev_maxIn;
+    na.wna = dv.prev_wna;
+    na.has_vals = dv.prev_has;
+    na.nb_cap = dv.nb_caps.p;
+    na.nodes = t.nodes.p;
+    na.bitsets = t.bitsets.p;
+    na.exists = dv.exists.p;
+    na.tree_splits = dv.tree_splits.p;
+    na.err = dv.err.p;
+    next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
+    h->stats.launches++;
+    if (cudaGetLastError() != cudaSuccess) {
+      set_error("next_level_kernel launch failed");
+      rc = H2OT_ERR_CUDA;
+    }
+  }
+  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage, dv.tree_splits.p, n_splits * sizeof(h2ot_split));
+  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage + dv.o_exists, dv.exists.p, S);
+  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage + dv.o_err, dv.err.p, sizeof(int32_t));
+  if (rc == H2OT_OK && !t.done_ev && cudaEventCreateWithFlags(&t.done_ev, cudaEventDisableTiming) != cudaSuccess) {
+    set_error("cudaEventCreate failed");
+    rc = H2OT_ERR_CUDA;
+  }
+  if (rc == H2OT_OK && cudaEventRecord(t.done_ev, h->stream) != cudaSuccess) {
+    set_error("cudaEventRecord failed");
+    rc = H2OT_ERR_CUDA;
+  }
+  dv.active = false;
+  h->defer_sync = false;
+  if (rc != H2OT_OK) {
+    if (h->steps_pending == 0) finish_call(h);
+    return rc;
+  }
+  dv.pending = true;
+  h->steps_pending++;
+  return H2OT_OK;
+}
+
+int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  TreeState::DevLoop& dv = t.dev;
+  if (!dv.pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_end without h2ot_tree_levels_begin");
+  dv.pending = false;
+  h->steps_pending--;
+  int rs = H2OT_OK;
+  if (h->steps_pending == 0) rs = finish_call(h);
+  else if (cudaEventSynchronize(t.done_ev) != cudaSuccess) {
+    set_error("cudaEventSynchronize failed waiting for a tree");
+    rs = H2OT_ERR_CUDA;
+  }
+  if (rs == H2OT_OK && h->xr_err_host && *h->xr_err_host) {
+    set_error("peer-memory exchange timed out waiting for another rank");
+    rs = H2OT_ERR_COMM;
+  }
+  if (rs != H2OT_OK) return rs;
+  int32_t err = 0;
+  memcpy(&err, dv.out_stage + dv.o_err, sizeof(err));
+  if (err) {
+    t.level_failed = true;
+    H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_levels: a histogram outgrew the level's planned layout");
+  }
+  const int D = dv.max_depth;
+  const size_t S = ((size_t)1 << (D + 1)) - 1, n_splits = ((size_t)1 << D) - 1;
+  if (out_splits) memcpy(out_splits, dv.out_stage, n_splits * sizeof(h2ot_split));
+  if (out_exists) memcpy(out_exists, dv.out_stage + dv.o_exists, S);
+  const double* conc = reinterpret_cast<const double*>(dv.out_stage + dv.o_conc);
+  for (int c = 0; c < h->C; c++)
+    if (conc[c] > 0) h->col_conc[c] = conc[c];
+  return H2OT_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ end of tree

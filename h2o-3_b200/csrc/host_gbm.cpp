@@ -169,6 +169,7 @@ struct ColMeta {  // Vec rollups + type (RollupStats.java:31-48)
 struct Node {
   int kind = 0;  // 0 undecided, 1 decided, 2 leaf
   int pid = kNoParent, nid = 0;
+  int sid = -1;  // slot of the node in the engine's static numbering when the tree's levels ran back to back on the device
   std::vector<Hist> hs;  // undecided only ([ncols]); empty == no histograms
   bool score_cols_null = true;
   std::vector<int> score_cols;
@@ -443,6 +444,120 @@ void to_device_node(const Node& n, h2ot_decided_node& d, std::vector<uint8_t>& p
 
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
+// Builds without per-node column sampling and with uniform-adaptive histograms can run all levels of a tree back to back on the
+// device (h2ot_tree_levels_begin / _end): _scoreCols == null for every node (T/DTree.java:455-461), so no host-side draw sits
+// between two levels. H2OT_DEVICE_LOOP=0 keeps the level-by-level host loop (the two must grow identical trees).
+bool use_device_loop(const h2ot_gbm* g) {
+  const char* e = getenv("H2OT_DEVICE_LOOP");  // read per tree: tests switch it between two builds of one process
+  const bool off = e != nullptr && atoi(e) == 0;
+  return !off && !g->capture && g->p.algo == H2OT_ALGO_GBM && g->p.histogram_type == 0 && g->mtry == g->ncols &&
+         g->mtry_per_tree == g->ncols && g->p.col_sample_rate_change_per_level == 1.0 && g->p.max_depth >= 1 && g->p.max_depth <= 8;
+}
+
+void hist_to_desc(const Hist& h, int order, h2ot_hist_desc& d) {
+  d = h2ot_hist_desc{};
+  if (!h.present) return;
+  d.min = h.min;
+  d.maxEx = h.max_ex;
+  d.step = h.step;
+  d.nbin = h.nbin;
+  d.order = (int16_t)order;
+  d.flags = H2OT_DESC_ACTIVE | (h.is_int > 0 ? H2OT_DESC_ISINT : 0) | (h.is_int == 2 ? H2OT_DESC_ISCAT : 0) |
+            (h.int_opt ? H2OT_DESC_INTOPT : 0) | (h.check_float ? H2OT_DESC_CHECKFLOAT : 0) | (h.init_na ? H2OT_DESC_INITNA : 0);
+}
+
+// DecidedNode record in the engine's static numbering (device-loop trees): decided nodes under their slot, LeafNodes under
+// leaf_base + (leaf nid - first leaf nid)
+void to_device_node_static(const std::vector<Node>& ns, int nid, int first_leaf, int leaf_base, h2ot_decided_node& d, std::vector<uint8_t>& pool) {
+  const Node& n = ns[(size_t)nid];
+  memset(&d, 0, sizeof(d));
+  d.nid = n.sid;
+  d.pid = n.pid == kNoParent ? -1 : ns[(size_t)n.pid].sid;
+  d.col = n.has_split ? n.split.col : -1;
+  d.equal = n.has_split ? n.split.equal : 0;
+  d.nasplit = n.has_split ? n.split.nasplit : H2OT_NA_NONE;
+  d.splat = n.splat;
+  for (int i = 0; i < 2; i++) {
+    const int c = n.nids[i];
+    d.child[i] = c < 0 ? -1 : (ns[(size_t)c].kind == 2 ? leaf_base + (c - first_leaf) : ns[(size_t)c].sid);
+  }
+  if (n.has_split && n.split.equal >= 2) {
+    d.bs_off = (int32_t)pool.size();
+    d.bs_nbits = n.split.bs_nbits;
+    d.bs_bitoff = n.split.bs_bitoff;
+    pool.insert(pool.end(), n.split.bs, n.split.bs + n.split.bs_nbytes);
+  }
+}
+
+// All levels of the K class-trees of one iteration on the device, then the host's mirror of each tree: nodes in H2O's creation
+// order (level by level, leaf order, left child first -- what build_layer_k's loop over the leaves produces), splits, varimp.
+int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) {
+  const int K = g->K, C = g->ncols, D = g->p.max_depth;
+  const size_t S = ((size_t)1 << (D + 1)) - 1, nS = ((size_t)1 << D) - 1;
+  const double t0 = now_s();
+  std::vector<h2ot_hist_desc> descs((size_t)C);
+  std::vector<int> ncol_active((size_t)K, 0);
+  for (int k = 0; k < K; k++) {
+    const Node& root = kt[k]->ns[0];
+    for (int c = 0; c < C; c++) {
+      hist_to_desc(root.hs.empty() ? Hist{} : root.hs[(size_t)c], c, descs[(size_t)c]);
+      ncol_active[(size_t)k] += (descs[(size_t)c].flags & H2OT_DESC_ACTIVE) ? 1 : 0;
+    }
+    GTRY(h2ot_tree_levels_begin(g->eng, k, D, descs.data(), g->p.min_rows, g->p.min_split_improvement, g->p.nbins, g->p.nbins_cats));
+  }
+  std::vector<h2ot_split> splits(nS);
+  std::vector<uint8_t> exists(S);
+  for (int k = 0; k < K; k++) {
+    GTRY(h2ot_tree_levels_end(g->eng, k, splits.data(), exists.data()));
+    Tree& t = *kt[k];
+    t.ns[0].sid = 0;
+    std::vector<int> cur{0}, next;
+    for (int depth = 0; depth < D && !cur.empty(); depth++) {
+      g->timing.levels++;
+      g->timing.hist_rows_cols += (double)g->nrows_global * (double)ncol_active[(size_t)k];
+      bool did = false;
+      next.clear();
+      for (int nid : cur) {
+        const int sid = t.ns[(size_t)nid].sid;
+        const h2ot_split& sp = splits[(size_t)sid];
+        {
+          Node& n = t.ns[(size_t)nid];
+          n.kind = 1;
+          n.hs.clear();
+          n.score_cols.clear();
+          if (sp.col < 0) {
+            n.has_split = false;
+            n.splat = NAN;
+            n.nids[0] = n.nids[1] = kUndecidedChild;
+            t.do_not_split(nid);
+            continue;
+          }
+          n.has_split = true;
+          n.split = sp;
+          n.splat = sp.splat;
+        }
+        did = true;
+        g->varimp[sp.col] += (float)(sp.se - (sp.se0 + sp.se1));  // T/SharedTree.java:697-700
+        for (int way = 0; way < 2; way++) {
+          const int csid = 2 * sid + 1 + way;
+          int child = kUndecidedChild;
+          if (exists[(size_t)csid]) {
+            child = t.new_undecided_stub(nid);  // (may move t.ns)
+            t.ns[(size_t)child].sid = csid;
+            next.push_back(child);
+          }
+          t.ns[(size_t)nid].nids[way] = child;
+        }
+      }
+      if (did) t.depth++;
+      cur.swap(next);
+    }
+    t.dirty.clear();
+  }
+  g->timing.level_s += now_s() - t0;
+  return H2OT_OK;
+}
+
 // One ScoreBuildHistogram2 pass + ScoreBuildOneTree.onCompletion for class-tree k (T/SharedTree.java:661-710).
 // last_level: the tree stops after this level (depth == max_depth - 1), so the children only need to exist with the right node
 // ids; their histograms and column draws (tree._rand is not used again) are skipped -- the widest level of a deep tree otherwise
@@ -641,7 +756,9 @@ int build_next_k_trees(h2ot_gbm* g) {
     kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed, false));
     GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, absmax[k]));
   }
-  for (int depth = 0; depth < g->p.max_depth; depth++) {
+  const bool on_device = use_device_loop(g);
+  if (on_device) GTRY(build_levels_on_device(g, kt));
+  for (int depth = 0; depth < g->p.max_depth && !on_device; depth++) {
     bool any = false;
     const bool last = depth == g->p.max_depth - 1;
     if (K > 1 && !g->capture) {
@@ -697,14 +814,16 @@ int build_next_k_trees(h2ot_gbm* g) {
     if (t.ns[0].kind == 2 || nleaf <= 0) continue;
     std::vector<h2ot_decided_node> dn;
     std::vector<uint8_t> pool;
+    const int leaf_base = on_device ? (1 << (g->p.max_depth + 1)) - 1 : leaves[k];  // the engine's id of the first LeafNode
     for (int nid = 0; nid < leaves[k]; nid++)
       if (t.ns[nid].kind == 1) {
         dn.emplace_back();
-        to_device_node(t.ns[nid], dn.back(), pool);
+        if (on_device) to_device_node_static(t.ns, nid, leaves[k], leaf_base, dn.back(), pool);
+        else to_device_node(t.ns[nid], dn.back(), pool);
       }
     GTRY(h2ot_set_tree(g->eng, k, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size()));
     std::vector<double> num(nleaf), den(nleaf);
-    GTRY(h2ot_gamma_pass(g->eng, k, leaves[k], nleaf, num.data(), den.data()));
+    GTRY(h2ot_gamma_pass(g->eng, k, leaf_base, nleaf, num.data(), den.data()));
     for (int i = 0; i < nleaf; i++) {
       double gamma = den[i] == 0 ? 0 : num[i] / den[i];
       if (den[i] != 0 && g->p.family >= H2OT_FAMILY_POISSON) {  // GammaPass.gamma(double): link for poisson / gamma / tweedie
@@ -727,9 +846,19 @@ int build_next_k_trees(h2ot_gbm* g) {
   std::vector<FinishedTree> outs(K);
   for (int k = 0; k < K; k++) {
     Tree& t = *kt[k];
-    std::vector<float> pred(t.len());
-    for (int i = 0; i < t.len(); i++) pred[i] = t.ns[i].pred;
-    GTRY(h2ot_add_tree(g->eng, k, t.len(), pred.data()));
+    if (on_device) {  // rows hold static ids: predictions under the same ids (LeafNodes from leaf_base on)
+      const int leaf_base = (1 << (g->p.max_depth + 1)) - 1;
+      const int nleaf = t.len() - leaves[k];
+      std::vector<float> pred((size_t)leaf_base + (size_t)std::max(nleaf, 0), 0.f);
+      for (int i = 0; i < leaves[k]; i++)
+        if (t.ns[i].sid >= 0) pred[(size_t)t.ns[i].sid] = t.ns[i].pred;
+      for (int i = 0; i < nleaf; i++) pred[(size_t)leaf_base + i] = t.ns[leaves[k] + i].pred;
+      GTRY(h2ot_add_tree(g->eng, k, (int)pred.size(), pred.data()));
+    } else {
+      std::vector<float> pred(t.len());
+      for (int i = 0; i < t.len(); i++) pred[i] = t.ns[i].pred;
+      GTRY(h2ot_add_tree(g->eng, k, t.len(), pred.data()));
+    }
     outs[k].nodes = std::move(t.ns);
     for (Node& n : outs[k].nodes) n.hs.clear();
     outs[k].leaves_start = leaves[k];

@@ -273,6 +273,21 @@ int h2ot_level_step_begin(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_
 int h2ot_level_step_end(h2ot_engine* h, int32_t k, double* out_min2, double* out_maxIn, double* out_wNA, uint8_t* out_has_vals,
                         h2ot_split* out_splits);
 
+/* ---- a whole tree with ONE host synchronisation: every level of class-tree k (h2ot_level_step for depth 0 .. max_depth - 1) is
+ * enqueued back to back, and what the Java side does between two levels -- the DecidedNode constructor and Split.nextLevelHistos with the
+ * DHistogram constructor rule (h2o-algos/src/main/java/hex/tree/DTree.java:312-417, 703-726; DHistogram.java:190-269, 453-459) -- runs
+ * on the device. For builds without per-node column sampling (UndecidedNode._scoreCols == null: mtries == ncols), with
+ * uniform-adaptive histograms and no float-split correction; root_descs[ncols] are the root's DHistograms.
+ * Node ids are STATIC inside these two calls: the nodes of depth d are the slots 2^d - 1 .. 2^(d+1) - 2 of a complete binary tree,
+ * child w of slot s being slot 2 s + 1 + w; NIDs_k holds such ids afterwards. _end waits for the tree and returns
+ * out_splits[2^max_depth - 1] (the split of every slot of depth < max_depth; col == -1: none) and out_exists[2^(max_depth+1) - 1]
+ * (1: the slot holds a node). The caller renumbers the nodes in creation order for its own tree (DTree numbers them as they are
+ * made: level by level, in leaf order, left child first) and passes the finished tree to h2ot_set_tree in static ids: decided
+ * nodes under their slot, LeafNodes under ids >= 2^(max_depth+1) - 1. Several class-trees may be begun before the first is ended. */
+int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h2ot_hist_desc* root_descs, double min_rows,
+                           double min_split_improvement, int32_t nbins, int32_t nbins_cats);
+int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists);
+
 /* ---- end of tree */
 /* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */
 int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,

@@ -386,7 +386,10 @@ def test_compressed_tree_bytes_match_dtree_compress(case):
             for lo, hi in ((0, 8), (32, 40)):
                 assert np.array_equal(ga[:, lo:hi], oa[:, lo:hi]), (t, k)
             gf, of = ga[:, 8:32].copy().view(np.float32), oa[:, 8:32].copy().view(np.float32)
-            bad = np.argwhere(~np.isclose(gf, of, rtol=3e-6, atol=0))
+            # (se0 / se1 = wYY - wY^2 / w cancel to noise in a nearly pure child: absolute slack at the scale of the tree's errors)
+            atol = np.zeros(6)
+            atol[4:6] = 1e-6 * float(np.max(np.abs(of[:, 4:6]))) if len(of) else 0.0
+            bad = np.argwhere(~(np.abs(gf - of) <= 3e-6 * np.abs(of) + atol))
             assert bad.size == 0, (t, k, bad[:4].tolist(), [(float(gf[i, j]), float(of[i, j])) for i, j in bad[:4]],
                                    ga[bad[0][0], :8].view(np.int32).tolist())
             total[k] += O.score_compressed(bits, Xn).astype(np.float64)
@@ -428,3 +431,47 @@ def test_device_auc2_matches_the_streaming_builder():
         if weights is None:
             assert abs(r["auc"] - h2ot_lib.auc(y[ok], F[ok])) < 1e-3
         gm.close()
+
+
+@pytest.mark.parametrize("case", ["bernoulli+cats+sampling", "gaussian+weights+offset", "multinomial", "deep+min_rows"])
+def test_device_level_loop_grows_the_same_trees_as_the_host_loop(case, monkeypatch):
+    """h2ot_tree_levels_begin / _end: all levels of a tree enqueued back to back, with the DecidedNode constructor and
+    Split.nextLevelHistos (T/DTree.java:312-417, 703-726) on the device, against the level-by-level loop that does them on the host
+    (H2OT_DEVICE_LOOP=0): identical trees (node numbering, splits, bitsets, predictions, varimp), and against the oracle."""
+    P = h2ot_lib.pkg()
+    X, y, cats = h2ot_lib.make_frame(n=40000, c=8, seed=71)
+    K, w, off = 1, None, None
+    kw = dict(ntrees=5, max_depth=6, nbins=20, seed=31)
+    if case == "bernoulli+cats+sampling":
+        kw.update(sample_rate=0.7, nbins_cats=8)
+    elif case == "gaussian+weights+offset":
+        rng = np.random.default_rng(2)
+        y = (np.nan_to_num(X[:, 0]) * 2 + np.nan_to_num(X[:, 2]) ** 2 + rng.normal(size=len(X))).astype(np.float32).astype(np.float64)
+        w = rng.integers(0, 3, len(X)).astype(np.float64)
+        off = (rng.random(len(X)) * 0.1).astype(np.float32).astype(np.float64)
+        kw.update(distribution="gaussian", nclass=1, nbins=32)
+    elif case == "multinomial":
+        # (noisy classes: with y a pure function of the features whole children become pure, their squared error is cancellation
+        # noise around 0, and DTree's `se <= 1e-30` test -- T/DTree.java:330 -- falls either way: a near-tie of the engine's exact
+        # sums against the oracle's sequential fp64 sums, not a property of the level loop under test)
+        y = np.argmax(np.nan_to_num(X[:, :3]) + 0.7 * np.random.default_rng(8).normal(size=(len(X), 3)), axis=1).astype(np.float64)
+        K = 3
+        kw.update(distribution="multinomial", nclass=3, ntrees=3)
+    else:
+        kw.update(max_depth=8, min_rows=400.0, ntrees=3)  # many leaves stop early: empty slots, cut-off children
+    sig = []
+    for loop in ("0", "1"):
+        monkeypatch.setenv("H2OT_DEVICE_LOOP", loop)
+        gm, om = _run_both(X, y, cats, w=w, off=off, capture=False, **kw)
+        eng_launches = gm.engine().stats().launches
+        nodes = [[bytes(gm.tree(t, k)[0]) for k in range(K)] for t in range(gm.ntrees)]
+        sig.append((nodes, [gm.predictions(k).tobytes() for k in range(K)], gm.varimp().tobytes(), [gm.tree(t, 0)[1] for t in range(gm.ntrees)]))
+        oms = om
+        gm.close()
+    assert sig[0][3] == sig[1][3]
+    assert sig[0][0] == sig[1][0], "trees differ between the host loop and the device loop"
+    assert sig[0][1] == sig[1][1] and sig[0][2] == sig[1][2]
+    monkeypatch.setenv("H2OT_DEVICE_LOOP", "1")
+    gm, om = _run_both(X, y, cats, w=w, off=off, capture=False, **kw)
+    h2ot_lib.compare_models(gm, om, K=K, check_levels=False)
+    gm.close()
