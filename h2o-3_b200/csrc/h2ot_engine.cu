@@ -1323,7 +1323,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
     }
   }
   // Columns whose rows pile up in a few bins (c / L large) serialise their atomics on those addresses. With unit weights the
-  // worst of them (a warp's 32 rows expected on 4 bins or fewer: binary and few-valued columns on the first levels) are
+  // worst of them (eight or more of a warp's 32 rows expected in one bin: binary and few-valued columns on the first levels) are
   // aggregated inside the warp before shared memory is touched -- on frames of 2^17 rows or more, whose fixed-point addends
   // stay below 2^44 (the aggregation sums them in 24-bit limbs); the others get 2 to 32 replicas of their histograms (lanes
   // pick one by lane id; the replicas are summed when the CTA merges) where that fits.
@@ -1331,7 +1331,7 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   const bool agg_ok = !h->w && !h->no_agg && !t.any_checkfloat && ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1) >= 18;
   for (int c = 0; c < C; c++) {
     if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
-    if (agg_ok && h->col_conc[c] * 32.0 / (double)L >= 4.0) {
+    if (agg_ok && h->col_conc[c] * 32.0 / (double)L >= 8.0) {
       col_agg[c] = 1;
       continue;
     }

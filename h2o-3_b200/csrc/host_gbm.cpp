@@ -507,6 +507,9 @@ int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) 
   }
   std::vector<h2ot_split> splits(nS);
   std::vector<uint8_t> exists(S);
+  // variable importance is a float sum whose order the reference fixes: per level, class-tree by class-tree, leaf by leaf
+  // (ScoreBuildOneTree.onCompletion of the K trees of one buildLayer, T/SharedTree.java:563-607, 697-700)
+  std::vector<std::vector<std::pair<int, float>>> vi((size_t)D * K);
   for (int k = 0; k < K; k++) {
     GTRY(h2ot_tree_levels_end(g->eng, k, splits.data(), exists.data()));
     Tree& t = *kt[k];
@@ -537,7 +540,7 @@ int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) 
           n.splat = sp.splat;
         }
         did = true;
-        g->varimp[sp.col] += (float)(sp.se - (sp.se0 + sp.se1));  // T/SharedTree.java:697-700
+        vi[(size_t)depth * K + k].emplace_back(sp.col, (float)(sp.se - (sp.se0 + sp.se1)));
         for (int way = 0; way < 2; way++) {
           const int csid = 2 * sid + 1 + way;
           int child = kUndecidedChild;
@@ -554,6 +557,8 @@ int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) 
     }
     t.dirty.clear();
   }
+  for (const auto& lvl : vi)
+    for (const auto& e : lvl) g->varimp[e.first] += e.second;
   g->timing.level_s += now_s() - t0;
   return H2OT_OK;
 }

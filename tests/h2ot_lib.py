@@ -117,7 +117,10 @@ def compare_models(gm, om, K=1, check_levels=True, rel=1e-6, ybound=1.0):
                     assert np.float32(a.splat).tobytes() == np.float32(b.splat).tobytes(), (t, k, a.nid)
                     for f in ("se", "se0", "se1", "n0", "n1", "p0", "p1", "tree_p0", "tree_p1"):
                         x, y = getattr(a, f), getattr(s, f)
-                        assert x == y or abs(x - y) <= 1e-6 * max(abs(x), abs(y)), (t, k, a.nid, f, x, y)
+                        # a child's squared error wYY - wY^2 / w cancels towards 0 in a nearly pure child: what is left is the float
+                        # rounding of the bins' sums, i.e. noise at 1e-6 of the NODE's error, not of the child's
+                        slack = 1e-6 * max(abs(a.se), abs(s.se)) if f in ("se0", "se1") else 0.0
+                        assert x == y or abs(x - y) <= 1e-6 * max(abs(x), abs(y)) + slack, (t, k, a.nid, f, x, y)
                     if a.equal >= 2:
                         assert (a.bs_nbits, a.bs_bitoff, a.bs_nbytes) == (s.bs_nbits, s.bs_bitoff, s.bs_nbytes)
                         assert bytes(a.bs[:a.bs_nbytes]) == bytes(s.bs[:s.bs_nbytes])
