@@ -422,7 +422,7 @@ def run_b200(args):
                 "launches": int(d["hist_launches"]),
                 "kernel_rows_x_cols_per_s": d["hist_rows_cols"] / (hist_ms * 1e-3) if hist_ms > 0 else 0.0,
                 "stage_ms_per_step": {k: d[k] / args.steps for k in ("ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals",
-                                                                        "ms_gamma", "ms_addtree")}}
+                                                                        "ms_gamma", "ms_addtree", "ms_exchange")}}
     # secondary ceiling (SURVEY 8d asks for it): the kernel's time goes into shared-memory atomics, ATOMS_PER_ITEM per (row, column)
     # item with unit weights; random-bin ATOMS.ADD runs at 12.4 lanes/clk/SM = 3490 G/s on this part (conflict free: 31 lanes/clk/SM;
     # tools/ubench_atomics2.cu "clean" lines, profiles/r01_ubench_atomics2_b200.txt)

@@ -74,7 +74,7 @@ class Stats(C.Structure):
                 ("ms_addtree", C.c_double), ("ms_sample", C.c_double), ("ms_ingest", C.c_double),
                 ("launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
                 ("hist_rows_cols", C.c_int64), ("hist_algo_bytes", C.c_int64), ("hist_launches", C.c_int64),
-                ("sparse_launches", C.c_int64)]
+                ("sparse_launches", C.c_int64), ("ms_exchange", C.c_double)]
 
 
 class GbmParams(C.Structure):
@@ -109,7 +109,7 @@ ENGINE_SYMBOLS = [
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_get_gamma_bounds", "h2ot_set_gamma_bounds", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
-    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
+    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_add_tree_scaled", "h2ot_set_sample_rate_per_class", "h2ot_set_lazy_sync", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64", "h2ot_reserve_exchange",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end", "h2ot_tree_levels_begin", "h2ot_tree_levels_end",
@@ -118,7 +118,7 @@ GBM_SYMBOLS = [
     "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
-    "h2ot_gbm_tree_compress", "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_auc", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
+    "h2ot_gbm_tree_compress", "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_auc", "h2ot_gbm_set_pred_noise_bandwidth", "h2ot_gbm_set_sample_rate_per_class", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
     "h2ot_gbm_capture_info", "h2ot_gbm_capture_desc", "h2ot_gbm_capture_vals", "h2ot_gbm_capture_nids",
     "h2ot_hostcheck_hist", "h2ot_hostcheck_find_max_ex", "h2ot_hostcheck_pcg_next_long", "h2ot_hostcheck_pcg_bounded",
     "h2ot_hostcheck_score_cols",
@@ -175,6 +175,11 @@ def load():
     L.h2ot_set_tree.argtypes = [vp, i32, i32, vp, vp, i64]
     L.h2ot_gamma_pass.argtypes = [vp, i32, i32, i32, vp, vp]
     L.h2ot_add_tree.argtypes = [vp, i32, i32, vp]
+    L.h2ot_add_tree_scaled.argtypes = [vp, i32, i32, vp, vp]
+    L.h2ot_set_sample_rate_per_class.argtypes = [vp, vp, i32]
+    L.h2ot_set_lazy_sync.argtypes = [vp, i32]
+    L.h2ot_gbm_set_pred_noise_bandwidth.argtypes = [vp, dbl]
+    L.h2ot_gbm_set_sample_rate_per_class.argtypes = [vp, vp, i32]
     L.h2ot_drf_init_model.argtypes = [vp]
     L.h2ot_sample.argtypes = [vp, i32, i64, dbl]
     L.h2ot_drf_collect_preds.argtypes = [vp, i32, i32, vp, i32, i32]
@@ -479,7 +484,8 @@ class GBM:
                  min_split_improvement=1e-5, sample_rate=1.0, col_sample_rate=1.0, col_sample_rate_per_tree=1.0,
                  col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
                  max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
-                 device=0, algo=0, mtries=-1, tweedie_power=1.5, histogram_type="AUTO"):
+                 device=0, algo=0, mtries=-1, tweedie_power=1.5, histogram_type="AUTO", pred_noise_bandwidth=0.0,
+                 sample_rate_per_class=None):
         self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
                                 nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, algo=algo,
                                 mtries=mtries, histogram_type={"AUTO": 0, "UniformAdaptive": 0, "Random": 1}[histogram_type],
@@ -489,6 +495,8 @@ class GBM:
                                 learn_rate_annealing=learn_rate_annealing, max_abs_leafnode_pred=max_abs_leafnode_pred,
                                 seed=seed, tweedie_power=tweedie_power)
         self.device = device
+        self.pred_noise_bandwidth = pred_noise_bandwidth
+        self.sample_rate_per_class = None if sample_rate_per_class is None else [float(r) for r in sample_rate_per_class]
         self.L = load()
         self.g = None
         self.K = 1 if distribution != "multinomial" else nclass
@@ -528,8 +536,16 @@ class GBM:
         if offset is not None:
             v = _f64(offset)
             _check(self.L.h2ot_gbm_set_offset(self.g, _p(v)))
+        self._extra_params()
         _check(self.L.h2ot_gbm_init(self.g))
         return self
+
+    def _extra_params(self):
+        if self.pred_noise_bandwidth:
+            _check(self.L.h2ot_gbm_set_pred_noise_bandwidth(self.g, float(self.pred_noise_bandwidth)))
+        if self.sample_rate_per_class is not None:
+            r = np.ascontiguousarray(self.sample_rate_per_class, dtype=np.float64)
+            _check(self.L.h2ot_gbm_set_sample_rate_per_class(self.g, _p(r), r.size))
 
     def load_chunks(self, nrows, columns, y, weights=None, offset=None, categorical=None):
         """Like load(), from H2O chunks: every column (and y / weights / offset) is a list of (codec, mem_bytes, n_rows) in row
@@ -559,6 +575,7 @@ class GBM:
             push(-2, weights)
         if offset is not None:
             push(-3, offset)
+        self._extra_params()
         _check(self.L.h2ot_gbm_init(self.g))
         return self
 

@@ -148,6 +148,7 @@ struct TreeState {  // per class-tree k
   DBuf<h2ot_split> d_cand;
   DBuf<long long> d_gamma;
   DBuf<float> d_pred;
+  DBuf<double> d_factor;  // per node: 1 + noise of GBM's pred_noise_bandwidth (h2ot_add_tree_scaled)
   int max_split_nbin = 0;
   bool any_cat = false;
   bool any_checkfloat = false;  // some descriptor of the level asks for the float-split correction (DRF)
@@ -206,6 +207,9 @@ struct h2ot_engine {
   std::vector<Timer> timers;
   std::vector<cudaEvent_t> event_pool;
   bool defer_sync = false;
+  bool lazy_sync = false;          // h2ot_set_lazy_sync: calls that return nothing to the host do not wait for the stream
+  std::vector<double> rate_per_class;  // Sample's _rate_per_class (empty: null)
+  DBuf<double> d_rate_per_class;
   std::vector<double> col_conc;    // per column: chance that two rows of the root share a bin (0 until a root level ran)
   int steps_pending = 0;  // h2ot_level_step_begin calls not yet ended
   int hist_mode = 0;
@@ -288,6 +292,15 @@ int finish_call(h2ot_engine* h) {
   CUDA_TRY(cudaGetLastError());
   if (h->xr_err_host && *h->xr_err_host) H2OT_FAIL(H2OT_ERR_COMM, "peer-memory exchange timed out waiting for another rank");
   return H2OT_OK;
+}
+// end of a call that hands nothing back to the host: with lazy sync on, the stream keeps running and the kernel timers and any
+// error are picked up by the next call that does synchronise
+int finish_call_lazy(h2ot_engine* h) {
+  if (h->lazy_sync) {
+    CUDA_TRY(cudaGetLastError());
+    return H2OT_OK;
+  }
+  return finish_call(h);
 }
 int h2d(h2ot_engine* h, void* dst, const void* src, size_t bytes) {
   if (!bytes) return H2OT_OK;
@@ -477,14 +490,14 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.stage) cudaFreeHost(t.stage);
     if (t.done_ev) cudaEventDestroy(t.done_ev);
     t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
-    t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_sp.release();
+    t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_factor.release(); t.d_sp.release();
     t.dev.lvl_alt.release(); t.dev.pack_alt.release(); t.dev.maxex[0].release(); t.dev.maxex[1].release(); t.dev.exists.release();
     t.dev.tree_splits.release(); t.dev.nb_caps.release(); t.dev.err.release();
     for (unsigned char* sp : t.dev.lvl_stage) if (sp) cudaFreeHost(sp);
     if (t.dev.out_stage) cudaFreeHost(t.dev.out_stage);
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
-  h->d_rollup.release(); h->d_cols.release();
+  h->d_rollup.release(); h->d_cols.release(); h->d_rate_per_class.release();
   for (cudaEvent_t e : h->event_pool) cudaEventDestroy(e);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
@@ -933,14 +946,15 @@ int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_
   const double b = t.work_bound > 0 ? t.work_bound : 1.0;
   t.ey = exponent_for(h->w_max * b, bitsN);
   t.eyy = exponent_for(h->w_max * b * b, bitsN);
-  if (sample_rate < 1.0) {
+  if (sample_rate < 1.0 || !h->rate_per_class.empty()) {  // SharedTreeParameters.useRowSampling (T/SharedTreeModel.java:86-88)
     TRY(t_begin(h, &h->stats.ms_sample));
-    sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed,
-                                                                 (float)sample_rate, sample_rate, h->resp, t.nids);
+    sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed, (float)sample_rate, sample_rate,
+                                                                 h->rate_per_class.empty() ? nullptr : h->d_rate_per_class.p,
+                                                                 (int)h->rate_per_class.size(), h->resp, t.nids);
     h->stats.launches++;
     TRY(t_end(h));
   }
-  return finish_call(h);
+  return finish_call_lazy(h);
 }
 
 
@@ -1825,12 +1839,15 @@ int h2ot_allreduce_level(h2ot_engine* h, int32_t k) {
   if (!t.built) H2OT_FAIL(H2OT_ERR_INVALID, "no level built");
   if (h->nccl.world <= 1 || !h->nccl.comm) return H2OT_OK;
   const size_t ns = (size_t)t.total_bins * 3 + t.L, nm = (size_t)t.L * h->C * 2;
+  TRY(t_begin(h, &h->stats.ms_exchange));
   if (t.in_xbuf) {
     TRY(xr_allreduce(h, (long long)ns, (long long)(ns + nm)));
+    TRY(t_end(h));
     return finish_call(h);
   }
   TRY(nccl_check(h, h->nccl.AllReduce(t.sums, t.sums, ns, /*ncclInt64*/ 4, /*ncclSum*/ 0, h->nccl.comm, h->stream), "ncclAllReduce(sums)"));
   TRY(nccl_check(h, h->nccl.AllReduce(t.mm, t.mm, nm, /*ncclUint64*/ 5, /*ncclMax*/ 2, h->nccl.comm, h->stream), "ncclAllReduce(minmax)"));
+  TRY(t_end(h));
   return finish_call(h);
 }
 
@@ -2230,7 +2247,7 @@ int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided
   CHECK_ENGINE(h);
   CHECK_K(h, k);
   TRY(upload_nodes(h, h->ts[k], n_nodes, nodes, bitset_pool, bitset_bytes, true));
-  return finish_call(h);
+  return finish_call_lazy(h);  // (the uploads come from the engine's own host mirror of the table)
 }
 
 int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_leaf_nodes, double* out_num, double* out_denom) {
@@ -2283,19 +2300,28 @@ int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_lea
   return H2OT_OK;
 }
 
-int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred) {
+static int add_tree_impl(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, const double* node_factor) {
   CHECK_ENGINE(h);
   CHECK_K(h, k);
   if (n_nodes <= 0 || !node_pred) H2OT_FAIL(H2OT_ERR_INVALID, "bad node_pred");
   TreeState& t = h->ts[k];
   TRY(t.d_pred.ensure(n_nodes));
   TRY(h2d(h, t.d_pred.p, node_pred, (size_t)n_nodes * sizeof(float)));
-  AddTreeArgs a{h->n, n_nodes, h->resp, h->w, t.nids, t.F, t.d_pred.p};
+  if (node_factor) {
+    TRY(t.d_factor.ensure(n_nodes));
+    TRY(h2d(h, t.d_factor.p, node_factor, (size_t)n_nodes * sizeof(double)));
+  }
+  AddTreeArgs a{h->n, n_nodes, h->resp, h->w, t.nids, t.F, t.d_pred.p, node_factor ? t.d_factor.p : nullptr};
   TRY(t_begin(h, &h->stats.ms_addtree));
   add_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
   h->stats.launches++;
   TRY(t_end(h));
-  return finish_call(h);
+  return finish_call_lazy(h);
+}
+int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred) { return add_tree_impl(h, k, n_nodes, node_pred, nullptr); }
+int h2ot_add_tree_scaled(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, const double* node_factor) {
+  if (!node_factor) H2OT_FAIL(H2OT_ERR_INVALID, "null node_factor");
+  return add_tree_impl(h, k, n_nodes, node_pred, node_factor);
 }
 
 int h2ot_score_tree(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_nodes, const float* node_pred) {
@@ -2387,11 +2413,12 @@ int h2ot_sample(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate
   CHECK_ENGINE(h);
   CHECK_K(h, k);
   TRY(t_begin(h, &h->stats.ms_sample));
-  sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed, (float)sample_rate,
-                                                               sample_rate, h->resp, h->ts[k].nids);
+  sample_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(h->n, h->cfg.row_offset, (long long)tree_seed, (float)sample_rate, sample_rate,
+                                                               h->rate_per_class.empty() ? nullptr : h->d_rate_per_class.p,
+                                                               (int)h->rate_per_class.size(), h->resp, h->ts[k].nids);
   h->stats.launches++;
   TRY(t_end(h));
-  return finish_call(h);
+  return finish_call_lazy(h);
 }
 
 int h2ot_drf_collect_preds(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, int32_t root_is_leaf, int32_t update_oobt) {
@@ -2568,6 +2595,26 @@ int h2ot_set_weight_bound(h2ot_engine* h, double bound) {
   h->w_max = bound;
   return H2OT_OK;
 }
+int h2ot_set_lazy_sync(h2ot_engine* h, int32_t on) {
+  CHECK_ENGINE(h);
+  h->lazy_sync = on != 0;
+  if (!on) return finish_call(h);
+  return H2OT_OK;
+}
+
+int h2ot_set_sample_rate_per_class(h2ot_engine* h, const double* rates, int32_t n) {
+  CHECK_ENGINE(h);
+  if (n < 0 || (n > 0 && !rates)) H2OT_FAIL(H2OT_ERR_INVALID, "bad rates");
+  if (n > 0 && n < h->cfg.nclass) H2OT_FAIL(H2OT_ERR_INVALID, "sample_rate_per_class needs one rate per response class");
+  h->rate_per_class.assign(rates, rates + n);
+  if (n > 0) {
+    TRY(h->d_rate_per_class.ensure(n));
+    TRY(h2d(h, h->d_rate_per_class.p, h->rate_per_class.data(), (size_t)n * sizeof(double)));
+    return finish_call(h);
+  }
+  return H2OT_OK;
+}
+
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode) {
   if (!h || mode < 0 || mode > 2) H2OT_FAIL(H2OT_ERR_INVALID, "bad mode");
   h->hist_mode = mode;

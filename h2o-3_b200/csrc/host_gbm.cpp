@@ -103,6 +103,20 @@ struct Pcg {
   float next_float() {  // java.util.Random.nextFloat over PCGRNG.next(24) (:86)
     return (float)(int32_t)(next_long() & ((1LL << 24) - 1)) / (float)(1 << 24);
   }
+  double next_double() {  // java.util.Random.nextDouble over PCGRNG.next(bits)
+    const int64_t a = next_long() & ((1LL << 26) - 1);
+    const int64_t b = next_long() & ((1LL << 27) - 1);
+    return (double)((a << 27) + b) * 0x1.0p-53;
+  }
+  double next_gaussian_after_seed() {  // java.util.Random.nextGaussian, first value after setSeed (polar method)
+    double v1, v2, s;
+    do {
+      v1 = 2 * next_double() - 1;
+      v2 = 2 * next_double() - 1;
+      s = v1 * v1 + v2 * v2;
+    } while (s >= 1 || s == 0);
+    return v1 * std::sqrt(-2 * std::log(s) / s);
+  }
   int32_t next_bounded(int32_t bound) {  // :88-118
     const uint64_t threshold = (uint64_t)((-(int64_t)bound) % (int64_t)bound) & 0xFFFFFFFFULL;
     for (;;) {
@@ -316,6 +330,8 @@ struct h2ot_gbm {
   std::vector<std::vector<FinishedTree>> trees;  // [tree][k]
   std::vector<float> varimp;
   bool capture = false;
+  double pred_noise_bandwidth = 0;            // GBMParameters._pred_noise_bandwidth (T/gbm/GBMModel.java:28)
+  std::vector<double> sample_rate_per_class;  // SharedTreeParameters._sample_rate_per_class (empty: null)
   std::vector<Capture> captures;
   h2ot_gbm_timing timing{};
   // scratch
@@ -744,6 +760,16 @@ int allreduce(h2ot_gbm* g, double* v, int64_t n, int op) {
   return h2ot_allreduce_host_f64(g->eng, v, n, op);
 }
 
+// AddTreeContributions' per-node factor 1 + nextGaussian * pred_noise_bandwidth, the generator re-seeded per (tree, class, node)
+// (T/gbm/GBM.java:1450, 1458-1463; the second factor of the seed is Java int arithmetic widened with its sign)
+double noise_factor(const h2ot_gbm* g, int k, int nid) {
+  const int32_t f2 = (int32_t)(0xFAAAAAABu + (uint32_t)(k * g->p.ntrees + g->ntrees_built));
+  const int64_t baseseed = (int64_t)(((uint64_t)0xDECAF + (uint64_t)g->p.seed) * (uint64_t)(int64_t)f2);
+  Pcg r(g->p.seed);
+  r.set_seed((int64_t)((uint64_t)baseseed + (uint64_t)(int64_t)nid));
+  return 1.0 + r.next_gaussian_after_seed() * g->pred_noise_bandwidth;
+}
+
 // GBM.buildNextKTrees (T/gbm/GBM.java:464-591)
 int build_next_k_trees(h2ot_gbm* g) {
   const int K = g->K;
@@ -858,11 +884,20 @@ int build_next_k_trees(h2ot_gbm* g) {
       for (int i = 0; i < leaves[k]; i++)
         if (t.ns[i].sid >= 0) pred[(size_t)t.ns[i].sid] = t.ns[i].pred;
       for (int i = 0; i < nleaf; i++) pred[(size_t)leaf_base + i] = t.ns[leaves[k] + i].pred;
-      GTRY(h2ot_add_tree(g->eng, k, (int)pred.size(), pred.data()));
+      if (g->pred_noise_bandwidth != 0) {
+        std::vector<double> fac(pred.size(), 1.0);
+        for (int i = 0; i < nleaf; i++) fac[(size_t)leaf_base + i] = noise_factor(g, k, leaves[k] + i);
+        if (nleaf <= 0) fac[0] = noise_factor(g, k, 0);
+        GTRY(h2ot_add_tree_scaled(g->eng, k, (int)pred.size(), pred.data(), fac.data()));
+      } else GTRY(h2ot_add_tree(g->eng, k, (int)pred.size(), pred.data()));
     } else {
       std::vector<float> pred(t.len());
       for (int i = 0; i < t.len(); i++) pred[i] = t.ns[i].pred;
-      GTRY(h2ot_add_tree(g->eng, k, t.len(), pred.data()));
+      if (g->pred_noise_bandwidth != 0) {
+        std::vector<double> fac(pred.size());
+        for (int i = 0; i < t.len(); i++) fac[i] = noise_factor(g, k, i);
+        GTRY(h2ot_add_tree_scaled(g->eng, k, t.len(), pred.data(), fac.data()));
+      } else GTRY(h2ot_add_tree(g->eng, k, t.len(), pred.data()));
     }
     outs[k].nodes = std::move(t.ns);
     for (Node& n : outs[k].nodes) n.hs.clear();
@@ -1175,6 +1210,8 @@ int h2ot_gbm_init(h2ot_gbm* g) {
     int64_t skipped = 0;
     GTRY(h2ot_init_model(g->eng, f0.data(), &skipped));
   }
+  // this driver sequences whole trees: calls that return nothing need not wait for the stream
+  GTRY(h2ot_set_lazy_sync(g->eng, 1));
   g->inited = true;
   return H2OT_OK;
 }
@@ -1549,6 +1586,21 @@ int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_t
     if (out_fps) out_fps[i] = f->fps[i];
   }
   return H2OT_OK;
+}
+int h2ot_gbm_set_pred_noise_bandwidth(h2ot_gbm* g, double bandwidth) {
+  if (!g || !(bandwidth >= 0)) GFAIL(H2OT_ERR_INVALID, "pred_noise_bandwidth must be >= 0");  // T/gbm/GBM.java:189-190
+  if (g->p.algo != H2OT_ALGO_GBM) GFAIL(H2OT_ERR_UNSUPPORTED, "pred_noise_bandwidth is a GBM parameter");
+  g->pred_noise_bandwidth = bandwidth;
+  return H2OT_OK;
+}
+int h2ot_gbm_set_sample_rate_per_class(h2ot_gbm* g, const double* rates, int32_t n) {
+  if (!g || n < 0 || (n > 0 && !rates)) GFAIL(H2OT_ERR_INVALID, "bad rates");
+  if (n > 0 && g->nclass < 2) GFAIL(H2OT_ERR_INVALID, "sample_rate_per_class needs a categorical response");
+  if (n > 0 && n != g->nclass) GFAIL(H2OT_ERR_INVALID, "sample_rate_per_class needs one rate per response class");
+  for (int i = 0; i < n; i++)
+    if (!(rates[i] >= 0 && rates[i] <= 1)) GFAIL(H2OT_ERR_INVALID, "sample rates must be within [0, 1]");
+  g->sample_rate_per_class.assign(rates, rates + n);
+  return h2ot_set_sample_rate_per_class(g->eng, rates, n);
 }
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");

@@ -253,11 +253,16 @@ __device__ __forceinline__ uint32_t pcg_next(unsigned long long& state, unsigned
   const uint32_t rot = (uint32_t)(old >> 59);
   return (xorshifted >> rot) | (xorshifted << ((-rot) & 31));
 }
+// rate_per_class: Sample._rate_per_class (T/Sample.java:14, 30), indexed by the response class; nullptr == null
 __global__ void __launch_bounds__(256) sample_kernel(int64_t n, int64_t row_offset, long long tree_seed, float rate,
-                                                     double rate_d, const double* resp, int32_t* nids) {
+                                                     double rate_d, const double* rate_per_class, int n_rates, const double* resp, int32_t* nids) {
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n; row += (int64_t)gridDim.x * blockDim.x) {
     bool skip = isnan(resp[row]);
     if (!skip) {
+      if (rate_per_class) {
+        const long long cls = (long long)resp[row];  // (int) ys.at8(row)
+        rate_d = (cls >= 0 && cls < n_rates) ? rate_per_class[cls] : 0.0;
+      }
       // rand.setSeed(_tree._seed + row + nids.start()) ; nextFloat() = next(24) / (float)(1 << 24)
       const unsigned long long inc = 3ULL;  // (seq << 1) | 1 with seq == 1
       unsigned long long state = 0ULL;
@@ -398,6 +403,7 @@ struct AddTreeArgs {
   int32_t* nids;
   double* F;
   const float* node_pred;
+  const double* node_factor;  // nullptr, or per node 1 + nextGaussian * pred_noise_bandwidth (T/gbm/GBM.java:1458-1463)
 };
 __global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
   for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < a.n; row += (int64_t)gridDim.x * blockDim.x) {
@@ -411,7 +417,8 @@ __global__ void __launch_bounds__(256) add_tree_kernel(AddTreeArgs a) {
     }
     a.nids[row] = nv;
     const float pred = nid < a.n_nodes ? a.node_pred[nid] : 0.f;
-    a.F[row] = (double)(float)__dadd_rn(a.F[row], (double)pred);  // float-rounded every tree (q3)
+    const double contrib = (a.node_factor && nid < a.n_nodes) ? __dmul_rn(a.node_factor[nid], (double)pred) : (double)pred;
+    a.F[row] = (double)(float)__dadd_rn(a.F[row], contrib);  // float-rounded every tree (q3)
   }
 }
 

@@ -143,6 +143,7 @@ typedef struct h2ot_stats { /* diagnostics: device time per kernel family (ms) a
   int64_t hist_algo_bytes;   /* algorithmic bytes of those passes (SURVEY.md section 8d formula) */
   int64_t hist_launches;     /* histogram-accumulation kernel launches (ms_hist / hist_launches = mean launch time) */
   int64_t sparse_launches;   /* of those: launches of the leaf-major kernel used on levels with per-node column sampling */
+  double ms_exchange;        /* cross-rank exchange of the level histograms (peer-memory kernel or the NCCL all-reduces), waits for the slowest rank included */
 } h2ot_stats;
 
 /* ---- lifetime: one engine per model build per GPU (created after T/SharedTree.java:385, destroyed in the finally at :407-425) */
@@ -217,6 +218,9 @@ int h2ot_set_gamma_bounds(h2ot_engine* h, const double in[2]);
 /* Starts class-tree k: clears its node table, fixes the accumulator scale from work_abs_bound
  * (>= max |Work_k| over ALL ranks), and runs Sample (T/Sample.java:22-36) when sample_rate < 1. */
 int h2ot_begin_tree(h2ot_engine* h, int32_t k, int64_t tree_seed, double sample_rate, double work_abs_bound);
+/* Sample._rate_per_class (T/Sample.java:14, 30; SharedTreeModel.java:59): rates[n] indexed by the response class, used by every
+ * later h2ot_begin_tree / h2ot_sample instead of their sample_rate (which then only has to be passed); n == 0 goes back to null. */
+int h2ot_set_sample_rate_per_class(h2ot_engine* h, const double* rates, int32_t n);
 
 /* Split points of the NEXT h2ot_build_level / h2ot_level_step of class-tree k: one pool of doubles, referenced by the
  * descriptors' splitpts_off / splitpts_n (DHistogram._splitPts as DHistogram.init leaves them, T/DHistogram.java:343-401).
@@ -298,6 +302,9 @@ int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided
 int h2ot_gamma_pass(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_leaf_nodes, double* out_num, double* out_denom);
 /* GBM.AddTreeContributions (T/gbm/GBM.java:1410-1470): Tree_k <- (float)(Tree_k + pred[nid]); NIDs_k <- 0 / DECIDED_ROW. */
 int h2ot_add_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred /*[n_nodes], leaf nids used*/);
+/* The same with GBM's pred_noise_bandwidth (T/gbm/GBM.java:1450-1463): Tree_k <- (float)(Tree_k + node_factor[nid] * pred[nid]); the
+ * caller draws the per-node factors 1 + nextGaussian * bandwidth (they depend on tree, class and node only, not on the row). */
+int h2ot_add_tree_scaled(h2ot_engine* h, int32_t k, int32_t n_nodes, const float* node_pred, const double* node_factor);
 
 /* ---- scoring a frame with finished trees: SharedTreeMojoModel.scoreTree + scoreTreeRange's
  * `preds[k] += tree value` (h2o-genmodel .../algos/tree/SharedTreeMojoModel.java:129-240, 1043-1076). Every row of the engine's frame
@@ -373,6 +380,10 @@ int h2ot_stats_reset(h2ot_engine* h);
 /* 0: default (shared-memory privatised histograms; leaf-major sparse kernel on levels with per-node column sampling),
  * 1: global (L2) atomics only, 2: column-major shared-memory kernels only — 1 and 2 are used by tests to cross-check. */
 int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
+/* on != 0: h2ot_begin_tree, h2ot_sample, h2ot_set_tree and h2ot_add_tree[_scaled] -- calls that hand nothing back to the host -- return
+ * without waiting for the stream; their work, kernel times and any error surface at the next call that does wait (every call that
+ * returns data). A model builder that sequences whole trees saves three stream synchronisations per tree. on == 0: waits now. */
+int h2ot_set_lazy_sync(h2ot_engine* h, int32_t on);
 
 /* ---- histogram of one column for callers that cannot allocate device memory.
  * No counterpart in the reference: it exists for embedders whose process may not call cudaMalloc once it is running (a JVM or

@@ -100,6 +100,12 @@ int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss);
  * order -- with AUCBuilder.reduce and evaluates AUC2.compute_auc. out_ths / out_tps / out_fps (nullable, 400 doubles each) receive
  * the final builder's bins, *out_nbins their number, *out_chunk_rows the rows per chunk the device used. */
 int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_ths, double* out_tps, double* out_fps, int64_t* out_chunk_rows);
+/* Two model parameters that are not in h2ot_gbm_params (set after h2ot_gbm_create, before h2ot_gbm_train):
+ * GBMParameters._pred_noise_bandwidth (h2o-algos/src/main/java/hex/tree/gbm/GBMModel.java:28; AddTreeContributions multiplies a
+ * leaf's value by 1 + nextGaussian * bandwidth, gbm/GBM.java:1450-1463) and SharedTreeParameters._sample_rate_per_class
+ * (hex/tree/SharedTreeModel.java:59; Sample.java:14-30: one rate per response class, n == number of classes; n == 0: null). */
+int h2ot_gbm_set_pred_noise_bandwidth(h2ot_gbm* g, double bandwidth);
+int h2ot_gbm_set_sample_rate_per_class(h2ot_gbm* g, const double* rates, int32_t n);
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out);
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out);
 h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g);

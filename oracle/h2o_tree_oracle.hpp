@@ -132,6 +132,18 @@ struct PCGRNG {
   double nextDouble() {                                        // java.util.Random.nextDouble
     return (double)(((int64_t)next(26) << 27) + next(27)) * 0x1.0p-53;
   }
+  // java.util.Random.nextGaussian (polar method) right after a setSeed, which drops a cached second value: only the first of
+  // the pair is ever used by AddTreeContributions (T/gbm/GBM.java:1460-1463). StrictMath.log / sqrt: libm's.
+  double nextGaussianAfterSeed() {
+    double v1, v2, s;
+    do {
+      v1 = 2 * nextDouble() - 1;
+      v2 = 2 * nextDouble() - 1;
+      s = v1 * v1 + v2 * v2;
+    } while (s >= 1 || s == 0);
+    const double multiplier = std::sqrt(-2 * std::log(s) / s);
+    return v1 * multiplier;
+  }
 };
 
 // java.util.Random (LCG) — only needed to replay TT/DHistogramTest.java:173-206 inputs.
@@ -211,6 +223,8 @@ struct Params {
   int nbins_top_level = 1 << 10;
   double min_split_improvement = 1e-5;
   double sample_rate = 1.0;
+  std::vector<double> sample_rate_per_class;  // empty == null (T/SharedTreeModel.java:59)
+  double pred_noise_bandwidth = 0;            // T/gbm/GBMModel.java:28
   double col_sample_rate = 1.0;
   double col_sample_rate_per_tree = 1.0;
   double col_sample_rate_change_per_level = 1.0;
@@ -1533,8 +1547,9 @@ struct GBM {
     for (int64_t row = 0; row < fr.nrows(); row++) {
       bool skip = std::isnan(fr.y[row]);
       if (!skip) {
+        const double rate = parms.sample_rate_per_class.empty() ? parms.sample_rate : parms.sample_rate_per_class[(size_t)(int)fr.y[row]];
         rand.setSeed((int64_t)((uint64_t)tree._seed + (uint64_t)row));
-        skip = rand.nextFloat() >= parms.sample_rate;
+        skip = rand.nextFloat() >= rate;
       }
       if (skip) nids_[k][row] = OUT_OF_BAG;
     }
@@ -1618,7 +1633,7 @@ struct GBM {
       ktrees[k]->newUndecided(NO_PARENT, hcs[k][0]);
       hcs[k][0] = ktrees[k]->node(0)._hs;
     }
-    if (parms.sample_rate < 1)
+    if (parms.sample_rate < 1 || !parms.sample_rate_per_class.empty())  // useRowSampling (T/SharedTreeModel.java:86-88)
       for (int k = 0; k < K; k++) sample(k, *ktrees[k]);
     for (int depth = 0; depth < parms.max_depth; depth++) {
       bool did_split = false;
@@ -1700,9 +1715,14 @@ struct GBM {
         leafNode._pred = (float)gf;
       }
     }
-    // AddTreeContributions :1410-1470 (pred_noise_bandwidth == 0)
+    // AddTreeContributions :1410-1470
     for (int k = 0; k < K; k++) {
       DTree& tree = *ktrees[k];
+      PCGRNG noise_rng(parms.seed);
+      // (0xDECAF + _seed) * (0xFAAAAAAB + k * _ntrees1 + _ntrees2): the second factor is Java INT arithmetic (0xFAAAAAAB is a
+      // negative int literal) widened with its sign, the product is long; _ntrees2 = trees built before this iteration
+      const int32_t f2 = (int32_t)(0xFAAAAAABu + (uint32_t)(k * parms.ntrees + ntrees_built));
+      const int64_t baseseed = (int64_t)(((uint64_t)0xDECAF + (uint64_t)parms.seed) * (uint64_t)(int64_t)f2);
       for (int64_t row = 0; row < fr.nrows(); row++) {
         int nid = nids_[k][row];
         nids_[k][row] = FRESH;
@@ -1711,7 +1731,12 @@ struct GBM {
           if (w == 0 || std::isnan(fr.y[row])) nids_[k][row] = DECIDED_ROW;
           continue;
         }
-        tree_[k][row] = (float)(tree_[k][row] + 1 * (double)tree.node(nid)._pred);
+        double factor = 1;
+        if (parms.pred_noise_bandwidth != 0) {
+          noise_rng.setSeed((int64_t)((uint64_t)baseseed + (uint64_t)(int64_t)nid));
+          factor += noise_rng.nextGaussianAfterSeed() * parms.pred_noise_bandwidth;
+        }
+        tree_[k][row] = (float)(tree_[k][row] + factor * (double)tree.node(nid)._pred);
       }
     }
     std::vector<TreeOut> outs(K);

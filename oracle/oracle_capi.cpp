@@ -206,6 +206,9 @@ struct OrcParams {
   long long chunk_rows;
   double tweedie_power;
   long long histogram_type;  // HistoType
+  double pred_noise_bandwidth;
+  long long n_rate_per_class;          // 0: sample_rate_per_class == null
+  double sample_rate_per_class[16];
 };
 static Params to_params(const OrcParams* p) {
   Params q;
@@ -229,6 +232,8 @@ static Params to_params(const OrcParams* p) {
   q.seed = p->seed;
   if (p->tweedie_power > 0) q.tweedie_power = p->tweedie_power;
   q.histogram_type = (int)p->histogram_type;
+  q.pred_noise_bandwidth = p->pred_noise_bandwidth;
+  q.sample_rate_per_class.assign(p->sample_rate_per_class, p->sample_rate_per_class + std::min<long long>(16, std::max<long long>(0, p->n_rate_per_class)));
   return q;
 }
 

@@ -37,7 +37,8 @@ class OrcParams(C.Structure):
                 ("col_sample_rate_change_per_level", C.c_double), ("learn_rate", C.c_double),
                 ("learn_rate_annealing", C.c_double), ("max_abs_leafnode_pred", C.c_double),
                 ("seed", C.c_longlong), ("chunk_rows", C.c_longlong), ("tweedie_power", C.c_double),
-                ("histogram_type", C.c_longlong)]
+                ("histogram_type", C.c_longlong), ("pred_noise_bandwidth", C.c_double), ("n_rate_per_class", C.c_longlong),
+                ("sample_rate_per_class", C.c_double * 16)]
 
 
 class OrcHistDesc(C.Structure):
@@ -59,6 +60,12 @@ def default_params(**kw):
                   learn_rate=0.1, learn_rate_annealing=1.0, max_abs_leafnode_pred=float(np.finfo(np.float64).max),
                   seed=1234, chunk_rows=0, tweedie_power=1.5, histogram_type=0)
     for k, v in kw.items():
+        if k == "sample_rate_per_class":
+            if v is not None:
+                p.n_rate_per_class = len(v)
+                for i, r in enumerate(v):
+                    p.sample_rate_per_class[i] = r
+            continue
         setattr(p, k, v)
     return p
 

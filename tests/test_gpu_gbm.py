@@ -475,3 +475,25 @@ def test_device_level_loop_grows_the_same_trees_as_the_host_loop(case, monkeypat
     gm, om = _run_both(X, y, cats, w=w, off=off, capture=False, **kw)
     h2ot_lib.compare_models(gm, om, K=K, check_levels=False)
     gm.close()
+
+
+@pytest.mark.parametrize("capture", [True, False])
+def test_sample_rate_per_class_and_pred_noise_bandwidth(capture):
+    """SharedTreeParameters._sample_rate_per_class (T/Sample.java:14-30: the row's rate is picked by its response class, and rows
+    are sampled even when sample_rate == 1) and GBMParameters._pred_noise_bandwidth (T/gbm/GBM.java:1450-1463: every leaf's value is
+    scaled by 1 + nextGaussian * bandwidth, the generator re-seeded per tree, class and node) against the oracle -- level by
+    level through the host loop (capture) and through the device loop."""
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=41)
+    gm, om = _run_both(X, y, cats, capture=capture, ntrees=5, max_depth=5, nbins=20, seed=77, sample_rate_per_class=[0.4, 0.9],
+                       pred_noise_bandwidth=0.25)
+    st = h2ot_lib.compare_models(gm, om, check_levels=capture)
+    if capture:
+        # out-of-bag rows follow the class rates: roughly 60 % of class 0 and 10 % of class 1 sit out of every tree
+        nids = gm.capture_nids(1)
+        oob = nids <= -2
+        assert abs(oob[y == 0].mean() - 0.6) < 0.03 and abs(oob[y == 1].mean() - 0.1) < 0.03
+    # the noise is real: the same build without it predicts differently
+    g0, _ = _run_both(X, y, cats, capture=False, ntrees=5, max_depth=5, nbins=20, seed=77, sample_rate_per_class=[0.4, 0.9])
+    assert not np.array_equal(g0.predictions(), gm.predictions())
+    g0.close()
+    gm.close()
