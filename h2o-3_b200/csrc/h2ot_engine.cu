@@ -127,6 +127,9 @@ struct TreeState {  // per class-tree k
     DBuf<int32_t> err;
     std::vector<unsigned char*> lvl_stage;   // pinned staging of each level's upload (the levels are enqueued ahead of the GPU)
     std::vector<size_t> lvl_stage_cap;
+    std::vector<char> lvl_stage_own;         // 1: a block of its own (not a slice of the arena)
+    unsigned char* arena = nullptr;          // pinned arena the levels' staging slices come from
+    size_t arena_cap = 0;
     unsigned char* out_stage = nullptr;      // pinned: splits, exists, err, root concentration
     size_t out_stage_cap = 0;
     // the previous level as the step kernel reads it
@@ -493,7 +496,8 @@ int h2ot_destroy(h2ot_engine* h) {
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_factor.release(); t.d_sp.release();
     t.dev.lvl_alt.release(); t.dev.pack_alt.release(); t.dev.maxex[0].release(); t.dev.maxex[1].release(); t.dev.exists.release();
     t.dev.tree_splits.release(); t.dev.nb_caps.release(); t.dev.err.release();
-    for (unsigned char* sp : t.dev.lvl_stage) if (sp) cudaFreeHost(sp);
+    for (size_t i = 0; i < t.dev.lvl_stage.size(); i++) if (t.dev.lvl_stage[i] && t.dev.lvl_stage_own[i]) cudaFreeHost(t.dev.lvl_stage[i]);
+    if (t.dev.arena) cudaFreeHost(t.dev.arena);
     if (t.dev.out_stage) cudaFreeHost(t.dev.out_stage);
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
@@ -1639,18 +1643,21 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     TRY(t.d_lvl.ensure(total));
     unsigned char* stage = nullptr;
     if (t.dev.active) {
-      // the device loop enqueues its levels ahead of the GPU: every level keeps its own pinned staging until the tree is done
+      // the device loop enqueues its levels ahead of the GPU: every level keeps its own slice of one pinned arena until the tree
+      // is done (h2ot_tree_levels_begin sized it for all levels; a level that needs more than its slice gets a block of its own)
       const size_t d = (size_t)t.dev.depth;
       if (t.dev.lvl_stage.size() <= d) {
         t.dev.lvl_stage.resize(d + 1, nullptr);
         t.dev.lvl_stage_cap.resize(d + 1, 0);
+        t.dev.lvl_stage_own.resize(d + 1, 0);
       }
       if (total > t.dev.lvl_stage_cap[d]) {
-        if (t.dev.lvl_stage[d]) cudaFreeHost(t.dev.lvl_stage[d]);
+        if (t.dev.lvl_stage[d] && t.dev.lvl_stage_own[d]) cudaFreeHost(t.dev.lvl_stage[d]);
         t.dev.lvl_stage[d] = nullptr;
         t.dev.lvl_stage_cap[d] = 0;
         CUDA_TRY(cudaMallocHost(&t.dev.lvl_stage[d], total * 2));
         t.dev.lvl_stage_cap[d] = total * 2;
+        t.dev.lvl_stage_own[d] = 1;
       }
       stage = t.dev.lvl_stage[d];
     } else {
@@ -2090,6 +2097,32 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
       caps[(size_t)d * C + c] = nb;
       if (nb > 0 && !(root_descs[c].flags & H2OT_DESC_ISCAT)) nb = std::max(nb >> 1, nbins);
       if (nb > 0 && (root_descs[c].flags & H2OT_DESC_ISCAT)) nb = std::min(std::max(nb, 1), nbins_cats);
+    }
+  }
+  {  // one pinned arena for the uploads of all levels: [descriptors of 2^d slots x C] + groups and column lists (bounded by the same)
+    std::vector<size_t> need((size_t)D);
+    size_t sum = 0;
+    for (int d = 0; d < D; d++) {
+      need[(size_t)d] = (((size_t)1 << d) * C * sizeof(DescDev) * 2 + ((size_t)C + 64) * 64 + 4095) & ~(size_t)4095;
+      sum += need[(size_t)d];
+    }
+    if (sum > dv.arena_cap) {
+      if (dv.arena) cudaFreeHost(dv.arena);
+      dv.arena = nullptr;
+      dv.arena_cap = 0;
+      CUDA_TRY(cudaMallocHost(&dv.arena, sum));
+      dv.arena_cap = sum;
+      for (size_t i = 0; i < dv.lvl_stage.size(); i++)
+        if (dv.lvl_stage[i] && dv.lvl_stage_own[i]) cudaFreeHost(dv.lvl_stage[i]);
+      dv.lvl_stage.assign((size_t)D, nullptr);
+      dv.lvl_stage_cap.assign((size_t)D, 0);
+      dv.lvl_stage_own.assign((size_t)D, 0);
+      size_t off = 0;
+      for (int d = 0; d < D; d++) {
+        dv.lvl_stage[(size_t)d] = dv.arena + off;
+        dv.lvl_stage_cap[(size_t)d] = need[(size_t)d];
+        off += need[(size_t)d];
+      }
     }
   }
   CUDA_TRY(cudaMemsetAsync(t.nodes.p, 0xFF, S * sizeof(h2ot_decided_node), h->stream));  // col = pid = -1
