@@ -381,6 +381,7 @@ def run_b200(args):
     eng = gm.engine()
     for _ in range(args.warmup):
         gm.train(1)
+    gm.flush()  # (pipelined builds return with the last tree still on the device)
     barrier()
     s0 = eng.stats()
     t0s = gm.timing()
@@ -394,6 +395,7 @@ def run_b200(args):
     e0.record()
     for _ in range(args.steps):
         gm.train(1)
+    gm.flush()  # the host waits for the last tree and mirrors it: the events below bracket the wall time of the K steps
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)

@@ -104,6 +104,7 @@ class GbmTiming(C.Structure):
 
 # every symbol declared in include/h2ot.h and include/h2ot_gbm.h (tests check that the library exports all of them)
 ENGINE_SYMBOLS = [
+    "h2ot_tree_finish_enqueue", "h2ot_tree_levels_end2", "h2ot_compute_residuals_async",
     "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
@@ -115,7 +116,7 @@ ENGINE_SYMBOLS = [
     "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end", "h2ot_tree_levels_begin", "h2ot_tree_levels_end",
 ]
 GBM_SYMBOLS = [
-    "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
+    "h2ot_gbm_flush", "h2ot_gbm_predict", "h2ot_gbm_create", "h2ot_gbm_destroy", "h2ot_gbm_set_column", "h2ot_gbm_load_chunk", "h2ot_gbm_chunks_done", "h2ot_gbm_set_response", "h2ot_gbm_set_weights",
     "h2ot_gbm_set_offset", "h2ot_gbm_comm_init", "h2ot_gbm_init", "h2ot_gbm_train", "h2ot_gbm_capture_levels",
     "h2ot_gbm_init_f", "h2ot_gbm_ntrees", "h2ot_gbm_tree_len", "h2ot_gbm_tree_leaves_start", "h2ot_gbm_tree_nodes",
     "h2ot_gbm_tree_compress", "h2ot_gbm_predictions", "h2ot_gbm_oobt", "h2ot_gbm_score", "h2ot_gbm_auc", "h2ot_gbm_set_pred_noise_bandwidth", "h2ot_gbm_set_sample_rate_per_class", "h2ot_gbm_varimp", "h2ot_gbm_timing_get", "h2ot_gbm_engine", "h2ot_gbm_ncaptures",
@@ -203,6 +204,7 @@ def load():
     L.h2ot_gbm_comm_init.argtypes = [vp, i32, i32, vp]
     L.h2ot_gbm_init.argtypes = [vp]
     L.h2ot_gbm_train.argtypes = [vp, i32]
+    L.h2ot_gbm_flush.argtypes = [vp]
     L.h2ot_gbm_capture_levels.argtypes = [vp, i32]
     L.h2ot_gbm_init_f.argtypes = [vp]
     L.h2ot_gbm_init_f.restype = dbl
@@ -585,6 +587,11 @@ class GBM:
     def train(self, n_iterations=None):
         n = self.params.ntrees if n_iterations is None else n_iterations
         _check(self.L.h2ot_gbm_train(self.g, n))
+        return self
+
+    def flush(self):
+        """Waits for the trees still in flight on the device (pipelined builds) and mirrors them."""
+        _check(self.L.h2ot_gbm_flush(self.g))
         return self
 
     def engine(self):

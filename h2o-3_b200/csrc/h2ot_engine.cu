@@ -137,8 +137,16 @@ struct TreeState {  // per class-tree k
     const double *prev_min2 = nullptr, *prev_maxIn = nullptr, *prev_wna = nullptr, *prev_maxex = nullptr;
     const uint8_t* prev_has = nullptr;
     const h2ot_split* prev_best = nullptr;
-    bool pending = false;
-    size_t o_exists = 0, o_err = 0, o_conc = 0;  // offsets inside out_stage
+    // Two trees of a class may be in flight (the host mirrors tree t while the device builds tree t + 1): every pinned staging
+    // area has two halves, a tree uses half `slot`
+    int next_slot = 0, n_pend = 0;
+    int pend_slots[2] = {0, 0};                  // oldest first
+    cudaEvent_t ev[2] = {nullptr, nullptr};      // recorded after a tree's last download was enqueued
+    size_t timer_mark[2] = {0, 0};               // engine timers recorded before ev[slot]
+    bool has_pred[2] = {false, false};           // h2ot_tree_finish_enqueue ran for the tree in this half
+    size_t arena_half = 0, out_half = 0;
+    std::vector<size_t> lvl_off;                 // offset of each level's slice inside an arena half
+    size_t o_exists = 0, o_err = 0, o_conc = 0, o_pred = 0;  // offsets inside an out_stage half
   } dev;
   DBuf<double> d_vals;
   // small per-level results, packed in one device buffer so that h2ot_level_step brings them back with one copy:
@@ -292,6 +300,7 @@ int finish_call(h2ot_engine* h) {
     if (t.b) h->event_pool.push_back(t.b);
   }
   h->timers.clear();
+  for (TreeState& ts : h->ts) ts.dev.timer_mark[0] = ts.dev.timer_mark[1] = 0;
   CUDA_TRY(cudaGetLastError());
   if (h->xr_err_host && *h->xr_err_host) H2OT_FAIL(H2OT_ERR_COMM, "peer-memory exchange timed out waiting for another rank");
   return H2OT_OK;
@@ -326,7 +335,7 @@ int grid_for(h2ot_engine* h, int64_t n, int block, int per_sm = 8) {
 int exponent_for(double bound, int bitsN, int cap_bits = 0) {
   if (!(bound > 0) || std::isinf(bound)) bound = 1.0;
   int e2;
-  std::frexp(bound, &e2);  // bound <= 2^e2
+  if (std::frexp(bound, &e2) == 0.5) e2--;  // bound <= 2^e2 (an exact power of two is its own bound: |y - p| <= 1 keeps e2 = 0)
   int e = 62 - bitsN - e2;
   if (cap_bits > 0) e = std::min(e, cap_bits - e2);
   return std::max(-900, std::min(900, e));
@@ -499,6 +508,7 @@ int h2ot_destroy(h2ot_engine* h) {
     for (size_t i = 0; i < t.dev.lvl_stage.size(); i++) if (t.dev.lvl_stage[i] && t.dev.lvl_stage_own[i]) cudaFreeHost(t.dev.lvl_stage[i]);
     if (t.dev.arena) cudaFreeHost(t.dev.arena);
     if (t.dev.out_stage) cudaFreeHost(t.dev.out_stage);
+    for (cudaEvent_t e : t.dev.ev) if (e) cudaEventDestroy(e);
   }
   h->d_Fp.release(); h->d_workp.release(); h->d_nidsp.release(); h->d_absmax.release(); h->d_scalar.release();
   h->d_rollup.release(); h->d_cols.release(); h->d_rate_per_class.release();
@@ -1651,6 +1661,8 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
         t.dev.lvl_stage_cap.resize(d + 1, 0);
         t.dev.lvl_stage_own.resize(d + 1, 0);
       }
+      // (a block of its own is shared by the two trees that may be in flight: drain the stream before touching it)
+      if (total > t.dev.lvl_stage_cap[d] || t.dev.lvl_stage_own[d]) CUDA_TRY(cudaStreamSynchronize(h->stream));
       if (total > t.dev.lvl_stage_cap[d]) {
         if (t.dev.lvl_stage[d] && t.dev.lvl_stage_own[d]) cudaFreeHost(t.dev.lvl_stage[d]);
         t.dev.lvl_stage[d] = nullptr;
@@ -2062,8 +2074,10 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   if (max_depth < 1 || max_depth > 10) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_levels: max_depth must be in 1..10");
   TreeState& t = h->ts[k];
   TreeState::DevLoop& dv = t.dev;
-  if (dv.pending || t.step_pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_begin: the previous tree / level of this class-tree was not ended");
+  if (dv.n_pend >= 2 || t.step_pending)
+    H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_begin: two trees of this class-tree are already in flight (or a level was not ended)");
   const int C = h->C, D = max_depth;
+  const int slot = dv.next_slot;
   const size_t S = ((size_t)1 << (D + 1)) - 1;  // static ids: levels 0 .. D (the last one only as children that exist or not)
   for (int c = 0; c < C; c++)
     if ((root_descs[c].flags & H2OT_DESC_ACTIVE) && (root_descs[c].flags & (H2OT_DESC_SPLITPTS | H2OT_DESC_CHECKFLOAT)))
@@ -2081,14 +2095,18 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   dv.o_exists = n_splits * sizeof(h2ot_split);
   dv.o_err = dv.o_exists + ((S + 7) & ~(size_t)7);
   dv.o_conc = dv.o_err + 8;
-  const size_t out_bytes = dv.o_conc + (size_t)C * sizeof(double);
-  if (out_bytes > dv.out_stage_cap) {
+  dv.o_pred = dv.o_conc + (size_t)C * sizeof(double);
+  const size_t out_bytes = (dv.o_pred + S * sizeof(float) + 63) & ~(size_t)63;
+  if (out_bytes * 2 > dv.out_stage_cap || out_bytes != dv.out_half) {
+    if (dv.n_pend > 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_begin: the tree shape changed while a tree is in flight");
     if (dv.out_stage) cudaFreeHost(dv.out_stage);
     dv.out_stage = nullptr;
     dv.out_stage_cap = 0;
-    CUDA_TRY(cudaMallocHost(&dv.out_stage, out_bytes));
-    dv.out_stage_cap = out_bytes;
+    CUDA_TRY(cudaMallocHost(&dv.out_stage, out_bytes * 2));
+    dv.out_stage_cap = out_bytes * 2;
+    dv.out_half = out_bytes;
   }
+  unsigned char* const out_stage = dv.out_stage + (size_t)slot * dv.out_half;
   // widest histogram a column can have at each depth (DHistogram ctor rule: max(parent nbin >> 1, nbins); categoricals keep theirs)
   std::vector<int32_t> caps((size_t)D * C, 0);
   for (int c = 0; c < C; c++) {
@@ -2106,24 +2124,30 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
       need[(size_t)d] = (((size_t)1 << d) * C * sizeof(DescDev) * 2 + ((size_t)C + 64) * 64 + 4095) & ~(size_t)4095;
       sum += need[(size_t)d];
     }
-    if (sum > dv.arena_cap) {
+    if (sum * 2 > dv.arena_cap || sum != dv.arena_half || dv.lvl_off.size() != (size_t)D) {
+      if (dv.n_pend > 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_begin: the tree shape changed while a tree is in flight");
+      CUDA_TRY(cudaStreamSynchronize(h->stream));
       if (dv.arena) cudaFreeHost(dv.arena);
       dv.arena = nullptr;
       dv.arena_cap = 0;
-      CUDA_TRY(cudaMallocHost(&dv.arena, sum));
-      dv.arena_cap = sum;
+      CUDA_TRY(cudaMallocHost(&dv.arena, sum * 2));
+      dv.arena_cap = sum * 2;
+      dv.arena_half = sum;
       for (size_t i = 0; i < dv.lvl_stage.size(); i++)
         if (dv.lvl_stage[i] && dv.lvl_stage_own[i]) cudaFreeHost(dv.lvl_stage[i]);
       dv.lvl_stage.assign((size_t)D, nullptr);
       dv.lvl_stage_cap.assign((size_t)D, 0);
       dv.lvl_stage_own.assign((size_t)D, 0);
+      dv.lvl_off.assign((size_t)D, 0);
       size_t off = 0;
       for (int d = 0; d < D; d++) {
-        dv.lvl_stage[(size_t)d] = dv.arena + off;
+        dv.lvl_off[(size_t)d] = off;
         dv.lvl_stage_cap[(size_t)d] = need[(size_t)d];
         off += need[(size_t)d];
       }
     }
+    for (int d = 0; d < D; d++)  // this tree's half (a level that outgrew its slice keeps its own block)
+      if (!dv.lvl_stage_own[(size_t)d]) dv.lvl_stage[(size_t)d] = dv.arena + (size_t)slot * dv.arena_half + dv.lvl_off[(size_t)d];
   }
   CUDA_TRY(cudaMemsetAsync(t.nodes.p, 0xFF, S * sizeof(h2ot_decided_node), h->stream));  // col = pid = -1
   CUDA_TRY(cudaMemsetAsync(dv.exists.p, 0, S, h->stream));
@@ -2175,7 +2199,7 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
     if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
     if (rc != H2OT_OK) break;
-    if (d == 0 && cudaMemcpyAsync(dv.out_stage + dv.o_conc, t.p_conc, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
+    if (d == 0 && cudaMemcpyAsync(out_stage + dv.o_conc, t.p_conc, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
       set_error("cudaMemcpyAsync failed");
       rc = H2OT_ERR_CUDA;
       break;
@@ -2217,14 +2241,14 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
       rc = H2OT_ERR_CUDA;
     }
   }
-  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage, dv.tree_splits.p, n_splits * sizeof(h2ot_split));
-  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage + dv.o_exists, dv.exists.p, S);
-  if (rc == H2OT_OK) rc = d2h(h, dv.out_stage + dv.o_err, dv.err.p, sizeof(int32_t));
-  if (rc == H2OT_OK && !t.done_ev && cudaEventCreateWithFlags(&t.done_ev, cudaEventDisableTiming) != cudaSuccess) {
+  if (rc == H2OT_OK) rc = d2h(h, out_stage, dv.tree_splits.p, n_splits * sizeof(h2ot_split));
+  if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_exists, dv.exists.p, S);
+  if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_err, dv.err.p, sizeof(int32_t));
+  if (rc == H2OT_OK && !dv.ev[slot] && cudaEventCreateWithFlags(&dv.ev[slot], cudaEventDisableTiming) != cudaSuccess) {
     set_error("cudaEventCreate failed");
     rc = H2OT_ERR_CUDA;
   }
-  if (rc == H2OT_OK && cudaEventRecord(t.done_ev, h->stream) != cudaSuccess) {
+  if (rc == H2OT_OK && cudaEventRecord(dv.ev[slot], h->stream) != cudaSuccess) {
     set_error("cudaEventRecord failed");
     rc = H2OT_ERR_CUDA;
   }
@@ -2234,47 +2258,166 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     if (h->steps_pending == 0) finish_call(h);
     return rc;
   }
-  dv.pending = true;
+  dv.next_slot = slot ^ 1;
+  dv.pend_slots[dv.n_pend++] = slot;
+  dv.timer_mark[slot] = h->timers.size();
+  dv.has_pred[slot] = false;
   h->steps_pending++;
   return H2OT_OK;
 }
 
-int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists) {
+// fold the first n engine timers (their events are known to have completed) into the stats
+static void fold_timers(h2ot_engine* h, size_t n) {
+  n = std::min(n, h->timers.size());
+  for (size_t i = 0; i < n; i++) {
+    Timer& t = h->timers[i];
+    float ms = 0;
+    if (t.a && t.b && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) *t.acc += ms;
+    else cudaGetLastError();
+    if (t.a) h->event_pool.push_back(t.a);
+    if (t.b) h->event_pool.push_back(t.b);
+  }
+  h->timers.erase(h->timers.begin(), h->timers.begin() + (ptrdiff_t)n);
+  for (TreeState& ts : h->ts)
+    for (size_t& m : ts.dev.timer_mark) m = m > n ? m - n : 0;
+}
+
+int h2ot_tree_levels_end2(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists, float* out_leaf_pred) {
   CHECK_ENGINE(h);
   CHECK_K(h, k);
   TreeState& t = h->ts[k];
   TreeState::DevLoop& dv = t.dev;
-  if (!dv.pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_end without h2ot_tree_levels_begin");
-  dv.pending = false;
+  if (dv.n_pend <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_end without h2ot_tree_levels_begin");
+  const int slot = dv.pend_slots[0];
+  dv.pend_slots[0] = dv.pend_slots[1];
+  dv.n_pend--;
   h->steps_pending--;
   int rs = H2OT_OK;
   if (h->steps_pending == 0) rs = finish_call(h);
-  else if (cudaEventSynchronize(t.done_ev) != cudaSuccess) {
+  else if (cudaEventSynchronize(dv.ev[slot]) != cudaSuccess) {  // younger trees keep running behind this one
     set_error("cudaEventSynchronize failed waiting for a tree");
     rs = H2OT_ERR_CUDA;
-  }
+  } else fold_timers(h, dv.timer_mark[slot]);
   if (rs == H2OT_OK && h->xr_err_host && *h->xr_err_host) {
     set_error("peer-memory exchange timed out waiting for another rank");
     rs = H2OT_ERR_COMM;
   }
   if (rs != H2OT_OK) return rs;
+  const unsigned char* out_stage = dv.out_stage + (size_t)slot * dv.out_half;
   int32_t err = 0;
-  memcpy(&err, dv.out_stage + dv.o_err, sizeof(err));
+  memcpy(&err, out_stage + dv.o_err, sizeof(err));
   if (err) {
     t.level_failed = true;
     H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_levels: a histogram outgrew the level's planned layout");
   }
   const int D = dv.max_depth;
   const size_t S = ((size_t)1 << (D + 1)) - 1, n_splits = ((size_t)1 << D) - 1;
-  if (out_splits) memcpy(out_splits, dv.out_stage, n_splits * sizeof(h2ot_split));
-  if (out_exists) memcpy(out_exists, dv.out_stage + dv.o_exists, S);
-  const double* conc = reinterpret_cast<const double*>(dv.out_stage + dv.o_conc);
+  if (out_splits) memcpy(out_splits, out_stage, n_splits * sizeof(h2ot_split));
+  if (out_exists) memcpy(out_exists, out_stage + dv.o_exists, S);
+  if (out_leaf_pred) {
+    if (!dv.has_pred[slot]) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_levels_end2: leaf predictions asked for, but h2ot_tree_finish_enqueue did not run");
+    memcpy(out_leaf_pred, out_stage + dv.o_pred, S * sizeof(float));
+  }
+  const double* conc = reinterpret_cast<const double*>(out_stage + dv.o_conc);
   for (int c = 0; c < h->C; c++)
     if (conc[c] > 0) h->col_conc[c] = conc[c];
   return H2OT_OK;
 }
+int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists) {
+  return h2ot_tree_levels_end2(h, k, out_splits, out_exists, nullptr);
+}
 
 // ------------------------------------------------------------------------------------------------ end of tree
+// The rest of a tree without the host (after h2ot_tree_levels_begin): GammaPass with the leaves numbered by their static slot,
+// the leaf values, AddTreeContributions, and the download of the leaf values next to the tree's splits. Nothing synchronises.
+int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_abs_leafnode_pred) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  TreeState& t = h->ts[k];
+  TreeState::DevLoop& dv = t.dev;
+  if (dv.n_pend <= 0) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_tree_finish_enqueue without h2ot_tree_levels_begin");
+  const int fam = h->cfg.family;
+  if (fam != H2OT_FAMILY_GAUSSIAN && fam != H2OT_FAMILY_BERNOULLI && fam != H2OT_FAMILY_MULTINOMIAL)
+    H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_tree_finish_enqueue: gaussian, bernoulli and multinomial only (the others take a log on the host)");
+  const int slot = dv.pend_slots[dv.n_pend - 1];
+  const int D = dv.max_depth;
+  const int S = (1 << (D + 1)) - 1, nS = (1 << D) - 1;
+  TRY(t.d_gamma.ensure((size_t)S * 4));
+  TRY(t.d_pred.ensure((size_t)S * 2));
+  CUDA_TRY(cudaMemsetAsync(t.d_gamma.p, 0, (size_t)S * 4 * sizeof(long long), h->stream));
+  leafify_kernel<<<(nS + 127) / 128, 128, 0, h->stream>>>(t.nodes.p, dv.exists.p, nS, S);
+  h->stats.launches++;
+  GammaArgs ga{};
+  ga.n = h->n;
+  ga.n_pad = h->n_pad;
+  ga.family = fam;
+  ga.leaf_start = S;
+  ga.n_leaf_nodes = S;
+  {
+    const int64_t per = (h->n + (int64_t)h->sm_count * 8 - 1) / ((int64_t)h->sm_count * 8);
+    ga.rows_per_cta = (int32_t)std::min<int64_t>(65536, std::max<int64_t>(2048, (per + 1023) / 1024 * 1024));
+  }
+  ga.resp = h->resp;
+  ga.w = h->w;
+  ga.work = t.work;
+  ga.nids = t.nids;
+  ga.nodes = t.nodes.p;
+  ga.bitsets = t.bitsets.p;
+  ga.cols = h->d_cols.p;
+  ga.acc = t.d_gamma.p;
+  const int e_num = exponent_for(h->w_max * h->gamma_bound[0], 17);
+  const int e_den = exponent_for(h->w_max * h->gamma_bound[1], 17);
+  ga.F = t.F;
+  ga.off = h->off;
+  ga.tweedie_power = h->cfg.tweedie_power;
+  ga.s_num = std::ldexp(1.0, e_num);
+  ga.s_den = std::ldexp(1.0, e_den);
+  const int grid = (int)((h->n + ga.rows_per_cta - 1) / ga.rows_per_cta);
+  TRY(t_begin(h, &h->stats.ms_gamma));
+  gamma_kernel<<<grid, 256, 0, h->stream>>>(ga);
+  h->stats.launches++;
+  TRY(t_end(h));
+  if (h->nccl.world > 1 && h->nccl.comm)
+    TRY(nccl_check(h, h->nccl.AllReduce(t.d_gamma.p, t.d_gamma.p, (size_t)S * 4, 4, 0, h->nccl.comm, h->stream), "ncclAllReduce(gamma)"));
+  LeafValueArgs lv{};
+  lv.S = S;
+  lv.acc = t.d_gamma.p;
+  lv.e_num = e_num;
+  lv.e_den = e_den;
+  lv.rate = rate;
+  lv.multinomial = fam == H2OT_FAMILY_MULTINOMIAL ? 1 : 0;
+  lv.max_abs = max_abs_leafnode_pred;
+  lv.pred = t.d_pred.p;
+  leaf_value_kernel<<<(2 * S + 127) / 128, 128, 0, h->stream>>>(lv);
+  h->stats.launches++;
+  AddTreeArgs a{h->n, 2 * S, h->resp, h->w, t.nids, t.F, t.d_pred.p, nullptr};
+  TRY(t_begin(h, &h->stats.ms_addtree));
+  add_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  TRY(d2h(h, dv.out_stage + (size_t)slot * dv.out_half + dv.o_pred, t.d_pred.p + S, (size_t)S * sizeof(float)));
+  CUDA_TRY(cudaEventRecord(dv.ev[slot], h->stream));
+  dv.timer_mark[slot] = h->timers.size();
+  dv.has_pred[slot] = true;
+  CUDA_TRY(cudaGetLastError());
+  return H2OT_OK;
+}
+
+// ComputePredAndRes without the read-back of max |residual|: for callers that know a bound (bernoulli and multinomial residuals
+// lie in [-1, 1]) and pass it to h2ot_begin_tree / h2ot_set_gamma_bounds themselves. Nothing synchronises.
+int h2ot_compute_residuals_async(h2ot_engine* h) {
+  CHECK_ENGINE(h);
+  if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
+  CUDA_TRY(cudaMemsetAsync(h->d_absmax.p, 0, (h->K + 2) * sizeof(unsigned int), h->stream));
+  ResidArgs a{h->n, h->K, h->cfg.nclass, h->cfg.family, h->resp, h->w, h->off, h->d_Fp.p, h->d_workp.p, h->d_absmax.p, h->cfg.tweedie_power};
+  TRY(t_begin(h, &h->stats.ms_residuals));
+  residuals_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
+  h->stats.launches++;
+  TRY(t_end(h));
+  CUDA_TRY(cudaGetLastError());
+  return H2OT_OK;
+}
+
 int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,
                   int64_t bitset_bytes) {
   CHECK_ENGINE(h);

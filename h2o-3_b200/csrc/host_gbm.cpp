@@ -22,6 +22,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <memory>
 #include <string>
 #include <vector>
@@ -346,6 +347,12 @@ struct h2ot_gbm {
     double t0 = 0, t_descs_done = 0;
   };
   std::vector<LevelScratch> scr;
+  // iterations whose trees are on the device (built, fitted, added to the predictions) but not yet mirrored on the host
+  struct PendingIter {
+    std::vector<std::unique_ptr<Tree>> kt;
+    std::vector<int> ncol_active;
+  };
+  std::deque<PendingIter> pending;
 };
 
 namespace {
@@ -507,12 +514,10 @@ void to_device_node_static(const std::vector<Node>& ns, int nid, int first_leaf,
 
 // All levels of the K class-trees of one iteration on the device, then the host's mirror of each tree: nodes in H2O's creation
 // order (level by level, leaf order, left child first -- what build_layer_k's loop over the leaves produces), splits, varimp.
-int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) {
+int enqueue_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt, std::vector<int>& ncol_active) {
   const int K = g->K, C = g->ncols, D = g->p.max_depth;
-  const size_t S = ((size_t)1 << (D + 1)) - 1, nS = ((size_t)1 << D) - 1;
-  const double t0 = now_s();
   std::vector<h2ot_hist_desc> descs((size_t)C);
-  std::vector<int> ncol_active((size_t)K, 0);
+  ncol_active.assign((size_t)K, 0);
   for (int k = 0; k < K; k++) {
     const Node& root = kt[k]->ns[0];
     for (int c = 0; c < C; c++) {
@@ -521,13 +526,22 @@ int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) 
     }
     GTRY(h2ot_tree_levels_begin(g->eng, k, D, descs.data(), g->p.min_rows, g->p.min_split_improvement, g->p.nbins, g->p.nbins_cats));
   }
+  return H2OT_OK;
+}
+
+// Waits for the K trees (oldest in flight per class) and mirrors them. slot_pred (optional): [K][S] leaf values by static child slot.
+int mirror_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt, const std::vector<int>& ncol_active,
+                            std::vector<float>* slot_pred) {
+  const int K = g->K, D = g->p.max_depth;
+  const size_t S = ((size_t)1 << (D + 1)) - 1, nS = ((size_t)1 << D) - 1;
   std::vector<h2ot_split> splits(nS);
   std::vector<uint8_t> exists(S);
+  if (slot_pred) slot_pred->assign((size_t)K * S, 0.f);
   // variable importance is a float sum whose order the reference fixes: per level, class-tree by class-tree, leaf by leaf
   // (ScoreBuildOneTree.onCompletion of the K trees of one buildLayer, T/SharedTree.java:563-607, 697-700)
   std::vector<std::vector<std::pair<int, float>>> vi((size_t)D * K);
   for (int k = 0; k < K; k++) {
-    GTRY(h2ot_tree_levels_end(g->eng, k, splits.data(), exists.data()));
+    GTRY(h2ot_tree_levels_end2(g->eng, k, splits.data(), exists.data(), slot_pred ? slot_pred->data() + (size_t)k * S : nullptr));
     Tree& t = *kt[k];
     t.ns[0].sid = 0;
     std::vector<int> cur{0}, next;
@@ -575,8 +589,45 @@ int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) 
   }
   for (const auto& lvl : vi)
     for (const auto& e : lvl) g->varimp[e.first] += e.second;
+  return H2OT_OK;
+}
+
+int build_levels_on_device(h2ot_gbm* g, std::vector<std::unique_ptr<Tree>>& kt) {
+  const double t0 = now_s();
+  std::vector<int> ncol_active;
+  GTRY(enqueue_levels_on_device(g, kt, ncol_active));
+  GTRY(mirror_levels_on_device(g, kt, ncol_active, nullptr));
   g->timing.level_s += now_s() - t0;
   return H2OT_OK;
+}
+
+// leaf insertion (T/gbm/GBM.java:655-679); returns the id of the first LeafNode. slot_pred: the leaves' values by static child
+// slot when the device fitted them (pipelined trees), else nullptr
+int insert_leaves(Tree& t, const float* slot_pred) {
+  const int leaf = t.len();
+  for (int nid = 0; nid < leaf; nid++) {
+    if (t.ns[nid].kind != 1) continue;
+    if (!t.ns[nid].has_split) {
+      if (nid == 0) {  // the root never split: it becomes a LeafNode in place
+        Node n;
+        n.kind = 2;
+        n.pid = kNoParent;
+        n.nid = 0;
+        t.ns[0] = n;
+        t.leaves++;
+      }
+      continue;
+    }
+    for (int i = 0; i < 2; i++) {
+      const int cn = t.ns[nid].nids[i];
+      if (cn == kUndecidedChild || t.ns[cn].kind == 0 || (t.ns[cn].kind == 1 && !t.ns[cn].has_split)) {
+        const int ln = t.new_leaf(nid);  // (may move t.ns)
+        t.ns[nid].nids[i] = ln;
+        if (slot_pred) t.ns[ln].pred = slot_pred[2 * t.ns[nid].sid + 1 + i];
+      }
+    }
+  }
+  return leaf;
 }
 
 // One ScoreBuildHistogram2 pass + ScoreBuildOneTree.onCompletion for class-tree k (T/SharedTree.java:661-710).
@@ -770,13 +821,91 @@ double noise_factor(const h2ot_gbm* g, int k, int nid) {
   return 1.0 + r.next_gaussian_after_seed() * g->pred_noise_bandwidth;
 }
 
+// ---- trees in a pipeline: the device runs an iteration start to finish (residuals, levels, leaf insertion, GammaPass, leaf values,
+// AddTreeContributions) with nothing waiting on the host, and the host mirrors iteration t while the device builds t + 1.
+// What lets the host step aside: static node ids (the device loop), residual bounds known in advance (|y - p| <= 1), leaf values
+// that need no transcendental (gaussian's bound is data dependent, so it keeps the synchronous path; poisson / gamma / tweedie take
+// a log), no per-node random numbers (pred_noise_bandwidth seeds by H2O node id). H2OT_PIPELINE=0 switches it off; the trees are
+// the same either way.
+bool use_pipeline(const h2ot_gbm* g) {
+  const char* e = getenv("H2OT_PIPELINE");
+  const bool off = e != nullptr && atoi(e) == 0;
+  return !off && use_device_loop(g) && (g->p.family == H2OT_FAMILY_BERNOULLI || g->p.family == H2OT_FAMILY_MULTINOMIAL) &&
+         g->pred_noise_bandwidth == 0;
+}
+
+int mirror_oldest_iteration(h2ot_gbm* g) {
+  if (g->pending.empty()) return H2OT_OK;
+  const double t0 = now_s();
+  h2ot_gbm::PendingIter it = std::move(g->pending.front());
+  g->pending.pop_front();
+  const int K = g->K;
+  const size_t S = ((size_t)1 << (g->p.max_depth + 1)) - 1;
+  std::vector<float> slot_pred;
+  GTRY(mirror_levels_on_device(g, it.kt, it.ncol_active, &slot_pred));
+  std::vector<FinishedTree> outs(K);
+  for (int k = 0; k < K; k++) {
+    Tree& t = *it.kt[k];
+    outs[k].leaves_start = insert_leaves(t, slot_pred.data() + (size_t)k * S);
+    outs[k].nodes = std::move(t.ns);
+    for (Node& n : outs[k].nodes) n.hs.clear();
+  }
+  g->trees.push_back(std::move(outs));
+  g->timing.level_s += now_s() - t0;
+  return H2OT_OK;
+}
+
+int flush_pending(h2ot_gbm* g) {
+  while (!g->pending.empty()) GTRY(mirror_oldest_iteration(g));
+  return H2OT_OK;
+}
+
+int build_next_k_trees_pipelined(h2ot_gbm* g) {
+  const int K = g->K;
+  const double t0 = now_s();
+  GTRY(h2ot_compute_residuals_async(g->eng));
+  const double gb[2] = {1.0, 0.25};  // |w z| / w <= 1, p (1 - p) <= 1/4
+  GTRY(h2ot_set_gamma_bounds(g->eng, gb));
+  h2ot_gbm::PendingIter it;
+  it.kt.resize((size_t)K);
+  const int adj_nbins = std::max(g->p.nbins_top_level, g->p.nbins);
+  const int64_t rseed = g->rand.next_long();
+  for (int k = 0; k < K; k++) {
+    it.kt[k] = std::make_unique<Tree>(g->ncols, g->mtry, g->mtry_per_tree, rseed, g->p.col_sample_rate_change_per_level);
+    it.kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed, false));
+    GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, 1.0));
+  }
+  GTRY(enqueue_levels_on_device(g, it.kt, it.ncol_active));
+  const double m1class = (g->nclass > 1 && g->p.family == H2OT_FAMILY_MULTINOMIAL) ? (double)(g->nclass - 1) / g->nclass : 1.0;
+  const double eff_lr = g->p.learn_rate * std::pow(g->p.learn_rate_annealing, (double)(g->ntrees_built - 1));
+  for (int k = 0; k < K; k++) GTRY(h2ot_tree_finish_enqueue(g->eng, k, eff_lr * m1class, g->p.max_abs_leafnode_pred));
+  g->pending.push_back(std::move(it));
+  g->ntrees_built++;
+  const double t1 = now_s();
+  g->timing.level_s += t1 - t0;
+  while (g->pending.size() > 1) GTRY(mirror_oldest_iteration(g));
+  static const bool trace = getenv("H2OT_TRACE_PIPE") != nullptr;
+  if (trace) fprintf(stderr, "[h2ot pipe] tree %d: enqueue %.3f ms, wait + mirror of the previous %.3f ms\n", g->ntrees_built, 1e3 * (t1 - t0), 1e3 * (now_s() - t1));
+  return H2OT_OK;
+}
+
 // GBM.buildNextKTrees (T/gbm/GBM.java:464-591)
 int build_next_k_trees(h2ot_gbm* g) {
+  if (use_pipeline(g)) return build_next_k_trees_pipelined(g);
+  GTRY(flush_pending(g));
   const int K = g->K;
   std::vector<double> absmax(K + 2, 0.0);
   GTRY(h2ot_compute_residuals(g->eng, absmax.data()));
-  GTRY(h2ot_get_gamma_bounds(g->eng, absmax.data() + K));
-  GTRY(allreduce(g, absmax.data(), K + 2, 1));
+  if (g->p.family == H2OT_FAMILY_BERNOULLI || g->p.family == H2OT_FAMILY_MULTINOMIAL) {
+    // bounds known in advance (|y - p| <= 1, p (1 - p) <= 1/4): the same fixed-point scale as the pipelined build, hence the
+    // same bits, and no all-reduce of the observed maxima
+    for (int k = 0; k < K; k++) absmax[k] = 1.0;
+    absmax[K] = 1.0;
+    absmax[K + 1] = 0.25;
+  } else {
+    GTRY(h2ot_get_gamma_bounds(g->eng, absmax.data() + K));
+    GTRY(allreduce(g, absmax.data(), K + 2, 1));
+  }
   GTRY(h2ot_set_gamma_bounds(g->eng, absmax.data() + K));
   std::vector<std::unique_ptr<Tree>> kt(K);
   std::vector<int> leaves(K, 0);
@@ -812,30 +941,7 @@ int build_next_k_trees(h2ot_gbm* g) {
     if (!any) break;
   }
   // leaf insertion (:655-679)
-  for (int k = 0; k < K; k++) {
-    Tree& t = *kt[k];
-    const int leaf = t.len();
-    leaves[k] = leaf;
-    for (int nid = 0; nid < leaf; nid++) {
-      if (t.ns[nid].kind != 1) continue;
-      if (!t.ns[nid].has_split) {
-        if (nid == 0) {  // the root never split: it becomes a LeafNode in place
-          Node n;
-          n.kind = 2;
-          n.pid = kNoParent;
-          n.nid = 0;
-          t.ns[0] = n;
-          t.leaves++;
-        }
-        continue;
-      }
-      for (int i = 0; i < 2; i++) {
-        const int cn = t.ns[nid].nids[i];
-        if (cn == kUndecidedChild || t.ns[cn].kind == 0 || (t.ns[cn].kind == 1 && !t.ns[cn].has_split))
-          t.ns[nid].nids[i] = t.new_leaf(nid);
-      }
-    }
-  }
+  for (int k = 0; k < K; k++) leaves[k] = insert_leaves(*kt[k], nullptr);
   // GammaPass + fitBestConstants (:1286-1407, 813-847)
   const double m1class = (g->nclass > 1 && g->p.family == H2OT_FAMILY_MULTINOMIAL) ? (double)(g->nclass - 1) / g->nclass : 1.0;
   const double eff_lr = g->p.learn_rate * std::pow(g->p.learn_rate_annealing, (double)(g->ntrees_built - 1));
@@ -1047,6 +1153,7 @@ int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int
 
 int h2ot_gbm_destroy(h2ot_gbm* g) {
   if (!g) return H2OT_OK;
+  flush_pending(g);  // (drains the trees in flight; an error here has nobody left to hear it)
   h2ot_destroy(g->eng);
   delete g;
   return H2OT_OK;
@@ -1226,17 +1333,33 @@ int h2ot_gbm_train(h2ot_gbm* g, int32_t n_iterations) {
 }
 
 int h2ot_gbm_capture_levels(h2ot_gbm* g, int32_t on) {
+  if (g) GTRY(flush_pending(g));
   if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
   g->capture = on != 0;
   return H2OT_OK;
 }
 
 double h2ot_gbm_init_f(h2ot_gbm* g) { return g ? g->init_f : NAN; }
-int32_t h2ot_gbm_ntrees(h2ot_gbm* g) { return g ? (int32_t)g->trees.size() : 0; }
-int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k) { return (int32_t)g->trees[tree][k].nodes.size(); }
-int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k) { return g->trees[tree][k].leaves_start; }
+int32_t h2ot_gbm_ntrees(h2ot_gbm* g) {
+  if (g) flush_pending(g);
+  return g ? (int32_t)g->trees.size() : 0;
+}
+// Waits for the trees still in flight on the device and mirrors them (every accessor does so by itself).
+int h2ot_gbm_flush(h2ot_gbm* g) {
+  if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
+  return flush_pending(g);
+}
+int32_t h2ot_gbm_tree_len(h2ot_gbm* g, int32_t tree, int32_t k) {
+  flush_pending(g);
+  return (int32_t)g->trees[tree][k].nodes.size();
+}
+int32_t h2ot_gbm_tree_leaves_start(h2ot_gbm* g, int32_t tree, int32_t k) {
+  flush_pending(g);
+  return g->trees[tree][k].leaves_start;
+}
 
 int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out || tree < 0 || tree >= (int)g->trees.size() || k < 0 || k >= g->K) GFAIL(H2OT_ERR_INVALID, "bad tree index");
   const std::vector<Node>& ns = g->trees[tree][k].nodes;
   for (size_t i = 0; i < ns.size(); i++) {
@@ -1272,6 +1395,7 @@ int h2ot_gbm_tree_nodes(h2ot_gbm* g, int32_t tree, int32_t k, h2ot_tree_node* ou
 // Two-call protocol: with bits_cap / aux_cap too small nothing is written and the needed lengths come back.
 int h2ot_gbm_tree_compress(h2ot_gbm* g, int32_t tree, int32_t k, uint8_t* bits, int64_t bits_cap, int64_t* bits_len, uint8_t* aux,
                            int64_t aux_cap, int64_t* aux_len) {
+  if (g) GTRY(flush_pending(g));
   if (!g || tree < 0 || tree >= (int)g->trees.size() || k < 0 || k >= g->K) GFAIL(H2OT_ERR_INVALID, "bad tree index");
   const std::vector<Node>& ns = g->trees[tree][k].nodes;
   const int n = (int)ns.size();
@@ -1374,10 +1498,12 @@ int h2ot_gbm_tree_compress(h2ot_gbm* g, int32_t tree, int32_t k, uint8_t* bits, 
 }
 
 int h2ot_gbm_predictions(h2ot_gbm* g, int32_t k, double* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_predictions(g->eng, k, out);
 }
 int h2ot_gbm_predict(h2ot_gbm* g, int64_t nrows, const double* const* columns, double* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !columns || !out || nrows <= 0) GFAIL(H2OT_ERR_INVALID, "bad argument");
   if (!g->inited) GFAIL(H2OT_ERR_INVALID, "model not initialised");
   h2ot_config cfg{};
@@ -1431,10 +1557,12 @@ int h2ot_gbm_predict(h2ot_gbm* g, int64_t nrows, const double* const* columns, d
 }
 
 int h2ot_gbm_oobt(h2ot_gbm* g, double* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   return h2ot_get_oobt(g->eng, out);
 }
 int h2ot_gbm_score(h2ot_gbm* g, double* out_mse, double* out_logloss) {
+  if (g) GTRY(flush_pending(g));
   if (!g) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (g->p.algo != H2OT_ALGO_GBM) GFAIL(H2OT_ERR_UNSUPPORTED, "device scoring covers GBM only");
   h2ot_metrics m{};
@@ -1535,6 +1663,7 @@ struct AucFold {
 }  // namespace
 
 int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_ths, double* out_tps, double* out_fps, int64_t* out_chunk_rows) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out_auc) GFAIL(H2OT_ERR_INVALID, "null argument");
   if (g->p.algo != H2OT_ALGO_GBM || g->p.family != H2OT_FAMILY_BERNOULLI) GFAIL(H2OT_ERR_UNSUPPORTED, "AUC2 covers bernoulli GBM");
   const int max_chunks = 4096;
@@ -1588,12 +1717,14 @@ int h2ot_gbm_auc(h2ot_gbm* g, double* out_auc, int32_t* out_nbins, double* out_t
   return H2OT_OK;
 }
 int h2ot_gbm_set_pred_noise_bandwidth(h2ot_gbm* g, double bandwidth) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !(bandwidth >= 0)) GFAIL(H2OT_ERR_INVALID, "pred_noise_bandwidth must be >= 0");  // T/gbm/GBM.java:189-190
   if (g->p.algo != H2OT_ALGO_GBM) GFAIL(H2OT_ERR_UNSUPPORTED, "pred_noise_bandwidth is a GBM parameter");
   g->pred_noise_bandwidth = bandwidth;
   return H2OT_OK;
 }
 int h2ot_gbm_set_sample_rate_per_class(h2ot_gbm* g, const double* rates, int32_t n) {
+  if (g) GTRY(flush_pending(g));
   if (!g || n < 0 || (n > 0 && !rates)) GFAIL(H2OT_ERR_INVALID, "bad rates");
   if (n > 0 && g->nclass < 2) GFAIL(H2OT_ERR_INVALID, "sample_rate_per_class needs a categorical response");
   if (n > 0 && n != g->nclass) GFAIL(H2OT_ERR_INVALID, "sample_rate_per_class needs one rate per response class");
@@ -1603,16 +1734,21 @@ int h2ot_gbm_set_sample_rate_per_class(h2ot_gbm* g, const double* rates, int32_t
   return h2ot_set_sample_rate_per_class(g->eng, rates, n);
 }
 int h2ot_gbm_varimp(h2ot_gbm* g, float* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   std::copy(g->varimp.begin(), g->varimp.end(), out);
   return H2OT_OK;
 }
 int h2ot_gbm_timing_get(h2ot_gbm* g, h2ot_gbm_timing* out) {
+  if (g) GTRY(flush_pending(g));
   if (!g || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
   *out = g->timing;
   return H2OT_OK;
 }
-h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g) { return g ? g->eng : nullptr; }
+h2ot_engine* h2ot_gbm_engine(h2ot_gbm* g) {
+  if (g) flush_pending(g);  // (the caller is about to use the engine directly)
+  return g ? g->eng : nullptr;
+}
 
 // ---- host-logic probes (no device needed): let the CPU test-suite compare this file's DHistogram / DTree / PCG bookkeeping
 // with an independent CPU restatement of the reference

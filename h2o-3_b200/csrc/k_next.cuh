@@ -11,6 +11,7 @@
 #pragma once
 #include "common.cuh"
 #include "k_level.cuh"
+#include "k_rows.cuh"
 
 namespace h2ot {
 
@@ -196,6 +197,53 @@ __global__ void __launch_bounds__(128) next_level_kernel(NextArgs a) {
     if (split && sp_s.equal >= 2)
       for (int i = threadIdx.x; i < sp_s.bs_nbytes; i += blockDim.x) a.bitsets[(size_t)pid * H2OT_MAX_BITSET_BYTES + i] = sp_s.bs[i];
   }
+}
+
+// After the last level: every child pointer that does not lead to a split node becomes a LeafNode (DTree leaf insertion,
+// T/gbm/GBM.java:655-679), numbered by its static slot: leaf id = S + slot, S = 2^(D+1) - 1. A child is a leaf when it never existed
+// or found no split (-1, see above) or sits on level D, which is never searched (slot >= nS = 2^D - 1).
+__global__ void __launch_bounds__(128) leafify_kernel(h2ot_decided_node* nodes, const uint8_t* exists, int nS, int S) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= nS || !exists[p]) return;
+  h2ot_decided_node dn = nodes[p];
+  if (dn.col < 0) return;
+#pragma unroll
+  for (int w = 0; w < 2; w++)
+    if (dn.child[w] < 0 || dn.child[w] >= nS) nodes[p].child[w] = S + 2 * p + 1 + w;
+}
+
+// GammaPass's sums to leaf values: fitBestConstants for gaussian / bernoulli / multinomial (T/gbm/GBM.java:813-847), the same
+// double arithmetic as host_gbm.cpp. pred[0 .. S) = 0 (rows that stayed on a node that is no leaf add nothing), pred[S + slot] = value.
+struct LeafValueArgs {
+  int32_t S;
+  const long long* acc;  // [S][4]: num.hi, num.lo, den.hi, den.lo (gamma_kernel's split fixed point)
+  int32_t e_num, e_den;
+  double rate;           // learn_rate (annealed) x (K - 1) / K for multinomial
+  int32_t multinomial;
+  double max_abs;
+  float* pred;           // [2 S]
+};
+__global__ void __launch_bounds__(128) leaf_value_kernel(LeafValueArgs a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * a.S) return;
+  if (i < a.S) {
+    a.pred[i] = 0.f;
+    return;
+  }
+  const long long* q = a.acc + (size_t)(i - a.S) * 4;
+  const double num = __dadd_rn(ldexp((double)q[0], kGammaSplitBits - a.e_num), ldexp((double)q[1], -a.e_num));
+  const double den = __dadd_rn(ldexp((double)q[2], kGammaSplitBits - a.e_den), ldexp((double)q[3], -a.e_den));
+  const double gamma = den == 0 ? 0.0 : __ddiv_rn(num, den);
+  double gf = __dmul_rn(a.rate, gamma);
+  if (a.multinomial) {
+    if (gf > 1e4) gf = (double)1e4f;
+    else if (gf < -1e4) gf = (double)-1e4f;
+  }
+  if (isnan(gf)) gf = 0;
+  else if (isinf(gf)) gf = (gf > 0 ? 1.0 : -1.0) * (double)1e4f;
+  if (gf > a.max_abs) gf = a.max_abs;
+  if (gf < -a.max_abs) gf = -a.max_abs;
+  a.pred[i] = (float)gf;
 }
 
 }  // namespace h2ot

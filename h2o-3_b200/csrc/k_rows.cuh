@@ -310,7 +310,10 @@ __device__ __forceinline__ void gamma_row(const GammaArgs& a, int64_t row, int n
   if (oob) nid = -nid + H2OT_OUT_OF_BAG;
   if (nid < 0) return;
   h2ot_decided_node dn = a.nodes[nid];
-  if (dn.col < 0) dn = a.nodes[dn.pid];
+  if (dn.col < 0) {
+    if (dn.pid < 0) return;  // the root found no split: the tree is a stump, no leaf to fit
+    dn = a.nodes[dn.pid];
+  }
   const int leafnid = child_node_id(dn, a.cols, a.bitsets, row);
   nid_out = leafnid;
   if (oob) return;

@@ -292,6 +292,21 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
                            double min_split_improvement, int32_t nbins, int32_t nbins_cats);
 int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists);
 
+/* ---- trees in a pipeline: no host synchronisation between the trees of a model. After h2ot_tree_levels_begin,
+ * h2ot_tree_finish_enqueue queues the rest of the tree behind its levels: the leaf insertion (every child pointer that does not lead
+ * to a split node becomes a LeafNode, T/gbm/GBM.java:655-679) with the leaves numbered by their static slot (leaf id =
+ * 2^(max_depth+1) - 1 + slot of the child), GammaPass (:1286-1407; per-leaf sums all-reduced over the communicator), the leaf values
+ * of fitBestConstants for gaussian / bernoulli / multinomial (:813-847: rate x num / den with rate = annealed learn_rate x (K-1)/K,
+ * the 1e4 clamp for multinomial, NaN -> 0, max_abs_leafnode_pred) and AddTreeContributions (:1410-1470). Then the next tree's
+ * h2ot_compute_residuals_async / h2ot_begin_tree / h2ot_tree_levels_begin may be enqueued before this tree is ended: up to TWO trees
+ * per class-tree may be in flight, _end returns the oldest. h2ot_tree_levels_end2 also returns the leaf values,
+ * out_leaf_pred[2^(max_depth+1) - 1] indexed by the child's slot (0 where the slot is no leaf).
+ * h2ot_compute_residuals_async is h2ot_compute_residuals without the read-back of max |residual|: the caller passes a bound it
+ * knows to h2ot_begin_tree (|y - p| <= 1 for bernoulli and multinomial) and to h2ot_set_gamma_bounds. */
+int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_abs_leafnode_pred);
+int h2ot_tree_levels_end2(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists, float* out_leaf_pred);
+int h2ot_compute_residuals_async(h2ot_engine* h);
+
 /* ---- end of tree */
 /* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */
 int h2ot_set_tree(h2ot_engine* h, int32_t k, int32_t n_nodes, const h2ot_decided_node* nodes, const uint8_t* bitset_pool,

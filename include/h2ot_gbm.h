@@ -69,8 +69,13 @@ int h2ot_gbm_set_offset(h2ot_gbm* g, const double* o);
 int h2ot_gbm_comm_init(h2ot_gbm* g, int32_t world_size, int32_t rank, const uint8_t id[H2OT_COMM_ID_BYTES]);
 /* Frame finalisation, rollups, init_f, MarkDecidedRows (GBM.initializeModelSpecifics, T/gbm/GBM.java:254-312) */
 int h2ot_gbm_init(h2ot_gbm* g);
-/* Builds the next n iterations (GBM.buildNextKTrees, T/gbm/GBM.java:464-591) */
+/* Builds the next n iterations (GBM.buildNextKTrees, T/gbm/GBM.java:464-591).
+ * bernoulli / multinomial GBMs whose levels run on the device (h2ot.h: h2ot_tree_levels_*) are built in a PIPELINE: the call may
+ * return while the last iteration is still on the device (its trees built, fitted and added to the predictions there) and its
+ * host mirror not yet made; every accessor below waits for it by itself, h2ot_gbm_flush does so explicitly (e.g. to stop a
+ * clock). H2OT_PIPELINE=0 in the environment builds the same trees one synchronisation at a time. */
 int h2ot_gbm_train(h2ot_gbm* g, int32_t n_iterations);
+int h2ot_gbm_flush(h2ot_gbm* g);
 int h2ot_gbm_capture_levels(h2ot_gbm* g, int32_t on); /* histogram monitor analogue (T/SharedTree.java:1253-1289) */
 
 double h2ot_gbm_init_f(h2ot_gbm* g);

@@ -460,18 +460,22 @@ def test_device_level_loop_grows_the_same_trees_as_the_host_loop(case, monkeypat
     else:
         kw.update(max_depth=8, min_rows=400.0, ntrees=3)  # many leaves stop early: empty slots, cut-off children
     sig = []
-    for loop in ("0", "1"):
+    # host loop; device loop with one synchronisation per tree; device loop with the trees in a pipeline (h2ot_tree_finish_enqueue:
+    # leaf insertion, GammaPass, leaf values and AddTreeContributions without the host -- bernoulli / multinomial only, the others
+    # fall back to the second mode by themselves)
+    for loop, pipe in (("0", "0"), ("1", "0"), ("1", "1")):
         monkeypatch.setenv("H2OT_DEVICE_LOOP", loop)
+        monkeypatch.setenv("H2OT_PIPELINE", pipe)
         gm, om = _run_both(X, y, cats, w=w, off=off, capture=False, **kw)
-        eng_launches = gm.engine().stats().launches
         nodes = [[bytes(gm.tree(t, k)[0]) for k in range(K)] for t in range(gm.ntrees)]
         sig.append((nodes, [gm.predictions(k).tobytes() for k in range(K)], gm.varimp().tobytes(), [gm.tree(t, 0)[1] for t in range(gm.ntrees)]))
-        oms = om
         gm.close()
-    assert sig[0][3] == sig[1][3]
-    assert sig[0][0] == sig[1][0], "trees differ between the host loop and the device loop"
-    assert sig[0][1] == sig[1][1] and sig[0][2] == sig[1][2]
+    for other in (1, 2):
+        assert sig[0][3] == sig[other][3]
+        assert sig[0][0] == sig[other][0], "trees differ between the host loop and the device loop (mode %d)" % other
+        assert sig[0][1] == sig[other][1] and sig[0][2] == sig[other][2]
     monkeypatch.setenv("H2OT_DEVICE_LOOP", "1")
+    monkeypatch.setenv("H2OT_PIPELINE", "1")
     gm, om = _run_both(X, y, cats, w=w, off=off, capture=False, **kw)
     h2ot_lib.compare_models(gm, om, K=K, check_levels=False)
     gm.close()
