@@ -218,6 +218,7 @@ struct h2ot_engine {
   std::vector<Timer> timers;
   std::vector<cudaEvent_t> event_pool;
   bool defer_sync = false;
+  bool in_tree_loop = false;  // inside h2ot_tree_levels_begin: per-level housekeeping copies are done once per tree
   bool lazy_sync = false;          // h2ot_set_lazy_sync: calls that return nothing to the host do not wait for the stream
   std::vector<double> rate_per_class;  // Sample's _rate_per_class (empty: null)
   DBuf<double> d_rate_per_class;
@@ -229,6 +230,8 @@ struct h2ot_engine {
   Nccl nccl;
   // peer-memory exchange (k_xreduce.cuh): [in: xr_cap words][out: xr_cap words][flags: kXrMaxWorld words]
   bool xr_enabled = false, xr_failed = false, xr_coop = true;
+  bool xr_ll = true;  // the push exchange with flagged lines (xr_ll_kernel); H2OT_XREDUCE=3 / 2 select the older pull versions
+  unsigned long long xr_ll_epoch = 0;
   unsigned long long* xr_buf = nullptr;
   size_t xr_cap = 0;
   XrPeers xr_peers{};
@@ -1084,8 +1087,9 @@ int xr_ensure(h2ot_engine* h, size_t words) {
   }
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   xr_release(h);  // collective: every rank grows at the same call, and nobody frees a buffer a peer still reads or maps
-  const size_t cap = std::max<size_t>(words * 2, 1 << 16);
-  const size_t total = (2 * cap + kXrMaxWorld) * sizeof(unsigned long long);
+  // [in: cap][out: cap][flags: 64][reduce-scatter lines: 2 parities x cap lines x 2 words][all-gather lines: the same]
+  const size_t cap = std::max<size_t>((words * 2 + 63) & ~(size_t)63, 1 << 16);
+  const size_t total = (10 * cap + 64) * sizeof(unsigned long long);
   CUDA_TRY(cudaMalloc(&h->xr_buf, total));
   CUDA_TRY(cudaMemset(h->xr_buf, 0, total));
   if (!h->xr_err) {
@@ -1095,6 +1099,7 @@ int xr_ensure(h2ot_engine* h, size_t words) {
     *h->xr_err_host = 0;
   }
   h->xr_epoch = 0;
+  h->xr_ll_epoch = 0;
   cudaIpcMemHandle_t mine;
   CUDA_TRY(cudaIpcGetMemHandle(&mine, h->xr_buf));
   DBuf<unsigned char> d_handles;
@@ -1147,7 +1152,14 @@ int xr_allreduce(h2ot_engine* h, long long n_sums, long long n) {
   const long long slice = (n + W - 1) / W;
   const int g_rs = (int)std::max<long long>(1, std::min<long long>((slice + 255) / 256, (long long)h->sm_count * 4));
   const int g_ag = (int)std::max<long long>(1, std::min<long long>((n + 255) / 256, (long long)h->sm_count * 4));
-  if (h->xr_coop) {  // one cooperative launch; the grid must be co-resident: at most 2 CTAs of 256 threads per SM here
+  if (h->xr_ll && W >= 2 && n >= W && (size_t)n + (size_t)W <= h->xr_cap) {  // pushed lines with the epoch inside, no barriers
+    const uint32_t ep = (uint32_t)(++h->xr_ll_epoch);
+    static const int per = getenv("H2OT_XR_PER") ? atoi(getenv("H2OT_XR_PER")) : 512;
+    const int grid = (int)std::max<long long>(1, std::min<long long>((n + per - 1) / per, (long long)h->sm_count * 2));
+    xr_ll_kernel<<<grid, 256, 0, h->stream>>>(h->xr_peers, W, R, 2 * h->xr_cap + 64, 6 * h->xr_cap + 64, 2 * h->xr_cap, n_sums, n, ep, timeout,
+                                              h->xr_err);
+    h->stats.launches += 1;
+  } else if (h->xr_coop) {  // one cooperative launch; the grid must be co-resident: at most 2 CTAs of 256 threads per SM here
     size_t cap = h->xr_cap, fo = flag_off;
     unsigned long long ep = h->xr_epoch + 1, to = timeout;
     h->xr_epoch += 2;
@@ -1163,7 +1175,8 @@ int xr_allreduce(h2ot_engine* h, long long n_sums, long long n) {
     xr_all_gather_kernel<<<g_ag, 256, 0, h->stream>>>(h->xr_peers, W, R, h->xr_cap, n);
     h->stats.launches += 4;
   }
-  CUDA_TRY(cudaMemcpyAsync(h->xr_err_host, h->xr_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  // (levels enqueued back to back fetch the error word once per tree, h2ot_tree_levels_begin)
+  if (!h->in_tree_loop) CUDA_TRY(cudaMemcpyAsync(h->xr_err_host, h->xr_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   CUDA_TRY(cudaGetLastError());
   return H2OT_OK;
 }
@@ -2169,6 +2182,7 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   dv.min_rows = min_rows;
   dv.active = true;
   h->defer_sync = true;
+  h->in_tree_loop = true;
   int rc = H2OT_OK;
   std::vector<h2ot_hist_desc> tmpl;
   for (int d = 0; d < D && rc == H2OT_OK; d++) {
@@ -2244,6 +2258,11 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   if (rc == H2OT_OK) rc = d2h(h, out_stage, dv.tree_splits.p, n_splits * sizeof(h2ot_split));
   if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_exists, dv.exists.p, S);
   if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_err, dv.err.p, sizeof(int32_t));
+  if (rc == H2OT_OK && h->xr_err && h->xr_err_host && h->nccl.world > 1 &&
+      cudaMemcpyAsync(h->xr_err_host, h->xr_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
+    set_error("cudaMemcpyAsync failed");
+    rc = H2OT_ERR_CUDA;
+  }
   if (rc == H2OT_OK && !dv.ev[slot] && cudaEventCreateWithFlags(&dv.ev[slot], cudaEventDisableTiming) != cudaSuccess) {
     set_error("cudaEventCreate failed");
     rc = H2OT_ERR_CUDA;
@@ -2254,6 +2273,7 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   }
   dv.active = false;
   h->defer_sync = false;
+  h->in_tree_loop = false;
   if (rc != H2OT_OK) {
     if (h->steps_pending == 0) finish_call(h);
     return rc;
@@ -2674,6 +2694,7 @@ int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8
     const char* e = getenv("H2OT_XREDUCE");
     h->xr_enabled = !(e && e[0] == '0');
     h->xr_coop = !(e && e[0] == '2');  // 2: the four-kernel sequence instead of the cooperative launch
+    h->xr_ll = !(e && (e[0] == '2' || e[0] == '3'));  // 3: the cooperative pull exchange (barriers) instead of the pushed lines
   }
   if (it != g_comms.end()) {
     h->nccl.comm = it->second;

@@ -98,23 +98,30 @@ __device__ __forceinline__ void xr_signal_wait(const XrPeers& peers, int world, 
   }
 }
 
+// (Remote loads take microseconds: every loop below issues all the loads of an iteration before it uses any of them -- one round
+// trip per iteration instead of one per peer.)
 __global__ void __launch_bounds__(256) xr_fused_kernel(XrPeers peers, int world, int rank, size_t cap, size_t flag_off, long long n_sums,
                                                        long long n, unsigned long long epoch, unsigned long long timeout_cycles, int* err) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  __shared__ long long s_lo[kXrMaxWorld + 1];
+  if (threadIdx.x <= world) s_lo[threadIdx.x] = n * threadIdx.x / world;
   if (blockIdx.x == 0) xr_signal_wait(peers, world, rank, flag_off, epoch, timeout_cycles, err);
   grid.sync();
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
   {
-    const long long lo = n * rank / world, hi = n * (rank + 1) / world;
+    const long long lo = s_lo[rank], hi = s_lo[rank + 1];
     unsigned long long* out = peers.buf[rank] + cap;
-    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
+    for (long long i = lo + tid; i < hi; i += stride) {
+      unsigned long long v[kXrMaxWorld];
+#pragma unroll
+      for (int p = 0; p < kXrMaxWorld; p++) v[p] = p < world ? __ldcv(peers.buf[p] + i) : 0ULL;
       unsigned long long acc = 0ULL;
       if (i < n_sums) {
-        for (int p = 0; p < world; p++) acc += __ldcv(peers.buf[p] + i);
+#pragma unroll
+        for (int p = 0; p < kXrMaxWorld; p++) acc += v[p];
       } else {
-        for (int p = 0; p < world; p++) {
-          const unsigned long long v = __ldcv(peers.buf[p] + i);
-          acc = v > acc ? v : acc;
-        }
+#pragma unroll
+        for (int p = 0; p < kXrMaxWorld; p++) acc = v[p] > acc ? v[p] : acc;
       }
       out[i] = acc;
     }
@@ -125,10 +132,133 @@ __global__ void __launch_bounds__(256) xr_fused_kernel(XrPeers peers, int world,
   grid.sync();
   {
     unsigned long long* in = peers.buf[rank];
-    for (int o = 0; o < world; o++) {
-      const long long lo = n * o / world, hi = n * (o + 1) / world;
-      const unsigned long long* src = peers.buf[o] + cap;
-      for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) in[i] = __ldcv(src + i);
+    constexpr int U = 4;
+    for (long long i0 = tid; i0 < n; i0 += U * stride) {
+      unsigned long long v[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const long long i = i0 + u * stride;
+        if (i < n) {
+          int o = 0;
+#pragma unroll
+          for (int q = 1; q < kXrMaxWorld; q++) o += (q < world && i >= s_lo[q]) ? 1 : 0;
+          v[u] = __ldcv(peers.buf[o] + cap + i);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const long long i = i0 + u * stride;
+        if (i < n) in[i] = v[u];
+      }
+    }
+  }
+}
+
+
+// ---- The exchange without barriers or fences: every 64-bit word travels as a 16-byte line {lo, flag, hi, flag} written with ONE
+// store, flag = the exchange's epoch (the two 8-byte halves of an aligned 16-byte store are each written atomically, so a reader
+// that sees both flags has the whole word). Ranks PUSH: (A) rank r stores word i of its input into the owner o(i)'s reduce-scatter
+// area, slot [r][i - lo(o)]; (B) the owner polls the W - 1 lines of each of its words, reduces, keeps the result and stores it into
+// every peer's all-gather area, slot [i]; (C) everybody polls the words it does not own. No grid-wide sync, no system-scope fence,
+// a plain launch; latency = two NVLink store flights plus the polls. Twice the bytes on the wire, which at 0.7-5.5 MB per level is
+// cheaper than the three barriers of the pull version (tools/xr_bench.py).
+// Buffers alternate by epoch parity: a rank can only be one exchange ahead of a peer (it needs the peer's lines to finish one), so
+// a line is never overwritten before it was read. A stale line carries an older epoch and is never mistaken for the current one.
+struct __align__(16) XrLine {
+  uint32_t d0, f0, d1, f1;
+};
+__device__ __forceinline__ void xr_line_store(XrLine* dst, unsigned long long v, uint32_t flag) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"((uint32_t)v), "r"(flag), "r"((uint32_t)(v >> 32)), "r"(flag)
+               : "memory");
+}
+__device__ __forceinline__ bool xr_line_load(const XrLine* src, uint32_t flag, unsigned long long& v) {
+  uint32_t d0, f0, d1, f1;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(d0), "=r"(f0), "=r"(d1), "=r"(f1) : "l"(src) : "memory");
+  v = ((unsigned long long)d1 << 32) | d0;
+  return f0 == flag && f1 == flag;
+}
+
+// rs_off / ag_off: word offsets of the two line areas inside every rank's buffer; half: words per parity of an area.
+// The grid must be co-resident (the pollers of one rank wait for the pushers of another): <= 2 CTAs per SM.
+__global__ void __launch_bounds__(256) xr_ll_kernel(XrPeers peers, int world, int rank, size_t rs_off, size_t ag_off, size_t half,
+                                                    long long n_sums, long long n, uint32_t epoch, unsigned long long timeout_cycles, int* err) {
+  __shared__ long long s_lo[kXrMaxWorld + 1];
+  if (threadIdx.x <= world) s_lo[threadIdx.x] = n * threadIdx.x / world;
+  __syncthreads();
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, stride = (long long)gridDim.x * blockDim.x;
+  const size_t par = (size_t)(epoch & 1u) * half;
+  const long long sl = (n + world - 1) / world;  // lines per sender in a reduce-scatter area
+  unsigned long long* in = peers.buf[rank];
+  const long long t0 = clock64();
+  bool dead = false;
+  // ---- A: push the words other ranks own
+  for (long long i = tid; i < n; i += stride) {
+    int o = 0;
+#pragma unroll
+    for (int q = 1; q < kXrMaxWorld; q++) o += (q < world && i >= s_lo[q]) ? 1 : 0;
+    if (o == rank) continue;
+    XrLine* dst = reinterpret_cast<XrLine*>(peers.buf[o] + rs_off + par) + (size_t)rank * sl + (size_t)(i - s_lo[o]);
+    xr_line_store(dst, in[i], epoch);
+  }
+  // ---- B: reduce the words this rank owns, publish them
+  {
+    const long long lo = s_lo[rank], hi = s_lo[rank + 1];
+    const XrLine* rs = reinterpret_cast<const XrLine*>(in + rs_off + par);
+    for (long long i = lo + tid; i < hi && !dead; i += stride) {
+      unsigned long long acc = in[i];
+      const bool is_sum = i < n_sums;
+      unsigned todo = ((1u << world) - 1u) & ~(1u << rank);
+      while (todo) {
+#pragma unroll
+        for (int p = 0; p < kXrMaxWorld; p++) {
+          if (!((todo >> p) & 1u)) continue;
+          unsigned long long v;
+          if (xr_line_load(rs + (size_t)p * sl + (size_t)(i - lo), epoch, v)) {
+            acc = is_sum ? acc + v : (v > acc ? v : acc);
+            todo &= ~(1u << p);
+          }
+        }
+        if (todo && (unsigned long long)(clock64() - t0) > timeout_cycles) {
+          atomicExch(err, 1);
+          dead = true;
+          break;
+        }
+      }
+      in[i] = acc;
+#pragma unroll
+      for (int p = 0; p < kXrMaxWorld; p++)
+        if (p < world && p != rank) xr_line_store(reinterpret_cast<XrLine*>(peers.buf[p] + ag_off + par) + (size_t)i, acc, epoch);
+    }
+  }
+  // ---- C: collect the words the others own
+  {
+    const XrLine* ag = reinterpret_cast<const XrLine*>(in + ag_off + par);
+    const long long lo = s_lo[rank], hi = s_lo[rank + 1];
+    constexpr int U = 4;
+    for (long long i0 = tid; i0 < n && !dead; i0 += U * stride) {
+      unsigned todo = 0u;
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const long long i = i0 + u * stride;
+        if (i < n && (i < lo || i >= hi)) todo |= 1u << u;
+      }
+      while (todo) {
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          if (!((todo >> u) & 1u)) continue;
+          const long long i = i0 + u * stride;
+          unsigned long long v;
+          if (xr_line_load(ag + (size_t)i, epoch, v)) {
+            in[i] = v;
+            todo &= ~(1u << u);
+          }
+        }
+        if (todo && (unsigned long long)(clock64() - t0) > timeout_cycles) {
+          atomicExch(err, 1);
+          dead = true;
+          break;
+        }
+      }
     }
   }
 }
