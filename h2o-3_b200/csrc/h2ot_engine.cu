@@ -112,6 +112,9 @@ struct TreeState {  // per class-tree k
   long long* sums = nullptr;          // this level's payload: d_sums, or the peer-mapped exchange buffer
   unsigned long long* mm = nullptr;
   bool in_xbuf = false;
+  bool best_pending = false;  // h2ot_find_splits left DecidedNode.bestCol to next_level_kernel
+  bool fin_pending = false;   // h2ot_finish_level left the finalize kernel to the split search (fin_args)
+  FinalizeArgs fin_args{};
   bool level_failed = false;  // a level call failed after score_decide had moved the rows: the tree has to be restarted
   // ---- levels enqueued back to back with the step between them on the device (h2ot_tree_levels_begin / _end, k_next.cuh)
   struct DevLoop {
@@ -1731,6 +1734,11 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
     na.exists = dv.exists.p;
     na.tree_splits = dv.tree_splits.p;
     na.err = dv.err.p;
+    if (t.best_pending) {
+      na.cand = t.d_cand.p;
+      na.best_out = const_cast<h2ot_split*>(dv.prev_best);
+      t.best_pending = false;
+    }
     next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
     h->stats.launches++;
     TRY(launch_score());
@@ -1921,10 +1929,18 @@ int h2ot_finish_level(h2ot_engine* h, int32_t k, double* out_vals, int64_t out_v
   fa.inv_sy = std::ldexp(1.0, -t.ey);
   fa.inv_syy = std::ldexp(1.0, -t.eyy);
   fa.inv_sw = std::ldexp(1.0, -ew);
-  TRY(t_begin(h, &h->stats.ms_finalize));
-  finalize_kernel<<<(unsigned)LC, 128, 0, h->stream>>>(fa);
-  h->stats.launches++;
-  TRY(t_end(h));
+  // levels enqueued back to back (h2ot_tree_levels_begin): the split search that follows does each pair's finalize itself
+  static const bool no_fuse_fin = getenv("H2OT_NO_FUSE_FIN") != nullptr;
+  const bool fuse = !no_fuse_fin && h->in_tree_loop && !out_vals && !out_min2 && !out_maxIn && !out_wNA && !out_has_vals;
+  t.fin_pending = fuse;
+  if (fuse) {
+    t.fin_args = fa;
+  } else {
+    TRY(t_begin(h, &h->stats.ms_finalize));
+    finalize_kernel<<<(unsigned)LC, 128, 0, h->stream>>>(fa);
+    h->stats.launches++;
+    TRY(t_end(h));
+  }
   if (out_vals) {
     if (out_vals_capacity < t.total_vals) H2OT_FAIL(H2OT_ERR_INVALID, "out_vals too small: need " + std::to_string(t.total_vals) + " doubles");
     TRY(d2h(h, out_vals, t.d_vals.p, (size_t)t.total_vals * sizeof(double)));
@@ -1960,11 +1976,22 @@ int h2ot_find_splits(h2ot_engine* h, int32_t k, double min_rows, double min_spli
   if (smem > (size_t)h->split_smem_max) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "histogram too wide for the split-search kernel");
   if (t.any_cat && ((t.max_split_nbin - 1) >> 3) + 1 > H2OT_MAX_BITSET_BYTES) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "categorical bitset above 4096 bits");
   SplitArgs sa{t.L, h->C, t.p_descs, t.d_vals.p, t.p_min2, t.p_maxIn, t.p_has, min_rows, min_split_improvement, t.d_cand.p,
-               t.any_splitpts ? t.d_sp.p : nullptr};
+               t.any_splitpts ? t.d_sp.p : nullptr, 0, FinalizeArgs{}};
+  if (t.fin_pending) {
+    sa.fused = 1;
+    sa.fin = t.fin_args;
+    t.fin_pending = false;
+  }
   TRY(t_begin(h, &h->stats.ms_split));
   find_split_kernel<<<(unsigned)LC, kSplitThreads, smem, h->stream>>>(sa);
-  best_col_kernel<<<t.L, 32, 0, h->stream>>>(t.L, h->C, t.p_descs, t.d_cand.p, t.p_best);
-  h->stats.launches += 2;
+  h->stats.launches++;
+  // levels enqueued back to back: next_level_kernel picks each leaf's column itself (nobody else reads p_best before it)
+  static const bool no_fuse_best = getenv("H2OT_NO_FUSE_BEST") != nullptr;
+  t.best_pending = !no_fuse_best && h->in_tree_loop && !out_splits;
+  if (!t.best_pending) {
+    best_col_kernel<<<t.L, 32, 0, h->stream>>>(t.L, h->C, t.p_descs, t.d_cand.p, t.p_best);
+    h->stats.launches++;
+  }
   TRY(t_end(h));
   if (out_splits) TRY(d2h(h, out_splits, t.p_best, (size_t)t.L * sizeof(h2ot_split)));
   return finish_call(h);
@@ -2183,6 +2210,8 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   dv.active = true;
   h->defer_sync = true;
   h->in_tree_loop = true;
+  t.best_pending = t.fin_pending = false;
+  TRY(t.d_cand.ensure(((size_t)1 << (D - 1)) * C));  // (never reallocated while a kernel of an earlier level still reads it)
   int rc = H2OT_OK;
   std::vector<h2ot_hist_desc> tmpl;
   for (int d = 0; d < D && rc == H2OT_OK; d++) {
@@ -2248,6 +2277,11 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     na.exists = dv.exists.p;
     na.tree_splits = dv.tree_splits.p;
     na.err = dv.err.p;
+    if (t.best_pending) {
+      na.cand = t.d_cand.p;
+      na.best_out = const_cast<h2ot_split*>(dv.prev_best);
+      t.best_pending = false;
+    }
     next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
     h->stats.launches++;
     if (cudaGetLastError() != cudaSuccess) {

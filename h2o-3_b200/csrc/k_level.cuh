@@ -691,8 +691,10 @@ struct FinalizeArgs {
   double inv_sy, inv_syy, inv_sw;
 };
 
-__global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
-  const int p = blockIdx.x;  // (l, c)
+// One (leaf, column) pair, by a CTA of 128 threads. smem_vals (nullable): the pair's finalised values are also left there
+// ([3 (nbin + 1)] doubles; the split search fused behind this reads them without the round trip through global memory).
+// Returns whether the pair has values (uniform over the CTA).
+__device__ __forceinline__ bool finalize_pair(const FinalizeArgs& a, int p, double* smem_vals) {
   const int l = p / a.C;
   const DescDev d = a.descs[p];
   const bool has = d.nbin >= 0 && a.leaf_rows[l] > 0;
@@ -708,17 +710,26 @@ __global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
   }
   if (!has) {
     if (a.conc && threadIdx.x == 0) a.conc[p] = 0.0;
-    return;
+    return false;
   }
   double sw = 0, sww = 0;
   for (int b = threadIdx.x; b <= d.nbin; b += blockDim.x) {
     const long long* s = a.acc + (d.gbin + b) * 3;
+    const long long s0 = s[0], s1 = s[1], s2 = s[2];
     double* v = a.vals + d.voff + (size_t)b * 3;
-    v[0] = __dmul_rn((double)s[0], a.inv_sw);
-    v[1] = (double)(float)__dmul_rn((double)s[1], a.inv_sy);
-    v[2] = (double)(float)__dmul_rn((double)s[2], a.inv_syy);
-    sw += (double)s[0];
-    sww += (double)s[0] * (double)s[0];
+    const double v0 = __dmul_rn((double)s0, a.inv_sw);
+    const double v1 = (double)(float)__dmul_rn((double)s1, a.inv_sy);
+    const double v2 = (double)(float)__dmul_rn((double)s2, a.inv_syy);
+    v[0] = v0;
+    v[1] = v1;
+    v[2] = v2;
+    if (smem_vals) {
+      smem_vals[3 * b] = v0;
+      smem_vals[3 * b + 1] = v1;
+      smem_vals[3 * b + 2] = v2;
+    }
+    sw += (double)s0;
+    sww += (double)s0 * (double)s0;
   }
   if (a.conc) {  // not part of the reference: feeds the planner's per-column cost estimate
     __shared__ double r_w[128], r_ww[128];
@@ -734,7 +745,10 @@ __global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) {
     }
     if (threadIdx.x == 0) a.conc[p] = r_w[0] > 0 ? r_ww[0] / (r_w[0] * r_w[0]) : 0.0;
   }
+  return true;
 }
+
+__global__ void __launch_bounds__(128) finalize_kernel(FinalizeArgs a) { finalize_pair(a, blockIdx.x, nullptr); }
 
 // per-row bin codes of one column under one descriptor (parity hook for DHistogram.bin)
 __global__ void bin_codes_kernel(int64_t n, ColRef col, DescDev d, const double* sp, uint16_t* out) {

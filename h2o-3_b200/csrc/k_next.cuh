@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "k_level.cuh"
 #include "k_rows.cuh"
+#include "k_split.cuh"
 
 namespace h2ot {
 
@@ -24,6 +25,8 @@ struct NextArgs {
   const DescDev* pdescs;       // parent level [Lp][C]
   const double* pmaxex;        // parent level _maxEx [Lp][C]
   const h2ot_split* best;      // parent level [Lp]
+  const h2ot_split* cand;      // nullptr, or the parent level's candidates [Lp][C]: DecidedNode.bestCol runs here first and fills best_out
+  h2ot_split* best_out;        // == best when cand is set
   const double* min2;          // [Lp * C]
   const double* maxIn;
   const double* wna;
@@ -64,7 +67,17 @@ __global__ void __launch_bounds__(128) next_level_kernel(NextArgs a) {
   __shared__ int s_cnt[2];
   __shared__ h2ot_split sp_s;
   if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
-  {  // the split record, word-wise into shared memory
+  if (a.cand) {
+    // DecidedNode.bestCol (T/DTree.java:616-656), otherwise a kernel of its own between the split search and this one: the first
+    // warp picks the leaf's column and copies the winner straight into shared memory; the record is then published for the host
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&sp_s);
+    for (int i = threadIdx.x; i < (int)(sizeof(h2ot_split) / 4); i += blockDim.x) dst[i] = 0u;
+    __syncthreads();
+    if (threadIdx.x < 32) best_col_warp(s, a.C, a.pdescs, a.cand, &sp_s);
+    __syncthreads();
+    uint32_t* pub = reinterpret_cast<uint32_t*>(a.best_out + s);
+    for (int i = threadIdx.x; i < (int)(sizeof(h2ot_split) / 4); i += blockDim.x) pub[i] = dst[i];
+  } else {  // the split record, word-wise into shared memory
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a.best + s);
     uint32_t* dst = reinterpret_cast<uint32_t*>(&sp_s);
     for (int i = threadIdx.x; i < (int)(sizeof(h2ot_split) / 4); i += blockDim.x) dst[i] = src[i];

@@ -27,6 +27,8 @@ struct SplitArgs {
   double min_rows, min_split_improvement;
   h2ot_split* cand;  // [L*C]
   const double* sp;  // the level's split-point pool or nullptr
+  int32_t fused;     // 1: the pair's finalize (fixed point -> _vals, min2 / maxIn / wNA, has_vals) runs here first, fin holds its arguments
+  FinalizeArgs fin;
 };
 
 constexpr int kSplitThreads = 128;
@@ -76,7 +78,11 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     out->splat = __int_as_float(0x7fc00000);
     out->bs_nbits = out->bs_bitoff = out->bs_nbytes = 0;
   }
-  if (d.nbin < 0 || !a.has_vals[p]) return;
+  if (d.nbin < 0) {
+    if (a.fused) finalize_pair(a.fin, p, nullptr);
+    return;
+  }
+  if (!a.fused && !a.has_vals[p]) return;
   const int nbins = d.nbin;
   const int n1 = nbins + 1;
   const bool is_cat_sorted = (d.flags & H2OT_DESC_ISCAT) && d.step == 1.0;
@@ -94,8 +100,20 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
   __shared__ int s_break;
   __shared__ Cand s_c[kSplitThreads];
 
-  const double* gv = a.vals + d.voff;
-  for (int i = tid; i < 3 * n1; i += blockDim.x) orig[i] = gv[i];
+  if (a.fused) {
+    if (!finalize_pair(a.fin, p, orig)) return;
+  } else {
+    const double* gv = a.vals + d.voff;
+    const int n3 = 3 * n1;
+    for (int i0 = tid; i0 < n3; i0 += 8 * kSplitThreads) {  // eight loads in flight per thread
+      double x[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) x[u] = i0 + u * kSplitThreads < n3 ? gv[i0 + u * kSplitThreads] : 0.0;
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+        if (i0 + u * kSplitThreads < n3) orig[i0 + u * kSplitThreads] = x[u];
+    }
+  }
   if (tid == 0) s_break = 0x7fffffff;
   __syncthreads();
   const double wNA = orig[3 * nbins], wYNA = orig[3 * nbins + 1], wYYNA = orig[3 * nbins + 2];
@@ -128,13 +146,28 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     v = sorted;
   }
 
-  // :1036-1067 and :1090-1121 — six sequential scans on six threads
+  // :1036-1067 and :1090-1121 — six sequential scans on six threads. The additions are a dependent chain (the reference's order is
+  // the result), but the loads and stores around them need not be: eight values are fetched before, and stored after, eight adds
+  // (left to the compiler, every load waited for the previous store -- source and destination could alias -- and an element cost
+  // ~100 clocks instead of one fp64 add).
   if (tid < 3) {
     double* dst = tid == 0 ? wlo : (tid == 1 ? wYlo : wYYlo);
     double s = 0.0;
     dst[0] = 0.0;
-#pragma unroll 8
-    for (int b = 1; b <= nbins; b++) {
+    int b = 1;
+    for (; b + 7 <= nbins; b += 8) {
+      double x[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) x[u] = v[3 * (b - 1 + u) + tid];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        s = __dadd_rn(s, x[u]);
+        x[u] = s;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++) dst[b + u] = x[u];
+    }
+    for (; b <= nbins; b++) {
       s = __dadd_rn(s, v[3 * (b - 1) + tid]);
       dst[b] = s;
     }
@@ -143,8 +176,20 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
     double* dst = j == 0 ? whi : (j == 1 ? wYhi : wYYhi);
     double s = 0.0;
     dst[nbins] = 0.0;
-#pragma unroll 8
-    for (int b = nbins - 1; b >= 0; b--) {
+    int b = nbins - 1;
+    for (; b - 7 >= 0; b -= 8) {
+      double x[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) x[u] = v[3 * (b - u) + j];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        s = __dadd_rn(s, x[u]);
+        x[u] = s;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++) dst[b - u] = x[u];
+    }
+    for (; b >= 0; b--) {
       s = __dadd_rn(s, v[3 * b + j]);
       dst[b] = s;
     }
@@ -366,9 +411,9 @@ __global__ void __launch_bounds__(kSplitThreads) find_split_kernel(SplitArgs a) 
 
 // DecidedNode.bestCol (T/DTree.java:616-656): first strictly smaller se() in _scoreCols order. One warp per leaf: lanes take
 // columns, a shuffle reduction keeps the lexicographic minimum of (se, position in _scoreCols), the warp copies the winner.
-__global__ void __launch_bounds__(32) best_col_kernel(int L, int C, const DescDev* descs, const h2ot_split* cand, h2ot_split* best_out) {
-  const int l = blockIdx.x;
-  const int lane = threadIdx.x;
+// (one full warp per leaf; best_col_kernel below, or the first warp of next_level_kernel when the levels run back to back)
+__device__ __forceinline__ void best_col_warp(int l, int C, const DescDev* descs, const h2ot_split* cand, h2ot_split* o) {  // o: the leaf's record
+  const int lane = threadIdx.x & 31;
   int bc = -1, border = 0x7fffffff;
   double bse = 0;
   for (int c = lane; c < C; c += 32) {
@@ -394,7 +439,6 @@ __global__ void __launch_bounds__(32) best_col_kernel(int L, int C, const DescDe
       border = oo;
     }
   }
-  h2ot_split* o = best_out + l;
   if (bc < 0) {
     if (lane == 0) {
       o->col = -1;
@@ -408,6 +452,9 @@ __global__ void __launch_bounds__(32) best_col_kernel(int L, int C, const DescDe
   const int nbytes = cand[(size_t)l * C + bc].bs_nbytes;
   const int nwords = 26 + (nbytes + 3) / 4;  // offsetof(h2ot_split, bs) == 104
   for (int i = lane; i < nwords; i += 32) dst[i] = src[i];
+}
+__global__ void __launch_bounds__(32) best_col_kernel(int L, int C, const DescDev* descs, const h2ot_split* cand, h2ot_split* best_out) {
+  best_col_warp(blockIdx.x, C, descs, cand, best_out + blockIdx.x);
 }
 
 }  // namespace h2ot
