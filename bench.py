@@ -372,8 +372,10 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    PROF_STEPS = 3  # untimed steps after the timed region, with every stage's CUDA-event timer on (stage_ms_per_step)
+
     def new_gbm(ntrees=None, device=local):
-        return getattr(P, wl["cls"])(ntrees=ntrees or (args.steps + args.warmup), device=device, **wl["model"])
+        return getattr(P, wl["cls"])(ntrees=ntrees or (args.steps + args.warmup + PROF_STEPS), device=device, **wl["model"])
 
     # ---------------- device-resident arm: W warm-up + K timed boosting iterations
     gm = new_gbm()
@@ -401,8 +403,10 @@ def run_b200(args):
     ms = e0.elapsed_time(e1)
     clocks = clk.stop() if rank == 0 else None
     s1 = eng.stats()
+    t1s = gm.timing()
+    t1s = type('T', (), dict(levels=t1s.levels, level_s=t1s.level_s, total_s=t1s.total_s, hist_rows_cols=t1s.hist_rows_cols))
     d = {f: getattr(s1, f) - snap0[f] for f, _ in s1._fields_}
-    rowcols = gm.timing().hist_rows_cols - rc0  # global rows x active cols over the timed level passes
+    rowcols = t1s.hist_rows_cols - rc0  # global rows x active cols over the timed level passes
     t = torch.tensor([ms, float(d["launches"])], dtype=torch.float64, device="cuda")
     if world > 1:
         tm = t.clone()
@@ -423,15 +427,26 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": d["hist_algo_bytes"] / n_hl, "ms_per_launch": hist_ms / n_hl,
                 "launches": int(d["hist_launches"]),
                 "kernel_rows_x_cols_per_s": d["hist_rows_cols"] / (hist_ms * 1e-3) if hist_ms > 0 else 0.0,
-                "stage_ms_per_step": {k: d[k] / args.steps for k in ("ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals",
-                                                                        "ms_gamma", "ms_addtree", "ms_exchange")}}
+                "stage_ms_per_step": None}
+    # stage breakdown: a separate, untimed pass. A timed section costs two event records in the stream (~3 us each way), so the
+    # timed region above times the histogram launches only (h2ot_set_timers mode 1) and the other stages are timed here.
+    eng.set_timers(2)
+    sp0 = eng.stats()
+    snap_p = {f: getattr(sp0, f) for f, _ in sp0._fields_}
+    for _ in range(PROF_STEPS):
+        gm.train(1)
+    gm.flush()
+    sp1 = eng.stats()
+    roofline["stage_ms_per_step"] = {k: (getattr(sp1, k) - snap_p[k]) / PROF_STEPS for k in (
+        "ms_score", "ms_hist", "ms_finalize", "ms_split", "ms_residuals", "ms_gamma", "ms_addtree", "ms_exchange")}
+    roofline["stage_ms_per_step"]["note"] = "%d extra steps after the timed region with every stage timed; ms_finalize is part of ms_split when the levels run back to back" % PROF_STEPS
+    eng.set_timers(1)
     # secondary ceiling (SURVEY 8d asks for it): the kernel's time goes into shared-memory atomics, ATOMS_PER_ITEM per (row, column)
     # item with unit weights; random-bin ATOMS.ADD runs at 12.4 lanes/clk/SM = 3490 G/s on this part (conflict free: 31 lanes/clk/SM;
     # tools/ubench_atomics2.cu "clean" lines, profiles/r01_ubench_atomics2_b200.txt)
     atoms = ATOMS_PER_ITEM * d["hist_rows_cols"] / (hist_ms * 1e-3) / 1e9 if hist_ms > 0 else 0.0
     roofline["smem_atomics"] = {"achieved": atoms, "peak": 3490.0, "unit": "Gatom/s", "frac": atoms / 3490.0, "atomics_per_item": ATOMS_PER_ITEM,
                                 "peak_source": "measured, tools/ubench_atomics2.cu (random-bin pattern) on B200"}
-    t1s = gm.timing()
     levels_per_step = (t1s.levels - t0s.levels) / args.steps
     roofline["host_ms_per_step"] = {"inside_level_calls": 1e3 * (t1s.level_s - t0s.level_s) / args.steps,
                                     "whole_step_wall": 1e3 * (t1s.total_s - t0s.total_s) / args.steps}
@@ -457,11 +472,11 @@ def run_b200(args):
                     single = single and bool(np.array_equal(g1.predictions(k)[r0:r1], my_preds[k]))
             g1.close()
             del fcols, fy
-            parity = {"trees_identical_across_ranks": bool(same), "trees_identical_to_1gpu": bool(single), "trees": args.steps + args.warmup,
+            parity = {"trees_identical_across_ranks": bool(same), "trees_identical_to_1gpu": bool(single), "trees": args.steps + args.warmup + PROF_STEPS,
                       "sha256": digests[0][:16]}
         barrier()
     else:
-        parity = {"trees_identical_across_ranks": True, "trees_identical_to_1gpu": True, "trees": args.steps + args.warmup,
+        parity = {"trees_identical_across_ranks": True, "trees_identical_to_1gpu": True, "trees": args.steps + args.warmup + PROF_STEPS,
                   "sha256": hashlib.sha256(mine).hexdigest()[:16]}
 
     # ---------------- end-to-end arm: whole job from pinned host buffers through the public API

@@ -110,7 +110,7 @@ ENGINE_SYMBOLS = [
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
     "h2ot_get_nids", "h2ot_set_nids", "h2ot_compute_residuals", "h2ot_get_gamma_bounds", "h2ot_set_gamma_bounds", "h2ot_begin_tree", "h2ot_build_level",
     "h2ot_level_buffers", "h2ot_allreduce_level", "h2ot_finish_level", "h2ot_find_splits", "h2ot_level_step", "h2ot_set_tree",
-    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_add_tree_scaled", "h2ot_set_sample_rate_per_class", "h2ot_set_lazy_sync", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
+    "h2ot_gamma_pass", "h2ot_add_tree", "h2ot_add_tree_scaled", "h2ot_set_sample_rate_per_class", "h2ot_set_lazy_sync", "h2ot_set_timers", "h2ot_score_metrics", "h2ot_drf_init_model", "h2ot_sample", "h2ot_drf_collect_preds", "h2ot_get_oobt",
     "h2ot_comm_unique_id", "h2ot_comm_init", "h2ot_allreduce_host_f64", "h2ot_reserve_exchange",
     "h2ot_get_weight_bound", "h2ot_set_weight_bound", "h2ot_debug_bin_codes", "h2ot_stats_get", "h2ot_stats_reset",
     "h2ot_set_hist_mode", "h2ot_auc_builders", "h2ot_hist_column_noalloc", "h2ot_load_chunk", "h2ot_debug_get_column", "h2ot_set_split_points", "h2ot_score_tree", "h2ot_level_step_begin", "h2ot_level_step_end", "h2ot_tree_levels_begin", "h2ot_tree_levels_end",
@@ -179,6 +179,7 @@ def load():
     L.h2ot_add_tree_scaled.argtypes = [vp, i32, i32, vp, vp]
     L.h2ot_set_sample_rate_per_class.argtypes = [vp, vp, i32]
     L.h2ot_set_lazy_sync.argtypes = [vp, i32]
+    L.h2ot_set_timers.argtypes = [vp, i32]
     L.h2ot_gbm_set_pred_noise_bandwidth.argtypes = [vp, dbl]
     L.h2ot_gbm_set_sample_rate_per_class.argtypes = [vp, vp, i32]
     L.h2ot_drf_init_model.argtypes = [vp]
@@ -450,6 +451,10 @@ class Engine:
 
     def stats_reset(self):
         _check(self.L.h2ot_stats_reset(self.h))
+
+    def set_timers(self, mode):
+        """2: every stage timed (CUDA events), 1: the histogram launches only, 0: none."""
+        _check(self.L.h2ot_set_timers(self.h, int(mode)))
 
     def set_hist_mode(self, mode):
         _check(self.L.h2ot_set_hist_mode(self.h, mode))

@@ -124,10 +124,18 @@ struct TreeState {  // per class-tree k
     double min_rows = 0;
     DBuf<unsigned char> lvl_alt, pack_alt;   // the previous level's descriptors / results (ping-pong with d_lvl / d_pack)
     DBuf<double> maxex[2];                   // _maxEx of the levels' histograms [slot][col] (ping-pong)
-    DBuf<uint8_t> exists;                    // [static id]
-    DBuf<h2ot_split> tree_splits;            // [static id]
+    // what the host reads back after a tree, in ONE device block laid out like a half of out_stage:
+    // [tree_splits: 2^D - 1][exists: 2^(D+1) - 1 bytes][err][root concentration: C doubles][leaf values: 2^(D+1) - 1 floats]
+    DBuf<unsigned char> out_dev;
+    struct { uint8_t* p = nullptr; } exists;            // [static id]
+    struct { h2ot_split* p = nullptr; } tree_splits;    // [static id < 2^D - 1]
+    struct { int32_t* p = nullptr; } err;
+    double* p_conc_out = nullptr;
+    float* p_pred_out = nullptr;
     DBuf<int32_t> nb_caps;                   // [depth][col] largest nbin the level's layout holds
-    DBuf<int32_t> err;
+    DBuf<double> root_maxex;                 // the root histograms' _maxEx [col]
+    std::vector<int32_t> h_caps;             // host copies of the two: uploaded again only when they change
+    std::vector<double> h_root_maxex;
     std::vector<unsigned char*> lvl_stage;   // pinned staging of each level's upload (the levels are enqueued ahead of the GPU)
     std::vector<size_t> lvl_stage_cap;
     std::vector<char> lvl_stage_own;         // 1: a block of its own (not a slice of the arena)
@@ -140,6 +148,7 @@ struct TreeState {  // per class-tree k
     const double *prev_min2 = nullptr, *prev_maxIn = nullptr, *prev_wna = nullptr, *prev_maxex = nullptr;
     const uint8_t* prev_has = nullptr;
     const h2ot_split* prev_best = nullptr;
+    const double* conc_src = nullptr;  // the root level's per-column concentration (finalize), copied out by the first step kernel
     // Two trees of a class may be in flight (the host mirrors tree t while the device builds tree t + 1): every pinned staging
     // area has two halves, a tree uses half `slot`
     int next_slot = 0, n_pend = 0;
@@ -221,6 +230,8 @@ struct h2ot_engine {
   std::vector<Timer> timers;
   std::vector<cudaEvent_t> event_pool;
   bool defer_sync = false;
+  bool timer_open = false;
+  int timer_mode = 2;  // h2ot_set_timers
   bool in_tree_loop = false;  // inside h2ot_tree_levels_begin: per-level housekeeping copies are done once per tree
   bool lazy_sync = false;          // h2ot_set_lazy_sync: calls that return nothing to the host do not wait for the stream
   std::vector<double> rate_per_class;  // Sample's _rate_per_class (empty: null)
@@ -276,6 +287,10 @@ int xr_ensure(h2ot_engine* h, size_t words);
 int xr_allreduce(h2ot_engine* h, long long n_sums, long long n);
 
 int t_begin(h2ot_engine* h, double* acc) {
+  // Every timed section costs two event records in the stream (~3 us: 0.14 ms of a 1.5 ms tree on an eighth of the Higgs frame):
+  // mode 2 times every stage, mode 1 the histogram launches only (what the roofline needs), mode 0 nothing.
+  h->timer_open = h->timer_mode >= 2 || (h->timer_mode == 1 && acc == &h->stats.ms_hist);
+  if (!h->timer_open) return H2OT_OK;
   Timer t;
   for (cudaEvent_t* e : {&t.a, &t.b}) {
     if (!h->event_pool.empty()) {
@@ -291,6 +306,8 @@ int t_begin(h2ot_engine* h, double* acc) {
   return H2OT_OK;
 }
 int t_end(h2ot_engine* h) {
+  if (!h->timer_open) return H2OT_OK;
+  h->timer_open = false;
   CUDA_TRY(cudaEventRecord(h->timers.back().b, h->stream));
   return H2OT_OK;
 }
@@ -509,8 +526,8 @@ int h2ot_destroy(h2ot_engine* h) {
     if (t.done_ev) cudaEventDestroy(t.done_ev);
     t.d_sums.release(); t.d_vals.release(); t.d_pack.release();
     t.d_cand.release(); t.d_gamma.release(); t.d_pred.release(); t.d_factor.release(); t.d_sp.release();
-    t.dev.lvl_alt.release(); t.dev.pack_alt.release(); t.dev.maxex[0].release(); t.dev.maxex[1].release(); t.dev.exists.release();
-    t.dev.tree_splits.release(); t.dev.nb_caps.release(); t.dev.err.release();
+    t.dev.lvl_alt.release(); t.dev.pack_alt.release(); t.dev.maxex[0].release(); t.dev.maxex[1].release(); t.dev.out_dev.release();
+    t.dev.nb_caps.release(); t.dev.root_maxex.release();
     for (size_t i = 0; i < t.dev.lvl_stage.size(); i++) if (t.dev.lvl_stage[i] && t.dev.lvl_stage_own[i]) cudaFreeHost(t.dev.lvl_stage[i]);
     if (t.dev.arena) cudaFreeHost(t.dev.arena);
     if (t.dev.out_stage) cudaFreeHost(t.dev.out_stage);
@@ -1739,6 +1756,10 @@ int h2ot_build_level(h2ot_engine* h, int32_t k, int32_t leaf_offset, int32_t n_l
       na.best_out = const_cast<h2ot_split*>(dv.prev_best);
       t.best_pending = false;
     }
+    if (na.Lp == 1) {
+      na.conc_src = dv.conc_src;
+      na.conc_dst = dv.p_conc_out;
+    }
     next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
     h->stats.launches++;
     TRY(launch_score());
@@ -2125,10 +2146,8 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   // ---- buffers of the whole tree, sized once
   TRY(t.nodes.ensure(S));
   TRY(t.bitsets.ensure(S * H2OT_MAX_BITSET_BYTES));
-  TRY(dv.exists.ensure(S));
-  TRY(dv.tree_splits.ensure(S));
-  TRY(dv.err.ensure(1));
   TRY(dv.nb_caps.ensure((size_t)D * C));
+  TRY(dv.root_maxex.ensure((size_t)C));
   TRY(dv.maxex[0].ensure(((size_t)1 << (D - 1)) * C));
   TRY(dv.maxex[1].ensure(((size_t)1 << (D - 1)) * C));
   const size_t n_splits = ((size_t)1 << D) - 1;  // nodes of levels 0 .. D-1
@@ -2147,6 +2166,12 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     dv.out_half = out_bytes;
   }
   unsigned char* const out_stage = dv.out_stage + (size_t)slot * dv.out_half;
+  TRY(dv.out_dev.ensure(dv.out_half));
+  dv.tree_splits.p = reinterpret_cast<h2ot_split*>(dv.out_dev.p);
+  dv.exists.p = dv.out_dev.p + dv.o_exists;
+  dv.err.p = reinterpret_cast<int32_t*>(dv.out_dev.p + dv.o_err);
+  dv.p_conc_out = reinterpret_cast<double*>(dv.out_dev.p + dv.o_conc);
+  dv.p_pred_out = reinterpret_cast<float*>(dv.out_dev.p + dv.o_pred);
   // widest histogram a column can have at each depth (DHistogram ctor rule: max(parent nbin >> 1, nbins); categoricals keep theirs)
   std::vector<int32_t> caps((size_t)D * C, 0);
   for (int c = 0; c < C; c++) {
@@ -2189,16 +2214,23 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     for (int d = 0; d < D; d++)  // this tree's half (a level that outgrew its slice keeps its own block)
       if (!dv.lvl_stage_own[(size_t)d]) dv.lvl_stage[(size_t)d] = dv.arena + (size_t)slot * dv.arena_half + dv.lvl_off[(size_t)d];
   }
-  CUDA_TRY(cudaMemsetAsync(t.nodes.p, 0xFF, S * sizeof(h2ot_decided_node), h->stream));  // col = pid = -1
-  CUDA_TRY(cudaMemsetAsync(dv.exists.p, 0, S, h->stream));
-  CUDA_TRY(cudaMemsetAsync(dv.exists.p, 1, 1, h->stream));  // the root
-  CUDA_TRY(cudaMemsetAsync(dv.err.p, 0, sizeof(int32_t), h->stream));
-  // (pageable sources: these two small copies are staged by the runtime before the call returns)
-  CUDA_TRY(cudaMemcpyAsync(dv.nb_caps.p, caps.data(), caps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  // node table: col = pid = -1 everywhere; only the root exists; no error; no concentration measured yet
+  tree_init_kernel<<<(unsigned)((S * sizeof(h2ot_decided_node) / 4 + 255) / 256), 256, 0, h->stream>>>(
+      reinterpret_cast<uint32_t*>(t.nodes.p), (int)(S * sizeof(h2ot_decided_node) / 4), dv.exists.p, (int)S, dv.err.p, dv.p_conc_out, C);
+  h->stats.launches++;
+  // the two small tables change only with the model's root histograms: uploaded when they differ from what the device holds
+  // (pageable sources: staged by the runtime before the call returns)
+  if (caps != dv.h_caps) {
+    CUDA_TRY(cudaMemcpyAsync(dv.nb_caps.p, caps.data(), caps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    dv.h_caps = caps;
+  }
   {
     std::vector<double> mx(C);
     for (int c = 0; c < C; c++) mx[c] = root_descs[c].maxEx;
-    CUDA_TRY(cudaMemcpyAsync(dv.maxex[0].p, mx.data(), (size_t)C * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (mx.size() != dv.h_root_maxex.size() || memcmp(mx.data(), dv.h_root_maxex.data(), mx.size() * sizeof(double)) != 0) {
+      CUDA_TRY(cudaMemcpyAsync(dv.root_maxex.p, mx.data(), (size_t)C * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      dv.h_root_maxex = mx;
+    }
   }
   t.n_nodes = (int)S;
   t.h_nodes.clear();
@@ -2242,18 +2274,14 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
     if (rc == H2OT_OK) rc = h2ot_finish_level(h, k, nullptr, 0, nullptr, nullptr, nullptr, nullptr, nullptr);
     if (rc == H2OT_OK) rc = h2ot_find_splits(h, k, min_rows, min_split_improvement, nullptr);
     if (rc != H2OT_OK) break;
-    if (d == 0 && cudaMemcpyAsync(out_stage + dv.o_conc, t.p_conc, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
-      set_error("cudaMemcpyAsync failed");
-      rc = H2OT_ERR_CUDA;
-      break;
-    }
+    if (d == 0) dv.conc_src = t.p_conc;  // (the step kernel behind the root level copies it into the tree's output block)
     dv.prev_descs = t.p_descs;
     dv.prev_min2 = t.p_min2;
     dv.prev_maxIn = t.p_maxIn;
     dv.prev_wna = t.p_wna;
     dv.prev_has = t.p_has;
     dv.prev_best = t.p_best;
-    dv.prev_maxex = dv.maxex[d & 1].p;
+    dv.prev_maxex = d == 0 ? dv.root_maxex.p : dv.maxex[d & 1].p;
   }
   if (rc == H2OT_OK) {  // the last level's nodes and whether their children exist
     NextArgs na{};
@@ -2282,6 +2310,10 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
       na.best_out = const_cast<h2ot_split*>(dv.prev_best);
       t.best_pending = false;
     }
+    if (na.Lp == 1) {
+      na.conc_src = dv.conc_src;
+      na.conc_dst = dv.p_conc_out;
+    }
     next_level_kernel<<<na.Lp, 128, 0, h->stream>>>(na);
     h->stats.launches++;
     if (cudaGetLastError() != cudaSuccess) {
@@ -2289,9 +2321,7 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
       rc = H2OT_ERR_CUDA;
     }
   }
-  if (rc == H2OT_OK) rc = d2h(h, out_stage, dv.tree_splits.p, n_splits * sizeof(h2ot_split));
-  if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_exists, dv.exists.p, S);
-  if (rc == H2OT_OK) rc = d2h(h, out_stage + dv.o_err, dv.err.p, sizeof(int32_t));
+  if (rc == H2OT_OK) rc = d2h(h, out_stage, dv.out_dev.p, dv.o_pred);  // splits, exists, err, root concentration in one copy
   if (rc == H2OT_OK && h->xr_err && h->xr_err_host && h->nccl.world > 1 &&
       cudaMemcpyAsync(h->xr_err_host, h->xr_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess) {
     set_error("cudaMemcpyAsync failed");
@@ -2442,6 +2472,7 @@ int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_
   lv.multinomial = fam == H2OT_FAMILY_MULTINOMIAL ? 1 : 0;
   lv.max_abs = max_abs_leafnode_pred;
   lv.pred = t.d_pred.p;
+  lv.pred_out = dv.p_pred_out;
   leaf_value_kernel<<<(2 * S + 127) / 128, 128, 0, h->stream>>>(lv);
   h->stats.launches++;
   AddTreeArgs a{h->n, 2 * S, h->resp, h->w, t.nids, t.F, t.d_pred.p, nullptr};
@@ -2449,7 +2480,7 @@ int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_
   add_tree_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
   h->stats.launches++;
   TRY(t_end(h));
-  TRY(d2h(h, dv.out_stage + (size_t)slot * dv.out_half + dv.o_pred, t.d_pred.p + S, (size_t)S * sizeof(float)));
+  TRY(d2h(h, dv.out_stage + (size_t)slot * dv.out_half + dv.o_pred, dv.p_pred_out, (size_t)S * sizeof(float)));
   CUDA_TRY(cudaEventRecord(dv.ev[slot], h->stream));
   dv.timer_mark[slot] = h->timers.size();
   dv.has_pred[slot] = true;
@@ -2824,6 +2855,11 @@ int h2ot_get_weight_bound(h2ot_engine* h, double* out) {
 int h2ot_set_weight_bound(h2ot_engine* h, double bound) {
   if (!h || !(bound > 0) || std::isinf(bound)) H2OT_FAIL(H2OT_ERR_INVALID, "weight bound must be positive and finite");
   h->w_max = bound;
+  return H2OT_OK;
+}
+int h2ot_set_timers(h2ot_engine* h, int32_t mode) {
+  if (!h || mode < 0 || mode > 2) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_set_timers: mode must be 0, 1 or 2");
+  h->timer_mode = mode;
   return H2OT_OK;
 }
 int h2ot_set_lazy_sync(h2ot_engine* h, int32_t on) {

@@ -1319,6 +1319,7 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   }
   // this driver sequences whole trees: calls that return nothing need not wait for the stream
   GTRY(h2ot_set_lazy_sync(g->eng, 1));
+  GTRY(h2ot_set_timers(g->eng, getenv("H2OT_STAGE_TIMERS") ? 2 : 1));
   g->inited = true;
   return H2OT_OK;
 }

@@ -39,7 +39,19 @@ struct NextArgs {
   uint8_t* exists;             // [static id]: the slot holds a node
   h2ot_split* tree_splits;     // [static id]: the node's split, kept for the host's mirror of the tree
   int32_t* err;                // set to 1 if a descriptor does not fit the layout (cannot happen unless the caps are wrong)
+  const double* conc_src;      // step behind the root level only: the root's per-column bin concentration [C] ...
+  double* conc_dst;            // ... copied into the tree's output block (the host's planner reads it after the tree)
 };
+
+// Start of a tree: node table all -1 (col = pid = -1), only the root exists, no error, no concentration measured.
+__global__ void __launch_bounds__(256) tree_init_kernel(uint32_t* node_words, int n_node_words, uint8_t* exists, int S, int32_t* err, double* conc,
+                                                        int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_node_words) node_words[i] = 0xFFFFFFFFu;
+  if (i < S) exists[i] = i == 0 ? 1 : 0;
+  if (i < C) conc[i] = 0.0;
+  if (i == 0) *err = 0;
+}
 
 __device__ __forceinline__ double next_ulp(double d) {  // Math.ulp(double)
   if (isnan(d)) return d;
@@ -67,6 +79,8 @@ __global__ void __launch_bounds__(128) next_level_kernel(NextArgs a) {
   __shared__ int s_cnt[2];
   __shared__ h2ot_split sp_s;
   if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  if (a.conc_src && s == 0)
+    for (int c = threadIdx.x; c < a.C; c += blockDim.x) a.conc_dst[c] = a.conc_src[c];
   if (a.cand) {
     // DecidedNode.bestCol (T/DTree.java:616-656), otherwise a kernel of its own between the split search and this one: the first
     // warp picks the leaf's column and copies the winner straight into shared memory; the record is then published for the host
@@ -235,6 +249,7 @@ struct LeafValueArgs {
   int32_t multinomial;
   double max_abs;
   float* pred;           // [2 S]
+  float* pred_out;       // [S] (nullable): the leaf values again, inside the tree's output block
 };
 __global__ void __launch_bounds__(128) leaf_value_kernel(LeafValueArgs a) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -257,6 +272,7 @@ __global__ void __launch_bounds__(128) leaf_value_kernel(LeafValueArgs a) {
   if (gf > a.max_abs) gf = a.max_abs;
   if (gf < -a.max_abs) gf = -a.max_abs;
   a.pred[i] = (float)gf;
+  if (a.pred_out) a.pred_out[i - a.S] = (float)gf;
 }
 
 }  // namespace h2ot

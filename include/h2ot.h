@@ -399,6 +399,11 @@ int h2ot_set_hist_mode(h2ot_engine* h, int32_t mode);
  * without waiting for the stream; their work, kernel times and any error surface at the next call that does wait (every call that
  * returns data). A model builder that sequences whole trees saves three stream synchronisations per tree. on == 0: waits now. */
 int h2ot_set_lazy_sync(h2ot_engine* h, int32_t on);
+/* How much of h2ot_stats' per-stage times is measured. A timed section costs two CUDA event records in the stream (~3 us; 45
+ * sections per tree are 9 % of a tree on an eighth of the Higgs frame, 2 % on the whole frame). 2 (default): every stage;
+ * 1: the histogram launches only (ms_hist, hist_launches, hist_algo_bytes: what a roofline needs); 0: nothing. The model builder
+ * (h2ot_gbm) selects 1 unless H2OT_STAGE_TIMERS is set in the environment. */
+int h2ot_set_timers(h2ot_engine* h, int32_t mode);
 
 /* ---- histogram of one column for callers that cannot allocate device memory.
  * No counterpart in the reference: it exists for embedders whose process may not call cudaMalloc once it is running (a JVM or

@@ -5,6 +5,7 @@ host never holds the frame. Per-tree time and stage breakdown."""
 import ctypes as C
 import importlib
 import os
+os.environ.setdefault("H2OT_STAGE_TIMERS", "1")  # these harnesses print every stage's time
 import sys
 import time
 

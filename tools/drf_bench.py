@@ -2,6 +2,7 @@
 """BASELINE configs[2]: DRF on the Higgs-shape frame (depth 12, mtries 5, sample_rate 0.63, nbins 20). Per-tree time."""
 import importlib
 import os
+os.environ.setdefault("H2OT_STAGE_TIMERS", "1")  # these harnesses print every stage's time
 import sys
 import time
 

@@ -3,6 +3,7 @@
 config states) and bernoulli. Per-iteration time."""
 import importlib
 import os
+os.environ.setdefault("H2OT_STAGE_TIMERS", "1")  # these harnesses print every stage's time
 import sys
 import time
 

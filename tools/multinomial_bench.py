@@ -2,6 +2,7 @@
 """BASELINE configs[4a] shape: covtype-like 581k x 54 (10 numeric + 44 binary), 7 classes, nbins 64, depth 5. Per-iteration time."""
 import importlib
 import os
+os.environ.setdefault("H2OT_STAGE_TIMERS", "1")  # these harnesses print every stage's time
 import sys
 import time
 
