@@ -251,6 +251,7 @@ struct h2ot_engine {
   XrPeers xr_peers{};
   void* xr_opened[kXrMaxWorld] = {nullptr};
   unsigned long long xr_epoch = 0;
+  std::string xr_key;  // communicator id + device: the process-wide parking slot of this engine's exchange buffer
   int xr_owner = -1;  // class-tree whose level lives in xr_buf between its build and its finish (one at a time)
   int* xr_err = nullptr;
   int* xr_err_host = nullptr;  // pinned mirror of xr_err, refreshed after every exchange
@@ -282,8 +283,9 @@ int check(h2ot_engine* h) {
   } while (0)
 
 void xr_release(h2ot_engine* h);
+bool xr_park(h2ot_engine* h);
 int xr_rank_barrier(h2ot_engine* h);
-int xr_ensure(h2ot_engine* h, size_t words);
+int xr_ensure(h2ot_engine* h, size_t words, bool exact = false);
 int xr_allreduce(h2ot_engine* h, long long n_sums, long long n);
 
 int t_begin(h2ot_engine* h, double* acc) {
@@ -498,7 +500,7 @@ int h2ot_destroy(h2ot_engine* h) {
   if (!h) return H2OT_OK;
   cudaSetDevice(h->cfg.device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  xr_release(h);  // collective when peers have mapped the buffer: needs the communicator
+  if (!xr_park(h)) xr_release(h);  // (release is collective when peers have mapped the buffer: needs the communicator)
   if (h->nccl.comm && h->nccl.CommDestroy && !h->nccl.shared) h->nccl.CommDestroy(h->nccl.comm);
   h->ar_dev.release();
   if (h->ar_host) cudaFreeHost(h->ar_host);
@@ -1075,6 +1077,66 @@ int xr_rank_barrier(h2ot_engine* h) {
   return H2OT_OK;
 }
 
+// Mapping a peer's buffer is the slow part of a sharded model's start (cudaIpcOpenMemHandle: ~80 ms for 7 peers), and a process
+// that builds one model after another over the same communicator needs it once: an engine that is destroyed PARKS its exchange
+// buffer (allocation, peer mappings, epochs: the flags inside the buffer live on) under its communicator + device, and the next
+// engine on that communicator adopts it instead of allocating. Every rank parks and adopts at the same calls (the ranks run the
+// same sequence of models), so the decision is collective without a message. Parked buffers are freed when a larger one is needed
+// (collectively, xr_release) or with the process.
+struct XrParked {
+  unsigned long long* buf = nullptr;
+  size_t cap = 0;
+  XrPeers peers{};
+  void* opened[kXrMaxWorld] = {nullptr};
+  unsigned long long epoch = 0, ll_epoch = 0;
+  int* err = nullptr;
+  int* err_host = nullptr;
+};
+static std::map<std::string, XrParked> g_xr_parked;
+static std::mutex g_xr_mutex;
+
+bool xr_park(h2ot_engine* h) {
+  if (!h->xr_buf || h->nccl.world <= 1 || h->xr_key.empty() || !h->nccl.shared) return false;
+  if (h->xr_err_host && *h->xr_err_host) return false;  // an exchange timed out: the epochs of the ranks may disagree
+  std::lock_guard<std::mutex> lock(g_xr_mutex);
+  if (g_xr_parked.count(h->xr_key)) return false;  // (two engines alive on one communicator: the second one frees its own)
+  XrParked p;
+  p.buf = h->xr_buf;
+  p.cap = h->xr_cap;
+  p.peers = h->xr_peers;
+  for (int i = 0; i < kXrMaxWorld; i++) p.opened[i] = h->xr_opened[i];
+  p.epoch = h->xr_epoch;
+  p.ll_epoch = h->xr_ll_epoch;
+  p.err = h->xr_err;
+  p.err_host = h->xr_err_host;
+  g_xr_parked[h->xr_key] = p;
+  h->xr_buf = nullptr;
+  h->xr_cap = 0;
+  for (int i = 0; i < kXrMaxWorld; i++) h->xr_opened[i] = nullptr;
+  h->xr_err = nullptr;
+  h->xr_err_host = nullptr;
+  return true;
+}
+bool xr_adopt(h2ot_engine* h) {
+  if (h->xr_buf || h->xr_key.empty()) return false;
+  std::lock_guard<std::mutex> lock(g_xr_mutex);
+  auto it = g_xr_parked.find(h->xr_key);
+  if (it == g_xr_parked.end()) return false;
+  const XrParked& p = it->second;
+  h->xr_buf = p.buf;
+  h->xr_cap = p.cap;
+  h->xr_peers = p.peers;
+  for (int i = 0; i < kXrMaxWorld; i++) h->xr_opened[i] = p.opened[i];
+  h->xr_epoch = p.epoch;
+  h->xr_ll_epoch = p.ll_epoch;
+  if (h->xr_err) cudaFree(h->xr_err);
+  if (h->xr_err_host) cudaFreeHost(h->xr_err_host);
+  h->xr_err = p.err;
+  h->xr_err_host = p.err_host;
+  g_xr_parked.erase(it);
+  return true;
+}
+
 // Unmaps the peers' exchange buffers and frees this rank's. A buffer that other processes have mapped must not be freed
 // while a peer may still read it or still holds the mapping, so the release is collective: barrier (nobody reads any more),
 // close the imported handles, barrier (nobody holds a mapping of ours any more), free.
@@ -1098,8 +1160,10 @@ void xr_release(h2ot_engine* h) {
 // Makes sure the exchange buffer holds `words` 64-bit words per half. Growing is collective (every rank plans the same
 // level, so every rank grows at the same call): allocate, trade CUDA IPC handles over the NCCL communicator, map the peers.
 // H2OT_ERR_UNSUPPORTED: peer mapping is not possible here; the caller falls back to the NCCL collectives for good.
-int xr_ensure(h2ot_engine* h, size_t words) {
+int xr_ensure(h2ot_engine* h, size_t words, bool exact) {
   if (words <= h->xr_cap) return H2OT_OK;
+  if (xr_adopt(h) && words <= h->xr_cap) return H2OT_OK;  // (too small: released below like a buffer of this engine's own)
+  const auto t_start = std::chrono::steady_clock::now();
   const int W = h->nccl.world, R = h->nccl.rank;
   if (W > kXrMaxWorld || !h->nccl.AllGather) {
     h->xr_failed = true;
@@ -1108,7 +1172,8 @@ int xr_ensure(h2ot_engine* h, size_t words) {
   CUDA_TRY(cudaStreamSynchronize(h->stream));
   xr_release(h);  // collective: every rank grows at the same call, and nobody frees a buffer a peer still reads or maps
   // [in: cap][out: cap][flags: 64][reduce-scatter lines: 2 parities x cap lines x 2 words][all-gather lines: the same]
-  const size_t cap = std::max<size_t>((words * 2 + 63) & ~(size_t)63, 1 << 16);
+  // (a caller that reserves the model's largest level asks for exactly that; growth on demand doubles)
+  const size_t cap = std::max<size_t>(((exact ? words + words / 8 : words * 2) + 63) & ~(size_t)63, 1 << 16);
   const size_t total = (10 * cap + 64) * sizeof(unsigned long long);
   CUDA_TRY(cudaMalloc(&h->xr_buf, total));
   CUDA_TRY(cudaMemset(h->xr_buf, 0, total));
@@ -1162,6 +1227,9 @@ int xr_ensure(h2ot_engine* h, size_t words) {
     return H2OT_ERR_UNSUPPORTED;
   }
   h->xr_cap = cap;
+  if (getenv("H2OT_TRACE_XR"))
+    fprintf(stderr, "[h2ot xr] rank %d: exchange buffer %.1f MB mapped from %d peers in %.1f ms\n", R, total / 1e6, W - 1,
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
   return H2OT_OK;
 }
 
@@ -2755,6 +2823,7 @@ int h2ot_comm_init(h2ot_engine* h, int32_t world_size, int32_t rank, const uint8
   std::lock_guard<std::mutex> lock(g_comm_mutex);
   const std::string key(reinterpret_cast<const char*>(id), H2OT_COMM_ID_BYTES);
   auto it = g_comms.find(key + ":" + std::to_string(h->cfg.device));
+  h->xr_key = key + ":" + std::to_string(h->cfg.device);
   {
     const char* e = getenv("H2OT_XREDUCE");
     h->xr_enabled = !(e && e[0] == '0');
@@ -2801,7 +2870,7 @@ int h2ot_reserve_exchange(h2ot_engine* h, int64_t max_level_bins, int64_t max_le
   CHECK_ENGINE(h);
   if (max_level_bins < 0 || max_level_pairs < 0 || max_leaves < 0) H2OT_FAIL(H2OT_ERR_INVALID, "negative sizes");
   if (!(h->xr_enabled && !h->xr_failed && h->nccl.world > 1)) return H2OT_OK;
-  const int rc = xr_ensure(h, (size_t)max_level_bins * 3 + (size_t)max_leaves + (size_t)max_level_pairs * 2);
+  const int rc = xr_ensure(h, (size_t)max_level_bins * 3 + (size_t)max_leaves + (size_t)max_level_pairs * 2, true);
   return rc == H2OT_ERR_UNSUPPORTED ? H2OT_OK : rc;  // no peer mapping here: the NCCL collectives serve the build
 }
 
