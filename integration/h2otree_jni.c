@@ -257,3 +257,67 @@ FN(getOobt)(JNIEnv* env, jclass cls, jlong h, jdoubleArray out) {
   UNPIN_D(v, out, 0);
   throw_if(env, rc);
 }
+
+/* ---- round 2: a whole tree per call, trees in a pipeline, sharded builds */
+FN(treeLevelsBegin)(JNIEnv* env, jclass cls, jlong h, jint k, jint maxDepth, jobject rootDescs, jdouble minRows, jdouble minSplitImprovement,
+                    jint nbins, jint nbinsCats) {
+  throw_if(env, h2ot_tree_levels_begin(H(h), k, maxDepth, (const h2ot_hist_desc*)buf(env, rootDescs), minRows, minSplitImprovement, nbins,
+                                       nbinsCats));
+}
+/* outSplits / outExists / outLeafPred: direct buffers of 2^D - 1 h2ot_split, 2^(D+1) - 1 bytes, 2^(D+1) - 1 floats (the last nullable) */
+FN(treeLevelsEnd)(JNIEnv* env, jclass cls, jlong h, jint k, jobject outSplits, jobject outExists, jobject outLeafPred) {
+  throw_if(env, h2ot_tree_levels_end2(H(h), k, (h2ot_split*)buf(env, outSplits), (uint8_t*)buf(env, outExists), (float*)buf(env, outLeafPred)));
+}
+FN(treeFinishEnqueue)(JNIEnv* env, jclass cls, jlong h, jint k, jdouble rate, jdouble maxAbsLeafnodePred) {
+  throw_if(env, h2ot_tree_finish_enqueue(H(h), k, rate, maxAbsLeafnodePred));
+}
+FN(computeResidualsAsync)(JNIEnv* env, jclass cls, jlong h) { throw_if(env, h2ot_compute_residuals_async(H(h))); }
+FN(setGammaBounds)(JNIEnv* env, jclass cls, jlong h, jdouble numBound, jdouble denomBound) {
+  const double b[2] = {numBound, denomBound};
+  throw_if(env, h2ot_set_gamma_bounds(H(h), b));
+}
+FN(addTreeScaled)(JNIEnv* env, jclass cls, jlong h, jint k, jfloatArray nodePred, jdoubleArray nodeFactor) {
+  const jsize n = (*env)->GetArrayLength(env, nodePred);
+  PIN_F(v, nodePred);
+  jdouble* f = (*env)->GetDoubleArrayElements(env, nodeFactor, NULL);
+  const int rc = f ? h2ot_add_tree_scaled(H(h), k, n, v, f) : H2OT_ERR_INVALID;
+  if (f) (*env)->ReleaseDoubleArrayElements(env, nodeFactor, f, JNI_ABORT);
+  UNPIN_F(v, nodePred, JNI_ABORT);
+  throw_if(env, rc);
+}
+FN(setSampleRatePerClass)(JNIEnv* env, jclass cls, jlong h, jdoubleArray rates) {
+  const jsize n = rates ? (*env)->GetArrayLength(env, rates) : 0;
+  PIN_D(v, rates);
+  const int rc = h2ot_set_sample_rate_per_class(H(h), v, n);
+  UNPIN_D(v, rates, JNI_ABORT);
+  throw_if(env, rc);
+}
+/* out: direct buffer of maxChunks * H2OT_AUC_STRIDE doubles; returns {nChunks, chunkRows} through outInfo[2] */
+FN(aucBuilders)(JNIEnv* env, jclass cls, jlong h, jint maxChunks, jlongArray outInfo, jobject out) {
+  int32_t n_chunks = 0;
+  int64_t chunk_rows = 0;
+  const int rc = h2ot_auc_builders(H(h), maxChunks, &n_chunks, &chunk_rows, (double*)buf(env, out));
+  if (rc == H2OT_OK && outInfo) {
+    const jlong info[2] = {n_chunks, chunk_rows};
+    (*env)->SetLongArrayRegion(env, outInfo, 0, 2, info);
+  }
+  throw_if(env, rc);
+}
+FN(setLazySync)(JNIEnv* env, jclass cls, jlong h, jboolean on) { throw_if(env, h2ot_set_lazy_sync(H(h), on ? 1 : 0)); }
+FN(setTimers)(JNIEnv* env, jclass cls, jlong h, jint mode) { throw_if(env, h2ot_set_timers(H(h), mode)); }
+FN(reserveExchange)(JNIEnv* env, jclass cls, jlong h, jlong maxLevelBins, jlong maxLevelPairs, jlong maxLeaves) {
+  throw_if(env, h2ot_reserve_exchange(H(h), maxLevelBins, maxLevelPairs, maxLeaves));
+}
+/* id: byte[H2OT_COMM_ID_BYTES], made on one node with commUniqueId and sent to the others (e.g. through the DKV) */
+FN(commUniqueId)(JNIEnv* env, jclass cls, jbyteArray outId) {
+  uint8_t id[H2OT_COMM_ID_BYTES];
+  const int rc = h2ot_comm_unique_id(id);
+  if (rc == H2OT_OK) (*env)->SetByteArrayRegion(env, outId, 0, H2OT_COMM_ID_BYTES, (const jbyte*)id);
+  throw_if(env, rc);
+}
+FN(commInit)(JNIEnv* env, jclass cls, jlong h, jint worldSize, jint rank, jbyteArray id) {
+  PIN_B(v, id);
+  const int rc = h2ot_comm_init(H(h), worldSize, rank, (const uint8_t*)v);
+  UNPIN_B(v, id, JNI_ABORT);
+  throw_if(env, rc);
+}

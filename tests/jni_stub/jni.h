@@ -40,5 +40,7 @@ struct JNINativeInterface_ {
   void (*ReleaseFloatArrayElements)(JNIEnv*, jfloatArray, jfloat*, jint);
   void (*ReleaseDoubleArrayElements)(JNIEnv*, jdoubleArray, jdouble*, jint);
   void (*SetDoubleArrayRegion)(JNIEnv*, jdoubleArray, jsize, jsize, const jdouble*);
+  void (*SetLongArrayRegion)(JNIEnv*, jlongArray, jsize, jsize, const jlong*);
+  void (*SetByteArrayRegion)(JNIEnv*, jbyteArray, jsize, jsize, const jbyte*);
 };
 #endif
