@@ -104,7 +104,7 @@ class GbmTiming(C.Structure):
 
 # every symbol declared in include/h2ot.h and include/h2ot_gbm.h (tests check that the library exports all of them)
 ENGINE_SYMBOLS = [
-    "h2ot_tree_finish_enqueue", "h2ot_tree_levels_end2", "h2ot_compute_residuals_async",
+    "h2ot_tree_finish_enqueue", "h2ot_tree_levels_end2", "h2ot_compute_residuals_async", "h2ot_residual_bounds_wait",
     "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",

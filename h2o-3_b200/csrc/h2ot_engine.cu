@@ -232,6 +232,9 @@ struct h2ot_engine {
   bool defer_sync = false;
   bool timer_open = false;
   int timer_mode = 2;  // h2ot_set_timers
+  unsigned int* bounds_host = nullptr;  // pinned: residual maxima of h2ot_compute_residuals_async
+  cudaEvent_t bounds_ev = nullptr;
+  bool bounds_pending = false;
   bool in_tree_loop = false;  // inside h2ot_tree_levels_begin: per-level housekeeping copies are done once per tree
   bool lazy_sync = false;          // h2ot_set_lazy_sync: calls that return nothing to the host do not wait for the stream
   std::vector<double> rate_per_class;  // Sample's _rate_per_class (empty: null)
@@ -517,6 +520,8 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->oobt) cudaFree(h->oobt);
   if (h->xr_err) cudaFree(h->xr_err);
   if (h->xr_err_host) cudaFreeHost(h->xr_err_host);
+  if (h->bounds_host) cudaFreeHost(h->bounds_host);
+  if (h->bounds_ev) cudaEventDestroy(h->bounds_ev);
   for (TreeState& t : h->ts) {
     if (t.F) cudaFree(t.F);
     if (t.work) cudaFree(t.work);
@@ -2556,9 +2561,11 @@ int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_
   return H2OT_OK;
 }
 
-// ComputePredAndRes without the read-back of max |residual|: for callers that know a bound (bernoulli and multinomial residuals
-// lie in [-1, 1]) and pass it to h2ot_begin_tree / h2ot_set_gamma_bounds themselves. Nothing synchronises.
-int h2ot_compute_residuals_async(h2ot_engine* h) {
+// ComputePredAndRes without waiting for max |residual|: for callers that know a bound (bernoulli and multinomial residuals lie in
+// [-1, 1]) or can derive one from an EARLIER tree's maxima (gaussian: |r'| <= (1 + learn_rate) max |r|). want_bounds != 0: the
+// maxima are all-reduced over the communicator on the stream and copied to pinned memory behind the kernel;
+// h2ot_residual_bounds_wait blocks until that copy -- not the rest of the stream -- is done. Nothing synchronises here.
+int h2ot_compute_residuals_async(h2ot_engine* h, int32_t want_bounds) {
   CHECK_ENGINE(h);
   if (!h->frame_final) H2OT_FAIL(H2OT_ERR_INVALID, "frame not finalized");
   CUDA_TRY(cudaMemsetAsync(h->d_absmax.p, 0, (h->K + 2) * sizeof(unsigned int), h->stream));
@@ -2567,7 +2574,33 @@ int h2ot_compute_residuals_async(h2ot_engine* h) {
   residuals_kernel<<<grid_for(h, h->n, 256), 256, 0, h->stream>>>(a);
   h->stats.launches++;
   TRY(t_end(h));
+  if (want_bounds) {
+    if (!h->bounds_host) CUDA_TRY(cudaMallocHost(&h->bounds_host, 64 * sizeof(unsigned int)));
+    if (h->K + 2 > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_compute_residuals_async: more than 62 class-trees");
+    if (!h->bounds_ev) CUDA_TRY(cudaEventCreateWithFlags(&h->bounds_ev, cudaEventDisableTiming));
+    // (positive floats order like their bit patterns: an unsigned max over the ranks is the max of the values)
+    if (h->nccl.world > 1 && h->nccl.comm)
+      TRY(nccl_check(h, h->nccl.AllReduce(h->d_absmax.p, h->d_absmax.p, (size_t)h->K + 2, /*ncclUint32*/ 3, /*ncclMax*/ 2, h->nccl.comm, h->stream),
+                     "ncclAllReduce(residual bounds)"));
+    TRY(d2h(h, h->bounds_host, h->d_absmax.p, (h->K + 2) * sizeof(unsigned int)));
+    CUDA_TRY(cudaEventRecord(h->bounds_ev, h->stream));
+    h->bounds_pending = true;
+  }
   CUDA_TRY(cudaGetLastError());
+  return H2OT_OK;
+}
+int h2ot_residual_bounds_wait(h2ot_engine* h, double* out_abs_max, double out_gamma_bounds[2]) {
+  CHECK_ENGINE(h);
+  if (!h->bounds_pending) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_residual_bounds_wait without h2ot_compute_residuals_async(want_bounds)");
+  CUDA_TRY(cudaEventSynchronize(h->bounds_ev));
+  h->bounds_pending = false;
+  for (int i = 0; i < h->K + 2; i++) {
+    float f;
+    memcpy(&f, &h->bounds_host[i], 4);
+    if (i < h->K) {
+      if (out_abs_max) out_abs_max[i] = (double)f;
+    } else if (out_gamma_bounds) out_gamma_bounds[i - h->K] = f > 0 ? (double)f : 1.0;
+  }
   return H2OT_OK;
 }
 

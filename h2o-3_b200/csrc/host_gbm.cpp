@@ -353,6 +353,10 @@ struct h2ot_gbm {
     std::vector<int> ncol_active;
   };
   std::deque<PendingIter> pending;
+  // gaussian: the fixed-point bound of a tree's residuals follows from the PREVIOUS tree's measured maximum (see residual_bound)
+  double y_abs_max = 0;      // max |response| over all rows
+  double prev_absmax = -1;   // max |Work| measured at the previous iteration (-1: none yet)
+  double prev_lr = 0;        // that iteration's effective learn rate
 };
 
 namespace {
@@ -830,8 +834,19 @@ double noise_factor(const h2ot_gbm* g, int k, int nid) {
 bool use_pipeline(const h2ot_gbm* g) {
   const char* e = getenv("H2OT_PIPELINE");
   const bool off = e != nullptr && atoi(e) == 0;
-  return !off && use_device_loop(g) && (g->p.family == H2OT_FAMILY_BERNOULLI || g->p.family == H2OT_FAMILY_MULTINOMIAL) &&
-         g->pred_noise_bandwidth == 0;
+  const int f = g->p.family;
+  return !off && use_device_loop(g) && g->pred_noise_bandwidth == 0 &&
+         (f == H2OT_FAMILY_BERNOULLI || f == H2OT_FAMILY_MULTINOMIAL || (f == H2OT_FAMILY_GAUSSIAN && !g->has_off));
+}
+
+// Gaussian residual bound for the fixed-point scale of iteration t, known before iteration t's residuals have been looked at:
+// a leaf's value is a weighted mean of its rows' residuals, |gamma| <= max |r|, so after adding learn_rate x gamma every residual
+// obeys |r'| <= (1 + learn_rate) max |r|; F is rounded to float once per tree, which moves a residual by at most 2^-24 |F| and
+// |F| <= max |y| + max |r|. The first iteration uses its own measured maximum. Both the pipelined and the tree-at-a-time build
+// take their scale from here, so they accumulate the same integers.
+double residual_bound(const h2ot_gbm* g, double measured_now) {
+  if (g->prev_absmax < 0) return measured_now;
+  return (1.0 + g->prev_lr) * g->prev_absmax + std::ldexp(g->y_abs_max + g->prev_absmax, -23);
 }
 
 int mirror_oldest_iteration(h2ot_gbm* g) {
@@ -863,9 +878,22 @@ int flush_pending(h2ot_gbm* g) {
 int build_next_k_trees_pipelined(h2ot_gbm* g) {
   const int K = g->K;
   const double t0 = now_s();
-  GTRY(h2ot_compute_residuals_async(g->eng));
-  const double gb[2] = {1.0, 0.25};  // |w z| / w <= 1, p (1 - p) <= 1/4
-  GTRY(h2ot_set_gamma_bounds(g->eng, gb));
+  const bool gaussian = g->p.family == H2OT_FAMILY_GAUSSIAN;
+  const double eff_lr_now = g->p.learn_rate * std::pow(g->p.learn_rate_annealing, (double)(g->ntrees_built - 1));
+  GTRY(h2ot_compute_residuals_async(g->eng, gaussian ? 1 : 0));
+  double bound = 1.0, a_now = -1;
+  if (gaussian) {
+    // the maximum of THIS iteration's residuals is fetched after the tree has been enqueued (it serves the next iteration);
+    // only the very first iteration has to wait for its own
+    if (g->prev_absmax < 0) GTRY(h2ot_residual_bounds_wait(g->eng, &a_now, nullptr));
+    bound = residual_bound(g, a_now);
+    if (!(bound > 0)) bound = 1.0;
+    const double gb[2] = {bound, 1.0};  // |w z| / w <= bound, w / w = 1
+    GTRY(h2ot_set_gamma_bounds(g->eng, gb));
+  } else {
+    const double gb[2] = {1.0, 0.25};  // |w z| / w <= 1, p (1 - p) <= 1/4
+    GTRY(h2ot_set_gamma_bounds(g->eng, gb));
+  }
   h2ot_gbm::PendingIter it;
   it.kt.resize((size_t)K);
   const int adj_nbins = std::max(g->p.nbins_top_level, g->p.nbins);
@@ -873,7 +901,7 @@ int build_next_k_trees_pipelined(h2ot_gbm* g) {
   for (int k = 0; k < K; k++) {
     it.kt[k] = std::make_unique<Tree>(g->ncols, g->mtry, g->mtry_per_tree, rseed, g->p.col_sample_rate_change_per_level);
     it.kt[k]->new_undecided(kNoParent, initial_hist(g, adj_nbins, rseed, false));
-    GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, 1.0));
+    GTRY(h2ot_begin_tree(g->eng, k, rseed, g->p.sample_rate, bound));
   }
   GTRY(enqueue_levels_on_device(g, it.kt, it.ncol_active));
   const double m1class = (g->nclass > 1 && g->p.family == H2OT_FAMILY_MULTINOMIAL) ? (double)(g->nclass - 1) / g->nclass : 1.0;
@@ -881,6 +909,11 @@ int build_next_k_trees_pipelined(h2ot_gbm* g) {
   for (int k = 0; k < K; k++) GTRY(h2ot_tree_finish_enqueue(g->eng, k, eff_lr * m1class, g->p.max_abs_leafnode_pred));
   g->pending.push_back(std::move(it));
   g->ntrees_built++;
+  if (gaussian) {  // (returns once the previous tree and this iteration's residual kernel are done: where the mirror below waits anyway)
+    if (a_now < 0) GTRY(h2ot_residual_bounds_wait(g->eng, &a_now, nullptr));
+    g->prev_absmax = a_now;
+    g->prev_lr = eff_lr_now;
+  }
   const double t1 = now_s();
   g->timing.level_s += t1 - t0;
   while (g->pending.size() > 1) GTRY(mirror_oldest_iteration(g));
@@ -905,6 +938,16 @@ int build_next_k_trees(h2ot_gbm* g) {
   } else {
     GTRY(h2ot_get_gamma_bounds(g->eng, absmax.data() + K));
     GTRY(allreduce(g, absmax.data(), K + 2, 1));
+    if (g->p.family == H2OT_FAMILY_GAUSSIAN && !g->has_off && g->p.algo == H2OT_ALGO_GBM) {
+      // the scale the pipelined build would use for this tree (residual_bound): same integers, same bits
+      const double a_now = absmax[0];
+      const double b = residual_bound(g, a_now);
+      absmax[0] = b > 0 ? b : 1.0;
+      absmax[K] = absmax[0];
+      absmax[K + 1] = 1.0;
+      g->prev_absmax = a_now;
+      g->prev_lr = g->p.learn_rate * std::pow(g->p.learn_rate_annealing, (double)(g->ntrees_built - 1));
+    }
   }
   GTRY(h2ot_set_gamma_bounds(g->eng, absmax.data() + K));
   std::vector<std::unique_ptr<Tree>> kt(K);
@@ -1290,9 +1333,10 @@ int h2ot_gbm_init(h2ot_gbm* g) {
     double ymax = 0;
     GTRY(h2ot_initial_stats(g->eng, &nd[0], &nd[1], (drf && g->nclass > 1) ? cls.data() : nullptr, &ymax));
     GTRY(allreduce(g, nd, 2, 0));
+    GTRY(allreduce(g, &ymax, 1, 1));
+    g->y_abs_max = ymax;
     if (drf) {
       GTRY(allreduce(g, cls.data(), (int64_t)g->nclass, 0));
-      GTRY(allreduce(g, &ymax, 1, 1));
       g->prior_class_dist.assign(std::max(1, g->nclass), 0.0);
       double tot = 0;
       for (int c = 0; c < g->nclass; c++) tot += cls[c];

@@ -301,11 +301,15 @@ int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint
  * h2ot_compute_residuals_async / h2ot_begin_tree / h2ot_tree_levels_begin may be enqueued before this tree is ended: up to TWO trees
  * per class-tree may be in flight, _end returns the oldest. h2ot_tree_levels_end2 also returns the leaf values,
  * out_leaf_pred[2^(max_depth+1) - 1] indexed by the child's slot (0 where the slot is no leaf).
- * h2ot_compute_residuals_async is h2ot_compute_residuals without the read-back of max |residual|: the caller passes a bound it
- * knows to h2ot_begin_tree (|y - p| <= 1 for bernoulli and multinomial) and to h2ot_set_gamma_bounds. */
+ * h2ot_compute_residuals_async is h2ot_compute_residuals without waiting for max |residual|: the caller passes a bound it knows
+ * to h2ot_begin_tree and h2ot_set_gamma_bounds -- |y - p| <= 1 for bernoulli and multinomial; for gaussian a bound derived from an
+ * EARLIER tree's maxima (a leaf's value is a weighted mean of its residuals, so |r'| <= (1 + learn_rate) max |r|). With
+ * want_bounds != 0 the maxima (all-reduced over the communicator) are copied to pinned memory behind the kernel and
+ * h2ot_residual_bounds_wait returns them, waiting for that copy only: out_abs_max[K], out_gamma_bounds[2] (both nullable). */
 int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_abs_leafnode_pred);
 int h2ot_tree_levels_end2(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists, float* out_leaf_pred);
-int h2ot_compute_residuals_async(h2ot_engine* h);
+int h2ot_compute_residuals_async(h2ot_engine* h, int32_t want_bounds);
+int h2ot_residual_bounds_wait(h2ot_engine* h, double* out_abs_max, double out_gamma_bounds[2]);
 
 /* ---- end of tree */
 /* Uploads the finished tree's DecidedNodes (children now pointing at LeafNodes; T/gbm/GBM.java:655-679). */

@@ -271,7 +271,18 @@ FN(treeLevelsEnd)(JNIEnv* env, jclass cls, jlong h, jint k, jobject outSplits, j
 FN(treeFinishEnqueue)(JNIEnv* env, jclass cls, jlong h, jint k, jdouble rate, jdouble maxAbsLeafnodePred) {
   throw_if(env, h2ot_tree_finish_enqueue(H(h), k, rate, maxAbsLeafnodePred));
 }
-FN(computeResidualsAsync)(JNIEnv* env, jclass cls, jlong h) { throw_if(env, h2ot_compute_residuals_async(H(h))); }
+FN(computeResidualsAsync)(JNIEnv* env, jclass cls, jlong h, jboolean wantBounds) {
+  throw_if(env, h2ot_compute_residuals_async(H(h), wantBounds ? 1 : 0));
+}
+/* outAbsMax[K] and outGammaBounds[2] (both nullable) */
+FN(residualBoundsWait)(JNIEnv* env, jclass cls, jlong h, jdoubleArray outAbsMax, jdoubleArray outGammaBounds) {
+  PIN_D(a, outAbsMax);
+  jdouble* b = outGammaBounds ? (*env)->GetDoubleArrayElements(env, outGammaBounds, NULL) : NULL;
+  const int rc = h2ot_residual_bounds_wait(H(h), a, b);
+  if (b) (*env)->ReleaseDoubleArrayElements(env, outGammaBounds, b, 0);
+  UNPIN_D(a, outAbsMax, 0);
+  throw_if(env, rc);
+}
 FN(setGammaBounds)(JNIEnv* env, jclass cls, jlong h, jdouble numBound, jdouble denomBound) {
   const double b[2] = {numBound, denomBound};
   throw_if(env, h2ot_set_gamma_bounds(H(h), b));

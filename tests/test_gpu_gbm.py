@@ -433,7 +433,7 @@ def test_device_auc2_matches_the_streaming_builder():
         gm.close()
 
 
-@pytest.mark.parametrize("case", ["bernoulli+cats+sampling", "gaussian+weights+offset", "multinomial", "deep+min_rows"])
+@pytest.mark.parametrize("case", ["bernoulli+cats+sampling", "gaussian+weights+offset", "gaussian+weights", "multinomial", "deep+min_rows"])
 def test_device_level_loop_grows_the_same_trees_as_the_host_loop(case, monkeypatch):
     """h2ot_tree_levels_begin / _end: all levels of a tree enqueued back to back, with the DecidedNode constructor and
     Split.nextLevelHistos (T/DTree.java:312-417, 703-726) on the device, against the level-by-level loop that does them on the host
@@ -444,12 +444,14 @@ def test_device_level_loop_grows_the_same_trees_as_the_host_loop(case, monkeypat
     kw = dict(ntrees=5, max_depth=6, nbins=20, seed=31)
     if case == "bernoulli+cats+sampling":
         kw.update(sample_rate=0.7, nbins_cats=8)
-    elif case == "gaussian+weights+offset":
+    elif case.startswith("gaussian"):
+        # (without an offset gaussian trees are pipelined too: their fixed-point scale comes from the previous tree's residuals)
         rng = np.random.default_rng(2)
         y = (np.nan_to_num(X[:, 0]) * 2 + np.nan_to_num(X[:, 2]) ** 2 + rng.normal(size=len(X))).astype(np.float32).astype(np.float64)
         w = rng.integers(0, 3, len(X)).astype(np.float64)
-        off = (rng.random(len(X)) * 0.1).astype(np.float32).astype(np.float64)
-        kw.update(distribution="gaussian", nclass=1, nbins=32)
+        if case.endswith("offset"):
+            off = (rng.random(len(X)) * 0.1).astype(np.float32).astype(np.float64)
+        kw.update(distribution="gaussian", nclass=1, nbins=32, ntrees=8)
     elif case == "multinomial":
         # (noisy classes: with y a pure function of the features whole children become pure, their squared error is cancellation
         # noise around 0, and DTree's `se <= 1e-30` test -- T/DTree.java:330 -- falls either way: a near-tie of the engine's exact
@@ -500,4 +502,59 @@ def test_sample_rate_per_class_and_pred_noise_bandwidth(capture):
     g0, _ = _run_both(X, y, cats, capture=False, ntrees=5, max_depth=5, nbins=20, seed=77, sample_rate_per_class=[0.4, 0.9])
     assert not np.array_equal(g0.predictions(), gm.predictions())
     g0.close()
+    gm.close()
+
+
+@pytest.mark.parametrize("dist_kw", [dict(distribution="bernoulli"), dict(distribution="multinomial", nclass=3)])
+def test_pipelined_build_one_iteration_at_a_time_with_accessors_in_between(dist_kw, monkeypatch):
+    """h2ot_gbm_train may return with the last iteration still on the device (pipelined bernoulli / multinomial builds): every
+    accessor has to wait for it and see a complete model. One iteration per call with reads in between must give the bytes of a
+    build that synchronises after every tree (H2OT_PIPELINE=0)."""
+    P = h2ot_lib.pkg()
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=5)
+    K = 1
+    if dist_kw["distribution"] == "multinomial":
+        y = np.argmax(np.nan_to_num(X[:, :3]) + 0.5 * np.random.default_rng(3).normal(size=(len(X), 3)), axis=1).astype(np.float64)
+        K = 3
+    kw = dict(ntrees=6, max_depth=5, nbins=20, seed=99, sample_rate=0.8, **dist_kw)
+    out = []
+    for pipe in ("0", "1"):
+        monkeypatch.setenv("H2OT_PIPELINE", pipe)
+        gm = P.GBM(**kw).load([X[:, c] for c in range(X.shape[1])], y, categorical=cats)
+        seen = []
+        for it in range(6):
+            gm.train(1)
+            if it % 2 == 0:
+                assert gm.ntrees == it + 1                     # waits for the tree in flight
+                seen.append(gm.predictions(0).copy())           # and sees its contribution
+            if it == 3:
+                assert len(gm.tree(3, K - 1)[0]) >= 1
+        gm.flush()
+        sc = gm.score()
+        out.append(([bytes(gm.tree(t, k)[0]) for t in range(6) for k in range(K)], [gm.predictions(k).tobytes() for k in range(K)],
+                    gm.varimp().tobytes(), [s.tobytes() for s in seen], sc))
+        gm.close()
+    assert out[0][0] == out[1][0], "pipelined trees differ from the tree-at-a-time build"
+    assert out[0][1] == out[1][1] and out[0][2] == out[1][2] and out[0][3] == out[1][3]
+    assert out[0][4] == out[1][4]
+
+
+def test_timer_modes():
+    """h2ot_set_timers: the model builder times the histogram launches only (mode 1); mode 2 times every stage; mode 0 none."""
+    P = h2ot_lib.pkg()
+    X, y, cats = h2ot_lib.make_frame(n=20000, c=5, seed=8)
+    gm = P.GBM(ntrees=6, max_depth=4, nbins=20, seed=1).load([X[:, c] for c in range(X.shape[1])], y, categorical=cats)
+    gm.train(2)
+    e = gm.engine()
+    s = e.stats()
+    # (one histogram launch per level and storage type of the frame's columns)
+    assert s.ms_hist > 0 and s.hist_launches >= 2 * 4 and s.ms_score == 0 and s.ms_split == 0 and s.ms_gamma == 0
+    e.set_timers(2)
+    gm.train(2)
+    s2 = gm.engine().stats()
+    assert s2.ms_score > 0 and s2.ms_split > 0 and s2.ms_gamma > 0 and s2.ms_hist > s.ms_hist
+    e.set_timers(0)
+    gm.train(2)
+    s3 = gm.engine().stats()
+    assert s3.ms_hist == s2.ms_hist and s3.hist_launches == 3 * s.hist_launches and s3.launches > s2.launches
     gm.close()

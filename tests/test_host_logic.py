@@ -4,6 +4,7 @@ column draws. (Everything else the driver does needs the engine and is covered b
 import ctypes as C
 
 import numpy as np
+import pytest
 
 import h2ot_lib
 import oracle_lib as O
@@ -65,3 +66,54 @@ def test_per_node_column_draws_match_oracle():
                                     a.ctypes.data_as(C.c_void_p), an.ctypes.data_as(C.c_void_p))
         O.lib().orc_tree_score_cols(ncols, mtry, mpt, 987654321, change, depth, O.ptr(present), n_nodes, O.ptr(b), O.ptr(bn))
         assert np.array_equal(an, bn) and np.array_equal(a, b), (ncols, mtry, mpt)
+
+
+@pytest.mark.parametrize("world,n,n_sums", [(2, 11, 7), (3, 100, 64), (8, 8, 8), (8, 86_101, 86_000), (5, 1000, 0), (16, 4099, 4099)])
+def test_pushed_line_exchange_layout(world, n, n_sums):
+    """The slot arithmetic of xr_ll_kernel (csrc/k_xreduce.cuh), restated: word i belongs to owner o(i) = the slice [n p / W, n (p+1) / W)
+    it falls in; rank r pushes it to the owner's reduce-scatter area at line r * ceil(n / W) + (i - lo(o)); the owner publishes the
+    reduced word at line i of every peer's all-gather area. No two writers may share a line, every line read must have been
+    written, everything must fit the area (n + W lines), and the result must be the sum (words < n_sums) / max (the rest) over ranks."""
+    rng = np.random.default_rng(world * 1000 + n)
+    data = rng.integers(0, 1 << 40, size=(world, n), dtype=np.uint64)
+    lo = [n * p // world for p in range(world + 1)]
+    sl = (n + world - 1) // world
+    cap_lines = n + world
+    rs = [dict() for _ in range(world)]   # per owner: line -> value
+    ag = [dict() for _ in range(world)]   # per reader: line -> value
+    owner = np.searchsorted(np.array(lo[1:world]), np.arange(n), side="right")  # sum over q of (i >= lo[q]), as the kernel counts
+    for i in range(n):
+        assert lo[owner[i]] <= i < lo[owner[i] + 1]
+    # A: push
+    for r in range(world):
+        for i in range(n):
+            o = int(owner[i])
+            if o == r:
+                continue
+            line = r * sl + (i - lo[o])
+            assert 0 <= line < cap_lines
+            assert line not in rs[o], "two senders share a reduce-scatter line"
+            rs[o][line] = data[r, i]
+    # B: reduce + publish
+    out = [data[r].copy() for r in range(world)]
+    for r in range(world):
+        for i in range(lo[r], lo[r + 1]):
+            acc = int(data[r, i])
+            for p in range(world):
+                if p == r:
+                    continue
+                v = int(rs[r][p * sl + (i - lo[r])])
+                acc = (acc + v) & 0xFFFFFFFFFFFFFFFF if i < n_sums else max(acc, v)
+            out[r][i] = acc
+            for p in range(world):
+                if p != r:
+                    assert i < cap_lines and i not in ag[p]
+                    ag[p][i] = acc
+    # C: gather
+    for r in range(world):
+        for i in range(n):
+            if not (lo[r] <= i < lo[r + 1]):
+                out[r][i] = ag[r][i]
+    want = np.where(np.arange(n) < n_sums, data.sum(axis=0, dtype=np.uint64), data.max(axis=0))
+    for r in range(world):
+        assert np.array_equal(out[r], want), r
