@@ -827,10 +827,10 @@ double noise_factor(const h2ot_gbm* g, int k, int nid) {
 
 // ---- trees in a pipeline: the device runs an iteration start to finish (residuals, levels, leaf insertion, GammaPass, leaf values,
 // AddTreeContributions) with nothing waiting on the host, and the host mirrors iteration t while the device builds t + 1.
-// What lets the host step aside: static node ids (the device loop), residual bounds known in advance (|y - p| <= 1), leaf values
-// that need no transcendental (gaussian's bound is data dependent, so it keeps the synchronous path; poisson / gamma / tweedie take
-// a log), no per-node random numbers (pred_noise_bandwidth seeds by H2O node id). H2OT_PIPELINE=0 switches it off; the trees are
-// the same either way.
+// What lets the host step aside: static node ids (the device loop), residual bounds known before the residuals are (|y - p| <= 1;
+// gaussian: residual_bound below, from the previous tree's maximum), leaf values that need no transcendental (poisson / gamma /
+// tweedie take a log), no per-node random numbers (pred_noise_bandwidth seeds by H2O node id). H2OT_PIPELINE=0 switches it off;
+// the trees are the same either way.
 bool use_pipeline(const h2ot_gbm* g) {
   const char* e = getenv("H2OT_PIPELINE");
   const bool off = e != nullptr && atoi(e) == 0;
