@@ -196,7 +196,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                       "-lms", "10"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", os.environ.get("H2OT_BENCH_CLOCK_MS", "10")], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
