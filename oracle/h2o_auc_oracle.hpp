@@ -5,8 +5,11 @@
 //   AUC_Impl (one builder per chunk, reduced pairwise)   h2o-core/src/main/java/hex/AUC2.java:341-353
 // The builder is order dependent by construction (a streaming 400-bin histogram merged greedily), so a result is defined by the
 // chunking: `aucOverChunks` builds one AUCBuilder per chunk of consecutive rows, in row order, and folds the builders left to
-// right. Parity status: AUC2Test's vectors need the JVM-side Vec plumbing; the restatement is pinned by source and by the exact
-// AUC of small inputs (with at most NBINS distinct predictions the builder never merges and the trapezoid sum is the exact AUC).
+// right. Parity status: pinned by the reference's fixture-free known answer AUCBuilderTest.testPerRow (a 10-bin builder's
+// thresholds after 100 rows: the merge path), by the inputs of AUC2Test.perfectAUC (exact AUCs: with at most NBINS distinct
+// predictions the builder never merges and the trapezoid sum is the exact AUC), and by source (tests/test_oracle_compress_auc.py).
+// AUCBuilderTest.testPerRow_compat (fast path == insert + mergeOneBin after every row of h2o-core/src/test/resources/hex/
+// aucbuilder.csv.gz, 240 618 rows) is re-run against this restatement where the reference tree is present.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -18,6 +21,7 @@ namespace h2o_oracle {
 struct AUCBuilder {
   static constexpr int NBINS = 400;  // AUC2.java:36
   int _nBins, _n = 0, _ssx = -1;
+  bool _useFastPath = true;  // :372-373, 385: false only in AUCBuilderTest.testPerRow_compat (insert, then mergeOneBin, every time)
   std::vector<double> _ths, _sqe, _tps, _fps;
   explicit AUCBuilder(int nBins = NBINS) : _nBins(nBins), _ths(2 * nBins, 0.0), _sqe(2 * nBins, 0.0), _tps(2 * nBins, 0.0), _fps(2 * nBins, 0.0) {}
 
@@ -106,7 +110,7 @@ struct AUCBuilder {
       return;
     }
     idx = -idx - 1;
-    if (_n == _nBins && idx > 0 && idx < _n && _ths[idx - 1] != _ths[idx]) {
+    if (_useFastPath && _n == _nBins && idx > 0 && idx < _n && _ths[idx - 1] != _ths[idx]) {
       const int ssx = find_smallest();
       const double dssx = _sqe[ssx] + _sqe[ssx + 1] + compute_delta_error(_ths[ssx + 1], k(ssx + 1), _ths[ssx], k(ssx));
       const double d0 = _sqe[idx - 1] + compute_delta_error(pred, w, _ths[idx - 1], k(idx - 1));

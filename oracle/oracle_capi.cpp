@@ -348,6 +348,35 @@ double orc_auc2(const double* pred, const double* act, const double* w, long lon
   return b.auc();
 }
 
+// One AUCBuilder of nbins bins fed row by row (AUCBuilderTest drives the class this way); returns _n, fills the first _n bins.
+int orc_auc_builder(int nbins, const double* pred, const int* act, const double* w, long long n, double* out_ths, double* out_tps, double* out_fps,
+                    double* out_sqe) {
+  AUCBuilder b(nbins);
+  for (long long i = 0; i < n; i++) b.perRow(pred[i], act[i], w ? w[i] : 1.0);
+  for (int i = 0; i < b._n; i++) {
+    if (out_ths) out_ths[i] = b._ths[i];
+    if (out_tps) out_tps[i] = b._tps[i];
+    if (out_fps) out_fps[i] = b._fps[i];
+    if (out_sqe) out_sqe[i] = b._sqe[i];
+  }
+  return b._n;
+}
+
+// AUCBuilderTest.testPerRow_compat: the fast path of perRow against insert + mergeOneBin, compared bin for bin after every row.
+// Returns the first row after which the two builders differ, or -1.
+long long orc_auc_builder_compat(int nbins, const double* pred, const int* act, long long n) {
+  AUCBuilder fast(nbins), slow(nbins);
+  slow._useFastPath = false;
+  for (long long i = 0; i < n; i++) {
+    fast.perRow(pred[i], act[i], 1.0);
+    slow.perRow(pred[i], act[i], 1.0);
+    if (fast._n != slow._n) return i;
+    for (int j = 0; j < nbins; j++)
+      if (fast._ths[j] != slow._ths[j] || fast._tps[j] != slow._tps[j] || fast._fps[j] != slow._fps[j] || fast._sqe[j] != slow._sqe[j]) return i;
+  }
+  return -1;
+}
+
 // ---- level captures (histogram-monitor analogue)
 int orc_model_ncaptures(void* m) { return (int)((GBMModel*)m)->captures.size(); }
 void orc_capture_info(void* m, int i, int* tree, int* k, int* leaf, int* nleaves) {

@@ -399,3 +399,16 @@ def auc2(pred, act, w=None, chunk_rows=1 << 62):
     ths, tps, fps = (np.zeros(800) for _ in range(3))
     a = lib().orc_auc2(ptr(pred), ptr(act), ptr(w), len(pred), min(int(chunk_rows), 1 << 62), C.byref(n), ptr(ths), ptr(tps), ptr(fps))
     return a, ths[:n.value], tps[:n.value], fps[:n.value]
+
+
+def auc_builder(nbins, pred, act, w=None):
+    """One AUC2.AUCBuilder of nbins bins fed row by row. Returns (ths, tps, fps, sqe) of its bins."""
+    pred = np.ascontiguousarray(pred, dtype=np.float64)
+    act = np.ascontiguousarray(act, dtype=np.int32)
+    w = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
+    out = [np.zeros(2 * nbins + 2) for _ in range(4)]
+    L = lib()
+    L.orc_auc_builder.restype = C.c_int
+    L.orc_auc_builder.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong] + [C.c_void_p] * 4
+    n = L.orc_auc_builder(int(nbins), ptr(pred), ptr(act), ptr(w), len(pred), *[ptr(o) for o in out])
+    return tuple(o[:n] for o in out)

@@ -7,7 +7,11 @@ CompressedTreeTest trains on smalldata/logreg/prostate.csv, which is not shipped
   * with at most 400 distinct predictions AUCBuilder never merges bins and AUC2's trapezoid sum is the exact AUC (AUC2.java:36, 262-277);
   * a single builder and per-chunk builders folded by reduce() agree when nothing has to be merged.
 """
+import ctypes as C
+import os
+
 import numpy as np
+import pytest
 
 import h2ot_lib
 import oracle_lib as O
@@ -81,3 +85,42 @@ def test_auc2_is_exact_without_merges_and_chunking_agrees():
     assert abs(a4 - h2ot_lib.auc(act, predc)) < 1e-3
     # edge cases: one class only (AUC2.java:263-264)
     assert O.auc2(pred, np.ones(n))[0] == 1.0 and O.auc2(pred, np.zeros(n))[0] == 0.0
+
+
+def test_auc_builder_known_answer_of_the_reference_test():
+    """h2o-core/src/test/java/hex/AUCBuilderTest.java:16-26 (testPerRow): a 10-bin builder fed i / 100 for i < 100, all actuals 1,
+    ends with these thresholds (the test's own tolerance: 1e-5)."""
+    ths, tps, fps, _ = O.auc_builder(10, np.arange(100) / 100.0, np.ones(100, dtype=np.int32))
+    assert len(ths) == 10
+    assert np.allclose(ths, [0.05, 0.16, 0.25, 0.335, 0.445, 0.555, 0.655, 0.76, 0.875, 0.965], rtol=0, atol=1e-5)
+    assert tps.sum() == 100 and fps.sum() == 0
+
+
+def test_auc2_equals_the_exact_auc_like_the_reference_test():
+    """AUC2Test.perfectAUC (h2o-core/src/test/java/hex/AUC2Test.java:66-74) checks AUC2.perfectAUC against a sort-based exact AUC on
+    these inputs; with fewer than 400 distinct predictions the streaming builder merges nothing, so the oracle's AUC2 must give the
+    same exact values: (0,1 | 0,1) = 1, (0,1,0 | 1,0,1) = 0, (.1,.2,.2,.9 | 0,1,1,1) = 1, (.1,.2,.2,.9 | 0,1,0,1) = 0.875 -- ties
+    count half (the diagonal across a tied group)."""
+    for p, a, want in (([0, 1], [0, 1], 1.0), ([0, 1, 0], [1, 0, 1], 0.0), ([0.1, 0.2, 0.2, 0.9], [0, 1, 1, 1], 1.0),
+                       ([0.1, 0.2, 0.2, 0.9], [0, 1, 0, 1], 0.875)):
+        got = O.auc2(np.array(p, dtype=np.float64), np.array(a, dtype=np.float64))[0]
+        assert abs(got - want) < 1e-15, (p, a, got, want)
+
+
+REF_AUC_ROWS = "/root/reference/h2o-core/src/test/resources/hex/aucbuilder.csv.gz"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_AUC_ROWS), reason="the reference tree (and its test resources) exists only in the build container")
+def test_auc_builder_fast_path_equals_merge_path_on_the_reference_rows():
+    """AUCBuilderTest.testPerRow_compat (h2o-core/src/test/java/hex/AUCBuilderTest.java:28-60): on the reference's own 240 618
+    (prediction, actual) rows the fast path of perRow must leave the builder exactly as insert + mergeOneBin does, after every
+    row. Read from the reference tree where it is (nothing is copied into this repository)."""
+    import gzip
+    rows = np.loadtxt(gzip.open(REF_AUC_ROWS, "rt"), delimiter=",")
+    pred = np.ascontiguousarray(rows[:, 0])
+    act = np.ascontiguousarray(rows[:, 1].astype(np.int32))
+    L = O.lib()
+    L.orc_auc_builder_compat.restype = C.c_longlong
+    L.orc_auc_builder_compat.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_longlong]
+    bad = L.orc_auc_builder_compat(400, O.ptr(pred), O.ptr(act), len(pred))
+    assert bad == -1, "fast path and merge path differ after row %d" % bad
