@@ -348,6 +348,34 @@ double orc_auc2(const double* pred, const double* act, const double* w, long lon
   return b.auc();
 }
 
+// A compressed tree written elsewhere (the reference's MOJO fixtures) decoded into a node table and serialised again.
+// Returns 0, or -1 with the reason in `err`; `reserved` (one int per decided node, nullable) receives the auxiliary records' second word.
+int orc_recompress_tree(const unsigned char* bits, long long nbits, const unsigned char* aux, long long naux, unsigned char* out_bits,
+                        long long* out_nbits, unsigned char* out_aux, long long* out_naux, int* reserved, int* kinds, char* err, int err_cap) {
+  try {
+    std::vector<uint8_t> b(bits, bits + nbits), a(aux, aux + naux);
+    std::vector<int> res;
+    const TreeOut t = decompressTree(b, a, &res);
+    const CompressedTreeBytes c = compressTree(t);
+    if ((long long)c.bits.size() > *out_nbits || (long long)c.aux.size() > *out_naux) throw std::runtime_error("output buffers too small");
+    memcpy(out_bits, c.bits.data(), c.bits.size());
+    memcpy(out_aux, c.aux.data(), c.aux.size());
+    *out_nbits = (long long)c.bits.size();
+    *out_naux = (long long)c.aux.size();
+    if (reserved)
+      for (size_t i = 0; i < res.size(); i++) reserved[i] = res[i];
+    if (kinds) {  // decided nodes by split kind: numeric, 32-bit bitset, long bitset, NA vs rest
+      kinds[0] = kinds[1] = kinds[2] = kinds[3] = 0;
+      for (const Node& n : t.nodes)
+        if (n.kind == DECIDED) kinds[n._split->_nasplit == NAvsREST ? 3 : (n._split->_equal <= 1 ? 0 : n._split->_equal - 1)]++;
+    }
+    return 0;
+  } catch (const std::exception& e) {
+    if (err && err_cap > 0) snprintf(err, (size_t)err_cap, "%s", e.what());
+    return -1;
+  }
+}
+
 // One AUCBuilder of nbins bins fed row by row (AUCBuilderTest drives the class this way); returns _n, fills the first _n bins.
 int orc_auc_builder(int nbins, const double* pred, const int* act, const double* w, long long n, double* out_ths, double* out_tps, double* out_fps,
                     double* out_sqe) {

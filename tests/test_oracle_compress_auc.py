@@ -124,3 +124,69 @@ def test_auc_builder_fast_path_equals_merge_path_on_the_reference_rows():
     L.orc_auc_builder_compat.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_longlong]
     bad = L.orc_auc_builder_compat(400, O.ptr(pred), O.ptr(act), len(pred))
     assert bad == -1, "fast path and merge path differ after row %d" % bad
+
+
+REF_MOJOS = "/root/reference/h2o-genmodel/src/test/resources/hex/genmodel"
+
+
+def _reference_trees():
+    """(label, mojo version, bits, aux) of every compressed tree the reference ships as a test fixture: the isolation-forest trees
+    lying open in the resources, and the GBM / DRF models inside the MOJO zips (stacked-ensemble zips hold whole sub-models)."""
+    import glob
+    import zipfile
+    out = []
+    iso = os.path.join(REF_MOJOS, "algos/isofor")
+    for f in sorted(glob.glob(os.path.join(iso, "trees", "t??_???.bin"))):
+        out.append(("isofor/" + os.path.basename(f), 1.30, open(f, "rb").read(), open(f[:-4] + "_aux.bin", "rb").read()))
+    for z in ("mojo.zip", "algos/ensemble/binomial_titanic.zip", "algos/ensemble/multinomial.zip", "algos/ensemble/regression.zip",
+              "algos/ensemble/binomial.zip"):
+        zf = zipfile.ZipFile(os.path.join(REF_MOJOS, z))
+        names = set(zf.namelist())
+        versions = {}
+        for n in names:
+            if n.endswith("model.ini"):
+                for line in zf.read(n).decode().splitlines():
+                    if line.startswith("mojo_version"):
+                        versions[n[:-len("model.ini")]] = float(line.split("=")[1])
+        for n in sorted(names):
+            if n.endswith(".bin") and not n.endswith("_aux.bin") and "/trees/t" in "/" + n and n[:-4] + "_aux.bin" in names:
+                prefix = n[:n.index("trees/")]
+                out.append((z + ":" + n, versions.get(prefix, 0.0), zf.read(n), zf.read(n[:-4] + "_aux.bin")))
+    return out
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_MOJOS), reason="the reference tree (and its test resources) exists only in the build container")
+def test_trees_serialised_by_the_reference_survive_decode_and_recompress():
+    """DTree.compress against bytes the reference itself wrote: every GBM / DRF / isolation-forest tree among the reference's MOJO
+    test fixtures is decoded into a node table (oracle decompressTree) and serialised again by the oracle's restatement of
+    DTree.compress / DecidedNode.size / compress / IcedBitSet.compress2/3 -- the bytes, and the auxiliary records, must come out
+    identical. (The second word of an auxiliary record is the node's parent id in old MOJOs and the size of its left subtree in
+    new ones -- SharedTreeMojoModel.AuxInfo.reserved -- so it is compared where it holds the count.)"""
+    L = O.lib()
+    L.orc_recompress_tree.restype = C.c_int
+    trees = _reference_trees()
+    assert len(trees) > 500
+    n_counts = 0
+    kinds_total = np.zeros(4, dtype=np.int64)
+    for label, version, bits, aux in trees:
+        ob, oa = C.create_string_buffer(len(bits) + 64), C.create_string_buffer(len(aux) + 64)
+        nb, na = C.c_longlong(len(ob)), C.c_longlong(len(oa))
+        res = (C.c_int * (len(aux) // 40 + 1))()
+        err = C.create_string_buffer(256)
+        kinds = (C.c_int * 4)()
+        rc = L.orc_recompress_tree(bits, C.c_longlong(len(bits)), aux, C.c_longlong(len(aux)), ob, C.byref(nb), oa, C.byref(na), res, kinds, err, 256)
+        assert rc == 0, (label, err.value)
+        assert ob.raw[:nb.value] == bits, label
+        got, want = np.frombuffer(oa.raw[:na.value], dtype=np.int32).reshape(-1, 10), np.frombuffer(aux, dtype=np.int32).reshape(-1, 10)
+        assert got.shape == want.shape, label
+        keep = [0, 2, 3, 4, 5, 6, 7, 8, 9]
+        assert np.array_equal(got[:, keep], want[:, keep]), label
+        if len(want) and np.array_equal(got[:, 1], want[:, 1]):
+            n_counts += 1
+        else:
+            assert version < 1.30 or len(want) == 0, (label, version)  # new MOJOs carry the left-subtree node count, as the oracle writes it
+        kinds_total += np.array(list(kinds))
+    assert n_counts > 50
+    # the fixtures exercise every split encoding: numeric thresholds, 32-bit and long category bitsets, NA-vs-rest
+    print("decided nodes by kind (numeric, bitset32, bitset, NAvsREST):", kinds_total)
+    assert kinds_total[0] > 1000 and kinds_total[1] + kinds_total[2] > 0
