@@ -9,7 +9,8 @@
 // test fixtures (h2o-genmodel/src/test/resources/hex/genmodel: mojo.zip, algos/ensemble/*.zip, algos/isofor/trees; 28 260 decided
 // nodes: 23 452 numeric, 3 965 32-bit bitsets, 664 long bitsets, 179 NA-vs-rest) are decoded with decompressTree below and serialised
 // again with compressTree: bits and auxiliary records come out byte for byte (tests/test_oracle_compress_auc.py, run where the
-// reference tree is present). On top of that the reference's own invariants: size() == bytes written (the assert at
+// reference tree is present); the scoreTree restatement reproduces GbmMojoModelTest.testScore0's known answer on the reference's
+// calibrated GBM MOJO. On top of that the reference's own invariants: size() == bytes written (the assert at
 // DTree.java:929) and scoreTree over the bytes == the node-table walk for every row (CompressedTreeTest.testNodeIdAssignment).
 #pragma once
 #include <cstdint>

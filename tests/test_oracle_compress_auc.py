@@ -190,3 +190,24 @@ def test_trees_serialised_by_the_reference_survive_decode_and_recompress():
     # the fixtures exercise every split encoding: numeric thresholds, 32-bit and long category bitsets, NA-vs-rest
     print("decided nodes by kind (numeric, bitset32, bitset, NAvsREST):", kinds_total)
     assert kinds_total[0] > 1000 and kinds_total[1] + kinds_total[2] > 0
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_MOJOS), reason="the reference tree (and its test resources) exists only in the build container")
+def test_score_tree_reader_known_answer_of_the_reference_mojo_test():
+    """GbmMojoModelTest.testScore0 (h2o-genmodel/src/test/java/hex/genmodel/algos/gbm/GbmMojoModelTest.java:32-37): the 10-tree GBM
+    MOJO under algos/gbm/calibrated scores this row as {0.5416688, 0.4583312} (1e-5). The oracle's restatement of
+    SharedTreeMojoModel.scoreTree reads the reference's tree bytes; the rest is GbmMojoModel.unifyPreds for a 2-class multinomial
+    model with one tree per iteration (f = sum of the trees + init_f, classes scored f and -f, GBM_rescale = softmax)."""
+    d = os.path.join(REF_MOJOS, "algos/gbm/calibrated")
+    init_f = None
+    for line in open(os.path.join(d, "model.ini")):
+        if line.startswith("init_f"):
+            init_f = float(line.split("=")[1])
+    row = np.array([[18.7, 1.51, 1.003, 132.53, 1.15, 0.2, 1.153, 8.3, 0.34, 0.0, 0.0]])
+    f = init_f
+    for t in range(10):
+        bits = open(os.path.join(d, "trees", "t00_%03d.bin" % t), "rb").read()
+        f += float(O.score_compressed(bits, row)[0])
+    p = np.exp([f, -f])
+    p /= p.sum()
+    assert np.allclose(p, [0.5416688, 0.4583312], rtol=0, atol=1e-5), p
