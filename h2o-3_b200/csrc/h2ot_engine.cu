@@ -2312,11 +2312,12 @@ int h2ot_tree_levels_begin(h2ot_engine* h, int32_t k, int32_t max_depth, const h
   dv.nbins = nbins;
   dv.nbins_cats = nbins_cats;
   dv.min_rows = min_rows;
+  TRY(t.d_cand.ensure(((size_t)1 << (D - 1)) * C));  // (never reallocated while a kernel of an earlier level still reads it)
+  // (no early return between here and the reset of these flags below: every failure goes through rc)
   dv.active = true;
   h->defer_sync = true;
   h->in_tree_loop = true;
   t.best_pending = t.fin_pending = false;
-  TRY(t.d_cand.ensure(((size_t)1 << (D - 1)) * C));  // (never reallocated while a kernel of an earlier level still reads it)
   int rc = H2OT_OK;
   std::vector<h2ot_hist_desc> tmpl;
   for (int d = 0; d < D && rc == H2OT_OK; d++) {
