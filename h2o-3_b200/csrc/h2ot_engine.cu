@@ -1465,7 +1465,8 @@ int plan_level(h2ot_engine* h, TreeState& t, int L, const h2ot_hist_desc* descs)
   const bool agg_ok = !h->w && !h->no_agg && !t.any_checkfloat && ceil_log2_u64((uint64_t)h->cfg.nrows_global + 1) >= 18;
   for (int c = 0; c < C; c++) {
     if (!col_words[c] || h->hist_mode == 1 || t.any_splitpts) continue;
-    if (agg_ok && h->col_conc[c] * 32.0 / (double)L >= 8.0) {
+    static const double agg_min = getenv("H2OT_AGG_MIN") ? atof(getenv("H2OT_AGG_MIN")) : 8.0;  // expected rows of a warp on one bin
+    if (agg_ok && h->col_conc[c] * 32.0 / (double)L >= agg_min) {
       col_agg[c] = 1;
       continue;
     }
