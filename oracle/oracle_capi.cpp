@@ -5,6 +5,7 @@
 #include "h2o_chunk_oracle.hpp"
 #include "h2o_compress_oracle.hpp"
 #include "h2o_auc_oracle.hpp"
+#include "h2o_metrics_oracle.hpp"
 
 using namespace h2o_oracle;
 
@@ -346,6 +347,15 @@ double orc_auc2(const double* pred, const double* act, const double* w, long lon
     if (out_fps) out_fps[i] = b._fps[i];
   }
   return b.auc();
+}
+
+// hex.tree.Score's sums over the model's Tree_k columns (F: K pointers to n doubles): out = {count, wcount, sumsqe, logloss}
+void orc_score_metrics(int family, int K, const double* const* F, const double* y, const double* w, long long n, double* out) {
+  const MetricSums s = scoreMetrics(family, K, F, y, w, n);
+  out[0] = s.count;
+  out[1] = s.wcount;
+  out[2] = s.sumsqe;
+  out[3] = s.logloss;
 }
 
 // A compressed tree written elsewhere (the reference's MOJO fixtures) decoded into a node table and serialised again.

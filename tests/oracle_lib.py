@@ -412,3 +412,17 @@ def auc_builder(nbins, pred, act, w=None):
     L.orc_auc_builder.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong] + [C.c_void_p] * 4
     n = L.orc_auc_builder(int(nbins), ptr(pred), ptr(act), ptr(w), len(pred), *[ptr(o) for o in out])
     return tuple(o[:n] for o in out)
+
+
+def score_metrics(family, Fk, y, w=None):
+    """hex.tree.Score's metric sums over Tree_k columns Fk ([K][n], link space incl. init_f). Returns dict(count, wcount, mse, logloss)."""
+    Fk = [np.ascontiguousarray(f, dtype=np.float64) for f in Fk]
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    w = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
+    ptrs = (C.c_void_p * len(Fk))(*[f.ctypes.data for f in Fk])
+    out = np.zeros(4)
+    L = lib()
+    L.orc_score_metrics.restype = None
+    L.orc_score_metrics.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p]
+    L.orc_score_metrics(int(family), len(Fk), ptrs, ptr(y), ptr(w), len(y), ptr(out))
+    return dict(count=out[0], wcount=out[1], mse=out[2] / out[1] if out[1] else float("nan"), logloss=out[3] / out[1] if out[1] else float("nan"))

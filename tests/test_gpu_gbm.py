@@ -227,6 +227,9 @@ def test_device_scoring_matches_metric_builders():
     want_mse = np.sum(w[ok] * (1 - pact) ** 2) / np.sum(w[ok])
     got = gm.score()
     assert abs(got["logloss"] - want_ll) <= 1e-12 * want_ll and abs(got["mse"] - want_mse) <= 1e-12 * want_mse
+    # ... and the oracle's restatement of MetricBuilderBinomial.perRow (oracle/h2o_metrics_oracle.hpp) on the same columns
+    om = O.score_metrics(O.BERNOULLI, [F], y, w)
+    assert abs(got["logloss"] - om["logloss"]) <= 1e-12 * om["logloss"] and abs(got["mse"] - om["mse"]) <= 1e-12 * om["mse"]
     gm.close()
     # multinomial
     rng = np.random.default_rng(3)
@@ -242,6 +245,8 @@ def test_device_scoring_matches_metric_builders():
     pact = p[np.arange(n), y.astype(int)]
     got = gm.score()
     assert abs(got["logloss"] - np.mean(-np.log(pact))) <= 1e-12 and abs(got["mse"] - np.mean((1 - pact) ** 2)) <= 1e-12
+    om = O.score_metrics(O.MULTINOMIAL, [Fk[:, k] for k in range(3)], y)
+    assert abs(got["logloss"] - om["logloss"]) <= 1e-12 and abs(got["mse"] - om["mse"]) <= 1e-12
     gm.close()
     # gaussian
     yg = (X[:, 0] * 2 + X[:, 1]).astype(np.float32).astype(np.float64)
@@ -250,6 +255,8 @@ def test_device_scoring_matches_metric_builders():
     gm.train()
     got = gm.score()
     assert abs(got["mse"] - np.mean((yg - gm.predictions()) ** 2)) <= 1e-12 * got["mse"] and got["logloss"] == 0.0
+    om = O.score_metrics(O.GAUSSIAN, [gm.predictions()], yg)
+    assert abs(got["mse"] - om["mse"]) <= 1e-12 * om["mse"]
     gm.close()
 
 

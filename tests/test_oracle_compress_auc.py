@@ -211,3 +211,26 @@ def test_score_tree_reader_known_answer_of_the_reference_mojo_test():
     p = np.exp([f, -f])
     p /= p.sum()
     assert np.allclose(p, [0.5416688, 0.4583312], rtol=0, atol=1e-5), p
+
+
+def test_metric_sums_restatement_on_known_values():
+    """MetricBuilderBinomial / Multinomial / Regression.perRow + MathUtils.logloss restated (oracle/h2o_metrics_oracle.hpp), on
+    values whose sums are known in closed form: a bernoulli model at f = 0 predicts 1/2 for every row (err = 1/2, logloss = ln 2),
+    rows with a missing actual or zero weight do not count, a certain wrong prediction is capped at -ln(1e-15), a 3-class model
+    with equal scores predicts 1/3 (logloss = ln 3, err^2 = 4/9), regression sums (y - f)^2."""
+    n = 1000
+    y = (np.arange(n) % 2).astype(np.float64)
+    y[::50] = np.nan
+    w = np.ones(n)
+    w[1::50] = 0
+    live = (~np.isnan(y)) & (w != 0)
+    m = O.score_metrics(O.BERNOULLI, [np.zeros(n)], y, w)
+    assert m["count"] == live.sum() and m["wcount"] == live.sum()
+    assert abs(m["logloss"] - np.log(2)) < 1e-12 and abs(m["mse"] - 0.25) < 1e-12  # (row-by-row sums: a few ulps per add)
+    m = O.score_metrics(O.BERNOULLI, [np.full(4, 800.0)], np.array([0.0, 0.0, 1.0, 1.0]))   # p1 == 1: two certain mistakes
+    assert abs(m["logloss"] - 0.5 * -np.log(1e-15)) < 1e-12 and abs(m["mse"] - 0.5) < 1e-15
+    m = O.score_metrics(O.MULTINOMIAL, [np.full(9, 0.3)] * 3, np.arange(9) % 3)
+    assert abs(m["logloss"] - np.log(3)) < 1e-12 and abs(m["mse"] - 4.0 / 9.0) < 1e-12
+    yg = np.array([1.0, 2.0, 4.0])
+    m = O.score_metrics(O.GAUSSIAN, [np.array([0.5, 2.5, 1.0])], yg, np.array([1.0, 2.0, 1.0]))
+    assert abs(m["mse"] - (0.25 + 2 * 0.25 + 9.0) / 4.0) < 1e-15 and m["logloss"] == 0
