@@ -22,7 +22,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libh2otree_b200.so")
 
 OK = 0
-FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2, "poisson": 3, "gamma": 4, "tweedie": 5}
+FAMILY = {"gaussian": 0, "bernoulli": 1, "multinomial": 2, "poisson": 3, "gamma": 4, "tweedie": 5, "laplace": 6, "quantile": 7}
 NA_NONE, NA_VS_REST, NA_LEFT, NA_RIGHT, LEFT, RIGHT = 0, 1, 2, 3, 4, 5
 DECIDED_ROW, OUT_OF_BAG = -1, -2
 STORE_F32, STORE_F64, STORE_U8, STORE_U16 = 0, 1, 2, 3
@@ -104,7 +104,7 @@ class GbmTiming(C.Structure):
 
 # every symbol declared in include/h2ot.h and include/h2ot_gbm.h (tests check that the library exports all of them)
 ENGINE_SYMBOLS = [
-    "h2ot_tree_finish_enqueue", "h2ot_tree_levels_end2", "h2ot_compute_residuals_async", "h2ot_residual_bounds_wait",
+    "h2ot_leaf_quantiles", "h2ot_tree_finish_enqueue", "h2ot_tree_levels_end2", "h2ot_compute_residuals_async", "h2ot_residual_bounds_wait",
     "h2ot_version", "h2ot_last_error", "h2ot_device_count", "h2ot_create", "h2ot_destroy", "h2ot_load_column",
     "h2ot_load_response", "h2ot_load_weights", "h2ot_load_offset", "h2ot_finalize_frame", "h2ot_column_info_get",
     "h2ot_init_model", "h2ot_initial_stats", "h2ot_set_predictions", "h2ot_get_predictions", "h2ot_get_work", "h2ot_set_work",
@@ -492,7 +492,9 @@ class GBM:
                  col_sample_rate_change_per_level=1.0, learn_rate=0.1, learn_rate_annealing=1.0,
                  max_abs_leafnode_pred=float(np.finfo(np.float64).max), distribution="bernoulli", nclass=2, seed=1234,
                  device=0, algo=0, mtries=-1, tweedie_power=1.5, histogram_type="AUTO", pred_noise_bandwidth=0.0,
-                 sample_rate_per_class=None):
+                 sample_rate_per_class=None, quantile_alpha=0.5):
+        if distribution == "quantile":  # (the parameter struct has one slot for the family's parameter)
+            tweedie_power = quantile_alpha
         self.params = GbmParams(ntrees=ntrees, max_depth=max_depth, nbins=nbins, nbins_cats=nbins_cats,
                                 nbins_top_level=nbins_top_level, family=FAMILY[distribution], nclass=nclass, algo=algo,
                                 mtries=mtries, histogram_type={"AUTO": 0, "UniformAdaptive": 0, "Random": 1}[histogram_type],

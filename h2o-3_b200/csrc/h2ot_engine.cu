@@ -20,6 +20,9 @@
 #include "k_xreduce.cuh"
 #include "k_auc.cuh"
 #include "k_next.cuh"
+#include "k_quant.cuh"
+
+#include <cub/device/device_radix_sort.cuh>
 
 namespace h2ot {
 
@@ -232,6 +235,11 @@ struct h2ot_engine {
   bool defer_sync = false;
   bool timer_open = false;
   int timer_mode = 2;  // h2ot_set_timers
+  DBuf<uint64_t> q_keys[2];       // h2ot_leaf_quantiles: sort buffers (value keys, strata) and CUB's scratch
+  DBuf<uint32_t> q_strata[2];
+  DBuf<unsigned char> q_tmp;
+  DBuf<unsigned long long> q_counts;
+  DBuf<long long> q_idx;
   unsigned int* bounds_host = nullptr;  // pinned: residual maxima of h2ot_compute_residuals_async
   cudaEvent_t bounds_ev = nullptr;
   bool bounds_pending = false;
@@ -387,7 +395,9 @@ int h2ot_destroy(h2ot_engine* h);
 static int create_into(const h2ot_config* cfg, h2ot_engine* h) {
   h->cfg = *cfg;
   if (h->cfg.nrows_global <= 0) h->cfg.nrows_global = cfg->nrows;
-  if (!(h->cfg.tweedie_power > 1.0 && h->cfg.tweedie_power < 2.0)) h->cfg.tweedie_power = 1.5;
+  if (h->cfg.family == H2OT_FAMILY_QUANTILE) {  // the slot holds _quantile_alpha (default 0.5, H/Model.java Parameters)
+    if (!(h->cfg.tweedie_power > 0.0 && h->cfg.tweedie_power < 1.0)) h->cfg.tweedie_power = 0.5;
+  } else if (!(h->cfg.tweedie_power > 1.0 && h->cfg.tweedie_power < 2.0)) h->cfg.tweedie_power = 1.5;
   h->n = cfg->nrows;
   h->n_pad = (cfg->nrows + kRowPad - 1) / kRowPad * kRowPad;
   h->C = cfg->ncols;
@@ -480,7 +490,7 @@ int h2ot_create(const h2ot_config* cfg, h2ot_engine** out) {
   if (cfg->nrows > ((int64_t)1 << 32) - 2 * kRowPad)  // row ids travel as 32-bit values inside the level kernels; a shard is far smaller anyway
     H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "more than 2^32 rows on one GPU: shard the rows over more engines");
   if (cfg->nclass_trees > 64) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "at most 64 class-trees");
-  if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_TWEEDIE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
+  if (cfg->family < H2OT_FAMILY_GAUSSIAN || cfg->family > H2OT_FAMILY_QUANTILE) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "unknown distribution family");
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
@@ -520,6 +530,8 @@ int h2ot_destroy(h2ot_engine* h) {
   if (h->oobt) cudaFree(h->oobt);
   if (h->xr_err) cudaFree(h->xr_err);
   if (h->xr_err_host) cudaFreeHost(h->xr_err_host);
+  h->q_keys[0].release(); h->q_keys[1].release(); h->q_strata[0].release(); h->q_strata[1].release(); h->q_tmp.release();
+  h->q_counts.release(); h->q_idx.release();
   if (h->bounds_host) cudaFreeHost(h->bounds_host);
   if (h->bounds_ev) cudaEventDestroy(h->bounds_ev);
   for (TreeState& t : h->ts) {
@@ -2487,6 +2499,102 @@ int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint
 }
 
 // ------------------------------------------------------------------------------------------------ end of tree
+// Quantile of the residuals per leaf (k_quant.cuh). use_tree != 0: strata are the rows' leaf ids leaf_start .. leaf_start + n_strata - 1
+// (NIDs_k after h2ot_gamma_pass; out-of-bag rows take part like the others, as in the reference, which stratifies by the NIDs
+// column alone) and the value is y - (Tree_k + offset); use_tree == 0: one stratum of all rows, value y - offset (the initial
+// prediction). out[s] = NaN for a stratum without rows. Unit weights and a single rank only.
+int h2ot_leaf_quantiles(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_strata, int32_t use_tree, double prob, double* out) {
+  CHECK_ENGINE(h);
+  CHECK_K(h, k);
+  if (!out || n_strata < 1 || !(prob >= 0 && prob <= 1)) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_leaf_quantiles: bad arguments");
+  if (!use_tree && n_strata != 1) H2OT_FAIL(H2OT_ERR_INVALID, "h2ot_leaf_quantiles: without a tree there is one stratum");
+  if (h->w) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_leaf_quantiles: observation weights are not supported (weighted quantiles)");
+  if (h->nccl.world > 1) H2OT_FAIL(H2OT_ERR_UNSUPPORTED, "h2ot_leaf_quantiles: single rank only (the order statistics span the shards)");
+  TreeState& t = h->ts[k];
+  const size_t np = (size_t)h->n_pad;
+  for (int i = 0; i < 2; i++) {
+    TRY(h->q_keys[i].ensure(np));
+    TRY(h->q_strata[i].ensure(np));
+  }
+  TRY(h->q_counts.ensure((size_t)n_strata + 1));
+  TRY(h->q_idx.ensure((size_t)n_strata * 2));
+  CUDA_TRY(cudaMemsetAsync(h->q_counts.p, 0, ((size_t)n_strata + 1) * sizeof(unsigned long long), h->stream));
+  QuantKeysArgs qa{};
+  qa.n = h->n;
+  qa.n_pad = h->n_pad;
+  qa.leaf_start = leaf_start;
+  qa.n_strata = n_strata;
+  qa.use_tree = use_tree ? 1 : 0;
+  qa.resp = h->resp;
+  qa.w = h->w;
+  qa.off = h->off;
+  qa.F = use_tree ? t.F : nullptr;
+  qa.nids = use_tree ? t.nids : nullptr;
+  qa.keys = h->q_keys[0].p;
+  qa.strata = h->q_strata[0].p;
+  qa.counts = h->q_counts.p;
+  quant_keys_kernel<<<grid_for(h, h->n_pad, 256), 256, 0, h->stream>>>(qa);
+  h->stats.launches++;
+  // value order first, then a stable sort by stratum: rows end up grouped by stratum, ascending inside
+  int sbits = 1;
+  while ((1 << sbits) < n_strata + 1) sbits++;
+  size_t tmp1 = 0, tmp2 = 0;
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp1, h->q_keys[0].p, h->q_keys[1].p, h->q_strata[0].p, h->q_strata[1].p, (int64_t)np, 0, 64, h->stream));
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp2, h->q_strata[1].p, h->q_strata[0].p, h->q_keys[1].p, h->q_keys[0].p, (int64_t)np, 0, sbits, h->stream));
+  TRY(h->q_tmp.ensure(std::max(tmp1, tmp2) + 256));
+  size_t tb = h->q_tmp.cap;
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(h->q_tmp.p, tb, h->q_keys[0].p, h->q_keys[1].p, h->q_strata[0].p, h->q_strata[1].p, (int64_t)np, 0, 64, h->stream));
+  tb = h->q_tmp.cap;
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(h->q_tmp.p, tb, h->q_strata[1].p, h->q_strata[0].p, h->q_keys[1].p, h->q_keys[0].p, (int64_t)np, 0, sbits, h->stream));
+  h->stats.launches += 2;
+  std::vector<unsigned long long> cnt((size_t)n_strata + 1);
+  TRY(d2h(h, cnt.data(), h->q_counts.p, cnt.size() * sizeof(unsigned long long)));
+  CUDA_TRY(cudaStreamSynchronize(h->stream));
+  // Histo.findQuantile: fractional row p2 = prob (n - 1), lo = element r2 = (long) p2, hi = element r2 + 1
+  std::vector<long long> idx((size_t)n_strata * 2, -1);
+  std::vector<long long> r2s((size_t)n_strata, 0);
+  long long off = 0;
+  for (int s = 0; s < n_strata; s++) {
+    const long long n = (long long)cnt[(size_t)s];
+    if (n > 0) {
+      const double p2 = prob * ((double)n - 1.0);
+      const long long r2 = (long long)p2;
+      r2s[(size_t)s] = r2;
+      idx[(size_t)s * 2] = off + r2;
+      idx[(size_t)s * 2 + 1] = r2 + 1 < n ? off + r2 + 1 : -1;
+    }
+    off += n;
+  }
+  TRY(h2d(h, h->q_idx.p, idx.data(), idx.size() * sizeof(long long)));
+  uint64_t* d_out = h->q_keys[1].p;  // (free again after the second sort)
+  quant_gather_kernel<<<(n_strata * 2 + 127) / 128, 128, 0, h->stream>>>(h->q_keys[0].p, h->q_idx.p, n_strata * 2, d_out);
+  h->stats.launches++;
+  std::vector<uint64_t> vals((size_t)n_strata * 2);
+  TRY(d2h(h, vals.data(), d_out, vals.size() * sizeof(uint64_t)));
+  TRY(finish_call(h));
+  for (int s = 0; s < n_strata; s++) {
+    const double n = (double)cnt[(size_t)s];
+    if (!(n > 0)) {
+      out[s] = NAN;
+      continue;
+    }
+    const double lo = dkey_inv(vals[(size_t)s * 2]);
+    if (idx[(size_t)s * 2 + 1] < 0) {
+      out[s] = lo;
+      continue;
+    }
+    const double hi = dkey_inv(vals[(size_t)s * 2 + 1]);
+    if (lo == hi) {  // Quantile.computeQuantile (:330-331)
+      out[s] = lo;
+      continue;
+    }
+    const double row = (double)r2s[(size_t)s];
+    const double plo = (row + 0) / (n - 1), phi = (row + 1) / (n - 1);  // linearInterpolate (:344-350)
+    out[s] = lo + (hi - lo) * (prob - plo) / (phi - plo);
+  }
+  return H2OT_OK;
+}
+
 // The rest of a tree without the host (after h2ot_tree_levels_begin): GammaPass with the leaves numbered by their static slot,
 // the leaf values, AddTreeContributions, and the download of the leaf values next to the tree's splits. Nothing synchronises.
 int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_abs_leafnode_pred) {

@@ -474,6 +474,15 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 // Builds without per-node column sampling and with uniform-adaptive histograms can run all levels of a tree back to back on the
 // device (h2ot_tree_levels_begin / _end): _scoreCols == null for every node (T/DTree.java:455-461), so no host-side draw sits
 // between two levels. H2OT_DEVICE_LOOP=0 keeps the level-by-level host loop (the two must grow identical trees).
+// laplace / quantile: leaves are fitted with the residuals' median / alpha-quantile (fitBestConstantsQuantile, T/gbm/GBM.java:522-527, 729-751)
+bool quantile_family(const h2ot_gbm* g) {
+  return g->p.algo == H2OT_ALGO_GBM && (g->p.family == H2OT_FAMILY_LAPLACE || g->p.family == H2OT_FAMILY_QUANTILE);
+}
+double quantile_prob(const h2ot_gbm* g) {
+  if (g->p.family == H2OT_FAMILY_LAPLACE) return 0.5;
+  return g->p.tweedie_power > 0.0 && g->p.tweedie_power < 1.0 ? g->p.tweedie_power : 0.5;  // (as the engine reads the slot)
+}
+
 bool use_device_loop(const h2ot_gbm* g) {
   const char* e = getenv("H2OT_DEVICE_LOOP");  // read per tree: tests switch it between two builds of one process
   const bool off = e != nullptr && atoi(e) == 0;
@@ -1004,9 +1013,21 @@ int build_next_k_trees(h2ot_gbm* g) {
     GTRY(h2ot_set_tree(g->eng, k, (int)dn.size(), dn.data(), pool.data(), (int64_t)pool.size()));
     std::vector<double> num(nleaf), den(nleaf);
     GTRY(h2ot_gamma_pass(g->eng, k, leaf_base, nleaf, num.data(), den.data()));
+    if (quantile_family(g)) {  // fitBestConstantsQuantile: the rows now sit on their leaves (NIDs_k), which are the strata
+      std::vector<double> q((size_t)nleaf);
+      GTRY(h2ot_leaf_quantiles(g->eng, k, leaf_base, nleaf, 1, quantile_prob(g), q.data()));
+      for (int i = 0; i < nleaf; i++) {
+        if (std::isnan(q[(size_t)i])) continue;  // no active rows for this NID (:745)
+        double val = eff_lr * q[(size_t)i];
+        if (val > g->p.max_abs_leafnode_pred) val = g->p.max_abs_leafnode_pred;
+        if (val < -g->p.max_abs_leafnode_pred) val = -g->p.max_abs_leafnode_pred;
+        t.ns[leaves[k] + i].pred = (float)val;
+      }
+      continue;
+    }
     for (int i = 0; i < nleaf; i++) {
       double gamma = den[i] == 0 ? 0 : num[i] / den[i];
-      if (den[i] != 0 && g->p.family >= H2OT_FAMILY_POISSON) {  // GammaPass.gamma(double): link for poisson / gamma / tweedie
+      if (den[i] != 0 && g->p.family >= H2OT_FAMILY_POISSON && g->p.family <= H2OT_FAMILY_TWEEDIE) {  // GammaPass.gamma(double): link for poisson / gamma / tweedie
         const double x = std::fmax(0.0, gamma);
         gamma = x == 0 ? -19.0 : std::fmax(-19.0, std::log(x));  // LogExpUtil.log
       }
@@ -1150,7 +1171,7 @@ extern "C" {
 int h2ot_gbm_create(const h2ot_gbm_params* p, int32_t device, int64_t nrows, int32_t ncols, int64_t row_offset, int64_t nrows_global,
                     int32_t has_weights, int32_t has_offset, h2ot_gbm** out) {
   if (!p || !out) GFAIL(H2OT_ERR_INVALID, "null argument");
-  if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_TWEEDIE) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
+  if (p->family < H2OT_FAMILY_GAUSSIAN || p->family > H2OT_FAMILY_QUANTILE) GFAIL(H2OT_ERR_UNSUPPORTED, "unsupported distribution family");
   if (p->algo == H2OT_ALGO_DRF && p->family > H2OT_FAMILY_MULTINOMIAL) GFAIL(H2OT_ERR_UNSUPPORTED, "DRF takes gaussian / bernoulli / multinomial");
   if (p->max_depth < 1 || p->nbins < 2 || p->nbins_cats < 2 || p->ntrees < 0) GFAIL(H2OT_ERR_INVALID, "bad tree parameters");
   if (p->nbins_cats > H2OT_MAX_BITSET_BYTES * 8) GFAIL(H2OT_ERR_UNSUPPORTED, "nbins_cats above 4096");
@@ -1349,9 +1370,13 @@ int h2ot_gbm_init(h2ot_gbm* g) {
   if (drf) g->init_f = g->nclass > 1 ? 0 : mean;  // T/drf/DRF.java:131
   else if (g->nclass > 2) g->init_f = 0;
   else if (g->p.family == H2OT_FAMILY_BERNOULLI) g->init_f = std::log(mean / (1 - mean));  // LogitFunction.link
-  else if (g->p.family >= H2OT_FAMILY_POISSON) {  // LogFunction.link == LogExpUtil.log
+  else if (g->p.family >= H2OT_FAMILY_POISSON && g->p.family <= H2OT_FAMILY_TWEEDIE) {  // LogFunction.link == LogExpUtil.log
     const double x = std::fmax(0.0, mean);
     g->init_f = x == 0 ? -19.0 : std::fmax(-19.0, std::log(x));
+  } else if (quantile_family(g)) {
+    // GBM.getInitialValueQuantile (T/gbm/GBM.java:272-276, 355-381): the median / alpha-quantile of y - offset
+    GTRY(h2ot_leaf_quantiles(g->eng, 0, 0, 1, 0, quantile_prob(g), &g->init_f));
+    if (std::isnan(g->init_f)) g->init_f = 0;
   } else g->init_f = mean;
   if (drf) {
     GTRY(h2ot_drf_init_model(g->eng));

@@ -220,7 +220,9 @@ __global__ void __launch_bounds__(256) residuals_kernel(ResidArgs a) {
         r = __dsub_rn(__dmul_rn(y, e1), e2);
         tn = fabs(__dmul_rn(y, e1));
         td = e2;
-      } else r = y - f;
+      } else if (a.family == H2OT_FAMILY_LAPLACE) r = f > y ? -0.5 : 0.5;                                     // H/DistributionFactory.java:418-420
+      else if (a.family == H2OT_FAMILY_QUANTILE) r = y > f ? 0.5 * a.tweedie_power : 0.5 * (a.tweedie_power - 1.0);  // :433 (alpha)
+      else r = y - f;
       const float rf = (float)r;
       a.work[0][row] = rf;
       amaxk = fmaxf(amaxk, fabsf(rf));
@@ -472,7 +474,7 @@ __global__ void __launch_bounds__(256) score_metrics_kernel(ScoreArgs2 a) {
     if (wv == 0.0 || isnan(wv)) continue;
     const double f = a.F[0][row] + (a.off ? a.off[row] : 0.0);
     double err;
-    if (a.family == H2OT_FAMILY_GAUSSIAN) {
+    if (a.family == H2OT_FAMILY_GAUSSIAN || a.family == H2OT_FAMILY_LAPLACE || a.family == H2OT_FAMILY_QUANTILE) {  // identity link
       err = y - f;
     } else if (a.family >= H2OT_FAMILY_POISSON) {
       err = y - exp_cap(f);  // ModelMetricsRegression on the response scale: ds[0] = linkInv(f)

@@ -40,6 +40,8 @@ extern "C" {
 #define H2OT_FAMILY_POISSON 3  /* H/DistributionFactory.java:274-307 (log link) */
 #define H2OT_FAMILY_GAMMA 4    /* :309-341 */
 #define H2OT_FAMILY_TWEEDIE 5  /* :343-379, power in h2ot_config.tweedie_power (1 < p < 2) */
+#define H2OT_FAMILY_LAPLACE 6  /* :406-421: negHalfGradient = sign(y - f) / 2; leaves are fitted with h2ot_leaf_quantiles(0.5) */
+#define H2OT_FAMILY_QUANTILE 7 /* :423-434, alpha in h2ot_config.tweedie_power; leaves are fitted with h2ot_leaf_quantiles(alpha) */
 
 /* T/DHistogram.java:152-168 NASplitDir */
 #define H2OT_NA_NONE 0
@@ -73,7 +75,7 @@ typedef struct h2ot_config {
   int32_t has_weights;
   int32_t has_offset;
   int32_t reserved;
-  double tweedie_power;  /* H2OT_FAMILY_TWEEDIE only (Model.Parameters._tweedie_power, default 1.5) */
+  double tweedie_power;  /* H2OT_FAMILY_TWEEDIE: Model.Parameters._tweedie_power (default 1.5); H2OT_FAMILY_QUANTILE: _quantile_alpha */
 } h2ot_config;
 
 /* Per (leaf, column) histogram descriptor == the DHistogram fields the CPU kernel reads
@@ -307,6 +309,12 @@ int h2ot_tree_levels_end(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint
  * want_bounds != 0 the maxima (all-reduced over the communicator) are copied to pinned memory behind the kernel and
  * h2ot_residual_bounds_wait returns them, waiting for that copy only: out_abs_max[K], out_gamma_bounds[2] (both nullable). */
 int h2ot_tree_finish_enqueue(h2ot_engine* h, int32_t k, double rate, double max_abs_leafnode_pred);
+/* Quantile.StratifiedQuantilesTask for GBM's laplace / quantile leaf fitting (h2o-algos/src/main/java/hex/tree/gbm/GBM.java:729-751;
+ * h2o-core/src/main/java/hex/quantile/Quantile.java:118-175, 267-350): out[s] = the prob-quantile (interpolated, CombineMethod
+ * INTERPOLATE) of y - (Tree_k + offset) over the rows whose NIDs_k is leaf_start + s, s < n_strata (call it after h2ot_gamma_pass
+ * has moved the rows onto their leaves); NaN where a leaf has no rows. With use_tree == 0 and n_strata == 1: the quantile of
+ * y - offset over all rows, GBM.getInitialValueQuantile (:355-381). Unit weights and a single rank only (H2OT_ERR_UNSUPPORTED). */
+int h2ot_leaf_quantiles(h2ot_engine* h, int32_t k, int32_t leaf_start, int32_t n_strata, int32_t use_tree, double prob, double* out);
 int h2ot_tree_levels_end2(h2ot_engine* h, int32_t k, h2ot_split* out_splits, uint8_t* out_exists, float* out_leaf_pred);
 int h2ot_compute_residuals_async(h2ot_engine* h, int32_t want_bounds);
 int h2ot_residual_bounds_wait(h2ot_engine* h, double* out_abs_max, double out_gamma_bounds[2]);

@@ -332,3 +332,10 @@ FN(commInit)(JNIEnv* env, jclass cls, jlong h, jint worldSize, jint rank, jbyteA
   UNPIN_B(v, id, JNI_ABORT);
   throw_if(env, rc);
 }
+/* laplace / quantile GBM: per-leaf quantiles of the residuals (and, with useTree == false and one stratum, the initial prediction) */
+FN(leafQuantiles)(JNIEnv* env, jclass cls, jlong h, jint k, jint leafStart, jint nStrata, jboolean useTree, jdouble prob, jdoubleArray out) {
+  PIN_D(v, out);
+  const int rc = h2ot_leaf_quantiles(H(h), k, leafStart, nStrata, useTree ? 1 : 0, prob, v);
+  UNPIN_D(v, out, 0);
+  throw_if(env, rc);
+}

@@ -211,7 +211,7 @@ struct IcedBitSet {
 // ----------------------------------------------------------------------------------------------
 // Parameters (T/SharedTreeModel.java:51-98, T/gbm/GBMModel.java:24-41 defaults)
 // ----------------------------------------------------------------------------------------------
-enum Family { GAUSSIAN = 0, BERNOULLI = 1, MULTINOMIAL = 2, POISSON = 3, GAMMA = 4, TWEEDIE = 5 };
+enum Family { GAUSSIAN = 0, BERNOULLI = 1, MULTINOMIAL = 2, POISSON = 3, GAMMA = 4, TWEEDIE = 5, LAPLACE = 6, QUANTILE = 7 };
 enum NASplitDir { NA_None = 0, NAvsREST = 1, NALeft = 2, NARight = 3, Left = 4, Right = 5 };  // T/DHistogram.java:152-168
 
 struct Params {
@@ -237,7 +237,7 @@ struct Params {
   bool drf = false;
   int mtries = -1;  // DRF only
   int nthreads = 1; // CPU threads for the SBH2 restatement (baseline timing)
-  double tweedie_power = 1.5;  // H/Model.java Parameters._tweedie_power
+  double tweedie_power = 1.5;  // H/Model.java Parameters._tweedie_power; for family QUANTILE this slot holds _quantile_alpha
   int histogram_type = 0;      // HistoType: 0 UniformAdaptive (== AUTO), 1 Random (T/SharedTreeModel.java HistogramType)
 };
 
@@ -1365,14 +1365,14 @@ inline double log_(double x) {                                          // LogEx
 }
 inline double linkInv(int family, double f) {
   switch (family) {
-    case GAUSSIAN: return f;
+    case GAUSSIAN: case LAPLACE: case QUANTILE: return f;
     case BERNOULLI: return 1 / (1 + exp_(-f));
     default: return exp_(f);
   }
 }
 inline double link(int family, double f) {
   switch (family) {
-    case GAUSSIAN: return f;
+    case GAUSSIAN: case LAPLACE: case QUANTILE: return f;
     case BERNOULLI: return log_(f / (1 - f));
     default: return log_(f);
   }
@@ -1383,8 +1383,28 @@ inline double negHalfGradient(int family, double y, double f, double p = 1.5) {
   switch (family) {
     case GAMMA: return y * exp_(-f) - 1;
     case TWEEDIE: return y * exp_(f * (1 - p)) - exp_(f * (2 - p));
+    case LAPLACE: return f > y ? -0.5 : 0.5;                    // Laplace :417-420
+    case QUANTILE: return y > f ? 0.5 * p : 0.5 * (p - 1);      // Quantile :432-433 (p == _quantileAlpha)
     default: return y - linkInv(family, f);
   }
+}
+// Quantile.Histo.findQuantile + computeQuantile / linearInterpolate (h2o-core/src/main/java/hex/quantile/Quantile.java:267-350) for
+// unit weights and CombineMethod.INTERPOLATE. The reference refines a 1024-bin histogram until the bins that hold rows r2 = (long)
+// (prob (n - 1)) and r2 + 1 are constant; what it then has are the two order statistics, which do not depend on how they were
+// found -- here the values are sorted. `v` is reordered.
+inline double quantileInterpolated(std::vector<double>& v, double prob) {
+  const double nrows = (double)v.size();
+  if (v.empty()) return NAN;
+  std::sort(v.begin(), v.end());
+  const double p2 = prob * (nrows - 1);
+  const long long r2 = (long long)p2;
+  const double lo = v[(size_t)r2];
+  if (r2 + 1 >= (long long)v.size()) return lo;
+  const double hi = v[(size_t)r2 + 1];
+  if (lo == hi) return lo;                                      // computeQuantile :331
+  const double row = (double)r2;
+  const double plo = (row + 0) / (nrows - 1), phi = (row + 1) / (nrows - 1);  // linearInterpolate :344-350
+  return lo + (hi - lo) * (prob - plo) / (phi - plo);
 }
 inline double initFNum(int family, double w, double o, double y, double p = 1.5) {
   switch (family) {
@@ -1501,6 +1521,14 @@ struct GBM {
     mtry_per_tree = std::max(1, j_d2i(parms.col_sample_rate_per_tree * ncols));
     mtry = std::max(1, j_d2i(parms.col_sample_rate * parms.col_sample_rate_per_tree * ncols));
     double initialPrediction = nclass > 2 ? 0 : getInitialValue();
+    if (parms.family == LAPLACE || parms.family == QUANTILE) {  // getInitialValueQuantile :272-276, 355-381: quantile of y - offset
+      if (!fr.w.empty()) throw std::runtime_error("oracle: laplace / quantile with observation weights is not restated");
+      std::vector<double> v;
+      for (int64_t row = 0; row < fr.nrows(); row++)
+        if (!std::isnan(fr.y[row])) v.push_back(fr.y[row] - (fr.off.empty() ? 0 : fr.off[row]));
+      initialPrediction = dist::quantileInterpolated(v, parms.family == LAPLACE ? 0.5 : parms.tweedie_power);
+      if (std::isnan(initialPrediction)) initialPrediction = 0;
+    }
     model.init_f = initialPrediction;
     if (initialPrediction != 0.0) std::fill(tree_[0].begin(), tree_[0].end(), initialPrediction);
     // MarkDecidedRows :288-349
@@ -1696,7 +1724,29 @@ struct GBM {
     // fitBestConstants :813-847
     double m1class = (nclass > 1 && parms.family == MULTINOMIAL) ? (double)(nclass - 1) / nclass : 1.0;
     double eff_lr = parms.learn_rate * std::pow(parms.learn_rate_annealing, (double)(ntrees_built - 1));  // :725-727
-    for (int k = 0; k < K; k++) {
+    if (parms.family == LAPLACE || parms.family == QUANTILE) {
+      // fitBestConstantsQuantile :522-527, 729-751: StratifiedQuantilesTask over diff = y - (f + o) (ComputeDiff :1132-1147) with the
+      // NIDs column as strata -- every row that GammaPass moved onto a leaf takes part, out-of-bag rows included
+      DTree& tree = *ktrees[0];
+      const double prob = parms.family == LAPLACE ? 0.5 : parms.tweedie_power;
+      const int nleaf = tree.len() - leaves[0];
+      std::vector<std::vector<double>> diffs((size_t)std::max(nleaf, 0));
+      if (tree.node(0).kind != LEAF)
+        for (int64_t row = 0; row < fr.nrows(); row++) {
+          const int nid = nids_[0][row];
+          if (nid < leaves[0] || std::isnan(fr.y[row])) continue;
+          diffs[(size_t)(nid - leaves[0])].push_back(fr.y[row] - (tree_[0][row] + (fr.off.empty() ? 0 : fr.off[row])));
+        }
+      for (int i = 0; i < nleaf; i++) {
+        const double q = dist::quantileInterpolated(diffs[(size_t)i], prob);
+        if (std::isnan(q)) continue;  // no active rows for this NID
+        double val = eff_lr * q;
+        if (val > parms.max_abs_leafnode_pred) val = parms.max_abs_leafnode_pred;
+        if (val < -parms.max_abs_leafnode_pred) val = -parms.max_abs_leafnode_pred;
+        tree.node(leaves[0] + i)._pred = (float)val;
+      }
+    }
+    for (int k = 0; k < K && parms.family != LAPLACE && parms.family != QUANTILE; k++) {
       DTree& tree = *ktrees[k];
       for (int i = 0; i < tree.len() - leaves[k]; i++) {
         Node& leafNode = tree.node(leaves[k] + i);

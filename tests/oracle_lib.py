@@ -47,7 +47,7 @@ class OrcHistDesc(C.Structure):
                 ("min2", C.c_double), ("maxIn", C.c_double)]
 
 
-GAUSSIAN, BERNOULLI, MULTINOMIAL, POISSON, GAMMA, TWEEDIE = 0, 1, 2, 3, 4, 5
+GAUSSIAN, BERNOULLI, MULTINOMIAL, POISSON, GAMMA, TWEEDIE, LAPLACE, QUANTILE = 0, 1, 2, 3, 4, 5, 6, 7
 HT_UniformAdaptive, HT_Random, HT_QuantilesGlobal, HT_UniformRobust = 0, 1, 2, 3
 NA_None, NAvsREST, NALeft, NARight, Left, Right = 0, 1, 2, 3, 4, 5
 
@@ -66,6 +66,9 @@ def default_params(**kw):
                 for i, r in enumerate(v):
                     p.sample_rate_per_class[i] = r
             continue
+        if k == "quantile_alpha":  # (one slot for the family's parameter)
+            p.tweedie_power = v
+            continue
         setattr(p, k, v)
     return p
 
@@ -82,7 +85,7 @@ def lib():
     if _lib is not None:
         return _lib
     src_m = max(os.path.getmtime(os.path.join(ORACLE_DIR, f)) for f in ("h2o_tree_oracle.hpp", "h2o_chunk_oracle.hpp", "h2o_compress_oracle.hpp",
-                                                                         "h2o_auc_oracle.hpp", "oracle_capi.cpp"))
+                                                                         "h2o_auc_oracle.hpp", "h2o_metrics_oracle.hpp", "oracle_capi.cpp"))
     if not os.path.exists(_SO) or os.path.getmtime(_SO) < src_m:
         build()
     L = C.CDLL(_SO)

@@ -14,7 +14,7 @@ def _run_both(X, y, cats=None, w=None, off=None, capture=True, **kw):
     P = h2ot_lib.pkg()
     dist = kw.pop("distribution", "bernoulli")
     nclass = kw.pop("nclass", 2 if dist == "bernoulli" else 1)
-    fam = {"gaussian": O.GAUSSIAN, "bernoulli": O.BERNOULLI, "multinomial": O.MULTINOMIAL}[dist]
+    fam = {"gaussian": O.GAUSSIAN, "bernoulli": O.BERNOULLI, "multinomial": O.MULTINOMIAL, "laplace": O.LAPLACE, "quantile": O.QUANTILE}[dist]
     ht = kw.pop("histogram_type", "AUTO")
     op = O.default_params(family=fam, nclass=nclass, histogram_type={"AUTO": 0, "Random": 1}[ht], **kw)
     kw["histogram_type"] = ht
@@ -564,4 +564,29 @@ def test_timer_modes():
     gm.train(2)
     s3 = gm.engine().stats()
     assert s3.ms_hist == s2.ms_hist and s3.hist_launches == 3 * s.hist_launches and s3.launches > s2.launches
+    gm.close()
+
+
+@pytest.mark.parametrize("dist,alpha", [("laplace", 0.5), ("quantile", 0.8), ("quantile", 0.25)])
+def test_laplace_and_quantile_distributions(dist, alpha):
+    """laplace / quantile GBM (H/DistributionFactory.java:406-434). The trees are grown on sign-like gradients,
+    the initial prediction is the median / alpha-quantile of the response (GBM.getInitialValueQuantile, T/gbm/GBM.java:355-381) and
+    every leaf is fitted with the quantile of its rows' residuals (fitBestConstantsQuantile :729-751 over
+    Quantile.StratifiedQuantilesTask): h2ot_leaf_quantiles sorts (leaf, residual) on the device and interpolates like
+    Quantile.linearInterpolate. Level by level against the oracle, with row sampling (out-of-bag rows take part in the leaf
+    quantiles, as in the reference)."""
+    X, y, cats = h2ot_lib.make_frame(n=30000, c=6, seed=17)
+    rng = np.random.default_rng(4)
+    y = (np.nan_to_num(X[:, 0]) * 1.5 - np.nan_to_num(X[:, 1]) + rng.standard_t(3, size=len(X))).astype(np.float32).astype(np.float64)
+    y[::97] = NaN
+    kw = dict(distribution=dist, nclass=1, ntrees=6, max_depth=4, nbins=20, seed=5, sample_rate=0.8)
+    if dist == "quantile":
+        kw["quantile_alpha"] = alpha
+    gm, om = _run_both(X, y, cats, capture=True, **kw)
+    h2ot_lib.compare_models(gm, om, ybound=1.0)
+    ok = ~np.isnan(y)
+    F = gm.predictions()
+    # the fitted quantile: about alpha of the training rows lie below the prediction
+    below = np.mean(y[ok] < F[ok])
+    assert abs(below - alpha) < 0.08, below
     gm.close()

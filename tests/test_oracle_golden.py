@@ -374,3 +374,22 @@ def test_splits_bin_and_binAt_agree_for_every_histogram_type(histo_type):
             if first[i] < N and b[first[i]] == i:  # Random can leave a bin empty (two equal split points)
                 assert abs(x[first[i]] - l2[i]) <= 1e-5, (i, x[first[i]], l2[i])
         assert h.bin(1.0) == 0 and h.bin(float("nan")) == 13 and h.bin(float("inf")) == 12
+
+
+@pytest.mark.parametrize("fam,alpha", [(O.LAPLACE, 0.5), (O.QUANTILE, 0.8), (O.QUANTILE, 0.1)])
+def test_quantile_families_initial_prediction_is_the_type7_quantile(fam, alpha):
+    """GBM.getInitialValueQuantile (T/gbm/GBM.java:355-381) through Quantile's INTERPOLATE method
+    (h2o-core/src/main/java/hex/quantile/Quantile.java:330-350): the order statistics around row prob (n - 1), interpolated linearly
+    -- numpy's default ("linear", Hyndman-Fan type 7) is the same definition, evaluated with another formula (a few ulps apart)."""
+    import h2ot_lib
+    X, y, cats = h2ot_lib.make_frame(n=5001, c=4, seed=3)
+    y = (np.nan_to_num(X[:, 0]) + np.random.default_rng(1).standard_t(3, size=len(X))).astype(np.float32).astype(np.float64)
+    y[::13] = np.nan
+    p = O.default_params(family=fam, nclass=1, ntrees=1, max_depth=2, nbins=20, seed=5, quantile_alpha=alpha)
+    m = O.Model(O.Frame(X, y, cat_cards=cats), p, capture=False)
+    want = np.quantile(y[~np.isnan(y)], alpha)
+    assert abs(m.init_f - want) <= 1e-12 * max(1.0, abs(want))
+    # and the leaves are fitted towards that quantile of the residuals: after one tree about alpha of the rows lie below the prediction
+    F = m.F()
+    ok = ~np.isnan(y)
+    assert abs(np.mean(y[ok] < F[ok]) - alpha) < 0.1
